@@ -1,0 +1,450 @@
+"""CPU ORACLE — test infrastructure only, never the product path.
+
+A plain numpy / torch-fp32 restatement of the reference's retrieval hot path
+(Martin1007Wang/EVI-RAG). Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs may import this module, and only as the checker or
+as the timed CPU baseline. Nothing under ``evi-rag_b200/`` imports it.
+
+Pinning: the reference ships no tests, golden vectors or fixtures. This
+restatement is pinned against the reference's own code imported in the build container
+(``oracle/make_golden.py`` -> ``tests/golden/*.npz``; ``tests/test_oracle_golden.py`` re-checks
+the oracle against those vectors on every run). The one third-party piece, torch_geometric's
+``MessagePassing(aggr="mean")`` (not vendored, not version-pinned by the reference:
+absent from requirements.txt), is restated from its published semantics in
+``dde_node_features`` — parity for that piece is "unpinned" (see DESIGN.md).
+
+Each function cites the reference file:line it follows.
+"""
+from __future__ import annotations
+
+from collections import deque
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+LN_EPS = 1e-5  # nn.LayerNorm default, retriever.py:162,177
+
+
+# ----------------------------------------------------------------------------------------------
+# a1: edge -> question segmentation                        src/utils/graph_utils.py:49-104
+# ----------------------------------------------------------------------------------------------
+def compute_edge_batch(edge_index: np.ndarray, ptr: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """``bucketize(edge_index[0], ptr[1:], right=True)`` + validation + ``edge_ptr`` cumsum."""
+    edge_index = np.asarray(edge_index, dtype=np.int64)
+    ptr = np.asarray(ptr, dtype=np.int64)
+    num_graphs = ptr.shape[0] - 1
+    if edge_index.ndim != 2 or edge_index.shape[0] != 2:
+        raise ValueError(f"edge_index must have shape [2, E], got {tuple(edge_index.shape)}")
+    eb = np.searchsorted(ptr[1:], edge_index[0], side="right").astype(np.int64)
+    tb = np.searchsorted(ptr[1:], edge_index[1], side="right").astype(np.int64)
+    if eb.size > 0:
+        if eb.min() < 0 or eb.max() >= num_graphs:
+            raise ValueError("edge_batch contains out-of-range indices")
+    if not np.array_equal(eb, tb):
+        raise ValueError("edge_index crosses graph boundaries; head/tail graph assignments differ.")
+    if eb.size > 1 and not bool(np.all(eb[:-1] <= eb[1:])):
+        raise ValueError("edge_batch is not non-decreasing along the flattened edge list")
+    counts = np.bincount(eb, minlength=num_graphs).astype(np.int64)
+    edge_ptr = np.zeros(num_graphs + 1, dtype=np.int64)
+    np.cumsum(counts, out=edge_ptr[1:])
+    return eb, edge_ptr
+
+
+# ----------------------------------------------------------------------------------------------
+# a3: DDE = rounds of directional mean propagation        src/models/components/graph.py:13-74
+# ----------------------------------------------------------------------------------------------
+def _mean_propagate(x: torch.Tensor, src: torch.Tensor, dst: torch.Tensor) -> torch.Tensor:
+    """PyG ``MessagePassing(aggr='mean', flow='source_to_target')``: messages go
+    ``edge_index[0] -> edge_index[1]``; mean over incoming edges with multiplicity; nodes with no
+    incoming edge get 0 (graph.py:16-23 + torch_geometric semantics)."""
+    out = torch.zeros_like(x)
+    out.index_add_(0, dst, x[src])
+    deg = torch.zeros(x.size(0), dtype=x.dtype)
+    deg.index_add_(0, dst, torch.ones(dst.numel(), dtype=x.dtype))
+    return out / deg.clamp(min=1).unsqueeze(-1)
+
+
+def dde_node_features(
+    topic_one_hot: torch.Tensor,
+    edge_index: torch.Tensor,
+    num_rounds: int = 2,
+    num_reverse_rounds: int = 2,
+    num_topics: int = 2,
+) -> torch.Tensor:
+    """Node structure features ``[N, C*(1+R_f+R_r)]`` laid out per topic class
+    ``[c0:(x0,f1..,r1..), c1:(...)]`` (retriever.py:519-553, graph.py:41-74)."""
+    x0 = topic_one_hot.to(torch.float32)[:, :num_topics]
+    feats = [x0]
+    h = x0
+    for _ in range(num_rounds):
+        h = _mean_propagate(h, edge_index[0], edge_index[1])
+        feats.append(h)
+    h = x0
+    for _ in range(num_reverse_rounds):
+        h = _mean_propagate(h, edge_index[1], edge_index[0])  # edge_index.flip(0), graph.py:47-48
+        feats.append(h)
+    stacked = torch.stack(feats, dim=-1)
+    return stacked.reshape(stacked.size(0), -1)
+
+
+# ----------------------------------------------------------------------------------------------
+# a4-a6: the scorer                                        src/models/components/retriever.py
+# ----------------------------------------------------------------------------------------------
+@dataclass
+class OracleOutput:
+    logits: torch.Tensor
+    query_ids: torch.Tensor
+    logits_fwd: Optional[torch.Tensor]
+    logits_bwd: Optional[torch.Tensor]
+    edge_embeddings: Optional[torch.Tensor]
+
+
+def _lin(x, sd, name):
+    return F.linear(x, sd[f"{name}.weight"], sd[f"{name}.bias"])
+
+
+def _score_direction(sd, q, h, r, t, s20, want_features: bool):
+    """``_score_edges`` + ``_encode_structure`` (retriever.py:453-495)."""
+    r_ctx = r * torch.sigmoid(_lin(q, sd, "q_gate.0")) + torch.tanh(_lin(q, sd, "q_bias.0"))
+    sc = F.gelu(
+        F.layer_norm(_lin(s20, sd, "struct_proj.0"), (sd["struct_proj.1.weight"].numel(),),
+                     sd["struct_proj.1.weight"], sd["struct_proj.1.bias"], LN_EPS)
+    )
+    nav = torch.sigmoid(_lin(sc, sd, "struct_gate_net.0"))
+    iv = h * r_ctx * t * nav
+    err = h + r_ctx - t
+    dist = -torch.norm(err, p=2, dim=-1, keepdim=True)
+    comb = torch.cat([iv, sc, err, dist], dim=-1)
+    z = _lin(comb, sd, "state_net.0")
+    g = F.gelu(F.layer_norm(z, (z.size(-1),), sd["state_net.1.weight"], sd["state_net.1.bias"], LN_EPS))
+    feat = _lin(g, sd, "state_net.4")
+    logit = _lin(feat, sd, "score_head").squeeze(-1)
+    return logit, (feat if want_features else None)
+
+
+@torch.no_grad()
+def retriever_forward(
+    sd: Dict[str, torch.Tensor],
+    *,
+    edge_index: torch.Tensor,
+    ptr: torch.Tensor,
+    question_emb: torch.Tensor,
+    node_embeddings: torch.Tensor,
+    node_embedding_ids: torch.Tensor,
+    edge_embeddings: torch.Tensor,
+    topic_one_hot: torch.Tensor,
+    direction_mode: str = "bidirectional",
+    num_rounds: int = 2,
+    num_reverse_rounds: int = 2,
+    want_features: bool = False,
+    edge_chunk: int = 32768,
+) -> OracleOutput:
+    """``Retriever._forward_impl`` in eval mode (retriever.py:195-289), fp32, same op order as the
+    reference (per-edge relation / gate / bias projections included). Edges are processed in
+    chunks only to bound memory; per-edge math is independent so results do not change."""
+    sd = {k: v.to(torch.float32) if v.is_floating_point() else v for k, v in sd.items()}
+    head, tail = edge_index[0].long(), edge_index[1].long()
+    E = head.numel()
+    eb, _ = compute_edge_batch(edge_index.numpy(), ptr.numpy())
+    query_ids = torch.from_numpy(eb)
+    if E == 0:
+        z = torch.empty(0)
+        return OracleOutput(z, query_ids, z, z, torch.empty(0, sd["state_net.4.weight"].size(0)))
+    q_proj = torch.tanh(_lin(question_emb.float(), sd, "query_proj.network.0"))
+    node_repr = torch.tanh(_lin(node_embeddings.float(), sd, "entity_proj.network.0"))
+    non_text = torch.tanh(_lin(sd["non_text_entity_emb.weight"], sd, "entity_proj.network.0"))[0]
+    mask = node_embedding_ids.long() == 0  # retriever.py:499-506
+    if bool(mask.any()):
+        node_repr = torch.where(mask.unsqueeze(-1), non_text.unsqueeze(0), node_repr)
+    ns = dde_node_features(topic_one_hot, edge_index.long(), num_rounds, num_reverse_rounds)
+
+    lf_all, lb_all, lo_all, fe_all = [], [], [], []
+    for s in range(0, E, edge_chunk):
+        sl = slice(s, min(E, s + edge_chunk))
+        hh, tt = head[sl], tail[sl]
+        q = q_proj[query_ids[sl]]
+        h, t = node_repr[hh], node_repr[tt]
+        r = torch.tanh(_lin(edge_embeddings[sl].float(), sd, "relation_proj.network.0"))
+        s_f = torch.cat([ns[hh], ns[tt]], dim=-1)  # retriever.py:509-517
+        s_b = torch.cat([ns[tt], ns[hh]], dim=-1)
+        lf = lb = ff = fb = None
+        if direction_mode in ("forward", "bidirectional"):
+            lf, ff = _score_direction(sd, q, h, r, t, s_f, want_features)
+        if direction_mode in ("backward", "bidirectional"):
+            lb, fb = _score_direction(sd, q, t, r, h, s_b, want_features)
+        if direction_mode == "bidirectional":  # retriever.py:369-381
+            st = torch.stack([lf, lb], dim=0)
+            w = torch.softmax(st, dim=0)
+            lo = (w * st).sum(dim=0)
+            fe = w[0].unsqueeze(-1) * ff + w[1].unsqueeze(-1) * fb if want_features else None
+        elif direction_mode == "forward":
+            lo, fe = lf, ff
+        else:
+            lo, fe = lb, fb
+        lo_all.append(lo)
+        lf_all.append(lf)
+        lb_all.append(lb)
+        fe_all.append(fe)
+    cat = lambda xs: torch.cat(xs) if xs[0] is not None else None
+    return OracleOutput(cat(lo_all), query_ids, cat(lf_all), cat(lb_all), cat(fe_all))
+
+
+# ----------------------------------------------------------------------------------------------
+# a10-a12: ragged top-k
+# ----------------------------------------------------------------------------------------------
+def segmented_topk(scores: np.ndarray, edge_ptr: np.ndarray, k: int) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """Per question: ``k_top = min(E_q, k)``; ``topk(scores_q, k_top, largest, sorted)``
+    (retriever_metrics.py:134-157, retriever_topk_edge_writer.py:295-303). Tie rule = the
+    stable-argsort rule of g_agent_builder.py:640-652: descending score, ascending index.
+    Returns ``values [B,k] f32`` (pad -inf), ``indices [B,k] i32`` (question-local, pad -1),
+    ``counts [B] i32``. NaN scores order as torch.topk does: NaN is the largest value."""
+    scores = np.asarray(scores, dtype=np.float32)
+    B = len(edge_ptr) - 1
+    vals = np.full((B, k), -np.inf, dtype=np.float32)
+    idx = np.full((B, k), -1, dtype=np.int32)
+    cnt = np.zeros(B, dtype=np.int32)
+    for b in range(B):
+        s = scores[int(edge_ptr[b]) : int(edge_ptr[b + 1])]
+        kt = min(len(s), k)
+        cnt[b] = kt
+        if kt == 0:
+            continue
+        key = np.where(np.isnan(s), np.float32(np.inf), s)
+        nan_first = np.isnan(s)
+        order = np.lexsort((np.arange(len(s)), -key.astype(np.float64), ~nan_first))[:kt]
+        vals[b, :kt] = s[order]
+        idx[b, :kt] = order
+    return vals, idx, cnt
+
+
+def sigmoid_f32(x: np.ndarray) -> np.ndarray:
+    """``torch.sigmoid`` on fp32 (retriever_topk_edge_writer.py:203)."""
+    return torch.sigmoid(torch.from_numpy(np.asarray(x, dtype=np.float32))).numpy()
+
+
+def writer_payload(
+    logits, logits_fwd, logits_bwd, edge_index, edge_attr, labels, node_global_ids, edge_ptr, k
+):
+    """Writer-flavour selection (retriever_topk_edge_writer.py:201-248, 295-328): sigmoid scores,
+    per-question top-k, gathered ``head/rel/tail`` global ids, label, fwd/bwd logits; rank = pos+1."""
+    scores = sigmoid_f32(logits)
+    vals, idx, cnt = segmented_topk(scores, edge_ptr, k)
+    B = len(edge_ptr) - 1
+    out = {
+        "score": vals,
+        "index": idx,
+        "count": cnt,
+        "head_id": np.full((B, k), -1, np.int64),
+        "tail_id": np.full((B, k), -1, np.int64),
+        "relation_id": np.full((B, k), -1, np.int64),
+        "label": np.zeros((B, k), np.float32),
+        "logit_fwd": np.zeros((B, k), np.float32),
+        "logit_bwd": np.zeros((B, k), np.float32),
+    }
+    for b in range(B):
+        kt = int(cnt[b])
+        g = idx[b, :kt].astype(np.int64) + int(edge_ptr[b])
+        out["head_id"][b, :kt] = node_global_ids[edge_index[0, g]]
+        out["tail_id"][b, :kt] = node_global_ids[edge_index[1, g]]
+        out["relation_id"][b, :kt] = edge_attr[g]
+        out["label"][b, :kt] = labels[g]
+        out["logit_fwd"][b, :kt] = logits_fwd[g]
+        out["logit_bwd"][b, :kt] = logits_bwd[g]
+    return out
+
+
+def recall_at_k(scores, labels, edge_ptr, k_values: Sequence[int]) -> Dict[int, float]:
+    """``EdgeRecallAtK`` (retriever_metrics.py:117-170): mean over questions of
+    hits@k / max(pos, eps); questions with zero edges are skipped, zero positives count as 0."""
+    max_k = max(k_values)
+    _, idx, cnt = segmented_topk(scores, edge_ptr, max_k)
+    sums = {int(k): 0.0 for k in k_values}
+    n = 0
+    for b in range(len(edge_ptr) - 1):
+        kt = int(cnt[b])
+        lab = np.asarray(labels[int(edge_ptr[b]) : int(edge_ptr[b + 1])], dtype=np.float32)
+        if lab.size == 0:
+            continue
+        n += 1
+        top = lab[idx[b, :kt]]
+        cum = np.cumsum(top)
+        denom = max(float(lab.sum()), 1e-6)
+        for k in k_values:
+            ke = min(int(k), kt)
+            sums[int(k)] += float(cum[ke - 1] / denom) if ke > 0 else 0.0
+    return {k: (v / n if n else 0.0) for k, v in sums.items()}
+
+
+# ----------------------------------------------------------------------------------------------
+# a13-a15: BFS hop distances and shortest-path edge labels  scripts/build_retrieval_pipeline.py
+# ----------------------------------------------------------------------------------------------
+DIST_UNREACHABLE = -1  # build_retrieval_pipeline.py:360
+
+
+def build_undirected_adjacency(num_nodes: int, edge_src, edge_dst) -> List[List[int]]:
+    """build_retrieval_pipeline.py:570-586: both directions, self loop once, drop out-of-range."""
+    adj: List[List[int]] = [[] for _ in range(num_nodes)]
+    for u, v in zip(edge_src, edge_dst):
+        u, v = int(u), int(v)
+        if u < 0 or v < 0 or u >= num_nodes or v >= num_nodes:
+            continue
+        adj[u].append(v)
+        if u != v:
+            adj[v].append(u)
+    for nb in adj:
+        nb.sort()
+    return adj
+
+
+def build_directed_adjacency(num_nodes: int, edge_src, edge_dst) -> List[List[int]]:
+    """build_retrieval_pipeline.py:589-603."""
+    adj: List[List[int]] = [[] for _ in range(num_nodes)]
+    for u, v in zip(edge_src, edge_dst):
+        u, v = int(u), int(v)
+        if u < 0 or v < 0 or u >= num_nodes or v >= num_nodes:
+            continue
+        adj[u].append(v)
+    for nb in adj:
+        nb.sort()
+    return adj
+
+
+def bfs_dist(num_nodes: int, adjacency, sources) -> List[int]:
+    """build_retrieval_pipeline.py:610-631: multi-source BFS, unreachable = -1."""
+    dist = [DIST_UNREACHABLE] * num_nodes
+    if num_nodes <= 0:
+        return dist
+    dq: deque = deque()
+    for s in sources:
+        s = int(s)
+        if 0 <= s < num_nodes and dist[s] < 0:
+            dist[s] = 0
+            dq.append(s)
+    while dq:
+        u = dq.popleft()
+        du = dist[u] + 1
+        for v in adjacency[u]:
+            if dist[v] >= 0:
+                continue
+            dist[v] = du
+            dq.append(v)
+    return dist
+
+
+def bfs_dist_np(num_nodes: int, edge_src, edge_dst, sources, *, directed: bool = False,
+                max_depth: int = -1) -> np.ndarray:
+    """Level-synchronous numpy BFS: same distances as ``bfs_dist`` over
+    ``build_(un)directed_adjacency`` (hop distance does not depend on visiting order).
+    ``max_depth >= 0`` caps the search (dist > cap -> -1; SURVEY.md §8d config 2 variant)."""
+    dist = np.full(num_nodes, DIST_UNREACHABLE, dtype=np.int32)
+    if num_nodes <= 0:
+        return dist
+    u = np.asarray(edge_src, dtype=np.int64)
+    v = np.asarray(edge_dst, dtype=np.int64)
+    ok = (u >= 0) & (v >= 0) & (u < num_nodes) & (v < num_nodes)
+    u, v = u[ok], v[ok]
+    if not directed:
+        u, v = np.concatenate([u, v]), np.concatenate([v, u])
+    src = np.asarray([int(s) for s in sources if 0 <= int(s) < num_nodes], dtype=np.int64)
+    dist[src] = 0
+    frontier = np.zeros(num_nodes, dtype=bool)
+    frontier[src] = True
+    level = 0
+    while frontier.any() and (max_depth < 0 or level < max_depth):
+        level += 1
+        cand = v[frontier[u]]
+        nxt = np.zeros(num_nodes, dtype=bool)
+        nxt[cand] = True
+        nxt &= dist < 0
+        dist[nxt] = level
+        frontier = nxt
+    return dist
+
+
+def shortest_path_union_mask_by_pair(num_nodes, edge_src, edge_dst, sources, targets, *, directed=False):
+    """build_retrieval_pipeline.py:691-752 (undirected) and :755-815 (qa_directed). One BFS per
+    unique in-range seed and answer; for each reachable (s, a) pair the edges lying on some
+    shortest path; returns ``(mask, pair_start, pair_answer, pair_edge_local_ids,
+    pair_edge_counts, pair_shortest_lengths)`` as python lists like the reference."""
+    num_edges = len(edge_src)
+    empty = ([False] * num_edges, [], [], [], [], [])
+    if num_nodes <= 0 or num_edges == 0 or len(sources) == 0 or len(targets) == 0:
+        return empty
+    es = np.asarray(edge_src, dtype=np.int64)
+    ed = np.asarray(edge_dst, dtype=np.int64)
+    valid = np.nonzero((es >= 0) & (ed >= 0) & (es < num_nodes) & (ed < num_nodes))[0]
+    if valid.size == 0:
+        return empty
+    esv, edv = es[valid], ed[valid]
+    starts = sorted({int(s) for s in sources if 0 <= int(s) < num_nodes})
+    answers = sorted({int(t) for t in targets if 0 <= int(t) < num_nodes})
+    if not starts or not answers:
+        return empty
+    if directed:
+        adj = build_directed_adjacency(num_nodes, edge_src, edge_dst)
+        radj = build_directed_adjacency(num_nodes, edge_dst, edge_src)
+    else:
+        adj = radj = build_undirected_adjacency(num_nodes, edge_src, edge_dst)
+    d_s = {s: np.asarray(bfs_dist(num_nodes, adj, [s]), dtype=np.int64) for s in starts}
+    d_a = {a: np.asarray(bfs_dist(num_nodes, radj, [a]), dtype=np.int64) for a in answers}
+    mask = np.zeros(num_edges, dtype=bool)
+    p_s, p_a, p_ids, p_cnt, p_len = [], [], [], [], []
+    for s in starts:
+        ds = d_s[s]
+        for a in answers:
+            da = d_a[a]
+            dsa = int(ds[a])
+            if dsa < 0:
+                continue
+            p_s.append(s)
+            p_a.append(a)
+            p_len.append(dsa)
+            m = (ds[esv] >= 0) & (da[edv] >= 0) & (ds[esv] + 1 + da[edv] == dsa)
+            if not directed:
+                m |= (ds[edv] >= 0) & (da[esv] >= 0) & (ds[edv] + 1 + da[esv] == dsa)
+            ids = valid[np.nonzero(m)[0]]
+            if ids.size:
+                mask[ids] = True
+                p_ids.extend(ids.tolist())
+            p_cnt.append(int(ids.size))
+    return mask.tolist(), p_s, p_a, p_ids, p_cnt, p_len
+
+
+def has_connectivity(graph, seeds, answers, *, path_mode: str = "undirected") -> bool:
+    """build_retrieval_pipeline.py:946-979: first-seen local ids, multi-source BFS, any answer reached."""
+    if not graph or not seeds or not answers:
+        return False
+    if path_mode not in ("undirected", "qa_directed"):
+        raise ValueError(f"Unsupported path_mode: {path_mode}. Expected one of ('undirected', 'qa_directed').")
+    node_index: Dict[str, int] = {}
+    es, ed = [], []
+    for h, _, t in graph:
+        es.append(node_index.setdefault(h, len(node_index)))
+        ed.append(node_index.setdefault(t, len(node_index)))
+    s_ids = [node_index[s] for s in seeds if s in node_index]
+    a_ids = [node_index[a] for a in answers if a in node_index]
+    if not s_ids or not a_ids:
+        return False
+    n = len(node_index)
+    adj = build_directed_adjacency(n, es, ed) if path_mode == "qa_directed" else build_undirected_adjacency(n, es, ed)
+    dist = bfs_dist(n, adj, s_ids)
+    return any(dist[a] >= 0 for a in a_ids)
+
+
+def labels_for_batch(qb, *, directed: bool = False) -> np.ndarray:
+    """Per-question shortest-path-union positive mask over a ragged batch (the ``labels`` field
+    the writer reads, built by build_graph via a14). ``qb`` is a synthetic ``QuestionBatch``."""
+    labels = np.zeros(qb.num_edges, dtype=np.float32)
+    for b in range(qb.num_graphs):
+        n0, n1 = int(qb.ptr[b]), int(qb.ptr[b + 1])
+        e0, e1 = int(qb.edge_ptr[b]), int(qb.edge_ptr[b + 1])
+        s = qb.q_local_indices[int(qb.q_ptr[b]) : int(qb.q_ptr[b + 1])] - n0
+        a = qb.a_local_indices[int(qb.a_ptr[b]) : int(qb.a_ptr[b + 1])] - n0
+        m = shortest_path_union_mask_by_pair(
+            n1 - n0, qb.edge_index[0, e0:e1] - n0, qb.edge_index[1, e0:e1] - n0, s, a, directed=directed
+        )[0]
+        labels[e0:e1] = np.asarray(m, dtype=np.float32)
+    return labels

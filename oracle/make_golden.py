@@ -1,0 +1,229 @@
+"""Generate ``tests/golden/*.npz`` by running the UNMODIFIED reference (build container only).
+
+    python oracle/make_golden.py
+
+The reference has no golden vectors of its own, so these fixtures — outputs of the
+reference's code on seeded inputs — are what pins the oracle and, through it, the CUDA path.
+Weights are rebuilt from ``evi_rag_b200.weights.make_state_dict`` (numpy PCG64) and loaded into
+the reference module with ``load_state_dict(strict=True)``; only inputs that cannot be rebuilt
+cheaply and the reference outputs are stored.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from oracle.ref_shims import load_reference  # noqa: E402
+from evi_rag_b200.synthetic import generate_questions, tiny_spec  # noqa: E402
+from evi_rag_b200.weights import make_state_dict  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def small_batch(seed: int, dim: int, num_questions: int = 3, median_edges: int = 120):
+    spec = tiny_spec(num_questions, median_edges, seed=seed, num_relations=24, num_entities=300)
+    qb = generate_questions(spec, dim=dim)
+    rng = np.random.default_rng([seed, dim, 99])
+    ent = (rng.standard_normal((spec.num_entities + 1, dim)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((spec.num_relations, dim)) * 0.5).astype(np.float32)
+    return qb, ent, rel
+
+
+def as_ref_batch(qb, ent, rel, with_edge_batch: bool):
+    b = types.SimpleNamespace()
+    b.edge_index = torch.from_numpy(qb.edge_index)
+    b.ptr = torch.from_numpy(qb.ptr)
+    b.question_emb = torch.from_numpy(qb.question_emb)
+    b.node_embedding_ids = torch.from_numpy(qb.node_embedding_ids)
+    b.edge_attr = torch.from_numpy(qb.edge_attr)
+    b.node_embeddings = torch.from_numpy(ent[qb.node_embedding_ids])
+    b.edge_embeddings = torch.from_numpy(rel[qb.edge_attr])
+    b.topic_one_hot = torch.from_numpy(qb.topic_one_hot)
+    if with_edge_batch:
+        b.edge_batch = None
+    return b
+
+
+def golden_scorer(Retriever):
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    cases = [
+        dict(tag="d1024_init", dim=1024, seed=11, trained=False, rounds=(2, 2)),
+        dict(tag="d1024_trained", dim=1024, seed=12, trained=True, rounds=(2, 2)),
+        dict(tag="d64_r31", dim=64, seed=13, trained=True, rounds=(3, 1)),
+        dict(tag="d64_r04", dim=64, seed=14, trained=False, rounds=(0, 4)),
+    ]
+    for c in cases:
+        qb, ent, rel = small_batch(c["seed"], c["dim"])
+        sd = make_state_dict(c["seed"], c["dim"], c["dim"], *c["rounds"], trained_like=c["trained"])
+        out = {}
+        for mode in ("bidirectional", "forward", "backward"):
+            m = Retriever(
+                emb_dim=c["dim"], hidden_dim=c["dim"], direction_mode=mode,
+                dde_cfg={"num_rounds": c["rounds"][0], "num_reverse_rounds": c["rounds"][1]},
+            ).eval()
+            m.load_state_dict(sd, strict=True)
+            batch = as_ref_batch(qb, ent, rel, with_edge_batch=False)
+            with torch.no_grad():
+                o = m(batch)
+                ns = m._build_node_structure_features(
+                    batch, edge_index=batch.edge_index, num_nodes=qb.num_nodes
+                )
+            out[f"{mode}.logits"] = o.logits.numpy()
+            out[f"{mode}.query_ids"] = o.query_ids.numpy()
+            if o.logits_fwd is not None:
+                out[f"{mode}.logits_fwd"] = o.logits_fwd.numpy()
+            if o.logits_bwd is not None:
+                out[f"{mode}.logits_bwd"] = o.logits_bwd.numpy()
+            fe = o.edge_embeddings.numpy()
+            out[f"{mode}.feat_head"] = fe[:4].copy()
+            out[f"{mode}.feat_rowsum"] = fe.sum(axis=1)
+            out[f"{mode}.feat_rowabs"] = np.abs(fe).sum(axis=1)
+            out["node_struct"] = ns.numpy()
+        np.savez_compressed(
+            os.path.join(GOLDEN, f"scorer_{c['tag']}.npz"),
+            meta=np.array([c["dim"], c["seed"], int(c["trained"]), c["rounds"][0], c["rounds"][1]]),
+            edge_index=qb.edge_index, ptr=qb.ptr, edge_attr=qb.edge_attr,
+            node_embedding_ids=qb.node_embedding_ids, topic_one_hot=qb.topic_one_hot,
+            question_emb=qb.question_emb,
+            entity_rows=ent[qb.node_embedding_ids].astype(np.float32),
+            relation_table=rel,
+            **out,
+        )
+        print("scorer", c["tag"], "E=", qb.num_edges, "N=", qb.num_nodes)
+
+
+def golden_dde(Retriever):
+    """DDE corner cases: duplicate edges, self loops, isolated nodes, 3-column topic input."""
+    rng = np.random.default_rng(5)
+    n, e = 37, 140
+    src = rng.integers(0, n - 5, e)
+    dst = rng.integers(0, n - 5, e)
+    src[:10], dst[:10] = src[10:20], dst[10:20]  # duplicates
+    src[20:24] = dst[20:24]  # self loops
+    edge_index = np.stack([src, dst]).astype(np.int64)
+    topic = np.zeros((n, 3), dtype=np.float32)
+    seeds = np.array([0, 7, 19])
+    topic[:, 0] = 1
+    topic[seeds, 0] = 0
+    topic[seeds, 1] = 1
+    topic[:, 2] = rng.random(n)
+    res = {}
+    for rf, rr in [(2, 2), (4, 4), (1, 0), (0, 0)]:
+        m = Retriever(emb_dim=8, hidden_dim=8, dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr})
+        b = types.SimpleNamespace(topic_one_hot=torch.from_numpy(topic))
+        ns = m._build_node_structure_features(b, edge_index=torch.from_numpy(edge_index), num_nodes=n)
+        res[f"ns_{rf}_{rr}"] = ns.numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "dde.npz"), edge_index=edge_index, topic=topic, **res)
+    print("dde ok")
+
+
+def golden_edge_batch(ref_compute_edge_batch):
+    ptr = np.array([0, 5, 5, 12, 20], dtype=np.int64)  # includes an empty graph
+    rng = np.random.default_rng(3)
+    heads, tails = [], []
+    for g in range(4):
+        lo, hi = ptr[g], ptr[g + 1]
+        if hi > lo:
+            k = 9
+            heads.append(rng.integers(lo, hi, k))
+            tails.append(rng.integers(lo, hi, k))
+    ei = np.stack([np.concatenate(heads), np.concatenate(tails)]).astype(np.int64)
+    eb, ep = ref_compute_edge_batch(
+        torch.from_numpy(ei), node_ptr=torch.from_numpy(ptr), num_graphs=4, device=torch.device("cpu")
+    )
+    errors = {}
+    bad_cross = ei.copy()
+    bad_cross[1, 0] = 19
+    bad_order = ei[:, ::-1].copy()
+    bad_range = ei.copy()
+    bad_range[:, -1] = 25
+    for tag, arr in (("cross", bad_cross), ("order", bad_order), ("range", bad_range)):
+        try:
+            ref_compute_edge_batch(
+                torch.from_numpy(arr), node_ptr=torch.from_numpy(ptr), num_graphs=4, device=torch.device("cpu")
+            )
+            errors[tag] = ""
+        except ValueError as ex:
+            errors[tag] = str(ex)
+    np.savez_compressed(
+        os.path.join(GOLDEN, "edge_batch.npz"), edge_index=ei, ptr=ptr, edge_batch=eb.numpy(),
+        edge_ptr=ep.numpy(), bad_cross=bad_cross, bad_order=bad_order, bad_range=bad_range,
+        err_cross=np.array(errors["cross"]), err_order=np.array(errors["order"]),
+        err_range=np.array(errors["range"]),
+    )
+    print("edge_batch ok", {k: v[:60] for k, v in errors.items()})
+
+
+def golden_bfs(brp):
+    rng = np.random.default_rng(17)
+    store = {}
+    n_cases = 0
+    for ci, (n, e) in enumerate([(1, 0), (9, 6), (40, 70), (120, 400), (300, 500), (64, 2000)]):
+        src = rng.integers(-1, n + 1, e)  # includes out-of-range ids -1 and n
+        dst = rng.integers(-1, n + 1, e)
+        if e > 4:
+            src[:3] = dst[:3]  # self loops
+        sources = rng.integers(-1, n + 1, 4).tolist()
+        sources.append(sources[0])  # duplicate
+        targets = rng.integers(0, n, 3).tolist() + [n + 3]
+        adj_u = brp._build_undirected_adjacency(n, src.tolist(), dst.tolist())
+        adj_d = brp._build_directed_adjacency(n, src.tolist(), dst.tolist())
+        store[f"c{ci}_n"] = np.array(n)
+        store[f"c{ci}_src"] = src.astype(np.int64)
+        store[f"c{ci}_dst"] = dst.astype(np.int64)
+        store[f"c{ci}_sources"] = np.array(sources, dtype=np.int64)
+        store[f"c{ci}_targets"] = np.array(targets, dtype=np.int64)
+        store[f"c{ci}_dist_u"] = np.array(brp._bfs_dist(n, adj_u, sources), dtype=np.int64)
+        store[f"c{ci}_dist_d"] = np.array(brp._bfs_dist(n, adj_d, sources), dtype=np.int64)
+        for mode in ("undirected", "qa_directed"):
+            mask, ps, pa, ids, cnt, ln = brp._shortest_path_union_mask_by_pair_mode(
+                n, src.tolist(), dst.tolist(), sources, targets, path_mode=mode
+            )
+            pre = f"c{ci}_{mode}"
+            store[f"{pre}_mask"] = np.array(mask, dtype=bool)
+            store[f"{pre}_ps"] = np.array(ps, dtype=np.int64)
+            store[f"{pre}_pa"] = np.array(pa, dtype=np.int64)
+            store[f"{pre}_ids"] = np.array(ids, dtype=np.int64)
+            store[f"{pre}_cnt"] = np.array(cnt, dtype=np.int64)
+            store[f"{pre}_len"] = np.array(ln, dtype=np.int64)
+        n_cases += 1
+    store["num_cases"] = np.array(n_cases)
+    # has_connectivity on string triples
+    triples = [("a", "r1", "b"), ("b", "r2", "c"), ("d", "r3", "c"), ("e", "r1", "f")]
+    hc = []
+    for seeds, answers, mode in [
+        (["a"], ["c"], "undirected"), (["a"], ["d"], "undirected"), (["a"], ["d"], "qa_directed"),
+        (["a"], ["f"], "undirected"), (["zz"], ["c"], "undirected"), (["c"], ["a"], "qa_directed"),
+        (["a", "e"], ["f"], "qa_directed"),
+    ]:
+        hc.append(brp.has_connectivity(triples, seeds, answers, path_mode=mode))
+    store["has_connectivity"] = np.array(hc, dtype=bool)
+    np.savez_compressed(os.path.join(GOLDEN, "bfs.npz"), **store)
+    print("bfs ok", n_cases, hc)
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    Retriever, ref_ceb, brp, kind = load_reference()
+    print("reference loaded; mean-aggregation provider:", kind)
+    golden_edge_batch(ref_ceb)
+    golden_bfs(brp)
+    golden_dde(Retriever)
+    golden_scorer(Retriever)
+    with open(os.path.join(GOLDEN, "PROVENANCE.txt"), "w", encoding="utf-8") as f:
+        f.write(
+            "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"
+            f"torch {torch.__version__}, numpy {np.__version__}; mean-aggregation provider: {kind}\n"
+        )
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,122 @@
+"""The oracle against the golden vectors produced by the unmodified reference
+(oracle/make_golden.py). CPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import evi_oracle as orc
+from evi_rag_b200.weights import make_state_dict
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=False)
+
+
+@pytest.mark.parametrize("tag", ["d1024_init", "d1024_trained", "d64_r31", "d64_r04"])
+def test_scorer_matches_reference(golden_dir, tag):
+    g = _load(golden_dir, f"scorer_{tag}.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    sd = make_state_dict(seed, dim, dim, rf, rr, trained_like=bool(trained))
+    rel = torch.from_numpy(g["relation_table"])
+    for mode in ("bidirectional", "forward", "backward"):
+        out = orc.retriever_forward(
+            sd,
+            edge_index=torch.from_numpy(g["edge_index"]),
+            ptr=torch.from_numpy(g["ptr"]),
+            question_emb=torch.from_numpy(g["question_emb"]),
+            node_embeddings=torch.from_numpy(g["entity_rows"]),
+            node_embedding_ids=torch.from_numpy(g["node_embedding_ids"]),
+            edge_embeddings=rel[torch.from_numpy(g["edge_attr"])],
+            topic_one_hot=torch.from_numpy(g["topic_one_hot"]),
+            direction_mode=mode, num_rounds=rf, num_reverse_rounds=rr, want_features=True,
+        )
+        scale = max(1.0, float(np.abs(g[f"{mode}.logits"]).max()))
+        np.testing.assert_allclose(out.logits.numpy(), g[f"{mode}.logits"], atol=2e-5 * scale, rtol=0)
+        assert np.array_equal(out.query_ids.numpy(), g[f"{mode}.query_ids"])
+        if mode != "backward":
+            np.testing.assert_allclose(out.logits_fwd.numpy(), g[f"{mode}.logits_fwd"], atol=2e-5 * scale, rtol=0)
+        if mode != "forward":
+            np.testing.assert_allclose(out.logits_bwd.numpy(), g[f"{mode}.logits_bwd"], atol=2e-5 * scale, rtol=0)
+        fe = out.edge_embeddings.numpy()
+        np.testing.assert_allclose(fe[:4], g[f"{mode}.feat_head"], atol=2e-5, rtol=1e-5)
+        np.testing.assert_allclose(np.abs(fe).sum(1), g[f"{mode}.feat_rowabs"], rtol=1e-5)
+    ns = orc.dde_node_features(
+        torch.from_numpy(g["topic_one_hot"]), torch.from_numpy(g["edge_index"]), rf, rr
+    )
+    np.testing.assert_allclose(ns.numpy(), g["node_struct"], atol=1e-7, rtol=0)
+
+
+def test_dde_corner_cases(golden_dir):
+    g = _load(golden_dir, "dde.npz")
+    for rf, rr in [(2, 2), (4, 4), (1, 0), (0, 0)]:
+        ns = orc.dde_node_features(torch.from_numpy(g["topic"]), torch.from_numpy(g["edge_index"]), rf, rr)
+        np.testing.assert_allclose(ns.numpy(), g[f"ns_{rf}_{rr}"], atol=1e-7, rtol=0)
+
+
+def test_edge_batch(golden_dir):
+    g = _load(golden_dir, "edge_batch.npz")
+    eb, ep = orc.compute_edge_batch(g["edge_index"], g["ptr"])
+    assert np.array_equal(eb, g["edge_batch"]) and np.array_equal(ep, g["edge_ptr"])
+    for tag, frag in (("cross", "crosses graph boundaries"), ("order", "not non-decreasing"), ("range", "out-of-range")):
+        assert frag in str(g[f"err_{tag}"])  # what the reference said
+        with pytest.raises(ValueError, match=frag):
+            orc.compute_edge_batch(g[f"bad_{tag}"], g["ptr"])
+
+
+def test_bfs_and_shortest_path_labels(golden_dir):
+    g = _load(golden_dir, "bfs.npz")
+    for ci in range(int(g["num_cases"])):
+        n = int(g[f"c{ci}_n"])
+        src, dst = g[f"c{ci}_src"], g[f"c{ci}_dst"]
+        sources, targets = g[f"c{ci}_sources"].tolist(), g[f"c{ci}_targets"].tolist()
+        du = orc.bfs_dist(n, orc.build_undirected_adjacency(n, src, dst), sources)
+        dd = orc.bfs_dist(n, orc.build_directed_adjacency(n, src, dst), sources)
+        assert np.array_equal(np.array(du, dtype=np.int64), g[f"c{ci}_dist_u"])
+        assert np.array_equal(np.array(dd, dtype=np.int64), g[f"c{ci}_dist_d"])
+        assert np.array_equal(orc.bfs_dist_np(n, src, dst, sources), g[f"c{ci}_dist_u"])
+        assert np.array_equal(orc.bfs_dist_np(n, src, dst, sources, directed=True), g[f"c{ci}_dist_d"])
+        for mode in ("undirected", "qa_directed"):
+            res = orc.shortest_path_union_mask_by_pair(
+                n, src.tolist(), dst.tolist(), sources, targets, directed=(mode == "qa_directed")
+            )
+            pre = f"c{ci}_{mode}"
+            for got, key in zip(res, ("mask", "ps", "pa", "ids", "cnt", "len")):
+                assert np.array_equal(np.asarray(got), g[f"{pre}_{key}"]), (ci, mode, key)
+    triples = [("a", "r1", "b"), ("b", "r2", "c"), ("d", "r3", "c"), ("e", "r1", "f")]
+    cases = [
+        (["a"], ["c"], "undirected"), (["a"], ["d"], "undirected"), (["a"], ["d"], "qa_directed"),
+        (["a"], ["f"], "undirected"), (["zz"], ["c"], "undirected"), (["c"], ["a"], "qa_directed"),
+        (["a", "e"], ["f"], "qa_directed"),
+    ]
+    got = [orc.has_connectivity(triples, s, a, path_mode=m) for s, a, m in cases]
+    assert got == g["has_connectivity"].tolist()
+
+
+def test_bfs_depth_cap():
+    rng = np.random.default_rng(0)
+    n, e = 200, 300
+    src, dst = rng.integers(0, n, e), rng.integers(0, n, e)
+    full = orc.bfs_dist_np(n, src, dst, [0, 5])
+    cap = orc.bfs_dist_np(n, src, dst, [0, 5], max_depth=2)
+    assert np.array_equal(cap, np.where((full >= 0) & (full <= 2), full, -1))
+
+
+def test_segmented_topk_matches_torch_topk_and_stable_argsort():
+    rng = np.random.default_rng(1)
+    edge_ptr = np.array([0, 0, 7, 300, 301, 1500])
+    scores = rng.standard_normal(1500).astype(np.float32)
+    scores[10:40] = scores[10]  # ties
+    vals, idx, cnt = orc.segmented_topk(scores, edge_ptr, 100)
+    for b in range(5):
+        s = torch.from_numpy(scores[edge_ptr[b]:edge_ptr[b + 1]])
+        kt = min(len(s), 100)
+        assert cnt[b] == kt
+        if kt == 0:
+            continue
+        tv = torch.topk(s, kt, largest=True, sorted=True).values.numpy()
+        np.testing.assert_array_equal(vals[b, :kt], tv)
+        order = torch.argsort(s, descending=True, stable=True)[:kt].numpy()  # g_agent_builder.py:651
+        np.testing.assert_array_equal(idx[b, :kt], order)
+        assert (idx[b, kt:] == -1).all()
