@@ -1,0 +1,378 @@
+// Persistent warp-specialised tcgen05 GEMM for sm_100a:  D[M,N] = A[M,K] * B[N,K]^T  (+ epilogue)
+//
+//  * A and B are 16-bit (fp16 or bf16), K-major (row-major [rows, K]); nn.Linear weights are
+//    already [N, K], activations are [M, K]  ->  no transposes anywhere.
+//  * TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B) stages 128x64 A tiles and 256x64 B tiles into a
+//    4-deep shared-memory ring; one elected thread issues tcgen05.mma (M=128, N=256, K=16) into a
+//    double-buffered fp32 accumulator in TMEM (2 x 256 columns); four epilogue warps drain the
+//    accumulator with tcgen05.ld while the next tile's MMAs run.
+//  * Grid = min(#tiles, #SMs); tiles are walked n-fastest so the CTAs that share an A row-block
+//    run at the same time and hit it in L2.
+//
+// The epilogue is a functor: Epi::apply(params, row, col0, acc[32]) is called once per row per
+// 32-column chunk; Epi::finish_row(params, row, n_blk, state) once per row per tile.
+#pragma once
+
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched at run time)
+
+#include "common.cuh"
+
+namespace evi {
+namespace gemm {
+
+constexpr int BM = 128;
+constexpr int BN = 256;
+constexpr int BK = 64;  // 64 x 16-bit = 128 B = one swizzle row
+constexpr int STAGES = 4;
+constexpr int UMMA_K = 16;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KB
+constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int ACC_STAGES = 2;
+constexpr int TMEM_COLS = ACC_STAGES * BN;  // 512
+constexpr int NUM_THREADS = 256;            // warps 0-3: TMA / MMA / TMEM-alloc / spare, 4-7: epilogue
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct TileCoord {
+  int m_blk, n_blk;
+};
+
+template <int FMT, class Epi>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+            int M, int N, int K, typename Epi::Params ep) {
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles need 1024-byte alignment
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+
+  const int warp_idx = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_m_blocks = (M + BM - 1) / BM;
+  const int num_n_blocks = (N + BN - 1) / BN;
+  const int num_tiles = num_m_blocks * num_n_blocks;
+  const int num_k_blocks = (K + BK - 1) / BK;
+
+  if (warp_idx == 0 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp_idx == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < ACC_STAGES; ++i) {
+      mbar_init(&tmem_full_bar[i], 1);
+      mbar_init(&tmem_empty_bar[i], 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp_idx == 2) {
+    tmem_alloc(tmem_base_slot, TMEM_COLS);
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp_idx == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_blk = tile / num_n_blocks, n_blk = tile % num_n_blocks;
+        for (int kb = 0; kb < num_k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_STAGE_BYTES;
+          mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
+          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BK, m_blk * BM);
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BK, n_blk * BN);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp_idx == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = umma_idesc_f16(FMT, BM, BN);
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+      tc_fence_after_sync();
+      const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
+      for (int kb = 0; kb < num_k_blocks; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after_sync();
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + stage * STAGE_BYTES);
+          const uint64_t da = umma_smem_desc_sw128(sa);
+          const uint64_t db = umma_smem_desc_sw128(sa + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // +32 bytes per K=16 step inside the 128-byte swizzle row (start address is >> 4)
+            umma_f16_ss(tmem_d, da + static_cast<uint64_t>(k * 2), db + static_cast<uint64_t>(k * 2),
+                        idesc, static_cast<uint32_t>((kb | k) != 0));
+          }
+          umma_commit(&empty_bar[stage]);                               // smem slot reusable
+          if (kb == num_k_blocks - 1) umma_commit(&tmem_full_bar[acc]);  // accumulator ready
+        }
+        __syncwarp();
+        if (++stage == STAGES) {
+          stage = 0;
+          phase ^= 1u;
+        }
+      }
+      if (++acc == ACC_STAGES) {
+        acc = 0;
+        acc_phase ^= 1u;
+      }
+    }
+  } else if (warp_idx >= 4) {
+    // ===================== epilogue (TMEM -> registers -> global) =====================
+    const int quarter = warp_idx & 3;  // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_blk = tile / num_n_blocks, n_blk = tile % num_n_blocks;
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after_sync();
+      const int row = m_blk * BM + quarter * 32 + lane;
+      const uint32_t taddr =
+          tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
+      typename Epi::RowState st;
+      Epi::init_row(st);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_wait();
+        const int col0 = n_blk * BN + c * 32;
+        if (row < M && col0 < N) Epi::template apply<FMT>(ep, st, row, col0, r);
+      }
+      if (row < M) Epi::finish_row(ep, st, row, n_blk);
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+      if (++acc == ACC_STAGES) {
+        acc = 0;
+        acc_phase ^= 1u;
+      }
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp_idx == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// --------------------------------------------------------------------------------------------
+// Epilogues
+// --------------------------------------------------------------------------------------------
+enum Act : int { kActNone = 0, kActTanh = 1, kActSigmoid = 2 };
+
+// out = act(acc + bias[n]); activation chosen per 256-column block (lets [W_gate ; W_bias] run as
+// one N=2048 GEMM). Writes a 16-bit copy (next GEMM operand / gather source) and/or fp32.
+struct EpiBiasAct {
+  struct Params {
+    const float* bias;   // [N]
+    void* out16;         // [M, ld16] 16-bit or null
+    float* out32;        // [M, ld32] or null
+    int ld16, ld32;
+    int act[8];          // per n-block activation
+  };
+  struct RowState {};
+  static EVI_DEVINL void init_row(RowState&) {}
+  template <int FMT>
+  static EVI_DEVINL void apply(const Params& p, RowState&, int row, int col0, uint32_t (&r)[32]) {
+    const int act = p.act[(col0 / BN) & 7];
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i));
+      v[i + 0] = __uint_as_float(r[i + 0]) + b.x;
+      v[i + 1] = __uint_as_float(r[i + 1]) + b.y;
+      v[i + 2] = __uint_as_float(r[i + 2]) + b.z;
+      v[i + 3] = __uint_as_float(r[i + 3]) + b.w;
+    }
+    if (act == kActTanh) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);
+    } else if (act == kActSigmoid) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = 1.0f / (1.0f + expf(-v[i]));
+    }
+    if (p.out32 != nullptr) {
+      float4* o = reinterpret_cast<float4*>(p.out32 + static_cast<size_t>(row) * p.ld32 + col0);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+    if (p.out16 != nullptr) {
+      uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out16) +
+                                          static_cast<size_t>(row) * p.ld16 + col0);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 w;
+        w.x = Op16<FMT>::pack2(v[8 * i + 0], v[8 * i + 1]);
+        w.y = Op16<FMT>::pack2(v[8 * i + 2], v[8 * i + 3]);
+        w.z = Op16<FMT>::pack2(v[8 * i + 4], v[8 * i + 5]);
+        w.w = Op16<FMT>::pack2(v[8 * i + 6], v[8 * i + 7]);
+        o[i] = w;
+      }
+    }
+  }
+  static EVI_DEVINL void finish_row(const Params&, RowState&, int, int) {}
+};
+
+// state_net.0 pre-activation: z = acc + dist[m] * w_dist[n] + b1[n]  (the 3073rd input column of
+// retriever.py:481 folded in as a rank-1 update), stored 16-bit, plus exact fp32 LayerNorm partial
+// sums (sum, sum of squares) per row per 256-column block.
+struct EpiPreNorm {
+  struct Params {
+    const float* bias;    // [N] state_net.0.bias
+    const float* w_dist;  // [N] state_net.0.weight[:, 3D]
+    const float* dist;    // [M]  -||err||
+    void* z16;            // [M, ldz]
+    float2* stats;        // [M, N / BN]
+    int ldz, n_blocks;
+  };
+  struct RowState {
+    float sum, sumsq, dist;
+  };
+  static EVI_DEVINL void init_row(RowState& s) { s.sum = 0.f, s.sumsq = 0.f, s.dist = 0.f; }
+  template <int FMT>
+  static EVI_DEVINL void apply(const Params& p, RowState& s, int row, int col0, uint32_t (&r)[32]) {
+    const float d = __ldg(p.dist + row);
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i));
+      const float4 w = __ldg(reinterpret_cast<const float4*>(p.w_dist + col0 + i));
+      v[i + 0] = __uint_as_float(r[i + 0]) + fmaf(d, w.x, b.x);
+      v[i + 1] = __uint_as_float(r[i + 1]) + fmaf(d, w.y, b.y);
+      v[i + 2] = __uint_as_float(r[i + 2]) + fmaf(d, w.z, b.z);
+      v[i + 3] = __uint_as_float(r[i + 3]) + fmaf(d, w.w, b.w);
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      s.sum += v[i];
+      s.sumsq = fmaf(v[i], v[i], s.sumsq);
+    }
+    uint4* o = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.z16) +
+                                        static_cast<size_t>(row) * p.ldz + col0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      uint4 w;
+      w.x = Op16<FMT>::pack2(v[8 * i + 0], v[8 * i + 1]);
+      w.y = Op16<FMT>::pack2(v[8 * i + 2], v[8 * i + 3]);
+      w.z = Op16<FMT>::pack2(v[8 * i + 4], v[8 * i + 5]);
+      w.w = Op16<FMT>::pack2(v[8 * i + 6], v[8 * i + 7]);
+      o[i] = w;
+    }
+  }
+  static EVI_DEVINL void finish_row(const Params& p, RowState& s, int row, int n_blk) {
+    p.stats[static_cast<size_t>(row) * p.n_blocks + n_blk] = make_float2(s.sum, s.sumsq);
+  }
+};
+
+// state_net.4 output: feat = acc + b2 (fp32, retriever.py:180) — only when edge features are requested
+struct EpiBiasF32 {
+  struct Params {
+    const float* bias;
+    float* out32;
+    int ld32;
+  };
+  struct RowState {};
+  static EVI_DEVINL void init_row(RowState&) {}
+  template <int FMT>
+  static EVI_DEVINL void apply(const Params& p, RowState&, int row, int col0, uint32_t (&r)[32]) {
+    float4* o = reinterpret_cast<float4*>(p.out32 + static_cast<size_t>(row) * p.ld32 + col0);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 4 * i));
+      o[i] = make_float4(__uint_as_float(r[4 * i]) + b.x, __uint_as_float(r[4 * i + 1]) + b.y,
+                         __uint_as_float(r[4 * i + 2]) + b.z, __uint_as_float(r[4 * i + 3]) + b.w);
+    }
+  }
+  static EVI_DEVINL void finish_row(const Params&, RowState&, int, int) {}
+};
+
+// --------------------------------------------------------------------------------------------
+// Host side: tensor maps + launch
+// --------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+inline EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// row-major [rows, cols] 16-bit matrix with row pitch ld (elements); box = box_rows x 64 cols
+inline bool make_tmap_2d(CUtensorMap* map, int fmt, const void* base, uint64_t rows, uint64_t cols,
+                         uint64_t ld, uint32_t box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(BK), box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, fmt == kFmtBF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                  2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+template <int FMT, class Epi>
+inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                  const typename Epi::Params& ep, int num_sms, cudaStream_t stream) {
+  if (M <= 0) return kOk;
+  if (K % 8 != 0 || lda % 8 != 0 || ldb % 8 != 0 || N % 32 != 0) return kErrInvalidArg;
+  CUtensorMap ta, tb;
+  if (!make_tmap_2d(&ta, FMT, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K),
+                    static_cast<uint64_t>(lda), BM))
+    return kErrCuda;
+  if (!make_tmap_2d(&tb, FMT, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K),
+                    static_cast<uint64_t>(ldb), BN))
+    return kErrCuda;
+  auto kern = gemm_kernel<FMT, Epi>;
+  static bool attr_set = false;  // per template instantiation
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
+      return kErrCuda;
+    attr_set = true;
+  }
+  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int grid = tiles < num_sms ? tiles : num_sms;
+  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
+  return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
+}
+
+}  // namespace gemm
+}  // namespace evi

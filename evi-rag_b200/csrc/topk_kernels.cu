@@ -1,0 +1,220 @@
+// Ragged per-question top-k. One CTA per question:
+//   1. MSB-first radix select (4 x 8-bit passes, warp-aggregated shared-memory histograms) finds
+//      the k-th largest order-preserving key and how many ties at that key are needed;
+//   2. everything above the threshold is collected unordered, ties are collected in ascending
+//      index order (ballot prefix scan) so the result is deterministic;
+//   3. the <= 1024 candidates are bitonic-sorted on (key desc, index asc).
+// Scores are read straight from global memory each pass: a question's scores (E_q * 4 B, ~20 KB
+// for WebQSP-shaped inputs) stay L1/L2 resident, so HBM sees them once.
+#include <math.h>
+
+#include "common.cuh"
+#include "evi_rag_b200.h"
+
+namespace evi {
+
+constexpr int kTopkThreads = 256;
+constexpr int kTopkMaxK = 1024;
+
+EVI_DEVINL float apply_transform(float x, int transform) {
+  return transform == EVI_TOPK_SIGMOID ? 1.0f / (1.0f + expf(-x)) : x;
+}
+// order-preserving float -> uint key; NaN sorts first like torch.topk, -0 == +0
+EVI_DEVINL uint32_t order_key(float x) {
+  if (x != x) return 0xFFFFFFFFu;
+  const uint32_t b = __float_as_uint(x + 0.0f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+
+// block-wide inclusive scan of one int per thread (blockDim == kTopkThreads)
+EVI_DEVINL int block_inclusive_scan(int v, int* warp_tot /*[8]*/, int* total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += y;
+  }
+  if (lane == 31) warp_tot[w] = incl;
+  __syncthreads();
+  int off = 0, tot = 0;
+#pragma unroll
+  for (int i = 0; i < kTopkThreads / 32; ++i) {
+    const int t = warp_tot[i];
+    if (i < w) off += t;
+    tot += t;
+  }
+  __syncthreads();
+  *total = tot;
+  return incl + off;
+}
+
+__global__ void __launch_bounds__(kTopkThreads)
+segmented_topk_kernel(const float* __restrict__ scores, const long long* __restrict__ edge_ptr, int k,
+                      int transform, float* __restrict__ values, int* __restrict__ indices,
+                      int* __restrict__ counts) {
+  __shared__ unsigned long long cand[kTopkMaxK];
+  __shared__ int hist[256];
+  __shared__ int warp_tot[kTopkThreads / 32];
+  __shared__ uint32_t sel_prefix;
+  __shared__ int sel_need, cursor;
+
+  const int b = blockIdx.x;
+  const long long e0 = edge_ptr[b];
+  const int n = static_cast<int>(edge_ptr[b + 1] - e0);
+  const int kt = n < k ? n : k;
+  const float* s = scores + e0;
+  const int tid = threadIdx.x;
+  if (tid == 0) counts[b] = kt;
+  for (int j = kt + tid; j < k; j += kTopkThreads) {
+    values[static_cast<size_t>(b) * k + j] = -INFINITY;
+    indices[static_cast<size_t>(b) * k + j] = -1;
+  }
+  if (kt == 0) return;
+
+  int P = 1;
+  while (P < kt) P <<= 1;
+  for (int j = kt + tid; j < P; j += kTopkThreads) cand[j] = 0ull;
+
+  if (n <= k) {
+    for (int i = tid; i < n; i += kTopkThreads)
+      cand[i] = (static_cast<unsigned long long>(order_key(apply_transform(s[i], transform))) << 32) |
+                static_cast<unsigned long long>(0xFFFFFFFFu - static_cast<uint32_t>(i));
+  } else {
+    if (tid == 0) sel_prefix = 0u, sel_need = kt, cursor = 0;
+    __syncthreads();
+    uint32_t mask = 0u;
+    for (int pass = 0; pass < 4; ++pass) {
+      const int shift = 24 - 8 * pass;
+      hist[tid] = 0;
+      __syncthreads();
+      const uint32_t prefix = sel_prefix;
+      const int need = sel_need;  // read before this pass's winner overwrites it
+      for (int base = 0; base < n; base += kTopkThreads) {
+        const int i = base + tid;
+        uint32_t key = 0u;
+        bool in = false;
+        if (i < n) {
+          key = order_key(apply_transform(s[i], transform));
+          in = (key & mask) == prefix;
+        }
+        const unsigned active = __ballot_sync(0xffffffffu, in);
+        if (in) {
+          const int bin = static_cast<int>((key >> shift) & 255u);
+          const unsigned peers = __match_any_sync(active, bin);
+          if ((tid & 31) == __ffs(peers) - 1) atomicAdd(&hist[bin], __popc(peers));
+        }
+      }
+      __syncthreads();
+      // thread t owns bin 255-t: inclusive scan over t == count of keys in bins >= 255-t
+      const int own = hist[255 - tid];
+      int total;
+      const int incl = block_inclusive_scan(own, warp_tot, &total);
+      if (incl >= need && incl - own < need) {
+        sel_prefix = prefix | (static_cast<uint32_t>(255 - tid) << shift);
+        sel_need = need - (incl - own);
+      }
+      mask |= 255u << shift;
+      __syncthreads();
+    }
+    const uint32_t kth = sel_prefix;
+    const int need = sel_need;       // ties at kth to take, >= 1
+    const int n_greater = kt - need;
+    for (int i = tid; i < n; i += kTopkThreads) {
+      const uint32_t key = order_key(apply_transform(s[i], transform));
+      if (key > kth)
+        cand[atomicAdd(&cursor, 1)] = (static_cast<unsigned long long>(key) << 32) |
+                                      static_cast<unsigned long long>(0xFFFFFFFFu - static_cast<uint32_t>(i));
+    }
+    int running = 0;
+    for (int base = 0; base < n && running < need; base += kTopkThreads) {
+      const int i = base + tid;
+      const bool tie = i < n && order_key(apply_transform(s[i], transform)) == kth;
+      int total;
+      const int incl = block_inclusive_scan(tie ? 1 : 0, warp_tot, &total);
+      const int rank = running + incl - 1;
+      if (tie && rank < need)
+        cand[n_greater + rank] = (static_cast<unsigned long long>(kth) << 32) |
+                                 static_cast<unsigned long long>(0xFFFFFFFFu - static_cast<uint32_t>(i));
+      running += total;
+    }
+  }
+  __syncthreads();
+  // bitonic sort, descending on the 64-bit composite
+  for (int size = 2; size <= P; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int i = tid; i < P; i += kTopkThreads) {
+        const int j = i ^ stride;
+        if (j > i) {
+          const unsigned long long a = cand[i], c = cand[j];
+          const bool descending = (i & size) == 0;
+          if (descending ? (a < c) : (a > c)) cand[i] = c, cand[j] = a;
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int j = tid; j < kt; j += kTopkThreads) {
+    const int idx = static_cast<int>(0xFFFFFFFFu - static_cast<uint32_t>(cand[j] & 0xFFFFFFFFull));
+    indices[static_cast<size_t>(b) * k + j] = idx;
+    values[static_cast<size_t>(b) * k + j] = apply_transform(s[idx], transform);
+  }
+}
+
+__global__ void topk_payload_kernel(const int* __restrict__ indices, const int* __restrict__ counts,
+                                    const long long* __restrict__ edge_ptr, int num_graphs, int k,
+                                    const long long* __restrict__ edge_index, long long num_edges,
+                                    const long long* __restrict__ node_global_ids,
+                                    const long long* __restrict__ edge_attr, const float* __restrict__ labels,
+                                    const float* __restrict__ logits_fwd, const float* __restrict__ logits_bwd,
+                                    long long* __restrict__ head_ids, long long* __restrict__ tail_ids,
+                                    long long* __restrict__ relation_ids, float* __restrict__ out_labels,
+                                    float* __restrict__ out_lf, float* __restrict__ out_lb) {
+  const long long t = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (t >= static_cast<long long>(num_graphs) * k) return;
+  const int b = static_cast<int>(t / k), j = static_cast<int>(t % k);
+  const bool valid = j < counts[b];
+  const long long e = valid ? edge_ptr[b] + indices[t] : 0;
+  if (head_ids) head_ids[t] = valid ? node_global_ids[edge_index[e]] : -1;
+  if (tail_ids) tail_ids[t] = valid ? node_global_ids[edge_index[num_edges + e]] : -1;
+  if (relation_ids) relation_ids[t] = valid ? edge_attr[e] : -1;
+  if (out_labels) out_labels[t] = valid && labels ? labels[e] : 0.f;
+  if (out_lf) out_lf[t] = valid && logits_fwd ? logits_fwd[e] : 0.f;
+  if (out_lb) out_lb[t] = valid && logits_bwd ? logits_bwd[e] : 0.f;
+}
+
+}  // namespace evi
+
+using namespace evi;
+
+extern "C" {
+
+int evi_abi_version(void) { return 1; }
+
+int evi_segmented_topk(const float* scores, const long long* edge_ptr, int num_graphs, int k, int transform,
+                       float* values, int* indices, int* counts, cudaStream_t stream) {
+  if (num_graphs <= 0) return kOk;
+  if (k <= 0 || k > kTopkMaxK || edge_ptr == nullptr || values == nullptr || indices == nullptr ||
+      counts == nullptr)
+    return kErrInvalidArg;
+  if (transform != EVI_TOPK_RAW && transform != EVI_TOPK_SIGMOID) return kErrInvalidArg;
+  segmented_topk_kernel<<<num_graphs, kTopkThreads, 0, stream>>>(scores, edge_ptr, k, transform, values, indices,
+                                                                 counts);
+  return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
+}
+
+int evi_topk_gather_payload(const int* indices, const int* counts, const long long* edge_ptr, int num_graphs,
+                            int k, const long long* edge_index, long long num_edges,
+                            const long long* node_global_ids, const long long* edge_attr, const float* labels,
+                            const float* logits_fwd, const float* logits_bwd, long long* head_ids,
+                            long long* tail_ids, long long* relation_ids, float* out_labels,
+                            float* out_logits_fwd, float* out_logits_bwd, cudaStream_t stream) {
+  if (num_graphs <= 0 || k <= 0) return kOk;
+  const long long total = static_cast<long long>(num_graphs) * k;
+  topk_payload_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, stream>>>(
+      indices, counts, edge_ptr, num_graphs, k, edge_index, num_edges, node_global_ids, edge_attr, labels,
+      logits_fwd, logits_bwd, head_ids, tail_ids, relation_ids, out_labels, out_logits_fwd, out_logits_bwd);
+  return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
+}
+
+}  // extern "C"

@@ -1,0 +1,101 @@
+"""ctypes binding of ``libevi_rag_b200.so`` (the C ABI declared in ``include/evi_rag_b200.h``).
+
+There is no CPU fallback: if the shared library is missing every compute call raises
+``RuntimeError`` telling the user to build it (``./build.sh`` or ``__graft_entry__.build()``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libevi_rag_b200.so")
+
+EVI_OK = 0
+_STATUS = {1: "invalid argument", 2: "CUDA error", 3: "workspace too small", 4: "unsupported shape"}
+
+FLAG_OUT_OF_RANGE, FLAG_CROSS_GRAPH, FLAG_NOT_MONOTONE = 1, 2, 4
+FMT_F16, FMT_BF16 = 0, 1
+DIR_BIDIRECTIONAL, DIR_FORWARD, DIR_BACKWARD = 0, 1, 2
+ACT_NONE, ACT_TANH, ACT_SIGMOID = 0, 1, 2
+TOPK_RAW, TOPK_SIGMOID = 0, 1
+
+_vp, _i, _ll, _f, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
+
+
+class ScoreArgs(C.Structure):
+    """``evi_score_args`` (include/evi_rag_b200.h)."""
+
+    _fields_ = [
+        ("num_edges", _ll), ("emb_dim", _i), ("hidden_dim", _i), ("direction", _i),
+        ("operand_format", _i), ("want_features", _i), ("ns_dim", _i), ("num_sms", _i),
+        ("num_nodes", _i), ("num_rel_rows", _i), ("num_questions", _i), ("flags", _vp),
+        ("head32", _vp), ("tail32", _vp), ("qid32", _vp), ("rel_slot32", _vp),
+        ("node_repr16", _vp), ("rel_repr16", _vp), ("gate_bias32", _vp), ("node_struct", _vp),
+        ("struct_w_t", _vp), ("struct_b", _vp), ("struct_ln_g", _vp), ("struct_ln_b", _vp),
+        ("nav_w", _vp), ("nav_b", _f),
+        ("w1_main16", _vp), ("w1_dist_col", _vp), ("w1_bias", _vp), ("ln1_g", _vp), ("ln1_b", _vp),
+        ("head_v", _vp), ("head_c0", _f), ("w2_16", _vp), ("w2_bias", _vp), ("head_w", _vp),
+        ("head_b", _f),
+        ("logits", _vp), ("logits_fwd", _vp), ("logits_bwd", _vp), ("edge_embeddings", _vp),
+        ("workspace", _vp), ("workspace_bytes", _sz),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/evi_rag_b200.h declares
+PROTOTYPES = {
+    "evi_abi_version": (_i, []),
+    "evi_edge_batch": (_i, [_vp, _ll, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "evi_dde_workspace_bytes": (_sz, [_i]),
+    "evi_dde_forward": (_i, [_vp, _vp, _ll, _i, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
+    "evi_build_csr": (_i, [_vp, _vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
+    "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "evi_shortest_path_pairs": (_i, [_vp, _vp, _i] + [_vp] * 9 + [_i] + [_vp] * 4 + [_vp]),
+    "evi_gather_rows": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp]),
+    "evi_convert_f32": (_i, [_vp, _vp, _ll, _i, _vp]),
+    "evi_project": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "evi_score_workspace_bytes": (_sz, [_ll, _i, _i]),
+    "evi_score_edges": (_i, [C.POINTER(ScoreArgs), _vp]),
+    "evi_segmented_topk": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "evi_topk_gather_payload": (_i, [_vp, _vp, _vp, _i, _i, _vp, _ll] + [_vp] * 11 + [_vp]),
+}
+
+_lib: Optional[C.CDLL] = None
+
+
+def load() -> C.CDLL:
+    """Load the library once and attach prototypes. Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: the CUDA extension is not built (run ./build.sh or "
+            "`python -c 'import __graft_entry__ as g; g.build()'`). There is no CPU fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str) -> None:
+    if status != EVI_OK:
+        raise RuntimeError(f"{what} failed: {_STATUS.get(status, 'status ' + str(status))}")
+
+
+def ptr(t) -> Optional[int]:
+    """Device pointer of a torch tensor (None -> NULL)."""
+    if t is None:
+        return None
+    return t.data_ptr()
+
+
+def stream_handle() -> int:
+    import torch
+
+    return torch.cuda.current_stream().cuda_stream

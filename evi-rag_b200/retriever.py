@@ -1,0 +1,569 @@
+"""Drop-in ``Retriever`` for EVI-RAG's retrieval hot path, computed by sm_100a kernels.
+
+Mirrors ``src/models/components/retriever.py`` of the reference: same constructor keywords and
+validation (:105-183, :555-570), same ``state_dict`` keys and shapes (so reference checkpoints load
+with ``strict=True`` and ``GraphEmbedder`` can still read them by suffix,
+``src/models/components/gflownet_embedder.py:489-533``), same duck-typed batch attributes
+(:201-204, :419-433, :526-545, :580-584), same ``RetrieverOutput`` fields (:80-99) and the same
+``ValueError`` conditions. A Hydra config switches over by changing one ``_target_``
+(``configs/model/retriever_module.yaml:8``).
+
+What differs (B200 design):
+  * all arithmetic runs in ``libevi_rag_b200.so``; there is no eager-PyTorch / CPU fallback;
+  * dense contractions use 16-bit tensor-core operands with fp32 accumulation
+    (``operand_dtype="fp16"`` by default, ``"bf16"`` selectable);
+  * with ``attach_embedding_tables`` the 1024-d text-embedding tables live in HBM and a batch only
+    needs ids (``node_embedding_ids``, ``edge_attr``) — the reference's per-edge CPU gather + H2D
+    of ``edge_embeddings`` (``src/data/components/embedding_store.py:101-150``) disappears;
+  * ``edge_embeddings`` ([E, H] fp32 features) are produced only when asked
+    (``return_edge_embeddings=True`` or ``extract_edge_tokens``): ``RetrieverModule`` drops them
+    in eval (``src/models/retriever_module.py:447-450``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Any, Dict, Optional
+
+import torch
+from torch import nn
+
+from . import lib as _lib
+
+_NUM_TOPICS_BINARY = 2
+_MAX_DDE_ROUNDS = 4
+_FP16_SAFE_MAX = 6.0e4
+
+
+@dataclass
+class RetrieverOutput:
+    """Same container as the reference (retriever.py:80-99)."""
+
+    logits: torch.Tensor
+    query_ids: torch.Tensor
+    relation_ids: Optional[torch.Tensor] = None
+    logits_fwd: Optional[torch.Tensor] = None
+    logits_bwd: Optional[torch.Tensor] = None
+    edge_embeddings: Optional[torch.Tensor] = None
+
+    def detach(self) -> "RetrieverOutput":
+        d = lambda t: t.detach() if t is not None else None
+        return RetrieverOutput(
+            logits=self.logits.detach(),
+            query_ids=self.query_ids.detach(),
+            relation_ids=d(self.relation_ids),
+            logits_fwd=d(self.logits_fwd),
+            logits_bwd=d(self.logits_bwd),
+            edge_embeddings=d(self.edge_embeddings),
+        )
+
+
+class EmbeddingProjector(nn.Module):
+    """Linear + Tanh holder with the reference's parameter names (projections.py:9-40)."""
+
+    def __init__(self, output_dim: int, *, input_dim: int) -> None:
+        super().__init__()
+        self.network = nn.Sequential(nn.Linear(input_dim, output_dim), nn.Tanh())
+
+
+class _DDEConfig(nn.Module):
+    """Round counts of the reference DDE (graph.py:26-39); the propagation itself is a kernel."""
+
+    def __init__(self, num_rounds: int = 2, num_reverse_rounds: int = 2) -> None:
+        super().__init__()
+        self.num_rounds = int(max(0, num_rounds))
+        self.num_reverse_rounds = int(max(0, num_reverse_rounds))
+        if self.num_rounds > _MAX_DDE_ROUNDS or self.num_reverse_rounds > _MAX_DDE_ROUNDS:
+            raise ValueError(
+                f"DDE supports at most {_MAX_DDE_ROUNDS} rounds per direction; "
+                f"got num_rounds={self.num_rounds}, num_reverse_rounds={self.num_reverse_rounds}."
+            )
+
+
+class Retriever(nn.Module):
+    """Retriever with the reference interface; forward is eval-only (no autograd)."""
+
+    def __init__(
+        self,
+        emb_dim: int,
+        hidden_dim: int,
+        topic_pe: bool = True,
+        num_topics: int = 2,
+        dde_cfg: Optional[Dict[str, int]] = None,
+        dropout_p: float = 0.1,
+        core_mode: str = "geometry",
+        direction_mode: str = "bidirectional",
+        hide_seek_cfg: Optional[Dict[str, Any]] = None,
+        *,
+        operand_dtype: str = "fp16",
+        return_edge_embeddings: bool = False,
+        max_workspace_bytes: int = 12 << 30,
+        validate: bool = True,
+        **_: Any,
+    ) -> None:
+        super().__init__()
+        self.emb_dim = int(emb_dim)
+        self.hidden_dim = int(hidden_dim)
+        self.use_topic_pe = bool(topic_pe)
+        if not self.use_topic_pe:
+            raise ValueError("topic_pe must be enabled; retriever requires topic_one_hot + DDE.")
+        self.num_topics = int(num_topics)
+        if self.num_topics != _NUM_TOPICS_BINARY:
+            raise ValueError(f"num_topics must be {_NUM_TOPICS_BINARY} (seed vs non-seed), got {self.num_topics}")
+        _ = self._normalize_core_mode(core_mode)
+        self.direction_mode = self._normalize_direction_mode(direction_mode)
+        if operand_dtype not in ("fp16", "bf16"):
+            raise ValueError(f"operand_dtype must be 'fp16' or 'bf16', got {operand_dtype!r}")
+        self.operand_dtype = operand_dtype
+        self.return_edge_embeddings = bool(return_edge_embeddings)
+        self.max_workspace_bytes = int(max_workspace_bytes)
+        self.validate = bool(validate)
+
+        d, h = self.emb_dim, self.hidden_dim
+        self.entity_proj = EmbeddingProjector(d, input_dim=d)
+        self.relation_proj = EmbeddingProjector(d, input_dim=d)
+        self.query_proj = EmbeddingProjector(d, input_dim=d)
+        self.non_text_entity_emb = nn.Embedding(1, d)
+        self.dde = _DDEConfig(**(dde_cfg or {}))
+        num_rounds, num_rev = self.dde.num_rounds, self.dde.num_reverse_rounds
+        self._topic_struct_dim = self.num_topics * (1 + num_rounds + num_rev)
+        struct_raw_dim = 2 * self._topic_struct_dim
+        self.register_buffer(
+            "parity_meta",
+            torch.tensor([int(self.use_topic_pe), self.num_topics, num_rounds, num_rev], dtype=torch.long),
+        )
+        self.q_gate = nn.Sequential(nn.Linear(d, d), nn.Sigmoid())
+        self.q_bias = nn.Sequential(nn.Linear(d, d), nn.Tanh())
+        self.struct_proj = nn.Sequential(nn.Linear(struct_raw_dim, d), nn.LayerNorm(d), nn.GELU())
+        self.struct_gate_net = nn.Sequential(nn.Linear(d, 1), nn.Sigmoid())
+        self.state_net = nn.Sequential(
+            nn.Linear(3 * d + 1, h), nn.LayerNorm(h), nn.GELU(), nn.Dropout(dropout_p), nn.Linear(h, h)
+        )
+        self.score_head = nn.Linear(h, 1)
+        self._init_hide_seek(hide_seek_cfg)
+
+        self._prepared: Optional[Dict[str, Any]] = None
+        self._prepared_key = None
+        self._tables: Optional[Dict[str, torch.Tensor]] = None
+        self._ws: Optional[torch.Tensor] = None
+        self._flags: Optional[torch.Tensor] = None
+        self._pending_flags = False
+
+    # ------------------------------------------------------------------ reference API
+    def forward(self, batch: Any) -> RetrieverOutput:
+        output, _ = self._forward_impl(batch, return_features=self.return_edge_embeddings)
+        return output
+
+    def extract_edge_tokens(self, batch: Any) -> torch.Tensor:
+        _, features = self._forward_impl(batch, return_features=True)
+        if features is None:
+            raise RuntimeError("extract_edge_tokens expected non-empty features but got None.")
+        return features
+
+    # ------------------------------------------------------------------ B200 additions
+    def attach_embedding_tables(self, entity_embeddings: torch.Tensor, relation_embeddings: torch.Tensor) -> None:
+        """Keep the text-embedding tables in HBM (operand dtype). ``entity_embeddings`` is
+        ``[max_id+1, D]`` with row 0 reserved for non-text entities and ``relation_embeddings``
+        ``[R, D]`` (scripts/text_encode_utils.py:60-67, embedding_store.py:60-99). Batches then
+        only need ``node_embedding_ids`` and ``edge_attr``."""
+        dev = self._device()
+        dt = torch.float16 if self.operand_dtype == "fp16" else torch.bfloat16
+        if entity_embeddings.dim() != 2 or entity_embeddings.size(1) != self.emb_dim:
+            raise ValueError(f"entity_embeddings must be [T, {self.emb_dim}], got {tuple(entity_embeddings.shape)}")
+        if relation_embeddings.dim() != 2 or relation_embeddings.size(1) != self.emb_dim:
+            raise ValueError(f"relation_embeddings must be [R, {self.emb_dim}], got {tuple(relation_embeddings.shape)}")
+        for name, t in (("entity", entity_embeddings), ("relation", relation_embeddings)):
+            if dt == torch.float16 and float(t.abs().max()) > _FP16_SAFE_MAX:
+                raise ValueError(f"{name} embeddings exceed the fp16 range; use operand_dtype='bf16'.")
+        self._tables = {
+            "entity": entity_embeddings.to(device=dev, dtype=dt).contiguous(),
+            "relation": relation_embeddings.to(device=dev, dtype=dt).contiguous(),
+        }
+
+    def check_flags(self) -> None:
+        """Read back the device-side validation word (one host sync) and raise like the
+        reference (graph_utils.py:66-99, retriever.py:594-604)."""
+        if not self._pending_flags or self._flags is None:
+            return
+        self._pending_flags = False
+        word = int(self._flags.item())
+        if word == 0:
+            return
+        self._flags.zero_()
+        if word & _lib.FLAG_OUT_OF_RANGE:
+            raise ValueError("Invalid edge_index range; edge_index / embedding ids out of range for this batch.")
+        if word & _lib.FLAG_CROSS_GRAPH:
+            raise ValueError("edge_index crosses graph boundaries; head/tail graph assignments differ. ")
+        if word & _lib.FLAG_NOT_MONOTONE:
+            raise ValueError(
+                "edge_batch is not non-decreasing along the flattened edge list, which breaks per-graph slicing; "
+                "Ensure edges are concatenated per-graph (PyG Batch)."
+            )
+
+    # ------------------------------------------------------------------ internals
+    def _device(self) -> torch.device:
+        return next(self.parameters()).device
+
+    def _fmt(self) -> int:
+        return _lib.FMT_F16 if self.operand_dtype == "fp16" else _lib.FMT_BF16
+
+    def _op_dtype(self) -> torch.dtype:
+        return torch.float16 if self.operand_dtype == "fp16" else torch.bfloat16
+
+    def _prepare_weights(self) -> Dict[str, Any]:
+        """16-bit / fp32 kernel-side copies of the parameters; rebuilt when any parameter changes."""
+        params = list(self.parameters())
+        key = (self.operand_dtype,) + tuple((p.data_ptr(), p._version) for p in params)
+        if self._prepared is not None and self._prepared_key == key:
+            return self._prepared
+        dev = self._device()
+        if dev.type != "cuda":
+            raise RuntimeError("evi_rag_b200.Retriever runs on CUDA only (no CPU fallback); call .cuda() first.")
+        if self.emb_dim != 1024 or self.hidden_dim != 1024:
+            raise ValueError("the sm_100a kernels are built for emb_dim == hidden_dim == 1024")
+        dt = self._op_dtype()
+        d = self.emb_dim
+
+        def w16(t: torch.Tensor) -> torch.Tensor:
+            t = t.detach().to(device=dev, dtype=torch.float32)
+            if dt == torch.float16 and float(t.abs().max()) > _FP16_SAFE_MAX:
+                raise ValueError("weights exceed the fp16 range; construct with operand_dtype='bf16'.")
+            return t.to(dt).contiguous()
+
+        f32 = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
+        sn0 = self.state_net[0]
+        sn4 = self.state_net[4]
+        wo = self.score_head.weight.detach().to(dev).double()[0]
+        p: Dict[str, Any] = {
+            "we": w16(self.entity_proj.network[0].weight), "be": f32(self.entity_proj.network[0].bias),
+            "wr": w16(self.relation_proj.network[0].weight), "br": f32(self.relation_proj.network[0].bias),
+            "wq": w16(self.query_proj.network[0].weight), "bq": f32(self.query_proj.network[0].bias),
+            "wgb": w16(torch.cat([self.q_gate[0].weight, self.q_bias[0].weight], dim=0)),
+            "bgb": f32(torch.cat([self.q_gate[0].bias, self.q_bias[0].bias], dim=0)),
+            "non_text": f32(self.non_text_entity_emb.weight[0]),
+            "ws_t": f32(self.struct_proj[0].weight.t()), "bs": f32(self.struct_proj[0].bias),
+            "ls_g": f32(self.struct_proj[1].weight), "ls_b": f32(self.struct_proj[1].bias),
+            "wn": f32(self.struct_gate_net[0].weight[0]), "bn": float(self.struct_gate_net[0].bias.detach()[0]),
+            "w1": w16(sn0.weight[:, : 3 * d]), "w1d": f32(sn0.weight[:, 3 * d]), "b1": f32(sn0.bias),
+            "l1_g": f32(self.state_net[1].weight), "l1_b": f32(self.state_net[1].bias),
+            "w2": w16(sn4.weight), "b2": f32(sn4.bias),
+            "v": (sn4.weight.detach().to(dev).double().t() @ wo).float().contiguous(),
+            "c0": float(wo @ sn4.bias.detach().to(dev).double() + self.score_head.bias.detach().to(dev).double()[0]),
+            "wo": f32(self.score_head.weight[0]), "bo": float(self.score_head.bias.detach()[0]),
+            "num_sms": torch.cuda.get_device_properties(dev).multi_processor_count,
+        }
+        self._prepared, self._prepared_key = p, key
+        return p
+
+    def _workspace(self, nbytes: int, dev: torch.device) -> torch.Tensor:
+        if self._ws is None or self._ws.numel() < nbytes or self._ws.device != dev:
+            self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+        return self._ws
+
+    def _project(self, x16, w16, bias, acts, *, out16=None, out32=None, p=None):
+        L = _lib.load()
+        act_arr = (C.c_int * 8)(*(list(acts) + [0] * (8 - len(acts))))
+        st = L.evi_project(
+            x16.data_ptr(), x16.size(0), w16.data_ptr(), w16.size(0), w16.size(1), bias.data_ptr(), act_arr,
+            _lib.ptr(out16), _lib.ptr(out32), self._fmt(), p["num_sms"], _lib.stream_handle(),
+        )
+        _lib.check(st, "evi_project")
+
+    @torch.no_grad()
+    def _forward_impl(self, batch: Any, *, return_features: bool):
+        if self.training and torch.is_grad_enabled():
+            raise NotImplementedError(
+                "evi_rag_b200.Retriever implements the inference path; train with the reference module "
+                "(identical state_dict) and load the checkpoint here."
+            )
+        edge_index = getattr(batch, "edge_index", None)
+        if edge_index is None:
+            raise ValueError("Batch missing edge_index required for scoring.")
+        dev = self._device()
+        edge_index = edge_index.to(device=dev)
+        if edge_index.dim() != 2 or edge_index.size(0) != 2:
+            raise ValueError(f"edge_index must have shape [2, E], got {tuple(edge_index.shape)}")
+        if edge_index.size(1) == 0:
+            return self._empty_output(head_idx=edge_index[0], return_features=return_features)
+        edge_index = edge_index.to(torch.long).contiguous()
+        E = int(edge_index.size(1))
+
+        question_emb = getattr(batch, "question_emb", None)
+        node_embedding_ids = getattr(batch, "node_embedding_ids", None)
+        edge_attr = getattr(batch, "edge_attr", None)
+        if question_emb is None or node_embedding_ids is None or edge_attr is None:
+            raise ValueError("Batch must provide question_emb, node_embedding_ids, and edge_attr.")
+        node_embeddings = getattr(batch, "node_embeddings", None)
+        edge_embeddings = getattr(batch, "edge_embeddings", None)
+        use_tables = node_embeddings is None or edge_embeddings is None
+        if use_tables and self._tables is None:
+            raise ValueError("Batch must provide node_embeddings and edge_embeddings.")
+
+        L = _lib.load()
+        p = self._prepare_weights()
+        stream = _lib.stream_handle()
+        fmt, dt = self._fmt(), self._op_dtype()
+        d = self.emb_dim
+        if self._flags is None or self._flags.device != dev:
+            self._flags = torch.zeros(2, dtype=torch.int32, device=dev)
+        flags = self._flags
+
+        question_emb = question_emb.to(device=dev, dtype=torch.float32).contiguous()
+        if not torch.is_tensor(node_embedding_ids):
+            node_embedding_ids = torch.as_tensor(node_embedding_ids, dtype=torch.long)
+        node_embedding_ids = node_embedding_ids.to(device=dev, dtype=torch.long).contiguous()
+        edge_attr_dev = edge_attr.to(device=dev, dtype=torch.long).contiguous() if torch.is_tensor(edge_attr) else \
+            torch.as_tensor(edge_attr, dtype=torch.long, device=dev)
+        B = int(question_emb.size(0))
+        N = int(node_embedding_ids.numel())
+
+        # ---- a1/a2: question id per edge (+ int32 copies for the kernels) ------------------
+        head32 = torch.empty(E, dtype=torch.int32, device=dev)
+        tail32 = torch.empty(E, dtype=torch.int32, device=dev)
+        qid32 = torch.empty(E, dtype=torch.int32, device=dev)
+        edge_batch = getattr(batch, "edge_batch", None)
+        if edge_batch is None:
+            node_ptr = getattr(batch, "ptr", None)
+            if node_ptr is None:
+                raise ValueError("Batch missing ptr required for edge_batch computation.")
+            node_ptr = node_ptr.to(device=dev, dtype=torch.long).contiguous()
+            num_graphs = int(node_ptr.numel() - 1)
+            if num_graphs <= 0:
+                raise ValueError(f"num_graphs must be positive, got {num_graphs}")
+            query_ids = torch.empty(E, dtype=torch.long, device=dev)
+            st = L.evi_edge_batch(edge_index.data_ptr(), E, node_ptr.data_ptr(), num_graphs, query_ids.data_ptr(),
+                                  qid32.data_ptr(), head32.data_ptr(), tail32.data_ptr(), None, flags.data_ptr(),
+                                  stream)
+            _lib.check(st, "evi_edge_batch")
+            self._pending_flags = True
+            batch.edge_batch = query_ids  # retriever.py:612
+        else:
+            if not torch.is_tensor(edge_batch):
+                edge_batch = torch.as_tensor(edge_batch, dtype=torch.long)
+            query_ids = edge_batch.to(device=dev, dtype=torch.long).view(-1)
+            if query_ids.numel() != E:
+                raise ValueError(f"edge_batch length mismatch: {query_ids.numel()} vs edges {E}")
+            head32.copy_(edge_index[0])
+            tail32.copy_(edge_index[1])
+            qid32.copy_(query_ids)
+
+        # ---- a4: projections (tanh(xW^T+b)) at their true granularity ---------------------
+        x_nodes = torch.empty((N, d), dtype=dt, device=dev)
+        if use_tables:
+            ent = self._tables["entity"]
+            st = L.evi_gather_rows(ent.data_ptr(), 0, ent.size(0), node_embedding_ids.data_ptr(),
+                                   node_embedding_ids.data_ptr(), p["non_text"].data_ptr(), N, d,
+                                   x_nodes.data_ptr(), fmt, flags.data_ptr(), stream)
+        else:
+            node_embeddings = node_embeddings.to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
+            if node_embeddings.size(0) != N:
+                raise ValueError(f"node_embeddings rows {node_embeddings.size(0)} != node_embedding_ids {N}")
+            st = L.evi_gather_rows(node_embeddings.data_ptr(), 1, N, None, node_embedding_ids.data_ptr(),
+                                   p["non_text"].data_ptr(), N, d, x_nodes.data_ptr(), fmt, flags.data_ptr(), stream)
+        _lib.check(st, "evi_gather_rows(nodes)")
+        self._pending_flags = True
+        node_repr = torch.empty((N, d), dtype=dt, device=dev)
+        self._project(x_nodes, p["we"], p["be"], [_lib.ACT_TANH] * 4, out16=node_repr, p=p)
+        del x_nodes
+
+        if use_tables:
+            rel_in = self._tables["relation"]
+            rel_slot32 = torch.empty(E, dtype=torch.int32, device=dev)
+            rel_slot32.copy_(edge_attr_dev)
+        else:
+            # per-edge relation rows, as the reference projects them (retriever.py:441)
+            edge_embeddings = edge_embeddings.to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
+            if edge_embeddings.size(0) != E:
+                raise ValueError(f"edge_embeddings rows {edge_embeddings.size(0)} != edges {E}")
+            rel_in = torch.empty((E, d), dtype=dt, device=dev)
+            _lib.check(L.evi_convert_f32(edge_embeddings.data_ptr(), rel_in.data_ptr(), E * d, fmt, stream),
+                       "evi_convert_f32")
+            rel_slot32 = torch.arange(E, dtype=torch.int32, device=dev)
+        rel_repr = torch.empty((rel_in.size(0), d), dtype=dt, device=dev)
+        self._project(rel_in, p["wr"], p["br"], [_lib.ACT_TANH] * 4, out16=rel_repr, p=p)
+
+        q16 = torch.empty((B, d), dtype=dt, device=dev)
+        _lib.check(L.evi_convert_f32(question_emb.data_ptr(), q16.data_ptr(), B * d, fmt, stream), "evi_convert_f32")
+        qp16 = torch.empty((B, d), dtype=dt, device=dev)
+        self._project(q16, p["wq"], p["bq"], [_lib.ACT_TANH] * 4, out16=qp16, p=p)
+        gate_bias = torch.empty((B, 2 * d), dtype=torch.float32, device=dev)
+        self._project(qp16, p["wgb"], p["bgb"], [_lib.ACT_SIGMOID] * 4 + [_lib.ACT_TANH] * 4, out32=gate_bias, p=p)
+
+        # ---- a3: DDE structure features ------------------------------------------------------
+        topic = getattr(batch, "topic_one_hot", None)
+        if topic is None:
+            raise ValueError("topic_one_hot is required for DDE-based structure features.")
+        if not torch.is_tensor(topic):
+            topic = torch.as_tensor(topic, dtype=torch.float32)
+        topic = topic.to(device=dev, dtype=torch.float32)
+        if topic.dim() == 1:
+            topic = topic.unsqueeze(-1)
+        if topic.dim() != 2:
+            raise ValueError(f"topic_one_hot must be 2D (N, C), got shape {tuple(topic.shape)}")
+        if topic.size(0) != N:
+            raise ValueError(f"topic_one_hot first dim {topic.size(0)} != num_nodes {N}")
+        if topic.size(-1) < self.num_topics:
+            raise ValueError(
+                f"topic_one_hot feature dim {topic.size(-1)} < num_topics={self.num_topics}; "
+                "rebuild g_retrieval caches or update configs/build_retrieval_pipeline.yaml."
+            )
+        topic = topic.contiguous()
+        rev = getattr(batch, "reverse_edge_index", None)
+        if rev is not None and torch.is_tensor(rev):
+            raise NotImplementedError("reverse_edge_index override is not supported (the dataset never sets it).")
+        ns_dim = 2 * (1 + self.dde.num_rounds + self.dde.num_reverse_rounds)
+        node_struct = torch.empty((N, ns_dim), dtype=torch.float32, device=dev)
+        dde_ws = self._workspace(int(L.evi_dde_workspace_bytes(N)), dev)
+        st = L.evi_dde_forward(head32.data_ptr(), tail32.data_ptr(), E, N, topic.data_ptr(), topic.size(1),
+                               self.dde.num_rounds, self.dde.num_reverse_rounds, node_struct.data_ptr(),
+                               dde_ws.data_ptr(), dde_ws.numel(), stream)
+        _lib.check(st, "evi_dde_forward")
+
+        # ---- a5/a6: edge scoring -------------------------------------------------------------
+        direction = {"bidirectional": _lib.DIR_BIDIRECTIONAL, "forward": _lib.DIR_FORWARD,
+                     "backward": _lib.DIR_BACKWARD}[self.direction_mode]
+        logits = torch.empty(E, dtype=torch.float32, device=dev)
+        logits_fwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_BACKWARD else None
+        logits_bwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_FORWARD else None
+        feats = torch.empty((E, self.hidden_dim), dtype=torch.float32, device=dev) if return_features else None
+        per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features))) / float(1 << 20)
+        chunk = max(1024, min(E, int(self.max_workspace_bytes / per_edge) // 1024 * 1024))
+        ws = self._workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features))), dev)
+        a = _lib.ScoreArgs()
+        a.emb_dim, a.hidden_dim, a.direction, a.operand_format = d, self.hidden_dim, direction, fmt
+        a.want_features, a.ns_dim, a.num_sms = int(return_features), ns_dim, p["num_sms"]
+        a.num_nodes, a.num_rel_rows, a.num_questions, a.flags = N, int(rel_repr.size(0)), B, flags.data_ptr()
+        a.node_repr16, a.rel_repr16 = node_repr.data_ptr(), rel_repr.data_ptr()
+        a.gate_bias32, a.node_struct = gate_bias.data_ptr(), node_struct.data_ptr()
+        a.struct_w_t, a.struct_b = p["ws_t"].data_ptr(), p["bs"].data_ptr()
+        a.struct_ln_g, a.struct_ln_b = p["ls_g"].data_ptr(), p["ls_b"].data_ptr()
+        a.nav_w, a.nav_b = p["wn"].data_ptr(), p["bn"]
+        a.w1_main16, a.w1_dist_col, a.w1_bias = p["w1"].data_ptr(), p["w1d"].data_ptr(), p["b1"].data_ptr()
+        a.ln1_g, a.ln1_b, a.head_v, a.head_c0 = p["l1_g"].data_ptr(), p["l1_b"].data_ptr(), p["v"].data_ptr(), p["c0"]
+        a.w2_16, a.w2_bias, a.head_w, a.head_b = p["w2"].data_ptr(), p["b2"].data_ptr(), p["wo"].data_ptr(), p["bo"]
+        a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+        for s in range(0, E, chunk):
+            n = min(chunk, E - s)
+            a.num_edges = n
+            a.head32, a.tail32 = head32.data_ptr() + 4 * s, tail32.data_ptr() + 4 * s
+            a.qid32, a.rel_slot32 = qid32.data_ptr() + 4 * s, rel_slot32.data_ptr() + 4 * s
+            a.logits = logits.data_ptr() + 4 * s
+            a.logits_fwd = logits_fwd.data_ptr() + 4 * s if logits_fwd is not None else None
+            a.logits_bwd = logits_bwd.data_ptr() + 4 * s if logits_bwd is not None else None
+            a.edge_embeddings = feats.data_ptr() + 4 * s * self.hidden_dim if feats is not None else None
+            _lib.check(L.evi_score_edges(C.byref(a), stream), "evi_score_edges")
+        self._pending_flags = True
+
+        # ---- a7: hide-and-seek bias (eval only when apply_in_eval; retriever.py:247-256) ----
+        logits_ref = logits_fwd if logits_fwd is not None else logits_bwd
+        edge_bias = self._compute_hide_seek_bias(batch, edge_index=edge_index, logits=logits_ref)
+        if edge_bias is not None:
+            # the same bias on both directions leaves the softmax weights unchanged
+            logits = logits + edge_bias
+            logits_fwd = logits_fwd + edge_bias if logits_fwd is not None else None
+            logits_bwd = logits_bwd + edge_bias if logits_bwd is not None else None
+        if self.direction_mode == "forward":
+            logits = logits_fwd
+        elif self.direction_mode == "backward":
+            logits = logits_bwd
+
+        if self.validate:
+            self.check_flags()
+        output = RetrieverOutput(
+            logits=logits,
+            query_ids=query_ids,
+            relation_ids=edge_attr,
+            logits_fwd=logits_fwd,
+            logits_bwd=logits_bwd,
+            edge_embeddings=feats,
+        )
+        return output, feats
+
+    # ---- a7 helpers: same semantics as retriever.py:291-367 -----------------------------------
+    def _init_hide_seek(self, hide_seek_cfg: Optional[Dict[str, Any]]) -> None:
+        cfg = hide_seek_cfg or {}
+        self.hide_seek_enabled = bool(cfg.get("enabled", False))
+        self.hide_seek_apply_in_eval = bool(cfg.get("apply_in_eval", False))
+        self.hide_seek_p_near = float(cfg.get("p_near", 0.0))
+        self.hide_seek_p_far = float(cfg.get("p_far", 0.0))
+        self.hide_seek_bias_near = float(cfg.get("bias_near", 0.0))
+        self.hide_seek_bias_far = float(cfg.get("bias_far", 0.0))
+        for name, prob in {"p_near": self.hide_seek_p_near, "p_far": self.hide_seek_p_far}.items():
+            if prob < 0.0 or prob > 1.0:
+                raise ValueError(f"hide_seek_cfg.{name} must be in [0, 1], got {prob}")
+        for name, bias in {"bias_near": self.hide_seek_bias_near, "bias_far": self.hide_seek_bias_far}.items():
+            if bias > 0.0:
+                raise ValueError(f"hide_seek_cfg.{name} must be <= 0 (penalty), got {bias}")
+
+    def _should_apply_hide_seek(self) -> bool:
+        if not self.hide_seek_enabled:
+            return False
+        if self.training:
+            return True
+        return self.hide_seek_apply_in_eval
+
+    def _compute_hide_seek_bias(self, batch: Any, *, edge_index: torch.Tensor, logits: torch.Tensor):
+        if not self._should_apply_hide_seek():
+            return None
+        edge_is_near = getattr(batch, "edge_is_near", None)
+        if edge_is_near is None:
+            q_local = getattr(batch, "q_local_indices", None)
+            a_local = getattr(batch, "a_local_indices", None)
+            if q_local is None or a_local is None:
+                raise ValueError("Batch missing q_local_indices/a_local_indices required for hide-and-seek.")
+            num_nodes = getattr(batch, "num_nodes", None)
+            if num_nodes is None:
+                raise ValueError("Batch missing num_nodes required for hide-and-seek.")
+            node_mask = torch.zeros(int(num_nodes), device=edge_index.device, dtype=torch.bool)
+            qa = torch.cat([torch.as_tensor(q_local).view(-1), torch.as_tensor(a_local).view(-1)]).to(edge_index.device)
+            if qa.numel() > 0:
+                node_mask[qa.long()] = True  # compute_qa_edge_mask, graph_utils.py:107-153
+            near_mask = node_mask[edge_index[0]] | node_mask[edge_index[1]]
+        else:
+            near_mask = torch.as_tensor(edge_is_near).to(device=edge_index.device, dtype=torch.bool)
+            if near_mask.numel() != edge_index.size(1):
+                raise ValueError(f"edge_is_near length mismatch: {near_mask.numel()} vs edges {edge_index.size(1)}")
+        if near_mask.numel() == 0:
+            return None
+        if self.hide_seek_p_near <= 0.0 and self.hide_seek_p_far <= 0.0:
+            return None
+        if self.hide_seek_bias_near == 0.0 and self.hide_seek_bias_far == 0.0:
+            return None
+        drop_prob = torch.where(near_mask, logits.new_tensor(self.hide_seek_p_near), logits.new_tensor(self.hide_seek_p_far))
+        drop_mask = torch.rand_like(drop_prob) < drop_prob
+        bias_values = torch.where(near_mask, logits.new_tensor(self.hide_seek_bias_near),
+                                  logits.new_tensor(self.hide_seek_bias_far))
+        return torch.where(drop_mask, bias_values, logits.new_zeros(drop_prob.shape))
+
+    def _empty_output(self, *, head_idx: torch.Tensor, return_features: bool):
+        """retriever.py:383-401."""
+        param = next(self.parameters(), None)
+        dtype = param.dtype if param is not None else torch.float32
+        device = head_idx.device
+        empty_logits = torch.empty(0, device=device, dtype=dtype)
+        features = torch.empty((0, self.hidden_dim), device=device, dtype=dtype)
+        output = RetrieverOutput(
+            logits=empty_logits, query_ids=head_idx.new_empty(0), relation_ids=None,
+            logits_fwd=empty_logits, logits_bwd=empty_logits, edge_embeddings=features,
+        )
+        return output, (features if return_features else None)
+
+    @staticmethod
+    def _normalize_core_mode(mode: str) -> str:
+        mode_clean = str(mode or "").strip().lower()
+        if mode_clean in {"geometry", "structured", "full"}:
+            return "geometry"
+        raise ValueError(f"core_mode must be 'geometry' for DDE-based retriever, got {mode!r}")
+
+    @staticmethod
+    def _normalize_direction_mode(mode: str) -> str:
+        mode_clean = str(mode or "").strip().lower()
+        if mode_clean in {"bidirectional", "forward", "backward"}:
+            return mode_clean
+        raise ValueError(
+            "direction_mode must be one of {'bidirectional', 'forward', 'backward'}, "
+            f"got {mode!r}."
+        )
+
+
+__all__ = ["Retriever", "RetrieverOutput"]

@@ -1,0 +1,185 @@
+/* evi_rag_b200.h — C ABI of libevi_rag_b200.so (sm_100a kernels for EVI-RAG's retrieval hot path).
+ *
+ * The reference (Martin1007Wang/EVI-RAG) is pure Python: it has no FFI / plugin registry for
+ * this path, so there is no existing binding to mirror. Each entry point below replaces the
+ * arithmetic of one reference function (cited file:line, relative to the reference root); the
+ * Python host side in evi-rag_b200/ keeps the reference's call signatures and error behaviour
+ * and calls these through ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns all memory
+ *   - the library keeps no global state and allocates nothing; all work is enqueued on `stream`
+ *   - return value: EVI_OK or an EVI_ERR_* code; data-dependent validation failures are
+ *     reported through a device-side `flags` word (EVI_FLAG_* bits) that the caller reads back
+ *   - operand_format: EVI_FMT_F16 / EVI_FMT_BF16 — the 16-bit tensor-core operand type
+ */
+#ifndef EVI_RAG_B200_H_
+#define EVI_RAG_B200_H_
+
+#include <stddef.h>
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EVI_OK 0
+#define EVI_ERR_INVALID_ARG 1
+#define EVI_ERR_CUDA 2
+#define EVI_ERR_WORKSPACE 3
+#define EVI_ERR_UNSUPPORTED 4
+
+#define EVI_FLAG_OUT_OF_RANGE 1u /* graph_utils.py:66-77, retriever.py:594-604 */
+#define EVI_FLAG_CROSS_GRAPH 2u  /* graph_utils.py:78-88 */
+#define EVI_FLAG_NOT_MONOTONE 4u /* graph_utils.py:89-99 */
+
+#define EVI_FMT_F16 0
+#define EVI_FMT_BF16 1
+
+#define EVI_DIR_BIDIRECTIONAL 0 /* retriever.py:258-276 direction_mode */
+#define EVI_DIR_FORWARD 1
+#define EVI_DIR_BACKWARD 2
+
+#define EVI_ACT_NONE 0
+#define EVI_ACT_TANH 1
+#define EVI_ACT_SIGMOID 2
+
+#define EVI_TOPK_RAW 0     /* metrics flavour: raw logits, retriever_metrics.py:145 */
+#define EVI_TOPK_SIGMOID 1 /* writer flavour: sigmoid(logits), retriever_topk_edge_writer.py:203 */
+
+int evi_abi_version(void);
+
+/* ---- graph ------------------------------------------------------------------------------- */
+
+/* compute_edge_batch — src/utils/graph_utils.py:49-104 and the range check of
+ * Retriever._compute_query_ids — src/models/components/retriever.py:594-604.
+ * edge_index [2,E] i64, ptr [B+1] i64  ->  edge_batch64 [E] i64 (query_ids), int32 copies of
+ * head / tail / question id for the kernels, edge_ptr [B+1] i64. Any output may be NULL. */
+int evi_edge_batch(const long long* edge_index, long long num_edges, const long long* ptr, int num_graphs,
+                   long long* edge_batch64, int* qid32, int* head32, int* tail32, long long* edge_ptr,
+                   unsigned* flags, cudaStream_t stream);
+
+/* DDE.forward + _build_node_structure_features — src/models/components/graph.py:26-74,
+ * src/models/components/retriever.py:519-553. topic_one_hot [N, ld_topic] f32 (first 2 columns
+ * used) -> node_struct [N, 2*(1+Rf+Rr)] f32. */
+size_t evi_dde_workspace_bytes(int num_nodes);
+int evi_dde_forward(const int* head32, const int* tail32, long long num_edges, int num_nodes,
+                    const float* topic_one_hot, int ld_topic, int num_rounds, int num_reverse_rounds,
+                    float* node_struct, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
+/* _build_undirected_adjacency / _build_directed_adjacency —
+ * scripts/build_retrieval_pipeline.py:570-603, as CSR. mode 0 undirected, 1 head->tail,
+ * 2 tail->head. row_ptr [N+1], adj [2E or E], scratch_counts [N]. */
+int evi_build_csr(const int* head32, const int* tail32, long long num_edges, int num_nodes, int mode,
+                  int* row_ptr, int* adj, int* scratch_counts, cudaStream_t stream);
+
+/* _bfs_dist — scripts/build_retrieval_pipeline.py:610-631. One CTA per job; a job is one
+ * question's node range plus a list of question-local source ids. dist_out[job_dist_off[j] + v]
+ * = hop distance or -1; max_depth < 0: uncapped. queue_workspace: 2 ints per dist element. */
+int evi_bfs_multi_source(const int* row_ptr, const int* adj, int num_jobs, const int* job_node_begin,
+                         const int* job_node_end, const long long* job_dist_off, const int* job_src_ptr,
+                         const int* sources, int max_depth, int* dist_out, int* queue_workspace,
+                         cudaStream_t stream);
+
+/* _select_shortest_edges_undirected / _directed + the mask OR of
+ * _shortest_path_union_mask_by_pair — scripts/build_retrieval_pipeline.py:650-752, 755-815.
+ * One CTA per (start, answer) pair; pair_count/pair_len = -1 for unreachable pairs. */
+int evi_shortest_path_pairs(const int* head32, const int* tail32, int num_pairs, const int* pair_edge_begin,
+                            const int* pair_edge_end, const int* pair_node_begin, const int* pair_num_nodes,
+                            const long long* pair_ds_off, const long long* pair_da_off,
+                            const int* pair_answer_local, const long long* pair_out_off, const int* dist,
+                            int directed, unsigned char* mask, unsigned char* pair_member, int* pair_count,
+                            int* pair_len, cudaStream_t stream);
+
+/* ---- scoring ----------------------------------------------------------------------------- */
+
+/* Embedding feed — src/data/components/embedding_store.py:101-150 (index_select of table rows)
+ * moved onto the device: dst16[r] = src[ids[r]] converted to the operand format. Rows whose
+ * sub_mask_ids[r] == 0 take sub_row (non_text_entity_emb, retriever.py:499-506). */
+int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const long long* ids,
+                    const long long* sub_mask_ids, const float* sub_row, int num_rows, int dim, void* dst16,
+                    int operand_format, unsigned* flags, cudaStream_t stream);
+int evi_convert_f32(const float* src, void* dst16, long long count, int operand_format, cudaStream_t stream);
+
+/* EmbeddingProjector / q_gate / q_bias — src/models/components/projections.py:9-40,
+ * retriever.py:157-158,436-441: out = act(x W^T + b) on tcgen05. w16 is [out_dim, in_dim]
+ * (nn.Linear layout). act_per_block[8]: activation per 256 output columns. */
+int evi_project(const void* x16, int num_rows, const void* w16, int out_dim, int in_dim, const float* bias,
+                const int* act_per_block, void* out16, float* out32, int operand_format, int num_sms,
+                cudaStream_t stream);
+
+/* _score_edges + _encode_structure + _combine_directional_outputs —
+ * src/models/components/retriever.py:453-495, 369-381. */
+typedef struct evi_score_args {
+  long long num_edges;
+  int emb_dim, hidden_dim;          /* 1024 / 1024 */
+  int direction;                    /* EVI_DIR_* */
+  int operand_format;               /* EVI_FMT_* */
+  int want_features;                /* 1: also produce edge_embeddings [E, H] f32 */
+  int ns_dim;                       /* node_struct width = 2*(1+Rf+Rr) */
+  int num_sms;
+  int num_nodes, num_rel_rows, num_questions; /* row counts of node_repr16 / rel_repr16 / gate_bias32 */
+  unsigned* flags;                  /* EVI_FLAG_OUT_OF_RANGE if an edge indexes outside those */
+  /* per-edge indices */
+  const int* head32;
+  const int* tail32;
+  const int* qid32;
+  const int* rel_slot32;            /* row of rel_repr16 for each edge */
+  /* projected operands */
+  const void* node_repr16;          /* [N, D] tanh(entity_proj) */
+  const void* rel_repr16;           /* [R, D] tanh(relation_proj) */
+  const float* gate_bias32;         /* [B, 2D] sigmoid(q_gate(q)) | tanh(q_bias(q)) */
+  const float* node_struct;         /* [N, ns_dim] */
+  /* weights (prepared once per checkpoint) */
+  const float* struct_w_t;          /* [2*ns_dim, D] struct_proj.0.weight^T */
+  const float* struct_b;            /* [D] */
+  const float* struct_ln_g;         /* [D] struct_proj.1 */
+  const float* struct_ln_b;
+  const float* nav_w;               /* [D] struct_gate_net.0.weight */
+  float nav_b;
+  const void* w1_main16;            /* [H, 3D] state_net.0.weight[:, :3D] */
+  const float* w1_dist_col;         /* [H] state_net.0.weight[:, 3D] */
+  const float* w1_bias;             /* [H] */
+  const float* ln1_g;               /* [H] state_net.1 */
+  const float* ln1_b;
+  const float* head_v;              /* [H] state_net.4.weight^T score_head.weight */
+  float head_c0;                    /* score_head.weight . state_net.4.bias + score_head.bias */
+  const void* w2_16;                /* [H, H] state_net.4.weight (features path) */
+  const float* w2_bias;             /* [H] */
+  const float* head_w;              /* [H] score_head.weight */
+  float head_b;
+  /* outputs */
+  float* logits;                    /* [E] */
+  float* logits_fwd;                /* [E] or NULL */
+  float* logits_bwd;                /* [E] or NULL */
+  float* edge_embeddings;           /* [E, H] or NULL */
+  void* workspace;
+  size_t workspace_bytes;
+} evi_score_args;
+
+size_t evi_score_workspace_bytes(long long num_edges, int direction, int want_features);
+int evi_score_edges(const evi_score_args* args, cudaStream_t stream);
+
+/* ---- ragged top-k ------------------------------------------------------------------------ */
+
+/* Per question q: k_top = min(E_q, k); descending score, ascending index on ties
+ * (torch.topk call sites: src/metrics/retriever_metrics.py:145,246, src/metrics/reachability.py:147,
+ * src/callbacks/retriever_topk_edge_writer.py:302; tie rule of the stable argsort in
+ * src/data/components/g_agent_builder.py:640-652). values [B,k] f32 (pad -inf),
+ * indices [B,k] i32 question-local (pad -1), counts [B] i32. k <= 1024. */
+int evi_segmented_topk(const float* scores, const long long* edge_ptr, int num_graphs, int k, int transform,
+                       float* values, int* indices, int* counts, cudaStream_t stream);
+
+/* Writer payload gather — src/callbacks/retriever_topk_edge_writer.py:303-310: for every selected
+ * edge the (head, relation, tail) global ids, label, fwd/bwd logits. All outputs [B,k]. */
+int evi_topk_gather_payload(const int* indices, const int* counts, const long long* edge_ptr, int num_graphs,
+                            int k, const long long* edge_index, long long num_edges,
+                            const long long* node_global_ids, const long long* edge_attr, const float* labels,
+                            const float* logits_fwd, const float* logits_bwd, long long* head_ids,
+                            long long* tail_ids, long long* relation_ids, float* out_labels,
+                            float* out_logits_fwd, float* out_logits_bwd, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EVI_RAG_B200_H_ */

@@ -1,0 +1,352 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle and the golden vectors
+produced by the unmodified reference. Tolerances are stated next to each check."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import evi_oracle as orc
+from evi_rag_b200.synthetic import generate_questions, tiny_spec
+from evi_rag_b200.weights import make_state_dict
+
+pytestmark = pytest.mark.gpu
+
+# scores: |gpu - oracle| <= tol * max|oracle| over the batch (north star: 1e-3 relative)
+SCORE_TOL = {"fp16": 1.0e-3, "bf16": 8.0e-3}
+
+
+def _g(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=False)
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda", 0)
+
+
+# ------------------------------------------------------------------ tcgen05 GEMM
+@pytest.mark.parametrize("fmt_name", ["fp16", "bf16"])
+@pytest.mark.parametrize("m", [1, 127, 128, 129, 300, 1111])
+def test_project_matches_matmul(dev, fmt_name, m):
+    from evi_rag_b200 import lib
+
+    L = lib.load()
+    dt = torch.float16 if fmt_name == "fp16" else torch.bfloat16
+    fmt = lib.FMT_F16 if fmt_name == "fp16" else lib.FMT_BF16
+    g = torch.Generator(device="cpu").manual_seed(m)
+    k, n = 1024, 2048
+    x = (torch.randn(m, k, generator=g) * 0.5).to(dt).to(dev)
+    w = (torch.randn(n, k, generator=g) / 32).to(dt).to(dev)
+    b = torch.randn(n, generator=g).to(dev)
+    out32 = torch.full((m, n), float("nan"), device=dev)
+    out16 = torch.zeros((m, n), dtype=dt, device=dev)
+    acts = [lib.ACT_SIGMOID] * 2 + [lib.ACT_TANH] * 2 + [lib.ACT_NONE] * 4
+    st = L.evi_project(x.data_ptr(), m, w.data_ptr(), n, k, b.data_ptr(), (C.c_int * 8)(*acts), out16.data_ptr(),
+                       out32.data_ptr(), fmt, 148, torch.cuda.current_stream().cuda_stream)
+    assert st == 0
+    torch.cuda.synchronize()
+    ref = x.float() @ w.float().t() + b
+    ref[:, :512] = torch.sigmoid(ref[:, :512])
+    ref[:, 512:1024] = torch.tanh(ref[:, 512:1024])
+    err = (out32 - ref).abs().max().item()
+    assert err < 2e-4, f"fp32 output max abs err {err}"  # same products, fp32 accumulation order only
+    assert (out16.float() - ref).abs().max().item() < (2e-3 if fmt_name == "fp16" else 3e-2) * max(1.0, ref.abs().max().item())
+
+
+def test_project_k3072_and_small_n(dev):
+    from evi_rag_b200 import lib
+
+    L = lib.load()
+    g = torch.Generator(device="cpu").manual_seed(5)
+    m, k, n = 515, 3072, 1024
+    x = (torch.randn(m, k, generator=g) * 0.3).half().to(dev)
+    w = (torch.randn(n, k, generator=g) / 55).half().to(dev)
+    b = torch.randn(n, generator=g).to(dev)
+    out32 = torch.empty((m, n), device=dev)
+    st = L.evi_project(x.data_ptr(), m, w.data_ptr(), n, k, b.data_ptr(), (C.c_int * 8)(*[0] * 8), None,
+                       out32.data_ptr(), lib.FMT_F16, 148, torch.cuda.current_stream().cuda_stream)
+    assert st == 0
+    ref = x.float() @ w.float().t() + b
+    assert (out32 - ref).abs().max().item() < 3e-4
+
+
+# ------------------------------------------------------------------ a1 edge_batch
+def test_edge_batch_golden_and_errors(dev, golden_dir):
+    from evi_rag_b200.graph import compute_edge_batch
+
+    g = _g(golden_dir, "edge_batch.npz")
+    eb, ep = compute_edge_batch(torch.from_numpy(g["edge_index"]), node_ptr=torch.from_numpy(g["ptr"]),
+                                num_graphs=4, device=dev)
+    assert eb.dtype == torch.long and ep.dtype == torch.long
+    assert np.array_equal(eb.cpu().numpy(), g["edge_batch"])
+    assert np.array_equal(ep.cpu().numpy(), g["edge_ptr"])
+    for tag, frag in (("cross", "crosses graph boundaries"), ("order", "not non-decreasing"), ("range", "out-of-range")):
+        with pytest.raises(ValueError, match=frag):
+            compute_edge_batch(torch.from_numpy(g[f"bad_{tag}"]), node_ptr=torch.from_numpy(g["ptr"]),
+                               num_graphs=4, device=dev)
+
+
+def test_edge_batch_large_random(dev):
+    from evi_rag_b200.graph import GraphBatch
+
+    qb = generate_questions(tiny_spec(64, 400, seed=3))
+    gb = GraphBatch.from_edge_index(qb.edge_index, qb.ptr, device=dev)
+    eb, ep = orc.compute_edge_batch(qb.edge_index, qb.ptr)
+    assert np.array_equal(gb.edge_batch.cpu().numpy(), eb)
+    assert np.array_equal(gb.edge_ptr.cpu().numpy(), ep) and np.array_equal(ep, qb.edge_ptr)
+    assert np.array_equal(gb.head32.cpu().numpy(), qb.edge_index[0].astype(np.int32))
+
+
+# ------------------------------------------------------------------ a3 DDE
+def test_dde_golden(dev, golden_dir):
+    from evi_rag_b200.graph import GraphBatch, dde_node_features
+
+    g = _g(golden_dir, "dde.npz")
+    n = g["topic"].shape[0]
+    gb = GraphBatch.from_edge_index(g["edge_index"], np.array([0, n]), device=dev)
+    for rf, rr in [(2, 2), (4, 4), (1, 0), (0, 0)]:
+        ns = dde_node_features(gb, torch.from_numpy(g["topic"]), rf, rr).cpu().numpy()
+        # exact rationals up to fp32 summation order
+        np.testing.assert_allclose(ns, g[f"ns_{rf}_{rr}"], atol=1e-6, rtol=0)
+
+
+def test_dde_batch_vs_oracle_and_deterministic(dev):
+    from evi_rag_b200.graph import GraphBatch, dde_node_features
+
+    qb = generate_questions(tiny_spec(16, 800, seed=9))
+    gb = GraphBatch.from_edge_index(qb.edge_index, qb.ptr, device=dev)
+    ns1 = dde_node_features(gb, torch.from_numpy(qb.topic_one_hot), 2, 2)
+    ns2 = dde_node_features(gb, torch.from_numpy(qb.topic_one_hot), 2, 2)
+    assert torch.equal(ns1, ns2)  # integer atomics: run-to-run bit-identical
+    ref = orc.dde_node_features(torch.from_numpy(qb.topic_one_hot), torch.from_numpy(qb.edge_index), 2, 2)
+    np.testing.assert_allclose(ns1.cpu().numpy(), ref.numpy(), atol=1e-6, rtol=0)
+
+
+# ------------------------------------------------------------------ a13-a15 BFS + labels
+def test_bfs_and_labels_golden(dev, golden_dir):
+    from evi_rag_b200 import graph as G
+
+    g = _g(golden_dir, "bfs.npz")
+    for ci in range(int(g["num_cases"])):
+        n = int(g[f"c{ci}_n"])
+        src, dst = g[f"c{ci}_src"].tolist(), g[f"c{ci}_dst"].tolist()
+        sources, targets = g[f"c{ci}_sources"].tolist(), g[f"c{ci}_targets"].tolist()
+        assert G.bfs_dist_edges(n, src, dst, sources) == g[f"c{ci}_dist_u"].tolist()
+        assert G.bfs_dist_edges(n, src, dst, sources, directed=True) == g[f"c{ci}_dist_d"].tolist()
+        adj = orc.build_undirected_adjacency(n, src, dst)
+        assert G._bfs_dist(n, adj, sources) == g[f"c{ci}_dist_u"].tolist()
+        for mode in ("undirected", "qa_directed"):
+            res = G._shortest_path_union_mask_by_pair_mode(n, src, dst, sources, targets, path_mode=mode)
+            pre = f"c{ci}_{mode}"
+            for got, key in zip(res, ("mask", "ps", "pa", "ids", "cnt", "len")):
+                assert np.array_equal(np.asarray(got), g[f"{pre}_{key}"]), (ci, mode, key)
+    triples = [("a", "r1", "b"), ("b", "r2", "c"), ("d", "r3", "c"), ("e", "r1", "f")]
+    cases = [
+        (["a"], ["c"], "undirected"), (["a"], ["d"], "undirected"), (["a"], ["d"], "qa_directed"),
+        (["a"], ["f"], "undirected"), (["zz"], ["c"], "undirected"), (["c"], ["a"], "qa_directed"),
+        (["a", "e"], ["f"], "qa_directed"),
+    ]
+    assert [G.has_connectivity(triples, s, a, path_mode=m) for s, a, m in cases] == g["has_connectivity"].tolist()
+
+
+def test_batched_bfs_and_labels_vs_oracle(dev):
+    from evi_rag_b200 import graph as G
+
+    qb = generate_questions(tiny_spec(24, 700, seed=4))
+    gb = G.GraphBatch.from_edge_index(qb.edge_index, qb.ptr, device=dev)
+    for cap in (-1, 2):
+        dist = G.batched_bfs(gb, qb.q_local_indices, qb.q_ptr, max_depth=cap).cpu().numpy()
+        for b in range(qb.num_graphs):
+            n0, n1, e0, e1 = qb.ptr[b], qb.ptr[b + 1], qb.edge_ptr[b], qb.edge_ptr[b + 1]
+            s = qb.q_local_indices[qb.q_ptr[b]:qb.q_ptr[b + 1]] - n0
+            ref = orc.bfs_dist_np(n1 - n0, qb.edge_index[0, e0:e1] - n0, qb.edge_index[1, e0:e1] - n0, s, max_depth=cap)
+            assert np.array_equal(dist[n0:n1], ref), (b, cap)  # bit-exact
+    for mode in ("undirected", "qa_directed"):
+        mask = G.batched_shortest_path_labels(gb, qb.q_local_indices, qb.q_ptr, qb.a_local_indices, qb.a_ptr,
+                                              path_mode=mode).cpu().numpy()
+        ref = orc.labels_for_batch(qb, directed=(mode == "qa_directed"))
+        assert np.array_equal(mask.astype(np.float32), ref), mode
+
+
+# ------------------------------------------------------------------ a10-a12 top-k
+def test_segmented_topk_exact(dev):
+    from evi_rag_b200.topk import segmented_topk
+
+    rng = np.random.default_rng(1)
+    sizes = [0, 7, 300, 1, 1500, 100, 101, 5000, 0, 20000]
+    edge_ptr = np.concatenate([[0], np.cumsum(sizes)])
+    scores = rng.standard_normal(edge_ptr[-1]).astype(np.float32)
+    scores[10:40] = scores[10]            # ties inside a segment
+    scores[2000:7000:3] = 0.25            # many ties straddling the k-th place
+    scores[1900] = -0.0
+    scores[1901] = 0.0
+    for k in (1, 100, 500, 1024):
+        tk = segmented_topk(torch.from_numpy(scores).to(dev), torch.from_numpy(edge_ptr).to(dev), k)
+        vals, idx, cnt = orc.segmented_topk(scores, edge_ptr, k)
+        assert np.array_equal(tk.counts.cpu().numpy(), cnt)
+        assert np.array_equal(tk.indices.cpu().numpy(), idx), k  # bit-exact incl. tie order
+        got = tk.values.cpu().numpy()
+        assert np.array_equal(got, vals) or np.array_equal(got.view(np.int32) & 0x7FFFFFFF, vals.view(np.int32) & 0x7FFFFFFF)
+
+
+def test_segmented_topk_sigmoid_and_nan(dev):
+    from evi_rag_b200.topk import segmented_topk
+
+    rng = np.random.default_rng(2)
+    edge_ptr = np.array([0, 900, 1800])
+    logits = (rng.standard_normal(1800) * 6).astype(np.float32)
+    logits[5] = np.nan
+    tk = segmented_topk(torch.from_numpy(logits).to(dev), torch.from_numpy(edge_ptr).to(dev), 100, sigmoid=True)
+    idx = tk.indices.cpu().numpy()
+    assert idx[0, 0] == 5  # NaN is the largest value for torch.topk
+    sig = torch.sigmoid(torch.from_numpy(logits).to(dev)).cpu().numpy()
+    _, ref_idx, _ = orc.segmented_topk(sig, edge_ptr, 100)
+    got_vals = tk.values.cpu().numpy()
+    for b in range(2):
+        # sigmoid may differ by an ulp between implementations: compare sets modulo the boundary value
+        a, r = set(idx[b].tolist()), set(ref_idx[b].tolist())
+        kth = np.sort(sig[edge_ptr[b]:edge_ptr[b + 1]][~np.isnan(sig[edge_ptr[b]:edge_ptr[b + 1]])])[::-1][99]
+        for i in a ^ r:
+            assert abs(sig[edge_ptr[b] + i] - kth) <= 1e-6
+        v = got_vals[b][~np.isnan(got_vals[b])]
+        assert np.all(v[:-1] >= v[1:])  # sorted
+
+
+# ------------------------------------------------------------------ a4-a8 scorer
+def _batch_from_golden(g, dev, with_rows=True):
+    import types
+
+    b = types.SimpleNamespace()
+    b.edge_index = torch.from_numpy(g["edge_index"])
+    b.ptr = torch.from_numpy(g["ptr"])
+    b.question_emb = torch.from_numpy(g["question_emb"])
+    b.node_embedding_ids = torch.from_numpy(g["node_embedding_ids"])
+    b.edge_attr = torch.from_numpy(g["edge_attr"])
+    b.topic_one_hot = torch.from_numpy(g["topic_one_hot"])
+    if with_rows:
+        b.node_embeddings = torch.from_numpy(g["entity_rows"])
+        b.edge_embeddings = torch.from_numpy(g["relation_table"][g["edge_attr"]])
+    return b
+
+
+@pytest.mark.parametrize("tag", ["d1024_init", "d1024_trained"])
+@pytest.mark.parametrize("operand", ["fp16", "bf16"])
+def test_retriever_matches_reference_golden(dev, golden_dir, tag, operand):
+    from evi_rag_b200.retriever import Retriever
+
+    g = _g(golden_dir, f"scorer_{tag}.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    sd = make_state_dict(seed, dim, dim, rf, rr, trained_like=bool(trained))
+    tol = SCORE_TOL[operand]
+    for mode in ("bidirectional", "forward", "backward"):
+        m = Retriever(emb_dim=dim, hidden_dim=dim, direction_mode=mode, operand_dtype=operand,
+                      dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr}, return_edge_embeddings=True).eval()
+        m.load_state_dict(sd, strict=True)
+        m.to(dev)
+        batch = _batch_from_golden(g, dev)
+        out = m(batch)
+        scale = float(np.abs(g[f"{mode}.logits"]).max())
+        err = np.abs(out.logits.cpu().numpy() - g[f"{mode}.logits"]).max()
+        assert err <= tol * scale, (mode, err, scale)
+        assert np.array_equal(out.query_ids.cpu().numpy(), g[f"{mode}.query_ids"])
+        assert out.query_ids.dtype == torch.long and out.relation_ids is batch.edge_attr
+        assert torch.equal(batch.edge_batch, out.query_ids)
+        if mode != "backward":
+            assert np.abs(out.logits_fwd.cpu().numpy() - g[f"{mode}.logits_fwd"]).max() <= tol * scale
+        else:
+            assert out.logits_fwd is None
+        if mode != "forward":
+            assert np.abs(out.logits_bwd.cpu().numpy() - g[f"{mode}.logits_bwd"]).max() <= tol * scale
+        fe = out.edge_embeddings.cpu().numpy()
+        fscale = float(np.abs(g[f"{mode}.feat_head"]).max())
+        assert np.abs(fe[:4] - g[f"{mode}.feat_head"]).max() <= 4 * tol * fscale
+        # the feature path recomputes logits the reference way; the collapsed head must agree with it
+        m.return_edge_embeddings = False
+        out2 = m(_batch_from_golden(g, dev))
+        assert out2.edge_embeddings is None
+        assert (out2.logits - out.logits).abs().max().item() <= tol * scale
+
+
+def test_retriever_table_mode_equals_batch_mode(dev, golden_dir):
+    from evi_rag_b200.retriever import Retriever
+
+    g = _g(golden_dir, "scorer_d1024_trained.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    m = Retriever(emb_dim=dim, hidden_dim=dim).eval()
+    m.load_state_dict(make_state_dict(seed, dim, dim, rf, rr, trained_like=True))
+    m.to(dev)
+    out_rows = m(_batch_from_golden(g, dev))
+    ent = np.zeros((int(g["node_embedding_ids"].max()) + 1, dim), dtype=np.float32)
+    ent[g["node_embedding_ids"]] = g["entity_rows"]
+    ent[0] = 0
+    m.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(g["relation_table"]))
+    out_tab = m(_batch_from_golden(g, dev, with_rows=False))
+    assert torch.equal(out_rows.logits, out_tab.logits)  # same kernels, same operands
+
+
+def test_retriever_vs_oracle_medium_with_topk(dev):
+    """Seeded synthetic questions: scores within tolerance and top-k sets equal modulo the
+    tolerance band around the k-th score (SURVEY §8c parity rule)."""
+    from evi_rag_b200.retriever import Retriever
+    from evi_rag_b200.topk import segmented_topk
+    import types
+
+    spec = tiny_spec(6, 900, seed=21, num_relations=64, num_entities=2000)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(1)
+    ent = (rng.standard_normal((2001, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((64, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(0, trained_like=True)
+    ref = orc.retriever_forward(
+        sd, edge_index=torch.from_numpy(qb.edge_index), ptr=torch.from_numpy(qb.ptr),
+        question_emb=torch.from_numpy(qb.question_emb), node_embeddings=torch.from_numpy(ent[qb.node_embedding_ids]),
+        node_embedding_ids=torch.from_numpy(qb.node_embedding_ids), edge_embeddings=torch.from_numpy(rel[qb.edge_attr]),
+        topic_one_hot=torch.from_numpy(qb.topic_one_hot))
+    m = Retriever(emb_dim=1024, hidden_dim=1024).eval()
+    m.load_state_dict(sd)
+    m.to(dev)
+    m.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(rel))
+    b = types.SimpleNamespace(edge_index=torch.from_numpy(qb.edge_index), ptr=torch.from_numpy(qb.ptr),
+                              question_emb=torch.from_numpy(qb.question_emb),
+                              node_embedding_ids=torch.from_numpy(qb.node_embedding_ids),
+                              edge_attr=torch.from_numpy(qb.edge_attr), topic_one_hot=torch.from_numpy(qb.topic_one_hot))
+    out = m(b)
+    refl = ref.logits.numpy()
+    scale = float(np.abs(refl).max())
+    tol = SCORE_TOL["fp16"] * scale
+    got = out.logits.cpu().numpy()
+    assert np.abs(got - refl).max() <= tol
+    k = 100
+    tk = segmented_topk(out.logits, torch.from_numpy(qb.edge_ptr).to(dev), k)
+    _, ref_idx, ref_cnt = orc.segmented_topk(refl, qb.edge_ptr, k)
+    assert np.array_equal(tk.counts.cpu().numpy(), ref_cnt)
+    idx = tk.indices.cpu().numpy()
+    for q in range(qb.num_graphs):
+        e0 = int(qb.edge_ptr[q])
+        kth = refl[e0 + ref_idx[q, ref_cnt[q] - 1]]
+        for i in set(idx[q, :ref_cnt[q]].tolist()) ^ set(ref_idx[q, :ref_cnt[q]].tolist()):
+            assert abs(refl[e0 + i] - kth) <= 2 * tol, (q, i)
+
+
+def test_retriever_errors_and_empty(dev):
+    from evi_rag_b200.retriever import Retriever
+    import types
+
+    m = Retriever(emb_dim=1024, hidden_dim=1024).eval().to(dev)
+    with pytest.raises(ValueError, match="missing edge_index"):
+        m(types.SimpleNamespace())
+    out = m(types.SimpleNamespace(edge_index=torch.zeros((2, 0), dtype=torch.long)))
+    assert out.logits.numel() == 0 and out.edge_embeddings.shape == (0, 1024) and out.relation_ids is None
+    b = types.SimpleNamespace(edge_index=torch.tensor([[0, 1], [1, 9]]), ptr=torch.tensor([0, 3]),
+                              question_emb=torch.zeros(1, 1024), node_embedding_ids=torch.tensor([1, 2, 0]),
+                              edge_attr=torch.tensor([0, 1]), node_embeddings=torch.zeros(3, 1024),
+                              edge_embeddings=torch.zeros(2, 1024), topic_one_hot=torch.zeros(3, 2))
+    with pytest.raises(ValueError, match="Invalid edge_index range"):
+        m(b)
+    b.edge_index = torch.tensor([[0, 1], [1, 2]])
+    del b.node_embeddings
+    with pytest.raises(ValueError, match="node_embeddings and edge_embeddings"):
+        m(b)

@@ -1,0 +1,122 @@
+"""CPU-only checks: the C-ABI library loads and exports every declared symbol, the host module
+mirrors the reference's constructor / state_dict contract, and the product path refuses to run
+without CUDA (no fallback)."""
+import os
+import re
+import types
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from evi_rag_b200 import lib
+
+    header = open(os.path.join(ROOT, "include", "evi_rag_b200.h"), encoding="utf-8").read()
+    declared = set(re.findall(r"\b(evi_[a-z0-9_]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    L = lib.load()
+    for name in sorted(declared):
+        assert hasattr(L, name), f"{name} declared in include/evi_rag_b200.h but not exported"
+    assert declared == set(lib.PROTOTYPES), declared ^ set(lib.PROTOTYPES)
+    assert L.evi_abi_version() == 1
+    assert L.evi_score_workspace_bytes(1000, lib.DIR_BIDIRECTIONAL, 0) > 1000 * 2 * (3 * 1024 + 1024) * 2
+
+
+def test_score_args_struct_layout_matches_header():
+    from evi_rag_b200 import lib
+
+    header = open(os.path.join(ROOT, "include", "evi_rag_b200.h"), encoding="utf-8").read()
+    body = header[header.index("typedef struct evi_score_args {"):header.index("} evi_score_args;")]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for stmt in body.split("{", 1)[1].split(";"):
+        stmt = stmt.strip()
+        if not stmt:
+            continue
+        for part in stmt.split(","):
+            names.append(re.findall(r"([A-Za-z_][A-Za-z0-9_]*)\s*$", part.strip())[0])
+    assert names == [f[0] for f in lib.ScoreArgs._fields_]
+
+
+def test_state_dict_contract_matches_reference_keys():
+    from evi_rag_b200.retriever import Retriever
+    from evi_rag_b200.weights import make_state_dict, state_dict_shapes
+
+    m = Retriever(emb_dim=1024, hidden_dim=1024, dde_cfg={"num_rounds": 2, "num_reverse_rounds": 2})
+    sd = m.state_dict()
+    expect = dict(state_dict_shapes())
+    expect["parity_meta"] = (4,)
+    assert {k: tuple(v.shape) for k, v in sd.items()} == expect  # SURVEY §8b key list
+    assert sd["parity_meta"].tolist() == [1, 2, 2, 2]
+    m.load_state_dict(make_state_dict(1), strict=True)
+    assert sum(p.numel() for p in m.parameters()) == 9_474_050  # reference model size
+
+
+def test_constructor_validation_like_reference():
+    from evi_rag_b200.retriever import Retriever
+
+    with pytest.raises(ValueError, match="topic_pe must be enabled"):
+        Retriever(8, 8, topic_pe=False)
+    with pytest.raises(ValueError, match="num_topics must be 2"):
+        Retriever(8, 8, num_topics=3)
+    with pytest.raises(ValueError, match="core_mode must be 'geometry'"):
+        Retriever(8, 8, core_mode="dot")
+    with pytest.raises(ValueError, match="direction_mode must be one of"):
+        Retriever(8, 8, direction_mode="both")
+    with pytest.raises(ValueError, match="at most 4 rounds"):
+        Retriever(8, 8, dde_cfg={"num_rounds": 5})
+    with pytest.raises(ValueError, match="must be in \\[0, 1\\]"):
+        Retriever(8, 8, hide_seek_cfg={"p_near": 1.5})
+    with pytest.raises(ValueError, match="must be <= 0"):
+        Retriever(8, 8, hide_seek_cfg={"bias_far": 0.5})
+    m = Retriever(8, 8, some_future_kwarg=1)  # extra kwargs are swallowed (retriever.py:116)
+    assert m.direction_mode == "bidirectional"
+
+
+def test_no_cpu_fallback():
+    from evi_rag_b200.retriever import Retriever
+    from evi_rag_b200.topk import segmented_topk
+
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    m = Retriever(1024, 1024).eval()
+    b = types.SimpleNamespace(edge_index=torch.tensor([[0], [1]]), ptr=torch.tensor([0, 2]),
+                              question_emb=torch.zeros(1, 1024), node_embedding_ids=torch.tensor([1, 2]),
+                              edge_attr=torch.tensor([0]), node_embeddings=torch.zeros(2, 1024),
+                              edge_embeddings=torch.zeros(1, 1024), topic_one_hot=torch.zeros(2, 2))
+    with pytest.raises(RuntimeError, match="CUDA only"):
+        m(b)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        segmented_topk(torch.zeros(4), torch.tensor([0, 4]), 2)
+
+
+def test_product_code_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "evi-rag_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f), encoding="utf-8").read()
+                assert "oracle" not in text.replace("oracle/", "").lower() or f == "weights.py" or \
+                    "import oracle" not in text and "from oracle" not in text, f
+
+
+def test_synthetic_generator_is_deterministic_and_shardable():
+    from evi_rag_b200.synthetic import generate_questions, tiny_spec
+    from oracle import evi_oracle as orc
+
+    spec = tiny_spec(12, 300, seed=3)
+    a = generate_questions(spec)
+    b = generate_questions(spec)
+    assert np.array_equal(a.edge_index, b.edge_index) and np.array_equal(a.question_emb, b.question_emb)
+    eb, ep = orc.compute_edge_batch(a.edge_index, a.ptr)  # valid PyG-style batch
+    assert np.array_equal(ep, a.edge_ptr)
+    assert (a.edge_index[0] != a.edge_index[1]).all()
+    key = (eb * 10**6 + a.edge_index[0]) * 10**6 + a.edge_index[1]
+    assert len(np.unique(key * 100 + a.edge_attr)) == a.num_edges  # no duplicate (h, r, t)
+    s = a.slice(3, 7)
+    assert s.num_graphs == 4 and s.ptr[0] == 0 and s.edge_index.min() >= 0 and s.edge_index.max() < s.num_nodes
+    assert set(np.unique(a.topic_one_hot.sum(1))) == {1.0}
