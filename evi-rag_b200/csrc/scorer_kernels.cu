@@ -258,7 +258,7 @@ struct TailParams {
 };
 
 template <int FMT>
-EVI_DEVINL float tail_one(const uint16_t* __restrict__ zrow, const float2* __restrict__ st, int n_blocks,
+EVI_DEVINL float tail_one(const float* __restrict__ zrow, const float2* __restrict__ st, int n_blocks,
                           const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
   float sum = 0.f, sumsq = 0.f;
   for (int i = 0; i < n_blocks; ++i) {
@@ -269,7 +269,7 @@ EVI_DEVINL float tail_one(const uint16_t* __restrict__ zrow, const float2* __res
   const float var = fmaxf(sumsq * (1.0f / D) - mean * mean, 0.f);
   const float rstd = rsqrtf(var + kLnEps);
   float z[32];
-  load_row16<FMT>(zrow, lane, z);
+  load_row32(zrow, lane, z);
   float acc = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -296,7 +296,7 @@ EVI_DEVINL float tail_one(const uint16_t* __restrict__ zrow, const float2* __res
 
 template <int FMT>
 __global__ void __launch_bounds__(256)
-score_tail_kernel(const uint16_t* __restrict__ z_fwd, const uint16_t* __restrict__ z_bwd,
+score_tail_kernel(const float* __restrict__ z_fwd, const float* __restrict__ z_bwd,
                   const float2* __restrict__ st_fwd, const float2* __restrict__ st_bwd, int n_blocks,
                   long long num_edges, TailParams tp, uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd,
                   float* __restrict__ logits, float* __restrict__ logits_fwd, float* __restrict__ logits_bwd) {
@@ -434,7 +434,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   const int ndir = do_f + do_b;
   const int n_blocks = D / gemm::BN;
   // workspace carve-up: A [ndir*E, 3D] 16-bit | z [ndir*E, D] 16-bit | stats [ndir*E, n_blocks] float2 |
-  //                     dist [ndir*E] f32 | (features) g [ndir*E, D] 16-bit | feat [ndir*E, D] f32
+  //                     (z is fp32) dist [ndir*E] f32 | (features) g [ndir*E, D] 16-bit | feat [ndir*E, D] f32
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
   size_t off = 0;
   auto take = [&](size_t bytes) {
@@ -444,7 +444,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   };
   const size_t rows = static_cast<size_t>(ndir) * E;
   uint16_t* A = reinterpret_cast<uint16_t*>(take(rows * 3 * D * 2));
-  uint16_t* Z = reinterpret_cast<uint16_t*>(take(rows * D * 2));
+  float* Z = reinterpret_cast<float*>(take(rows * D * sizeof(float)));
   float2* ST = reinterpret_cast<float2*>(take(rows * n_blocks * sizeof(float2)));
   float* DIST = reinterpret_cast<float*>(take(rows * sizeof(float)));
   uint16_t* G = nullptr;
@@ -478,7 +478,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   if (check_launch() != kOk) return kErrCuda;
 
   gemm::EpiPreNorm::Params zp;
-  zp.bias = a.w1_bias, zp.w_dist = a.w1_dist_col, zp.dist = DIST, zp.z16 = Z, zp.stats = ST;
+  zp.bias = a.w1_bias, zp.w_dist = a.w1_dist_col, zp.dist = DIST, zp.z32 = Z, zp.stats = ST;
   zp.ldz = D, zp.n_blocks = n_blocks;
   int rc = gemm::launch<FMT, gemm::EpiPreNorm>(A, 3 * D, a.w1_main16, 3 * D, static_cast<int>(rows), D, 3 * D, zp,
                                                a.num_sms, stream);
@@ -486,8 +486,8 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
 
   TailParams tp;
   tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
-  const uint16_t* z_f = do_f ? Z : nullptr;
-  const uint16_t* z_b = do_b ? Z + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
+  const float* z_f = do_f ? Z : nullptr;
+  const float* z_b = do_b ? Z + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
   const float2* st_f = ST;
   const float2* st_b = ST + (do_f ? static_cast<size_t>(E) * n_blocks : 0);
   uint16_t* g_f = G;
@@ -522,7 +522,7 @@ size_t evi_score_workspace_bytes(long long num_edges, int direction, int want_fe
   const size_t ndir = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
   const size_t rows = ndir * static_cast<size_t>(num_edges);
   auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
-  size_t total = al(rows * 3 * D * 2) + al(rows * D * 2) + al(rows * (D / gemm::BN) * sizeof(float2)) +
+  size_t total = al(rows * 3 * D * 2) + al(rows * D * sizeof(float)) + al(rows * (D / gemm::BN) * sizeof(float2)) +
                  al(rows * sizeof(float));
   if (want_features) total += al(rows * D * 2) + al(rows * D * sizeof(float));
   return total + 256;

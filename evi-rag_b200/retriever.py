@@ -305,7 +305,7 @@ class Retriever(nn.Module):
         fmt, dt = self._fmt(), self._op_dtype()
         d = self.emb_dim
         if self._flags is None or self._flags.device != dev:
-            self._flags = torch.zeros(2, dtype=torch.int32, device=dev)
+            self._flags = torch.zeros(1, dtype=torch.int32, device=dev)
         flags = self._flags
 
         question_emb = question_emb.to(device=dev, dtype=torch.float32).contiguous()
