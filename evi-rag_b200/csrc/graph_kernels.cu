@@ -328,8 +328,7 @@ int evi_edge_batch(const long long* edge_index, long long num_edges, const long 
                    long long* edge_batch64, int* qid32, int* head32, int* tail32, long long* edge_ptr,
                    unsigned* flags, cudaStream_t stream) {
   if (num_graphs <= 0 || num_edges < 0 || ptr == nullptr || flags == nullptr) return kErrInvalidArg;
-  if (cudaMemsetAsync(flags, 0, sizeof(unsigned), stream) != cudaSuccess) return kErrCuda;
-  if (num_edges == 0) {
+  if (num_edges == 0) {  // flags is OR-ed into, never cleared: the caller zeroes it
     if (edge_ptr) fill_i64_kernel<<<cdiv(num_graphs + 1, 256), 256, 0, stream>>>(edge_ptr, num_graphs + 1, 0);
     return check_launch();
   }

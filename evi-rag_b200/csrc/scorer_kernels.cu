@@ -480,8 +480,10 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   gemm::EpiPreNorm::Params zp;
   zp.bias = a.w1_bias, zp.w_dist = a.w1_dist_col, zp.dist = DIST, zp.z32 = Z, zp.stats = ST;
   zp.ldz = D, zp.n_blocks = n_blocks;
+  if (a.ev_gemm_begin) cudaEventRecord(static_cast<cudaEvent_t>(a.ev_gemm_begin), stream);
   int rc = gemm::launch<FMT, gemm::EpiPreNorm>(A, 3 * D, a.w1_main16, 3 * D, static_cast<int>(rows), D, 3 * D, zp,
                                                a.num_sms, stream);
+  if (a.ev_gemm_end) cudaEventRecord(static_cast<cudaEvent_t>(a.ev_gemm_end), stream);
   if (rc != kOk) return rc;
 
   TailParams tp;

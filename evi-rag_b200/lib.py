@@ -40,6 +40,7 @@ class ScoreArgs(C.Structure):
         ("head_b", _f),
         ("logits", _vp), ("logits_fwd", _vp), ("logits_bwd", _vp), ("edge_embeddings", _vp),
         ("workspace", _vp), ("workspace_bytes", _sz),
+        ("ev_gemm_begin", _vp), ("ev_gemm_end", _vp),
     ]
 
 
@@ -63,6 +64,42 @@ PROTOTYPES = {
 
 _lib: Optional[C.CDLL] = None
 
+# kernels launched per C-ABI call (bench.py reports the total as `gpu_launches`)
+_KERNELS_PER_CALL = {
+    "evi_edge_batch": lambda a: 1,
+    "evi_dde_forward": lambda a: 1 + (2 if a[2] > 0 else 1) * max(a[6], a[7]),
+    "evi_build_csr": lambda a: 3 if a[2] > 0 else 1,
+    "evi_bfs_multi_source": lambda a: 1,
+    "evi_shortest_path_pairs": lambda a: 1,
+    "evi_gather_rows": lambda a: 1,
+    "evi_convert_f32": lambda a: 1,
+    "evi_project": lambda a: 1,
+    "evi_score_edges": lambda a: 5 if a[0]._obj.want_features else 3,
+    "evi_segmented_topk": lambda a: 1,
+    "evi_topk_gather_payload": lambda a: 1,
+}
+LAUNCHES = {"kernels": 0, "calls": 0}
+
+
+class _Counted:
+    """CDLL facade that counts kernel launches per call."""
+
+    def __init__(self, cdll):
+        self._cdll = cdll
+        for name in PROTOTYPES:
+            fn = getattr(cdll, name)
+            counter = _KERNELS_PER_CALL.get(name)
+            setattr(self, name, self._wrap(fn, counter) if counter else fn)
+
+    @staticmethod
+    def _wrap(fn, counter):
+        def call(*args):
+            LAUNCHES["kernels"] += counter(args)
+            LAUNCHES["calls"] += 1
+            return fn(*args)
+
+        return call
+
 
 def load() -> C.CDLL:
     """Load the library once and attach prototypes. Raises if it has not been built."""
@@ -79,8 +116,8 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    _lib = lib
-    return lib
+    _lib = _Counted(lib)
+    return _lib
 
 
 def check(status: int, what: str) -> None:

@@ -1,0 +1,129 @@
+"""The retrieval hot path as one call: ids in, top-k evidence out.
+
+``RetrievalPipeline.run(batch)`` is the public entry point ``bench.py`` times end to end. Per batch
+of questions it runs, on the current CUDA stream:
+
+  1. edge segmentation / validation               (graph_utils.py:49-104)
+  2. multi-source BFS hop distance from the seeds (build_retrieval_pipeline.py:610-631), depth-capped
+  3. DDE structure features + projections + triple scoring (retriever.py:185-289)
+  4. ragged top-k and the writer's gather         (retriever_topk_edge_writer.py:201-328)
+
+Inputs may be host (pinned) or device tensors with the reference's batch attribute names; outputs
+are fixed-shape ``[B, k]`` arrays (what the reference pickles per graph, as arrays).
+"""
+from __future__ import annotations
+
+import types
+from typing import Any, Dict, Optional
+
+import numpy as np
+import torch
+
+from . import graph as G
+from .retriever import Retriever
+from .topk import segmented_topk, writer_payload
+
+_BATCH_FIELDS = ("edge_index", "edge_attr", "ptr", "node_embedding_ids", "node_global_ids", "topic_one_hot",
+                 "question_emb", "q_local_indices", "q_ptr")
+
+
+def host_batch(qb, pin: bool = True) -> types.SimpleNamespace:
+    """A synthetic ``QuestionBatch`` as (pinned) host tensors under the reference's attribute names."""
+    b = types.SimpleNamespace()
+    for name in _BATCH_FIELDS:
+        t = torch.from_numpy(np.ascontiguousarray(getattr(qb, name)))
+        if pin and torch.cuda.is_available():
+            t = t.pin_memory()
+        setattr(b, name, t)
+    b.num_graphs = qb.num_graphs
+    b.q_ptr_host = np.asarray(qb.q_ptr)
+    b.ptr_host = np.asarray(qb.ptr)
+    return b
+
+
+def device_batch(hb, device) -> types.SimpleNamespace:
+    """Async H2D of every field of a host batch (non_blocking from pinned memory)."""
+    b = types.SimpleNamespace()
+    for name in _BATCH_FIELDS:
+        setattr(b, name, getattr(hb, name).to(device, non_blocking=True))
+    b.num_graphs, b.q_ptr_host, b.ptr_host = hb.num_graphs, hb.q_ptr_host, hb.ptr_host
+    return b
+
+
+def h2d_bytes(hb) -> int:
+    return int(sum(getattr(hb, n).numel() * getattr(hb, n).element_size() for n in _BATCH_FIELDS))
+
+
+class RetrievalPipeline:
+    def __init__(self, model: Retriever, top_k: int = 100, bfs_max_depth: int = 2, writer_scores: bool = True,
+                 validate: bool = True) -> None:
+        self.model = model
+        self.top_k = int(top_k)
+        self.bfs_max_depth = int(bfs_max_depth)
+        self.writer_scores = bool(writer_scores)
+        self.validate = bool(validate)
+        self._out_pinned: Optional[Dict[str, torch.Tensor]] = None
+
+    @torch.no_grad()
+    def run_device(self, b: Any) -> Dict[str, torch.Tensor]:
+        """Inputs already on the device. Returns device tensors."""
+        dev = b.edge_index.device
+        gb = G.GraphBatch.from_edge_index(b.edge_index, b.ptr_host, device=dev, validate=False)
+        # seeds -> question-local ids on the device; jobs = one per question
+        row_ptr, adj = G.build_csr(gb.head32, gb.tail32, gb.num_nodes, G.CSR_UNDIRECTED)
+        local_seeds = b.q_local_indices - torch.repeat_interleave(
+            b.ptr[:-1], (b.q_ptr[1:] - b.q_ptr[:-1]))
+        dist = self._bfs(row_ptr, adj, b, local_seeds)
+        b._evi_graph = gb
+        was = self.model.validate
+        self.model.validate = False
+        try:
+            out = self.model(b)
+        finally:
+            self.model.validate = was
+        tk = segmented_topk(out.logits, gb.edge_ptr, self.top_k, sigmoid=self.writer_scores)
+        res = writer_payload(tk, gb.edge_ptr, edge_index=b.edge_index, node_global_ids=b.node_global_ids,
+                             edge_attr=b.edge_attr, labels=None, logits_fwd=out.logits_fwd,
+                             logits_bwd=out.logits_bwd)
+        res["bfs_dist"] = dist
+        res["flags"] = self.model._flags
+        return res
+
+    def _bfs(self, row_ptr, adj, b, local_seeds):
+        from . import lib as _lib
+
+        L = _lib.load()
+        dev = row_ptr.device
+        B = b.num_graphs
+        ptr32 = b.ptr.to(torch.int32)
+        n_total = int(b.ptr_host[-1])
+        dist = torch.empty(max(1, n_total), dtype=torch.int32, device=dev)
+        queue = torch.empty(max(1, 2 * n_total), dtype=torch.int32, device=dev)
+        st = L.evi_bfs_multi_source(row_ptr.data_ptr(), adj.data_ptr(), B, ptr32.data_ptr(),
+                                    ptr32[1:].contiguous().data_ptr(), b.ptr.data_ptr(),
+                                    b.q_ptr.to(torch.int32).data_ptr(), local_seeds.to(torch.int32).data_ptr(),
+                                    self.bfs_max_depth, dist.data_ptr(), queue.data_ptr(), _lib.stream_handle())
+        _lib.check(st, "evi_bfs_multi_source")
+        return dist[:n_total]
+
+    @torch.no_grad()
+    def run(self, hb: Any, device=None, post_device=None) -> Dict[str, torch.Tensor]:
+        """Host batch in, host (pinned) results out: H2D of the ids, the hot path, D2H of the
+        selected triples and BFS distances. Synchronises before returning."""
+        dev = torch.device(device) if device is not None else self.model._device()
+        b = device_batch(hb, dev)
+        res = self.run_device(b)
+        if post_device is not None:
+            post_device(res)  # e.g. the NCCL gather of the selected triples
+        keys = ("score", "index", "count", "head_id", "tail_id", "relation_id", "logit_fwd", "logit_bwd",
+                "bfs_dist", "flags")
+        out = {k: res[k].to("cpu", non_blocking=True) for k in keys}
+        torch.cuda.current_stream(dev).synchronize()
+        if self.validate:
+            self.model._pending_flags = True
+            self.model.check_flags()
+        return out
+
+    @staticmethod
+    def d2h_bytes(res: Dict[str, torch.Tensor]) -> int:
+        return int(sum(t.numel() * t.element_size() for t in res.values()))

@@ -1,0 +1,65 @@
+"""Multi-GPU: questions are independent units, so the batch shards across ranks with no data-path
+collective (no edge crosses graphs, src/utils/graph_utils.py:78-88). The only exchange is the
+gather of the selected triples and the metric sums — the reference does it with
+``all_gather_object`` pickles (src/callbacks/retriever_topk_edge_writer.py:449-462) and
+torchmetrics ``dist_reduce_fx="sum"`` (src/metrics/retriever_metrics.py:90-91); here it is one
+all-gather of fixed-shape ``[Q, k]`` arrays and one all-reduce of a small vector.
+
+Works with any ``torch.distributed`` backend (NCCL over NVLink on the GPU box, gloo in CPU tests).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def partition_by_edges(edge_counts: Sequence[int], world_size: int) -> List[Tuple[int, int]]:
+    """Contiguous split of the question list so every rank gets ~sum(E_q)/world edges
+    (prefix sum over E_q). Returns ``[(q_begin, q_end)] * world_size``."""
+    counts = np.asarray(edge_counts, dtype=np.int64)
+    n = int(counts.shape[0])
+    if world_size <= 0:
+        raise ValueError("world_size must be positive")
+    prefix = np.concatenate([[0], np.cumsum(counts)])
+    total = int(prefix[-1])
+    bounds = [0]
+    for r in range(1, world_size):
+        target = total * r / world_size
+        q = int(np.searchsorted(prefix, target, side="left"))
+        # pick the closer of the two neighbouring cut points, keep cuts monotone
+        if q > 0 and abs(prefix[q - 1] - target) <= abs(prefix[min(q, n)] - target):
+            q -= 1
+        bounds.append(min(max(q, bounds[-1]), n))
+    bounds.append(n)
+    return [(bounds[r], bounds[r + 1]) for r in range(world_size)]
+
+
+def gather_topk(local: Dict[str, torch.Tensor], num_local_questions: int, group=None) -> Dict[str, torch.Tensor]:
+    """All-gather per-rank ``[Q_r, k]`` (or ``[Q_r]``) arrays into global question order. Ranks may
+    hold different Q_r: arrays are padded to the max and trimmed after the exchange."""
+    world = dist.get_world_size(group)
+    dev = next(iter(local.values())).device
+    q_local = torch.tensor([num_local_questions], dtype=torch.long, device=dev)
+    q_all = [torch.zeros_like(q_local) for _ in range(world)]
+    dist.all_gather(q_all, q_local, group=group)
+    q_all = [int(t.item()) for t in q_all]
+    q_max = max(q_all)
+    out: Dict[str, torch.Tensor] = {}
+    for name, t in local.items():
+        pad_shape = (q_max,) + tuple(t.shape[1:])
+        padded = torch.zeros(pad_shape, dtype=t.dtype, device=dev)
+        padded[: t.shape[0]] = t
+        parts = [torch.empty_like(padded) for _ in range(world)]
+        dist.all_gather(parts, padded, group=group)
+        out[name] = torch.cat([p[:q] for p, q in zip(parts, q_all)], dim=0)
+    return out
+
+
+def allreduce_sums(values: torch.Tensor, group=None) -> torch.Tensor:
+    """Sum a small vector of metric accumulators over ranks (``dist_reduce_fx='sum'``)."""
+    out = values.clone()
+    dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)
+    return out

@@ -155,6 +155,10 @@ typedef struct evi_score_args {
   float* edge_embeddings;           /* [E, H] or NULL */
   void* workspace;
   size_t workspace_bytes;
+  /* optional cudaEvent_t pair recorded on `stream` around the state_net.0 GEMM launch (the
+   * dominant kernel) so a caller can time it without a profiler; NULL to skip */
+  void* ev_gemm_begin;
+  void* ev_gemm_end;
 } evi_score_args;
 
 size_t evi_score_workspace_bytes(long long num_edges, int direction, int want_features);
