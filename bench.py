@@ -234,6 +234,8 @@ def run_ours(args):
     dev_batches = [device_batch(hb, dev) for hb in host_batches]
     torch.cuda.synchronize(dev)
     gemm_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for a, b in gemm_ev:  # torch creates the cudaEvent_t lazily; record once so .cuda_event is a live handle
+        a.record(); b.record()
     for i in range(args.warmup):
         exchange(pipe.run_device(dev_batches[i]), dev_batches[i].num_graphs)
     sync_all()

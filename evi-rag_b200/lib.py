@@ -79,6 +79,8 @@ _KERNELS_PER_CALL = {
     "evi_topk_gather_payload": lambda a: 1,
 }
 LAUNCHES = {"kernels": 0, "calls": 0}
+# EVI_DEBUG_SYNC=1: synchronize around every C-ABI call so a device fault names the call that made it
+_DEBUG_SYNC = os.environ.get("EVI_DEBUG_SYNC", "0") == "1"
 
 
 class _Counted:
@@ -96,7 +98,17 @@ class _Counted:
         def call(*args):
             LAUNCHES["kernels"] += counter(args)
             LAUNCHES["calls"] += 1
-            return fn(*args)
+            if not _DEBUG_SYNC:
+                return fn(*args)
+            import torch
+
+            torch.cuda.synchronize()  # a fault raised here belongs to work queued before this call
+            st = fn(*args)
+            try:
+                torch.cuda.synchronize()
+            except Exception as exc:  # noqa: BLE001
+                raise RuntimeError(f"device fault inside {fn.__name__}: {exc}") from exc
+            return st
 
         return call
 

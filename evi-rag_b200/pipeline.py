@@ -95,13 +95,20 @@ class RetrievalPipeline:
         L = _lib.load()
         dev = row_ptr.device
         B = b.num_graphs
+        # every temporary passed by address stays referenced until the call returns: a tensor freed
+        # between two argument evaluations can be handed back by the caching allocator for the next one
         ptr32 = b.ptr.to(torch.int32)
+        node_end32 = ptr32[1:].contiguous()
+        src_ptr32 = b.q_ptr.to(torch.int32).contiguous()
+        seeds32 = local_seeds.to(torch.int32).contiguous()
+        if seeds32.numel() == 0:
+            seeds32 = torch.zeros(1, dtype=torch.int32, device=dev)
+        dist_off = b.ptr.to(torch.long).contiguous()
         n_total = int(b.ptr_host[-1])
         dist = torch.empty(max(1, n_total), dtype=torch.int32, device=dev)
         queue = torch.empty(max(1, 2 * n_total), dtype=torch.int32, device=dev)
-        st = L.evi_bfs_multi_source(row_ptr.data_ptr(), adj.data_ptr(), B, ptr32.data_ptr(),
-                                    ptr32[1:].contiguous().data_ptr(), b.ptr.data_ptr(),
-                                    b.q_ptr.to(torch.int32).data_ptr(), local_seeds.to(torch.int32).data_ptr(),
+        st = L.evi_bfs_multi_source(row_ptr.data_ptr(), adj.data_ptr(), B, ptr32.data_ptr(), node_end32.data_ptr(),
+                                    dist_off.data_ptr(), src_ptr32.data_ptr(), seeds32.data_ptr(),
                                     self.bfs_max_depth, dist.data_ptr(), queue.data_ptr(), _lib.stream_handle())
         _lib.check(st, "evi_bfs_multi_source")
         return dist[:n_total]
