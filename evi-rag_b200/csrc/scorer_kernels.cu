@@ -10,7 +10,7 @@
 namespace evi {
 
 constexpr int D = 1024;        // emb_dim == hidden_dim (configs/model/retriever_module.yaml:10-11)
-constexpr int kMaxStruct = 36; // 2*2*(1+4+4)
+constexpr int kMaxNodeStruct = 18;  // 2*(1+4+4)
 constexpr float kLnEps = 1e-5f;
 
 static inline int check_launch() { return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda; }
@@ -59,22 +59,60 @@ __global__ void gather_rows_kernel(const void* __restrict__ src, long long src_r
 }
 
 // ---------------------------------------------------------------------------------------------
+// Per-node half of struct_proj.0 (retriever.py:486-495 applied to retriever.py:509-517):
+//   W_s [s_fwd ; s_bwd-half] splits by node:  W_s [ns[a], ns[b]] + b_s = U[a] + V[b]
+//   U[n] = W_s[:, :ns] ns[n] + b_s,   V[n] = W_s[:, ns:] ns[n]            -> uv [N, 2D] fp32
+// so the per-edge kernel adds two gathered rows instead of 2*ns FMAs per element.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+node_struct_proj_kernel(const float* __restrict__ node_struct, int num_nodes, int ns_dim,
+                        const float* __restrict__ ws_t /*[2*ns_dim, D]*/, const float* __restrict__ bs,
+                        float* __restrict__ uv) {
+  const int n = blockIdx.x * 2 + (threadIdx.x >> 7);  // 128 threads per node, 8 columns of U and of V each
+  if (n >= num_nodes) return;
+  const int c = (threadIdx.x & 127) * 8;
+  float u[8], v[8];
+  {
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bs + c));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bs + c + 4));
+    u[0] = b0.x, u[1] = b0.y, u[2] = b0.z, u[3] = b0.w, u[4] = b1.x, u[5] = b1.y, u[6] = b1.z, u[7] = b1.w;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+  }
+  const float* ns = node_struct + static_cast<size_t>(n) * ns_dim;
+  for (int k = 0; k < ns_dim; ++k) {
+    const float s = __ldg(ns + k);
+    if (s == 0.f) continue;  // most DDE features are exactly zero
+    const float* wu = ws_t + static_cast<size_t>(k) * D + c;
+    const float* wv = ws_t + static_cast<size_t>(ns_dim + k) * D + c;
+    const float4 a0 = __ldg(reinterpret_cast<const float4*>(wu)), a1 = __ldg(reinterpret_cast<const float4*>(wu + 4));
+    const float4 c0 = __ldg(reinterpret_cast<const float4*>(wv)), c1 = __ldg(reinterpret_cast<const float4*>(wv + 4));
+    u[0] = fmaf(s, a0.x, u[0]), u[1] = fmaf(s, a0.y, u[1]), u[2] = fmaf(s, a0.z, u[2]), u[3] = fmaf(s, a0.w, u[3]);
+    u[4] = fmaf(s, a1.x, u[4]), u[5] = fmaf(s, a1.y, u[5]), u[6] = fmaf(s, a1.z, u[6]), u[7] = fmaf(s, a1.w, u[7]);
+    v[0] = fmaf(s, c0.x, v[0]), v[1] = fmaf(s, c0.y, v[1]), v[2] = fmaf(s, c0.z, v[2]), v[3] = fmaf(s, c0.w, v[3]);
+    v[4] = fmaf(s, c1.x, v[4]), v[5] = fmaf(s, c1.y, v[5]), v[6] = fmaf(s, c1.z, v[6]), v[7] = fmaf(s, c1.w, v[7]);
+  }
+  float* o = uv + static_cast<size_t>(n) * 2 * D + c;
+  *reinterpret_cast<float4*>(o) = make_float4(u[0], u[1], u[2], u[3]);
+  *reinterpret_cast<float4*>(o + 4) = make_float4(u[4], u[5], u[6], u[7]);
+  *reinterpret_cast<float4*>(o + D) = make_float4(v[0], v[1], v[2], v[3]);
+  *reinterpret_cast<float4*>(o + D + 4) = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+// ---------------------------------------------------------------------------------------------
 // Edge operand kernel: one warp per edge, both directions.
-//   s_f = [ns[h], ns[t]], s_b = [ns[t], ns[h]]                          retriever.py:509-517
-//   sc  = GELU(LN(W_s s + b_s)) ; nav = sigmoid(w_n . sc + b_n)          retriever.py:486-495
+//   x_f = U[h] + V[t], x_b = U[t] + V[h]                                 (struct_proj.0, see above)
+//   sc  = GELU(LN(x)) ; nav = sigmoid(w_n . sc + b_n)                    retriever.py:486-495
 //   r_ctx = rel * gate[q] + bias[q]                                      retriever.py:464
 //   iv  = h * r_ctx * t * nav ; err = h + r_ctx - t ; dist = -||err||    retriever.py:472-478
 // Writes operand rows A_dir[e] = [iv | sc | err] (16-bit, 3*D) and dist_dir[e].
 // Lane l owns columns {256*i + 8*l .. +7}, i = 0..3  (128-bit loads / stores).
 // ---------------------------------------------------------------------------------------------
 struct StructParams {
-  const float* ws_t;   // [S, D] struct_proj.0.weight transposed
-  const float* bs;     // [D]
   const float* ln_g;   // [D] struct_proj.1.weight
   const float* ln_b;   // [D]
   const float* wn;     // [D] struct_gate_net.0.weight
   float bn;
-  int s_dim;           // 2 * node_struct width
 };
 
 template <int FMT>
@@ -109,32 +147,43 @@ EVI_DEVINL void store_row16(uint16_t* __restrict__ base, int lane, const float (
     *reinterpret_cast<uint4*>(base + i * 256 + lane * 8) = w;
   }
 }
+template <int FMT>
+EVI_DEVINL void unpack8(const uint4& w, float (&v)[8]) {
+  const float2 a = Op16<FMT>::unpack2(w.x), b = Op16<FMT>::unpack2(w.y), c = Op16<FMT>::unpack2(w.z),
+               d = Op16<FMT>::unpack2(w.w);
+  v[0] = a.x, v[1] = a.y, v[2] = b.x, v[3] = b.y, v[4] = c.x, v[5] = c.y, v[6] = d.x, v[7] = d.y;
+}
+template <int FMT>
+EVI_DEVINL uint4 pack8(const float (&v)[8]) {
+  uint4 w;
+  w.x = Op16<FMT>::pack2(v[0], v[1]);
+  w.y = Op16<FMT>::pack2(v[2], v[3]);
+  w.z = Op16<FMT>::pack2(v[4], v[5]);
+  w.w = Op16<FMT>::pack2(v[6], v[7]);
+  return w;
+}
+// streaming 128-bit store: operand rows are written once and read once by the GEMM's TMA
+EVI_DEVINL void st_cs_v4(void* p, const uint4& w) {
+  asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w.x), "r"(w.y), "r"(w.z), "r"(w.w)
+               : "memory");
+}
 
-// struct context for one direction; returns nav. `x` receives sc.
-EVI_DEVINL float struct_context(const StructParams& sp, const float* __restrict__ s_ws_t /*smem [S][D]*/,
-                                const float* __restrict__ s_vec /*smem: bs, g, b, wn each [D]*/,
-                                const float* __restrict__ sa, const float* __restrict__ sb, int half, int lane,
-                                float (&x)[32]) {
+// struct context of one direction: writes sc (16-bit) to `sc_out`, returns nav.
+// ua / vb: the U row of the first node and the V row of the second. s_vec (smem): ln_g | ln_b | wn.
+template <int FMT>
+EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __restrict__ vb,
+                                const float* __restrict__ s_vec, float bn, int lane,
+                                uint16_t* __restrict__ sc_out) {
+  float x[32];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const float4 b0 = *reinterpret_cast<const float4*>(s_vec + i * 256 + lane * 8);
-    const float4 b1 = *reinterpret_cast<const float4*>(s_vec + i * 256 + lane * 8 + 4);
-    x[i * 8 + 0] = b0.x, x[i * 8 + 1] = b0.y, x[i * 8 + 2] = b0.z, x[i * 8 + 3] = b0.w;
-    x[i * 8 + 4] = b1.x, x[i * 8 + 5] = b1.y, x[i * 8 + 6] = b1.z, x[i * 8 + 7] = b1.w;
-  }
-  for (int k = 0; k < 2 * half; ++k) {
-    const float s = k < half ? sa[k] : sb[k - half];  // warp-uniform
-    if (s == 0.f) continue;                            // most DDE features are exactly zero
-    const float* w = s_ws_t + k * D;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float4 w0 = *reinterpret_cast<const float4*>(w + i * 256 + lane * 8);
-      const float4 w1 = *reinterpret_cast<const float4*>(w + i * 256 + lane * 8 + 4);
-      x[i * 8 + 0] = fmaf(s, w0.x, x[i * 8 + 0]), x[i * 8 + 1] = fmaf(s, w0.y, x[i * 8 + 1]);
-      x[i * 8 + 2] = fmaf(s, w0.z, x[i * 8 + 2]), x[i * 8 + 3] = fmaf(s, w0.w, x[i * 8 + 3]);
-      x[i * 8 + 4] = fmaf(s, w1.x, x[i * 8 + 4]), x[i * 8 + 5] = fmaf(s, w1.y, x[i * 8 + 5]);
-      x[i * 8 + 6] = fmaf(s, w1.z, x[i * 8 + 6]), x[i * 8 + 7] = fmaf(s, w1.w, x[i * 8 + 7]);
-    }
+    const int c = i * 256 + lane * 8;
+    const float4 u0 = __ldg(reinterpret_cast<const float4*>(ua + c));
+    const float4 u1 = __ldg(reinterpret_cast<const float4*>(ua + c + 4));
+    const float4 v0 = __ldg(reinterpret_cast<const float4*>(vb + c));
+    const float4 v1 = __ldg(reinterpret_cast<const float4*>(vb + c + 4));
+    x[i * 8 + 0] = u0.x + v0.x, x[i * 8 + 1] = u0.y + v0.y, x[i * 8 + 2] = u0.z + v0.z, x[i * 8 + 3] = u0.w + v0.w;
+    x[i * 8 + 4] = u1.x + v1.x, x[i * 8 + 5] = u1.y + v1.y, x[i * 8 + 6] = u1.z + v1.z, x[i * 8 + 7] = u1.w + v1.w;
   }
   float sum = 0.f;
 #pragma unroll
@@ -150,45 +199,46 @@ EVI_DEVINL float struct_context(const StructParams& sp, const float* __restrict_
   float nav = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
+    const int c = i * 256 + lane * 8;
+    float g[8], b[8], w[8], y[8];
+    *reinterpret_cast<float4*>(g) = *reinterpret_cast<const float4*>(s_vec + c);
+    *reinterpret_cast<float4*>(g + 4) = *reinterpret_cast<const float4*>(s_vec + c + 4);
+    *reinterpret_cast<float4*>(b) = *reinterpret_cast<const float4*>(s_vec + D + c);
+    *reinterpret_cast<float4*>(b + 4) = *reinterpret_cast<const float4*>(s_vec + D + c + 4);
+    *reinterpret_cast<float4*>(w) = *reinterpret_cast<const float4*>(s_vec + 2 * D + c);
+    *reinterpret_cast<float4*>(w + 4) = *reinterpret_cast<const float4*>(s_vec + 2 * D + c + 4);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int col = i * 256 + lane * 8 + j;
-      const float y = gelu_erf(fmaf((x[i * 8 + j] - mean) * rstd, s_vec[D + col], s_vec[2 * D + col]));
-      x[i * 8 + j] = y;
-      nav = fmaf(y, s_vec[3 * D + col], nav);
+      y[j] = gelu_fast(fmaf((x[i * 8 + j] - mean) * rstd, g[j], b[j]));
+      nav = fmaf(y[j], w[j], nav);
     }
+    st_cs_v4(sc_out + c, pack8<FMT>(y));
   }
-  return 1.0f / (1.0f + expf(-(warp_sum(nav) + sp.bn)));
+  return 1.0f / (1.0f + __expf(-(warp_sum(nav) + bn)));
 }
 
 constexpr int kEdgeWarps = 8;
 
 template <int FMT>
-__global__ void __launch_bounds__(kEdgeWarps * 32)
+__global__ void __launch_bounds__(kEdgeWarps * 32, 2)
 edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
                     const uint16_t* __restrict__ node_repr,   // [N, D]
                     const uint16_t* __restrict__ rel_repr,    // [R, D]
                     const float* __restrict__ gate_bias,      // [B, 2D]: sigmoid gate | tanh bias
-                    const float* __restrict__ node_struct, int ns_dim, StructParams sp,
-                    int do_fwd, int do_bwd, int num_nodes, int num_rel_rows, int num_questions,
+                    const float* __restrict__ node_uv,        // [N, 2D]: U | V (node_struct_proj_kernel)
+                    StructParams sp, int do_fwd, int do_bwd, int num_nodes, int num_rel_rows, int num_questions,
                     unsigned* __restrict__ flags,
                     uint16_t* __restrict__ a_fwd, uint16_t* __restrict__ a_bwd,  // [E, 3D]
                     float* __restrict__ dist_fwd, float* __restrict__ dist_bwd) {
-  extern __shared__ float smem_f[];
-  float* s_ws_t = smem_f;                       // [S][D]
-  float* s_vec = smem_f + sp.s_dim * D;         // bs | ln_g | ln_b | wn
-  float* s_ns = s_vec + 4 * D;                  // per warp: 2 * ns_dim
-  for (int i = threadIdx.x; i < sp.s_dim * D; i += blockDim.x) s_ws_t[i] = sp.ws_t[i];
+  __shared__ __align__(16) float s_vec[3 * D];  // ln_g | ln_b | wn
   for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    s_vec[i] = sp.bs[i];
-    s_vec[D + i] = sp.ln_g[i];
-    s_vec[2 * D + i] = sp.ln_b[i];
-    s_vec[3 * D + i] = sp.wn[i];
+    s_vec[i] = sp.ln_g[i];
+    s_vec[D + i] = sp.ln_b[i];
+    s_vec[2 * D + i] = sp.wn[i];
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* my_ns = s_ns + warp * 2 * kMaxStruct;
   for (long long e = blockIdx.x * static_cast<long long>(kEdgeWarps) + warp; e < num_edges;
        e += static_cast<long long>(gridDim.x) * kEdgeWarps) {
     int h = __ldg(head + e), t = __ldg(tail + e), q = __ldg(qid + e), rs = __ldg(rel_slot + e);
@@ -199,47 +249,68 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
       if (lane == 0) atomicOr(flags, kFlagOutOfRange);  // keep going on row 0: no wild reads
       h = t = q = rs = 0;
     }
-    __syncwarp();
-    if (lane < ns_dim) {
-      my_ns[lane] = __ldg(node_struct + static_cast<size_t>(h) * ns_dim + lane);
-      my_ns[kMaxStruct + lane] = __ldg(node_struct + static_cast<size_t>(t) * ns_dim + lane);
-    }
-    __syncwarp();
-    float hv[32], tv[32], rv[32], x[32];
-    load_row16<FMT>(node_repr + static_cast<size_t>(h) * D, lane, hv);
-    load_row16<FMT>(node_repr + static_cast<size_t>(t) * D, lane, tv);
-    load_row16<FMT>(rel_repr + static_cast<size_t>(rs) * D, lane, rv);
-    {
-      float gv[32];
-      load_row32(gate_bias + static_cast<size_t>(q) * 2 * D, lane, gv);
+    uint16_t* row_f = a_fwd + static_cast<size_t>(e) * 3 * D;
+    uint16_t* row_b = a_bwd + static_cast<size_t>(e) * 3 * D;
+    const float* uv_h = node_uv + static_cast<size_t>(h) * 2 * D;
+    const float* uv_t = node_uv + static_cast<size_t>(t) * 2 * D;
+    float nav_f = 0.f, nav_b = 0.f;
+    if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, s_vec, sp.bn, lane, row_f + D);
+    if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, s_vec, sp.bn, lane, row_b + D);
+
+    const uint16_t* hp = node_repr + static_cast<size_t>(h) * D;
+    const uint16_t* tp = node_repr + static_cast<size_t>(t) * D;
+    const uint16_t* rp = rel_repr + static_cast<size_t>(rs) * D;
+    const float* gp = gate_bias + static_cast<size_t>(q) * 2 * D;
+    float n2f = 0.f, n2b = 0.f;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) rv[j] *= gv[j];
-      load_row32(gate_bias + static_cast<size_t>(q) * 2 * D + D, lane, gv);
+    for (int i = 0; i < 4; ++i) {
+      const int c = i * 256 + lane * 8;
+      float hv[8], tv[8], rv[8], g[8], b[8], o[8];
+      unpack8<FMT>(ldg_nc_v4(hp + c), hv);
+      unpack8<FMT>(ldg_nc_v4(tp + c), tv);
+      unpack8<FMT>(ldg_nc_v4(rp + c), rv);
+      *reinterpret_cast<float4*>(g) = __ldg(reinterpret_cast<const float4*>(gp + c));
+      *reinterpret_cast<float4*>(g + 4) = __ldg(reinterpret_cast<const float4*>(gp + c + 4));
+      *reinterpret_cast<float4*>(b) = __ldg(reinterpret_cast<const float4*>(gp + D + c));
+      *reinterpret_cast<float4*>(b + 4) = __ldg(reinterpret_cast<const float4*>(gp + D + c + 4));
 #pragma unroll
-      for (int j = 0; j < 32; ++j) rv[j] += gv[j];  // rv = r_ctx
-    }
+      for (int j = 0; j < 8; ++j) rv[j] = fmaf(rv[j], g[j], b[j]);  // r_ctx
+      if (do_fwd) {
 #pragma unroll
-    for (int dir = 0; dir < 2; ++dir) {
-      if (dir == 0 ? !do_fwd : !do_bwd) continue;
-      const float* sa = dir == 0 ? my_ns : my_ns + kMaxStruct;
-      const float* sb = dir == 0 ? my_ns + kMaxStruct : my_ns;
-      uint16_t* arow = (dir == 0 ? a_fwd : a_bwd) + static_cast<size_t>(e) * 3 * D;
-      const float nav = struct_context(sp, s_ws_t, s_vec, sa, sb, ns_dim, lane, x);
-      store_row16<FMT>(arow + D, lane, x);
-      float n2 = 0.f;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float hh = dir == 0 ? hv[j] : tv[j], tt = dir == 0 ? tv[j] : hv[j];
-        const float er = hh + rv[j] - tt;
-        n2 = fmaf(er, er, n2);
-        x[j] = er;
+        for (int j = 0; j < 8; ++j) {
+          o[j] = hv[j] + rv[j] - tv[j];
+          n2f = fmaf(o[j], o[j], n2f);
+        }
+        st_cs_v4(row_f + 2 * D + c, pack8<FMT>(o));
       }
-      store_row16<FMT>(arow + 2 * D, lane, x);
+      if (do_bwd) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) x[j] = hv[j] * rv[j] * tv[j] * nav;
-      store_row16<FMT>(arow, lane, x);
-      n2 = warp_sum(n2);
-      if (lane == 0) (dir == 0 ? dist_fwd : dist_bwd)[e] = -sqrtf(n2);
+        for (int j = 0; j < 8; ++j) {
+          o[j] = tv[j] + rv[j] - hv[j];
+          n2b = fmaf(o[j], o[j], n2b);
+        }
+        st_cs_v4(row_b + 2 * D + c, pack8<FMT>(o));
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rv[j] = hv[j] * rv[j] * tv[j];  // symmetric DistMult term
+      if (do_fwd) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rv[j] * nav_f;
+        st_cs_v4(row_f + c, pack8<FMT>(o));
+      }
+      if (do_bwd) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rv[j] * nav_b;
+        st_cs_v4(row_b + c, pack8<FMT>(o));
+      }
+    }
+    if (do_fwd) {
+      n2f = warp_sum(n2f);
+      if (lane == 0) dist_fwd[e] = -sqrtf(n2f);
+    }
+    if (do_bwd) {
+      n2b = warp_sum(n2b);
+      if (lane == 0) dist_bwd[e] = -sqrtf(n2b);
     }
   }
 }
@@ -285,7 +356,7 @@ EVI_DEVINL float tail_one(const float* __restrict__ zrow, const float2* __restri
     const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float y = gelu_erf(fmaf((z[i * 8 + j] - mean) * rstd, gg[j], bb[j]));
+      const float y = gelu_fast(fmaf((z[i * 8 + j] - mean) * rstd, gg[j], bb[j]));
       z[i * 8 + j] = y;
       acc = fmaf(y, vv[j], acc);
     }
@@ -460,21 +531,16 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   float* dist_b = DIST + (do_f ? E : 0);
 
   StructParams sp;
-  sp.ws_t = a.struct_w_t, sp.bs = a.struct_b, sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b;
-  sp.wn = a.nav_w, sp.bn = a.nav_b, sp.s_dim = 2 * a.ns_dim;
-  if (a.ns_dim > kMaxStruct / 2 || a.ns_dim < 2) return kErrInvalidArg;
-  if (a.flags == nullptr || a.num_nodes <= 0 || a.num_rel_rows <= 0 || a.num_questions <= 0) return kErrInvalidArg;
-  const size_t smem = (static_cast<size_t>(sp.s_dim) * D + 4 * D + kEdgeWarps * 2 * kMaxStruct) * sizeof(float);
-  auto ek = edge_operand_kernel<FMT>;
-  if (cudaFuncSetAttribute(ek, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)) != cudaSuccess)
-    return kErrCuda;
+  sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
+  if (a.flags == nullptr || a.node_uv32 == nullptr || a.num_nodes <= 0 || a.num_rel_rows <= 0 ||
+      a.num_questions <= 0)
+    return kErrInvalidArg;
   long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
-  const int grid = static_cast<int>(want < 4LL * a.num_sms ? want : 4LL * a.num_sms);
-  ek<<<grid, kEdgeWarps * 32, smem, stream>>>(a.head32, a.tail32, a.qid32, a.rel_slot32, E,
-                                             static_cast<const uint16_t*>(a.node_repr16),
-                                             static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32,
-                                             a.node_struct, a.ns_dim, sp, do_f, do_b, a.num_nodes, a.num_rel_rows,
-                                             a.num_questions, a.flags, A_f, A_b, dist_f, dist_b);
+  const int grid = static_cast<int>(want < 2LL * a.num_sms ? want : 2LL * a.num_sms);
+  edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
+      a.head32, a.tail32, a.qid32, a.rel_slot32, E, static_cast<const uint16_t*>(a.node_repr16),
+      static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
+      a.num_rel_rows, a.num_questions, a.flags, A_f, A_b, dist_f, dist_b);
   if (check_launch() != kOk) return kErrCuda;
 
   gemm::EpiPreNorm::Params zp;
@@ -541,6 +607,17 @@ int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const l
     return gather_rows_impl<kFmtBF16>(src, src_is_f32, src_rows, ids, sub_mask_ids, sub_row, num_rows, dst16, flags,
                                       stream);
   return kErrInvalidArg;
+}
+
+int evi_struct_project(const float* node_struct, int num_nodes, int ns_dim, const float* struct_w_t,
+                       const float* struct_b, float* node_uv32, cudaStream_t stream) {
+  if (num_nodes <= 0) return kOk;
+  if (ns_dim < 2 || ns_dim > kMaxNodeStruct || node_struct == nullptr || struct_w_t == nullptr ||
+      struct_b == nullptr || node_uv32 == nullptr)
+    return kErrInvalidArg;
+  node_struct_proj_kernel<<<(num_nodes + 1) / 2, 256, 0, stream>>>(node_struct, num_nodes, ns_dim, struct_w_t,
+                                                                   struct_b, node_uv32);
+  return check_launch();
 }
 
 int evi_convert_f32(const float* src, void* dst16, long long count, int operand_format, cudaStream_t stream) {

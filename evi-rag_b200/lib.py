@@ -29,11 +29,11 @@ class ScoreArgs(C.Structure):
 
     _fields_ = [
         ("num_edges", _ll), ("emb_dim", _i), ("hidden_dim", _i), ("direction", _i),
-        ("operand_format", _i), ("want_features", _i), ("ns_dim", _i), ("num_sms", _i),
+        ("operand_format", _i), ("want_features", _i), ("num_sms", _i),
         ("num_nodes", _i), ("num_rel_rows", _i), ("num_questions", _i), ("flags", _vp),
         ("head32", _vp), ("tail32", _vp), ("qid32", _vp), ("rel_slot32", _vp),
-        ("node_repr16", _vp), ("rel_repr16", _vp), ("gate_bias32", _vp), ("node_struct", _vp),
-        ("struct_w_t", _vp), ("struct_b", _vp), ("struct_ln_g", _vp), ("struct_ln_b", _vp),
+        ("node_repr16", _vp), ("rel_repr16", _vp), ("gate_bias32", _vp), ("node_uv32", _vp),
+        ("struct_ln_g", _vp), ("struct_ln_b", _vp),
         ("nav_w", _vp), ("nav_b", _f),
         ("w1_main16", _vp), ("w1_dist_col", _vp), ("w1_bias", _vp), ("ln1_g", _vp), ("ln1_b", _vp),
         ("head_v", _vp), ("head_c0", _f), ("w2_16", _vp), ("w2_bias", _vp), ("head_w", _vp),
@@ -54,6 +54,7 @@ PROTOTYPES = {
     "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
     "evi_shortest_path_pairs": (_i, [_vp, _vp, _i] + [_vp] * 9 + [_i] + [_vp] * 4 + [_vp]),
     "evi_gather_rows": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp]),
+    "evi_struct_project": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_convert_f32": (_i, [_vp, _vp, _ll, _i, _vp]),
     "evi_project": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     "evi_score_workspace_bytes": (_sz, [_ll, _i, _i]),
@@ -72,6 +73,7 @@ _KERNELS_PER_CALL = {
     "evi_bfs_multi_source": lambda a: 1,
     "evi_shortest_path_pairs": lambda a: 1,
     "evi_gather_rows": lambda a: 1,
+    "evi_struct_project": lambda a: 1,
     "evi_convert_f32": lambda a: 1,
     "evi_project": lambda a: 1,
     "evi_score_edges": lambda a: 5 if a[0]._obj.want_features else 3,

@@ -428,6 +428,9 @@ class Retriever(nn.Module):
                                self.dde.num_rounds, self.dde.num_reverse_rounds, node_struct.data_ptr(),
                                dde_ws.data_ptr(), dde_ws.numel(), stream)
         _lib.check(st, "evi_dde_forward")
+        node_uv = torch.empty((N, 2 * d), dtype=torch.float32, device=dev)
+        _lib.check(L.evi_struct_project(node_struct.data_ptr(), N, ns_dim, p["ws_t"].data_ptr(), p["bs"].data_ptr(),
+                                        node_uv.data_ptr(), stream), "evi_struct_project")
 
         # ---- a5/a6: edge scoring -------------------------------------------------------------
         direction = {"bidirectional": _lib.DIR_BIDIRECTIONAL, "forward": _lib.DIR_FORWARD,
@@ -441,11 +444,10 @@ class Retriever(nn.Module):
         ws = self._workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features))), dev)
         a = _lib.ScoreArgs()
         a.emb_dim, a.hidden_dim, a.direction, a.operand_format = d, self.hidden_dim, direction, fmt
-        a.want_features, a.ns_dim, a.num_sms = int(return_features), ns_dim, p["num_sms"]
+        a.want_features, a.num_sms = int(return_features), p["num_sms"]
         a.num_nodes, a.num_rel_rows, a.num_questions, a.flags = N, int(rel_repr.size(0)), B, flags.data_ptr()
         a.node_repr16, a.rel_repr16 = node_repr.data_ptr(), rel_repr.data_ptr()
-        a.gate_bias32, a.node_struct = gate_bias.data_ptr(), node_struct.data_ptr()
-        a.struct_w_t, a.struct_b = p["ws_t"].data_ptr(), p["bs"].data_ptr()
+        a.gate_bias32, a.node_uv32 = gate_bias.data_ptr(), node_uv.data_ptr()
         a.struct_ln_g, a.struct_ln_b = p["ls_g"].data_ptr(), p["ls_b"].data_ptr()
         a.nav_w, a.nav_b = p["wn"].data_ptr(), p["bn"]
         a.w1_main16, a.w1_dist_col, a.w1_bias = p["w1"].data_ptr(), p["w1d"].data_ptr(), p["b1"].data_ptr()

@@ -108,6 +108,14 @@ int evi_project(const void* x16, int num_rows, const void* w16, int out_dim, int
                 const int* act_per_block, void* out16, float* out32, int operand_format, int num_sms,
                 cudaStream_t stream);
 
+/* struct_proj.0 of _encode_structure (retriever.py:486-495) on the edge structure vector
+ * [ns[a], ns[b]] of _edge_structure_from_nodes (retriever.py:509-517), split by node:
+ *   W_s [ns[a] ; ns[b]] + b_s = U[a] + V[b],  U[n] = W_s[:, :ns_dim] ns[n] + b_s,  V[n] = W_s[:, ns_dim:] ns[n].
+ * node_struct [N, ns_dim] f32 (evi_dde_forward), struct_w_t [2*ns_dim, D] = struct_proj.0.weight^T
+ * -> node_uv32 [N, 2D] f32 (U | V). */
+int evi_struct_project(const float* node_struct, int num_nodes, int ns_dim, const float* struct_w_t,
+                       const float* struct_b, float* node_uv32, cudaStream_t stream);
+
 /* _score_edges + _encode_structure + _combine_directional_outputs —
  * src/models/components/retriever.py:453-495, 369-381. */
 typedef struct evi_score_args {
@@ -116,7 +124,6 @@ typedef struct evi_score_args {
   int direction;                    /* EVI_DIR_* */
   int operand_format;               /* EVI_FMT_* */
   int want_features;                /* 1: also produce edge_embeddings [E, H] f32 */
-  int ns_dim;                       /* node_struct width = 2*(1+Rf+Rr) */
   int num_sms;
   int num_nodes, num_rel_rows, num_questions; /* row counts of node_repr16 / rel_repr16 / gate_bias32 */
   unsigned* flags;                  /* EVI_FLAG_OUT_OF_RANGE if an edge indexes outside those */
@@ -129,10 +136,8 @@ typedef struct evi_score_args {
   const void* node_repr16;          /* [N, D] tanh(entity_proj) */
   const void* rel_repr16;           /* [R, D] tanh(relation_proj) */
   const float* gate_bias32;         /* [B, 2D] sigmoid(q_gate(q)) | tanh(q_bias(q)) */
-  const float* node_struct;         /* [N, ns_dim] */
+  const float* node_uv32;           /* [N, 2D] per-node halves of struct_proj.0 (evi_struct_project) */
   /* weights (prepared once per checkpoint) */
-  const float* struct_w_t;          /* [2*ns_dim, D] struct_proj.0.weight^T */
-  const float* struct_b;            /* [D] */
   const float* struct_ln_g;         /* [D] struct_proj.1 */
   const float* struct_ln_b;
   const float* nav_w;               /* [D] struct_gate_net.0.weight */
