@@ -49,6 +49,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-questions", type=int, default=8)
     ap.add_argument("--operand-dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--pipeline-chunks", type=int, default=4,
+                    help="edge chunks per batch whose operand / GEMM / tail stages overlap on three streams (1: serial)")
     return ap.parse_args()
 
 
@@ -201,7 +203,8 @@ def run_ours(args):
     spec = WEBQSP_10K
     QB = args.questions_per_step
     sd = make_state_dict(0, trained_like=True)
-    model = Retriever(emb_dim=1024, hidden_dim=1024, operand_dtype=args.operand_dtype).eval()
+    model = Retriever(emb_dim=1024, hidden_dim=1024, operand_dtype=args.operand_dtype,
+                      pipeline_chunks=args.pipeline_chunks).eval()
     model.load_state_dict(sd, strict=True)
     model.to(dev)
     ent, rel = make_embedding_tables(spec)

@@ -120,6 +120,19 @@ EVI_DEVINL uint4 ldg_nc_v4(const void* p) {
   return r;
 }
 
+// 256-bit loads (sm_100: LDG.E.256): one lane reads 8 consecutive floats, a warp 1 KB contiguous.
+// `_stream`: read-once rows (no L1 allocation); `_keep`: rows re-read by neighbouring warps.
+EVI_DEVINL void ldg_v8_stream(const float* p, float (&v)[8]) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(p));
+}
+EVI_DEVINL void ldg_v8_keep(const float* p, float (&v)[8]) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "l"(p));
+}
+
 // ---------------------------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------------------------

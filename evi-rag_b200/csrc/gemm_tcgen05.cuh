@@ -37,8 +37,11 @@ struct TileCoord {
   int m_blk, n_blk;
 };
 
+// minBlocksPerSM = 2 only caps registers at 128/thread (shared memory keeps one CTA per SM): the
+// CTA then takes exactly half the register file and an 8-warp, 128-register elementwise CTA of the
+// scoring pipeline fits beside it.
 template <int FMT, class Epi>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(NUM_THREADS, 2)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             int M, int N, int K, typename Epi::Params ep) {
   extern __shared__ uint8_t smem_raw[];
@@ -359,6 +362,10 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
   if (!attr_set) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
       return kErrCuda;
+    // The driver configures the SM for the smallest shared-memory carve-out that holds the CTA (196 KB
+    // here), which leaves no room for the 13 KB of a co-resident elementwise CTA. Ask for the largest
+    // split (228 KB) so the scoring pipeline's operand kernel can be placed beside the GEMM CTA.
+    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_set = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);

@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(kBfsThreads)
 bfs_jobs_kernel(const int* __restrict__ row_ptr, const int* __restrict__ adj,
                 const int* __restrict__ job_node_begin, const int* __restrict__ job_node_end,
                 const long long* __restrict__ job_dist_off, const int* __restrict__ job_src_ptr,
-                const int* __restrict__ sources /* question-local ids */, int max_depth,
+                const int* __restrict__ sources, int sources_are_global, int max_depth,
                 int* __restrict__ dist_out, int* __restrict__ queue_ws) {
   const int job = blockIdx.x;
   const int n0 = job_node_begin[job], n1 = job_node_end[job];
@@ -245,7 +245,7 @@ bfs_jobs_kernel(const int* __restrict__ row_ptr, const int* __restrict__ adj,
   __syncthreads();
   // sources: in-range, first occurrence only (build_retrieval_pipeline.py:617-621)
   for (int i = job_src_ptr[job] + threadIdx.x; i < job_src_ptr[job + 1]; i += blockDim.x) {
-    const int s = sources[i];
+    const int s = sources[i] - (sources_are_global ? n0 : 0);
     if (s >= 0 && s < nn && atomicCAS(dist + s, -1, 0) == -1) q_cur[atomicAdd(&cur_size, 1)] = s;
   }
   __syncthreads();
@@ -393,12 +393,12 @@ int evi_build_csr(const int* head32, const int* tail32, long long num_edges, int
 
 int evi_bfs_multi_source(const int* row_ptr, const int* adj, int num_jobs, const int* job_node_begin,
                          const int* job_node_end, const long long* job_dist_off, const int* job_src_ptr,
-                         const int* sources, int max_depth, int* dist_out, int* queue_workspace,
-                         cudaStream_t stream) {
+                         const int* sources, int sources_are_global, int max_depth, int* dist_out,
+                         int* queue_workspace, cudaStream_t stream) {
   if (num_jobs <= 0) return kOk;
   bfs_jobs_kernel<<<num_jobs, kBfsThreads, 0, stream>>>(row_ptr, adj, job_node_begin, job_node_end, job_dist_off,
-                                                        job_src_ptr, sources, max_depth, dist_out,
-                                                        queue_workspace);
+                                                        job_src_ptr, sources, sources_are_global, max_depth,
+                                                        dist_out, queue_workspace);
   return check_launch();
 }
 

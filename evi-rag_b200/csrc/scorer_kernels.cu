@@ -4,6 +4,9 @@
 // Dense contractions run on tcgen05 (gemm_tcgen05.cuh); the per-edge elementwise work that builds
 // the GEMM operand rows ([h*r*t*nav | GELU(LN(struct)) | h+r-t]) and the LayerNorm/GELU/score-head
 // tail run in the warp-per-edge kernels below with 128-bit loads of the 1024-d rows.
+#include <cstdio>
+#include <cstdlib>
+
 #include "gemm_tcgen05.cuh"
 #include "evi_rag_b200.h"
 
@@ -64,39 +67,51 @@ __global__ void gather_rows_kernel(const void* __restrict__ src, long long src_r
 //   U[n] = W_s[:, :ns] ns[n] + b_s,   V[n] = W_s[:, ns:] ns[n]            -> uv [N, 2D] fp32
 // so the per-edge kernel adds two gathered rows instead of 2*ns FMAs per element.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+constexpr int kUvNodes = 8;  // nodes per CTA: every weight row fetched from L1 feeds 8 nodes
+
+__global__ void __launch_bounds__(128)
 node_struct_proj_kernel(const float* __restrict__ node_struct, int num_nodes, int ns_dim,
                         const float* __restrict__ ws_t /*[2*ns_dim, D]*/, const float* __restrict__ bs,
                         float* __restrict__ uv) {
-  const int n = blockIdx.x * 2 + (threadIdx.x >> 7);  // 128 threads per node, 8 columns of U and of V each
-  if (n >= num_nodes) return;
-  const int c = (threadIdx.x & 127) * 8;
-  float u[8], v[8];
+  __shared__ float s_ns[kUvNodes][kMaxNodeStruct];
+  const int n0 = blockIdx.x * kUvNodes;
+  for (int i = threadIdx.x; i < kUvNodes * ns_dim; i += blockDim.x) {
+    const int n = n0 + i / ns_dim;
+    s_ns[i / ns_dim][i % ns_dim] = n < num_nodes ? __ldg(node_struct + static_cast<size_t>(n) * ns_dim + i % ns_dim) : 0.f;
+  }
+  __syncthreads();
+  const int c = threadIdx.x * 8;  // 8 columns of U and the same 8 of V
+  float u[kUvNodes][8], v[kUvNodes][8];
   {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bs + c));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bs + c + 4));
-    u[0] = b0.x, u[1] = b0.y, u[2] = b0.z, u[3] = b0.w, u[4] = b1.x, u[5] = b1.y, u[6] = b1.z, u[7] = b1.w;
+    float b[8];
+    ldg_v8_keep(bs + c, b);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) v[j] = 0.f;
+    for (int n = 0; n < kUvNodes; ++n)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) u[n][j] = b[j], v[n][j] = 0.f;
   }
-  const float* ns = node_struct + static_cast<size_t>(n) * ns_dim;
   for (int k = 0; k < ns_dim; ++k) {
-    const float s = __ldg(ns + k);
-    if (s == 0.f) continue;  // most DDE features are exactly zero
-    const float* wu = ws_t + static_cast<size_t>(k) * D + c;
-    const float* wv = ws_t + static_cast<size_t>(ns_dim + k) * D + c;
-    const float4 a0 = __ldg(reinterpret_cast<const float4*>(wu)), a1 = __ldg(reinterpret_cast<const float4*>(wu + 4));
-    const float4 c0 = __ldg(reinterpret_cast<const float4*>(wv)), c1 = __ldg(reinterpret_cast<const float4*>(wv + 4));
-    u[0] = fmaf(s, a0.x, u[0]), u[1] = fmaf(s, a0.y, u[1]), u[2] = fmaf(s, a0.z, u[2]), u[3] = fmaf(s, a0.w, u[3]);
-    u[4] = fmaf(s, a1.x, u[4]), u[5] = fmaf(s, a1.y, u[5]), u[6] = fmaf(s, a1.z, u[6]), u[7] = fmaf(s, a1.w, u[7]);
-    v[0] = fmaf(s, c0.x, v[0]), v[1] = fmaf(s, c0.y, v[1]), v[2] = fmaf(s, c0.z, v[2]), v[3] = fmaf(s, c0.w, v[3]);
-    v[4] = fmaf(s, c1.x, v[4]), v[5] = fmaf(s, c1.y, v[5]), v[6] = fmaf(s, c1.z, v[6]), v[7] = fmaf(s, c1.w, v[7]);
+    float wu[8], wv[8];
+    ldg_v8_keep(ws_t + static_cast<size_t>(k) * D + c, wu);
+    ldg_v8_keep(ws_t + static_cast<size_t>(ns_dim + k) * D + c, wv);
+#pragma unroll
+    for (int n = 0; n < kUvNodes; ++n) {
+      const float sv = s_ns[n][k];  // broadcast
+#pragma unroll
+      for (int j = 0; j < 8; ++j) u[n][j] = fmaf(sv, wu[j], u[n][j]), v[n][j] = fmaf(sv, wv[j], v[n][j]);
+    }
   }
-  float* o = uv + static_cast<size_t>(n) * 2 * D + c;
-  *reinterpret_cast<float4*>(o) = make_float4(u[0], u[1], u[2], u[3]);
-  *reinterpret_cast<float4*>(o + 4) = make_float4(u[4], u[5], u[6], u[7]);
-  *reinterpret_cast<float4*>(o + D) = make_float4(v[0], v[1], v[2], v[3]);
-  *reinterpret_cast<float4*>(o + D + 4) = make_float4(v[4], v[5], v[6], v[7]);
+#pragma unroll
+  for (int n = 0; n < kUvNodes; ++n) {
+    if (n0 + n >= num_nodes) break;
+    float* o = uv + static_cast<size_t>(n0 + n) * 2 * D + c;
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(o), "f"(u[n][0]), "f"(u[n][1]),
+                 "f"(u[n][2]), "f"(u[n][3]), "f"(u[n][4]), "f"(u[n][5]), "f"(u[n][6]), "f"(u[n][7])
+                 : "memory");
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(o + D), "f"(v[n][0]), "f"(v[n][1]),
+                 "f"(v[n][2]), "f"(v[n][3]), "f"(v[n][4]), "f"(v[n][5]), "f"(v[n][6]), "f"(v[n][7])
+                 : "memory");
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -129,10 +144,10 @@ EVI_DEVINL void load_row16(const uint16_t* __restrict__ base, int lane, float (&
 EVI_DEVINL void load_row32(const float* __restrict__ base, int lane, float (&v)[32]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const float4 a = __ldg(reinterpret_cast<const float4*>(base + i * 256 + lane * 8));
-    const float4 b = __ldg(reinterpret_cast<const float4*>(base + i * 256 + lane * 8 + 4));
-    v[i * 8 + 0] = a.x, v[i * 8 + 1] = a.y, v[i * 8 + 2] = a.z, v[i * 8 + 3] = a.w;
-    v[i * 8 + 4] = b.x, v[i * 8 + 5] = b.y, v[i * 8 + 6] = b.z, v[i * 8 + 7] = b.w;
+    float t[8];
+    ldg_v8_stream(base + i * 256 + lane * 8, t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[i * 8 + j] = t[j];
   }
 }
 template <int FMT>
@@ -169,21 +184,19 @@ EVI_DEVINL void st_cs_v4(void* p, const uint4& w) {
 }
 
 // struct context of one direction: writes sc (16-bit) to `sc_out`, returns nav.
-// ua / vb: the U row of the first node and the V row of the second. s_vec (smem): ln_g | ln_b | wn.
+// ua / vb: the U row of the first node and the V row of the second.
 template <int FMT>
 EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __restrict__ vb,
-                                const float* __restrict__ s_vec, float bn, int lane,
-                                uint16_t* __restrict__ sc_out) {
+                                const StructParams& sp, int lane, uint16_t* __restrict__ sc_out) {
   float x[32];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int c = i * 256 + lane * 8;
-    const float4 u0 = __ldg(reinterpret_cast<const float4*>(ua + c));
-    const float4 u1 = __ldg(reinterpret_cast<const float4*>(ua + c + 4));
-    const float4 v0 = __ldg(reinterpret_cast<const float4*>(vb + c));
-    const float4 v1 = __ldg(reinterpret_cast<const float4*>(vb + c + 4));
-    x[i * 8 + 0] = u0.x + v0.x, x[i * 8 + 1] = u0.y + v0.y, x[i * 8 + 2] = u0.z + v0.z, x[i * 8 + 3] = u0.w + v0.w;
-    x[i * 8 + 4] = u1.x + v1.x, x[i * 8 + 5] = u1.y + v1.y, x[i * 8 + 6] = u1.z + v1.z, x[i * 8 + 7] = u1.w + v1.w;
+    float u[8], v[8];
+    ldg_v8_stream(ua + c, u);
+    ldg_v8_stream(vb + c, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) x[i * 8 + j] = u[j] + v[j];
   }
   float sum = 0.f;
 #pragma unroll
@@ -201,12 +214,9 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
   for (int i = 0; i < 4; ++i) {
     const int c = i * 256 + lane * 8;
     float g[8], b[8], w[8], y[8];
-    *reinterpret_cast<float4*>(g) = *reinterpret_cast<const float4*>(s_vec + c);
-    *reinterpret_cast<float4*>(g + 4) = *reinterpret_cast<const float4*>(s_vec + c + 4);
-    *reinterpret_cast<float4*>(b) = *reinterpret_cast<const float4*>(s_vec + D + c);
-    *reinterpret_cast<float4*>(b + 4) = *reinterpret_cast<const float4*>(s_vec + D + c + 4);
-    *reinterpret_cast<float4*>(w) = *reinterpret_cast<const float4*>(s_vec + 2 * D + c);
-    *reinterpret_cast<float4*>(w + 4) = *reinterpret_cast<const float4*>(s_vec + 2 * D + c + 4);
+    ldg_v8_keep(sp.ln_g + c, g);  // 12 KB of parameters: L1-resident, no shared memory (a CTA with static
+    ldg_v8_keep(sp.ln_b + c, b);  // shared memory does not fit beside the GEMM CTA's carve-out)
+    ldg_v8_keep(sp.wn + c, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       y[j] = gelu_fast(fmaf((x[i * 8 + j] - mean) * rstd, g[j], b[j]));
@@ -214,13 +224,13 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
     }
     st_cs_v4(sc_out + c, pack8<FMT>(y));
   }
-  return 1.0f / (1.0f + __expf(-(warp_sum(nav) + bn)));
+  return 1.0f / (1.0f + __expf(-(warp_sum(nav) + sp.bn)));
 }
 
-constexpr int kEdgeWarps = 8;
+constexpr int kEdgeWarps = 4;  // 4 warps x 128 registers = a quarter of the register file: fits beside the GEMM CTA
 
 template <int FMT>
-__global__ void __launch_bounds__(kEdgeWarps * 32, 2)
+__global__ void __launch_bounds__(kEdgeWarps * 32, 4)
 edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
                     const uint16_t* __restrict__ node_repr,   // [N, D]
@@ -231,13 +241,6 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
                     unsigned* __restrict__ flags,
                     uint16_t* __restrict__ a_fwd, uint16_t* __restrict__ a_bwd,  // [E, 3D]
                     float* __restrict__ dist_fwd, float* __restrict__ dist_bwd) {
-  __shared__ __align__(16) float s_vec[3 * D];  // ln_g | ln_b | wn
-  for (int i = threadIdx.x; i < D; i += blockDim.x) {
-    s_vec[i] = sp.ln_g[i];
-    s_vec[D + i] = sp.ln_b[i];
-    s_vec[2 * D + i] = sp.wn[i];
-  }
-  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (long long e = blockIdx.x * static_cast<long long>(kEdgeWarps) + warp; e < num_edges;
        e += static_cast<long long>(gridDim.x) * kEdgeWarps) {
@@ -254,8 +257,8 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
     const float* uv_h = node_uv + static_cast<size_t>(h) * 2 * D;
     const float* uv_t = node_uv + static_cast<size_t>(t) * 2 * D;
     float nav_f = 0.f, nav_b = 0.f;
-    if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, s_vec, sp.bn, lane, row_f + D);
-    if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, s_vec, sp.bn, lane, row_b + D);
+    if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, row_f + D);
+    if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, sp, lane, row_b + D);
 
     const uint16_t* hp = node_repr + static_cast<size_t>(h) * D;
     const uint16_t* tp = node_repr + static_cast<size_t>(t) * D;
@@ -269,10 +272,8 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
       unpack8<FMT>(ldg_nc_v4(hp + c), hv);
       unpack8<FMT>(ldg_nc_v4(tp + c), tv);
       unpack8<FMT>(ldg_nc_v4(rp + c), rv);
-      *reinterpret_cast<float4*>(g) = __ldg(reinterpret_cast<const float4*>(gp + c));
-      *reinterpret_cast<float4*>(g + 4) = __ldg(reinterpret_cast<const float4*>(gp + c + 4));
-      *reinterpret_cast<float4*>(b) = __ldg(reinterpret_cast<const float4*>(gp + D + c));
-      *reinterpret_cast<float4*>(b + 4) = __ldg(reinterpret_cast<const float4*>(gp + D + c + 4));
+      ldg_v8_keep(gp + c, g);
+      ldg_v8_keep(gp + D + c, b);
 #pragma unroll
       for (int j = 0; j < 8; ++j) rv[j] = fmaf(rv[j], g[j], b[j]);  // r_ctx
       if (do_fwd) {
@@ -345,15 +346,10 @@ EVI_DEVINL float tail_one(const float* __restrict__ zrow, const float2* __restri
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int col = i * 256 + lane * 8;
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(tp.ln_g + col));
-    const float4 g1 = __ldg(reinterpret_cast<const float4*>(tp.ln_g + col + 4));
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(tp.ln_b + col));
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(tp.ln_b + col + 4));
-    const float4 v0 = __ldg(reinterpret_cast<const float4*>(tp.v + col));
-    const float4 v1 = __ldg(reinterpret_cast<const float4*>(tp.v + col + 4));
-    const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-    const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-    const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    float gg[8], bb[8], vv[8];
+    ldg_v8_keep(tp.ln_g + col, gg);
+    ldg_v8_keep(tp.ln_b + col, bb);
+    ldg_v8_keep(tp.v + col, vv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float y = gelu_fast(fmaf((z[i * 8 + j] - mean) * rstd, gg[j], bb[j]));
@@ -497,16 +493,42 @@ static int linear_act_impl(const void* x16, int m, const void* w16, int n, int k
   return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, k, m, n, k, p, num_sms, stream);
 }
 
+// One chunk of edges [e0, e0 + n): operand rows on s_op, state_net.0 GEMM on s_gemm, LayerNorm/GELU/head
+// tail on s_tail. The three streams may be the same one (serial) or different (pipelined by the caller
+// through the events below). `ws` is one per-chunk workspace buffer.
+struct ChunkEvents {
+  cudaEvent_t wait_op = nullptr;    // s_op waits for it before writing A / dist (buffer reuse)
+  cudaEvent_t wait_op2 = nullptr;   // s_op also waits for it: the previous chunk's GEMM is about to start
+  cudaEvent_t op_done = nullptr;    // recorded on s_op, waited by s_gemm
+  cudaEvent_t wait_gemm = nullptr;  // s_gemm also waits for it (z / stats buffer reuse)
+  cudaEvent_t gemm_ready = nullptr; // recorded on s_gemm right before the GEMM launch
+  cudaEvent_t op_start = nullptr;   // (trace only) recorded on s_op once its waits have passed
+  cudaEvent_t gemm_done = nullptr;  // recorded on s_gemm, waited by s_tail
+  cudaEvent_t tail_done = nullptr;  // recorded on s_tail
+  cudaEvent_t time_begin = nullptr, time_end = nullptr;  // optional timing pair around the GEMM
+};
+
+// An SM keeps one L1 / shared-memory split while CTAs are resident, so a kernel that prefers a large L1
+// is not placed beside the GEMM CTA (which configures the SM for maximum shared memory). In pipelined
+// mode the elementwise kernels ask for the same split; serial mode leaves them the default (larger L1).
+template <class K>
+static void prefer_carveout(K kernel, bool max_shared) {
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                       max_shared ? cudaSharedmemCarveoutMaxShared : cudaSharedmemCarveoutDefault);
+}
+
 template <int FMT>
-static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
-  const long long E = a.num_edges;
-  if (E <= 0) return kOk;
+static int score_chunk(const evi_score_args& a, long long e0, long long n, uint8_t* ws, size_t ws_bytes,
+                       cudaStream_t s_op, cudaStream_t s_gemm, cudaStream_t s_tail, const ChunkEvents& ev) {
+  const long long E = n;
+  const bool overlapped = s_gemm != s_op;
+  prefer_carveout(edge_operand_kernel<FMT>, overlapped);
+  prefer_carveout(score_tail_kernel<FMT>, overlapped);
   const int do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
   const int ndir = do_f + do_b;
   const int n_blocks = D / gemm::BN;
-  // workspace carve-up: A [ndir*E, 3D] 16-bit | z [ndir*E, D] 16-bit | stats [ndir*E, n_blocks] float2 |
-  //                     (z is fp32) dist [ndir*E] f32 | (features) g [ndir*E, D] 16-bit | feat [ndir*E, D] f32
-  uint8_t* ws = static_cast<uint8_t*>(a.workspace);
+  // workspace carve-up: A [ndir*E, 3D] 16-bit | z [ndir*E, D] f32 | stats [ndir*E, n_blocks] float2 |
+  //                     dist [ndir*E] f32 | (features) g [ndir*E, D] 16-bit | feat [ndir*E, D] f32
   size_t off = 0;
   auto take = [&](size_t bytes) {
     uint8_t* p = ws + off;
@@ -524,33 +546,48 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
     G = reinterpret_cast<uint16_t*>(take(rows * D * 2));
     FEAT = reinterpret_cast<float*>(take(rows * D * sizeof(float)));
   }
-  if (off > a.workspace_bytes) return kErrWorkspace;
+  if (off > ws_bytes) return kErrWorkspace;
   uint16_t* A_f = A;
   uint16_t* A_b = A + (do_f ? static_cast<size_t>(E) * 3 * D : 0);
   float* dist_f = DIST;
   float* dist_b = DIST + (do_f ? E : 0);
+  float* logits = a.logits ? a.logits + e0 : nullptr;
+  float* logits_fwd = a.logits_fwd ? a.logits_fwd + e0 : nullptr;
+  float* logits_bwd = a.logits_bwd ? a.logits_bwd + e0 : nullptr;
+  float* edge_emb = a.edge_embeddings ? a.edge_embeddings + static_cast<size_t>(e0) * D : nullptr;
 
   StructParams sp;
   sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
-  if (a.flags == nullptr || a.node_uv32 == nullptr || a.num_nodes <= 0 || a.num_rel_rows <= 0 ||
-      a.num_questions <= 0)
-    return kErrInvalidArg;
+  if (ev.wait_op && cudaStreamWaitEvent(s_op, ev.wait_op, 0) != cudaSuccess) return kErrCuda;
+  if (ev.wait_op2 && cudaStreamWaitEvent(s_op, ev.wait_op2, 0) != cudaSuccess) return kErrCuda;
+  if (ev.op_start) cudaEventRecord(ev.op_start, s_op);
   long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
-  const int grid = static_cast<int>(want < 2LL * a.num_sms ? want : 2LL * a.num_sms);
-  edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
-      a.head32, a.tail32, a.qid32, a.rel_slot32, E, static_cast<const uint16_t*>(a.node_repr16),
+  const int grid = static_cast<int>(want < 4LL * a.num_sms ? want : 4LL * a.num_sms);
+  edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, s_op>>>(
+      a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
       static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
       a.num_rel_rows, a.num_questions, a.flags, A_f, A_b, dist_f, dist_b);
   if (check_launch() != kOk) return kErrCuda;
+  if (ev.op_done) {
+    if (cudaEventRecord(ev.op_done, s_op) != cudaSuccess || cudaStreamWaitEvent(s_gemm, ev.op_done, 0) != cudaSuccess)
+      return kErrCuda;
+  }
+  if (ev.wait_gemm && cudaStreamWaitEvent(s_gemm, ev.wait_gemm, 0) != cudaSuccess) return kErrCuda;
 
   gemm::EpiPreNorm::Params zp;
   zp.bias = a.w1_bias, zp.w_dist = a.w1_dist_col, zp.dist = DIST, zp.z32 = Z, zp.stats = ST;
   zp.ldz = D, zp.n_blocks = n_blocks;
-  if (a.ev_gemm_begin) cudaEventRecord(static_cast<cudaEvent_t>(a.ev_gemm_begin), stream);
+  if (ev.gemm_ready && cudaEventRecord(ev.gemm_ready, s_gemm) != cudaSuccess) return kErrCuda;
+  if (ev.time_begin) cudaEventRecord(ev.time_begin, s_gemm);
   int rc = gemm::launch<FMT, gemm::EpiPreNorm>(A, 3 * D, a.w1_main16, 3 * D, static_cast<int>(rows), D, 3 * D, zp,
-                                               a.num_sms, stream);
-  if (a.ev_gemm_end) cudaEventRecord(static_cast<cudaEvent_t>(a.ev_gemm_end), stream);
+                                               a.num_sms, s_gemm);
+  if (ev.time_end) cudaEventRecord(ev.time_end, s_gemm);
   if (rc != kOk) return rc;
+  if (ev.gemm_done) {
+    if (cudaEventRecord(ev.gemm_done, s_gemm) != cudaSuccess ||
+        cudaStreamWaitEvent(s_tail, ev.gemm_done, 0) != cudaSuccess)
+      return kErrCuda;
+  }
 
   TailParams tp;
   tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
@@ -562,22 +599,126 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   uint16_t* g_b = G ? G + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
   const int tgrid = static_cast<int>((E + 7) / 8);
   if (!a.want_features) {
-    score_tail_kernel<FMT><<<tgrid, 256, 0, stream>>>(z_f, z_b, st_f, st_b, n_blocks, E, tp, nullptr, nullptr,
-                                                      a.logits, a.logits_fwd, a.logits_bwd);
-    return check_launch();
+    score_tail_kernel<FMT><<<tgrid, 256, 0, s_tail>>>(z_f, z_b, st_f, st_b, n_blocks, E, tp, nullptr, nullptr,
+                                                      logits, logits_fwd, logits_bwd);
+    if (check_launch() != kOk) return kErrCuda;
+    if (ev.tail_done && cudaEventRecord(ev.tail_done, s_tail) != cudaSuccess) return kErrCuda;
+    return kOk;
   }
-  score_tail_kernel<FMT><<<tgrid, 256, 0, stream>>>(z_f, z_b, st_f, st_b, n_blocks, E, tp, do_f ? g_f : nullptr,
+  score_tail_kernel<FMT><<<tgrid, 256, 0, s_tail>>>(z_f, z_b, st_f, st_b, n_blocks, E, tp, do_f ? g_f : nullptr,
                                                     do_b ? g_b : nullptr, nullptr, nullptr, nullptr);
   if (check_launch() != kOk) return kErrCuda;
   gemm::EpiBiasF32::Params fp;
   fp.bias = a.w2_bias, fp.out32 = FEAT, fp.ld32 = D;
-  rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(rows), D, D, fp, a.num_sms, stream);
+  rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(rows), D, D, fp, a.num_sms, s_tail);
   if (rc != kOk) return rc;
   const float* f_f = do_f ? FEAT : nullptr;
   const float* f_b = do_b ? FEAT + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
-  feature_blend_kernel<<<tgrid, 256, 0, stream>>>(f_f, f_b, a.head_w, a.head_b, E, a.edge_embeddings, a.logits,
-                                                  a.logits_fwd, a.logits_bwd);
-  return check_launch();
+  feature_blend_kernel<<<tgrid, 256, 0, s_tail>>>(f_f, f_b, a.head_w, a.head_b, E, edge_emb, logits, logits_fwd,
+                                                  logits_bwd);
+  if (check_launch() != kOk) return kErrCuda;
+  if (ev.tail_done && cudaEventRecord(ev.tail_done, s_tail) != cudaSuccess) return kErrCuda;
+  return kOk;
+}
+
+static size_t chunk_workspace_bytes(long long num_edges, int direction, int want_features) {
+  const size_t ndir = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
+  const size_t rows = ndir * static_cast<size_t>(num_edges);
+  auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
+  size_t total = al(rows * 3 * D * 2) + al(rows * D * sizeof(float)) + al(rows * (D / gemm::BN) * sizeof(float2)) +
+                 al(rows * sizeof(float));
+  if (want_features) total += al(rows * D * 2) + al(rows * D * sizeof(float));
+  return total + 256;
+}
+
+// All edges, chunk by chunk. With two auxiliary streams the three stages of consecutive chunks overlap:
+// the operand kernel of chunk c+1 (ALU/L1-bound) and the tail of chunk c-1 (HBM-bound) run beside the
+// tensor-bound GEMM of chunk c; two workspace buffers alternate. Only events order the stages — no kernel
+// ever waits on another kernel's flag.
+template <int FMT>
+static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
+  const long long E = a.num_edges;
+  if (E <= 0) return kOk;
+  if (a.flags == nullptr || a.node_uv32 == nullptr || a.num_nodes <= 0 || a.num_rel_rows <= 0 ||
+      a.num_questions <= 0)
+    return kErrInvalidArg;
+  const long long chunk = a.chunk_edges > 0 && a.chunk_edges < E ? a.chunk_edges : E;
+  const long long nchunks = (E + chunk - 1) / chunk;
+  const size_t per = chunk_workspace_bytes(chunk, a.direction, a.want_features);
+  uint8_t* ws = static_cast<uint8_t*>(a.workspace);
+  cudaStream_t s_gemm = static_cast<cudaStream_t>(a.stream_gemm), s_tail = static_cast<cudaStream_t>(a.stream_tail);
+  // the operand kernels get their own stream too when the caller gives one: the caller's stream is often
+  // the legacy default stream, and work there does not run beside work of other streams
+  cudaStream_t s_op = a.stream_op ? static_cast<cudaStream_t>(a.stream_op) : stream;
+  const bool pipelined = s_gemm != nullptr && s_tail != nullptr && nchunks > 1 && a.workspace_bytes >= 2 * per;
+  if (!pipelined) {
+    if (a.workspace_bytes < per) return kErrWorkspace;
+    for (long long c = 0; c < nchunks; ++c) {
+      ChunkEvents ev;
+      if (c == (nchunks > 1 ? 1 : 0)) {
+        ev.time_begin = static_cast<cudaEvent_t>(a.ev_gemm_begin), ev.time_end = static_cast<cudaEvent_t>(a.ev_gemm_end);
+      }
+      const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
+      const int rc = score_chunk<FMT>(a, e0, n, ws, per, stream, stream, stream, ev);
+      if (rc != kOk) return rc;
+    }
+    return kOk;
+  }
+  // events: [0, n) op_done, [n, 2n) gemm_done, [2n, 3n) tail_done, [3n] begin, (3n, 4n] gemm_ready
+  const size_t nev = static_cast<size_t>(5 * nchunks + 1);
+  cudaEvent_t* evs = new cudaEvent_t[nev];
+  size_t made = 0;
+  int rc = kOk;
+  const bool trace = getenv("EVI_TRACE") != nullptr;  // debug: print the stage timeline of this call
+  for (; made < nev; ++made)
+    if (cudaEventCreateWithFlags(&evs[made], trace ? cudaEventDefault : cudaEventDisableTiming) != cudaSuccess) {
+      rc = kErrCuda;
+      break;
+    }
+  if (rc == kOk) {
+    cudaEvent_t begin = evs[3 * nchunks];
+    if (cudaEventRecord(begin, stream) != cudaSuccess || cudaStreamWaitEvent(s_gemm, begin, 0) != cudaSuccess ||
+        cudaStreamWaitEvent(s_tail, begin, 0) != cudaSuccess ||
+        (s_op != stream && cudaStreamWaitEvent(s_op, begin, 0) != cudaSuccess))
+      rc = kErrCuda;
+  }
+  for (long long c = 0; rc == kOk && c < nchunks; ++c) {
+    ChunkEvents ev;
+    ev.op_done = evs[c], ev.gemm_done = evs[nchunks + c], ev.tail_done = evs[2 * nchunks + c];
+    if (c >= 2) ev.wait_op = evs[nchunks + c - 2], ev.wait_gemm = evs[2 * nchunks + c - 2];
+    // the operand kernel of chunk c starts only once the GEMM of chunk c-1 is being launched: the GEMM's
+    // one-CTA-per-SM grid is placed first (it needs a whole SM's shared memory) and the elementwise CTAs
+    // fill the register space left beside it, instead of occupying the SMs ahead of it
+    ev.gemm_ready = evs[3 * nchunks + 1 + c];
+    if (c >= 1) ev.wait_op2 = evs[3 * nchunks + c];
+    if (trace) ev.op_start = evs[4 * nchunks + 1 + c];
+    if (c == 1) ev.time_begin = static_cast<cudaEvent_t>(a.ev_gemm_begin), ev.time_end = static_cast<cudaEvent_t>(a.ev_gemm_end);
+    const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
+    rc = score_chunk<FMT>(a, e0, n, ws + (c & 1) * per, per, s_op, s_gemm, s_tail, ev);
+  }
+  if (rc == kOk) {
+    // the caller's stream continues only after the last tail (tails are ordered on s_tail), GEMM and operand kernel
+    if (cudaStreamWaitEvent(stream, evs[3 * nchunks - 1], 0) != cudaSuccess ||
+        cudaStreamWaitEvent(stream, evs[2 * nchunks - 1], 0) != cudaSuccess ||
+        cudaStreamWaitEvent(stream, evs[nchunks - 1], 0) != cudaSuccess)
+      rc = kErrCuda;
+  }
+  if (trace && rc == kOk) {
+    cudaStreamSynchronize(stream);
+    for (long long c = 0; c < nchunks; ++c) {
+      float t_op = 0, t_gr = 0, t_gd = 0, t_td = 0, t_os = 0;
+      cudaEventElapsedTime(&t_os, evs[3 * nchunks], evs[4 * nchunks + 1 + c]);
+      cudaEventElapsedTime(&t_op, evs[3 * nchunks], evs[c]);
+      cudaEventElapsedTime(&t_gr, evs[3 * nchunks], evs[3 * nchunks + 1 + c]);
+      cudaEventElapsedTime(&t_gd, evs[3 * nchunks], evs[nchunks + c]);
+      cudaEventElapsedTime(&t_td, evs[3 * nchunks], evs[2 * nchunks + c]);
+      fprintf(stderr, "[evi trace] chunk %lld: op_start %.3f op_done %.3f  gemm_start %.3f  gemm_done %.3f  tail_done %.3f ms\n",
+              c, t_os, t_op, t_gr, t_gd, t_td);
+    }
+  }
+  for (size_t i = 0; i < made; ++i) cudaEventDestroy(evs[i]);  // deferred until the events complete
+  delete[] evs;
+  return rc;
 }
 
 }  // namespace evi
@@ -586,14 +727,8 @@ using namespace evi;
 
 extern "C" {
 
-size_t evi_score_workspace_bytes(long long num_edges, int direction, int want_features) {
-  const size_t ndir = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
-  const size_t rows = ndir * static_cast<size_t>(num_edges);
-  auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
-  size_t total = al(rows * 3 * D * 2) + al(rows * D * sizeof(float)) + al(rows * (D / gemm::BN) * sizeof(float2)) +
-                 al(rows * sizeof(float));
-  if (want_features) total += al(rows * D * 2) + al(rows * D * sizeof(float));
-  return total + 256;
+size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features, int num_buffers) {
+  return chunk_workspace_bytes(chunk_edges, direction, want_features) * static_cast<size_t>(num_buffers < 1 ? 1 : num_buffers);
 }
 
 int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const long long* ids,
@@ -615,7 +750,7 @@ int evi_struct_project(const float* node_struct, int num_nodes, int ns_dim, cons
   if (ns_dim < 2 || ns_dim > kMaxNodeStruct || node_struct == nullptr || struct_w_t == nullptr ||
       struct_b == nullptr || node_uv32 == nullptr)
     return kErrInvalidArg;
-  node_struct_proj_kernel<<<(num_nodes + 1) / 2, 256, 0, stream>>>(node_struct, num_nodes, ns_dim, struct_w_t,
+  node_struct_proj_kernel<<<(num_nodes + kUvNodes - 1) / kUvNodes, 128, 0, stream>>>(node_struct, num_nodes, ns_dim, struct_w_t,
                                                                    struct_b, node_uv32);
   return check_launch();
 }

@@ -104,12 +104,16 @@ class GraphBatch:
         return int(self.ptr_host.shape[0] - 1)
 
     @classmethod
-    def from_edge_index(cls, edge_index, ptr, device=None, validate: bool = True) -> "GraphBatch":
+    def from_edge_index(cls, edge_index, ptr, device=None, validate: bool = True, ptr_dev=None) -> "GraphBatch":
+        """``ptr`` is the host copy of the node offsets; ``ptr_dev`` an optional device copy (saves a
+        synchronous pageable H2D when the caller already has one)."""
         dev = _dev(device)
         L = _lib.load()
         ei = torch.as_tensor(edge_index).to(device=dev, dtype=torch.long).contiguous()
         ptr_host = np.asarray(torch.as_tensor(ptr).cpu().numpy(), dtype=np.int64)
-        ptr_dev = torch.from_numpy(ptr_host).to(dev)
+        if ptr_dev is None:
+            ptr_dev = torch.from_numpy(ptr_host).to(dev)
+        ptr_dev = ptr_dev.to(device=dev, dtype=torch.long).contiguous()
         E, B = int(ei.size(1)), int(ptr_host.shape[0] - 1)
         head32 = torch.empty(E, dtype=torch.int32, device=dev)
         tail32 = torch.empty(E, dtype=torch.int32, device=dev)
@@ -185,7 +189,7 @@ def bfs_jobs(row_ptr: torch.Tensor, adj: torch.Tensor, job_node_begin: np.ndarra
     d_nb, d_ne, d_off = up(nb, np.int32), up(ne, np.int32), up(job_off, np.int64)
     d_sp, d_src = up(job_src_ptr, np.int32), up(sources_local if len(sources_local) else np.zeros(1), np.int32)
     st = L.evi_bfs_multi_source(row_ptr.data_ptr(), adj.data_ptr(), len(nb), d_nb.data_ptr(), d_ne.data_ptr(),
-                                d_off.data_ptr(), d_sp.data_ptr(), d_src.data_ptr(), int(max_depth), dist.data_ptr(),
+                                d_off.data_ptr(), d_sp.data_ptr(), d_src.data_ptr(), 0, int(max_depth), dist.data_ptr(),
                                 queue.data_ptr(), _lib.stream_handle())
     _lib.check(st, "evi_bfs_multi_source")
     return dist[:total], dist_off

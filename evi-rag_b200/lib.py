@@ -41,6 +41,7 @@ class ScoreArgs(C.Structure):
         ("logits", _vp), ("logits_fwd", _vp), ("logits_bwd", _vp), ("edge_embeddings", _vp),
         ("workspace", _vp), ("workspace_bytes", _sz),
         ("ev_gemm_begin", _vp), ("ev_gemm_end", _vp),
+        ("chunk_edges", _ll), ("stream_gemm", _vp), ("stream_tail", _vp), ("stream_op", _vp),
     ]
 
 
@@ -51,13 +52,13 @@ PROTOTYPES = {
     "evi_dde_workspace_bytes": (_sz, [_i]),
     "evi_dde_forward": (_i, [_vp, _vp, _ll, _i, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
     "evi_build_csr": (_i, [_vp, _vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
-    "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]),
+    "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "evi_shortest_path_pairs": (_i, [_vp, _vp, _i] + [_vp] * 9 + [_i] + [_vp] * 4 + [_vp]),
     "evi_gather_rows": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp]),
     "evi_struct_project": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_convert_f32": (_i, [_vp, _vp, _ll, _i, _vp]),
     "evi_project": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
-    "evi_score_workspace_bytes": (_sz, [_ll, _i, _i]),
+    "evi_score_workspace_bytes": (_sz, [_ll, _i, _i, _i]),
     "evi_score_edges": (_i, [C.POINTER(ScoreArgs), _vp]),
     "evi_segmented_topk": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_topk_gather_payload": (_i, [_vp, _vp, _vp, _i, _i, _vp, _ll] + [_vp] * 11 + [_vp]),
@@ -76,10 +77,18 @@ _KERNELS_PER_CALL = {
     "evi_struct_project": lambda a: 1,
     "evi_convert_f32": lambda a: 1,
     "evi_project": lambda a: 1,
-    "evi_score_edges": lambda a: 5 if a[0]._obj.want_features else 3,
+    "evi_score_edges": lambda a: (5 if a[0]._obj.want_features else 3) * _num_chunks(a[0]._obj),
     "evi_segmented_topk": lambda a: 1,
     "evi_topk_gather_payload": lambda a: 1,
 }
+
+
+def _num_chunks(a) -> int:
+    if a.chunk_edges <= 0 or a.chunk_edges >= a.num_edges:
+        return 1
+    return int((a.num_edges + a.chunk_edges - 1) // a.chunk_edges)
+
+
 LAUNCHES = {"kernels": 0, "calls": 0}
 # EVI_DEBUG_SYNC=1: synchronize around every C-ABI call so a device fault names the call that made it
 _DEBUG_SYNC = os.environ.get("EVI_DEBUG_SYNC", "0") == "1"

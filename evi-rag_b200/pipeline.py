@@ -68,12 +68,10 @@ class RetrievalPipeline:
     def run_device(self, b: Any) -> Dict[str, torch.Tensor]:
         """Inputs already on the device. Returns device tensors."""
         dev = b.edge_index.device
-        gb = G.GraphBatch.from_edge_index(b.edge_index, b.ptr_host, device=dev, validate=False)
-        # seeds -> question-local ids on the device; jobs = one per question
+        gb = G.GraphBatch.from_edge_index(b.edge_index, b.ptr_host, device=dev, validate=False, ptr_dev=b.ptr)
+        # jobs = one per question; seeds stay batch-global, the kernel subtracts the question's node offset
         row_ptr, adj = G.build_csr(gb.head32, gb.tail32, gb.num_nodes, G.CSR_UNDIRECTED)
-        local_seeds = b.q_local_indices - torch.repeat_interleave(
-            b.ptr[:-1], (b.q_ptr[1:] - b.q_ptr[:-1]))
-        dist = self._bfs(row_ptr, adj, b, local_seeds)
+        dist = self._bfs(row_ptr, adj, b, b.q_local_indices)
         b._evi_graph = gb
         was = self.model.validate
         self.model.validate = False
@@ -89,7 +87,7 @@ class RetrievalPipeline:
         res["flags"] = self.model._flags
         return res
 
-    def _bfs(self, row_ptr, adj, b, local_seeds):
+    def _bfs(self, row_ptr, adj, b, seeds_global):
         from . import lib as _lib
 
         L = _lib.load()
@@ -100,7 +98,7 @@ class RetrievalPipeline:
         ptr32 = b.ptr.to(torch.int32)
         node_end32 = ptr32[1:].contiguous()
         src_ptr32 = b.q_ptr.to(torch.int32).contiguous()
-        seeds32 = local_seeds.to(torch.int32).contiguous()
+        seeds32 = seeds_global.to(torch.int32).contiguous()
         if seeds32.numel() == 0:
             seeds32 = torch.zeros(1, dtype=torch.int32, device=dev)
         dist_off = b.ptr.to(torch.long).contiguous()
@@ -108,7 +106,7 @@ class RetrievalPipeline:
         dist = torch.empty(max(1, n_total), dtype=torch.int32, device=dev)
         queue = torch.empty(max(1, 2 * n_total), dtype=torch.int32, device=dev)
         st = L.evi_bfs_multi_source(row_ptr.data_ptr(), adj.data_ptr(), B, ptr32.data_ptr(), node_end32.data_ptr(),
-                                    dist_off.data_ptr(), src_ptr32.data_ptr(), seeds32.data_ptr(),
+                                    dist_off.data_ptr(), src_ptr32.data_ptr(), seeds32.data_ptr(), 1,
                                     self.bfs_max_depth, dist.data_ptr(), queue.data_ptr(), _lib.stream_handle())
         _lib.check(st, "evi_bfs_multi_source")
         return dist[:n_total]

@@ -98,6 +98,7 @@ class Retriever(nn.Module):
         operand_dtype: str = "fp16",
         return_edge_embeddings: bool = False,
         max_workspace_bytes: int = 12 << 30,
+        pipeline_chunks: int = 4,
         validate: bool = True,
         **_: Any,
     ) -> None:
@@ -117,6 +118,8 @@ class Retriever(nn.Module):
         self.operand_dtype = operand_dtype
         self.return_edge_embeddings = bool(return_edge_embeddings)
         self.max_workspace_bytes = int(max_workspace_bytes)
+        self.pipeline_chunks = max(1, int(pipeline_chunks))
+        self._streams = None
         self.validate = bool(validate)
 
         d, h = self.emb_dim, self.hidden_dim
@@ -261,6 +264,14 @@ class Retriever(nn.Module):
         if self._ws is None or self._ws.numel() < nbytes or self._ws.device != dev:
             self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
         return self._ws
+
+    def _aux_streams(self, dev: torch.device):
+        """(GEMM stream, tail stream, operand stream) for the chunk pipeline; the GEMM one has the higher priority so
+        its CTAs are placed first whenever an SM frees up."""
+        if self._streams is None or self._streams[0].device != dev:
+            self._streams = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev, priority=0),
+                             torch.cuda.Stream(device=dev, priority=0))
+        return self._streams
 
     def _project(self, x16, w16, bias, acts, *, out16=None, out32=None, p=None):
         L = _lib.load()
@@ -439,9 +450,17 @@ class Retriever(nn.Module):
         logits_fwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_BACKWARD else None
         logits_bwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_FORWARD else None
         feats = torch.empty((E, self.hidden_dim), dtype=torch.float32, device=dev) if return_features else None
-        per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features))) / float(1 << 20)
-        chunk = max(1024, min(E, int(self.max_workspace_bytes / per_edge) // 1024 * 1024))
-        ws = self._workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features))), dev)
+        # chunking: `pipeline_chunks` chunks per batch (never below 16k edges per chunk), two workspace
+        # buffers when the aux streams are in use, bounded by max_workspace_bytes
+        pipelined = self.pipeline_chunks > 1 and not return_features
+        nbuf = 2 if pipelined else 1
+        per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features), 1)) / float(1 << 20)
+        chunk_cap = max(1024, int(self.max_workspace_bytes / (per_edge * nbuf)) // 1024 * 1024)
+        chunk = -(-E // self.pipeline_chunks) if pipelined else E
+        chunk = min(chunk_cap, max(16384, (chunk + 1023) // 1024 * 1024))
+        if chunk >= E:
+            chunk, nbuf, pipelined = E, 1, False
+        ws = self._workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features), nbuf)), dev)
         a = _lib.ScoreArgs()
         a.emb_dim, a.hidden_dim, a.direction, a.operand_format = d, self.hidden_dim, direction, fmt
         a.want_features, a.num_sms = int(return_features), p["num_sms"]
@@ -454,20 +473,20 @@ class Retriever(nn.Module):
         a.ln1_g, a.ln1_b, a.head_v, a.head_c0 = p["l1_g"].data_ptr(), p["l1_b"].data_ptr(), p["v"].data_ptr(), p["c0"]
         a.w2_16, a.w2_bias, a.head_w, a.head_b = p["w2"].data_ptr(), p["b2"].data_ptr(), p["wo"].data_ptr(), p["bo"]
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
+        a.num_edges, a.chunk_edges = E, chunk
+        a.head32, a.tail32, a.qid32, a.rel_slot32 = head32.data_ptr(), tail32.data_ptr(), qid32.data_ptr(), rel_slot32.data_ptr()
+        a.logits = logits.data_ptr()
+        a.logits_fwd = logits_fwd.data_ptr() if logits_fwd is not None else None
+        a.logits_bwd = logits_bwd.data_ptr() if logits_bwd is not None else None
+        a.edge_embeddings = feats.data_ptr() if feats is not None else None
+        if pipelined:
+            s_gemm, s_tail, s_op = self._aux_streams(dev)
+            a.stream_gemm, a.stream_tail, a.stream_op = s_gemm.cuda_stream, s_tail.cuda_stream, s_op.cuda_stream
         self.last_chunk_edges = min(chunk, E)
-        events = self.gemm_events  # (torch.cuda.Event begin, end) around the dominant GEMM, or None
-        for s in range(0, E, chunk):
-            n = min(chunk, E - s)
-            a.num_edges = n
-            a.ev_gemm_begin = events[0].cuda_event if events is not None and s == 0 else None
-            a.ev_gemm_end = events[1].cuda_event if events is not None and s == 0 else None
-            a.head32, a.tail32 = head32.data_ptr() + 4 * s, tail32.data_ptr() + 4 * s
-            a.qid32, a.rel_slot32 = qid32.data_ptr() + 4 * s, rel_slot32.data_ptr() + 4 * s
-            a.logits = logits.data_ptr() + 4 * s
-            a.logits_fwd = logits_fwd.data_ptr() + 4 * s if logits_fwd is not None else None
-            a.logits_bwd = logits_bwd.data_ptr() + 4 * s if logits_bwd is not None else None
-            a.edge_embeddings = feats.data_ptr() + 4 * s * self.hidden_dim if feats is not None else None
-            _lib.check(L.evi_score_edges(C.byref(a), stream), "evi_score_edges")
+        events = self.gemm_events  # (torch.cuda.Event begin, end) around one state_net.0 GEMM launch, or None
+        a.ev_gemm_begin = events[0].cuda_event if events is not None else None
+        a.ev_gemm_end = events[1].cuda_event if events is not None else None
+        _lib.check(L.evi_score_edges(C.byref(a), stream), "evi_score_edges")
         self._pending_flags = True
 
         # ---- a7: hide-and-seek bias (eval only when apply_in_eval; retriever.py:247-256) ----

@@ -74,12 +74,13 @@ int evi_build_csr(const int* head32, const int* tail32, long long num_edges, int
                   int* row_ptr, int* adj, int* scratch_counts, cudaStream_t stream);
 
 /* _bfs_dist — scripts/build_retrieval_pipeline.py:610-631. One CTA per job; a job is one
- * question's node range plus a list of question-local source ids. dist_out[job_dist_off[j] + v]
+ * question's node range plus a list of source ids (question-local, or batch-global when
+ * sources_are_global != 0: the job's node_begin is subtracted). dist_out[job_dist_off[j] + v]
  * = hop distance or -1; max_depth < 0: uncapped. queue_workspace: 2 ints per dist element. */
 int evi_bfs_multi_source(const int* row_ptr, const int* adj, int num_jobs, const int* job_node_begin,
                          const int* job_node_end, const long long* job_dist_off, const int* job_src_ptr,
-                         const int* sources, int max_depth, int* dist_out, int* queue_workspace,
-                         cudaStream_t stream);
+                         const int* sources, int sources_are_global, int max_depth, int* dist_out,
+                         int* queue_workspace, cudaStream_t stream);
 
 /* _select_shortest_edges_undirected / _directed + the mask OR of
  * _shortest_path_union_mask_by_pair — scripts/build_retrieval_pipeline.py:650-752, 755-815.
@@ -160,13 +161,22 @@ typedef struct evi_score_args {
   float* edge_embeddings;           /* [E, H] or NULL */
   void* workspace;
   size_t workspace_bytes;
-  /* optional cudaEvent_t pair recorded on `stream` around the state_net.0 GEMM launch (the
-   * dominant kernel) so a caller can time it without a profiler; NULL to skip */
+  /* optional cudaEvent_t pair recorded around one state_net.0 GEMM launch (the dominant kernel; the
+   * second chunk when there are several) so a caller can time it without a profiler; NULL to skip */
   void* ev_gemm_begin;
   void* ev_gemm_end;
+  /* chunking / pipelining: edges are processed `chunk_edges` at a time (<= 0: all at once). With two
+   * auxiliary streams (cudaStream_t; the GEMM one ideally of higher priority), more than one chunk and
+   * a workspace of two chunk buffers, the operand kernel of chunk c+1 and the tail of chunk c-1 run
+   * beside the GEMM of chunk c; `stream` rejoins after the last chunk. NULL: everything on `stream`. */
+  long long chunk_edges;
+  void* stream_gemm;
+  void* stream_tail;
+  void* stream_op;                  /* optional third stream for the operand kernels (else `stream`) */
 } evi_score_args;
 
-size_t evi_score_workspace_bytes(long long num_edges, int direction, int want_features);
+/* bytes for `num_buffers` (1 serial, 2 pipelined) per-chunk workspaces of `chunk_edges` edges */
+size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features, int num_buffers);
 int evi_score_edges(const evi_score_args* args, cudaStream_t stream);
 
 /* ---- ragged top-k ------------------------------------------------------------------------ */
