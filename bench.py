@@ -31,7 +31,7 @@ if ROOT not in sys.path:
 from evi_rag_b200.synthetic import WEBQSP_10K, generate_questions, make_embedding_tables  # noqa: E402
 from evi_rag_b200.weights import make_state_dict  # noqa: E402
 
-F_GEMM1_PER_EDGE_DIR = 2 * 3073 * 1024           # state_net.0 contraction, one direction
+F_SC_PER_EDGE_DIR = 2 * 1024 * 1024              # W_sc sc: the per-edge, per-direction block of state_net.0
 F_EDGE = 16_871_424                              # SURVEY §8d, bidirectional scoring per edge
 F_NODE = 2_097_152
 TOP_K = 100
@@ -50,7 +50,7 @@ def parse_args():
     ap.add_argument("--operand-dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pipeline-chunks", type=int, default=4,
-                    help="edge chunks per batch whose operand / GEMM / tail stages overlap on three streams (1: serial)")
+                    help="edge chunks per batch (bounds the scoring workspace)")
     return ap.parse_args()
 
 
@@ -292,7 +292,7 @@ def run_ours(args):
         return
 
     peak_tf, peak_hbm, peak_src = measured_peaks()
-    gemm_flops = [2 * ce * F_GEMM1_PER_EDGE_DIR for ce in chunk_edges]  # both directions in one launch
+    gemm_flops = [2 * ce * F_SC_PER_EDGE_DIR for ce in chunk_edges]  # both directions in one launch
     achieved_tf = float(np.mean([f / (ms * 1e-3) / 1e12 for f, ms in zip(gemm_flops, gemm_ms)]))
     step_flops = e_all * F_EDGE + n_all * F_NODE
     line = {
@@ -319,7 +319,8 @@ def run_ours(args):
         "gpu_launches": int(launches_all),
         "clocks": clocks,
         "roofline": {
-            "bound": "tensor", "kernel": "gemm_kernel<EpiPreNorm> (state_net.0: [2E,3072]x[3072,1024])",
+            "bound": "tensor", "kernel": "gemm_kernel<EpiStoreF32> (W_sc block of state_net.0: [2E_chunk,1024]x[1024,1024]; "
+                                         "flops counted = executed by that launch)",
             "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
             "traffic": None, "peak_source": peak_src,
             "ms_per_launch": float(np.mean(gemm_ms)), "share_of_step": float(np.sum(gemm_ms)) / ms_dev,

@@ -180,6 +180,23 @@ EVI_DEVINL void tma_load_2d(void* smem_dst, const void* tmap, uint64_t* bar, int
       : "memory");
 }
 
+// 2-D tiled bulk tensor store shared -> global (bulk async-group completion). The box is clipped to
+// the tensor map's bounds, so partial tiles need no masking.
+EVI_DEVINL void tma_store_2d(const void* tmap, const void* smem_src, int c_inner, int c_outer) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap),
+               "r"(smem_u32(smem_src)), "r"(c_inner), "r"(c_outer)
+               : "memory");
+}
+EVI_DEVINL void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+EVI_DEVINL void bulk_wait_group_read() {  // the sources of all but the N newest groups have been read
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+EVI_DEVINL void bulk_wait_group() {  // all but the N newest groups are complete (writes performed)
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // ---------------------------------------------------------------------------------------------
 // tcgen05: TMEM allocation, MMA issue, commit, TMEM loads
 // ---------------------------------------------------------------------------------------------

@@ -31,24 +31,33 @@ constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
 constexpr int ACC_STAGES = 2;
 constexpr int TMEM_COLS = ACC_STAGES * BN;  // 512
 constexpr int NUM_THREADS = 256;            // warps 0-3: TMA / MMA / TMEM-alloc / spare, 4-7: epilogue
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+// fp32 epilogues stage 32x32 sub-tiles (one 128-byte swizzle row per accumulator row) in shared memory
+// and write them with TMA stores: 2 buffers x 4 KB per epilogue warp
+constexpr int EPI_STAGE_BYTES = 32 * 128;
+constexpr int EPI_SMEM_BYTES = 4 * 2 * EPI_STAGE_BYTES;
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_SMEM_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 
 struct TileCoord {
   int m_blk, n_blk;
 };
 
-// minBlocksPerSM = 2 only caps registers at 128/thread (shared memory keeps one CTA per SM): the
-// CTA then takes exactly half the register file and an 8-warp, 128-register elementwise CTA of the
-// scoring pipeline fits beside it.
 template <int FMT, class Epi>
-__global__ void __launch_bounds__(NUM_THREADS, 2)
+__global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-            int M, int N, int K, typename Epi::Params ep) {
+            const __grid_constant__ CUtensorMap tmap_c, int M, int N, int K, const int* __restrict__ m_dev,
+            typename Epi::Params ep) {
+  // optional device-side row count (e.g. the number of distinct (question, relation) pairs, known
+  // only on the device): rows beyond it are neither loaded nor written
+  if (m_dev != nullptr) {
+    const int md = __ldg(m_dev);
+    M = md < M ? md : M;
+  }
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte alignment
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint8_t* epi_stage = smem + STAGES * STAGE_BYTES;  // 1024-byte aligned (STAGE_BYTES is a multiple of 1024)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_stage + EPI_SMEM_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
@@ -64,6 +73,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    if (Epi::kTmaStore) tma_prefetch_desc(&tmap_c);
   }
   if (warp_idx == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) {
@@ -157,15 +167,44 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
       typename Epi::RowState st;
       Epi::init_row(st);
+      if constexpr (Epi::kTmaStore) {
+        // accumulator row -> registers -> epilogue math -> swizzled 32x32 fp32 sub-tile in shared memory ->
+        // one TMA store per sub-tile (full 128-byte lines, clipped at the matrix edge by the tensor map)
+        uint8_t* my_stage = epi_stage + quarter * 2 * EPI_STAGE_BYTES;
+        const int row0 = m_blk * BM + quarter * 32;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
-        tmem_ld_wait();
-        const int col0 = n_blk * BN + c * 32;
-        if (row < M && col0 < N) Epi::template apply<FMT>(ep, st, row, col0, r);
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
+          uint8_t* buf = my_stage + (c & 1) * EPI_STAGE_BYTES;
+          if (lane == 0) bulk_wait_group_read<1>();  // the store issued two sub-tiles ago has left `buf`
+          __syncwarp();
+          tmem_ld_wait();
+          const int col0 = n_blk * BN + c * 32;
+          Epi::template transform<FMT>(ep, st, row, col0, r);
+          uint8_t* dst = buf + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) =
+                make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (row0 < M && col0 < N) tma_store_2d(&tmap_c, buf, col0, row0);
+            bulk_commit_group();  // always (an empty group is fine): keeps the buffer accounting of wait_group exact
+          }
+        }
+      } else {
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
+          tmem_ld_wait();
+          const int col0 = n_blk * BN + c * 32;
+          if (row < M && col0 < N) Epi::template apply<FMT>(ep, st, row, col0, r);
+        }
+        if (row < M) Epi::finish_row(ep, st, row, n_blk);
       }
-      if (row < M) Epi::finish_row(ep, st, row, n_blk);
       tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
@@ -174,6 +213,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
         acc_phase ^= 1u;
       }
     }
+    if (Epi::kTmaStore && lane == 0) bulk_wait_group<0>();  // every store of this warp has been performed
   }
 
   tc_fence_before_sync();
@@ -192,6 +232,7 @@ enum Act : int { kActNone = 0, kActTanh = 1, kActSigmoid = 2 };
 // out = act(acc + bias[n]); activation chosen per 256-column block (lets [W_gate ; W_bias] run as
 // one N=2048 GEMM). Writes a 16-bit copy (next GEMM operand / gather source) and/or fp32.
 struct EpiBiasAct {
+  static constexpr bool kTmaStore = false;
   struct Params {
     const float* bias;   // [N]
     void* out16;         // [M, ld16] 16-bit or null
@@ -207,7 +248,8 @@ struct EpiBiasAct {
     float v[32];
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
-      const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i));
+      const float4 b = p.bias != nullptr ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
       v[i + 0] = __uint_as_float(r[i + 0]) + b.x;
       v[i + 1] = __uint_as_float(r[i + 1]) + b.y;
       v[i + 2] = __uint_as_float(r[i + 2]) + b.z;
@@ -247,6 +289,7 @@ struct EpiBiasAct {
 // 1e-3 score budget), plus fp32 LayerNorm partial sums (sum, sum of squares) per row per
 // 256-column block.
 struct EpiPreNorm {
+  static constexpr bool kTmaStore = false;
   struct Params {
     const float* bias;    // [N] state_net.0.bias
     const float* w_dist;  // [N] state_net.0.weight[:, 3D]
@@ -288,6 +331,7 @@ struct EpiPreNorm {
 
 // state_net.4 output: feat = acc + b2 (fp32, retriever.py:180) — only when edge features are requested
 struct EpiBiasF32 {
+  static constexpr bool kTmaStore = false;
   struct Params {
     const float* bias;
     float* out32;
@@ -306,6 +350,43 @@ struct EpiBiasF32 {
     }
   }
   static EVI_DEVINL void finish_row(const Params&, RowState&, int, int) {}
+};
+
+// fp32 output through the staged TMA store: out = act(acc + bias[n]) with bias optional and the
+// activation chosen per 256-column block. Covers the partial products W_iv m / W_sc sc of state_net.0
+// (no bias, no activation), P = W_err node_repr, Rq = W_err r_ctx + b_1 and the gate|bias projection.
+struct EpiF32Tma {
+  static constexpr bool kTmaStore = true;
+  struct Params {
+    const float* bias;  // [N] or null
+    int act[8];         // per n-block activation
+  };
+  struct RowState {};
+  static EVI_DEVINL void init_row(RowState&) {}
+  template <int FMT>
+  static EVI_DEVINL void transform(const Params& p, RowState&, int, int col0, uint32_t (&r)[32]) {
+    const int act = p.act[(col0 / BN) & 7];
+    if (p.bias == nullptr && act == kActNone) return;
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 b = p.bias != nullptr ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+      v[i + 0] = __uint_as_float(r[i + 0]) + b.x;
+      v[i + 1] = __uint_as_float(r[i + 1]) + b.y;
+      v[i + 2] = __uint_as_float(r[i + 2]) + b.z;
+      v[i + 3] = __uint_as_float(r[i + 3]) + b.w;
+    }
+    if (act == kActTanh) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);
+    } else if (act == kActSigmoid) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = 1.0f / (1.0f + expf(-v[i]));
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
+  }
 };
 
 // --------------------------------------------------------------------------------------------
@@ -329,6 +410,20 @@ inline EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
+// row-major [rows, cols] fp32 output matrix with row pitch ld (elements); box = 32 rows x 32 cols (128 B)
+inline bool make_tmap_out_f32(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 4};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
 // row-major [rows, cols] 16-bit matrix with row pitch ld (elements); box = box_rows x 64 cols
 inline bool make_tmap_2d(CUtensorMap* map, int fmt, const void* base, uint64_t rows, uint64_t cols,
                          uint64_t ld, uint32_t box_rows) {
@@ -347,7 +442,8 @@ inline bool make_tmap_2d(CUtensorMap* map, int fmt, const void* base, uint64_t r
 
 template <int FMT, class Epi>
 inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
-                  const typename Epi::Params& ep, int num_sms, cudaStream_t stream) {
+                  const typename Epi::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev = nullptr,
+                  float* out32 = nullptr, int ldc = 0) {
   if (M <= 0) return kOk;
   if (K % 8 != 0 || lda % 8 != 0 || ldb % 8 != 0 || N % 32 != 0) return kErrInvalidArg;
   CUtensorMap ta, tb;
@@ -357,20 +453,22 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
   if (!make_tmap_2d(&tb, FMT, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K),
                     static_cast<uint64_t>(ldb), BN))
     return kErrCuda;
+  CUtensorMap tc = ta;  // placeholder when the epilogue stores by itself
+  if (Epi::kTmaStore) {
+    if (out32 == nullptr || ldc % 4 != 0 || (reinterpret_cast<uintptr_t>(out32) & 15) != 0) return kErrInvalidArg;
+    if (!make_tmap_out_f32(&tc, out32, static_cast<uint64_t>(M), static_cast<uint64_t>(N), static_cast<uint64_t>(ldc)))
+      return kErrCuda;
+  }
   auto kern = gemm_kernel<FMT, Epi>;
   static bool attr_set = false;  // per template instantiation
   if (!attr_set) {
     if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
       return kErrCuda;
-    // The driver configures the SM for the smallest shared-memory carve-out that holds the CTA (196 KB
-    // here), which leaves no room for the 13 KB of a co-resident elementwise CTA. Ask for the largest
-    // split (228 KB) so the scoring pipeline's operand kernel can be placed beside the GEMM CTA.
-    cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     attr_set = true;
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms ? tiles : num_sms;
-  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
+  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, M, N, K, m_dev, ep);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 

@@ -270,6 +270,52 @@ bfs_jobs_kernel(const int* __restrict__ row_ptr, const int* __restrict__ adj,
 }
 
 // ---------------------------------------------------------------------------------------------
+// a13, depth-capped flavour: level-synchronous sweeps over the question's edge list (no CSR needed).
+// One CTA per job; dist lives in shared memory; each level reads the job's edges once, coalesced
+// (8 B/edge/level). Meant for the small hop caps of retrieval (2-hop / 4-hop subgraphs): the cost is
+// O(levels * E_q), so uncapped BFS over long-diameter graphs should use the CSR frontier kernel above.
+// A node reached at level L+1 is written by every thread that discovers it with the same value, so
+// the result does not depend on thread order.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSweepThreads = 1024;
+
+__global__ void __launch_bounds__(kSweepThreads)
+bfs_sweep_kernel(const int* __restrict__ head, const int* __restrict__ tail,
+                 const long long* __restrict__ job_edge_begin, const long long* __restrict__ job_edge_end,
+                 const int* __restrict__ job_node_begin, const int* __restrict__ job_node_end,
+                 const long long* __restrict__ job_dist_off, const int* __restrict__ job_src_ptr,
+                 const int* __restrict__ sources, int sources_are_global, int directed, int max_depth,
+                 int smem_nodes, int* __restrict__ dist_out) {
+  extern __shared__ int sdist[];
+  const int job = blockIdx.x;
+  const int n0 = job_node_begin[job], nn = job_node_end[job] - n0;
+  const long long e0 = job_edge_begin[job], e1 = job_edge_end[job];
+  int* gdist = dist_out + job_dist_off[job];
+  int* dist = nn <= smem_nodes ? sdist : gdist;  // oversized jobs work in global memory
+  for (int i = threadIdx.x; i < nn; i += blockDim.x) dist[i] = -1;
+  __syncthreads();
+  for (int i = job_src_ptr[job] + threadIdx.x; i < job_src_ptr[job + 1]; i += blockDim.x) {
+    const int s = sources[i] - (sources_are_global ? n0 : 0);
+    if (s >= 0 && s < nn) dist[s] = 0;
+  }
+  __syncthreads();
+  for (int level = 0; max_depth < 0 || level < max_depth; ++level) {
+    int changed = 0;
+    for (long long e = e0 + threadIdx.x; e < e1; e += blockDim.x) {
+      const int u = __ldg(head + e) - n0, v = __ldg(tail + e) - n0;
+      if (static_cast<unsigned>(u) >= static_cast<unsigned>(nn) || static_cast<unsigned>(v) >= static_cast<unsigned>(nn))
+        continue;  // dropped like the reference adjacency builders (:579-580)
+      const int du = dist[u], dv = dist[v];
+      if (du == level && dv == -1) dist[v] = level + 1, changed = 1;
+      if (!directed && dv == level && du == -1) dist[u] = level + 1, changed = 1;
+    }
+    if (!__syncthreads_or(changed)) break;
+  }
+  if (dist != gdist)
+    for (int i = threadIdx.x; i < nn; i += blockDim.x) gdist[i] = dist[i];
+}
+
+// ---------------------------------------------------------------------------------------------
 // a14: per (start, answer) pair: edges on some shortest path. One CTA per pair.
 //   undirected: ds[u]+1+da[v]==dsa  or  ds[v]+1+da[u]==dsa ; directed: first test only.
 // Writes the OR-mask over pairs, the per-pair edge membership bytes and counts / lengths.
@@ -399,6 +445,25 @@ int evi_bfs_multi_source(const int* row_ptr, const int* adj, int num_jobs, const
   bfs_jobs_kernel<<<num_jobs, kBfsThreads, 0, stream>>>(row_ptr, adj, job_node_begin, job_node_end, job_dist_off,
                                                         job_src_ptr, sources, sources_are_global, max_depth,
                                                         dist_out, queue_workspace);
+  return check_launch();
+}
+
+int evi_bfs_edge_sweep(const int* head32, const int* tail32, int num_jobs, const long long* job_edge_begin,
+                       const long long* job_edge_end, const int* job_node_begin, const int* job_node_end,
+                       const long long* job_dist_off, const int* job_src_ptr, const int* sources,
+                       int sources_are_global, int directed, int max_depth, int* dist_out, cudaStream_t stream) {
+  if (num_jobs <= 0) return kOk;
+  constexpr int kSmemNodes = 40 * 1024;  // 160 KB of dist per CTA
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(bfs_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemNodes * 4) !=
+        cudaSuccess)
+      return kErrCuda;
+    attr_set = true;
+  }
+  bfs_sweep_kernel<<<num_jobs, kSweepThreads, kSmemNodes * 4, stream>>>(
+      head32, tail32, job_edge_begin, job_edge_end, job_node_begin, job_node_end, job_dist_off, job_src_ptr, sources,
+      sources_are_global, directed, max_depth, kSmemNodes, dist_out);
   return check_launch();
 }
 

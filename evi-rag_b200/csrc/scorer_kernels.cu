@@ -227,10 +227,14 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
   return 1.0f / (1.0f + __expf(-(warp_sum(nav) + sp.bn)));
 }
 
-constexpr int kEdgeWarps = 4;  // 4 warps x 128 registers = a quarter of the register file: fits beside the GEMM CTA
+constexpr int kEdgeWarps = 8;
 
+// Operand rows of one chunk of edges (the inputs of the two per-edge contractions of state_net.0):
+//   m16  [E, D]   h * r_ctx * t            (shared by both directions: iv_dir = nav_dir * m)
+//   sc16 [nd*E, D] struct context, forward rows first, then backward rows
+//   scal [E, 4]   nav_f, nav_b, dist_f, dist_b
 template <int FMT>
-__global__ void __launch_bounds__(kEdgeWarps * 32, 4)
+__global__ void __launch_bounds__(kEdgeWarps * 32)
 edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
                     const uint16_t* __restrict__ node_repr,   // [N, D]
@@ -239,8 +243,8 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
                     const float* __restrict__ node_uv,        // [N, 2D]: U | V (node_struct_proj_kernel)
                     StructParams sp, int do_fwd, int do_bwd, int num_nodes, int num_rel_rows, int num_questions,
                     unsigned* __restrict__ flags,
-                    uint16_t* __restrict__ a_fwd, uint16_t* __restrict__ a_bwd,  // [E, 3D]
-                    float* __restrict__ dist_fwd, float* __restrict__ dist_bwd) {
+                    uint16_t* __restrict__ m16, uint16_t* __restrict__ sc_fwd, uint16_t* __restrict__ sc_bwd,
+                    float4* __restrict__ scal) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (long long e = blockIdx.x * static_cast<long long>(kEdgeWarps) + warp; e < num_edges;
        e += static_cast<long long>(gridDim.x) * kEdgeWarps) {
@@ -252,96 +256,74 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
       if (lane == 0) atomicOr(flags, kFlagOutOfRange);  // keep going on row 0: no wild reads
       h = t = q = rs = 0;
     }
-    uint16_t* row_f = a_fwd + static_cast<size_t>(e) * 3 * D;
-    uint16_t* row_b = a_bwd + static_cast<size_t>(e) * 3 * D;
     const float* uv_h = node_uv + static_cast<size_t>(h) * 2 * D;
     const float* uv_t = node_uv + static_cast<size_t>(t) * 2 * D;
     float nav_f = 0.f, nav_b = 0.f;
-    if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, row_f + D);
-    if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, sp, lane, row_b + D);
+    if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, sc_fwd + static_cast<size_t>(e) * D);
+    if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, sp, lane, sc_bwd + static_cast<size_t>(e) * D);
 
     const uint16_t* hp = node_repr + static_cast<size_t>(h) * D;
     const uint16_t* tp = node_repr + static_cast<size_t>(t) * D;
     const uint16_t* rp = rel_repr + static_cast<size_t>(rs) * D;
     const float* gp = gate_bias + static_cast<size_t>(q) * 2 * D;
+    uint16_t* mrow = m16 + static_cast<size_t>(e) * D;
     float n2f = 0.f, n2b = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int c = i * 256 + lane * 8;
-      float hv[8], tv[8], rv[8], g[8], b[8], o[8];
+      float hv[8], tv[8], rv[8], g[8], b[8];
       unpack8<FMT>(ldg_nc_v4(hp + c), hv);
       unpack8<FMT>(ldg_nc_v4(tp + c), tv);
       unpack8<FMT>(ldg_nc_v4(rp + c), rv);
       ldg_v8_keep(gp + c, g);
       ldg_v8_keep(gp + D + c, b);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) rv[j] = fmaf(rv[j], g[j], b[j]);  // r_ctx
-      if (do_fwd) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          o[j] = hv[j] + rv[j] - tv[j];
-          n2f = fmaf(o[j], o[j], n2f);
-        }
-        st_cs_v4(row_f + 2 * D + c, pack8<FMT>(o));
+      for (int j = 0; j < 8; ++j) {
+        rv[j] = fmaf(rv[j], g[j], b[j]);  // r_ctx (retriever.py:464)
+        const float d = hv[j] - tv[j];
+        const float ef = rv[j] + d, eb = rv[j] - d;  // err of either direction (retriever.py:477)
+        n2f = fmaf(ef, ef, n2f);
+        n2b = fmaf(eb, eb, n2b);
+        rv[j] = hv[j] * rv[j] * tv[j];  // symmetric DistMult term (retriever.py:472)
       }
-      if (do_bwd) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          o[j] = tv[j] + rv[j] - hv[j];
-          n2b = fmaf(o[j], o[j], n2b);
-        }
-        st_cs_v4(row_b + 2 * D + c, pack8<FMT>(o));
-      }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) rv[j] = hv[j] * rv[j] * tv[j];  // symmetric DistMult term
-      if (do_fwd) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rv[j] * nav_f;
-        st_cs_v4(row_f + c, pack8<FMT>(o));
-      }
-      if (do_bwd) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rv[j] * nav_b;
-        st_cs_v4(row_b + c, pack8<FMT>(o));
-      }
+      st_cs_v4(mrow + c, pack8<FMT>(rv));
     }
-    if (do_fwd) {
-      n2f = warp_sum(n2f);
-      if (lane == 0) dist_fwd[e] = -sqrtf(n2f);
-    }
-    if (do_bwd) {
-      n2b = warp_sum(n2b);
-      if (lane == 0) dist_bwd[e] = -sqrtf(n2b);
-    }
+    n2f = warp_sum(n2f);
+    n2b = warp_sum(n2b);
+    if (lane == 0) scal[e] = make_float4(nav_f, nav_b, -sqrtf(n2f), -sqrtf(n2b));
   }
 }
 
 // ---------------------------------------------------------------------------------------------
-// Tail: LayerNorm (exact fp32 stats from the GEMM epilogue) + GELU + collapsed score head.
+// Tail: assemble the state_net.0 pre-activation of both directions from its linear pieces,
+//   z_dir = nav_dir * (W_iv m) + W_sc sc_dir +- (P[h] - P[t]) + Rq[pair] + dist_dir * w_dist
+//   P[n] = W_err node_repr[n],  Rq[pair] = W_err r_ctx[pair] + b_1          (retriever.py:477-482, linear in err)
+// then LayerNorm (two-pass, fp32, in registers) + GELU + the collapsed score head
 //   logit = w_o . (W_2 g + b_2) + b_o = (W_2^T w_o) . g + (w_o . b_2 + b_o)      retriever.py:482-483
 // and the fwd/bwd softmax combine (retriever.py:369-381). One warp per edge.
 // Optionally writes g (16-bit) for the feature path (state_net.4 as a second GEMM).
 // ---------------------------------------------------------------------------------------------
 struct TailParams {
-  const float* ln_g;  // state_net.1.weight
+  const float* w_dist;  // [H] state_net.0.weight[:, 3D]
+  const float* ln_g;    // state_net.1.weight
   const float* ln_b;
-  const float* v;     // W_2^T w_o
-  float c0;           // w_o . b_2 + b_o
+  const float* v;       // W_2^T w_o
+  float c0;             // w_o . b_2 + b_o
 };
 
 template <int FMT>
-EVI_DEVINL float tail_one(const float* __restrict__ zrow, const float2* __restrict__ st, int n_blocks,
-                          const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
-  float sum = 0.f, sumsq = 0.f;
-  for (int i = 0; i < n_blocks; ++i) {
-    const float2 s = __ldg(st + i);
-    sum += s.x, sumsq += s.y;
+EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
+  float sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) sum += z[j];
+  const float mean = warp_sum(sum) * (1.0f / D);
+  float var = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float d = z[j] - mean;
+    var = fmaf(d, d, var);
   }
-  const float mean = sum * (1.0f / D);
-  const float var = fmaxf(sumsq * (1.0f / D) - mean * mean, 0.f);
-  const float rstd = rsqrtf(var + kLnEps);
-  float z[32];
-  load_row32(zrow, lane, z);
+  const float rstd = rsqrtf(warp_sum(var) * (1.0f / D) + kLnEps);
   float acc = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -363,29 +345,61 @@ EVI_DEVINL float tail_one(const float* __restrict__ zrow, const float2* __restri
 
 template <int FMT>
 __global__ void __launch_bounds__(256)
-score_tail_kernel(const float* __restrict__ z_fwd, const float* __restrict__ z_bwd,
-                  const float2* __restrict__ st_fwd, const float2* __restrict__ st_bwd, int n_blocks,
-                  long long num_edges, TailParams tp, uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd,
-                  float* __restrict__ logits, float* __restrict__ logits_fwd, float* __restrict__ logits_bwd) {
+score_tail_kernel(const float* __restrict__ mm,                                  // [E, D]  W_iv m
+                  const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,  // [E, D]  W_sc sc_dir (or null)
+                  const float4* __restrict__ scal, const int* __restrict__ head, const int* __restrict__ tail,
+                  const int* __restrict__ pair_slot, const float* __restrict__ node_p, const float* __restrict__ pair_rq,
+                  int num_nodes, int pair_rows, long long num_edges, TailParams tp, uint16_t* __restrict__ g_fwd,
+                  uint16_t* __restrict__ g_bwd, float* __restrict__ logits, float* __restrict__ logits_fwd,
+                  float* __restrict__ logits_bwd) {
   const int lane = threadIdx.x & 31;
   const long long e = blockIdx.x * static_cast<long long>(blockDim.x >> 5) + (threadIdx.x >> 5);
   if (e >= num_edges) return;
+  int h = __ldg(head + e), t = __ldg(tail + e), ps = __ldg(pair_slot + e);
+  if (static_cast<unsigned>(h) >= static_cast<unsigned>(num_nodes) ||
+      static_cast<unsigned>(t) >= static_cast<unsigned>(num_nodes) ||
+      static_cast<unsigned>(ps) >= static_cast<unsigned>(pair_rows))
+    h = t = ps = 0;  // flagged by the operand kernel / pair kernel
+  const float4 sc = __ldg(scal + e);
+  const bool has_f = s_fwd != nullptr, has_b = s_bwd != nullptr;
+  const float* mrow = mm + static_cast<size_t>(e) * D;
+  const float* ph = node_p + static_cast<size_t>(h) * D;
+  const float* pt = node_p + static_cast<size_t>(t) * D;
+  const float* rq = pair_rq + static_cast<size_t>(ps) * D;
+  float zf[32], zb[32];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 256 + lane * 8;
+    float m[8], a[8], b[8], r[8], wd[8];
+    ldg_v8_stream(mrow + c, m);
+    ldg_v8_keep(ph + c, a);
+    ldg_v8_keep(pt + c, b);
+    ldg_v8_keep(rq + c, r);
+    ldg_v8_keep(tp.w_dist + c, wd);
+    if (has_f) {
+      float s[8];
+      ldg_v8_stream(s_fwd + static_cast<size_t>(e) * D + c, s);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], s[j]) + (a[j] - b[j]) + fmaf(sc.z, wd[j], r[j]);
+    }
+    if (has_b) {
+      float s[8];
+      ldg_v8_stream(s_bwd + static_cast<size_t>(e) * D + c, s);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], s[j]) - (a[j] - b[j]) + fmaf(sc.w, wd[j], r[j]);
+    }
+  }
   float lf = 0.f, lb = 0.f;
-  const bool has_f = z_fwd != nullptr, has_b = z_bwd != nullptr;
-  if (has_f)
-    lf = tail_one<FMT>(z_fwd + static_cast<size_t>(e) * D, st_fwd + static_cast<size_t>(e) * n_blocks, n_blocks, tp,
-                       lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
-  if (has_b)
-    lb = tail_one<FMT>(z_bwd + static_cast<size_t>(e) * D, st_bwd + static_cast<size_t>(e) * n_blocks, n_blocks, tp,
-                       lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
+  if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
+  if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
   if (lane == 0) {
     if (has_f && logits_fwd) logits_fwd[e] = lf;
     if (has_b && logits_bwd) logits_bwd[e] = lb;
     if (logits) {
       float out;
       if (has_f && has_b) {  // softmax([lf, lb]) weighted sum
-        const float m = fmaxf(lf, lb);
-        const float ef = expf(lf - m), eb = expf(lb - m);
+        const float mx = fmaxf(lf, lb);
+        const float ef = expf(lf - mx), eb = expf(lb - mx);
         const float inv = 1.0f / (ef + eb);
         out = (ef * inv) * lf + (eb * inv) * lb;
       } else {
@@ -464,6 +478,121 @@ __global__ void convert_f32_to_16_kernel(const float* __restrict__ src, uint16_t
   reinterpret_cast<uint4*>(dst)[i] = w;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Distinct (question, relation) pairs of a batch. r_ctx = rel * gate[q] + bias[q] (retriever.py:464)
+// depends only on the pair, so W_err r_ctx is computed once per pair instead of once per edge and
+// direction. One CTA per question: relation bitmap in shared memory -> rank of each relation id
+// inside the question -> pair slot = base (one atomicAdd per question) + rank. Slot numbering
+// across questions depends on CTA order; nothing downstream depends on the numbering.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+relation_pairs_kernel(const int* __restrict__ rel, const long long* __restrict__ edge_ptr, int num_relations,
+                      int words, int capacity, int* __restrict__ pair_slot, int* __restrict__ pair_q,
+                      int* __restrict__ pair_rel, int* __restrict__ num_pairs, unsigned* __restrict__ flags) {
+  extern __shared__ uint32_t bm[];       // [words] bitmap, then [words] exclusive popcount prefix
+  uint32_t* prefix = bm + words;
+  __shared__ int warp_tot[8];
+  __shared__ int s_carry, s_base;
+  const int q = blockIdx.x, tid = threadIdx.x;
+  const long long e0 = edge_ptr[q], e1 = edge_ptr[q + 1];
+  for (int i = tid; i < words; i += blockDim.x) bm[i] = 0u;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (long long e = e0 + tid; e < e1; e += blockDim.x) {
+    const int r = __ldg(rel + e);
+    if (static_cast<unsigned>(r) >= static_cast<unsigned>(num_relations)) {
+      atomicOr(flags, kFlagOutOfRange);
+      continue;
+    }
+    atomicOr(&bm[r >> 5], 1u << (r & 31));
+  }
+  __syncthreads();
+  const int lane = tid & 31, w = tid >> 5;
+  for (int base = 0; base < words; base += blockDim.x) {
+    const int i = base + tid;
+    const int c = i < words ? __popc(bm[i]) : 0;
+    int incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    int off = s_carry;
+    for (int j = 0; j < w; ++j) off += warp_tot[j];
+    if (i < words) prefix[i] = static_cast<uint32_t>(off + incl - c);
+    __syncthreads();
+    if (tid == blockDim.x - 1) s_carry = off + incl;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    const int count = s_carry;
+    int b = atomicAdd(num_pairs, count);
+    if (b + count > capacity) {
+      atomicOr(flags, kFlagOutOfRange);
+      b = 0;  // never write outside the pair arrays; the flag makes the host raise
+    }
+    s_base = b;
+  }
+  __syncthreads();
+  const int pbase = s_base;
+  const bool fits = pbase + s_carry <= capacity;
+  for (long long e = e0 + tid; e < e1; e += blockDim.x) {
+    const int r = __ldg(rel + e);
+    int slot = 0;
+    if (static_cast<unsigned>(r) < static_cast<unsigned>(num_relations) && fits)
+      slot = pbase + static_cast<int>(prefix[r >> 5]) + __popc(bm[r >> 5] & ((1u << (r & 31)) - 1u));
+    pair_slot[e] = slot;
+  }
+  if (fits) {
+    for (int i = tid; i < words; i += blockDim.x) {
+      uint32_t bits = bm[i];
+      int slot = pbase + static_cast<int>(prefix[i]);
+      while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        pair_q[slot] = q;
+        pair_rel[slot] = i * 32 + b;
+        ++slot;
+      }
+    }
+  }
+}
+
+// rc16[slot] = fp16/bf16(rel_repr[pair_rel] * gate[pair_q] + bias[pair_q]); one warp per pair slot
+template <int FMT>
+__global__ void __launch_bounds__(256)
+pair_context_kernel(const int* __restrict__ pair_q, const int* __restrict__ pair_rel, const int* __restrict__ num_pairs,
+                    int capacity, const uint16_t* __restrict__ rel_repr, int num_rel_rows,
+                    const float* __restrict__ gate_bias, int num_questions, uint16_t* __restrict__ rc16,
+                    unsigned* __restrict__ flags) {
+  const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int n = min(__ldg(num_pairs), capacity);
+  if (slot >= n) return;
+  const int lane = threadIdx.x & 31;
+  int q = __ldg(pair_q + slot), r = __ldg(pair_rel + slot);
+  if (static_cast<unsigned>(q) >= static_cast<unsigned>(num_questions) ||
+      static_cast<unsigned>(r) >= static_cast<unsigned>(num_rel_rows)) {
+    if (lane == 0) atomicOr(flags, kFlagOutOfRange);
+    q = r = 0;
+  }
+  const uint16_t* rp = rel_repr + static_cast<size_t>(r) * D;
+  const float* gp = gate_bias + static_cast<size_t>(q) * 2 * D;
+  uint16_t* out = rc16 + static_cast<size_t>(slot) * D;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 256 + lane * 8;
+    float rv[8], g[8], b[8];
+    unpack8<FMT>(ldg_nc_v4(rp + c), rv);
+    ldg_v8_keep(gp + c, g);
+    ldg_v8_keep(gp + D + c, b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) rv[j] = fmaf(rv[j], g[j], b[j]);
+    *reinterpret_cast<uint4*>(out + c) = pack8<FMT>(rv);
+  }
+}
+
 // -------------------------------------------------------------------------------------------
 // host-side dispatch on operand format
 // -------------------------------------------------------------------------------------------
@@ -484,73 +613,60 @@ static int gather_rows_impl(const void* src, int src_is_f32, long long src_rows,
 }
 
 template <int FMT>
-static int linear_act_impl(const void* x16, int m, const void* w16, int n, int k, const float* bias,
-                           const int* act_per_block, void* out16, float* out32, int num_sms,
+static int linear_act_impl(const void* x16, int m, const int* m_dev, const void* w16, int ldw, int n, int k,
+                           const float* bias, const int* act_per_block, void* out16, float* out32, int num_sms,
                            cudaStream_t stream) {
+  if (out16 == nullptr && out32 != nullptr) {  // fp32 only: staged TMA-store epilogue
+    gemm::EpiF32Tma::Params t;
+    t.bias = bias;
+    for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
+    return gemm::launch<FMT, gemm::EpiF32Tma>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out32, n);
+  }
   gemm::EpiBiasAct::Params p;
   p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = n, p.ld32 = n;
   for (int i = 0; i < 8; ++i) p.act[i] = act_per_block[i];
-  return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, k, m, n, k, p, num_sms, stream);
+  return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
 }
 
-// One chunk of edges [e0, e0 + n): operand rows on s_op, state_net.0 GEMM on s_gemm, LayerNorm/GELU/head
-// tail on s_tail. The three streams may be the same one (serial) or different (pipelined by the caller
-// through the events below). `ws` is one per-chunk workspace buffer.
-struct ChunkEvents {
-  cudaEvent_t wait_op = nullptr;    // s_op waits for it before writing A / dist (buffer reuse)
-  cudaEvent_t wait_op2 = nullptr;   // s_op also waits for it: the previous chunk's GEMM is about to start
-  cudaEvent_t op_done = nullptr;    // recorded on s_op, waited by s_gemm
-  cudaEvent_t wait_gemm = nullptr;  // s_gemm also waits for it (z / stats buffer reuse)
-  cudaEvent_t gemm_ready = nullptr; // recorded on s_gemm right before the GEMM launch
-  cudaEvent_t op_start = nullptr;   // (trace only) recorded on s_op once its waits have passed
-  cudaEvent_t gemm_done = nullptr;  // recorded on s_gemm, waited by s_tail
-  cudaEvent_t tail_done = nullptr;  // recorded on s_tail
-  cudaEvent_t time_begin = nullptr, time_end = nullptr;  // optional timing pair around the GEMM
-};
-
-// An SM keeps one L1 / shared-memory split while CTAs are resident, so a kernel that prefers a large L1
-// is not placed beside the GEMM CTA (which configures the SM for maximum shared memory). In pipelined
-// mode the elementwise kernels ask for the same split; serial mode leaves them the default (larger L1).
-template <class K>
-static void prefer_carveout(K kernel, bool max_shared) {
-  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                       max_shared ? cudaSharedmemCarveoutMaxShared : cudaSharedmemCarveoutDefault);
+// workspace of one chunk of `E` edges:
+//   m16 [E, D] 16-bit | sc16 [nd*E, D] 16-bit | mm [E, D] f32 | s [nd*E, D] f32 | scal [E] float4
+//   (features) g16 [nd*E, D] 16-bit | feat [nd*E, D] f32
+static size_t chunk_workspace_bytes(long long num_edges, int direction, int want_features) {
+  const size_t nd = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
+  const size_t E = static_cast<size_t>(num_edges);
+  auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
+  size_t total = al(E * D * 2) + al(nd * E * D * 2) + al(E * D * sizeof(float)) + al(nd * E * D * sizeof(float)) +
+                 al(E * sizeof(float4));
+  if (want_features) total += al(nd * E * D * 2) + al(nd * E * D * sizeof(float));
+  return total + 256;
 }
 
 template <int FMT>
-static int score_chunk(const evi_score_args& a, long long e0, long long n, uint8_t* ws, size_t ws_bytes,
-                       cudaStream_t s_op, cudaStream_t s_gemm, cudaStream_t s_tail, const ChunkEvents& ev) {
-  const long long E = n;
-  const bool overlapped = s_gemm != s_op;
-  prefer_carveout(edge_operand_kernel<FMT>, overlapped);
-  prefer_carveout(score_tail_kernel<FMT>, overlapped);
+static int score_chunk(const evi_score_args& a, long long e0, long long E, uint8_t* ws, size_t ws_bytes,
+                       cudaStream_t stream, cudaEvent_t time_begin, cudaEvent_t time_end) {
   const int do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
-  const int ndir = do_f + do_b;
-  const int n_blocks = D / gemm::BN;
-  // workspace carve-up: A [ndir*E, 3D] 16-bit | z [ndir*E, D] f32 | stats [ndir*E, n_blocks] float2 |
-  //                     dist [ndir*E] f32 | (features) g [ndir*E, D] 16-bit | feat [ndir*E, D] f32
+  const size_t nd = static_cast<size_t>(do_f + do_b);
   size_t off = 0;
   auto take = [&](size_t bytes) {
     uint8_t* p = ws + off;
     off += (bytes + 255) & ~static_cast<size_t>(255);
     return p;
   };
-  const size_t rows = static_cast<size_t>(ndir) * E;
-  uint16_t* A = reinterpret_cast<uint16_t*>(take(rows * 3 * D * 2));
-  float* Z = reinterpret_cast<float*>(take(rows * D * sizeof(float)));
-  float2* ST = reinterpret_cast<float2*>(take(rows * n_blocks * sizeof(float2)));
-  float* DIST = reinterpret_cast<float*>(take(rows * sizeof(float)));
+  const size_t n = static_cast<size_t>(E);
+  uint16_t* M16 = reinterpret_cast<uint16_t*>(take(n * D * 2));
+  uint16_t* SC16 = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
+  float* MM = reinterpret_cast<float*>(take(n * D * sizeof(float)));
+  float* S = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
+  float4* SCAL = reinterpret_cast<float4*>(take(n * sizeof(float4)));
   uint16_t* G = nullptr;
   float* FEAT = nullptr;
   if (a.want_features) {
-    G = reinterpret_cast<uint16_t*>(take(rows * D * 2));
-    FEAT = reinterpret_cast<float*>(take(rows * D * sizeof(float)));
+    G = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
+    FEAT = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
   }
   if (off > ws_bytes) return kErrWorkspace;
-  uint16_t* A_f = A;
-  uint16_t* A_b = A + (do_f ? static_cast<size_t>(E) * 3 * D : 0);
-  float* dist_f = DIST;
-  float* dist_b = DIST + (do_f ? E : 0);
+  uint16_t* sc_f = SC16;
+  uint16_t* sc_b = SC16 + (do_f ? n * D : 0);
   float* logits = a.logits ? a.logits + e0 : nullptr;
   float* logits_fwd = a.logits_fwd ? a.logits_fwd + e0 : nullptr;
   float* logits_bwd = a.logits_bwd ? a.logits_bwd + e0 : nullptr;
@@ -558,167 +674,76 @@ static int score_chunk(const evi_score_args& a, long long e0, long long n, uint8
 
   StructParams sp;
   sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
-  if (ev.wait_op && cudaStreamWaitEvent(s_op, ev.wait_op, 0) != cudaSuccess) return kErrCuda;
-  if (ev.wait_op2 && cudaStreamWaitEvent(s_op, ev.wait_op2, 0) != cudaSuccess) return kErrCuda;
-  if (ev.op_start) cudaEventRecord(ev.op_start, s_op);
-  long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
-  const int grid = static_cast<int>(want < 4LL * a.num_sms ? want : 4LL * a.num_sms);
-  edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, s_op>>>(
+  const long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
+  const int grid = static_cast<int>(want < 8LL * a.num_sms ? want : 8LL * a.num_sms);
+  edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
       a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
       static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
-      a.num_rel_rows, a.num_questions, a.flags, A_f, A_b, dist_f, dist_b);
+      a.num_rel_rows, a.num_questions, a.flags, M16, sc_f, sc_b, SCAL);
   if (check_launch() != kOk) return kErrCuda;
-  if (ev.op_done) {
-    if (cudaEventRecord(ev.op_done, s_op) != cudaSuccess || cudaStreamWaitEvent(s_gemm, ev.op_done, 0) != cudaSuccess)
-      return kErrCuda;
-  }
-  if (ev.wait_gemm && cudaStreamWaitEvent(s_gemm, ev.wait_gemm, 0) != cudaSuccess) return kErrCuda;
 
-  gemm::EpiPreNorm::Params zp;
-  zp.bias = a.w1_bias, zp.w_dist = a.w1_dist_col, zp.dist = DIST, zp.z32 = Z, zp.stats = ST;
-  zp.ldz = D, zp.n_blocks = n_blocks;
-  if (ev.gemm_ready && cudaEventRecord(ev.gemm_ready, s_gemm) != cudaSuccess) return kErrCuda;
-  if (ev.time_begin) cudaEventRecord(ev.time_begin, s_gemm);
-  int rc = gemm::launch<FMT, gemm::EpiPreNorm>(A, 3 * D, a.w1_main16, 3 * D, static_cast<int>(rows), D, 3 * D, zp,
-                                               a.num_sms, s_gemm);
-  if (ev.time_end) cudaEventRecord(ev.time_end, s_gemm);
+  // state_net.0 split by input block (weight columns [iv | sc | err | dist], retriever.py:470-481):
+  //   W_iv m -> MM (once per edge, shared by both directions),  W_sc sc_dir -> S (once per edge and direction)
+  const uint16_t* w1 = static_cast<const uint16_t*>(a.w1_main16);
+  gemm::EpiF32Tma::Params plain;
+  plain.bias = nullptr;
+  for (int i = 0; i < 8; ++i) plain.act[i] = gemm::kActNone;
+  int rc = gemm::launch<FMT, gemm::EpiF32Tma>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, a.num_sms, stream,
+                                              nullptr, MM, D);
   if (rc != kOk) return rc;
-  if (ev.gemm_done) {
-    if (cudaEventRecord(ev.gemm_done, s_gemm) != cudaSuccess ||
-        cudaStreamWaitEvent(s_tail, ev.gemm_done, 0) != cudaSuccess)
-      return kErrCuda;
-  }
+  if (time_begin) cudaEventRecord(time_begin, stream);
+  rc = gemm::launch<FMT, gemm::EpiF32Tma>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, a.num_sms,
+                                          stream, nullptr, S, D);
+  if (time_end) cudaEventRecord(time_end, stream);
+  if (rc != kOk) return rc;
 
   TailParams tp;
-  tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
-  const float* z_f = do_f ? Z : nullptr;
-  const float* z_b = do_b ? Z + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
-  const float2* st_f = ST;
-  const float2* st_b = ST + (do_f ? static_cast<size_t>(E) * n_blocks : 0);
+  tp.w_dist = a.w1_dist_col, tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
+  const float* s_f = do_f ? S : nullptr;
+  const float* s_b = do_b ? S + (do_f ? n * D : 0) : nullptr;
   uint16_t* g_f = G;
-  uint16_t* g_b = G ? G + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
+  uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
   const int tgrid = static_cast<int>((E + 7) / 8);
-  if (!a.want_features) {
-    score_tail_kernel<FMT><<<tgrid, 256, 0, s_tail>>>(z_f, z_b, st_f, st_b, n_blocks, E, tp, nullptr, nullptr,
-                                                      logits, logits_fwd, logits_bwd);
-    if (check_launch() != kOk) return kErrCuda;
-    if (ev.tail_done && cudaEventRecord(ev.tail_done, s_tail) != cudaSuccess) return kErrCuda;
-    return kOk;
-  }
-  score_tail_kernel<FMT><<<tgrid, 256, 0, s_tail>>>(z_f, z_b, st_f, st_b, n_blocks, E, tp, do_f ? g_f : nullptr,
-                                                    do_b ? g_b : nullptr, nullptr, nullptr, nullptr);
+  const bool feats = a.want_features != 0;
+  score_tail_kernel<FMT><<<tgrid, 256, 0, stream>>>(
+      MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+      a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
+      feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
   if (check_launch() != kOk) return kErrCuda;
+  if (!feats) return kOk;
+  // feature path: state_net.4 as a second GEMM, logits from the fp32 features, softmax-weighted blend
   gemm::EpiBiasF32::Params fp;
   fp.bias = a.w2_bias, fp.out32 = FEAT, fp.ld32 = D;
-  rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(rows), D, D, fp, a.num_sms, s_tail);
+  rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(nd * n), D, D, fp, a.num_sms, stream);
   if (rc != kOk) return rc;
   const float* f_f = do_f ? FEAT : nullptr;
-  const float* f_b = do_b ? FEAT + (do_f ? static_cast<size_t>(E) * D : 0) : nullptr;
-  feature_blend_kernel<<<tgrid, 256, 0, s_tail>>>(f_f, f_b, a.head_w, a.head_b, E, edge_emb, logits, logits_fwd,
+  const float* f_b = do_b ? FEAT + (do_f ? n * D : 0) : nullptr;
+  feature_blend_kernel<<<tgrid, 256, 0, stream>>>(f_f, f_b, a.head_w, a.head_b, E, edge_emb, logits, logits_fwd,
                                                   logits_bwd);
-  if (check_launch() != kOk) return kErrCuda;
-  if (ev.tail_done && cudaEventRecord(ev.tail_done, s_tail) != cudaSuccess) return kErrCuda;
-  return kOk;
+  return check_launch();
 }
 
-static size_t chunk_workspace_bytes(long long num_edges, int direction, int want_features) {
-  const size_t ndir = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
-  const size_t rows = ndir * static_cast<size_t>(num_edges);
-  auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
-  size_t total = al(rows * 3 * D * 2) + al(rows * D * sizeof(float)) + al(rows * (D / gemm::BN) * sizeof(float2)) +
-                 al(rows * sizeof(float));
-  if (want_features) total += al(rows * D * 2) + al(rows * D * sizeof(float));
-  return total + 256;
-}
-
-// All edges, chunk by chunk. With two auxiliary streams the three stages of consecutive chunks overlap:
-// the operand kernel of chunk c+1 (ALU/L1-bound) and the tail of chunk c-1 (HBM-bound) run beside the
-// tensor-bound GEMM of chunk c; two workspace buffers alternate. Only events order the stages — no kernel
-// ever waits on another kernel's flag.
 template <int FMT>
 static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   const long long E = a.num_edges;
   if (E <= 0) return kOk;
-  if (a.flags == nullptr || a.node_uv32 == nullptr || a.num_nodes <= 0 || a.num_rel_rows <= 0 ||
-      a.num_questions <= 0)
+  if (a.flags == nullptr || a.node_uv32 == nullptr || a.node_p32 == nullptr || a.pair_rq32 == nullptr ||
+      a.pair_slot32 == nullptr || a.num_nodes <= 0 || a.num_rel_rows <= 0 || a.num_questions <= 0 ||
+      a.num_pair_rows <= 0)
     return kErrInvalidArg;
   const long long chunk = a.chunk_edges > 0 && a.chunk_edges < E ? a.chunk_edges : E;
   const long long nchunks = (E + chunk - 1) / chunk;
   const size_t per = chunk_workspace_bytes(chunk, a.direction, a.want_features);
+  if (a.workspace_bytes < per) return kErrWorkspace;
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
-  cudaStream_t s_gemm = static_cast<cudaStream_t>(a.stream_gemm), s_tail = static_cast<cudaStream_t>(a.stream_tail);
-  // the operand kernels get their own stream too when the caller gives one: the caller's stream is often
-  // the legacy default stream, and work there does not run beside work of other streams
-  cudaStream_t s_op = a.stream_op ? static_cast<cudaStream_t>(a.stream_op) : stream;
-  const bool pipelined = s_gemm != nullptr && s_tail != nullptr && nchunks > 1 && a.workspace_bytes >= 2 * per;
-  if (!pipelined) {
-    if (a.workspace_bytes < per) return kErrWorkspace;
-    for (long long c = 0; c < nchunks; ++c) {
-      ChunkEvents ev;
-      if (c == (nchunks > 1 ? 1 : 0)) {
-        ev.time_begin = static_cast<cudaEvent_t>(a.ev_gemm_begin), ev.time_end = static_cast<cudaEvent_t>(a.ev_gemm_end);
-      }
-      const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-      const int rc = score_chunk<FMT>(a, e0, n, ws, per, stream, stream, stream, ev);
-      if (rc != kOk) return rc;
-    }
-    return kOk;
-  }
-  // events: [0, n) op_done, [n, 2n) gemm_done, [2n, 3n) tail_done, [3n] begin, (3n, 4n] gemm_ready
-  const size_t nev = static_cast<size_t>(5 * nchunks + 1);
-  cudaEvent_t* evs = new cudaEvent_t[nev];
-  size_t made = 0;
-  int rc = kOk;
-  const bool trace = getenv("EVI_TRACE") != nullptr;  // debug: print the stage timeline of this call
-  for (; made < nev; ++made)
-    if (cudaEventCreateWithFlags(&evs[made], trace ? cudaEventDefault : cudaEventDisableTiming) != cudaSuccess) {
-      rc = kErrCuda;
-      break;
-    }
-  if (rc == kOk) {
-    cudaEvent_t begin = evs[3 * nchunks];
-    if (cudaEventRecord(begin, stream) != cudaSuccess || cudaStreamWaitEvent(s_gemm, begin, 0) != cudaSuccess ||
-        cudaStreamWaitEvent(s_tail, begin, 0) != cudaSuccess ||
-        (s_op != stream && cudaStreamWaitEvent(s_op, begin, 0) != cudaSuccess))
-      rc = kErrCuda;
-  }
-  for (long long c = 0; rc == kOk && c < nchunks; ++c) {
-    ChunkEvents ev;
-    ev.op_done = evs[c], ev.gemm_done = evs[nchunks + c], ev.tail_done = evs[2 * nchunks + c];
-    if (c >= 2) ev.wait_op = evs[nchunks + c - 2], ev.wait_gemm = evs[2 * nchunks + c - 2];
-    // the operand kernel of chunk c starts only once the GEMM of chunk c-1 is being launched: the GEMM's
-    // one-CTA-per-SM grid is placed first (it needs a whole SM's shared memory) and the elementwise CTAs
-    // fill the register space left beside it, instead of occupying the SMs ahead of it
-    ev.gemm_ready = evs[3 * nchunks + 1 + c];
-    if (c >= 1) ev.wait_op2 = evs[3 * nchunks + c];
-    if (trace) ev.op_start = evs[4 * nchunks + 1 + c];
-    if (c == 1) ev.time_begin = static_cast<cudaEvent_t>(a.ev_gemm_begin), ev.time_end = static_cast<cudaEvent_t>(a.ev_gemm_end);
+  for (long long c = 0; c < nchunks; ++c) {
+    const bool timed = c == (nchunks > 1 ? 1 : 0);
     const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-    rc = score_chunk<FMT>(a, e0, n, ws + (c & 1) * per, per, s_op, s_gemm, s_tail, ev);
+    const int rc = score_chunk<FMT>(a, e0, n, ws, per, stream, timed ? static_cast<cudaEvent_t>(a.ev_gemm_begin) : nullptr,
+                                    timed ? static_cast<cudaEvent_t>(a.ev_gemm_end) : nullptr);
+    if (rc != kOk) return rc;
   }
-  if (rc == kOk) {
-    // the caller's stream continues only after the last tail (tails are ordered on s_tail), GEMM and operand kernel
-    if (cudaStreamWaitEvent(stream, evs[3 * nchunks - 1], 0) != cudaSuccess ||
-        cudaStreamWaitEvent(stream, evs[2 * nchunks - 1], 0) != cudaSuccess ||
-        cudaStreamWaitEvent(stream, evs[nchunks - 1], 0) != cudaSuccess)
-      rc = kErrCuda;
-  }
-  if (trace && rc == kOk) {
-    cudaStreamSynchronize(stream);
-    for (long long c = 0; c < nchunks; ++c) {
-      float t_op = 0, t_gr = 0, t_gd = 0, t_td = 0, t_os = 0;
-      cudaEventElapsedTime(&t_os, evs[3 * nchunks], evs[4 * nchunks + 1 + c]);
-      cudaEventElapsedTime(&t_op, evs[3 * nchunks], evs[c]);
-      cudaEventElapsedTime(&t_gr, evs[3 * nchunks], evs[3 * nchunks + 1 + c]);
-      cudaEventElapsedTime(&t_gd, evs[3 * nchunks], evs[nchunks + c]);
-      cudaEventElapsedTime(&t_td, evs[3 * nchunks], evs[2 * nchunks + c]);
-      fprintf(stderr, "[evi trace] chunk %lld: op_start %.3f op_done %.3f  gemm_start %.3f  gemm_done %.3f  tail_done %.3f ms\n",
-              c, t_os, t_op, t_gr, t_gd, t_td);
-    }
-  }
-  for (size_t i = 0; i < made; ++i) cudaEventDestroy(evs[i]);  // deferred until the events complete
-  delete[] evs;
-  return rc;
+  return kOk;
 }
 
 }  // namespace evi
@@ -727,8 +752,8 @@ using namespace evi;
 
 extern "C" {
 
-size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features, int num_buffers) {
-  return chunk_workspace_bytes(chunk_edges, direction, want_features) * static_cast<size_t>(num_buffers < 1 ? 1 : num_buffers);
+size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features) {
+  return chunk_workspace_bytes(chunk_edges, direction, want_features);
 }
 
 int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const long long* ids,
@@ -769,17 +794,58 @@ int evi_convert_f32(const float* src, void* dst16, long long count, int operand_
   return check_launch();
 }
 
-int evi_project(const void* x16, int num_rows, const void* w16, int out_dim, int in_dim, const float* bias,
-                const int* act_per_block, void* out16, float* out32, int operand_format, int num_sms,
-                cudaStream_t stream) {
-  if (out_dim % gemm::BN != 0 || out_dim / gemm::BN > 8 || in_dim % gemm::BK != 0) return kErrUnsupported;
+int evi_project(const void* x16, int num_rows, const int* num_rows_dev, const void* w16, int ld_w, int out_dim,
+                int in_dim, const float* bias, const int* act_per_block, void* out16, float* out32,
+                int operand_format, int num_sms, cudaStream_t stream) {
+  if (out_dim % gemm::BN != 0 || out_dim / gemm::BN > 8 || in_dim % gemm::BK != 0 || ld_w < in_dim) return kErrUnsupported;
   if (operand_format == kFmtF16)
-    return linear_act_impl<kFmtF16>(x16, num_rows, w16, out_dim, in_dim, bias, act_per_block, out16, out32, num_sms,
-                                    stream);
+    return linear_act_impl<kFmtF16>(x16, num_rows, num_rows_dev, w16, ld_w, out_dim, in_dim, bias, act_per_block, out16,
+                                    out32, num_sms, stream);
   if (operand_format == kFmtBF16)
-    return linear_act_impl<kFmtBF16>(x16, num_rows, w16, out_dim, in_dim, bias, act_per_block, out16, out32,
-                                     num_sms, stream);
+    return linear_act_impl<kFmtBF16>(x16, num_rows, num_rows_dev, w16, ld_w, out_dim, in_dim, bias, act_per_block,
+                                     out16, out32, num_sms, stream);
   return kErrInvalidArg;
+}
+
+int evi_relation_pairs(const int* rel32, const long long* edge_ptr, int num_questions, int num_relations,
+                       int capacity, int* pair_slot32, int* pair_q32, int* pair_rel32, int* num_pairs,
+                       unsigned* flags, cudaStream_t stream) {
+  if (num_questions <= 0) return kOk;
+  if (num_relations <= 0 || capacity <= 0 || rel32 == nullptr || edge_ptr == nullptr || pair_slot32 == nullptr ||
+      pair_q32 == nullptr || pair_rel32 == nullptr || num_pairs == nullptr || flags == nullptr)
+    return kErrInvalidArg;
+  const int words = (num_relations + 31) / 32;
+  const size_t smem = static_cast<size_t>(words) * 8;
+  if (smem > 200 * 1024) return kErrUnsupported;  // > 819k relation ids
+  static bool attr_set = false;
+  if (smem > 48 * 1024 && !attr_set) {
+    if (cudaFuncSetAttribute(relation_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) !=
+        cudaSuccess)
+      return kErrCuda;
+    attr_set = true;
+  }
+  if (cudaMemsetAsync(num_pairs, 0, sizeof(int), stream) != cudaSuccess) return kErrCuda;
+  relation_pairs_kernel<<<num_questions, 256, smem, stream>>>(rel32, edge_ptr, num_relations, words, capacity,
+                                                              pair_slot32, pair_q32, pair_rel32, num_pairs, flags);
+  return check_launch();
+}
+
+int evi_pair_context(const int* pair_q32, const int* pair_rel32, const int* num_pairs, int capacity,
+                     const void* rel_repr16, int num_rel_rows, const float* gate_bias32, int num_questions,
+                     void* rc16, int operand_format, unsigned* flags, cudaStream_t stream) {
+  if (capacity <= 0) return kOk;
+  const int grid = (capacity + 7) / 8;
+  if (operand_format == kFmtF16)
+    pair_context_kernel<kFmtF16><<<grid, 256, 0, stream>>>(pair_q32, pair_rel32, num_pairs, capacity,
+                                                           static_cast<const uint16_t*>(rel_repr16), num_rel_rows,
+                                                           gate_bias32, num_questions, static_cast<uint16_t*>(rc16), flags);
+  else if (operand_format == kFmtBF16)
+    pair_context_kernel<kFmtBF16><<<grid, 256, 0, stream>>>(pair_q32, pair_rel32, num_pairs, capacity,
+                                                            static_cast<const uint16_t*>(rel_repr16), num_rel_rows,
+                                                            gate_bias32, num_questions, static_cast<uint16_t*>(rc16), flags);
+  else
+    return kErrInvalidArg;
+  return check_launch();
 }
 
 int evi_score_edges(const evi_score_args* args, cudaStream_t stream) {

@@ -22,6 +22,7 @@ from . import lib as _lib
 
 _PATH_MODES = ("undirected", "qa_directed")
 CSR_UNDIRECTED, CSR_FORWARD, CSR_REVERSE = 0, 1, 2
+SWEEP_MAX_DEPTH = 8  # hop caps up to this use the edge-list sweep kernel (O(depth * E)); beyond it, CSR frontiers
 
 
 def _dev(device=None) -> torch.device:
@@ -199,13 +200,35 @@ def batched_bfs(gb: GraphBatch, sources: np.ndarray, src_ptr: np.ndarray, *, dir
                 max_depth: int = -1) -> torch.Tensor:
     """Multi-source hop distance for every question of the batch: ``sources`` are batch-global
     node ids grouped by ``src_ptr [B+1]``. Returns ``dist [N] int32`` (-1 unreachable)."""
-    row_ptr, adj = build_csr(gb.head32, gb.tail32, gb.num_nodes, CSR_FORWARD if directed else CSR_UNDIRECTED)
     ptr = gb.ptr_host
     B = gb.num_graphs
+    if 0 <= max_depth <= SWEEP_MAX_DEPTH:
+        return _sweep_bfs(gb, sources, src_ptr, directed=directed, max_depth=max_depth)
+    row_ptr, adj = build_csr(gb.head32, gb.tail32, gb.num_nodes, CSR_FORWARD if directed else CSR_UNDIRECTED)
     q_of_src = np.repeat(np.arange(B), np.diff(src_ptr))
     local = np.asarray(sources, dtype=np.int64) - ptr[:-1][q_of_src]
     dist, _ = bfs_jobs(row_ptr, adj, ptr[:-1], ptr[1:], src_ptr, local, max_depth)
     return dist
+
+
+def _sweep_bfs(gb: GraphBatch, sources: np.ndarray, src_ptr: np.ndarray, *, directed: bool, max_depth: int) -> torch.Tensor:
+    """Depth-capped multi-source BFS straight from the edge list (``evi_bfs_edge_sweep``)."""
+    L = _lib.load()
+    dev = gb.head32.device
+    up = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).to(dev)
+    ptr = gb.ptr_host
+    n_total = int(ptr[-1])
+    d_nb, d_ne, d_off = up(ptr[:-1], np.int32), up(ptr[1:], np.int32), up(ptr[:-1], np.int64)
+    d_sp = up(src_ptr, np.int32)
+    d_src = up(sources if len(sources) else np.zeros(1), np.int32)
+    e_begin = gb.edge_ptr[:-1].contiguous()
+    e_end = gb.edge_ptr[1:].contiguous()
+    dist = torch.empty(max(1, n_total), dtype=torch.int32, device=dev)
+    st = L.evi_bfs_edge_sweep(gb.head32.data_ptr(), gb.tail32.data_ptr(), gb.num_graphs, e_begin.data_ptr(),
+                              e_end.data_ptr(), d_nb.data_ptr(), d_ne.data_ptr(), d_off.data_ptr(), d_sp.data_ptr(),
+                              d_src.data_ptr(), 1, int(directed), int(max_depth), dist.data_ptr(), _lib.stream_handle())
+    _lib.check(st, "evi_bfs_edge_sweep")
+    return dist[:n_total]
 
 
 def batched_shortest_path_labels(gb: GraphBatch, seeds: np.ndarray, seed_ptr: np.ndarray, answers: np.ndarray,

@@ -30,18 +30,19 @@ class ScoreArgs(C.Structure):
     _fields_ = [
         ("num_edges", _ll), ("emb_dim", _i), ("hidden_dim", _i), ("direction", _i),
         ("operand_format", _i), ("want_features", _i), ("num_sms", _i),
-        ("num_nodes", _i), ("num_rel_rows", _i), ("num_questions", _i), ("flags", _vp),
-        ("head32", _vp), ("tail32", _vp), ("qid32", _vp), ("rel_slot32", _vp),
+        ("num_nodes", _i), ("num_rel_rows", _i), ("num_questions", _i), ("num_pair_rows", _i), ("flags", _vp),
+        ("head32", _vp), ("tail32", _vp), ("qid32", _vp), ("rel_slot32", _vp), ("pair_slot32", _vp),
         ("node_repr16", _vp), ("rel_repr16", _vp), ("gate_bias32", _vp), ("node_uv32", _vp),
+        ("node_p32", _vp), ("pair_rq32", _vp),
         ("struct_ln_g", _vp), ("struct_ln_b", _vp),
         ("nav_w", _vp), ("nav_b", _f),
-        ("w1_main16", _vp), ("w1_dist_col", _vp), ("w1_bias", _vp), ("ln1_g", _vp), ("ln1_b", _vp),
+        ("w1_main16", _vp), ("w1_dist_col", _vp), ("ln1_g", _vp), ("ln1_b", _vp),
         ("head_v", _vp), ("head_c0", _f), ("w2_16", _vp), ("w2_bias", _vp), ("head_w", _vp),
         ("head_b", _f),
         ("logits", _vp), ("logits_fwd", _vp), ("logits_bwd", _vp), ("edge_embeddings", _vp),
         ("workspace", _vp), ("workspace_bytes", _sz),
         ("ev_gemm_begin", _vp), ("ev_gemm_end", _vp),
-        ("chunk_edges", _ll), ("stream_gemm", _vp), ("stream_tail", _vp), ("stream_op", _vp),
+        ("chunk_edges", _ll),
     ]
 
 
@@ -53,12 +54,15 @@ PROTOTYPES = {
     "evi_dde_forward": (_i, [_vp, _vp, _ll, _i, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
     "evi_build_csr": (_i, [_vp, _vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "evi_bfs_edge_sweep": (_i, [_vp, _vp, _i] + [_vp] * 7 + [_i, _i, _i, _vp, _vp]),
     "evi_shortest_path_pairs": (_i, [_vp, _vp, _i] + [_vp] * 9 + [_i] + [_vp] * 4 + [_vp]),
     "evi_gather_rows": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp]),
     "evi_struct_project": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_convert_f32": (_i, [_vp, _vp, _ll, _i, _vp]),
-    "evi_project": (_i, [_vp, _i, _vp, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
-    "evi_score_workspace_bytes": (_sz, [_ll, _i, _i, _i]),
+    "evi_project": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
+    "evi_relation_pairs": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "evi_pair_context": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _i, _vp, _i, _vp, _vp]),
+    "evi_score_workspace_bytes": (_sz, [_ll, _i, _i]),
     "evi_score_edges": (_i, [C.POINTER(ScoreArgs), _vp]),
     "evi_segmented_topk": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_topk_gather_payload": (_i, [_vp, _vp, _vp, _i, _i, _vp, _ll] + [_vp] * 11 + [_vp]),
@@ -72,12 +76,15 @@ _KERNELS_PER_CALL = {
     "evi_dde_forward": lambda a: 1 + (2 if a[2] > 0 else 1) * max(a[6], a[7]),
     "evi_build_csr": lambda a: 3 if a[2] > 0 else 1,
     "evi_bfs_multi_source": lambda a: 1,
+    "evi_bfs_edge_sweep": lambda a: 1,
     "evi_shortest_path_pairs": lambda a: 1,
     "evi_gather_rows": lambda a: 1,
     "evi_struct_project": lambda a: 1,
     "evi_convert_f32": lambda a: 1,
     "evi_project": lambda a: 1,
-    "evi_score_edges": lambda a: (5 if a[0]._obj.want_features else 3) * _num_chunks(a[0]._obj),
+    "evi_relation_pairs": lambda a: 1,
+    "evi_pair_context": lambda a: 1,
+    "evi_score_edges": lambda a: (6 if a[0]._obj.want_features else 4) * _num_chunks(a[0]._obj),
     "evi_segmented_topk": lambda a: 1,
     "evi_topk_gather_payload": lambda a: 1,
 }

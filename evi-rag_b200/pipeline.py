@@ -70,8 +70,7 @@ class RetrievalPipeline:
         dev = b.edge_index.device
         gb = G.GraphBatch.from_edge_index(b.edge_index, b.ptr_host, device=dev, validate=False, ptr_dev=b.ptr)
         # jobs = one per question; seeds stay batch-global, the kernel subtracts the question's node offset
-        row_ptr, adj = G.build_csr(gb.head32, gb.tail32, gb.num_nodes, G.CSR_UNDIRECTED)
-        dist = self._bfs(row_ptr, adj, b, b.q_local_indices)
+        dist = self._bfs(gb, b, b.q_local_indices)
         b._evi_graph = gb
         was = self.model.validate
         self.model.validate = False
@@ -87,11 +86,13 @@ class RetrievalPipeline:
         res["flags"] = self.model._flags
         return res
 
-    def _bfs(self, row_ptr, adj, b, seeds_global):
+    def _bfs(self, gb, b, seeds_global):
+        """Multi-source hop distance from each question's seeds, undirected, capped at ``bfs_max_depth``:
+        edge-list sweeps for small caps (no CSR), the CSR frontier kernel when uncapped."""
         from . import lib as _lib
 
         L = _lib.load()
-        dev = row_ptr.device
+        dev = gb.head32.device
         B = b.num_graphs
         # every temporary passed by address stays referenced until the call returns: a tensor freed
         # between two argument evaluations can be handed back by the caching allocator for the next one
@@ -104,6 +105,15 @@ class RetrievalPipeline:
         dist_off = b.ptr.to(torch.long).contiguous()
         n_total = int(b.ptr_host[-1])
         dist = torch.empty(max(1, n_total), dtype=torch.int32, device=dev)
+        if 0 <= self.bfs_max_depth <= G.SWEEP_MAX_DEPTH:
+            edge_end = gb.edge_ptr[1:].contiguous()
+            st = L.evi_bfs_edge_sweep(gb.head32.data_ptr(), gb.tail32.data_ptr(), B, gb.edge_ptr.data_ptr(),
+                                      edge_end.data_ptr(), ptr32.data_ptr(), node_end32.data_ptr(), dist_off.data_ptr(),
+                                      src_ptr32.data_ptr(), seeds32.data_ptr(), 1, 0, self.bfs_max_depth,
+                                      dist.data_ptr(), _lib.stream_handle())
+            _lib.check(st, "evi_bfs_edge_sweep")
+            return dist[:n_total]
+        row_ptr, adj = G.build_csr(gb.head32, gb.tail32, gb.num_nodes, G.CSR_UNDIRECTED)
         queue = torch.empty(max(1, 2 * n_total), dtype=torch.int32, device=dev)
         st = L.evi_bfs_multi_source(row_ptr.data_ptr(), adj.data_ptr(), B, ptr32.data_ptr(), node_end32.data_ptr(),
                                     dist_off.data_ptr(), src_ptr32.data_ptr(), seeds32.data_ptr(), 1,

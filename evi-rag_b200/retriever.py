@@ -119,7 +119,6 @@ class Retriever(nn.Module):
         self.return_edge_embeddings = bool(return_edge_embeddings)
         self.max_workspace_bytes = int(max_workspace_bytes)
         self.pipeline_chunks = max(1, int(pipeline_chunks))
-        self._streams = None
         self.validate = bool(validate)
 
         d, h = self.emb_dim, self.hidden_dim
@@ -149,6 +148,7 @@ class Retriever(nn.Module):
         self._prepared_key = None
         self._tables: Optional[Dict[str, torch.Tensor]] = None
         self._ws: Optional[torch.Tensor] = None
+        self._ws_score: Optional[torch.Tensor] = None
         self.gemm_events = None
         self.last_chunk_edges = 0
         self._flags: Optional[torch.Tensor] = None
@@ -265,20 +265,21 @@ class Retriever(nn.Module):
             self._ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
         return self._ws
 
-    def _aux_streams(self, dev: torch.device):
-        """(GEMM stream, tail stream, operand stream) for the chunk pipeline; the GEMM one has the higher priority so
-        its CTAs are placed first whenever an SM frees up."""
-        if self._streams is None or self._streams[0].device != dev:
-            self._streams = (torch.cuda.Stream(device=dev, priority=-1), torch.cuda.Stream(device=dev, priority=0),
-                             torch.cuda.Stream(device=dev, priority=0))
-        return self._streams
+    def _score_workspace(self, nbytes: int, dev: torch.device) -> torch.Tensor:
+        if self._ws_score is None or self._ws_score.numel() < nbytes or self._ws_score.device != dev:
+            self._ws_score = None
+            self._ws_score = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+        return self._ws_score
 
-    def _project(self, x16, w16, bias, acts, *, out16=None, out32=None, p=None):
+    def _project(self, x16, w16, bias, acts, *, out16=None, out32=None, p=None, rows_dev=None, col0=0, in_dim=None):
+        """out = act(x16 @ w16[:, col0:col0+in_dim]^T + bias); ``rows_dev``: device int bounding the rows."""
         L = _lib.load()
         act_arr = (C.c_int * 8)(*(list(acts) + [0] * (8 - len(acts))))
+        in_dim = int(w16.size(1)) if in_dim is None else int(in_dim)
         st = L.evi_project(
-            x16.data_ptr(), x16.size(0), w16.data_ptr(), w16.size(0), w16.size(1), bias.data_ptr(), act_arr,
-            _lib.ptr(out16), _lib.ptr(out32), self._fmt(), p["num_sms"], _lib.stream_handle(),
+            x16.data_ptr(), x16.size(0), _lib.ptr(rows_dev), w16.data_ptr() + 2 * int(col0), w16.size(1), w16.size(0),
+            in_dim, _lib.ptr(bias), act_arr, _lib.ptr(out16), _lib.ptr(out32), self._fmt(), p["num_sms"],
+            _lib.stream_handle(),
         )
         _lib.check(st, "evi_project")
 
@@ -410,6 +411,40 @@ class Retriever(nn.Module):
         gate_bias = torch.empty((B, 2 * d), dtype=torch.float32, device=dev)
         self._project(qp16, p["wgb"], p["bgb"], [_lib.ACT_SIGMOID] * 4 + [_lib.ACT_TANH] * 4, out32=gate_bias, p=p)
 
+        # ---- err block of state_net.0, linear in err = h + r_ctx - t (retriever.py:477-481): once per node and
+        # once per distinct (question, relation) pair instead of once per edge and direction
+        node_p = torch.empty((N, self.hidden_dim), dtype=torch.float32, device=dev)
+        self._project(node_repr, p["w1"], None, [_lib.ACT_NONE] * 4, out32=node_p, p=p, col0=2 * d, in_dim=d)
+        pair_slot32 = torch.empty(E, dtype=torch.int32, device=dev)
+        if use_tables and graph is not None and graph.num_edges == E:
+            edge_ptr_dev = graph.edge_ptr
+        elif use_tables:
+            # edges are grouped by question (validated by evi_edge_batch): edge_ptr from the question ids
+            edge_ptr_dev = torch.searchsorted(query_ids, torch.arange(B + 1, device=dev, dtype=torch.long))
+        if use_tables:
+            cap = E
+            pair_q32 = torch.empty(cap, dtype=torch.int32, device=dev)
+            pair_rel32 = torch.empty(cap, dtype=torch.int32, device=dev)
+            num_pairs = torch.empty(1, dtype=torch.int32, device=dev)
+            st = L.evi_relation_pairs(rel_slot32.data_ptr(), edge_ptr_dev.data_ptr(), B, int(rel_repr.size(0)), cap,
+                                      pair_slot32.data_ptr(), pair_q32.data_ptr(), pair_rel32.data_ptr(),
+                                      num_pairs.data_ptr(), flags.data_ptr(), stream)
+            _lib.check(st, "evi_relation_pairs")
+        else:
+            cap = E  # per-edge relation rows: every edge is its own pair
+            pair_slot32.copy_(rel_slot32)
+            pair_q32, pair_rel32 = qid32, rel_slot32
+            num_pairs = torch.full((1,), E, dtype=torch.int32, device=dev)
+        rc16 = torch.empty((cap, d), dtype=dt, device=dev)
+        st = L.evi_pair_context(pair_q32.data_ptr(), pair_rel32.data_ptr(), num_pairs.data_ptr(), cap,
+                                rel_repr.data_ptr(), int(rel_repr.size(0)), gate_bias.data_ptr(), B, rc16.data_ptr(), fmt,
+                                flags.data_ptr(), stream)
+        _lib.check(st, "evi_pair_context")
+        pair_rq = torch.empty((cap, self.hidden_dim), dtype=torch.float32, device=dev)
+        self._project(rc16, p["w1"], p["b1"], [_lib.ACT_NONE] * 4, out32=pair_rq, p=p, rows_dev=num_pairs, col0=2 * d,
+                      in_dim=d)
+        del rc16
+
         # ---- a3: DDE structure features ------------------------------------------------------
         topic = getattr(batch, "topic_one_hot", None)
         if topic is None:
@@ -450,40 +485,38 @@ class Retriever(nn.Module):
         logits_fwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_BACKWARD else None
         logits_bwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_FORWARD else None
         feats = torch.empty((E, self.hidden_dim), dtype=torch.float32, device=dev) if return_features else None
-        # chunking: `pipeline_chunks` chunks per batch (never below 16k edges per chunk), two workspace
-        # buffers when the aux streams are in use, bounded by max_workspace_bytes
-        pipelined = self.pipeline_chunks > 1 and not return_features
-        nbuf = 2 if pipelined else 1
-        per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features), 1)) / float(1 << 20)
-        chunk_cap = max(1024, int(self.max_workspace_bytes / (per_edge * nbuf)) // 1024 * 1024)
-        chunk = -(-E // self.pipeline_chunks) if pipelined else E
+        # chunking bounds the workspace: `pipeline_chunks` chunks per batch (never below 16k edges per chunk),
+        # capped by max_workspace_bytes
+        per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features))) / float(1 << 20)
+        chunk_cap = max(1024, int(self.max_workspace_bytes / per_edge) // 1024 * 1024)
+        chunk = -(-E // self.pipeline_chunks)
         chunk = min(chunk_cap, max(16384, (chunk + 1023) // 1024 * 1024))
         if chunk >= E:
-            chunk, nbuf, pipelined = E, 1, False
-        ws = self._workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features), nbuf)), dev)
+            chunk = E
+        ws = self._score_workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features))), dev)
         a = _lib.ScoreArgs()
         a.emb_dim, a.hidden_dim, a.direction, a.operand_format = d, self.hidden_dim, direction, fmt
         a.want_features, a.num_sms = int(return_features), p["num_sms"]
         a.num_nodes, a.num_rel_rows, a.num_questions, a.flags = N, int(rel_repr.size(0)), B, flags.data_ptr()
+        a.num_pair_rows = cap
         a.node_repr16, a.rel_repr16 = node_repr.data_ptr(), rel_repr.data_ptr()
         a.gate_bias32, a.node_uv32 = gate_bias.data_ptr(), node_uv.data_ptr()
+        a.node_p32, a.pair_rq32 = node_p.data_ptr(), pair_rq.data_ptr()
         a.struct_ln_g, a.struct_ln_b = p["ls_g"].data_ptr(), p["ls_b"].data_ptr()
         a.nav_w, a.nav_b = p["wn"].data_ptr(), p["bn"]
-        a.w1_main16, a.w1_dist_col, a.w1_bias = p["w1"].data_ptr(), p["w1d"].data_ptr(), p["b1"].data_ptr()
+        a.w1_main16, a.w1_dist_col = p["w1"].data_ptr(), p["w1d"].data_ptr()
         a.ln1_g, a.ln1_b, a.head_v, a.head_c0 = p["l1_g"].data_ptr(), p["l1_b"].data_ptr(), p["v"].data_ptr(), p["c0"]
         a.w2_16, a.w2_bias, a.head_w, a.head_b = p["w2"].data_ptr(), p["b2"].data_ptr(), p["wo"].data_ptr(), p["bo"]
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         a.num_edges, a.chunk_edges = E, chunk
         a.head32, a.tail32, a.qid32, a.rel_slot32 = head32.data_ptr(), tail32.data_ptr(), qid32.data_ptr(), rel_slot32.data_ptr()
+        a.pair_slot32 = pair_slot32.data_ptr()
         a.logits = logits.data_ptr()
         a.logits_fwd = logits_fwd.data_ptr() if logits_fwd is not None else None
         a.logits_bwd = logits_bwd.data_ptr() if logits_bwd is not None else None
         a.edge_embeddings = feats.data_ptr() if feats is not None else None
-        if pipelined:
-            s_gemm, s_tail, s_op = self._aux_streams(dev)
-            a.stream_gemm, a.stream_tail, a.stream_op = s_gemm.cuda_stream, s_tail.cuda_stream, s_op.cuda_stream
         self.last_chunk_edges = min(chunk, E)
-        events = self.gemm_events  # (torch.cuda.Event begin, end) around one state_net.0 GEMM launch, or None
+        events = self.gemm_events  # (torch.cuda.Event begin, end) around one W_sc GEMM launch, or None
         a.ev_gemm_begin = events[0].cuda_event if events is not None else None
         a.ev_gemm_end = events[1].cuda_event if events is not None else None
         _lib.check(L.evi_score_edges(C.byref(a), stream), "evi_score_edges")

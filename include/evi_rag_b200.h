@@ -82,6 +82,14 @@ int evi_bfs_multi_source(const int* row_ptr, const int* adj, int num_jobs, const
                          const int* sources, int sources_are_global, int max_depth, int* dist_out,
                          int* queue_workspace, cudaStream_t stream);
 
+/* _bfs_dist for small hop caps, straight from the edge list (no CSR): level-synchronous sweeps over
+ * each job's edges [job_edge_begin, job_edge_end) with dist in shared memory; O(levels * E_job) reads.
+ * Same outputs as evi_bfs_multi_source over the undirected (directed = 0) or head->tail (1) adjacency. */
+int evi_bfs_edge_sweep(const int* head32, const int* tail32, int num_jobs, const long long* job_edge_begin,
+                       const long long* job_edge_end, const int* job_node_begin, const int* job_node_end,
+                       const long long* job_dist_off, const int* job_src_ptr, const int* sources,
+                       int sources_are_global, int directed, int max_depth, int* dist_out, cudaStream_t stream);
+
 /* _select_shortest_edges_undirected / _directed + the mask OR of
  * _shortest_path_union_mask_by_pair — scripts/build_retrieval_pipeline.py:650-752, 755-815.
  * One CTA per (start, answer) pair; pair_count/pair_len = -1 for unreachable pairs. */
@@ -103,11 +111,15 @@ int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const l
 int evi_convert_f32(const float* src, void* dst16, long long count, int operand_format, cudaStream_t stream);
 
 /* EmbeddingProjector / q_gate / q_bias — src/models/components/projections.py:9-40,
- * retriever.py:157-158,436-441: out = act(x W^T + b) on tcgen05. w16 is [out_dim, in_dim]
- * (nn.Linear layout). act_per_block[8]: activation per 256 output columns. */
-int evi_project(const void* x16, int num_rows, const void* w16, int out_dim, int in_dim, const float* bias,
-                const int* act_per_block, void* out16, float* out32, int operand_format, int num_sms,
-                cudaStream_t stream);
+ * retriever.py:157-158,436-441: out = act(x W^T + b) on tcgen05. w16 is [out_dim, in_dim] with row
+ * pitch ld_w elements (nn.Linear layout; ld_w > in_dim selects a column block of a wider matrix,
+ * e.g. the err block of state_net.0.weight). bias may be NULL. act_per_block[8]: activation per 256
+ * output columns. num_rows_dev (optional, device int): rows beyond *num_rows_dev (rounded up to a multiple
+ * of 32) are skipped — for row counts only the device knows (the number of distinct (question, relation)
+ * pairs). out32 alone selects the staged TMA-store epilogue and must be 16-byte aligned. */
+int evi_project(const void* x16, int num_rows, const int* num_rows_dev, const void* w16, int ld_w, int out_dim,
+                int in_dim, const float* bias, const int* act_per_block, void* out16, float* out32,
+                int operand_format, int num_sms, cudaStream_t stream);
 
 /* struct_proj.0 of _encode_structure (retriever.py:486-495) on the edge structure vector
  * [ns[a], ns[b]] of _edge_structure_from_nodes (retriever.py:509-517), split by node:
@@ -117,8 +129,27 @@ int evi_project(const void* x16, int num_rows, const void* w16, int out_dim, int
 int evi_struct_project(const float* node_struct, int num_nodes, int ns_dim, const float* struct_w_t,
                        const float* struct_b, float* node_uv32, cudaStream_t stream);
 
+/* Distinct (question, relation) pairs of a batch. The gated relation r_ctx = rel * sigmoid(W_g q) +
+ * tanh(W_b q) of retriever.py:464 depends only on the pair, so its contraction with the err block of
+ * state_net.0 is done once per pair (evi_pair_context + evi_project) instead of per edge and direction.
+ * rel32 [E] relation id per edge in [0, num_relations), edge_ptr [B+1] -> pair_slot32 [E],
+ * pair_q32 / pair_rel32 [capacity], *num_pairs (device). Slot numbering across questions is
+ * unspecified. capacity >= E never overflows; an overflow sets EVI_FLAG_OUT_OF_RANGE. */
+int evi_relation_pairs(const int* rel32, const long long* edge_ptr, int num_questions, int num_relations,
+                       int capacity, int* pair_slot32, int* pair_q32, int* pair_rel32, int* num_pairs,
+                       unsigned* flags, cudaStream_t stream);
+/* rc16[slot] = rel_repr16[pair_rel[slot]] * gate[pair_q[slot]] + bias[pair_q[slot]] in the operand
+ * format, for slot < min(*num_pairs, capacity). gate_bias32 [B, 2D] = sigmoid gate | tanh bias. */
+int evi_pair_context(const int* pair_q32, const int* pair_rel32, const int* num_pairs, int capacity,
+                     const void* rel_repr16, int num_rel_rows, const float* gate_bias32, int num_questions,
+                     void* rc16, int operand_format, unsigned* flags, cudaStream_t stream);
+
 /* _score_edges + _encode_structure + _combine_directional_outputs —
- * src/models/components/retriever.py:453-495, 369-381. */
+ * src/models/components/retriever.py:453-495, 369-381. state_net.0 is linear in its input
+ * [iv | sc | err | dist] (retriever.py:481), so it is evaluated by pieces:
+ *   z_dir = nav_dir * (W_iv m) + W_sc sc_dir +- (P[h] - P[t]) + Rq[pair] + dist_dir * w_dist
+ * with m = h * r_ctx * t shared by both directions, P = W_err node_repr (per node) and
+ * Rq = W_err r_ctx + b_1 (per pair) supplied by the caller through evi_project. */
 typedef struct evi_score_args {
   long long num_edges;
   int emb_dim, hidden_dim;          /* 1024 / 1024 */
@@ -126,18 +157,21 @@ typedef struct evi_score_args {
   int operand_format;               /* EVI_FMT_* */
   int want_features;                /* 1: also produce edge_embeddings [E, H] f32 */
   int num_sms;
-  int num_nodes, num_rel_rows, num_questions; /* row counts of node_repr16 / rel_repr16 / gate_bias32 */
+  int num_nodes, num_rel_rows, num_questions, num_pair_rows; /* rows of node_* / rel_repr16 / gate_bias32 / pair_rq32 */
   unsigned* flags;                  /* EVI_FLAG_OUT_OF_RANGE if an edge indexes outside those */
   /* per-edge indices */
   const int* head32;
   const int* tail32;
   const int* qid32;
   const int* rel_slot32;            /* row of rel_repr16 for each edge */
+  const int* pair_slot32;           /* row of pair_rq32 for each edge (evi_relation_pairs) */
   /* projected operands */
   const void* node_repr16;          /* [N, D] tanh(entity_proj) */
   const void* rel_repr16;           /* [R, D] tanh(relation_proj) */
   const float* gate_bias32;         /* [B, 2D] sigmoid(q_gate(q)) | tanh(q_bias(q)) */
   const float* node_uv32;           /* [N, 2D] per-node halves of struct_proj.0 (evi_struct_project) */
+  const float* node_p32;            /* [N, H] W_err node_repr */
+  const float* pair_rq32;           /* [pairs, H] W_err r_ctx + state_net.0.bias */
   /* weights (prepared once per checkpoint) */
   const float* struct_ln_g;         /* [D] struct_proj.1 */
   const float* struct_ln_b;
@@ -145,7 +179,6 @@ typedef struct evi_score_args {
   float nav_b;
   const void* w1_main16;            /* [H, 3D] state_net.0.weight[:, :3D] */
   const float* w1_dist_col;         /* [H] state_net.0.weight[:, 3D] */
-  const float* w1_bias;             /* [H] */
   const float* ln1_g;               /* [H] state_net.1 */
   const float* ln1_b;
   const float* head_v;              /* [H] state_net.4.weight^T score_head.weight */
@@ -161,22 +194,16 @@ typedef struct evi_score_args {
   float* edge_embeddings;           /* [E, H] or NULL */
   void* workspace;
   size_t workspace_bytes;
-  /* optional cudaEvent_t pair recorded around one state_net.0 GEMM launch (the dominant kernel; the
-   * second chunk when there are several) so a caller can time it without a profiler; NULL to skip */
+  /* optional cudaEvent_t pair recorded around one W_sc sc GEMM launch (the dominant kernel; the second
+   * chunk when there are several) so a caller can time it without a profiler; NULL to skip */
   void* ev_gemm_begin;
   void* ev_gemm_end;
-  /* chunking / pipelining: edges are processed `chunk_edges` at a time (<= 0: all at once). With two
-   * auxiliary streams (cudaStream_t; the GEMM one ideally of higher priority), more than one chunk and
-   * a workspace of two chunk buffers, the operand kernel of chunk c+1 and the tail of chunk c-1 run
-   * beside the GEMM of chunk c; `stream` rejoins after the last chunk. NULL: everything on `stream`. */
+  /* edges are processed `chunk_edges` at a time (<= 0: all at once) to bound the workspace */
   long long chunk_edges;
-  void* stream_gemm;
-  void* stream_tail;
-  void* stream_op;                  /* optional third stream for the operand kernels (else `stream`) */
 } evi_score_args;
 
-/* bytes for `num_buffers` (1 serial, 2 pipelined) per-chunk workspaces of `chunk_edges` edges */
-size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features, int num_buffers);
+/* bytes of the per-chunk workspace for `chunk_edges` edges */
+size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features);
 int evi_score_edges(const evi_score_args* args, cudaStream_t stream);
 
 /* ---- ragged top-k ------------------------------------------------------------------------ */

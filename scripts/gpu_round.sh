@@ -6,7 +6,7 @@ TAG="${1:-r01}"
 OUT=gpurun_out
 mkdir -p "$OUT"
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > "$OUT/${TAG}_smi.txt" 2>&1
-timeout 900 python -m pytest tests -m gpu -x -q > "$OUT/${TAG}_pytest.log" 2>&1; echo "pytest exit $?" | tee -a "$OUT/${TAG}_pytest.log"
+timeout 900 python -m pytest tests -m gpu -x -q -s > "$OUT/${TAG}_pytest.log" 2>&1; echo "pytest exit $?" | tee -a "$OUT/${TAG}_pytest.log"
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > "$OUT/${TAG}_smoke.log" 2>&1; echo "smoke exit $?" | tee -a "$OUT/${TAG}_smoke.log"
 timeout 900 python bench.py --steps 10 --warmup 3 > "$OUT/${TAG}_bench.json" 2> "$OUT/${TAG}_bench.err"; echo "bench exit $?"
 tail -c 3000 "$OUT/${TAG}_bench.json"
@@ -16,7 +16,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
     --log-file "$OUT/${TAG}_launches.csv" python bench.py $BARGS > "$OUT/${TAG}_ncu_list.log" 2>&1
 echo "ncu list exit $?"
 timeout 600 python bench.py $BARGS > "$OUT/${TAG}_plain2.log" 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:gemm_kernel -s 6 -c 2 \
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"gemm_kernel|score_tail_kernel|edge_operand_kernel" -s 9 -c 4 \
     -o "$OUT/${TAG}_gemm" -f python bench.py $BARGS > "$OUT/${TAG}_ncu_full.log" 2>&1
 echo "ncu full exit $?"
 ls -la "$OUT"

@@ -59,8 +59,8 @@ def test_project_matches_matmul(dev, fmt_name, m):
     out32 = torch.full((m, n), float("nan"), device=dev)
     out16 = torch.zeros((m, n), dtype=dt, device=dev)
     acts = [lib.ACT_SIGMOID] * 2 + [lib.ACT_TANH] * 2 + [lib.ACT_NONE] * 4
-    st = L.evi_project(x.data_ptr(), m, w.data_ptr(), n, k, b.data_ptr(), (C.c_int * 8)(*acts), out16.data_ptr(),
-                       out32.data_ptr(), fmt, 148, torch.cuda.current_stream().cuda_stream)
+    st = L.evi_project(x.data_ptr(), m, None, w.data_ptr(), k, n, k, b.data_ptr(), (C.c_int * 8)(*acts),
+                       out16.data_ptr(), out32.data_ptr(), fmt, 148, torch.cuda.current_stream().cuda_stream)
     assert st == 0
     torch.cuda.synchronize()
     ref = x.float() @ w.float().t() + b
@@ -81,11 +81,23 @@ def test_project_k3072_and_small_n(dev):
     w = (torch.randn(n, k, generator=g) / 55).half().to(dev)
     b = torch.randn(n, generator=g).to(dev)
     out32 = torch.empty((m, n), device=dev)
-    st = L.evi_project(x.data_ptr(), m, w.data_ptr(), n, k, b.data_ptr(), (C.c_int * 8)(*[0] * 8), None,
+    st = L.evi_project(x.data_ptr(), m, None, w.data_ptr(), k, n, k, b.data_ptr(), (C.c_int * 8)(*[0] * 8), None,
                        out32.data_ptr(), lib.FMT_F16, 148, torch.cuda.current_stream().cuda_stream)
     assert st == 0
     ref = x.float() @ w.float().t() + b
     assert (out32 - ref).abs().max().item() < 3e-4
+    # column block of a wider weight matrix (ld_w > in_dim), no bias, device-side row bound
+    k2 = 1024
+    rows_dev = torch.tensor([300], dtype=torch.int32, device=dev)
+    out_b = torch.full((m, n), float("nan"), device=dev)
+    xs = x[:, :k2].contiguous()
+    st = L.evi_project(xs.data_ptr(), m, rows_dev.data_ptr(), w.data_ptr() + 2 * 2048, k, n, k2, None,
+                       (C.c_int * 8)(*[0] * 8), None, out_b.data_ptr(), lib.FMT_F16, 148,
+                       torch.cuda.current_stream().cuda_stream)
+    assert st == 0
+    ref_b = xs.float() @ w[:, 2048:].float().t()
+    assert (out_b[:300] - ref_b[:300]).abs().max().item() < 3e-4
+    assert torch.isnan(out_b[320:]).all()  # rows beyond *num_rows_dev (rounded up to a 32-row group) are never written
 
 
 # ------------------------------------------------------------------ a1 edge_batch
@@ -172,18 +184,41 @@ def test_batched_bfs_and_labels_vs_oracle(dev):
 
     qb = generate_questions(tiny_spec(24, 700, seed=4))
     gb = G.GraphBatch.from_edge_index(qb.edge_index, qb.ptr, device=dev)
-    for cap in (-1, 2):
-        dist = G.batched_bfs(gb, qb.q_local_indices, qb.q_ptr, max_depth=cap).cpu().numpy()
+    # caps 0..8 run the edge-list sweep kernel, -1 and 9 the CSR frontier kernel
+    for cap, directed in ((-1, False), (0, False), (1, False), (2, False), (4, True), (8, False), (9, False), (-1, True)):
+        dist = G.batched_bfs(gb, qb.q_local_indices, qb.q_ptr, max_depth=cap, directed=directed).cpu().numpy()
         for b in range(qb.num_graphs):
             n0, n1, e0, e1 = qb.ptr[b], qb.ptr[b + 1], qb.edge_ptr[b], qb.edge_ptr[b + 1]
             s = qb.q_local_indices[qb.q_ptr[b]:qb.q_ptr[b + 1]] - n0
-            ref = orc.bfs_dist_np(n1 - n0, qb.edge_index[0, e0:e1] - n0, qb.edge_index[1, e0:e1] - n0, s, max_depth=cap)
-            assert np.array_equal(dist[n0:n1], ref), (b, cap)  # bit-exact
+            ref = orc.bfs_dist_np(n1 - n0, qb.edge_index[0, e0:e1] - n0, qb.edge_index[1, e0:e1] - n0, s, max_depth=cap,
+                                  directed=directed)
+            assert np.array_equal(dist[n0:n1], ref), (b, cap, directed)  # bit-exact
     for mode in ("undirected", "qa_directed"):
         mask = G.batched_shortest_path_labels(gb, qb.q_local_indices, qb.q_ptr, qb.a_local_indices, qb.a_ptr,
                                               path_mode=mode).cpu().numpy()
         ref = orc.labels_for_batch(qb, directed=(mode == "qa_directed"))
         assert np.array_equal(mask.astype(np.float32), ref), mode
+
+
+def test_bfs_sweep_long_path_and_oversized_job(dev):
+    """The sweep kernel on a path graph (diameter >> cap), and on a job too large for shared memory."""
+    from evi_rag_b200 import graph as G
+
+    n = 50_000  # > 40k nodes: dist of this job lives in global memory
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(n)
+    src = np.concatenate([perm[:-1], rng.integers(0, n, 5000)])
+    dst = np.concatenate([perm[1:], rng.integers(0, n, 5000)])
+    small_n = 300
+    ei = np.stack([np.concatenate([src, np.arange(small_n - 1) + n]), np.concatenate([dst, np.arange(1, small_n) + n])])
+    ptr = np.asarray([0, n, n + small_n], dtype=np.int64)
+    gb = G.GraphBatch.from_edge_index(ei.astype(np.int64), ptr, device=dev)
+    seeds, seed_ptr = np.asarray([perm[0], perm[7], n + 5], dtype=np.int64), np.asarray([0, 2, 3], dtype=np.int64)
+    for cap in (3, 8):
+        dist = G.batched_bfs(gb, seeds, seed_ptr, max_depth=cap).cpu().numpy()
+        ref0 = orc.bfs_dist_np(n, src, dst, seeds[:2], max_depth=cap)
+        ref1 = orc.bfs_dist_np(small_n, np.arange(small_n - 1), np.arange(1, small_n), [5], max_depth=cap)
+        assert np.array_equal(dist[:n], ref0) and np.array_equal(dist[n:], ref1), cap
 
 
 # ------------------------------------------------------------------ a10-a12 top-k
@@ -368,3 +403,36 @@ def test_retriever_errors_and_empty(dev):
     del b.node_embeddings
     with pytest.raises(ValueError, match="node_embeddings and edge_embeddings"):
         m(b)
+
+
+# ------------------------------------------------------------------ (question, relation) pairs
+@pytest.mark.parametrize("num_rel", [7, 64, 6000, 70001])
+def test_relation_pairs_match_numpy_unique(dev, num_rel):
+    from evi_rag_b200 import lib
+
+    L = lib.load()
+    rng = np.random.default_rng(num_rel)
+    sizes = rng.integers(0, 3000, size=37)
+    sizes[3] = 0
+    edge_ptr = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    E, B = int(edge_ptr[-1]), len(sizes)
+    rel = np.minimum((num_rel * rng.random(E) ** 3).astype(np.int64), num_rel - 1).astype(np.int32)
+    qid = np.repeat(np.arange(B), sizes)
+    d_rel, d_ptr = torch.from_numpy(rel).to(dev), torch.from_numpy(edge_ptr).to(dev)
+    slot = torch.full((E,), -1, dtype=torch.int32, device=dev)
+    pq = torch.full((E,), -1, dtype=torch.int32, device=dev)
+    pr = torch.full((E,), -1, dtype=torch.int32, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    flags = torch.zeros(1, dtype=torch.int32, device=dev)
+    st = L.evi_relation_pairs(d_rel.data_ptr(), d_ptr.data_ptr(), B, num_rel, E, slot.data_ptr(), pq.data_ptr(),
+                              pr.data_ptr(), cnt.data_ptr(), flags.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    assert st == 0
+    torch.cuda.synchronize()
+    n = int(cnt.item())
+    key = qid.astype(np.int64) * num_rel + rel
+    assert n == np.unique(key).size and int(flags.item()) == 0
+    slot, pq, pr = slot.cpu().numpy(), pq.cpu().numpy(), pr.cpu().numpy()
+    assert slot.min() >= 0 and slot.max() < n
+    assert np.array_equal(pq[slot], qid) and np.array_equal(pr[slot], rel)  # every edge finds its own pair
+    assert np.unique(pq[:n].astype(np.int64) * num_rel + pr[:n]).size == n  # slots are distinct pairs
+    assert (pq[n:] == -1).all()
