@@ -63,6 +63,9 @@ class RetrievalPipeline:
         self.writer_scores = bool(writer_scores)
         self.validate = bool(validate)
         self._out_pinned: Optional[Dict[str, torch.Tensor]] = None
+        self._copy_stream = None
+        self._slots = None
+        self._slot_free = None
 
     @torch.no_grad()
     def run_device(self, b: Any) -> Dict[str, torch.Tensor]:
@@ -138,6 +141,55 @@ class RetrievalPipeline:
             self.model._pending_flags = True
             self.model.check_flags()
         return out
+
+    @torch.no_grad()
+    def run_stream(self, host_batches, device=None, post_device=None):
+        """Generator over ``run`` results for a sequence of host batches, software-pipelined: the H2D copy
+        of batch i+1 (own stream, two reusable device slots) overlaps the kernels of batch i, and the host
+        waits for the D2H of batch i only after batch i+1 has been queued. Same copies, same kernels and
+        same outputs as calling ``run`` per batch."""
+        dev = torch.device(device) if device is not None else self.model._device()
+        compute = torch.cuda.current_stream(dev)
+        if self._copy_stream is None or self._copy_stream.device != dev:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._slots = [dict(), dict()]
+            self._slot_free = [None, None]
+        keys = ("score", "index", "count", "head_id", "tail_id", "relation_id", "logit_fwd", "logit_bwd",
+                "bfs_dist", "flags")
+        pending = None
+        for i, hb in enumerate(host_batches):
+            slot = self._slots[i & 1]
+            with torch.cuda.stream(self._copy_stream):
+                if self._slot_free[i & 1] is not None:  # the kernels that last read this slot have finished
+                    self._copy_stream.wait_event(self._slot_free[i & 1])
+                b = types.SimpleNamespace()
+                for name in _BATCH_FIELDS:
+                    src = getattr(hb, name)
+                    buf = slot.get(name)
+                    if buf is None or buf.numel() < src.numel() or buf.dtype != src.dtype:
+                        buf = torch.empty(max(1, int(src.numel() * 1.25)), dtype=src.dtype, device=dev)
+                        slot[name] = buf
+                    view = buf[: src.numel()].view(src.shape)
+                    view.copy_(src, non_blocking=True)
+                    setattr(b, name, view)
+                copied = torch.cuda.Event()
+                copied.record(self._copy_stream)
+            b.num_graphs, b.q_ptr_host, b.ptr_host = hb.num_graphs, hb.q_ptr_host, hb.ptr_host
+            compute.wait_event(copied)
+            res = self.run_device(b)
+            if post_device is not None:
+                post_device(res)
+            out = {k: res[k].to("cpu", non_blocking=True) for k in keys}
+            done = torch.cuda.Event()
+            done.record(compute)
+            self._slot_free[i & 1] = done
+            if pending is not None:
+                pending[0].synchronize()
+                yield pending[1]
+            pending = (done, out)
+        if pending is not None:
+            pending[0].synchronize()
+            yield pending[1]
 
     @staticmethod
     def d2h_bytes(res: Dict[str, torch.Tensor]) -> int:

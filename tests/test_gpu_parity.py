@@ -436,3 +436,124 @@ def test_relation_pairs_match_numpy_unique(dev, num_rel):
     assert np.array_equal(pq[slot], qid) and np.array_equal(pr[slot], rel)  # every edge finds its own pair
     assert np.unique(pq[:n].astype(np.int64) * num_rel + pr[:n]).size == n  # slots are distinct pairs
     assert (pq[n:] == -1).all()
+
+
+# ------------------------------------------------------------------ pipeline entry points
+def test_pipeline_run_stream_equals_run(dev):
+    """The software-pipelined streaming call returns exactly what per-batch `run` returns."""
+    from evi_rag_b200.pipeline import RetrievalPipeline, host_batch
+    from evi_rag_b200.retriever import Retriever
+    from evi_rag_b200.synthetic import make_embedding_tables
+
+    spec = tiny_spec(12, 500, seed=21, num_relations=90, num_entities=1500)
+    model = Retriever(emb_dim=1024, hidden_dim=1024).eval()
+    model.load_state_dict(make_state_dict(2, trained_like=True), strict=True)
+    model.to(dev)
+    ent, rel = make_embedding_tables(spec)
+    model.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(rel))
+    pipe = RetrievalPipeline(model, top_k=50, bfs_max_depth=2)
+    hbs = [host_batch(generate_questions(spec, q_start=q0, q_count=n)) for q0, n in ((0, 5), (5, 3), (8, 4), (0, 12))]
+    one_by_one = [pipe.run(hb, dev) for hb in hbs]
+    streamed = list(pipe.run_stream(hbs, dev))
+    assert len(streamed) == len(hbs)
+    for a, b in zip(one_by_one, streamed):
+        assert a.keys() == b.keys()
+        for k in a:
+            assert torch.equal(a[k], b[k]), k  # same kernels on the same inputs: bit-identical
+    assert int(streamed[-1]["flags"].item()) == 0
+
+
+# ------------------------------------------------------------------ BASELINE configs 3 and 5 at test size
+def _oracle_and_model(qb, spec, dev, sd_seed=0, zero_topic=False, **retriever_kw):
+    import types
+
+    from evi_rag_b200.retriever import Retriever
+
+    rng = np.random.default_rng(spec.seed)
+    ent = (rng.standard_normal((spec.num_entities + 1, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((spec.num_relations, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(sd_seed, trained_like=True)
+    topic = np.zeros_like(qb.topic_one_hot) if zero_topic else qb.topic_one_hot
+    t = torch.from_numpy
+    ref = orc.retriever_forward(sd, edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
+                                node_embeddings=t(ent[qb.node_embedding_ids]), node_embedding_ids=t(qb.node_embedding_ids),
+                                edge_embeddings=t(rel[qb.edge_attr]), topic_one_hot=t(topic))
+    m = Retriever(emb_dim=1024, hidden_dim=1024, **retriever_kw).eval()
+    m.load_state_dict(sd)
+    m.to(dev)
+    m.attach_embedding_tables(t(ent), t(rel))
+    b = types.SimpleNamespace(edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
+                              node_embedding_ids=t(qb.node_embedding_ids), edge_attr=t(qb.edge_attr),
+                              topic_one_hot=t(topic))
+    return ref, m, b
+
+
+def _check_topk_sets(idx, cnt, ref_scores, edge_ptr, k, tol):
+    _, ref_idx, ref_cnt = orc.segmented_topk(ref_scores, edge_ptr, k)
+    assert np.array_equal(cnt, ref_cnt)
+    for q in range(len(edge_ptr) - 1):
+        if ref_cnt[q] == 0:
+            continue
+        e0 = int(edge_ptr[q])
+        kth = ref_scores[e0 + ref_idx[q, ref_cnt[q] - 1]]
+        for i in set(idx[q, :ref_cnt[q]].tolist()) ^ set(ref_idx[q, :ref_cnt[q]].tolist()):
+            assert abs(ref_scores[e0 + i] - kth) <= tol, (q, i)
+
+
+def test_config3_cwq_shaped_4hop(dev):
+    """BASELINE config 3 at test size: larger ragged subgraphs, 4-hop capped BFS, scoring, top-100, and the
+    chunked scoring path (several chunks per batch, a chunk boundary inside a question)."""
+    from evi_rag_b200 import graph as G
+    from evi_rag_b200.topk import segmented_topk
+
+    spec = tiny_spec(5, 4000, seed=33, num_relations=300, num_entities=5000, min_edges=1500, max_edges=9000)
+    qb = generate_questions(spec)
+    ref, m, b = _oracle_and_model(qb, spec, dev, sd_seed=4, pipeline_chunks=3)
+    m.max_workspace_bytes = 18 * 1024 * 5000  # forces ~5k-edge chunks
+    out = m(b)
+    assert m.last_chunk_edges < qb.num_edges
+    refl = ref.logits.numpy()
+    check_scores(out.logits.cpu().numpy(), refl, "fp16", "config3/logits")
+    tk = segmented_topk(out.logits, torch.from_numpy(qb.edge_ptr).to(dev), 100)
+    _check_topk_sets(tk.indices.cpu().numpy(), tk.counts.cpu().numpy(), refl, qb.edge_ptr, 100,
+                     SCORE_TOL["fp16"] * float(np.abs(refl).max()))
+    gb = G.GraphBatch.from_edge_index(qb.edge_index, qb.ptr, device=dev)
+    dist = G.batched_bfs(gb, qb.q_local_indices, qb.q_ptr, max_depth=4).cpu().numpy()
+    for q in range(qb.num_graphs):
+        n0, n1, e0, e1 = qb.ptr[q], qb.ptr[q + 1], qb.edge_ptr[q], qb.edge_ptr[q + 1]
+        s = qb.q_local_indices[qb.q_ptr[q]:qb.q_ptr[q + 1]] - n0
+        assert np.array_equal(dist[n0:n1], orc.bfs_dist_np(n1 - n0, qb.edge_index[0, e0:e1] - n0,
+                                                            qb.edge_index[1, e0:e1] - n0, s, max_depth=4))
+
+
+@pytest.mark.parametrize("dde_on", [True, False])
+def test_config5_mask_ablation_sweep(dev, dde_on):
+    """BASELINE config 5: DDE on / off (topic_one_hot zeroed like `_forward_with_topic_ablation`,
+    retriever_module.py:459-467) and k in {50, 100, 200, 500}: one selection at max k whose prefixes are the
+    smaller k's, like the writer (retriever_topk_edge_writer.py:324-327)."""
+    from evi_rag_b200.topk import segmented_topk
+
+    spec = tiny_spec(6, 1200, seed=44, num_relations=120, num_entities=2500)
+    qb = generate_questions(spec)
+    ref, m, b = _oracle_and_model(qb, spec, dev, sd_seed=5, zero_topic=not dde_on)
+    out = m(b)
+    refl = ref.logits.numpy()
+    check_scores(out.logits.cpu().numpy(), refl, "fp16", f"config5/dde_{'on' if dde_on else 'off'}")
+    edge_ptr = torch.from_numpy(qb.edge_ptr).to(dev)
+    gpu_scores = out.logits.cpu().numpy()
+    top500 = segmented_topk(out.logits, edge_ptr, 500, sigmoid=True)
+    idx500, cnt500 = top500.indices.cpu().numpy(), top500.counts.cpu().numpy()
+    for k in (50, 100, 200, 500):
+        tk = segmented_topk(out.logits, edge_ptr, k, sigmoid=True)  # writer flavour
+        idx, cnt = tk.indices.cpu().numpy(), tk.counts.cpu().numpy()
+        assert np.array_equal(cnt, np.minimum(cnt500, k))
+        for q in range(qb.num_graphs):
+            assert np.array_equal(idx[q, :cnt[q]], idx500[q, :cnt[q]])  # prefix property, bit-exact
+        raw = segmented_topk(out.logits, edge_ptr, k)  # metrics flavour: raw logits
+        ridx, rcnt = raw.indices.cpu().numpy(), raw.counts.cpu().numpy()
+        # selection itself is exact on the GPU's own scores ...
+        _, oi, oc = orc.segmented_topk(gpu_scores, qb.edge_ptr, k)
+        assert np.array_equal(ridx, oi) and np.array_equal(rcnt, oc)
+        # ... and equals the reference's sets up to the score tolerance at the k-th boundary
+        _check_topk_sets(ridx, rcnt, refl, qb.edge_ptr, k, SCORE_TOL["fp16"] * float(np.abs(refl).max()))
