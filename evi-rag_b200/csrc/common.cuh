@@ -180,6 +180,16 @@ EVI_DEVINL void tma_load_2d(void* smem_dst, const void* tmap, uint64_t* bar, int
       : "memory");
 }
 
+// 1-D bulk copy global -> shared (the TMA engine moves `bytes`, a multiple of 16, both addresses 16-byte
+// aligned); completion is signalled on an mbarrier through its transaction count
+EVI_DEVINL void bulk_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+EVI_DEVINL void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
 // 2-D tiled bulk tensor store shared -> global (bulk async-group completion). The box is clipped to
 // the tensor map's bounds, so partial tiles need no masking.
 EVI_DEVINL void tma_store_2d(const void* tmap, const void* smem_src, int c_inner, int c_outer) {

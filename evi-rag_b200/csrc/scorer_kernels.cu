@@ -234,7 +234,7 @@ constexpr int kEdgeWarps = 8;
 //   sc16 [nd*E, D] struct context, forward rows first, then backward rows
 //   scal [E, 4]   nav_f, nav_b, dist_f, dist_b
 template <int FMT>
-__global__ void __launch_bounds__(kEdgeWarps * 32)
+__global__ void __launch_bounds__(kEdgeWarps * 32, 3)
 edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
                     const uint16_t* __restrict__ node_repr,   // [N, D]
@@ -406,6 +406,130 @@ score_tail_kernel(const float* __restrict__ mm,                                 
         out = has_f ? lf : lb;
       }
       logits[e] = out;
+    }
+  }
+}
+
+// Same tail, fed by the TMA engine: persistent CTAs of 16 warps around a ring of eight 24 KB shared-memory
+// buffers. 1-D bulk copies fill a buffer with the six fp32 rows of one edge (W_iv m, W_sc sc_f, W_sc sc_b,
+// P[h], P[t], Rq[pair]); warps b and b+8 take turns on buffer b: the warp that has just moved its edge
+// from the buffer into registers hands the buffer back to the TMA engine for its partner's next edge and
+// then does LayerNorm / GELU / the head dot in registers. 192 KB stay in flight per SM without spending
+// registers or LSU issue slots on it (the register-fed version above waits on the long scoreboard 57% of
+// the time at 46% of DRAM peak). Each warp has its own full-barrier, so every barrier is waited on by one
+// warp through consecutive phases.
+constexpr int kTailWarps = 16;
+constexpr int kTailBufs = 8;
+constexpr int kTailRowBytes = D * 4;
+constexpr int kTailBufBytes = 6 * kTailRowBytes;
+constexpr int kTailSmemBytes = kTailBufs * kTailBufBytes + kTailWarps * 8;
+
+template <int FMT>
+__global__ void __launch_bounds__(kTailWarps * 32, 1)
+score_tail_bulk_kernel(const float* __restrict__ mm, const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,
+                       const float4* __restrict__ scal, const int* __restrict__ head, const int* __restrict__ tail,
+                       const int* __restrict__ pair_slot, const float* __restrict__ node_p,
+                       const float* __restrict__ pair_rq, int num_nodes, int pair_rows, long long num_edges,
+                       TailParams tp, uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd,
+                       float* __restrict__ logits, float* __restrict__ logits_fwd, float* __restrict__ logits_bwd) {
+  extern __shared__ __align__(128) uint8_t tail_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* buf = reinterpret_cast<float*>(tail_smem + (warp % kTailBufs) * kTailBufBytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail_smem + kTailBufs * kTailBufBytes);
+  uint64_t* my_bar = bars + warp;
+  uint64_t* partner_bar = bars + (warp + kTailBufs) % kTailWarps;
+  const bool has_f = s_fwd != nullptr, has_b = s_bwd != nullptr;
+  const uint32_t tx_bytes = static_cast<uint32_t>((4 + (has_f ? 1 : 0) + (has_b ? 1 : 0)) * kTailRowBytes);
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kTailWarps; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  // CTA-local sequence s -> edge blockIdx.x + s * gridDim.x; warp w takes s = w, w + 16, ...; s uses buffer s % 8
+  const long long cta_stride = gridDim.x;
+  auto edge_of = [&](long long s) { return blockIdx.x + s * cta_stride; };
+  auto load_ids = [&](long long edge, int& h, int& t, int& ps) {
+    h = __ldg(head + edge), t = __ldg(tail + edge), ps = __ldg(pair_slot + edge);
+    if (static_cast<unsigned>(h) >= static_cast<unsigned>(num_nodes) ||
+        static_cast<unsigned>(t) >= static_cast<unsigned>(num_nodes) ||
+        static_cast<unsigned>(ps) >= static_cast<unsigned>(pair_rows))
+      h = t = ps = 0;  // flagged by the operand / pair kernels
+  };
+  auto issue = [&](uint64_t* bar, long long edge, int h, int t, int ps) {  // one lane
+    mbar_arrive_expect_tx(bar, tx_bytes);
+    bulk_load_1d(buf + 0 * D, mm + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
+    if (has_f) bulk_load_1d(buf + 1 * D, s_fwd + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
+    if (has_b) bulk_load_1d(buf + 2 * D, s_bwd + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
+    bulk_load_1d(buf + 3 * D, node_p + static_cast<size_t>(h) * D, kTailRowBytes, bar);
+    bulk_load_1d(buf + 4 * D, node_p + static_cast<size_t>(t) * D, kTailRowBytes, bar);
+    bulk_load_1d(buf + 5 * D, pair_rq + static_cast<size_t>(ps) * D, kTailRowBytes, bar);
+  };
+
+  long long s = warp;
+  if (warp < kTailBufs && edge_of(s) < num_edges) {  // the first eight edges: each buffer's first owner loads its own
+    int h, t, ps;
+    load_ids(edge_of(s), h, t, ps);
+    if (lane == 0) issue(my_bar, edge_of(s), h, t, ps);
+  }
+  uint32_t phase = 0;
+  for (; edge_of(s) < num_edges; s += kTailWarps) {
+    const long long e = edge_of(s);
+    const long long e_part = edge_of(s + kTailBufs);  // the partner warp's next edge: same buffer, loaded by this warp
+    int hn = 0, tn = 0, pn = 0;
+    if (e_part < num_edges) load_ids(e_part, hn, tn, pn);  // in flight while this edge's rows land
+    const float4 sc = __ldg(scal + e);
+    mbar_wait(my_bar, phase);
+    phase ^= 1u;
+    float zf[32], zb[32];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = i * 256 + lane * 8;
+      float wd[8];
+      ldg_v8_keep(tp.w_dist + c, wd);
+      const float4 m0 = *reinterpret_cast<const float4*>(buf + c), m1 = *reinterpret_cast<const float4*>(buf + c + 4);
+      const float4 a0 = *reinterpret_cast<const float4*>(buf + 3 * D + c), a1 = *reinterpret_cast<const float4*>(buf + 3 * D + c + 4);
+      const float4 b0 = *reinterpret_cast<const float4*>(buf + 4 * D + c), b1 = *reinterpret_cast<const float4*>(buf + 4 * D + c + 4);
+      const float4 r0 = *reinterpret_cast<const float4*>(buf + 5 * D + c), r1 = *reinterpret_cast<const float4*>(buf + 5 * D + c + 4);
+      const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+      const float d[8] = {a0.x - b0.x, a0.y - b0.y, a0.z - b0.z, a0.w - b0.w, a1.x - b1.x, a1.y - b1.y, a1.z - b1.z, a1.w - b1.w};
+      const float r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+      if (has_f) {
+        const float4 s0 = *reinterpret_cast<const float4*>(buf + 1 * D + c), s1 = *reinterpret_cast<const float4*>(buf + 1 * D + c + 4);
+        const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], sv[j]) + d[j] + fmaf(sc.z, wd[j], r[j]);
+      }
+      if (has_b) {
+        const float4 s0 = *reinterpret_cast<const float4*>(buf + 2 * D + c), s1 = *reinterpret_cast<const float4*>(buf + 2 * D + c + 4);
+        const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], sv[j]) - d[j] + fmaf(sc.w, wd[j], r[j]);
+      }
+    }
+    // every lane has moved its part of the buffer into registers: hand the buffer to the partner's next edge
+    __syncwarp();
+    if (e_part < num_edges && lane == 0) {
+      fence_proxy_async_all();
+      issue(partner_bar, e_part, hn, tn, pn);
+    }
+    float lf = 0.f, lb = 0.f;
+    if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
+    if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
+    if (lane == 0) {
+      if (has_f && logits_fwd) logits_fwd[e] = lf;
+      if (has_b && logits_bwd) logits_bwd[e] = lb;
+      if (logits) {
+        float out;
+        if (has_f && has_b) {  // softmax([lf, lb]) weighted sum
+          const float mx = fmaxf(lf, lb);
+          const float ef = expf(lf - mx), eb = expf(lb - mx);
+          const float inv = 1.0f / (ef + eb);
+          out = (ef * inv) * lf + (eb * inv) * lb;
+        } else {
+          out = has_f ? lf : lb;
+        }
+        logits[e] = out;
+      }
     }
   }
 }
@@ -705,10 +829,27 @@ static int score_chunk(const evi_score_args& a, long long e0, long long E, uint8
   uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
   const int tgrid = static_cast<int>((E + 7) / 8);
   const bool feats = a.want_features != 0;
-  score_tail_kernel<FMT><<<tgrid, 256, 0, stream>>>(
-      MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
-      a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
-      feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
+  static const bool legacy_tail = getenv("EVI_TAIL_LEGACY") != nullptr;  // A/B switch: register-fed tail
+  if (legacy_tail) {
+    score_tail_kernel<FMT><<<tgrid, 256, 0, stream>>>(
+        MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+        a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
+        feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
+  } else {
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[FMT]) {
+      if (cudaFuncSetAttribute(score_tail_bulk_kernel<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               kTailSmemBytes) != cudaSuccess)
+        return kErrCuda;
+      attr_set[FMT] = true;
+    }
+    const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
+    const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
+    score_tail_bulk_kernel<FMT><<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
+        MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+        a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
+        feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
+  }
   if (check_launch() != kOk) return kErrCuda;
   if (!feats) return kOk;
   // feature path: state_net.4 as a second GEMM, logits from the fp32 features, softmax-weighted blend

@@ -66,6 +66,7 @@ class RetrievalPipeline:
         self._copy_stream = None
         self._slots = None
         self._slot_free = None
+        self._out_slots = None
 
     @torch.no_grad()
     def run_device(self, b: Any) -> Dict[str, torch.Tensor]:
@@ -154,6 +155,7 @@ class RetrievalPipeline:
             self._copy_stream = torch.cuda.Stream(device=dev)
             self._slots = [dict(), dict()]
             self._slot_free = [None, None]
+            self._out_slots = [dict(), dict(), dict()]
         keys = ("score", "index", "count", "head_id", "tail_id", "relation_id", "logit_fwd", "logit_bwd",
                 "bfs_dist", "flags")
         pending = None
@@ -179,7 +181,20 @@ class RetrievalPipeline:
             res = self.run_device(b)
             if post_device is not None:
                 post_device(res)
-            out = {k: res[k].to("cpu", non_blocking=True) for k in keys}
+            # results land in one of three rotating sets of pinned host buffers (allocating pinned memory per
+            # batch would call cudaHostAlloc, which synchronises the device); a yielded dict stays valid until
+            # two more batches have been yielded
+            oslot = self._out_slots[i % 3]
+            out = {}
+            for k in keys:
+                src = res[k]
+                buf = oslot.get(k)
+                if buf is None or buf.numel() < src.numel() or buf.dtype != src.dtype:
+                    buf = torch.empty(max(1, int(src.numel() * 1.25)), dtype=src.dtype, pin_memory=True)
+                    oslot[k] = buf
+                view = buf[: src.numel()].view(src.shape)
+                view.copy_(src, non_blocking=True)
+                out[k] = view
             done = torch.cuda.Event()
             done.record(compute)
             self._slot_free[i & 1] = done

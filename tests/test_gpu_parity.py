@@ -454,7 +454,7 @@ def test_pipeline_run_stream_equals_run(dev):
     pipe = RetrievalPipeline(model, top_k=50, bfs_max_depth=2)
     hbs = [host_batch(generate_questions(spec, q_start=q0, q_count=n)) for q0, n in ((0, 5), (5, 3), (8, 4), (0, 12))]
     one_by_one = [pipe.run(hb, dev) for hb in hbs]
-    streamed = list(pipe.run_stream(hbs, dev))
+    streamed = [{k: v.clone() for k, v in r.items()} for r in pipe.run_stream(hbs, dev)]  # buffers rotate
     assert len(streamed) == len(hbs)
     for a, b in zip(one_by_one, streamed):
         assert a.keys() == b.keys()
