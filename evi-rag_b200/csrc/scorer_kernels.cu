@@ -8,6 +8,7 @@
 #include <cstdlib>
 
 #include "gemm_tcgen05.cuh"
+#include "gemm2_tcgen05.cuh"
 #include "evi_rag_b200.h"
 
 namespace evi {
@@ -17,6 +18,17 @@ constexpr int kMaxNodeStruct = 18;  // 2*(1+4+4)
 constexpr float kLnEps = 1e-5f;
 
 static inline int check_launch() { return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda; }
+
+// fp32-output GEMM: the CTA-pair kernel (256x256 tiles, tcgen05 cta_group::2) unless EVI_GEMM_1SM is set
+template <int FMT>
+static int gemm_f32(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                    const gemm::EpiF32Tma::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev, float* out32,
+                    int ldc) {
+  static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr;
+  if (one_sm || num_sms < 2)
+    return gemm::launch<FMT, gemm::EpiF32Tma>(A, lda, B, ldb, M, N, K, ep, num_sms, stream, m_dev, out32, ldc);
+  return gemm2::launch<FMT, gemm::EpiF32Tma>(A, lda, B, ldb, M, N, K, ep, num_sms, stream, m_dev, out32, ldc);
+}
 
 // ---------------------------------------------------------------------------------------------
 // Row gather / convert: fp32 or 16-bit source rows -> dense 16-bit GEMM operand.
@@ -744,7 +756,7 @@ static int linear_act_impl(const void* x16, int m, const int* m_dev, const void*
     gemm::EpiF32Tma::Params t;
     t.bias = bias;
     for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
-    return gemm::launch<FMT, gemm::EpiF32Tma>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out32, n);
+    return gemm_f32<FMT>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out32, n);
   }
   gemm::EpiBiasAct::Params p;
   p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = n, p.ld32 = n;
@@ -812,12 +824,10 @@ static int score_chunk(const evi_score_args& a, long long e0, long long E, uint8
   gemm::EpiF32Tma::Params plain;
   plain.bias = nullptr;
   for (int i = 0; i < 8; ++i) plain.act[i] = gemm::kActNone;
-  int rc = gemm::launch<FMT, gemm::EpiF32Tma>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, a.num_sms, stream,
-                                              nullptr, MM, D);
+  int rc = gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, a.num_sms, stream, nullptr, MM, D);
   if (rc != kOk) return rc;
   if (time_begin) cudaEventRecord(time_begin, stream);
-  rc = gemm::launch<FMT, gemm::EpiF32Tma>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, a.num_sms,
-                                          stream, nullptr, S, D);
+  rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, a.num_sms, stream, nullptr, S, D);
   if (time_end) cudaEventRecord(time_end, stream);
   if (rc != kOk) return rc;
 
