@@ -183,6 +183,148 @@ __global__ void topk_payload_kernel(const int* __restrict__ indices, const int* 
   if (out_lb) out_lb[t] = valid && logits_bwd ? logits_bwd[e] : 0.f;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Metric consumers of one ragged top-k, one CTA per question, from the selected
+// indices instead of one torch.topk + several host syncs per graph and per metric:
+//   hits[b, i]   = positives among the first min(k_i, k_top) selected edges     retriever_metrics.py:134-157
+//   pos[b]       = positives among all edges of the question (label > 0.5)      retriever_metrics.py:43,142
+//   reach[b, i]  = some answer node is connected to some seed node by the first min(k_i, k_top)
+//                  selected edges (union-find)                                   reachability.py:329-381
+//   margin[b]    = min positive score - max negative score                       retriever_metrics.py:372-386
+// k_values must be ascending (normalize_k_values, src/utils/metrics.py:25-40).
+// ---------------------------------------------------------------------------------------------
+constexpr int kMetricThreads = 128;
+constexpr int kMaxMetricK = 16;
+
+struct MetricKs {
+  int v[kMaxMetricK];
+  int n;
+};
+
+EVI_DEVINL int uf_find(int* parent, int x) {
+  while (parent[x] != x) {
+    parent[x] = parent[parent[x]];  // path halving (reachability.py:300-304)
+    x = parent[x];
+  }
+  return x;
+}
+
+__global__ void __launch_bounds__(kMetricThreads)
+topk_metrics_kernel(const int* __restrict__ indices, const int* __restrict__ counts,
+                    const long long* __restrict__ edge_ptr, int k, MetricKs ks,
+                    const float* __restrict__ labels, const float* __restrict__ scores,
+                    const int* __restrict__ head, const int* __restrict__ tail, const long long* __restrict__ node_ptr,
+                    const long long* __restrict__ seeds, const long long* __restrict__ seed_ptr,
+                    const long long* __restrict__ answers, const long long* __restrict__ answer_ptr,
+                    int* __restrict__ uf_parent,  // [total nodes] scratch
+                    float* __restrict__ hits, float* __restrict__ pos, unsigned char* __restrict__ reach,
+                    unsigned char* __restrict__ reach_valid, float* __restrict__ margin,
+                    unsigned char* __restrict__ margin_valid) {
+  __shared__ float red_a[kMetricThreads / 32], red_b[kMetricThreads / 32];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const long long e0 = edge_ptr[b];
+  const int ne = static_cast<int>(edge_ptr[b + 1] - e0);
+  const int kt = counts[b];
+  const int* idx = indices + static_cast<size_t>(b) * k;
+
+  if (labels != nullptr) {
+    // positives of the whole question, and hits at each k
+    float p = 0.f;
+    for (int i = tid; i < ne; i += kMetricThreads) p += labels[e0 + i] > 0.5f ? 1.f : 0.f;
+    p = warp_sum(p);
+    if (lane == 0) red_a[w] = p;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int i = 0; i < kMetricThreads / 32; ++i) t += red_a[i];
+      pos[b] = t;
+    }
+    __syncthreads();
+    for (int ki = 0; ki < ks.n; ++ki) {
+      const int ke = ks.v[ki] < kt ? ks.v[ki] : kt;
+      float h = 0.f;
+      for (int j = tid; j < ke; j += kMetricThreads) h += labels[e0 + idx[j]] > 0.5f ? 1.f : 0.f;
+      h = warp_sum(h);
+      if (lane == 0) red_a[w] = h;
+      __syncthreads();
+      if (tid == 0) {
+        float t = 0.f;
+        for (int i = 0; i < kMetricThreads / 32; ++i) t += red_a[i];
+        hits[static_cast<size_t>(b) * ks.n + ki] = t;
+      }
+      __syncthreads();
+    }
+    if (scores != nullptr && margin != nullptr) {
+      float mn = INFINITY, mx = -INFINITY;  // min over positives, max over negatives
+      for (int i = tid; i < ne; i += kMetricThreads) {
+        const float s = scores[e0 + i];
+        if (labels[e0 + i] > 0.5f) mn = fminf(mn, s); else mx = fmaxf(mx, s);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      }
+      if (lane == 0) red_a[w] = mn, red_b[w] = mx;
+      __syncthreads();
+      if (tid == 0) {
+        for (int i = 1; i < kMetricThreads / 32; ++i) mn = fminf(mn, red_a[i]), mx = fmaxf(mx, red_b[i]);
+        const bool ok = mn != INFINITY && mx != -INFINITY;  // has a positive and a negative
+        margin[b] = ok ? mn - mx : 0.f;
+        margin_valid[b] = ok ? 1 : 0;
+      }
+      __syncthreads();
+    }
+  }
+
+  if (reach == nullptr) return;
+  const long long n0 = node_ptr[b];
+  const int nn = static_cast<int>(node_ptr[b + 1] - n0);
+  int* parent = uf_parent + n0;
+  for (int i = tid; i < nn; i += kMetricThreads) parent[i] = i;
+  __syncthreads();
+  if (tid != 0) return;
+  // seeds / answers inside this question's node range (reachability.py:160-165)
+  const long long s0 = seed_ptr[b], s1 = seed_ptr[b + 1], a0 = answer_ptr[b], a1 = answer_ptr[b + 1];
+  int n_seed = 0, n_ans = 0;
+  for (long long i = s0; i < s1; ++i) n_seed += (seeds[i] >= n0 && seeds[i] < n0 + nn) ? 1 : 0;
+  for (long long i = a0; i < a1; ++i) n_ans += (answers[i] >= n0 && answers[i] < n0 + nn) ? 1 : 0;
+  const bool valid = ne > 0 && nn > 0 && n_seed > 0 && n_ans > 0;
+  reach_valid[b] = valid ? 1 : 0;
+  if (!valid) {
+    for (int ki = 0; ki < ks.n; ++ki) reach[static_cast<size_t>(b) * ks.n + ki] = 0;
+    return;
+  }
+  auto reachable = [&]() {
+    for (long long a = a0; a < a1; ++a) {
+      if (answers[a] < n0 || answers[a] >= n0 + nn) continue;
+      const int ra = uf_find(parent, static_cast<int>(answers[a] - n0));
+      for (long long s = s0; s < s1; ++s) {
+        if (seeds[s] < n0 || seeds[s] >= n0 + nn) continue;
+        if (uf_find(parent, static_cast<int>(seeds[s] - n0)) == ra) return true;
+      }
+    }
+    return false;
+  };
+  int next = 0;
+  bool cur = false;
+  for (int j = 0; j < kt && next < ks.n; ++j) {
+    const long long e = e0 + idx[j];
+    const int u = head[e] - static_cast<int>(n0), v = tail[e] - static_cast<int>(n0);
+    if (u >= 0 && v >= 0 && u < nn && v < nn) {
+      const int ru = uf_find(parent, u), rv = uf_find(parent, v);
+      if (ru != rv) parent[rv] = ru;
+    }
+    bool fresh = false;
+    while (next < ks.n && j + 1 >= (ks.v[next] < kt ? ks.v[next] : kt)) {
+      if (!fresh) cur = reachable(), fresh = true;
+      reach[static_cast<size_t>(b) * ks.n + next] = cur ? 1 : 0;
+      ++next;
+    }
+  }
+  for (; next < ks.n; ++next) reach[static_cast<size_t>(b) * ks.n + next] = cur ? 1 : 0;  // kt == 0 cannot happen when valid
+}
+
 }  // namespace evi
 
 using namespace evi;
@@ -214,6 +356,35 @@ int evi_topk_gather_payload(const int* indices, const int* counts, const long lo
   topk_payload_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, stream>>>(
       indices, counts, edge_ptr, num_graphs, k, edge_index, num_edges, node_global_ids, edge_attr, labels,
       logits_fwd, logits_bwd, head_ids, tail_ids, relation_ids, out_labels, out_logits_fwd, out_logits_bwd);
+  return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
+}
+
+int evi_topk_metrics(const int* indices, const int* counts, const long long* edge_ptr, int num_graphs, int k,
+                     const int* k_values_host, int num_k, const float* labels, const float* scores, const int* head32,
+                     const int* tail32, const long long* node_ptr, const long long* seeds, const long long* seed_ptr,
+                     const long long* answers, const long long* answer_ptr, int* uf_parent_scratch, float* hits,
+                     float* pos, unsigned char* reach, unsigned char* reach_valid, float* margin,
+                     unsigned char* margin_valid, cudaStream_t stream) {
+  if (num_graphs <= 0) return kOk;
+  if (num_k <= 0 || num_k > kMaxMetricK || k <= 0 || indices == nullptr || counts == nullptr || edge_ptr == nullptr ||
+      k_values_host == nullptr)
+    return kErrInvalidArg;
+  if (labels != nullptr && (hits == nullptr || pos == nullptr)) return kErrInvalidArg;
+  if (margin != nullptr && (scores == nullptr || labels == nullptr || margin_valid == nullptr)) return kErrInvalidArg;
+  if (reach != nullptr && (head32 == nullptr || tail32 == nullptr || node_ptr == nullptr || seeds == nullptr ||
+                           seed_ptr == nullptr || answers == nullptr || answer_ptr == nullptr ||
+                           uf_parent_scratch == nullptr || reach_valid == nullptr))
+    return kErrInvalidArg;
+  MetricKs ks;
+  ks.n = num_k;
+  for (int i = 0; i < num_k; ++i) {
+    if (k_values_host[i] <= 0 || (i > 0 && k_values_host[i] <= k_values_host[i - 1])) return kErrInvalidArg;
+    ks.v[i] = k_values_host[i];
+  }
+  topk_metrics_kernel<<<num_graphs, kMetricThreads, 0, stream>>>(indices, counts, edge_ptr, k, ks, labels, scores, head32,
+                                                              tail32, node_ptr, seeds, seed_ptr, answers, answer_ptr,
+                                                              uf_parent_scratch, hits, pos, reach, reach_valid, margin,
+                                                              margin_valid);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 

@@ -66,6 +66,7 @@ PROTOTYPES = {
     "evi_score_edges": (_i, [C.POINTER(ScoreArgs), _vp]),
     "evi_segmented_topk": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_topk_gather_payload": (_i, [_vp, _vp, _vp, _i, _i, _vp, _ll] + [_vp] * 11 + [_vp]),
+    "evi_topk_metrics": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i] + [_vp] * 16 + [_vp]),
 }
 
 _lib: Optional[C.CDLL] = None
@@ -87,6 +88,7 @@ _KERNELS_PER_CALL = {
     "evi_score_edges": lambda a: (6 if a[0]._obj.want_features else 4) * _num_chunks(a[0]._obj),
     "evi_segmented_topk": lambda a: 1,
     "evi_topk_gather_payload": lambda a: 1,
+    "evi_topk_metrics": lambda a: 1,
 }
 
 

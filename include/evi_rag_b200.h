@@ -225,6 +225,21 @@ int evi_topk_gather_payload(const int* indices, const int* counts, const long lo
                             long long* tail_ids, long long* relation_ids, float* out_labels,
                             float* out_logits_fwd, float* out_logits_bwd, cudaStream_t stream);
 
+/* Metric consumers of one ragged top-k, one CTA per question (all outputs optional in groups):
+ *   labels  -> hits [B, num_k] (positives among the first min(k_i, k_top) selected edges) and pos [B]
+ *              (EdgeRecallAtK / BridgeEdgeRecallAtK, src/metrics/retriever_metrics.py:134-157, 234-258)
+ *   scores  -> margin [B] = min positive - max negative score, margin_valid [B] (ScoreMargin, :372-386)
+ *   graph   -> reach [B, num_k]: an answer node is connected to a seed node by the first min(k_i, k_top)
+ *              selected edges, reach_valid [B] (AnswerReachability, src/metrics/reachability.py:129-179, 329-381)
+ * k_values_host: ascending host array (normalize_k_values), num_k <= 16. seeds / answers are batch-global node
+ * ids grouped by seed_ptr / answer_ptr [B+1]; uf_parent_scratch: one int per node of the batch. */
+int evi_topk_metrics(const int* indices, const int* counts, const long long* edge_ptr, int num_graphs, int k,
+                     const int* k_values_host, int num_k, const float* labels, const float* scores, const int* head32,
+                     const int* tail32, const long long* node_ptr, const long long* seeds, const long long* seed_ptr,
+                     const long long* answers, const long long* answer_ptr, int* uf_parent_scratch, float* hits,
+                     float* pos, unsigned char* reach, unsigned char* reach_valid, float* margin,
+                     unsigned char* margin_valid, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -271,11 +271,109 @@ def recall_at_k(scores, labels, edge_ptr, k_values: Sequence[int]) -> Dict[int, 
         n += 1
         top = lab[idx[b, :kt]]
         cum = np.cumsum(top)
-        denom = max(float(lab.sum()), 1e-6)
+        denom = max(float(lab.sum()), 1.0)  # _COUNT_EPS = 1.0 (retriever_metrics.py:12,148)
         for k in k_values:
             ke = min(int(k), kt)
             sums[int(k)] += float(cum[ke - 1] / denom) if ke > 0 else 0.0
     return {k: (v / n if n else 0.0) for k, v in sums.items()}
+
+
+def qa_edge_mask(edge_index: np.ndarray, num_nodes: int, q_local_indices, a_local_indices) -> np.ndarray:
+    """``compute_qa_edge_mask`` (src/utils/graph_utils.py:107-153): edges touching a seed or answer node."""
+    node_mask = np.zeros(int(num_nodes), dtype=bool)
+    qa = np.concatenate([np.asarray(q_local_indices, dtype=np.int64).ravel(), np.asarray(a_local_indices, dtype=np.int64).ravel()])
+    if qa.size:
+        node_mask[qa] = True
+    return node_mask[edge_index[0]] | node_mask[edge_index[1]]
+
+
+def bridge_recall_at_k(scores, labels, edge_index, edge_ptr, num_nodes, q_local_indices, a_local_indices,
+                       k_values: Sequence[int]) -> Dict[int, float]:
+    """``BridgeEdgeRecallAtK`` (retriever_metrics.py:173-268): near edges are dropped before the per-graph
+    top-k; graphs without a bridge positive are skipped."""
+    keep = ~qa_edge_mask(edge_index, num_nodes, q_local_indices, a_local_indices)
+    sums = {int(k): 0.0 for k in k_values}
+    n = 0
+    max_k = max(k_values)
+    for b in range(len(edge_ptr) - 1):
+        sl = slice(int(edge_ptr[b]), int(edge_ptr[b + 1]))
+        sc = np.asarray(scores[sl])[keep[sl]]
+        lab = (np.asarray(labels[sl])[keep[sl]] > 0.5).astype(np.float32)
+        if sc.size == 0 or lab.sum() <= 0:
+            continue
+        _, idx, cnt = segmented_topk(sc, np.asarray([0, sc.size]), max_k)
+        kt = int(cnt[0])
+        cum = np.cumsum(lab[idx[0, :kt]])
+        for k in k_values:
+            ke = min(int(k), kt)
+            sums[int(k)] += float(cum[ke - 1] / max(float(lab.sum()), 1.0)) if ke > 0 else 0.0
+        n += 1
+    return {k: (v / max(n, 1)) for k, v in sums.items()}
+
+
+def score_margin(scores, labels, edge_ptr) -> float:
+    """``ScoreMargin`` (retriever_metrics.py:331-395): mean over graphs with a positive and a negative of
+    min(pos scores) - max(neg scores)."""
+    tot, n = 0.0, 0
+    for b in range(len(edge_ptr) - 1):
+        sl = slice(int(edge_ptr[b]), int(edge_ptr[b + 1]))
+        sc, lab = np.asarray(scores[sl], dtype=np.float32), np.asarray(labels[sl]) > 0.5
+        if sc.size == 0 or not lab.any() or lab.all():
+            continue
+        tot += float(sc[lab].min() - sc[~lab].max())
+        n += 1
+    return tot / max(n, 1)
+
+
+def reachability_at_k(scores, edge_index, edge_ptr, node_ptr, q_local_indices, q_ptr, a_local_indices, a_ptr,
+                      k_values: Sequence[int]) -> Dict[int, float]:
+    """``AnswerReachability`` (src/metrics/reachability.py:129-179, 200-228, 329-381): union-find over the first
+    min(k, k_top) top-scored edges; a graph is valid when it has edges, in-range seeds and in-range answers."""
+    ks = sorted({int(k) for k in k_values if int(k) > 0})
+    hits = {k: 0.0 for k in ks}
+    valid = 0
+    for g in range(len(edge_ptr) - 1):
+        e0, e1 = int(edge_ptr[g]), int(edge_ptr[g + 1])
+        if e1 <= e0:
+            continue
+        n0, n1 = int(node_ptr[g]), int(node_ptr[g + 1])
+        nn = n1 - n0
+        qn = np.asarray(q_local_indices[int(q_ptr[g]):int(q_ptr[g + 1])], dtype=np.int64)
+        an = np.asarray(a_local_indices[int(a_ptr[g]):int(a_ptr[g + 1])], dtype=np.int64)
+        ql = qn[(qn >= n0) & (qn < n1)] - n0
+        al = an[(an >= n0) & (an < n1)] - n0
+        if nn <= 0 or ql.size == 0 or al.size == 0:
+            continue
+        _, idx, cnt = segmented_topk(np.asarray(scores[e0:e1]), np.asarray([0, e1 - e0]), max(ks))
+        kt = int(cnt[0])
+        parent = list(range(nn))
+
+        def find(x):
+            while parent[x] != x:
+                parent[x] = parent[parent[x]]
+                x = parent[x]
+            return x
+
+        def reachable():
+            roots = {find(int(s)) for s in ql}
+            return any(find(int(a)) in roots for a in al)
+
+        k_check = sorted({min(k, kt) for k in ks})
+        reach_map, nxt = {}, 0
+        for j in range(kt):
+            u, v = int(edge_index[0, e0 + idx[0, j]]) - n0, int(edge_index[1, e0 + idx[0, j]]) - n0
+            if 0 <= u < nn and 0 <= v < nn:
+                ru, rv = find(u), find(v)
+                if ru != rv:
+                    parent[rv] = ru
+            while nxt < len(k_check) and j + 1 >= k_check[nxt]:
+                reach_map[k_check[nxt]] = reachable()
+                nxt += 1
+        valid += 1
+        for k in ks:
+            if reach_map[min(k, kt)]:
+                hits[k] += 1.0
+    return {k: hits[k] / max(valid, 1) for k in ks}
 
 
 # ----------------------------------------------------------------------------------------------

@@ -557,3 +557,38 @@ def test_config5_mask_ablation_sweep(dev, dde_on):
         assert np.array_equal(ridx, oi) and np.array_equal(rcnt, oc)
         # ... and equals the reference's sets up to the score tolerance at the k-th boundary
         _check_topk_sets(ridx, rcnt, refl, qb.edge_ptr, k, SCORE_TOL["fp16"] * float(np.abs(refl).max()))
+
+
+# ------------------------------------------------------------------ a10 metric consumers
+def test_retriever_metrics_match_oracle(dev):
+    """edge/recall@k, bridge/recall@k, answer/reachability@k and edge/score_margin from one ragged top-k per
+    batch against the per-graph loops of the reference metrics (restated in the oracle)."""
+    from evi_rag_b200 import graph as G
+    from evi_rag_b200.metrics import retriever_metrics
+
+    spec = tiny_spec(40, 600, seed=9, num_relations=50, num_entities=900, unreachable_frac=0.2)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(2)
+    # shortest-path positives (a14) plus 2% random ones: path positives of 1-2 hop answers all touch a seed or an
+    # answer, so bridge recall needs positives elsewhere to be exercised
+    labels = np.maximum(orc.labels_for_batch(qb), (rng.random(qb.num_edges) < 0.02).astype(np.float32))
+    # scores that partly agree with the labels so recall / reachability are neither 0 nor 1, with exact ties
+    scores = np.round(rng.standard_normal(qb.num_edges) + 1.5 * labels * (rng.random(qb.num_edges) < 0.6), 2).astype(np.float32)
+    ks = [1, 10, 25, 50, 100, 200, 300, 400, 500]  # configs/window/default.yaml:8
+    gb = G.GraphBatch.from_edge_index(qb.edge_index, qb.ptr, device=dev)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    got = retriever_metrics(t(scores), t(labels), gb.edge_ptr, ks, graph=gb, node_ptr=t(qb.ptr),
+                            q_local_indices=t(qb.q_local_indices), q_ptr=t(qb.q_ptr),
+                            a_local_indices=t(qb.a_local_indices), a_ptr=t(qb.a_ptr))
+    rec = orc.recall_at_k(scores, labels, qb.edge_ptr, ks)
+    brec = orc.bridge_recall_at_k(scores, labels, qb.edge_index, qb.edge_ptr, qb.num_nodes, qb.q_local_indices,
+                                  qb.a_local_indices, ks)
+    reach = orc.reachability_at_k(scores, qb.edge_index, qb.edge_ptr, qb.ptr, qb.q_local_indices, qb.q_ptr,
+                                  qb.a_local_indices, qb.a_ptr, ks)
+    for k in ks:
+        assert abs(got[f"edge/recall@{k}"] - rec[k]) < 1e-6, k
+        assert abs(got[f"bridge/recall@{k}"] - brec[k]) < 1e-6, k
+        assert abs(got[f"answer/reachability@{k}"] - reach[k]) < 1e-7, k  # integer counts: exact
+    assert abs(got["edge/score_margin"] - orc.score_margin(scores, labels, qb.edge_ptr)) < 1e-5
+    assert 0.0 < got["answer/reachability@100"] < 1.0 and 0.0 < got["edge/recall@50"] < 1.0
+    assert 0.0 < got["bridge/recall@100"] < 1.0
