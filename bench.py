@@ -185,6 +185,18 @@ def measured_peaks():
     return 1400.0, 6650.0, "fallback (B200_PROFILING.md: ~1.4 PF sustained)"
 
 
+def roofline_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the roofline kernel, from the committed
+    `ncu --set full` capture (profiles/roofline_traffic.json, written by scripts/summarize_ncu.py); null if absent."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if not os.path.exists(p):
+        return None
+    try:
+        return float(json.load(open(p))["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def run_ours(args):
     import torch.distributed as dist
 
@@ -325,7 +337,7 @@ def run_ours(args):
             "bound": "tensor", "kernel": "gemm_kernel<EpiStoreF32> (W_sc block of state_net.0: [2E_chunk,1024]x[1024,1024]; "
                                          "flops counted = executed by that launch)",
             "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
-            "traffic": None, "peak_source": peak_src,
+            "traffic": roofline_traffic(), "peak_source": peak_src,
             "ms_per_launch": float(np.mean(gemm_ms)), "share_of_step": float(np.sum(gemm_ms)) / ms_dev,
             "step_algorithmic_tflops": step_flops / (ms_dev * 1e-3) / 1e12 / world,
             "step_frac_of_peak": step_flops / (ms_dev * 1e-3) / 1e12 / world / peak_tf,

@@ -16,7 +16,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
     --log-file "$OUT/${TAG}_launches.csv" python bench.py $BARGS > "$OUT/${TAG}_ncu_list.log" 2>&1
 echo "ncu list exit $?"
 timeout 600 python bench.py $BARGS > "$OUT/${TAG}_plain2.log" 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"gemm_kernel|score_tail_kernel|edge_operand_kernel" -s 9 -c 4 \
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:"gemm2_kernel|score_tail_bulk_kernel|edge_operand_kernel" -s 10 -c 8 \
     -o "$OUT/${TAG}_gemm" -f python bench.py $BARGS > "$OUT/${TAG}_ncu_full.log" 2>&1
 echo "ncu full exit $?"
 ls -la "$OUT"
