@@ -10,44 +10,9 @@
 
 #include "common.cuh"
 #include "evi_rag_b200.h"
+#include "select.cuh"
 
 namespace evi {
-
-constexpr int kTopkThreads = 256;
-constexpr int kTopkMaxK = 1024;
-
-EVI_DEVINL float apply_transform(float x, int transform) {
-  return transform == EVI_TOPK_SIGMOID ? 1.0f / (1.0f + expf(-x)) : x;
-}
-// order-preserving float -> uint key; NaN sorts first like torch.topk, -0 == +0
-EVI_DEVINL uint32_t order_key(float x) {
-  if (x != x) return 0xFFFFFFFFu;
-  const uint32_t b = __float_as_uint(x + 0.0f);
-  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
-
-// block-wide inclusive scan of one int per thread (blockDim == kTopkThreads)
-EVI_DEVINL int block_inclusive_scan(int v, int* warp_tot /*[8]*/, int* total) {
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  int incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int y = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += y;
-  }
-  if (lane == 31) warp_tot[w] = incl;
-  __syncthreads();
-  int off = 0, tot = 0;
-#pragma unroll
-  for (int i = 0; i < kTopkThreads / 32; ++i) {
-    const int t = warp_tot[i];
-    if (i < w) off += t;
-    tot += t;
-  }
-  __syncthreads();
-  *total = tot;
-  return incl + off;
-}
 
 __global__ void __launch_bounds__(kTopkThreads)
 segmented_topk_kernel(const float* __restrict__ scores, const long long* __restrict__ edge_ptr, int k,
@@ -331,7 +296,7 @@ using namespace evi;
 
 extern "C" {
 
-int evi_abi_version(void) { return 3; }
+int evi_abi_version(void) { return 4; }
 
 int evi_segmented_topk(const float* scores, const long long* edge_ptr, int num_graphs, int k, int transform,
                        float* values, int* indices, int* counts, cudaStream_t stream) {

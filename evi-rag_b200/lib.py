@@ -46,6 +46,23 @@ class ScoreArgs(C.Structure):
     ]
 
 
+class GAgentArgs(C.Structure):
+    """``evi_gagent_args`` (include/evi_rag_b200.h)."""
+
+    _fields_ = [(n, _i) for n in ("num_graphs", "cap", "score_mode", "topk_stride", "max_starts", "max_answers")] + [
+        (n, _vp) for n in (
+            "raw_scores", "labels", "head32", "tail32", "edge_attr", "edge_ptr", "node_ptr", "node_global_ids",
+            "node_embedding_ids", "start_entity_ids", "start_ptr", "answer_entity_ids", "answer_ptr", "topk_indices",
+            "topk_counts", "mark", "status", "num_triples", "num_nodes_out", "num_start_locals", "num_answers",
+            "num_answer_locals", "env_edge_ids", "edge_heads_global", "edge_tails_global", "edge_relations",
+            "edge_scores", "edge_labels", "edge_head_locals", "edge_tail_locals", "node_entity_ids",
+            "node_embedding_ids_out", "node_batch_index", "start_node_locals", "answer_ids_unique",
+            "answer_node_locals")]
+
+
+GAGENT_LOGITS, GAGENT_NODE_SOFTMAX, GAGENT_MAX_CAP = 0, 1, 2048
+GAGENT_EMPTY, GAGENT_NO_START_NODE, GAGENT_OVERFLOW, GAGENT_NO_START_LOCAL, GAGENT_NO_ANSWER = 1, 2, 4, 8, 16
+
 # name -> (restype, argtypes); every symbol include/evi_rag_b200.h declares
 PROTOTYPES = {
     "evi_abi_version": (_i, []),
@@ -67,6 +84,10 @@ PROTOTYPES = {
     "evi_segmented_topk": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_topk_gather_payload": (_i, [_vp, _vp, _vp, _i, _i, _vp, _ll] + [_vp] * 11 + [_vp]),
     "evi_topk_metrics": (_i, [_vp, _vp, _vp, _i, _i, _vp, _i] + [_vp] * 16 + [_vp]),
+    "evi_node_softmax_workspace_bytes": (_sz, [_i]),
+    "evi_node_softmax_logit": (_i, [_vp, _vp, _vp, _ll, _i, _i, _f, _f, _vp, _sz, _vp, _vp, _vp]),
+    "evi_gagent_start_edges": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp]),
+    "evi_gagent_build": (_i, [C.POINTER(GAgentArgs), _vp]),
 }
 
 _lib: Optional[C.CDLL] = None
@@ -89,6 +110,9 @@ _KERNELS_PER_CALL = {
     "evi_segmented_topk": lambda a: 1,
     "evi_topk_gather_payload": lambda a: 1,
     "evi_topk_metrics": lambda a: 1,
+    "evi_node_softmax_logit": lambda a: 1 if a[5] == 0 else 3,
+    "evi_gagent_start_edges": lambda a: 1,
+    "evi_gagent_build": lambda a: 1,
 }
 
 

@@ -240,6 +240,82 @@ int evi_topk_metrics(const int* indices, const int* counts, const long long* edg
                      float* pos, unsigned char* reach, unsigned char* reach_valid, float* margin,
                      unsigned char* margin_valid, cudaStream_t stream);
 
+/* ---- g_agent selection (src/data/components/g_agent_builder.py) --------------------------------------- */
+
+#define EVI_GAGENT_LOGITS 0        /* score_mode "logits" */
+#define EVI_GAGENT_NODE_SOFTMAX 1  /* score_mode "node_softmax" (default) */
+#define EVI_GAGENT_MAX_CAP 2048
+/* per-question status bits */
+#define EVI_GAGENT_EMPTY 1           /* no edges: the reference skips the question (g_agent_builder.py:205-207) */
+#define EVI_GAGENT_NO_START_NODE 2   /* "Start entities missing from retrieval graph" ValueError (:285-286) */
+#define EVI_GAGENT_OVERFLOW 4        /* more than `cap` selected edges or more than 64 start nodes */
+#define EVI_GAGENT_NO_START_LOCAL 8  /* retrieval_failed: no start entity among the kept nodes (:393-395) */
+#define EVI_GAGENT_NO_ANSWER 16      /* no answer among the kept nodes: dropped or dummy sample (:430-470) */
+
+/* Calibration `s / T + b` (:164-165) and GAgentBuilder._node_softmax_logit (:594-626) for a whole batch:
+ * out = logit(clamp(0.5 (softmax over edges sharing the head + softmax over edges sharing the tail))).
+ * head32 / tail32 are batch-global node ids. calibrated [E] receives the calibrated logits; with
+ * EVI_GAGENT_LOGITS out = calibrated (:579-580). workspace: evi_node_softmax_workspace_bytes(num_nodes). */
+size_t evi_node_softmax_workspace_bytes(int num_nodes);
+int evi_node_softmax_logit(const float* scores, const int* head32, const int* tail32, long long num_edges,
+                           int num_nodes, int score_mode, float temperature, float bias, void* workspace,
+                           size_t workspace_bytes, float* calibrated, float* out, cudaStream_t stream);
+
+/* GAgentBuilder._select_start_edges (:654-724): per question the start nodes are the nodes whose global id is
+ * in start_entity_ids (:283-287); for each, k_s = min(deg, clamp(ceil(deg * ratio), min, max)) best incident
+ * entries, incident list = heads then tails, stable descending. mark [E] u8 is cleared and receives the union
+ * (start_max_edges < 0 means None); status [B] receives EVI_GAGENT_NO_START_NODE / EVI_GAGENT_OVERFLOW. */
+int evi_gagent_start_edges(const float* sel_scores, const int* head32, const int* tail32, const long long* edge_ptr,
+                           const long long* node_ptr, int num_graphs, const long long* node_global_ids,
+                           const long long* start_entity_ids, const long long* start_ptr, float start_keep_ratio,
+                           int start_min_edges, int start_max_edges, unsigned char* mark, int* status,
+                           cudaStream_t stream);
+
+/* GAgentBuilder._build_and_add_sample steps A, C, D (:298-428), one CTA per question: union of `mark` with the
+ * top-k (evi_segmented_topk on the selection scores), (h, r, t) dedup in first-seen order with max raw score /
+ * label, sorted unique entity ids, locals, re-normalised scores, start / answer locals. Edge outputs are
+ * [B, cap], node outputs [B, 2 cap], anchors [B, max_starts] / [B, max_answers]; counts are [B]. */
+typedef struct evi_gagent_args {
+  int num_graphs, cap, score_mode, topk_stride, max_starts, max_answers;
+  const float* raw_scores;            /* [E] calibrated logits */
+  const float* labels;                /* [E] or NULL */
+  const int* head32;                  /* [E] batch-global node ids */
+  const int* tail32;
+  const long long* edge_attr;         /* [E] relation ids */
+  const long long* edge_ptr;          /* [B+1] */
+  const long long* node_ptr;          /* [B+1] */
+  const long long* node_global_ids;   /* [N] */
+  const long long* node_embedding_ids;/* [N] */
+  const long long* start_entity_ids;  /* ragged by start_ptr [B+1], given order */
+  const long long* start_ptr;
+  const long long* answer_entity_ids; /* ragged by answer_ptr [B+1], given order */
+  const long long* answer_ptr;
+  const int* topk_indices;            /* [B, topk_stride] question-local */
+  const int* topk_counts;             /* [B] */
+  unsigned char* mark;                /* [E] from evi_gagent_start_edges; updated in place */
+  int* status;                        /* [B] in/out */
+  int* num_triples;                   /* [B] */
+  int* num_nodes_out;
+  int* num_start_locals;
+  int* num_answers;
+  int* num_answer_locals;
+  int* env_edge_ids;                  /* [B, cap] question-local id of the first edge of each kept triple */
+  long long* edge_heads_global;       /* [B, cap] */
+  long long* edge_tails_global;
+  long long* edge_relations;
+  float* edge_scores;                 /* re-normalised */
+  float* edge_labels;
+  int* edge_head_locals;
+  int* edge_tail_locals;
+  long long* node_entity_ids;         /* [B, 2 cap] ascending */
+  long long* node_embedding_ids_out;
+  int* node_batch_index;              /* batch node index of each kept node */
+  int* start_node_locals;             /* [B, max_starts] */
+  long long* answer_ids_unique;       /* [B, max_answers] */
+  int* answer_node_locals;            /* [B, max_answers] */
+} evi_gagent_args;
+int evi_gagent_build(const evi_gagent_args* args, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

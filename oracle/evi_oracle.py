@@ -546,3 +546,167 @@ def labels_for_batch(qb, *, directed: bool = False) -> np.ndarray:
         )[0]
         labels[e0:e1] = np.asarray(m, dtype=np.float32)
     return labels
+
+
+# ----------------------------------------------------------------------------------------------
+# a12: g_agent selection                     src/data/components/g_agent_builder.py:148-724
+# ----------------------------------------------------------------------------------------------
+GAGENT_PROB_EPS = np.float32(1e-6)  # g_agent_builder.py:20
+
+
+def node_softmax_logit(scores, heads, tails, num_nodes: int) -> np.ndarray:
+    """``_node_softmax_logit`` (g_agent_builder.py:594-626): logit of the mean of the softmax over edges
+    sharing the head and the softmax over edges sharing the tail, clamped to [1e-6, 1-1e-6]. fp32,
+    sums in ascending edge order (CPU ``scatter_add_``)."""
+    s = np.asarray(scores, dtype=np.float32)
+    if s.size == 0:
+        return s
+    h = np.asarray(heads, dtype=np.int64)
+    t = np.asarray(tails, dtype=np.int64)
+
+    def side(idx):
+        mx = np.full(num_nodes, -np.inf, dtype=np.float32)
+        np.maximum.at(mx, idx, s)
+        ex = np.exp(s - mx[idx]).astype(np.float32)
+        sm = np.zeros(num_nodes, dtype=np.float32)
+        np.add.at(sm, idx, ex)
+        return (ex / np.maximum(sm[idx], GAGENT_PROB_EPS)).astype(np.float32)
+
+    prob = ((side(h) + side(t)) * np.float32(0.5)).astype(np.float32)
+    prob = np.clip(prob, GAGENT_PROB_EPS, np.float32(1.0) - GAGENT_PROB_EPS).astype(np.float32)
+    return (np.log(prob) - np.log1p(-prob)).astype(np.float32)
+
+
+def gagent_select_topk(scores, edge_top_k: int) -> np.ndarray:
+    """``_select_topk_edges`` (g_agent_builder.py:640-652): every edge (index order) when E <= k, else the
+    first k of a stable descending argsort."""
+    s = np.asarray(scores, dtype=np.float32).reshape(-1)
+    if s.size <= edge_top_k:
+        return np.arange(s.size, dtype=np.int64)
+    return np.argsort(-s.astype(np.float64), kind="stable")[:edge_top_k].astype(np.int64)
+
+
+def gagent_start_edge_budget(deg, keep_ratio: float, min_edges: int, max_edges: Optional[int]) -> np.ndarray:
+    """k_s = min(deg, clamp(ceil(deg * ratio) in fp32, min_edges, max_edges)) (g_agent_builder.py:676-686)."""
+    deg = np.asarray(deg, dtype=np.int64)
+    k = np.ceil(deg.astype(np.float32) * np.float32(keep_ratio)).astype(np.int64)
+    if min_edges > 0:
+        k = np.maximum(k, min_edges)
+    if max_edges is not None:
+        k = np.zeros_like(k) if max_edges == 0 else np.minimum(k, max_edges)
+    return np.minimum(k, deg)
+
+
+def gagent_select_start_edges(heads, tails, scores, start_nodes, num_nodes: int, keep_ratio: float = 0.25,
+                              min_edges: int = 1, max_edges: Optional[int] = None) -> np.ndarray:
+    """``_select_start_edges`` (g_agent_builder.py:654-724): for every unique start node the k_s best incident
+    entries, the incident list being (edges with head == s, in edge order) then (edges with tail == s),
+    ranked by a stable descending sort; returns the sorted unique edge ids."""
+    h = np.asarray(heads, dtype=np.int64).reshape(-1)
+    t = np.asarray(tails, dtype=np.int64).reshape(-1)
+    s = np.asarray(scores, dtype=np.float32).reshape(-1)
+    starts = np.unique(np.asarray(start_nodes, dtype=np.int64))
+    if starts.size == 0 or s.size == 0:
+        return np.empty(0, dtype=np.int64)
+    deg = np.bincount(h, minlength=num_nodes) + np.bincount(t, minlength=num_nodes)
+    budget = gagent_start_edge_budget(deg[starts], keep_ratio, min_edges, max_edges)
+    picked: List[int] = []
+    for node, k_s in zip(starts.tolist(), budget.tolist()):
+        if k_s <= 0:
+            continue
+        inc_edges = np.concatenate([np.nonzero(h == node)[0], np.nonzero(t == node)[0]])
+        order = np.argsort(-s[inc_edges].astype(np.float64), kind="stable")[:k_s]
+        picked.extend(inc_edges[order].tolist())
+    return np.unique(np.asarray(picked, dtype=np.int64))
+
+
+def gagent_build_sample(*, heads, tails, relations, labels, scores, node_global_ids, node_embedding_ids,
+                        start_entity_ids, answer_entity_ids, edge_top_k: int = 50, score_mode: str = "node_softmax",
+                        start_keep_ratio: float = 0.25, start_min_edges: int = 1,
+                        start_max_edges: Optional[int] = None, allow_empty_answer: bool = False,
+                        selection_scores=None):
+    """``GAgentBuilder._build_and_add_sample`` steps A, C, D (g_agent_builder.py:236-470) for one question:
+    selection on the normalised scores, union with the start edges, (h, r, t) dedup in first-seen order
+    with max raw score / label, re-indexing on the sorted unique entity ids, re-normalised scores, start /
+    answer locals. ``heads`` / ``tails`` are question-local node indices; ``scores`` are the calibrated
+    logits; ``selection_scores`` (tests only) replaces the normalised scores of step A so that a selection can
+    be checked bit-exactly on scores computed elsewhere. Returns ``None`` where the reference drops the sample, else a dict of arrays."""
+    h = np.asarray(heads, dtype=np.int64)
+    t = np.asarray(tails, dtype=np.int64)
+    r = np.asarray(relations, dtype=np.int64)
+    raw = np.asarray(scores, dtype=np.float32)
+    lab = np.asarray(labels, dtype=np.float32)
+    gids = np.asarray(node_global_ids, dtype=np.int64)
+    emb = np.asarray(node_embedding_ids, dtype=np.int64)
+    starts_e = np.asarray(start_entity_ids, dtype=np.int64).reshape(-1)
+    answers_e = np.asarray(answer_entity_ids, dtype=np.int64).reshape(-1)
+    N = int(gids.size)
+    if h.size == 0:
+        return None
+    if start_max_edges is None:
+        start_max_edges = edge_top_k  # GAgentSettings.__post_init__, g_agent_builder.py:71-72
+    norm = (lambda s_, h_, t_, n_: s_) if score_mode == "logits" else node_softmax_logit
+    start_locals = np.nonzero(np.isin(gids, starts_e))[0]
+    if start_locals.size == 0:
+        raise ValueError("Start entities missing from retrieval graph")
+    sel_scores = norm(raw, h, t, N) if selection_scores is None else np.asarray(selection_scores, dtype=np.float32)
+    top = gagent_select_topk(sel_scores, edge_top_k)
+    st = gagent_select_start_edges(h, t, sel_scores, start_locals, N, start_keep_ratio, start_min_edges,
+                                   start_max_edges)
+    env = np.unique(np.concatenate([top, st]))
+    # (h, r, t) dedup, first-seen order, max aggregation (g_agent_builder.py:338-354)
+    agg: Dict[Tuple[int, int, int], List[float]] = {}
+    for e in env.tolist():
+        key = (int(gids[h[e]]), int(r[e]), int(gids[t[e]]))
+        cur = agg.get(key)
+        if cur is None:
+            agg[key] = [float(raw[e]), float(lab[e])]
+        else:
+            cur[0] = max(cur[0], float(raw[e]))
+            cur[1] = max(cur[1], float(lab[e]))
+    triples = list(agg.keys())
+    eh = np.asarray([k[0] for k in triples], dtype=np.int64)
+    er = np.asarray([k[1] for k in triples], dtype=np.int64)
+    et = np.asarray([k[2] for k in triples], dtype=np.int64)
+    es = np.asarray([agg[k][0] for k in triples], dtype=np.float32)
+    el = np.asarray([agg[k][1] for k in triples], dtype=np.float32)
+    node_entity_ids = np.unique(np.concatenate([eh, et]))
+    lookup = {int(g): int(e_) for g, e_ in zip(gids.tolist(), emb.tolist())}
+    node_emb = np.asarray([lookup[int(g)] for g in node_entity_ids.tolist()], dtype=np.int64)
+    hl = np.searchsorted(node_entity_ids, eh).astype(np.int64)
+    tl = np.searchsorted(node_entity_ids, et).astype(np.int64)
+    es_norm = norm(es, hl, tl, int(node_entity_ids.size))
+
+    def ordered_locals(ids):
+        out, seen = [], set()
+        for g in ids.tolist():
+            p = int(np.searchsorted(node_entity_ids, g))
+            if p < node_entity_ids.size and node_entity_ids[p] == g and p not in seen:
+                seen.add(p)
+                out.append(p)
+        return np.asarray(out, dtype=np.int64)
+
+    start_node_locals = ordered_locals(starts_e)
+    if start_node_locals.size == 0:
+        return None
+    seen_a, ordered_a = set(), []
+    for a in answers_e.tolist():
+        if a not in seen_a:
+            seen_a.add(a)
+            ordered_a.append(a)
+    answers_u = np.asarray(ordered_a, dtype=np.int64)
+    # the reference does not dedup answer locals beyond the id dedup (g_agent_builder.py:423-428)
+    answer_node_locals = ordered_locals(answers_u)
+    dummy = answer_node_locals.size == 0
+    if dummy:
+        if not allow_empty_answer:
+            return None
+        el = np.zeros_like(el)
+    return {
+        "env_edge_ids": env, "edge_heads_global": eh, "edge_relations": er, "edge_tails_global": et,
+        "edge_scores": es_norm, "edge_labels": el, "edge_head_locals": hl, "edge_tail_locals": tl,
+        "node_entity_ids": node_entity_ids, "node_embedding_ids": node_emb,
+        "start_node_locals": start_node_locals, "answer_entity_ids": answers_u,
+        "answer_node_locals": answer_node_locals, "is_dummy_agent": dummy,
+        "is_answer_reachable": not dummy,
+    }

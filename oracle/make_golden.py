@@ -210,6 +210,131 @@ def golden_bfs(brp):
     print("bfs ok", n_cases, hc)
 
 
+def gagent_inputs(seed: int):
+    """Four hand-shaped questions for the g_agent selection: E <= k, ties (scores quantised to 0.25),
+    duplicate (h, r, t) triples, self loops, a single-edge question, absent start / answer ids."""
+    rng = np.random.default_rng(seed)
+    sizes = [(30, 14), (220, 60), (640, 150), (1, 2)]
+    ei, rel, lab, gid, emb, ptr, eptr = [], [], [], [], [], [0], [0]
+    starts, answers = [], []
+    for qi, (e, n) in enumerate(sizes):
+        n0 = ptr[-1]
+        h = rng.integers(0, n, e)
+        t = rng.integers(0, n, e)
+        if e > 1:
+            hub = int(rng.integers(0, n))
+            h[: e // 4] = hub  # a hub start node with many incident edges
+            t[e // 4: e // 3] = hub
+            t[0] = h[0]  # self loop on the hub
+        r = rng.integers(0, 6, e)
+        if e > 20:  # duplicate triples
+            for j in range(5):
+                src = int(rng.integers(0, e))
+                dst = int(rng.integers(0, e))
+                h[dst], t[dst], r[dst] = h[src], t[src], r[src]
+        ei.append(np.stack([h + n0, t + n0]))
+        rel.append(r)
+        lab.append((rng.random(e) < 0.1).astype(np.float32))
+        g = rng.permutation(5000)[:n].astype(np.int64) + 1000 * qi
+        gid.append(g)
+        emb.append(np.where(rng.random(n) < 0.3, 0, rng.integers(1, 900, n)).astype(np.int64))
+        ptr.append(n0 + n)
+        eptr.append(eptr[-1] + e)
+        st = [int(g[hub])] if e > 1 else [int(g[0])]
+        if qi == 2:
+            st = [int(g[int(h[7])]), 999999, int(g[hub]), int(g[hub])]
+        starts.append(st)
+        an = [int(g[int(t[e // 2])]), 888888, int(g[int(t[e // 2])])] if qi != 1 else [777777]
+        answers.append(an)
+    E = eptr[-1]
+    logits = (np.round(rng.standard_normal(E) * 2.0 * 4) / 4).astype(np.float32)
+    return dict(edge_index=np.concatenate(ei, axis=1).astype(np.int64), edge_attr=np.concatenate(rel).astype(np.int64),
+                labels=np.concatenate(lab), node_global_ids=np.concatenate(gid), node_embedding_ids=np.concatenate(emb),
+                ptr=np.asarray(ptr, np.int64), edge_ptr=np.asarray(eptr, np.int64), logits=logits,
+                starts=starts, answers=answers)
+
+
+GAGENT_SETTINGS = [
+    dict(tag="default", edge_top_k=50),
+    dict(tag="logits_k20", edge_top_k=20, score_mode="logits", start_keep_ratio=0.5, start_min_edges=2,
+         start_max_edges=5),
+    dict(tag="dummy_ok", edge_top_k=50, allow_empty_answer=True, score_temperature=2.0, score_bias=0.5),
+    dict(tag="no_start_edges", edge_top_k=64, start_max_edges=0, start_min_edges=0),
+]
+
+GAGENT_FIELDS = ["edge_relations", "edge_scores", "edge_labels", "edge_head_locals", "edge_tail_locals",
+                 "node_entity_ids", "node_embedding_ids", "start_node_locals", "answer_entity_ids",
+                 "answer_node_locals"]
+
+
+def golden_gagent():
+    """Runs the reference ``GAgentBuilder.process_batch`` (g_agent_builder.py:148-236) with an in-memory
+    sample store; also pins ``_node_softmax_logit`` / ``_select_topk_edges`` / ``_select_start_edges``."""
+    import sys as _sys
+
+    import torch_geometric
+
+    if not hasattr(torch_geometric, "data"):  # g_agent_builder.py:10 only needs the names
+        d = types.ModuleType("torch_geometric.data")
+        d.Data = type("Data", (), {})
+        d.Batch = type("Batch", (d.Data,), {})
+        d.Dataset = type("Dataset", (), {})
+        torch_geometric.data = d
+        _sys.modules["torch_geometric.data"] = d
+    from src.data.components.g_agent_builder import GAgentBuilder, GAgentSettings
+
+    inp = gagent_inputs(23)
+    B = len(inp["ptr"]) - 1
+    store = {k: v for k, v in inp.items() if k not in ("starts", "answers")}
+    store["start_ptr"] = np.cumsum([0] + [len(s) for s in inp["starts"]]).astype(np.int64)
+    store["start_entity_ids"] = np.asarray([x for s in inp["starts"] for x in s], np.int64)
+    store["answer_ptr"] = np.cumsum([0] + [len(s) for s in inp["answers"]]).astype(np.int64)
+    store["answer_entity_ids"] = np.asarray([x for s in inp["answers"] for x in s], np.int64)
+
+    class Store:
+        def load_sample(self, sid):
+            i = int(sid[1:])
+            return {"question_emb": np.zeros(4, np.float32), "question": f"question {i}",
+                    "seed_entity_ids": inp["starts"][i], "answer_entity_ids": inp["answers"][i]}
+
+    batch = types.SimpleNamespace(
+        ptr=torch.from_numpy(inp["ptr"]), edge_index=torch.from_numpy(inp["edge_index"]),
+        edge_attr=torch.from_numpy(inp["edge_attr"]), labels=torch.from_numpy(inp["labels"]),
+        node_global_ids=torch.from_numpy(inp["node_global_ids"]),
+        node_embedding_ids=torch.from_numpy(inp["node_embedding_ids"]), sample_id=[f"s{i}" for i in range(B)])
+    qid = np.repeat(np.arange(B), np.diff(inp["edge_ptr"]))
+    out = types.SimpleNamespace(logits=torch.from_numpy(inp["logits"]), query_ids=torch.from_numpy(qid))
+    for cfg in GAGENT_SETTINGS:
+        kw = {k: v for k, v in cfg.items() if k != "tag"}
+        builder = GAgentBuilder(GAgentSettings(**kw), embedding_store=Store())
+        builder.process_batch(batch, out)
+        kept = np.zeros(B, dtype=bool)
+        for smp in builder.samples:
+            i = int(smp.sample_id[1:])
+            kept[i] = True
+            for f in GAGENT_FIELDS:
+                store[f"{cfg['tag']}_q{i}_{f}"] = getattr(smp, f).numpy()
+            store[f"{cfg['tag']}_q{i}_is_dummy_agent"] = np.array(bool(smp.is_dummy_agent))
+        store[f"{cfg['tag']}_kept"] = kept
+        store[f"{cfg['tag']}_retrieval_failed"] = np.array(builder.stats["retrieval_failed"])
+    # the three static selection helpers on question 2
+    e0, e1 = int(inp["edge_ptr"][2]), int(inp["edge_ptr"][3])
+    n0, n1 = int(inp["ptr"][2]), int(inp["ptr"][3])
+    h = torch.from_numpy(inp["edge_index"][0, e0:e1] - n0)
+    t = torch.from_numpy(inp["edge_index"][1, e0:e1] - n0)
+    sc = torch.from_numpy(inp["logits"][e0:e1])
+    ns = GAgentBuilder._node_softmax_logit(edge_scores=sc, edge_head_locals=h, edge_tail_locals=t, num_nodes=n1 - n0)
+    store["helper_node_softmax"] = ns.numpy()
+    store["helper_topk"] = GAgentBuilder._select_topk_edges(edge_scores=sc, edge_top_k=37).numpy()
+    starts = torch.tensor([int(h[0]), int(h[7]), int(h[0])])
+    store["helper_starts"] = starts.numpy()
+    store["helper_start_edges"] = GAgentBuilder._select_start_edges(
+        heads=h, tails=t, edge_scores=sc, start_node_locals=starts, num_nodes=n1 - n0, start_keep_ratio=0.25,
+        start_min_edges=1, start_max_edges=40).numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "gagent.npz"), **store)
+    print("gagent ok", {c["tag"]: store[f"{c['tag']}_kept"].tolist() for c in GAGENT_SETTINGS})
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     Retriever, ref_ceb, brp, kind = load_reference()
@@ -218,6 +343,7 @@ def main():
     golden_bfs(brp)
     golden_dde(Retriever)
     golden_scorer(Retriever)
+    golden_gagent()
     with open(os.path.join(GOLDEN, "PROVENANCE.txt"), "w", encoding="utf-8") as f:
         f.write(
             "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"

@@ -120,3 +120,58 @@ def test_segmented_topk_matches_torch_topk_and_stable_argsort():
         order = torch.argsort(s, descending=True, stable=True)[:kt].numpy()  # g_agent_builder.py:651
         np.testing.assert_array_equal(idx[b, :kt], order)
         assert (idx[b, kt:] == -1).all()
+
+
+GAGENT_SETTINGS = {
+    "default": dict(edge_top_k=50),
+    "logits_k20": dict(edge_top_k=20, score_mode="logits", start_keep_ratio=0.5, start_min_edges=2, start_max_edges=5),
+    "dummy_ok": dict(edge_top_k=50, allow_empty_answer=True, score_temperature=2.0, score_bias=0.5),
+    "no_start_edges": dict(edge_top_k=64, start_max_edges=0, start_min_edges=0),
+}
+GAGENT_INT_FIELDS = ["edge_relations", "edge_head_locals", "edge_tail_locals", "node_entity_ids", "node_embedding_ids",
+                     "start_node_locals", "answer_entity_ids", "answer_node_locals"]
+
+
+def gagent_question(g, i):
+    e0, e1 = int(g["edge_ptr"][i]), int(g["edge_ptr"][i + 1])
+    n0, n1 = int(g["ptr"][i]), int(g["ptr"][i + 1])
+    return dict(
+        heads=g["edge_index"][0, e0:e1] - n0, tails=g["edge_index"][1, e0:e1] - n0, relations=g["edge_attr"][e0:e1],
+        labels=g["labels"][e0:e1], scores=g["logits"][e0:e1], node_global_ids=g["node_global_ids"][n0:n1],
+        node_embedding_ids=g["node_embedding_ids"][n0:n1],
+        start_entity_ids=g["start_entity_ids"][int(g["start_ptr"][i]):int(g["start_ptr"][i + 1])],
+        answer_entity_ids=g["answer_entity_ids"][int(g["answer_ptr"][i]):int(g["answer_ptr"][i + 1])])
+
+
+def test_gagent_helpers_match_reference(golden_dir):
+    g = _load(golden_dir, "gagent.npz")
+    q = gagent_question(g, 2)
+    n = len(q["node_global_ids"])
+    ns = orc.node_softmax_logit(q["scores"], q["heads"], q["tails"], n)
+    np.testing.assert_allclose(ns, g["helper_node_softmax"], atol=2e-5, rtol=1e-5)
+    assert np.array_equal(orc.gagent_select_topk(q["scores"], 37), g["helper_topk"])
+    st = orc.gagent_select_start_edges(q["heads"], q["tails"], q["scores"], g["helper_starts"], n, 0.25, 1, 40)
+    assert np.array_equal(st, g["helper_start_edges"])
+
+
+@pytest.mark.parametrize("tag", list(GAGENT_SETTINGS))
+def test_gagent_samples_match_reference(golden_dir, tag):
+    g = _load(golden_dir, "gagent.npz")
+    cfg = dict(GAGENT_SETTINGS[tag])
+    temp, bias = cfg.pop("score_temperature", 1.0), cfg.pop("score_bias", 0.0)
+    failed = 0
+    for i in range(len(g["ptr"]) - 1):
+        q = gagent_question(g, i)
+        if temp != 1.0 or bias != 0.0:  # g_agent_builder.py:164-165
+            q["scores"] = (torch.from_numpy(q["scores"]) / float(temp) + float(bias)).numpy()
+        out = orc.gagent_build_sample(**q, **cfg)
+        assert (out is not None) == bool(g[f"{tag}_kept"][i])
+        if out is None:
+            failed += 1
+            continue
+        for f in GAGENT_INT_FIELDS:
+            assert np.array_equal(out[f], g[f"{tag}_q{i}_{f}"]), (tag, i, f)
+        np.testing.assert_allclose(out["edge_scores"], g[f"{tag}_q{i}_edge_scores"], atol=2e-5, rtol=1e-5)
+        assert np.array_equal(out["edge_labels"], g[f"{tag}_q{i}_edge_labels"])
+        assert bool(out["is_dummy_agent"]) == bool(g[f"{tag}_q{i}_is_dummy_agent"])
+    assert failed == int(g[f"{tag}_retrieval_failed"])
