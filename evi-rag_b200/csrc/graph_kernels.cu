@@ -364,6 +364,146 @@ shortest_pairs_kernel(const int* __restrict__ head, const int* __restrict__ tail
   if (threadIdx.x == 0) pair_count[p] = total, pair_len[p] = dsa;
 }
 
+// ---------------------------------------------------------------------------------------------
+// a16: deterministic single shortest path (_shortest_path_single, build_retrieval_pipeline.py:453-530).
+// The reference runs a FIFO BFS over adjacency lists sorted by (neighbour, edge idx) from the ascending
+// unique sources, so parent[v] is the earliest-queued neighbour one level up and parent_edge[v] the smallest
+// edge idx between them; the queue position of v is the rank of (queue position of parent, v) inside its level.
+// Level-synchronous restatement, one CTA per job: a sweep over the job's edges does
+// atomicMin(key[v], queue_pos[u] << 32 | edge idx) for frontier u; the new level is then ranked by sorting
+// (parent queue position, node id) (bitonic, in the job's scratch). Level 0 ranks are the ordered compaction of
+// the source ids. The path is read back from the best target (min dist, then min id) through key[].
+// ---------------------------------------------------------------------------------------------
+constexpr int kSpsThreads = 256;
+
+__global__ void __launch_bounds__(kSpsThreads)
+shortest_path_single_kernel(const int* __restrict__ head, const int* __restrict__ tail,
+                            const long long* __restrict__ job_edge_begin, const long long* __restrict__ job_edge_end,
+                            const int* __restrict__ job_node_begin, const int* __restrict__ job_node_end,
+                            const int* __restrict__ job_src_ptr, const int* __restrict__ sources,
+                            const int* __restrict__ job_tgt_ptr, const int* __restrict__ targets, int ids_are_global,
+                            const long long* __restrict__ job_sort_off, int* __restrict__ dist_ws,
+                            int* __restrict__ order_ws, unsigned long long* __restrict__ key_ws,
+                            unsigned long long* __restrict__ sort_ws, int max_len, int* __restrict__ path_len,
+                            int* __restrict__ path_edges, int* __restrict__ path_nodes) {
+  __shared__ int counter;
+  __shared__ int warp_tot[kSpsThreads / 32];
+  const int job = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int n0 = job_node_begin[job], nn = job_node_end[job] - n0;
+  const long long e0 = job_edge_begin[job];
+  const int ne = static_cast<int>(job_edge_end[job] - e0);
+  int* d = dist_ws + n0;
+  int* ord = order_ws + n0;
+  unsigned long long* key = key_ws + n0;
+  unsigned long long* sb = sort_ws + job_sort_off[job];
+  const int* hq = head + e0;
+  const int* tq = tail + e0;
+  const int base_id = ids_are_global ? n0 : 0;
+  for (int i = tid; i < nn; i += kSpsThreads) d[i] = -1, key[i] = ~0ull;
+  __syncthreads();
+  for (int i = job_src_ptr[job] + tid; i < job_src_ptr[job + 1]; i += kSpsThreads) {
+    const int sidx = sources[i] - base_id;
+    if (sidx >= 0 && sidx < nn) d[sidx] = 0;
+  }
+  __syncthreads();
+  // queue positions of level 0 = rank of the source ids (sorted(set(sources)), :481)
+  int running = 0;
+  for (int b0 = 0; b0 < nn; b0 += kSpsThreads) {
+    const int i = b0 + tid;
+    const int on = (i < nn && d[i] == 0) ? 1 : 0;
+    int incl = on;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    if (lane == 31) warp_tot[w] = incl;
+    __syncthreads();
+    int off = 0, tot = 0;
+#pragma unroll
+    for (int j = 0; j < kSpsThreads / 32; ++j) {
+      if (j < w) off += warp_tot[j];
+      tot += warp_tot[j];
+    }
+    if (on) ord[i] = running + off + incl - 1;
+    running += tot;
+    __syncthreads();
+  }
+  const int num_src = running;
+  for (int level = 0; num_src > 0; ++level) {
+    for (int e = tid; e < ne; e += kSpsThreads) {
+      const int u = hq[e] - n0, v = tq[e] - n0;
+      if (static_cast<unsigned>(u) >= static_cast<unsigned>(nn) || static_cast<unsigned>(v) >= static_cast<unsigned>(nn) ||
+          u == v)
+        continue;  // out-of-range endpoints are dropped (:466); a self loop never discovers a node
+      const int du = d[u], dv = d[v];
+      if (du == level && (dv == -1 || dv == level + 1)) {
+        atomicMin(&key[v], (static_cast<unsigned long long>(ord[u]) << 32) | static_cast<unsigned>(e));
+        if (dv == -1) d[v] = level + 1;
+      }
+      if (dv == level && (du == -1 || du == level + 1)) {
+        atomicMin(&key[u], (static_cast<unsigned long long>(ord[v]) << 32) | static_cast<unsigned>(e));
+        if (du == -1) d[u] = level + 1;
+      }
+    }
+    if (tid == 0) counter = 0;
+    __syncthreads();
+    for (int i = tid; i < nn; i += kSpsThreads)
+      if (d[i] == level + 1) sb[atomicAdd(&counter, 1)] = (key[i] & 0xFFFFFFFF00000000ull) | static_cast<unsigned>(i);
+    __syncthreads();
+    const int F = counter;
+    if (F == 0) break;
+    int P = 1;
+    while (P < F) P <<= 1;
+    for (int i = F + tid; i < P; i += kSpsThreads) sb[i] = ~0ull;
+    __syncthreads();
+    for (int size = 2; size <= P; size <<= 1) {
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        for (int i = tid; i < P; i += kSpsThreads) {
+          const int j = i ^ stride;
+          if (j > i) {
+            const unsigned long long x = sb[i], y = sb[j];
+            const bool ascending = (i & size) == 0;
+            if (ascending ? (x > y) : (x < y)) sb[i] = y, sb[j] = x;
+          }
+        }
+        __syncthreads();
+      }
+    }
+    for (int r = tid; r < F; r += kSpsThreads) ord[static_cast<int>(sb[r] & 0xFFFFFFFFull)] = r;
+    __syncthreads();
+  }
+  if (tid != 0) return;
+  int best = -1, best_d = 0;
+  if (num_src > 0)
+    for (int i = job_tgt_ptr[job]; i < job_tgt_ptr[job + 1]; ++i) {
+      const int t = targets[i] - base_id;
+      if (t < 0 || t >= nn || d[t] < 0) continue;
+      if (best < 0 || d[t] < best_d || (d[t] == best_d && t < best)) best = t, best_d = d[t];
+    }
+  if (best < 0) {
+    path_len[job] = -1;
+    return;
+  }
+  if (best_d > max_len) {
+    path_len[job] = -2;
+    return;
+  }
+  int* pe = path_edges + static_cast<size_t>(job) * max_len;
+  int* pn = path_nodes + static_cast<size_t>(job) * (max_len + 1);
+  int cur = best;
+  pn[best_d] = cur;
+  for (int i = best_d - 1; i >= 0; --i) {
+    const int e = static_cast<int>(key[cur] & 0xFFFFFFFFull);
+    const int u = hq[e] - n0, v = tq[e] - n0;
+    const int prev = u == cur ? v : u;
+    pe[i] = e;
+    pn[i] = prev;
+    cur = prev;
+  }
+  path_len[job] = best_d;
+}
+
 }  // namespace evi
 
 using namespace evi;
@@ -478,6 +618,24 @@ int evi_shortest_path_pairs(const int* head32, const int* tail32, int num_pairs,
                                                        pair_node_begin, pair_num_nodes, pair_ds_off, pair_da_off,
                                                        pair_answer_local, pair_out_off, dist, directed, mask,
                                                        pair_member, pair_count, pair_len);
+  return check_launch();
+}
+
+int evi_shortest_path_single(const int* head32, const int* tail32, int num_jobs, const long long* job_edge_begin,
+                             const long long* job_edge_end, const int* job_node_begin, const int* job_node_end,
+                             const int* job_src_ptr, const int* sources, const int* job_tgt_ptr, const int* targets,
+                             int ids_are_global, const long long* job_sort_off, int* dist_ws, int* order_ws,
+                             unsigned long long* key_ws, unsigned long long* sort_ws, int max_len, int* path_len,
+                             int* path_edges, int* path_nodes, cudaStream_t stream) {
+  if (num_jobs <= 0) return kOk;
+  if (max_len < 0 || job_edge_begin == nullptr || job_node_begin == nullptr || job_src_ptr == nullptr ||
+      job_tgt_ptr == nullptr || job_sort_off == nullptr || dist_ws == nullptr || order_ws == nullptr ||
+      key_ws == nullptr || sort_ws == nullptr || path_len == nullptr || path_edges == nullptr || path_nodes == nullptr)
+    return kErrInvalidArg;
+  shortest_path_single_kernel<<<num_jobs, kSpsThreads, 0, stream>>>(
+      head32, tail32, job_edge_begin, job_edge_end, job_node_begin, job_node_end, job_src_ptr, sources, job_tgt_ptr,
+      targets, ids_are_global, job_sort_off, dist_ws, order_ws, key_ws, sort_ws, max_len, path_len, path_edges,
+      path_nodes);
   return check_launch();
 }
 

@@ -407,3 +407,89 @@ def has_connectivity(graph: Sequence[Tuple[str, str, str]], seeds: Sequence[str]
         raise ValueError(f"Unsupported path_mode: {path_mode}. Expected one of {_PATH_MODES}.")
     dist = bfs_dist_edges(len(node_index), es, ed, s_ids, directed=(path_mode == "qa_directed"))
     return any(dist[a] >= 0 for a in a_ids)
+
+
+# ------------------------------------------------------------------------------------------
+# a16: deterministic single shortest path
+# ------------------------------------------------------------------------------------------
+def _next_pow2(x: np.ndarray) -> np.ndarray:
+    x = np.maximum(np.asarray(x, dtype=np.int64), 1)
+    return (1 << np.ceil(np.log2(x)).astype(np.int64)).astype(np.int64)
+
+
+def shortest_path_single_jobs(head32: torch.Tensor, tail32: torch.Tensor, edge_begin, edge_end, node_begin, node_end,
+                              sources, src_ptr, targets, tgt_ptr, *, ids_are_global: bool = True,
+                              max_len: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+    """``evi_shortest_path_single`` for a list of jobs (one per question graph). Returns host arrays
+    ``path_len [J]`` (-1: no path), ``path_edges [J, max_len]`` (job-local edge ids) and ``path_nodes [J, max_len+1]``
+    (job-local node ids, source first)."""
+    L = _lib.load()
+    dev = head32.device
+    node_begin = np.asarray(node_begin, dtype=np.int64)
+    node_end = np.asarray(node_end, dtype=np.int64)
+    J = int(node_begin.shape[0])
+    nn = node_end - node_begin
+    if max_len is None:
+        max_len = int(max(1, nn.max(initial=1)))
+    pow2 = _next_pow2(nn)
+    sort_off = np.zeros(J, dtype=np.int64)
+    np.cumsum(pow2[:-1], out=sort_off[1:])
+    n_total = int(max(1, node_end.max(initial=1)))
+    up = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).to(dev)
+    nz = lambda a: a if len(a) else np.zeros(1)
+    d_eb, d_ee = up(edge_begin, np.int64), up(edge_end, np.int64)
+    d_nb, d_ne = up(node_begin, np.int32), up(node_end, np.int32)
+    d_sp, d_src = up(src_ptr, np.int32), up(nz(np.asarray(sources, dtype=np.int64).clip(-1, 2**31 - 2)), np.int32)
+    d_tp, d_tgt = up(tgt_ptr, np.int32), up(nz(np.asarray(targets, dtype=np.int64).clip(-1, 2**31 - 2)), np.int32)
+    d_so = up(sort_off, np.int64)
+    dist = torch.empty(n_total, dtype=torch.int32, device=dev)
+    order = torch.empty(n_total, dtype=torch.int32, device=dev)
+    key = torch.empty(n_total, dtype=torch.int64, device=dev)
+    sortbuf = torch.empty(int(max(1, pow2.sum())), dtype=torch.int64, device=dev)
+    plen = torch.empty(J, dtype=torch.int32, device=dev)
+    pedges = torch.zeros((J, max(1, max_len)), dtype=torch.int32, device=dev)
+    pnodes = torch.zeros((J, max_len + 1), dtype=torch.int32, device=dev)
+    st = L.evi_shortest_path_single(
+        head32.data_ptr(), tail32.data_ptr(), J, d_eb.data_ptr(), d_ee.data_ptr(), d_nb.data_ptr(), d_ne.data_ptr(),
+        d_sp.data_ptr(), d_src.data_ptr(), d_tp.data_ptr(), d_tgt.data_ptr(), int(ids_are_global), d_so.data_ptr(),
+        dist.data_ptr(), order.data_ptr(), key.data_ptr(), sortbuf.data_ptr(), int(max_len), plen.data_ptr(),
+        pedges.data_ptr(), pnodes.data_ptr(), _lib.stream_handle())
+    _lib.check(st, "evi_shortest_path_single")
+    plen_h = plen.cpu().numpy()
+    if (plen_h == -2).any():
+        raise RuntimeError("shortest path longer than max_len; raise max_len")
+    return plen_h, pedges.cpu().numpy(), pnodes.cpu().numpy()
+
+
+def batched_shortest_path_single(gb: GraphBatch, seeds: np.ndarray, seed_ptr: np.ndarray, answers: np.ndarray,
+                                 answer_ptr: np.ndarray, *, max_len: Optional[int] = None):
+    """One deterministic shortest path per question of a batch (seeds / answers are batch-global node ids)."""
+    ptr = gb.ptr_host
+    ep = gb.edge_ptr_np()
+    return shortest_path_single_jobs(gb.head32, gb.tail32, ep[:-1], ep[1:], ptr[:-1], ptr[1:], seeds, seed_ptr, answers,
+                                     answer_ptr, ids_are_global=True, max_len=max_len)
+
+
+def _shortest_path_single(num_nodes: int, edge_src: Sequence[int], edge_dst: Sequence[int], sources: Sequence[int],
+                          targets: Sequence[int]) -> Tuple[List[int], List[int]]:
+    """Reference signature and return convention (build_retrieval_pipeline.py:453-530): ``(edges, nodes)``,
+    ``([], [])`` when there is no path, ``([], [t])`` when the best target is itself a source."""
+    if not len(sources) or not len(targets) or num_nodes <= 0:
+        return [], []
+    src, dst = _single_graph_batch(num_nodes, edge_src, edge_dst)
+    E = int(src.numel())
+    if E == 0:
+        src = torch.zeros(1, dtype=torch.int32, device=src.device)
+        dst = torch.zeros(1, dtype=torch.int32, device=src.device)
+    plen, pe, pn = shortest_path_single_jobs(src, dst, [0], [E], [0], [num_nodes], [int(s) for s in sources],
+                                             [0, len(sources)], [int(t) for t in targets], [0, len(targets)],
+                                             ids_are_global=False)
+    n = int(plen[0])
+    if n < 0:
+        return [], []
+    return pe[0, :n].tolist(), pn[0, :n + 1].tolist()
+
+
+def shortest_path_edge_indices_undirected(num_nodes, edge_src, edge_dst, seeds, answers):
+    """build_retrieval_pipeline.py:935-943."""
+    return _shortest_path_single(num_nodes, edge_src, edge_dst, seeds, answers)

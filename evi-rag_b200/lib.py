@@ -73,6 +73,7 @@ PROTOTYPES = {
     "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "evi_bfs_edge_sweep": (_i, [_vp, _vp, _i] + [_vp] * 7 + [_i, _i, _i, _vp, _vp]),
     "evi_shortest_path_pairs": (_i, [_vp, _vp, _i] + [_vp] * 9 + [_i] + [_vp] * 4 + [_vp]),
+    "evi_shortest_path_single": (_i, [_vp, _vp, _i] + [_vp] * 8 + [_i] + [_vp] * 5 + [_i] + [_vp] * 3 + [_vp]),
     "evi_gather_rows": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp]),
     "evi_struct_project": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_convert_f32": (_i, [_vp, _vp, _ll, _i, _vp]),
@@ -100,6 +101,7 @@ _KERNELS_PER_CALL = {
     "evi_bfs_multi_source": lambda a: 1,
     "evi_bfs_edge_sweep": lambda a: 1,
     "evi_shortest_path_pairs": lambda a: 1,
+    "evi_shortest_path_single": lambda a: 1,
     "evi_gather_rows": lambda a: 1,
     "evi_struct_project": lambda a: 1,
     "evi_convert_f32": lambda a: 1,

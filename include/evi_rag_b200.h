@@ -240,6 +240,20 @@ int evi_topk_metrics(const int* indices, const int* counts, const long long* edg
                      float* pos, unsigned char* reach, unsigned char* reach_valid, float* margin,
                      unsigned char* margin_valid, cudaStream_t stream);
 
+/* _shortest_path_single — scripts/build_retrieval_pipeline.py:453-530 (exported there as
+ * shortest_path_edge_indices_undirected, :935-943): the deterministic single shortest path from the sources to
+ * the best target (min distance, then min id), undirected, parents chosen as the reference's FIFO BFS over
+ * (neighbour, edge idx)-sorted adjacency does. One CTA per job; jobs laid out like evi_bfs_edge_sweep.
+ * Scratch: dist_ws / order_ws [N] i32, key_ws [N] u64, sort_ws [sum of next_pow2(nodes of job)] u64 at
+ * job_sort_off. Outputs: path_len [jobs] (edges on the path; -1 no path, -2 longer than max_len), path_edges
+ * [jobs, max_len] job-local edge ids, path_nodes [jobs, max_len + 1] job-local node ids, source first. */
+int evi_shortest_path_single(const int* head32, const int* tail32, int num_jobs, const long long* job_edge_begin,
+                             const long long* job_edge_end, const int* job_node_begin, const int* job_node_end,
+                             const int* job_src_ptr, const int* sources, const int* job_tgt_ptr, const int* targets,
+                             int ids_are_global, const long long* job_sort_off, int* dist_ws, int* order_ws,
+                             unsigned long long* key_ws, unsigned long long* sort_ws, int max_len, int* path_len,
+                             int* path_edges, int* path_nodes, cudaStream_t stream);
+
 /* ---- g_agent selection (src/data/components/g_agent_builder.py) --------------------------------------- */
 
 #define EVI_GAGENT_LOGITS 0        /* score_mode "logits" */

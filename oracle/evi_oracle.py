@@ -710,3 +710,51 @@ def gagent_build_sample(*, heads, tails, relations, labels, scores, node_global_
         "answer_node_locals": answer_node_locals, "is_dummy_agent": dummy,
         "is_answer_reachable": not dummy,
     }
+
+
+# ----------------------------------------------------------------------------------------------
+# a16: deterministic single shortest path          scripts/build_retrieval_pipeline.py:453-530
+# ----------------------------------------------------------------------------------------------
+def shortest_path_single(num_nodes: int, edge_src, edge_dst, sources, targets) -> Tuple[List[int], List[int]]:
+    """FIFO BFS from the ascending unique in-range sources over adjacency lists sorted by (neighbour, edge
+    idx); best target = min distance then min id; the path follows parent / parent_edge back to a source.
+    Returns ``(edges, nodes)``; ``([], [])`` without a path, ``([], [t])`` when the target is a source."""
+    if len(sources) == 0 or len(targets) == 0 or num_nodes <= 0:
+        return [], []
+    adj: List[List[Tuple[int, int]]] = [[] for _ in range(num_nodes)]
+    for idx, (u, v) in enumerate(zip(edge_src, edge_dst)):
+        u, v = int(u), int(v)
+        if 0 <= u < num_nodes and 0 <= v < num_nodes:
+            adj[u].append((v, idx))
+            if u != v:
+                adj[v].append((u, idx))
+    for a in adj:
+        a.sort()
+    src_u = sorted({int(s) for s in sources if 0 <= int(s) < num_nodes})
+    tgt_u = sorted({int(t) for t in targets if 0 <= int(t) < num_nodes})
+    if not src_u or not tgt_u:
+        return [], []
+    dist = [-1] * num_nodes
+    parent = [-1] * num_nodes
+    parent_edge = [-1] * num_nodes
+    q = deque()
+    for s in src_u:
+        dist[s] = 0
+        q.append(s)
+    while q:
+        cur = q.popleft()
+        for nb, e in adj[cur]:
+            if dist[nb] == -1:
+                dist[nb] = dist[cur] + 1
+                parent[nb], parent_edge[nb] = cur, e
+                q.append(nb)
+    reach = [(dist[t], t) for t in tgt_u if dist[t] >= 0]
+    if not reach:
+        return [], []
+    _, cur = min(reach)
+    nodes, edges = [cur], []
+    while dist[cur] != 0:
+        edges.append(parent_edge[cur])
+        cur = parent[cur]
+        nodes.append(cur)
+    return edges[::-1], nodes[::-1]

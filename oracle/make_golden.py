@@ -194,6 +194,9 @@ def golden_bfs(brp):
             store[f"{pre}_ids"] = np.array(ids, dtype=np.int64)
             store[f"{pre}_cnt"] = np.array(cnt, dtype=np.int64)
             store[f"{pre}_len"] = np.array(ln, dtype=np.int64)
+        sp_e, sp_n = brp._shortest_path_single(n, src.tolist(), dst.tolist(), sources, targets)
+        store[f"c{ci}_single_edges"] = np.array(sp_e, dtype=np.int64)
+        store[f"c{ci}_single_nodes"] = np.array(sp_n, dtype=np.int64)
         n_cases += 1
     store["num_cases"] = np.array(n_cases)
     # has_connectivity on string triples
@@ -335,6 +338,82 @@ def golden_gagent():
     print("gagent ok", {c["tag"]: store[f"{c['tag']}_kept"].tolist() for c in GAGENT_SETTINGS})
 
 
+def golden_writer():
+    """Runs the reference ``RetrieverTopKEdgeWriter`` (retriever_topk_edge_writer.py:68-349) through its predict
+    hooks on a small CPU batch and stores the artifact it writes plus the inputs. ``lightning`` is absent here;
+    only the ``BasePredictionWriter`` base-class name is needed, so a one-line stand-in is installed."""
+    import json
+    import sys as _sys
+    import tempfile
+
+    if "lightning" not in _sys.modules:
+        lt = types.ModuleType("lightning")
+        ltp = types.ModuleType("lightning.pytorch")
+        ltc = types.ModuleType("lightning.pytorch.callbacks")
+
+        class BasePredictionWriter:
+            def __init__(self, write_interval="batch"):
+                self.interval = write_interval
+
+        ltc.BasePredictionWriter = BasePredictionWriter
+        for name in ("LightningModule", "Trainer", "Callback"):  # names only (type hints in src/utils/logging_utils.py)
+            setattr(lt, name, type(name, (), {}))
+        lt.pytorch, ltp.callbacks = ltp, ltc
+        _sys.modules.update({"lightning": lt, "lightning.pytorch": ltp, "lightning.pytorch.callbacks": ltc})
+    # src/utils/logging_utils.py (home of infer_batch_size) imports these at module level and never uses them here
+    for mod_name, attrs in (("lightning_utilities", {}), ("lightning_utilities.core", {}),
+                            ("lightning_utilities.core.rank_zero", {"rank_zero_only": lambda f: f, "rank_prefixed_message": lambda m, r=None: m}),
+                            ("omegaconf", {"OmegaConf": type("OmegaConf", (), {}), "DictConfig": dict})):
+        if mod_name not in _sys.modules:
+            try:
+                __import__(mod_name)
+            except Exception:
+                m = types.ModuleType(mod_name)
+                m.__dict__.update(attrs)
+                _sys.modules[mod_name] = m
+    if "src.callbacks" not in _sys.modules:  # skip the package __init__ (it imports Lightning callbacks wholesale)
+        from oracle.ref_shims import REFERENCE_ROOT
+
+        pkg = types.ModuleType("src.callbacks")
+        pkg.__path__ = [os.path.join(REFERENCE_ROOT, "src", "callbacks")]
+        _sys.modules["src.callbacks"] = pkg
+    from src.callbacks.retriever_topk_edge_writer import RetrieverTopKEdgeWriter
+    from src.models.components.retriever import RetrieverOutput
+
+    spec = tiny_spec(4, 60, seed=41, num_relations=12, num_entities=200)
+    qb = generate_questions(spec, dim=8)
+    rng = np.random.default_rng(41)
+    E, B = qb.num_edges, qb.num_graphs
+    logits = rng.permutation(E).astype(np.float32) * 0.01 - 0.3 * E * 0.01  # distinct: torch.topk's tie order is unspecified
+    lf, lb = (rng.standard_normal(E)).astype(np.float32), (rng.standard_normal(E)).astype(np.float32)
+    labels = (rng.random(E) < 0.1).astype(np.float32)
+    answers = [qb.node_global_ids[qb.a_local_indices[qb.a_ptr[b]:qb.a_ptr[b + 1]]] for b in range(B)]
+    a_ptr = np.cumsum([0] + [len(a) for a in answers]).astype(np.int64)
+    batch = types.SimpleNamespace(
+        num_graphs=B, ptr=torch.from_numpy(qb.ptr), edge_index=torch.from_numpy(qb.edge_index),
+        edge_attr=torch.from_numpy(qb.edge_attr), labels=torch.from_numpy(labels),
+        node_global_ids=torch.from_numpy(qb.node_global_ids), answer_entity_ids=torch.from_numpy(np.concatenate(answers)),
+        answer_entity_ids_ptr=torch.from_numpy(a_ptr), sample_id=[f"q{i}" for i in range(B)],
+        question=[f"who is {i}?" for i in range(B)], _slice_dict={"edge_index": torch.from_numpy(qb.edge_ptr)})
+    qid = np.repeat(np.arange(B), np.diff(qb.edge_ptr))
+    out = RetrieverOutput(logits=torch.from_numpy(logits), query_ids=torch.from_numpy(qid), relation_ids=None,
+                          logits_fwd=torch.from_numpy(lf), logits_bwd=torch.from_numpy(lb))
+    with tempfile.TemporaryDirectory() as tmp:
+        w = RetrieverTopKEdgeWriter(output_dir=tmp, split="test", topk_values=[5, 1, 20, 5])
+        trainer = types.SimpleNamespace(global_rank=0)
+        w.on_predict_start(trainer, None)
+        w.write_on_batch_end(trainer, None, out, None, batch, 0, 0)
+        w.on_predict_end(trainer, None)
+        payload = torch.load(os.path.join(tmp, "test.pt"), weights_only=False)
+        manifest = json.loads(open(os.path.join(tmp, "test.manifest.json")).read())
+    torch.save({"payload": payload, "manifest": manifest}, os.path.join(GOLDEN, "writer_artifact.pt"))
+    np.savez_compressed(os.path.join(GOLDEN, "writer_inputs.npz"), edge_index=qb.edge_index, edge_attr=qb.edge_attr,
+                        ptr=qb.ptr, edge_ptr=qb.edge_ptr, node_global_ids=qb.node_global_ids, logits=logits,
+                        logits_fwd=lf, logits_bwd=lb, labels=labels, answer_entity_ids=np.concatenate(answers),
+                        answer_ptr=a_ptr)
+    print("writer ok", len(payload["samples"]), manifest)
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     Retriever, ref_ceb, brp, kind = load_reference()
@@ -344,6 +423,7 @@ def main():
     golden_dde(Retriever)
     golden_scorer(Retriever)
     golden_gagent()
+    golden_writer()
     with open(os.path.join(GOLDEN, "PROVENANCE.txt"), "w", encoding="utf-8") as f:
         f.write(
             "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"

@@ -592,3 +592,91 @@ def test_retriever_metrics_match_oracle(dev):
     assert abs(got["edge/score_margin"] - orc.score_margin(scores, labels, qb.edge_ptr)) < 1e-5
     assert 0.0 < got["answer/reachability@100"] < 1.0 and 0.0 < got["edge/recall@50"] < 1.0
     assert 0.0 < got["bridge/recall@100"] < 1.0
+
+
+# ------------------------------------------------------------------ a16: deterministic single shortest path
+def test_shortest_path_single_golden_and_random(dev, golden_dir):
+    from evi_rag_b200 import graph as G
+
+    g = _g(golden_dir, "bfs.npz")
+    for c in range(int(g["num_cases"])):
+        e, n = G._shortest_path_single(int(g[f"c{c}_n"]), g[f"c{c}_src"].tolist(), g[f"c{c}_dst"].tolist(),
+                                       g[f"c{c}_sources"].tolist(), g[f"c{c}_targets"].tolist())
+        assert e == g[f"c{c}_single_edges"].tolist() and n == g[f"c{c}_single_nodes"].tolist(), c
+    assert G.shortest_path_edge_indices_undirected(5, [0, 1], [1, 2], [], [2]) == ([], [])
+    assert G._shortest_path_single(5, [0, 1], [1, 2], [0], [0, 2]) == ([], [0])  # a target that is a source
+    assert G._shortest_path_single(5, [0, 1], [1, 2], [0], [4]) == ([], [])      # unreachable
+    # sparse random graphs: long paths, many equal-length alternatives, duplicate edges, several sources
+    rng = np.random.default_rng(5)
+    n_jobs, heads, tails, ptr, eptr, srcs, sp, tgts, tp = 24, [], [], [0], [0], [], [0], [], [0]
+    for j in range(n_jobs):
+        n = int(rng.integers(2, 700))
+        e = int(n * rng.uniform(0.9, 2.5))
+        h, t = rng.integers(0, n, e), rng.integers(0, n, e)
+        h[: e // 10], t[: e // 10] = h[e // 10: 2 * (e // 10)], t[e // 10: 2 * (e // 10)]  # duplicates
+        heads.append(h + ptr[-1]); tails.append(t + ptr[-1])
+        s = rng.integers(0, n, int(rng.integers(1, 4))) + ptr[-1]
+        a = rng.integers(0, n, int(rng.integers(1, 6))) + ptr[-1]
+        srcs += s.tolist(); sp.append(len(srcs)); tgts += a.tolist(); tp.append(len(tgts))
+        ptr.append(ptr[-1] + n); eptr.append(eptr[-1] + e)
+    ei = np.stack([np.concatenate(heads), np.concatenate(tails)]).astype(np.int64)
+    gb = G.GraphBatch.from_edge_index(ei, np.asarray(ptr, np.int64), device=dev)
+    plen, pe, pn = G.batched_shortest_path_single(gb, np.asarray(srcs), np.asarray(sp), np.asarray(tgts), np.asarray(tp))
+    longest = 0
+    for j in range(n_jobs):
+        n0, e0, e1 = ptr[j], eptr[j], eptr[j + 1]
+        re, rn = orc.shortest_path_single(ptr[j + 1] - n0, ei[0, e0:e1] - n0, ei[1, e0:e1] - n0,
+                                          [x - n0 for x in srcs[sp[j]:sp[j + 1]]], [x - n0 for x in tgts[tp[j]:tp[j + 1]]])
+        if plen[j] < 0:
+            assert (re, rn) == ([], []), j
+        else:
+            assert pe[j, :plen[j]].tolist() == re and pn[j, :plen[j] + 1].tolist() == rn, j
+            longest = max(longest, int(plen[j]))
+    assert longest >= 4
+
+
+# ------------------------------------------------------------------ (f3) writer artifact
+def test_writer_artifact_matches_reference(dev, golden_dir, tmp_path):
+    import types
+
+    from evi_rag_b200.writer import RetrieverTopKEdgeWriter, load_artifact
+
+    g = _g(golden_dir, "writer_inputs.npz")
+    ref = torch.load(os.path.join(golden_dir, "writer_artifact.pt"), weights_only=False)
+    B = len(g["ptr"]) - 1
+    batch = types.SimpleNamespace(
+        num_graphs=B, ptr=torch.from_numpy(g["ptr"]), edge_index=torch.from_numpy(g["edge_index"]),
+        edge_attr=torch.from_numpy(g["edge_attr"]), labels=torch.from_numpy(g["labels"]),
+        node_global_ids=torch.from_numpy(g["node_global_ids"]), answer_entity_ids=torch.from_numpy(g["answer_entity_ids"]),
+        answer_entity_ids_ptr=torch.from_numpy(g["answer_ptr"]), sample_id=[f"q{i}" for i in range(B)],
+        question=[f"who is {i}?" for i in range(B)], _slice_dict={"edge_index": torch.from_numpy(g["edge_ptr"])})
+    qid = torch.from_numpy(np.repeat(np.arange(B), np.diff(g["edge_ptr"]))).to(dev)
+    out = types.SimpleNamespace(logits=torch.from_numpy(g["logits"]).to(dev), query_ids=qid,
+                                logits_fwd=torch.from_numpy(g["logits_fwd"]).to(dev),
+                                logits_bwd=torch.from_numpy(g["logits_bwd"]).to(dev))
+    for use_slice in (True, False):
+        if not use_slice:
+            batch._slice_dict = {"answer_entity_ids": batch.answer_entity_ids_ptr}
+            batch.answer_entity_ids_ptr = None
+        w = RetrieverTopKEdgeWriter(output_dir=tmp_path / str(use_slice), split="test", topk_values=[5, 1, 20, 5])
+        trainer = types.SimpleNamespace(global_rank=0)
+        w.on_test_start(trainer, None)
+        w.on_test_batch_end(trainer, None, out, batch, 0)
+        w.on_test_end(trainer, None)
+        got = load_artifact(tmp_path / str(use_slice), "test")
+        assert {k: v for k, v in got["manifest"].items() if k != "created_at"} == \
+               {k: v for k, v in ref["manifest"].items() if k != "created_at"}
+        assert got["settings"] == ref["payload"]["settings"]
+        assert len(got["samples"]) == len(ref["payload"]["samples"])
+        for a, b in zip(got["samples"], ref["payload"]["samples"]):
+            assert (a["sample_id"], a["question"], a["answer_entity_ids"]) == (b["sample_id"], b["question"], b["answer_entity_ids"])
+            assert list(a["triplets_by_k"]) == list(b["triplets_by_k"])
+            for k in b["triplets_by_k"]:
+                assert len(a["triplets_by_k"][k]) == len(b["triplets_by_k"][k])
+                for x, y in zip(a["triplets_by_k"][k], b["triplets_by_k"][k]):
+                    assert list(x) == list(y)  # same keys in the same order
+                    for key in y:
+                        if key == "score":
+                            assert abs(x[key] - y[key]) <= 1e-6  # sigmoid: expf rounding
+                        else:
+                            assert x[key] == y[key], (key, x, y)

@@ -120,3 +120,25 @@ def test_synthetic_generator_is_deterministic_and_shardable():
     s = a.slice(3, 7)
     assert s.num_graphs == 4 and s.ptr[0] == 0 and s.edge_index.min() >= 0 and s.edge_index.max() < s.num_nodes
     assert set(np.unique(a.topic_one_hot.sum(1))) == {1.0}
+
+
+def test_writer_and_gagent_host_validation(tmp_path):
+    from evi_rag_b200.gagent import GAgentSettings
+    from evi_rag_b200.writer import RetrieverTopKEdgeWriter, normalize_k_values
+
+    assert normalize_k_values([5, "1", 20, 5, -3, "x"]) == [1, 5, 20]
+    assert normalize_k_values(None, default=(1, 5, 10)) == [1, 5, 10]
+    with pytest.raises(ValueError):
+        RetrieverTopKEdgeWriter(output_dir=tmp_path, artifact_name=" ")
+    with pytest.raises(ValueError):
+        RetrieverTopKEdgeWriter(output_dir=tmp_path, schema_version=0)
+    w = RetrieverTopKEdgeWriter(output_dir=tmp_path, topk_values=[10, 5])
+    assert w.topk_values == [5, 10] and w._max_topk == 10
+    (tmp_path / "test.pt").write_bytes(b"x")
+    with pytest.raises(FileExistsError):
+        RetrieverTopKEdgeWriter(output_dir=tmp_path, overwrite=False).on_predict_start(None, None)
+    s = GAgentSettings(edge_top_k=7)
+    assert s.start_max_edges == 7 and s.to_metadata()["output_path"].endswith("g_agent_samples.pt")
+    for bad in (dict(max_hops=-1), dict(score_temperature=0.0), dict(start_keep_ratio=1.5), dict(score_mode="x")):
+        with pytest.raises(ValueError):
+            GAgentSettings(**bad)

@@ -175,3 +175,31 @@ def test_gagent_samples_match_reference(golden_dir, tag):
         assert np.array_equal(out["edge_labels"], g[f"{tag}_q{i}_edge_labels"])
         assert bool(out["is_dummy_agent"]) == bool(g[f"{tag}_q{i}_is_dummy_agent"])
     assert failed == int(g[f"{tag}_retrieval_failed"])
+
+
+def test_shortest_path_single_matches_reference(golden_dir):
+    g = _load(golden_dir, "bfs.npz")
+    for c in range(int(g["num_cases"])):
+        e, n = orc.shortest_path_single(int(g[f"c{c}_n"]), g[f"c{c}_src"], g[f"c{c}_dst"], g[f"c{c}_sources"].tolist(),
+                                        g[f"c{c}_targets"].tolist())
+        assert e == g[f"c{c}_single_edges"].tolist() and n == g[f"c{c}_single_nodes"].tolist(), c
+
+
+def test_writer_payload_matches_reference_artifact(golden_dir):
+    g = _load(golden_dir, "writer_inputs.npz")
+    art = torch.load(os.path.join(golden_dir, "writer_artifact.pt"), weights_only=False)
+    ks = art["payload"]["settings"]["topk_values"]
+    assert ks == [1, 5, 20]
+    out = orc.writer_payload(g["logits"], g["logits_fwd"], g["logits_bwd"], g["edge_index"], g["edge_attr"], g["labels"],
+                             g["node_global_ids"], g["edge_ptr"], max(ks))
+    for b, smp in enumerate(art["payload"]["samples"]):
+        assert smp["sample_id"] == f"q{b}"
+        assert smp["answer_entity_ids"] == g["answer_entity_ids"][g["answer_ptr"][b]:g["answer_ptr"][b + 1]].tolist()
+        for k in ks:
+            trip = smp["triplets_by_k"][k]
+            assert len(trip) == min(k, int(out["count"][b]))
+            for j, t in enumerate(trip):
+                assert (t["head_entity_id"], t["relation_id"], t["tail_entity_id"], t["rank"]) == (
+                    int(out["head_id"][b, j]), int(out["relation_id"][b, j]), int(out["tail_id"][b, j]), j + 1)
+                assert abs(t["score"] - float(out["score"][b, j])) <= 1e-7 and t["label"] == float(out["label"][b, j])
+                assert t["logit_fwd"] == float(out["logit_fwd"][b, j]) and t["logit_bwd"] == float(out["logit_bwd"][b, j])
