@@ -9,7 +9,7 @@ Works with any ``torch.distributed`` backend (NCCL over NVLink on the GPU box, g
 """
 from __future__ import annotations
 
-from typing import Dict, List, Sequence, Tuple
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -37,24 +37,48 @@ def partition_by_edges(edge_counts: Sequence[int], world_size: int) -> List[Tupl
     return [(bounds[r], bounds[r + 1]) for r in range(world_size)]
 
 
-def gather_topk(local: Dict[str, torch.Tensor], num_local_questions: int, group=None) -> Dict[str, torch.Tensor]:
-    """All-gather per-rank ``[Q_r, k]`` (or ``[Q_r]``) arrays into global question order. Ranks may
-    hold different Q_r: arrays are padded to the max and trimmed after the exchange."""
+def gather_topk(local: Dict[str, torch.Tensor], num_local_questions: int, group=None,
+                counts: Optional[Sequence[int]] = None) -> Dict[str, torch.Tensor]:
+    """All-gather per-rank ``[Q_r, k]`` (or ``[Q_r]``) arrays into global question order with ONE collective:
+    the arrays are packed row-wise into a single ``[Q_max, row_bytes]`` byte matrix, exchanged with
+    ``all_gather_into_tensor`` and unpacked. Ranks may hold different Q_r; when the caller already knows every
+    rank's question count (``counts``, e.g. from ``partition_by_edges``) no size exchange and no host
+    synchronisation happen, otherwise one small all-gather of the counts precedes the exchange."""
     world = dist.get_world_size(group)
     dev = next(iter(local.values())).device
-    q_local = torch.tensor([num_local_questions], dtype=torch.long, device=dev)
-    q_all = [torch.zeros_like(q_local) for _ in range(world)]
-    dist.all_gather(q_all, q_local, group=group)
-    q_all = [int(t.item()) for t in q_all]
+    if counts is None:
+        q_local = torch.tensor([num_local_questions], dtype=torch.long, device=dev)
+        q_all_t = [torch.zeros_like(q_local) for _ in range(world)]
+        dist.all_gather(q_all_t, q_local, group=group)
+        q_all = [int(t.item()) for t in q_all_t]
+    else:
+        q_all = [int(c) for c in counts]
+        if len(q_all) != world or q_all[dist.get_rank(group)] != num_local_questions:
+            raise ValueError(f"counts {q_all} do not match world size {world} / local count {num_local_questions}")
     q_max = max(q_all)
+    names = list(local)
+    rows, widths = [], []
+    for name in names:
+        t = local[name].contiguous()
+        if t.shape[0] != num_local_questions:
+            raise ValueError(f"{name}: leading dimension {t.shape[0]} != {num_local_questions} questions")
+        b = t.reshape(num_local_questions, -1).view(torch.uint8)
+        rows.append(b)
+        widths.append(int(b.shape[1]))
+    packed = torch.zeros((q_max, sum(widths)), dtype=torch.uint8, device=dev)
+    if num_local_questions:
+        torch.cat(rows, dim=1, out=packed[:num_local_questions])
+    gathered = torch.empty((world * q_max, sum(widths)), dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(gathered, packed, group=group)
+    if any(q != q_max for q in q_all):
+        gathered = torch.cat([gathered[r * q_max: r * q_max + q] for r, q in enumerate(q_all)], dim=0)
     out: Dict[str, torch.Tensor] = {}
-    for name, t in local.items():
-        pad_shape = (q_max,) + tuple(t.shape[1:])
-        padded = torch.zeros(pad_shape, dtype=t.dtype, device=dev)
-        padded[: t.shape[0]] = t
-        parts = [torch.empty_like(padded) for _ in range(world)]
-        dist.all_gather(parts, padded, group=group)
-        out[name] = torch.cat([p[:q] for p, q in zip(parts, q_all)], dim=0)
+    col = 0
+    total = sum(q_all)
+    for name, wdt in zip(names, widths):
+        t = local[name]
+        out[name] = gathered[:, col: col + wdt].contiguous().view(t.dtype).reshape((total,) + tuple(t.shape[1:]))
+        col += wdt
     return out
 
 

@@ -40,9 +40,13 @@ def _worker(rank: int, world: int, port: int, edge_counts, k: int, out_dir: str)
         local = _fake_topk(q0, q1, k)
         got = gather_topk(local, q1 - q0)
         full = _fake_topk(0, len(edge_counts), k)
+        known = gather_topk(local, q1 - q0, counts=[b - a for a, b in parts])  # no size exchange
         for name in full:
             assert got[name].dtype == full[name].dtype, name
             assert torch.equal(got[name], full[name]), (rank, name)
+            assert torch.equal(known[name], full[name]), (rank, name)
+        with pytest.raises(ValueError):
+            gather_topk(local, q1 - q0, counts=[1] * (world + 1))
         # metric accumulators: hits / totals summed over ranks (dist_reduce_fx="sum")
         acc = torch.tensor([float(q1 - q0), float(sum(edge_counts[q0:q1]))], dtype=torch.float64)
         tot = allreduce_sums(acc)
