@@ -1,0 +1,363 @@
+"""Single-graph retrieval over a sharded triple pool (BASELINE config 4).
+
+The reference only knows per-question subgraphs (AGENTS.md:47); its dataset build cuts them out of the knowledge
+graph offline. This module does that cut on the device, per query batch, from one large triple pool:
+
+1. depth-capped multi-source BFS from the query's seed entities over the undirected pool — the hop-distance
+   semantics of ``_bfs_dist`` (scripts/build_retrieval_pipeline.py:610-631);
+2. candidate triples = edges whose two endpoints were reached, capped at ``cap`` by smallest
+   ``(dist_head + dist_tail, edge id)``;
+3. the candidates of a query, in ascending edge id, become one question subgraph (``topic_one_hot`` =
+   one-hot(is seed)) and go through the same ``Retriever`` kernels and ragged top-k as every other config.
+
+Sharding: the pool is edge-partitioned by contiguous head-node range; every shard indexes its own
+triples by head and by tail (global node ids). A BFS level is "expand the frontier over my triples" followed by an
+exchange of the newly reached (query, node) pairs, so all shards hold the same visited set; the candidate cut is
+"my `cap` best" per shard followed by an exchange and the same selection over the union. Scoring shards by query
+(the subgraphs are small once cut). Shards can be several objects on one device (tests) or one per rank of a
+``torch.distributed`` group (NCCL on the GPU box).
+
+Index construction (``TriplePoolShard.from_triples``) is a one-off load-time sort, like the reference's offline
+parquet build; the per-query path below is kernels from ``csrc/pool_kernels.cu`` plus sizes read back at batch
+boundaries.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import types
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import lib as _lib
+from .sharding import gather_topk, partition_by_edges
+from .topk import segmented_topk
+
+_EMPTY = -1  # 0xFFFF... as int64: padding of exchange buffers
+
+
+def _next_pow2(x: int) -> int:
+    p = 1
+    while p < x:
+        p <<= 1
+    return p
+
+
+def partition_pool_by_head(heads: np.ndarray, num_nodes: int, world: int) -> List[Tuple[int, int]]:
+    """Contiguous head-node ranges ``[(lo, hi)] * world`` holding about ``E / world`` triples each."""
+    deg = np.bincount(np.asarray(heads, dtype=np.int64), minlength=num_nodes)
+    return partition_by_edges(deg, world)
+
+
+@dataclass
+class TriplePoolShard:
+    """Device-resident index of one shard's triples by head (fwd) and by tail (rev), global node ids."""
+
+    fwd_ptr: torch.Tensor    # [num_nodes + 1] i32
+    fwd_other: torch.Tensor  # [M] i32 tail
+    fwd_rel: torch.Tensor    # [M] i32
+    fwd_eid: torch.Tensor    # [M] i64 global edge id
+    rev_ptr: torch.Tensor    # [num_nodes + 1] i32
+    rev_other: torch.Tensor  # [M] i32 head
+    num_nodes: int
+
+    @classmethod
+    def from_triples(cls, heads, rels, tails, edge_ids, num_nodes: int, device) -> "TriplePoolShard":
+        dev = torch.device(device)
+        h = torch.as_tensor(np.asarray(heads), dtype=torch.long, device=dev)
+        t = torch.as_tensor(np.asarray(tails), dtype=torch.long, device=dev)
+        r = torch.as_tensor(np.asarray(rels), dtype=torch.long, device=dev)
+        e = torch.as_tensor(np.asarray(edge_ids), dtype=torch.long, device=dev)
+        if h.numel() and (int(h.min()) < 0 or int(t.min()) < 0 or int(h.max()) >= num_nodes or int(t.max()) >= num_nodes):
+            raise ValueError("triple endpoints must lie in [0, num_nodes)")
+
+        def rows(key):
+            order = torch.argsort(key, stable=True)
+            ptr = torch.zeros(num_nodes + 1, dtype=torch.long, device=dev)
+            ptr[1:] = torch.cumsum(torch.bincount(key, minlength=num_nodes), 0)
+            return order, ptr.to(torch.int32)
+
+        fo, fptr = rows(h)
+        ro, rptr = rows(t)
+        pad = lambda x, dt: (x if x.numel() else torch.zeros(1, dtype=x.dtype, device=dev)).to(dt).contiguous()
+        return cls(fptr.contiguous(), pad(t[fo], torch.int32), pad(r[fo], torch.int32), pad(e[fo], torch.long),
+                   rptr.contiguous(), pad(h[ro], torch.int32), int(num_nodes))
+
+    @property
+    def num_triples(self) -> int:
+        return int(self.fwd_ptr[-1])
+
+    def c_struct(self) -> _lib.PoolShard:
+        s = _lib.PoolShard()
+        s.fwd_ptr, s.fwd_other, s.fwd_rel = self.fwd_ptr.data_ptr(), self.fwd_other.data_ptr(), self.fwd_rel.data_ptr()
+        s.fwd_eid, s.rev_ptr, s.rev_other = self.fwd_eid.data_ptr(), self.rev_ptr.data_ptr(), self.rev_other.data_ptr()
+        s.num_nodes = self.num_nodes
+        return s
+
+
+class _ShardState:
+    """Per-shard scratch of one query batch: the visited hash table and the visited-pair list."""
+
+    def __init__(self, shard: TriplePoolShard, table_capacity: int, visited_cap: int, dev):
+        self.shard = shard
+        self.keys = torch.empty(table_capacity, dtype=torch.long, device=dev)
+        self.dist = torch.empty(table_capacity, dtype=torch.uint8, device=dev)
+        self.local_id = torch.empty(table_capacity, dtype=torch.int32, device=dev)
+        self.visited = torch.empty(visited_cap, dtype=torch.long, device=dev)
+        self.visited_count = torch.zeros(1, dtype=torch.long, device=dev)
+        self.fresh = torch.empty(visited_cap, dtype=torch.long, device=dev)
+        self.fresh_count = torch.zeros(1, dtype=torch.long, device=dev)
+        self.flags = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.table = _lib.PoolTable()
+        self.table.keys, self.table.dist = self.keys.data_ptr(), self.dist.data_ptr()
+        self.table.local_id, self.table.capacity = self.local_id.data_ptr(), table_capacity
+        self.cshard = shard.c_struct()
+        self.bounds = [0]
+
+
+class PoolRetriever:
+    """Query batch -> per-query candidate subgraphs -> scores -> top-k global edge ids."""
+
+    def __init__(self, shards: Sequence[TriplePoolShard], model: Any, *, node_embedding_ids: Optional[torch.Tensor] = None,
+                 cap: int = 20000, top_k: int = 500, depth: int = 2, table_capacity: int = 1 << 22,
+                 visited_cap: Optional[int] = None, group=None, num_sms: int = 148) -> None:
+        if not shards:
+            raise ValueError("at least one shard is required")
+        if not (0 < cap <= _lib.POOL_MAX_CAP):
+            raise ValueError(f"cap must be in [1, {_lib.POOL_MAX_CAP}], got {cap}")
+        if not (0 <= depth <= 250):
+            raise ValueError(f"depth must be in [0, 250], got {depth}")
+        if table_capacity & (table_capacity - 1):
+            raise ValueError("table_capacity must be a power of two")
+        self.shards = list(shards)
+        self.model = model
+        self.dev = self.shards[0].fwd_ptr.device
+        if self.dev.type != "cuda":
+            raise RuntimeError("PoolRetriever runs on CUDA tensors only (no CPU fallback).")
+        self.cap, self.top_k, self.depth = int(cap), int(top_k), int(depth)
+        self.table_capacity = int(table_capacity)
+        self.visited_cap = int(visited_cap) if visited_cap is not None else self.table_capacity // 2
+        self.node_embedding_ids = None if node_embedding_ids is None else \
+            node_embedding_ids.to(device=self.dev, dtype=torch.long).contiguous()
+        self.group = group
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = dist.get_rank(group) if self.world > 1 else 0
+        if self.world > 1 and len(self.shards) != 1:
+            raise ValueError("with torch.distributed every rank holds exactly one shard")
+        self.num_sms = int(num_sms)
+        self.L = _lib.load()
+
+    # ------------------------------------------------------------------ exchange helpers
+    def _gather_var(self, t: torch.Tensor, n: int) -> List[torch.Tensor]:
+        """All ranks' ``t[:n]`` (different n per rank): sizes first, then one padded all-gather."""
+        sizes = [torch.zeros(1, dtype=torch.long, device=self.dev) for _ in range(self.world)]
+        dist.all_gather(sizes, torch.tensor([n], dtype=torch.long, device=self.dev), group=self.group)
+        sizes = [int(s.item()) for s in sizes]
+        m = max(max(sizes), 1)
+        buf = torch.full((m,), _EMPTY, dtype=t.dtype, device=self.dev)
+        buf[:n] = t[:n]
+        out = torch.empty(self.world * m, dtype=t.dtype, device=self.dev)
+        dist.all_gather_into_tensor(out, buf, group=self.group)
+        return [out[r * m: r * m + sizes[r]] for r in range(self.world)]
+
+    def _check(self, st: _ShardState) -> None:
+        word = int(st.flags.item())
+        if word & _lib.POOL_TABLE_FULL:
+            raise RuntimeError("visited hash table full: raise table_capacity or use smaller query batches")
+        if word & _lib.POOL_VISITED_FULL:
+            raise RuntimeError("visited list full: raise visited_cap or use smaller query batches")
+
+    # ------------------------------------------------------------------ steps 1-2: BFS + candidate cut
+    def extract(self, seeds: torch.Tensor, seed_ptr: torch.Tensor) -> types.SimpleNamespace:
+        """``seeds`` = global node ids grouped by ``seed_ptr [Q+1]``. Returns the subgraph batch (device tensors under
+        the reference's PyG attribute names) plus ``edge_global_id [E]`` and ``edge_ptr [Q+1]``."""
+        L, dev, stream = self.L, self.dev, _lib.stream_handle()
+        seeds = torch.as_tensor(seeds, dtype=torch.long, device=dev).view(-1)
+        seed_ptr = torch.as_tensor(seed_ptr, dtype=torch.long, device=dev).view(-1)
+        Q = int(seed_ptr.numel() - 1)
+        num_nodes = self.shards[0].num_nodes
+        qid = torch.repeat_interleave(torch.arange(Q, device=dev), seed_ptr[1:] - seed_ptr[:-1])
+        ok = (seeds >= 0) & (seeds < num_nodes)  # out-of-range sources are ignored (:616-618)
+        seed_pairs = torch.where(ok, (qid << 32) | seeds.clamp(min=0), torch.full_like(seeds, _EMPTY)).contiguous()
+        states = [_ShardState(s, self.table_capacity, self.visited_cap, dev) for s in self.shards]
+        multi = len(states) > 1 or self.world > 1
+        for st in states:
+            _lib.check(L.evi_pool_reset(C.byref(st.table), stream), "evi_pool_reset")
+            _lib.check(L.evi_pool_insert(C.byref(st.table), seed_pairs.data_ptr(), int(seed_pairs.numel()), 0,
+                                         st.visited.data_ptr(), st.visited_count.data_ptr(), self.visited_cap,
+                                         st.flags.data_ptr(), stream), "evi_pool_insert")
+            st.bounds.append(int(st.visited_count.item()))
+        for level in range(self.depth):
+            for st in states:
+                st.fresh_count.zero_()
+                _lib.check(L.evi_pool_expand(
+                    C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), st.bounds[level], st.bounds[level + 1],
+                    level, st.visited_count.data_ptr(), self.visited_cap, st.fresh.data_ptr() if multi else None,
+                    st.fresh_count.data_ptr() if multi else None, self.visited_cap, st.flags.data_ptr(), self.num_sms,
+                    stream), "evi_pool_expand")
+            if multi:  # frontier exchange: every shard learns the pairs the others reached at this level
+                lists = [st.fresh[: int(st.fresh_count.item())] for st in states]
+                if self.world > 1:
+                    remote = self._gather_var(lists[0], int(lists[0].numel()))
+                    others_of = [[remote[r] for r in range(self.world) if r != self.rank]]
+                else:
+                    others_of = [[lists[j] for j in range(len(states)) if j != i] for i in range(len(states))]
+                for st, others in zip(states, others_of):
+                    for pairs in others:
+                        if pairs.numel():
+                            pairs = pairs.contiguous()
+                            _lib.check(L.evi_pool_insert(C.byref(st.table), pairs.data_ptr(), int(pairs.numel()), level + 1,
+                                                         st.visited.data_ptr(), st.visited_count.data_ptr(),
+                                                         self.visited_cap, st.flags.data_ptr(), stream), "evi_pool_insert")
+            for st in states:
+                st.bounds.append(int(st.visited_count.item()))
+                self._check(st)
+        sels = [self._shard_candidates(st, Q) for st in states]
+        sel = self._merge(sels, Q) if multi else sels[0]
+        return self._pack(states[0], sel, Q)
+
+    def _select(self, key, ht, rel, seg_off, Q: int):
+        dev, cap = self.dev, self.cap
+        sort_len = _next_pow2(cap)
+        u64 = lambda *s: torch.empty(s, dtype=torch.long, device=dev)
+        stage_key, stage_ht, stage_rel = u64(Q, cap), u64(Q, cap), torch.empty((Q, cap), dtype=torch.int32, device=dev)
+        out = {"key": u64(Q, cap), "ht": u64(Q, cap), "rel": torch.empty((Q, cap), dtype=torch.int32, device=dev),
+               "count": torch.empty(Q, dtype=torch.int32, device=dev)}
+        sort_ws = u64(Q, sort_len)
+        _lib.check(self.L.evi_pool_select(key.data_ptr(), ht.data_ptr(), rel.data_ptr(), seg_off.data_ptr(), Q, cap, sort_len,
+                                          stage_key.data_ptr(), stage_ht.data_ptr(), stage_rel.data_ptr(), sort_ws.data_ptr(),
+                                          out["key"].data_ptr(), out["ht"].data_ptr(), out["rel"].data_ptr(),
+                                          out["count"].data_ptr(), _lib.stream_handle()), "evi_pool_select")
+        return out
+
+    def _shard_candidates(self, st: _ShardState, Q: int):
+        L, dev, stream = self.L, self.dev, _lib.stream_handle()
+        nv = st.bounds[-1]
+        count = torch.zeros(Q, dtype=torch.int32, device=dev)
+        _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 0,
+                                         count.data_ptr(), None, None, None, None, None, self.num_sms, stream),
+                   "evi_pool_candidates")
+        off = torch.zeros(Q + 1, dtype=torch.long, device=dev)
+        off[1:] = torch.cumsum(count.long(), 0)
+        total = max(int(off[-1].item()), 1)
+        key = torch.empty(total, dtype=torch.long, device=dev)
+        ht = torch.empty(total, dtype=torch.long, device=dev)
+        rel = torch.empty(total, dtype=torch.int32, device=dev)
+        cursor = torch.zeros(Q, dtype=torch.int32, device=dev)
+        _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 1, None,
+                                         off.data_ptr(), cursor.data_ptr(), key.data_ptr(), ht.data_ptr(), rel.data_ptr(),
+                                         self.num_sms, stream), "evi_pool_candidates")
+        return self._select(key, ht, rel, off, Q)
+
+    def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int):
+        """The cap smallest keys over the union of every shard's survivors (padding = all-ones keys)."""
+        dev, cap = self.dev, self.cap
+        valid = lambda s: torch.arange(cap, device=dev).unsqueeze(0) < s["count"].unsqueeze(1)
+        for s in sels:
+            s["key"] = torch.where(valid(s), s["key"], torch.full_like(s["key"], _EMPTY))
+        if self.world > 1:
+            parts = {}
+            for name in ("key", "ht", "rel"):
+                t = sels[0][name].contiguous()
+                out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=dev)
+                dist.all_gather_into_tensor(out, t, group=self.group)
+                parts[name] = out
+        else:
+            parts = {name: torch.stack([s[name] for s in sels]) for name in ("key", "ht", "rel")}
+        S = int(parts["key"].shape[0])
+        cat = {name: t.permute(1, 0, 2).reshape(Q * S * cap).contiguous() for name, t in parts.items()}
+        seg_off = torch.arange(Q + 1, dtype=torch.long, device=dev) * (S * cap)
+        return self._select(cat["key"], cat["ht"], cat["rel"], seg_off, Q)
+
+    def _pack(self, st: _ShardState, sel, Q: int) -> types.SimpleNamespace:
+        L, dev, cap, stream = self.L, self.dev, self.cap, _lib.stream_handle()
+        node_count = torch.empty(Q, dtype=torch.int32, device=dev)
+        node_global = torch.empty((Q, 2 * cap), dtype=torch.int32, device=dev)
+        node_is_seed = torch.empty((Q, 2 * cap), dtype=torch.uint8, device=dev)
+        _lib.check(L.evi_pool_relabel(C.byref(st.table), sel["ht"].data_ptr(), sel["count"].data_ptr(), Q, cap,
+                                      node_count.data_ptr(), node_global.data_ptr(), node_is_seed.data_ptr(), stream),
+                   "evi_pool_relabel")
+        edge_ptr = torch.zeros(Q + 1, dtype=torch.long, device=dev)
+        edge_ptr[1:] = torch.cumsum(sel["count"].long(), 0)
+        node_ptr = torch.zeros(Q + 1, dtype=torch.long, device=dev)
+        node_ptr[1:] = torch.cumsum(node_count.long(), 0)
+        sizes = torch.stack([edge_ptr[-1], node_ptr[-1]]).tolist()  # one read-back to size the batch arrays
+        E, N = int(sizes[0]), int(sizes[1])
+        b = types.SimpleNamespace()
+        b.edge_index = torch.zeros((2, max(E, 1)), dtype=torch.long, device=dev)
+        b.edge_attr = torch.zeros(max(E, 1), dtype=torch.long, device=dev)
+        b.edge_global_id = torch.zeros(max(E, 1), dtype=torch.long, device=dev)
+        b.node_global_ids = torch.zeros(max(N, 1), dtype=torch.long, device=dev)
+        b.node_embedding_ids = torch.zeros(max(N, 1), dtype=torch.long, device=dev)
+        b.topic_one_hot = torch.zeros((max(N, 1), 2), dtype=torch.float32, device=dev)
+        _lib.check(L.evi_pool_pack(C.byref(st.table), sel["key"].data_ptr(), sel["ht"].data_ptr(), sel["rel"].data_ptr(),
+                                   sel["count"].data_ptr(), Q, cap, edge_ptr.data_ptr(), node_ptr.data_ptr(),
+                                   node_global.data_ptr(), node_is_seed.data_ptr(), _lib.ptr(self.node_embedding_ids),
+                                   max(E, 1), b.edge_index.data_ptr(), b.edge_attr.data_ptr(), b.edge_global_id.data_ptr(),
+                                   b.node_global_ids.data_ptr(), b.node_embedding_ids.data_ptr(),
+                                   b.topic_one_hot.data_ptr(), stream), "evi_pool_pack")
+        b.edge_index, b.edge_attr, b.edge_global_id = b.edge_index[:, :E], b.edge_attr[:E], b.edge_global_id[:E]
+        b.node_global_ids, b.node_embedding_ids, b.topic_one_hot = b.node_global_ids[:N], b.node_embedding_ids[:N], b.topic_one_hot[:N]
+        b.ptr, b.edge_ptr, b.num_graphs = node_ptr, edge_ptr, Q
+        b.candidate_keys, b.candidate_count = sel["key"], sel["count"]
+        return b
+
+    # ------------------------------------------------------------------ step 3: score + top-k
+    @staticmethod
+    def _slice(b, q0: int, q1: int, question_emb: torch.Tensor) -> types.SimpleNamespace:
+        """Questions [q0, q1) of a subgraph batch, re-based to their own batch-global node ids."""
+        ep, npt = b.edge_ptr.tolist(), b.ptr.tolist()
+        e0, e1, n0, n1 = ep[q0], ep[q1], npt[q0], npt[q1]
+        s = types.SimpleNamespace()
+        s.edge_index = (b.edge_index[:, e0:e1] - n0).contiguous()
+        s.edge_attr, s.edge_global_id = b.edge_attr[e0:e1].contiguous(), b.edge_global_id[e0:e1]
+        s.node_embedding_ids, s.topic_one_hot = b.node_embedding_ids[n0:n1].contiguous(), b.topic_one_hot[n0:n1].contiguous()
+        s.ptr, s.edge_ptr = (b.ptr[q0:q1 + 1] - n0).contiguous(), (b.edge_ptr[q0:q1 + 1] - e0).contiguous()
+        s.question_emb, s.num_graphs = question_emb[q0:q1].contiguous(), q1 - q0
+        return s
+
+    def score(self, b: types.SimpleNamespace, question_emb: torch.Tensor) -> Dict[str, torch.Tensor]:
+        """Bidirectional scores of every candidate and the per-query top-k as global edge ids."""
+        dev, k = self.dev, self.top_k
+        Q = b.num_graphs
+        question_emb = question_emb.to(device=dev, dtype=torch.float32)
+        if self.world > 1:  # queries shard across ranks by candidate count; results are gathered on every rank
+            counts = (b.edge_ptr[1:] - b.edge_ptr[:-1]).tolist()
+            parts = partition_by_edges(counts, self.world)
+            q0, q1 = parts[self.rank]
+            sb = self._slice(b, q0, q1, question_emb)
+        else:
+            parts, q0, q1, sb = [(0, Q)], 0, Q, b
+            sb.question_emb = question_emb.contiguous()
+        nq = q1 - q0
+        if nq > 0 and sb.edge_index.size(1) > 0:
+            out = self.model(sb)
+            top = segmented_topk(out.logits, sb.edge_ptr, k)
+            gidx = (top.indices.long() + sb.edge_ptr[:-1].unsqueeze(1)).clamp(min=0, max=sb.edge_global_id.numel() - 1)
+            valid = torch.arange(k, device=dev).unsqueeze(0) < top.counts.unsqueeze(1)
+            res = {"edge_id": torch.where(valid, sb.edge_global_id[gidx], torch.full_like(gidx, -1)),
+                   "score": top.values, "count": top.counts}
+            logits = out.logits
+        else:
+            res = {"edge_id": torch.full((nq, k), -1, dtype=torch.long, device=dev),
+                   "score": torch.full((nq, k), float("-inf"), device=dev),
+                   "count": torch.zeros(nq, dtype=torch.int32, device=dev)}
+            logits = torch.empty(0, device=dev)
+        if self.world > 1:
+            res = gather_topk(res, nq, group=self.group, counts=[b_ - a_ for a_, b_ in parts])
+        res["logits_local"] = logits
+        return res
+
+    def retrieve(self, question_emb: torch.Tensor, seeds, seed_ptr) -> Dict[str, torch.Tensor]:
+        """``edge_id [Q, k]`` (global triple ids, -1 padded), ``score [Q, k]``, ``count [Q]``, plus the candidate
+        subgraph batch under ``"batch"``."""
+        b = self.extract(seeds, seed_ptr)
+        res = self.score(b, question_emb)
+        res["batch"] = b
+        return res
+
+
+__all__ = ["TriplePoolShard", "PoolRetriever", "partition_pool_by_head"]

@@ -60,6 +60,20 @@ class GAgentArgs(C.Structure):
             "answer_node_locals")]
 
 
+class PoolShard(C.Structure):
+    """``evi_pool_shard`` (include/evi_rag_b200.h)."""
+
+    _fields_ = [(n, _vp) for n in ("fwd_ptr", "fwd_other", "fwd_rel", "fwd_eid", "rev_ptr", "rev_other")] + [
+        ("num_nodes", _i)]
+
+
+class PoolTable(C.Structure):
+    """``evi_pool_table`` (include/evi_rag_b200.h)."""
+
+    _fields_ = [("keys", _vp), ("dist", _vp), ("local_id", _vp), ("capacity", C.c_ulonglong)]
+
+
+POOL_TABLE_FULL, POOL_VISITED_FULL, POOL_MAX_CAP = 1, 2, 32768
 GAGENT_LOGITS, GAGENT_NODE_SOFTMAX, GAGENT_MAX_CAP = 0, 1, 2048
 GAGENT_EMPTY, GAGENT_NO_START_NODE, GAGENT_OVERFLOW, GAGENT_NO_START_LOCAL, GAGENT_NO_ANSWER = 1, 2, 4, 8, 16
 
@@ -89,6 +103,15 @@ PROTOTYPES = {
     "evi_node_softmax_logit": (_i, [_vp, _vp, _vp, _ll, _i, _i, _f, _f, _vp, _sz, _vp, _vp, _vp]),
     "evi_gagent_start_edges": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp]),
     "evi_gagent_build": (_i, [C.POINTER(GAgentArgs), _vp]),
+    "evi_pool_reset": (_i, [C.POINTER(PoolTable), _vp]),
+    "evi_pool_insert": (_i, [C.POINTER(PoolTable), _vp, _ll, _i, _vp, _vp, C.c_ulonglong, _vp, _vp]),
+    "evi_pool_expand": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, C.c_ulonglong, _i, _vp,
+                             C.c_ulonglong, _vp, _vp, C.c_ulonglong, _vp, _i, _vp]),
+    "evi_pool_candidates": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, _i] + [_vp] * 6 +
+                            [_i, _vp]),
+    "evi_pool_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i] + [_vp] * 8 + [_vp]),
+    "evi_pool_relabel": (_i, [C.POINTER(PoolTable), _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
+    "evi_pool_pack": (_i, [C.POINTER(PoolTable)] + [_vp] * 4 + [_i, _i] + [_vp] * 5 + [_ll] + [_vp] * 6 + [_vp]),
 }
 
 _lib: Optional[C.CDLL] = None
@@ -115,6 +138,12 @@ _KERNELS_PER_CALL = {
     "evi_node_softmax_logit": lambda a: 1 if a[5] == 0 else 3,
     "evi_gagent_start_edges": lambda a: 1,
     "evi_gagent_build": lambda a: 1,
+    "evi_pool_insert": lambda a: 1 if a[2] > 0 else 0,
+    "evi_pool_expand": lambda a: 1 if a[4] > a[3] else 0,
+    "evi_pool_candidates": lambda a: 1 if a[3] > 0 else 0,
+    "evi_pool_select": lambda a: 1,
+    "evi_pool_relabel": lambda a: 2,
+    "evi_pool_pack": lambda a: 1,
 }
 
 

@@ -330,6 +330,65 @@ typedef struct evi_gagent_args {
 } evi_gagent_args;
 int evi_gagent_build(const evi_gagent_args* args, cudaStream_t stream);
 
+/* ---- single-graph retrieval over a sharded triple pool (BASELINE config 4; no reference code path) ------ */
+/* A shard owns a subset of the triples, indexed by GLOBAL node id twice: rows by head (fwd_*) and rows by tail
+ * (rev_*). The visited set of a query batch is an open-addressing hash table keyed by (query << 32 | node) with the
+ * hop distance (scripts/build_retrieval_pipeline.py:610-631 semantics, depth-capped) as value. Candidates of a
+ * query = edges with both endpoints visited; key = (dist_h + dist_t) << 40 | global edge id; the `cap` smallest
+ * keys survive and are returned in ascending edge-id order. */
+#define EVI_POOL_TABLE_FULL 1u
+#define EVI_POOL_VISITED_FULL 2u
+#define EVI_POOL_MAX_CAP 32768
+typedef struct evi_pool_shard {
+  const int* fwd_ptr;        /* [num_nodes + 1] */
+  const int* fwd_other;      /* tail per entry */
+  const int* fwd_rel;
+  const long long* fwd_eid;  /* global edge id per entry */
+  const int* rev_ptr;        /* [num_nodes + 1] */
+  const int* rev_other;      /* head per entry */
+  int num_nodes;
+} evi_pool_shard;
+typedef struct evi_pool_table {
+  unsigned long long* keys;   /* [capacity] */
+  unsigned char* dist;        /* [capacity] */
+  int* local_id;              /* [capacity] */
+  unsigned long long capacity;/* power of two */
+} evi_pool_table;
+int evi_pool_reset(const evi_pool_table* table, cudaStream_t stream);
+/* merge pairs discovered elsewhere (the frontier exchange) or the seeds (dist_value 0); ~0 entries are padding */
+int evi_pool_insert(const evi_pool_table* table, const unsigned long long* pairs, long long num_pairs, int dist_value,
+                    unsigned long long* visited, unsigned long long* visited_count, unsigned long long visited_cap,
+                    unsigned* flags, cudaStream_t stream);
+/* expand visited[begin, end) (the level-`level` frontier) over the shard, both directions; discoveries go to
+ * visited (appended) and, when fresh != NULL, to fresh (what the other shards must be told) */
+int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, unsigned long long* visited,
+                    unsigned long long begin, unsigned long long end, int level, unsigned long long* visited_count,
+                    unsigned long long visited_cap, unsigned long long* fresh, unsigned long long* fresh_count,
+                    unsigned long long fresh_cap, unsigned* flags, int num_sms, cudaStream_t stream);
+/* emit == 0: cand_count [Q] += candidates of this shard; emit == 1: write them at cand_off[q] + cursor[q]++ */
+int evi_pool_candidates(const evi_pool_table* table, const evi_pool_shard* shard, const unsigned long long* visited,
+                        unsigned long long num_visited, int emit, int* cand_count, const long long* cand_off,
+                        int* cursor, unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel,
+                        int num_sms, cudaStream_t stream);
+/* per segment [seg_off[q], seg_off[q+1]): the cap smallest keys, ascending edge id; outputs [Q, cap];
+ * stage_* [Q, cap] and sort_ws [Q, sort_len] (sort_len = power of two >= cap) are scratch */
+int evi_pool_select(const unsigned long long* cand_key, const unsigned long long* cand_ht, const int* cand_rel,
+                    const long long* seg_off, int num_queries, int cap, int sort_len, unsigned long long* stage_key,
+                    unsigned long long* stage_ht, int* stage_rel, unsigned long long* sort_ws,
+                    unsigned long long* out_key, unsigned long long* out_ht, int* out_rel, int* out_count,
+                    cudaStream_t stream);
+/* local node ids of the selected subgraphs: node_count [Q], node_global / node_is_seed [Q, 2 cap] */
+int evi_pool_relabel(const evi_pool_table* table, const unsigned long long* sel_ht, const int* sel_count,
+                     int num_queries, int cap, int* node_count, int* node_global, unsigned char* node_is_seed,
+                     cudaStream_t stream);
+/* the PyG-style batch the scorer takes (edge_index in batch-global node ids, one_hot(is_seed) topic features) */
+int evi_pool_pack(const evi_pool_table* table, const unsigned long long* sel_key, const unsigned long long* sel_ht,
+                  const int* sel_rel, const int* sel_count, int num_queries, int cap, const long long* edge_ptr,
+                  const long long* node_ptr, const int* node_global, const unsigned char* node_is_seed,
+                  const long long* node_embedding_table, long long num_edges_out, long long* edge_index,
+                  long long* edge_attr, long long* edge_global_id, long long* node_global_ids,
+                  long long* node_embedding_ids, float* topic_one_hot, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -758,3 +758,52 @@ def shortest_path_single(num_nodes: int, edge_src, edge_dst, sources, targets) -
         cur = parent[cur]
         nodes.append(cur)
     return edges[::-1], nodes[::-1]
+
+
+# ----------------------------------------------------------------------------------------------
+# config 4: single-graph retrieval (no reference code path; SURVEY.md §8(d) row 4 defines it as the
+# composition of _bfs_dist and the reference scorer on the extracted subgraph)
+# ----------------------------------------------------------------------------------------------
+def pool_candidates(heads, tails, num_nodes: int, seeds, *, depth: int = 2, cap: int = 20000):
+    """One query: capped multi-source BFS from ``seeds`` over the undirected pool, candidates = edges with both
+    endpoints reached, the ``cap`` smallest by ``(dist_h + dist_t, edge id)``, returned in ascending edge id.
+    Returns ``(edge_ids [C] i64, dist [num_nodes] i32)``."""
+    h = np.asarray(heads, dtype=np.int64)
+    t = np.asarray(tails, dtype=np.int64)
+    dist = bfs_dist_np(num_nodes, h, t, seeds, max_depth=depth)
+    ok = (dist[h] >= 0) & (dist[t] >= 0)
+    eid = np.nonzero(ok)[0]
+    prio = dist[h[eid]].astype(np.int64) + dist[t[eid]].astype(np.int64)
+    order = np.lexsort((eid, prio))[:cap]
+    return np.sort(eid[order]), dist
+
+
+def pool_subgraph_batch(heads, rels, tails, num_nodes: int, seeds_per_query, *, depth: int = 2, cap: int = 20000,
+                        node_embedding_ids=None):
+    """Candidate subgraphs of a query batch in the reference's batch layout (nodes = ascending global ids)."""
+    h_all, r_all, t_all = (np.asarray(x, dtype=np.int64) for x in (heads, rels, tails))
+    ei, ea, eg, ng, topic, ptr, eptr = [], [], [], [], [], [0], [0]
+    for seeds in seeds_per_query:
+        eid, dist = pool_candidates(h_all, t_all, num_nodes, seeds, depth=depth, cap=cap)
+        nodes = np.unique(np.concatenate([h_all[eid], t_all[eid]])) if eid.size else np.empty(0, np.int64)
+        hl = np.searchsorted(nodes, h_all[eid]) + ptr[-1]
+        tl = np.searchsorted(nodes, t_all[eid]) + ptr[-1]
+        ei.append(np.stack([hl, tl]).astype(np.int64))
+        ea.append(r_all[eid])
+        eg.append(eid)
+        ng.append(nodes)
+        oh = np.zeros((nodes.size, 2), dtype=np.float32)
+        oh[np.arange(nodes.size), (dist[nodes] == 0).astype(np.int64)] = 1.0
+        topic.append(oh)
+        ptr.append(ptr[-1] + nodes.size)
+        eptr.append(eptr[-1] + eid.size)
+    node_global = np.concatenate(ng) if ng else np.empty(0, np.int64)
+    emb = node_global if node_embedding_ids is None else np.asarray(node_embedding_ids, dtype=np.int64)[node_global]
+    return {
+        "edge_index": np.concatenate(ei, axis=1) if ei else np.zeros((2, 0), np.int64),
+        "edge_attr": np.concatenate(ea) if ea else np.empty(0, np.int64),
+        "edge_global_id": np.concatenate(eg) if eg else np.empty(0, np.int64),
+        "node_global_ids": node_global, "node_embedding_ids": emb,
+        "topic_one_hot": np.concatenate(topic) if topic else np.zeros((0, 2), np.float32),
+        "ptr": np.asarray(ptr, dtype=np.int64), "edge_ptr": np.asarray(eptr, dtype=np.int64),
+    }
