@@ -46,7 +46,8 @@ def parse_args():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--questions-per-step", type=int, default=128)
     ap.add_argument("--ref-questions-per-step", type=int, default=4)
-    ap.add_argument("--cpu-sample-questions", type=int, default=8)
+    ap.add_argument("--cpu-sample-questions", type=int, default=160,
+                    help="questions of the cpu_baseline sample (batches of 32 like configs/data/retriever.yaml:8; ~15 s)")
     ap.add_argument("--operand-dtype", default="fp16", choices=["fp16", "bf16"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--pipeline-chunks", type=int, default=4,
@@ -142,7 +143,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "200", "-i", str(self.idx)], stdout=open(self.path, "w"),
+                                          "-lms", "25", "-i", str(self.idx)], stdout=open(self.path, "w"),
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -353,11 +354,13 @@ def run_ours(args):
         },
     }
     if world == 1 and not args.no_cpu_baseline:
-        n = args.cpu_sample_questions
-        qps, dt = time_cpu(spec, sd, ent, rel, n, 1, 1)
+        per = min(32, max(1, args.cpu_sample_questions))
+        n_steps = max(1, args.cpu_sample_questions // per)
+        qps, dt = time_cpu(spec, sd, ent, rel, per, n_steps, 1)
         line["cpu_baseline"] = {"value": qps, "unit": "questions/s", "cores": os.cpu_count() or 1, "kind": "port",
-                                "sample": f"{n} questions of the same workload after {n} warm-up questions; oracle port "
-                                          f"of the reference path (torch fp32, {os.cpu_count()} threads), {dt:.1f} s"}
+                                "sample": f"{n_steps * per} questions of the same workload in batches of {per} after one "
+                                          f"warm-up batch; oracle port of the reference path (torch fp32, "
+                                          f"{os.cpu_count()} threads), {dt:.1f} s"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -103,6 +103,7 @@ PROTOTYPES = {
     "evi_node_softmax_logit": (_i, [_vp, _vp, _vp, _ll, _i, _i, _f, _f, _vp, _sz, _vp, _vp, _vp]),
     "evi_gagent_start_edges": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _f, _i, _i, _vp, _vp, _vp]),
     "evi_gagent_build": (_i, [C.POINTER(GAgentArgs), _vp]),
+    "evi_retriever_loss": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _vp, _f, _f, _f, _f, _f, _vp, _vp, _vp, _vp]),
     "evi_pool_reset": (_i, [C.POINTER(PoolTable), _vp]),
     "evi_pool_insert": (_i, [C.POINTER(PoolTable), _vp, _ll, _i, _vp, _vp, C.c_ulonglong, _vp, _vp]),
     "evi_pool_expand": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, C.c_ulonglong, _i, _vp,
@@ -138,6 +139,7 @@ _KERNELS_PER_CALL = {
     "evi_node_softmax_logit": lambda a: 1 if a[5] == 0 else 3,
     "evi_gagent_start_edges": lambda a: 1,
     "evi_gagent_build": lambda a: 1,
+    "evi_retriever_loss": lambda a: 3 if a[14] else 2,
     "evi_pool_insert": lambda a: 1 if a[2] > 0 else 0,
     "evi_pool_expand": lambda a: 1 if a[4] > a[3] else 0,
     "evi_pool_candidates": lambda a: 1 if a[3] > 0 else 0,

@@ -389,6 +389,20 @@ int evi_pool_pack(const evi_pool_table* table, const unsigned long long* sel_key
                   long long* edge_attr, long long* edge_global_id, long long* node_global_ids,
                   long long* node_embedding_ids, float* topic_one_hot, cudaStream_t stream);
 
+/* ---- RetrieverLoss (src/losses/retriever_loss.py:72-178) -------------------------------------------------- */
+/* Segmented multi-positive InfoNCE (+ optional BCE) over the edges of each question (edges grouped by question,
+ * edge_ptr [B+1]); positives are targets > 0.5; edge_is_near [E] u8 or NULL selects the near / bridge edge weights
+ * (:214-217). stats [B, EVI_LOSS_STATS] and summary [EVI_LOSS_SUMMARY] are outputs:
+ *   summary = {infonce, bce, valid infonce graphs, valid bce graphs, pos edges, neg edges, graphs without pos,
+ *              graphs without neg, mean sigmoid over pos, over neg, edges, infonce_weight*infonce + bce_weight*bce}
+ * grad_logits [E] (optional, needs qid32 [E]) receives d(total)/d(logits). */
+#define EVI_LOSS_STATS 12
+#define EVI_LOSS_SUMMARY 12
+int evi_retriever_loss(const float* logits, const float* targets, const long long* edge_ptr, const int* qid32,
+                       long long num_edges, int num_graphs, const unsigned char* edge_is_near, float edge_weight_near,
+                       float edge_weight_bridge, float infonce_temperature, float infonce_weight, float bce_weight,
+                       float* stats, float* summary, float* grad_logits, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

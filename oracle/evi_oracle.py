@@ -807,3 +807,57 @@ def pool_subgraph_batch(heads, rels, tails, num_nodes: int, seeds_per_query, *, 
         "topic_one_hot": np.concatenate(topic) if topic else np.zeros((0, 2), np.float32),
         "ptr": np.asarray(ptr, dtype=np.int64), "edge_ptr": np.asarray(eptr, dtype=np.int64),
     }
+
+
+# ----------------------------------------------------------------------------------------------
+# (f) rank 4: RetrieverLoss                                   src/losses/retriever_loss.py:72-297
+# ----------------------------------------------------------------------------------------------
+def retriever_loss(logits, targets, edge_batch, num_graphs: int, *, infonce_temperature: float = 1.0,
+                   infonce_weight: float = 1.0, bce_weight: float = 0.0, edge_is_near=None,
+                   edge_weight_near: float = 1.0, edge_weight_bridge: float = 1.0):
+    """Multi-positive InfoNCE per question (``logsumexp(all) - logsumexp(positives)``, mean over questions with at
+    least one positive and one negative, :72-146) plus optional BCE (:148-178), and the analytic gradient with
+    respect to the logits. float64. Returns ``(total, grad [E], info dict)``."""
+    x = np.asarray(logits, dtype=np.float64)
+    y = np.asarray(targets, dtype=np.float64)
+    g = np.asarray(edge_batch, dtype=np.int64)
+    weighted = edge_weight_near != 1.0 or edge_weight_bridge != 1.0
+    w = np.where(np.asarray(edge_is_near, dtype=bool), edge_weight_near, edge_weight_bridge) if weighted else np.ones_like(x)
+    pos = y > 0.5
+    s = x / infonce_temperature + (np.log(np.maximum(w, 1e-6)) if weighted else 0.0)
+    grad = np.zeros_like(x)
+    inf_terms, bce_terms, inf_valid, bce_valid = [], [], [], []
+    for q in range(num_graphs):
+        m = g == q
+        if not m.any():
+            continue
+        sq, pq = s[m], pos[m]
+        if pq.any() and (~pq).any():
+            lse_all = np.logaddexp.reduce(sq)
+            lse_pos = np.logaddexp.reduce(sq[pq])
+            inf_terms.append(lse_all - lse_pos)
+            inf_valid.append(q)
+        denom = max(w[m].sum(), 1e-6) if weighted else float(m.sum())
+        if (w[m].sum() > 0) if weighted else True:
+            xb, yb = x[m], y[m]
+            bce_terms.append((w[m] * (np.maximum(xb, 0) - xb * yb + np.log1p(np.exp(-np.abs(xb))))).sum() / denom)
+            bce_valid.append((q, denom))
+    any_inf = pos.any() and (~pos).any() and len(inf_terms) > 0
+    l_inf = float(np.mean(inf_terms)) if any_inf else 0.0
+    l_bce = float(np.mean(bce_terms)) if (bce_weight > 0 and bce_terms) else 0.0
+    if any_inf and infonce_weight > 0:
+        for q in inf_valid:
+            m = g == q
+            sq, pq = s[m], pos[m]
+            d = np.exp(sq - np.logaddexp.reduce(sq))
+            d[pq] -= np.exp(sq[pq] - np.logaddexp.reduce(sq[pq]))
+            grad[m] += infonce_weight * d / (infonce_temperature * len(inf_valid))
+    if bce_weight > 0 and bce_terms:
+        for q, denom in bce_valid:
+            m = g == q
+            grad[m] += bce_weight * w[m] * (1 / (1 + np.exp(-x[m])) - y[m]) / (denom * len(bce_valid))
+    sig = 1 / (1 + np.exp(-x))
+    info = {"infonce": l_inf, "bce": l_bce, "infonce_graphs": float(len(inf_valid)) if any_inf else 0.0,
+            "pos_prob": float(sig[pos].mean()) if pos.any() else 0.0,
+            "neg_prob": float(sig[~pos].mean()) if (~pos).any() else 0.0}
+    return infonce_weight * l_inf + bce_weight * l_bce, grad, info

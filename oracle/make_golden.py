@@ -414,6 +414,53 @@ def golden_writer():
     print("writer ok", len(payload["samples"]), manifest)
 
 
+LOSS_CASES = [
+    dict(tag="infonce", kw=dict()),
+    dict(tag="temp_bce", kw=dict(infonce_temperature=0.5, infonce_weight=0.7, bce_weight=0.3)),
+    dict(tag="weighted", kw=dict(bce_weight=1.0, edge_weight_near=2.0, edge_weight_bridge=0.5)),
+    dict(tag="bce_only", kw=dict(infonce_weight=0.0, bce_weight=1.0)),
+]
+
+
+def golden_loss():
+    """Reference ``RetrieverLoss`` (src/losses/retriever_loss.py:29-297): loss, components, metrics and the autograd
+    gradient with respect to the logits. Questions: mixed, no positives, all positives, one edge, large."""
+    from src.losses.retriever_loss import RetrieverLoss
+
+    rng = np.random.default_rng(77)
+    sizes = [40, 25, 8, 1, 3000, 17]
+    eb = np.repeat(np.arange(len(sizes)), sizes)
+    E = eb.size
+    logits = (rng.standard_normal(E) * 3.0).astype(np.float32)
+    targets = (rng.random(E) < 0.08).astype(np.float32)
+    targets[eb == 1] = 0.0
+    targets[eb == 2] = 1.0
+    targets[np.nonzero(eb == 0)[0][:3]] = 1.0
+    targets[np.nonzero(eb == 5)[0][0]] = 1.0
+    near = rng.random(E) < 0.4
+    store = dict(logits=logits, targets=targets, edge_batch=eb.astype(np.int64), edge_is_near=near)
+    for case in LOSS_CASES:
+        loss_fn = RetrieverLoss(**case["kw"])
+        x = torch.from_numpy(logits).clone().requires_grad_(True)
+        out = loss_fn(types.SimpleNamespace(logits=x), torch.from_numpy(targets), edge_batch=torch.from_numpy(eb),
+                      num_graphs=len(sizes), edge_is_near=torch.from_numpy(near))
+        if out.loss.requires_grad:
+            out.loss.backward()
+        g = x.grad.numpy() if x.grad is not None else np.zeros(E, np.float32)
+        store[f"{case['tag']}_loss"] = np.array(float(out.loss))
+        store[f"{case['tag']}_grad"] = g
+        for k, v in {**out.components, **out.metrics}.items():
+            store[f"{case['tag']}_m_{k}"] = np.array(float(v))
+    # degenerate batch: no negatives anywhere -> zero InfoNCE with the short metrics dict (:84-91)
+    loss_fn = RetrieverLoss()
+    out = loss_fn(types.SimpleNamespace(logits=torch.from_numpy(logits[:8])), torch.ones(8), edge_batch=torch.zeros(8, dtype=torch.long),
+                  num_graphs=1)
+    store["allpos_loss"] = np.array(float(out.loss))
+    store["allpos_keys"] = np.array(sorted(out.metrics.keys()))
+    np.savez_compressed(os.path.join(GOLDEN, "loss.npz"), **store)
+    print("loss ok", {c["tag"]: float(store[f"{c['tag']}_loss"]) for c in LOSS_CASES})
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     Retriever, ref_ceb, brp, kind = load_reference()
@@ -424,6 +471,7 @@ def main():
     golden_scorer(Retriever)
     golden_gagent()
     golden_writer()
+    golden_loss()
     with open(os.path.join(GOLDEN, "PROVENANCE.txt"), "w", encoding="utf-8") as f:
         f.write(
             "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"

@@ -680,3 +680,57 @@ def test_writer_artifact_matches_reference(dev, golden_dir, tmp_path):
                             assert abs(x[key] - y[key]) <= 1e-6  # sigmoid: expf rounding
                         else:
                             assert x[key] == y[key], (key, x, y)
+
+
+# ------------------------------------------------------------------ (f4) RetrieverLoss
+LOSS_CASES = {
+    "infonce": dict(),
+    "temp_bce": dict(infonce_temperature=0.5, infonce_weight=0.7, bce_weight=0.3),
+    "weighted": dict(bce_weight=1.0, edge_weight_near=2.0, edge_weight_bridge=0.5),
+    "bce_only": dict(infonce_weight=0.0, bce_weight=1.0),
+}
+
+
+@pytest.mark.parametrize("tag", list(LOSS_CASES))
+def test_retriever_loss_matches_reference(dev, golden_dir, tag):
+    """Loss, components, metrics and d(loss)/d(logits) against the reference's own values (fp32 sums in a different
+    order: 2e-5 relative on the scalars, 2e-6 + 1e-4 relative on the gradient)."""
+    import types
+
+    from evi_rag_b200.loss import RetrieverLoss
+
+    g = _g(golden_dir, "loss.npz")
+    x = torch.from_numpy(g["logits"]).to(dev).requires_grad_(True)
+    out = RetrieverLoss(**LOSS_CASES[tag])(types.SimpleNamespace(logits=x), torch.from_numpy(g["targets"]),
+                                           edge_batch=torch.from_numpy(g["edge_batch"]), num_graphs=6,
+                                           edge_is_near=torch.from_numpy(g["edge_is_near"]))
+    ref_loss = float(g[f"{tag}_loss"])
+    assert abs(float(out.loss.detach()) - ref_loss) <= 2e-5 * max(1.0, abs(ref_loss))
+    (out.loss * 2.0).backward()
+    np.testing.assert_allclose(x.grad.cpu().numpy() / 2.0, g[f"{tag}_grad"], atol=2e-6, rtol=1e-4)
+    ref_metrics = {k[len(tag) + 3:]: float(g[k]) for k in g.files if k.startswith(f"{tag}_m_")}
+    got = {**out.components, **out.metrics}
+    assert set(got) == set(ref_metrics)
+    for k, v in ref_metrics.items():
+        assert abs(got[k] - v) <= 2e-5 * max(1.0, abs(v)), (k, got[k], v)
+
+
+def test_retriever_loss_degenerate_and_errors(dev, golden_dir):
+    import types
+
+    from evi_rag_b200.loss import RetrieverLoss
+
+    g = _g(golden_dir, "loss.npz")
+    out = RetrieverLoss()(types.SimpleNamespace(logits=torch.from_numpy(g["logits"][:8]).to(dev)), torch.ones(8),
+                          edge_batch=torch.zeros(8, dtype=torch.long), num_graphs=1)
+    assert float(out.loss) == float(g["allpos_loss"]) == 0.0
+    assert sorted(out.metrics.keys()) == g["allpos_keys"].tolist()
+    with pytest.raises(ValueError):
+        RetrieverLoss(path_weight=0.5)
+    with pytest.raises(ValueError):
+        RetrieverLoss(infonce_weight=0.0, bce_weight=0.0)
+    with pytest.raises(ValueError):
+        RetrieverLoss(edge_weight_near=2.0)(types.SimpleNamespace(logits=torch.zeros(4, device=dev)), torch.zeros(4),
+                                            edge_batch=torch.zeros(4, dtype=torch.long), num_graphs=1)
+    with pytest.raises(ValueError):
+        RetrieverLoss()(types.SimpleNamespace(logits=torch.zeros(4, device=dev)), torch.zeros(4), edge_batch=None)

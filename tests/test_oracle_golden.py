@@ -203,3 +203,22 @@ def test_writer_payload_matches_reference_artifact(golden_dir):
                     int(out["head_id"][b, j]), int(out["relation_id"][b, j]), int(out["tail_id"][b, j]), j + 1)
                 assert abs(t["score"] - float(out["score"][b, j])) <= 1e-7 and t["label"] == float(out["label"][b, j])
                 assert t["logit_fwd"] == float(out["logit_fwd"][b, j]) and t["logit_bwd"] == float(out["logit_bwd"][b, j])
+
+
+LOSS_CASES = {
+    "infonce": dict(),
+    "temp_bce": dict(infonce_temperature=0.5, infonce_weight=0.7, bce_weight=0.3),
+    "weighted": dict(bce_weight=1.0, edge_weight_near=2.0, edge_weight_bridge=0.5),
+    "bce_only": dict(infonce_weight=0.0, bce_weight=1.0),
+}
+
+
+@pytest.mark.parametrize("tag", list(LOSS_CASES))
+def test_retriever_loss_matches_reference(golden_dir, tag):
+    g = _load(golden_dir, "loss.npz")
+    total, grad, info = orc.retriever_loss(g["logits"], g["targets"], g["edge_batch"], 6, edge_is_near=g["edge_is_near"],
+                                           **LOSS_CASES[tag])
+    assert abs(total - float(g[f"{tag}_loss"])) <= 2e-5 * max(1.0, abs(total))
+    np.testing.assert_allclose(grad, g[f"{tag}_grad"], atol=2e-6, rtol=1e-4)
+    for k in ("infonce", "bce", "infonce_graphs", "pos_prob", "neg_prob"):
+        assert abs(info[k] - float(g[f"{tag}_m_{k}"])) <= 2e-5 * max(1.0, abs(info[k])), k
