@@ -130,15 +130,20 @@ pool_expand_kernel(PoolTable t, PoolShard s, unsigned long long* __restrict__ vi
 }
 
 // Candidates of this shard: every local edge (u -> v) whose endpoints are both visited for the query, found from
-// the head side so that each edge is seen once. EMIT = false counts per query, EMIT = true writes
-// key = (dist_u + dist_v) << 40 | edge id, (u, v) and the relation at cand_off[q] + running index.
+// the head side so that each edge is seen once. Priority class = dist_u + dist_v (clamped to kPoolPrioBins - 1).
+//   EMIT = false: cand_count[q, class] += 1 (warp-reduced per class);
+//   EMIT = true : only classes <= class_limit[q] (the class in which the running count reaches `cap`; everything
+//                 above can never survive the cut) are written: key = (dist_u + dist_v) << 40 | edge id, (u, v) and
+//                 the relation at cand_off[q] + cursor[q] (one atomicAdd per warp iteration, ballot-ranked lanes).
+constexpr int kPoolPrioBins = 8;
+
 template <bool EMIT>
 __global__ void __launch_bounds__(256)
 pool_candidates_kernel(PoolTable t, PoolShard s, const unsigned long long* __restrict__ visited,
                        unsigned long long num_visited, int* __restrict__ cand_count,
-                       const long long* __restrict__ cand_off, int* __restrict__ cursor,
-                       unsigned long long* __restrict__ cand_key, unsigned long long* __restrict__ cand_ht,
-                       int* __restrict__ cand_rel) {
+                       const int* __restrict__ class_limit, const long long* __restrict__ cand_off,
+                       int* __restrict__ cursor, unsigned long long* __restrict__ cand_key,
+                       unsigned long long* __restrict__ cand_ht, int* __restrict__ cand_rel) {
   const int lane = threadIdx.x & 31;
   const unsigned long long warp = (blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x) >> 5;
   const unsigned long long nwarps = (gridDim.x * static_cast<unsigned long long>(blockDim.x)) >> 5;
@@ -150,27 +155,70 @@ pool_candidates_kernel(PoolTable t, PoolShard s, const unsigned long long* __res
     const int r0 = s.fwd_ptr[u], r1 = s.fwd_ptr[u + 1];
     if (r0 == r1) continue;
     const int du = t.dist[pool_find(t, key)];
-    int found = 0;
-    for (int i = r0 + lane; i < r1; i += 32) {
-      const int v = s.fwd_other[i];
-      const int slot = pool_find(t, qbits | static_cast<unsigned>(v));
-      if (slot < 0) continue;
+    const int limit = EMIT ? class_limit[q] : 0;
+    if (EMIT && du > limit) continue;  // dist_v >= 0: every edge of this row is above the limit
+    int found[kPoolPrioBins];
+#pragma unroll
+    for (int b = 0; b < kPoolPrioBins; ++b) found[b] = 0;
+    for (int base = r0; base < r1; base += 32) {
+      const int i = base + lane;
+      int slot = -1, v = 0;
+      if (i < r1) {
+        v = s.fwd_other[i];
+        slot = pool_find(t, qbits | static_cast<unsigned>(v));
+      }
+      const int prio = slot >= 0 ? du + t.dist[slot] : 0;
+      const int cls = prio < kPoolPrioBins - 1 ? prio : kPoolPrioBins - 1;
       if (!EMIT) {
-        ++found;
+        if (slot >= 0) {
+#pragma unroll
+          for (int b = 0; b < kPoolPrioBins; ++b) found[b] += cls == b ? 1 : 0;
+        }
       } else {
-        const long long pos = cand_off[q] + atomicAdd(&cursor[q], 1);
-        const unsigned long long prio = static_cast<unsigned long long>(du + t.dist[slot]);
-        cand_key[pos] = (prio << kPoolEidBits) | static_cast<unsigned long long>(s.fwd_eid[i]);
-        cand_ht[pos] = (static_cast<unsigned long long>(static_cast<unsigned>(u)) << 32) | static_cast<unsigned>(v);
-        cand_rel[pos] = s.fwd_rel[i];
+        const bool take = slot >= 0 && cls <= limit;
+        const unsigned m = __ballot_sync(0xffffffffu, take);
+        if (m != 0u) {
+          long long base_pos = 0;
+          if (lane == 0) base_pos = cand_off[q] + atomicAdd(&cursor[q], __popc(m));
+          base_pos = __shfl_sync(0xffffffffu, base_pos, 0);
+          if (take) {
+            const long long pos = base_pos + __popc(m & ((1u << lane) - 1u));
+            cand_key[pos] = (static_cast<unsigned long long>(prio) << kPoolEidBits) |
+                            static_cast<unsigned long long>(s.fwd_eid[i]);
+            cand_ht[pos] = (static_cast<unsigned long long>(static_cast<unsigned>(u)) << 32) | static_cast<unsigned>(v);
+            cand_rel[pos] = s.fwd_rel[i];
+          }
+        }
       }
     }
     if (!EMIT) {
-      found = __reduce_add_sync(0xffffffffu, found);
-      if (lane == 0 && found) atomicAdd(&cand_count[q], found);
+#pragma unroll
+      for (int b = 0; b < kPoolPrioBins; ++b) {
+        const int c = __reduce_add_sync(0xffffffffu, found[b]);
+        if (lane == 0 && c) atomicAdd(&cand_count[q * kPoolPrioBins + b], c);
+      }
     }
   }
 }
+
+// per query: the class in which the running count reaches cap, and how many candidates will be emitted
+__global__ void pool_boundary_kernel(const int* __restrict__ cand_count, int num_queries, int cap,
+                                     int* __restrict__ class_limit, int* __restrict__ emit_count) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= num_queries) return;
+  long long run = 0;
+  int limit = kPoolPrioBins - 1;
+  for (int b = 0; b < kPoolPrioBins; ++b) {
+    run += cand_count[q * kPoolPrioBins + b];
+    if (run >= cap) { limit = b; break; }
+  }
+  class_limit[q] = limit;
+  emit_count[q] = static_cast<int>(run);
+}
+
+}  // namespace evi
+
+namespace evi {
 
 // ---------------------------------------------------------------------------------------------
 // Per query: keep the `cap` smallest keys of segment [seg_off[q], seg_off[q+1]) and return them ordered by edge
@@ -417,22 +465,30 @@ int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, un
 }
 
 int evi_pool_candidates(const evi_pool_table* table, const evi_pool_shard* shard, const unsigned long long* visited,
-                        unsigned long long num_visited, int emit, int* cand_count, const long long* cand_off,
-                        int* cursor, unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel,
-                        int num_sms, cudaStream_t stream) {
-  if (num_visited == 0) return kOk;
-  if (!table_ok(table) || !shard_ok(shard) || visited == nullptr) return kErrInvalidArg;
+                        unsigned long long num_visited, int emit, int num_queries, int cap, int* cand_count,
+                        int* class_limit, int* emit_count, const long long* cand_off, int* cursor,
+                        unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel, int num_sms,
+                        cudaStream_t stream) {
+  if (!table_ok(table) || !shard_ok(shard) || visited == nullptr || num_queries <= 0 || cap <= 0 ||
+      cand_count == nullptr || class_limit == nullptr || emit_count == nullptr)
+    return kErrInvalidArg;
   const int grid = static_cast<int>(num_visited * 32 / 256 + 1 < static_cast<unsigned long long>(sweep_grid(num_sms))
                                         ? num_visited * 32 / 256 + 1 : sweep_grid(num_sms));
   if (!emit) {
-    if (cand_count == nullptr) return kErrInvalidArg;
-    pool_candidates_kernel<false><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
-                                                            cand_count, nullptr, nullptr, nullptr, nullptr, nullptr);
+    if (cudaMemsetAsync(cand_count, 0, sizeof(int) * num_queries * kPoolPrioBins, stream) != cudaSuccess) return kErrCuda;
+    if (num_visited > 0)
+      pool_candidates_kernel<false><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
+                                                              cand_count, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                                              nullptr);
+    pool_boundary_kernel<<<(num_queries + 127) / 128, 128, 0, stream>>>(cand_count, num_queries, cap, class_limit,
+                                                                       emit_count);
   } else {
     if (cand_off == nullptr || cursor == nullptr || cand_key == nullptr || cand_ht == nullptr || cand_rel == nullptr)
       return kErrInvalidArg;
-    pool_candidates_kernel<true><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
-                                                           nullptr, cand_off, cursor, cand_key, cand_ht, cand_rel);
+    if (num_visited > 0)
+      pool_candidates_kernel<true><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
+                                                             nullptr, class_limit, cand_off, cursor, cand_key, cand_ht,
+                                                             cand_rel);
   }
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }

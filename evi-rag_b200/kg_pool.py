@@ -215,9 +215,22 @@ class PoolRetriever:
             for st in states:
                 st.bounds.append(int(st.visited_count.item()))
                 self._check(st)
+        self._last_state = states[0]  # kept for traversal_stats()
         sels = [self._shard_candidates(st, Q) for st in states]
         sel = self._merge(sels, Q) if multi else sels[0]
         return self._pack(states[0], sel, Q)
+
+    def traversal_stats(self) -> Dict[str, int]:
+        """Adjacency entries shard 0 read for the last batch (bandwidth accounting, not on the timed path): both
+        rows of every expanded pair, and the head row of every visited pair twice (count pass + emit pass)."""
+        st = self._last_state
+        nodes = st.visited[: st.bounds[-1]] & 0xFFFFFFFF
+        fdeg = (st.shard.fwd_ptr[nodes + 1] - st.shard.fwd_ptr[nodes]).long()
+        rdeg = (st.shard.rev_ptr[nodes + 1] - st.shard.rev_ptr[nodes]).long()
+        n_exp = st.bounds[self.depth] if self.depth < len(st.bounds) else st.bounds[-1]
+        return {"visited_pairs": int(st.bounds[-1]),
+                "expand_entries": int((fdeg[:n_exp] + rdeg[:n_exp]).sum()),
+                "candidate_entries": int(2 * fdeg.sum())}
 
     def _select(self, key, ht, rel, seg_off, Q: int):
         dev, cap = self.dev, self.cap
@@ -236,20 +249,23 @@ class PoolRetriever:
     def _shard_candidates(self, st: _ShardState, Q: int):
         L, dev, stream = self.L, self.dev, _lib.stream_handle()
         nv = st.bounds[-1]
-        count = torch.zeros(Q, dtype=torch.int32, device=dev)
-        _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 0,
-                                         count.data_ptr(), None, None, None, None, None, self.num_sms, stream),
-                   "evi_pool_candidates")
+        count = torch.empty((Q, 8), dtype=torch.int32, device=dev)
+        limit = torch.empty(Q, dtype=torch.int32, device=dev)
+        emit_count = torch.empty(Q, dtype=torch.int32, device=dev)
+        _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 0, Q, self.cap,
+                                         count.data_ptr(), limit.data_ptr(), emit_count.data_ptr(), None, None, None, None,
+                                         None, self.num_sms, stream), "evi_pool_candidates")
         off = torch.zeros(Q + 1, dtype=torch.long, device=dev)
-        off[1:] = torch.cumsum(count.long(), 0)
+        off[1:] = torch.cumsum(emit_count.long(), 0)
         total = max(int(off[-1].item()), 1)
         key = torch.empty(total, dtype=torch.long, device=dev)
         ht = torch.empty(total, dtype=torch.long, device=dev)
         rel = torch.empty(total, dtype=torch.int32, device=dev)
         cursor = torch.zeros(Q, dtype=torch.int32, device=dev)
-        _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 1, None,
-                                         off.data_ptr(), cursor.data_ptr(), key.data_ptr(), ht.data_ptr(), rel.data_ptr(),
-                                         self.num_sms, stream), "evi_pool_candidates")
+        _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 1, Q, self.cap,
+                                         count.data_ptr(), limit.data_ptr(), emit_count.data_ptr(), off.data_ptr(),
+                                         cursor.data_ptr(), key.data_ptr(), ht.data_ptr(), rel.data_ptr(), self.num_sms,
+                                         stream), "evi_pool_candidates")
         return self._select(key, ht, rel, off, Q)
 
     def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int):

@@ -108,8 +108,8 @@ PROTOTYPES = {
     "evi_pool_insert": (_i, [C.POINTER(PoolTable), _vp, _ll, _i, _vp, _vp, C.c_ulonglong, _vp, _vp]),
     "evi_pool_expand": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, C.c_ulonglong, _i, _vp,
                              C.c_ulonglong, _vp, _vp, C.c_ulonglong, _vp, _i, _vp]),
-    "evi_pool_candidates": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, _i] + [_vp] * 6 +
-                            [_i, _vp]),
+    "evi_pool_candidates": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, _i, _i, _i] +
+                            [_vp] * 8 + [_i, _vp]),
     "evi_pool_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i] + [_vp] * 8 + [_vp]),
     "evi_pool_relabel": (_i, [C.POINTER(PoolTable), _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_pool_pack": (_i, [C.POINTER(PoolTable)] + [_vp] * 4 + [_i, _i] + [_vp] * 5 + [_ll] + [_vp] * 6 + [_vp]),
@@ -142,7 +142,7 @@ _KERNELS_PER_CALL = {
     "evi_retriever_loss": lambda a: 3 if a[14] else 2,
     "evi_pool_insert": lambda a: 1 if a[2] > 0 else 0,
     "evi_pool_expand": lambda a: 1 if a[4] > a[3] else 0,
-    "evi_pool_candidates": lambda a: 1 if a[3] > 0 else 0,
+    "evi_pool_candidates": lambda a: (1 if a[3] > 0 else 0) + (0 if a[4] else 1),
     "evi_pool_select": lambda a: 1,
     "evi_pool_relabel": lambda a: 2,
     "evi_pool_pack": lambda a: 1,

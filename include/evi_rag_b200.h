@@ -365,11 +365,14 @@ int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, un
                     unsigned long long begin, unsigned long long end, int level, unsigned long long* visited_count,
                     unsigned long long visited_cap, unsigned long long* fresh, unsigned long long* fresh_count,
                     unsigned long long fresh_cap, unsigned* flags, int num_sms, cudaStream_t stream);
-/* emit == 0: cand_count [Q] += candidates of this shard; emit == 1: write them at cand_off[q] + cursor[q]++ */
+/* emit == 0: cand_count [Q, 8] = candidates of this shard per priority class (dist_h + dist_t, clamped to 7),
+ * class_limit [Q] = the class in which the running count reaches cap, emit_count [Q] = candidates of the classes up
+ * to it; emit == 1: write those at cand_off[q] + cursor[q]++ (classes above the limit cannot survive the cut) */
 int evi_pool_candidates(const evi_pool_table* table, const evi_pool_shard* shard, const unsigned long long* visited,
-                        unsigned long long num_visited, int emit, int* cand_count, const long long* cand_off,
-                        int* cursor, unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel,
-                        int num_sms, cudaStream_t stream);
+                        unsigned long long num_visited, int emit, int num_queries, int cap, int* cand_count,
+                        int* class_limit, int* emit_count, const long long* cand_off, int* cursor,
+                        unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel, int num_sms,
+                        cudaStream_t stream);
 /* per segment [seg_off[q], seg_off[q+1]): the cap smallest keys, ascending edge id; outputs [Q, cap];
  * stage_* [Q, cap] and sort_ws [Q, sort_len] (sort_len = power of two >= cap) are scratch */
 int evi_pool_select(const unsigned long long* cand_key, const unsigned long long* cand_ht, const int* cand_rel,

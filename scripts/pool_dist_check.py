@@ -36,6 +36,7 @@ def main():
     ap.add_argument("--k", type=int, default=500)
     ap.add_argument("--table", type=int, default=1 << 26)
     ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--hub-seeds", action="store_true", help="draw seeds in proportion to degree (popular entities)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -61,7 +62,10 @@ def main():
     model.load_state_dict(sd, strict=True)
     model.to(dev)
     model.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(rel))
-    seeds = rng.integers(0, args.nodes, args.queries).astype(np.int64)  # one seed per query, uniform (mostly low degree)
+    if args.hub_seeds:
+        seeds = h[rng.integers(0, args.triples, args.queries)].astype(np.int64)  # endpoint of a random triple
+    else:
+        seeds = rng.integers(0, args.nodes, args.queries).astype(np.int64)  # uniform: mostly low-degree entities
     sp = np.arange(args.queries + 1, dtype=np.int64)
     qemb = torch.from_numpy((rng.standard_normal((args.queries, 1024)) * 0.5).astype(np.float32))
 
@@ -84,8 +88,15 @@ def main():
         t2 = time.perf_counter()
         times["extract_ms"].append((t1 - t0) * 1e3)
         times["score_ms"].append((t2 - t1) * 1e3)
+    # adjacency entries the traversal reads on this shard: both rows of every pair expanded (levels 0..depth-1), and
+    # the head row of every visited pair twice (count pass + emit pass); each entry costs 4 B of adjacency + an
+    # 8 B hash probe (+ 12 B of relation / edge id when emitted)
+    stats = pr.traversal_stats()
     out = {"world": world, "triples": args.triples, "nodes": args.nodes, "queries": args.queries, "cap": args.cap, "k": args.k,
-           "candidates": int(b.edge_ptr[-1]), "extract_ms": min(times["extract_ms"]), "score_ms": min(times["score_ms"])}
+           "candidates": int(b.edge_ptr[-1]), "extract_ms": min(times["extract_ms"]), "score_ms": min(times["score_ms"]), **stats}
+    entries = stats["expand_entries"] + stats["candidate_entries"]
+    out["traversal_entries_per_s"] = entries / (out["extract_ms"] * 1e-3)
+    out["traversal_algorithmic_GBps"] = entries * 12 / (out["extract_ms"] * 1e-3) / 1e9
     if world > 1:
         if rank == 0:  # the same queries over the whole pool on one shard
             dist_group_world = pr.world
