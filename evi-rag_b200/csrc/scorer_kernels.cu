@@ -777,101 +777,129 @@ static size_t chunk_workspace_bytes(long long num_edges, int direction, int want
   return total + 256;
 }
 
+// One chunk of edges = three stages that can be enqueued separately (the pipelined mode overlaps the tensor-bound
+// stage of chunk c with the HBM-bound stages of its neighbours):
+//   operand  edge_operand_kernel -> M16, SC16, SCAL
+//   gemm     W_iv m -> MM, W_sc sc -> S
+//   tail     z assembly, LN, GELU, v-dot, softmax combine -> logits (or the features path)
 template <int FMT>
-static int score_chunk(const evi_score_args& a, long long e0, long long E, uint8_t* ws, size_t ws_bytes,
-                       cudaStream_t stream, cudaEvent_t time_begin, cudaEvent_t time_end) {
-  const int do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
-  const size_t nd = static_cast<size_t>(do_f + do_b);
-  size_t off = 0;
-  auto take = [&](size_t bytes) {
-    uint8_t* p = ws + off;
-    off += (bytes + 255) & ~static_cast<size_t>(255);
-    return p;
-  };
-  const size_t n = static_cast<size_t>(E);
-  uint16_t* M16 = reinterpret_cast<uint16_t*>(take(n * D * 2));
-  uint16_t* SC16 = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
-  float* MM = reinterpret_cast<float*>(take(n * D * sizeof(float)));
-  float* S = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
-  float4* SCAL = reinterpret_cast<float4*>(take(n * sizeof(float4)));
-  uint16_t* G = nullptr;
-  float* FEAT = nullptr;
-  if (a.want_features) {
-    G = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
-    FEAT = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
-  }
-  if (off > ws_bytes) return kErrWorkspace;
-  uint16_t* sc_f = SC16;
-  uint16_t* sc_b = SC16 + (do_f ? n * D : 0);
-  float* logits = a.logits ? a.logits + e0 : nullptr;
-  float* logits_fwd = a.logits_fwd ? a.logits_fwd + e0 : nullptr;
-  float* logits_bwd = a.logits_bwd ? a.logits_bwd + e0 : nullptr;
-  float* edge_emb = a.edge_embeddings ? a.edge_embeddings + static_cast<size_t>(e0) * D : nullptr;
+struct ChunkPlan {
+  const evi_score_args& a;
+  long long e0, E;
+  int do_f, do_b;
+  size_t nd, n;
+  uint16_t *M16, *SC16, *G;
+  float *MM, *S, *FEAT;
+  float4* SCAL;
+  bool ok;
 
-  StructParams sp;
-  sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
-  const long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
-  const int grid = static_cast<int>(want < 8LL * a.num_sms ? want : 8LL * a.num_sms);
-  edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
-      a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
-      static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
-      a.num_rel_rows, a.num_questions, a.flags, M16, sc_f, sc_b, SCAL);
-  if (check_launch() != kOk) return kErrCuda;
+  ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes)
+      : a(args), e0(e0_), E(E_), G(nullptr), FEAT(nullptr) {
+    do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
+    nd = static_cast<size_t>(do_f + do_b);
+    n = static_cast<size_t>(E);
+    size_t off = 0;
+    auto take = [&](size_t bytes) {
+      uint8_t* p = ws + off;
+      off += (bytes + 255) & ~static_cast<size_t>(255);
+      return p;
+    };
+    M16 = reinterpret_cast<uint16_t*>(take(n * D * 2));
+    SC16 = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
+    MM = reinterpret_cast<float*>(take(n * D * sizeof(float)));
+    S = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
+    SCAL = reinterpret_cast<float4*>(take(n * sizeof(float4)));
+    if (a.want_features) {
+      G = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
+      FEAT = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
+    }
+    ok = off <= ws_bytes;
+  }
+
+  int operand(cudaStream_t stream) const {
+    uint16_t* sc_f = SC16;
+    uint16_t* sc_b = SC16 + (do_f ? n * D : 0);
+    StructParams sp;
+    sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
+    const long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
+    const int grid = static_cast<int>(want < 8LL * a.num_sms ? want : 8LL * a.num_sms);
+    edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
+        a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
+        static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
+        a.num_rel_rows, a.num_questions, a.flags, M16, sc_f, sc_b, SCAL);
+    return check_launch();
+  }
 
   // state_net.0 split by input block (weight columns [iv | sc | err | dist], retriever.py:470-481):
   //   W_iv m -> MM (once per edge, shared by both directions),  W_sc sc_dir -> S (once per edge and direction)
-  const uint16_t* w1 = static_cast<const uint16_t*>(a.w1_main16);
-  gemm::EpiF32Tma::Params plain;
-  plain.bias = nullptr;
-  for (int i = 0; i < 8; ++i) plain.act[i] = gemm::kActNone;
-  int rc = gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, a.num_sms, stream, nullptr, MM, D);
-  if (rc != kOk) return rc;
-  if (time_begin) cudaEventRecord(time_begin, stream);
-  rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, a.num_sms, stream, nullptr, S, D);
-  if (time_end) cudaEventRecord(time_end, stream);
-  if (rc != kOk) return rc;
-
-  TailParams tp;
-  tp.w_dist = a.w1_dist_col, tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
-  const float* s_f = do_f ? S : nullptr;
-  const float* s_b = do_b ? S + (do_f ? n * D : 0) : nullptr;
-  uint16_t* g_f = G;
-  uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
-  const int tgrid = static_cast<int>((E + 7) / 8);
-  const bool feats = a.want_features != 0;
-  static const bool legacy_tail = getenv("EVI_TAIL_LEGACY") != nullptr;  // A/B switch: register-fed tail
-  if (legacy_tail) {
-    score_tail_kernel<FMT><<<tgrid, 256, 0, stream>>>(
-        MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
-        a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
-        feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
-  } else {
-    static bool attr_set[2] = {false, false};
-    if (!attr_set[FMT]) {
-      if (cudaFuncSetAttribute(score_tail_bulk_kernel<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               kTailSmemBytes) != cudaSuccess)
-        return kErrCuda;
-      attr_set[FMT] = true;
-    }
-    const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
-    const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
-    score_tail_bulk_kernel<FMT><<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
-        MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
-        a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
-        feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
+  int gemms(cudaStream_t stream, int gemm_sms, cudaEvent_t time_begin, cudaEvent_t time_end) const {
+    const uint16_t* w1 = static_cast<const uint16_t*>(a.w1_main16);
+    gemm::EpiF32Tma::Params plain;
+    plain.bias = nullptr;
+    for (int i = 0; i < 8; ++i) plain.act[i] = gemm::kActNone;
+    int rc = gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, gemm_sms, stream, nullptr, MM, D);
+    if (rc != kOk) return rc;
+    if (time_begin) cudaEventRecord(time_begin, stream);
+    rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, gemm_sms, stream, nullptr, S, D);
+    if (time_end) cudaEventRecord(time_end, stream);
+    return rc;
   }
-  if (check_launch() != kOk) return kErrCuda;
-  if (!feats) return kOk;
-  // feature path: state_net.4 as a second GEMM, logits from the fp32 features, softmax-weighted blend
-  gemm::EpiBiasF32::Params fp;
-  fp.bias = a.w2_bias, fp.out32 = FEAT, fp.ld32 = D;
-  rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(nd * n), D, D, fp, a.num_sms, stream);
-  if (rc != kOk) return rc;
-  const float* f_f = do_f ? FEAT : nullptr;
-  const float* f_b = do_b ? FEAT + (do_f ? n * D : 0) : nullptr;
-  feature_blend_kernel<<<tgrid, 256, 0, stream>>>(f_f, f_b, a.head_w, a.head_b, E, edge_emb, logits, logits_fwd,
-                                                  logits_bwd);
-  return check_launch();
+
+  // tail_mode 0: TMA ring (persistent, 192 KB of shared memory per CTA); 1: register-fed, `tail_threads` per CTA
+  // (no shared memory, so its CTAs fit beside a resident GEMM CTA)
+  int tail(cudaStream_t stream, int tail_mode, int tail_threads) const {
+    float* logits = a.logits ? a.logits + e0 : nullptr;
+    float* logits_fwd = a.logits_fwd ? a.logits_fwd + e0 : nullptr;
+    float* logits_bwd = a.logits_bwd ? a.logits_bwd + e0 : nullptr;
+    float* edge_emb = a.edge_embeddings ? a.edge_embeddings + static_cast<size_t>(e0) * D : nullptr;
+    TailParams tp;
+    tp.w_dist = a.w1_dist_col, tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
+    const float* s_f = do_f ? S : nullptr;
+    const float* s_b = do_b ? S + (do_f ? n * D : 0) : nullptr;
+    uint16_t* g_f = G;
+    uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
+    const bool feats = a.want_features != 0;
+    if (tail_mode == 1) {
+      const int warps = tail_threads / 32;
+      const int tgrid = static_cast<int>((E + warps - 1) / warps);
+      score_tail_kernel<FMT><<<tgrid, tail_threads, 0, stream>>>(
+          MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+          a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
+          feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
+    } else {
+      static bool attr_set[2] = {false, false};
+      if (!attr_set[FMT]) {
+        if (cudaFuncSetAttribute(score_tail_bulk_kernel<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 kTailSmemBytes) != cudaSuccess)
+          return kErrCuda;
+        attr_set[FMT] = true;
+      }
+      const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
+      const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
+      score_tail_bulk_kernel<FMT><<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
+          MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+          a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
+          feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
+    }
+    if (check_launch() != kOk) return kErrCuda;
+    if (!feats) return kOk;
+    // feature path: state_net.4 as a second GEMM, logits from the fp32 features, softmax-weighted blend
+    gemm::EpiBiasF32::Params fp;
+    fp.bias = a.w2_bias, fp.out32 = FEAT, fp.ld32 = D;
+    int rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(nd * n), D, D, fp, a.num_sms, stream);
+    if (rc != kOk) return rc;
+    const float* f_f = do_f ? FEAT : nullptr;
+    const float* f_b = do_b ? FEAT + (do_f ? n * D : 0) : nullptr;
+    const int tgrid = static_cast<int>((E + 7) / 8);
+    feature_blend_kernel<<<tgrid, 256, 0, stream>>>(f_f, f_b, a.head_w, a.head_b, E, edge_emb, logits, logits_fwd,
+                                                    logits_bwd);
+    return check_launch();
+  }
+};
+
+static int env_int(const char* name, int fallback) {
+  const char* v = getenv(name);
+  return v != nullptr && *v != '\0' ? atoi(v) : fallback;
 }
 
 template <int FMT>
@@ -887,14 +915,75 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   const size_t per = chunk_workspace_bytes(chunk, a.direction, a.want_features);
   if (a.workspace_bytes < per) return kErrWorkspace;
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
-  for (long long c = 0; c < nchunks; ++c) {
-    const bool timed = c == (nchunks > 1 ? 1 : 0);
-    const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-    const int rc = score_chunk<FMT>(a, e0, n, ws, per, stream, timed ? static_cast<cudaEvent_t>(a.ev_gemm_begin) : nullptr,
-                                    timed ? static_cast<cudaEvent_t>(a.ev_gemm_end) : nullptr);
-    if (rc != kOk) return rc;
+  // experiment knobs (A/B on the GPU box): tail kernel flavour / CTA size, SMs given to the GEMM
+  static const int tail_mode_serial = env_int("EVI_TAIL_LEGACY", 0) ? 1 : 0;
+  static const int tail_mode_pipe = env_int("EVI_PIPE_TAIL", 1);
+  static const int tail_threads = env_int("EVI_TAIL_THREADS", 128);
+  static const int gemm_sms_env = env_int("EVI_GEMM_SMS", 0);
+  const int gemm_sms = gemm_sms_env > 0 && gemm_sms_env < a.num_sms ? gemm_sms_env : a.num_sms;
+  cudaStream_t aux = static_cast<cudaStream_t>(a.aux_stream);
+  const bool pipelined = aux != nullptr && aux != stream && nchunks >= 2 && a.workspace_bytes >= 2 * per &&
+                         !a.want_features;
+  if (!pipelined) {
+    for (long long c = 0; c < nchunks; ++c) {
+      const bool timed = c == (nchunks > 1 ? 1 : 0);
+      const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
+      ChunkPlan<FMT> plan(a, e0, n, ws, per);
+      if (!plan.ok) return kErrWorkspace;
+      int rc = plan.operand(stream);
+      if (rc != kOk) return rc;
+      rc = plan.gemms(stream, gemm_sms, timed ? static_cast<cudaEvent_t>(a.ev_gemm_begin) : nullptr,
+                      timed ? static_cast<cudaEvent_t>(a.ev_gemm_end) : nullptr);
+      if (rc != kOk) return rc;
+      rc = plan.tail(stream, tail_mode_serial, 256);
+      if (rc != kOk) return rc;
+    }
+    return kOk;
   }
-  return kOk;
+  // Pipelined over two streams and two workspace halves: the GEMMs of chunk c (caller's stream, tensor-bound) run
+  // while the aux stream does the tail of chunk c-1 and the operand rows of chunk c+1 (HBM-bound; their CTAs use no
+  // shared memory and fit beside the resident GEMM CTAs). Aux-stream order: op0, op1, tail0, op2, tail1, ...
+  // so op(c) follows tail(c-2) (same workspace half) and gemm(c) waits for op(c), which follows tail(c-2).
+  const int n_ev = static_cast<int>(2 * nchunks + 2);
+  cudaEvent_t evs[2 * 64 + 2];
+  if (nchunks > 64) return kErrUnsupported;
+  for (int i = 0; i < n_ev; ++i)
+    if (cudaEventCreateWithFlags(&evs[i], cudaEventDisableTiming) != cudaSuccess) return kErrCuda;
+  cudaEvent_t* ev_op = evs;
+  cudaEvent_t* ev_g = evs + nchunks;
+  cudaEvent_t ev_start = evs[2 * nchunks], ev_end = evs[2 * nchunks + 1];
+  auto plan_of = [&](long long c) {
+    const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
+    return ChunkPlan<FMT>(a, e0, n, ws + (c & 1) * per, per);
+  };
+  int rc = kOk;
+  cudaEventRecord(ev_start, stream);
+  cudaStreamWaitEvent(aux, ev_start, 0);
+  rc = plan_of(0).operand(aux);
+  cudaEventRecord(ev_op[0], aux);
+  for (long long c = 0; c < nchunks && rc == kOk; ++c) {
+    const bool timed = c == 1;
+    cudaStreamWaitEvent(stream, ev_op[c], 0);
+    rc = plan_of(c).gemms(stream, gemm_sms, timed ? static_cast<cudaEvent_t>(a.ev_gemm_begin) : nullptr,
+                          timed ? static_cast<cudaEvent_t>(a.ev_gemm_end) : nullptr);
+    cudaEventRecord(ev_g[c], stream);
+    if (rc == kOk && c >= 1) {
+      cudaStreamWaitEvent(aux, ev_g[c - 1], 0);
+      rc = plan_of(c - 1).tail(aux, tail_mode_pipe, tail_threads);
+    }
+    if (rc == kOk && c + 1 < nchunks) {
+      rc = plan_of(c + 1).operand(aux);
+      cudaEventRecord(ev_op[c + 1], aux);
+    }
+  }
+  if (rc == kOk) {
+    cudaStreamWaitEvent(aux, ev_g[nchunks - 1], 0);
+    rc = plan_of(nchunks - 1).tail(aux, tail_mode_pipe, tail_threads);
+  }
+  cudaEventRecord(ev_end, aux);
+  cudaStreamWaitEvent(stream, ev_end, 0);  // the caller's stream owns the results again
+  for (int i = 0; i < n_ev; ++i) cudaEventDestroy(evs[i]);
+  return rc;
 }
 
 }  // namespace evi

@@ -43,6 +43,7 @@ class ScoreArgs(C.Structure):
         ("workspace", _vp), ("workspace_bytes", _sz),
         ("ev_gemm_begin", _vp), ("ev_gemm_end", _vp),
         ("chunk_edges", _ll),
+        ("aux_stream", _vp),
     ]
 
 
@@ -132,7 +133,7 @@ _KERNELS_PER_CALL = {
     "evi_project": lambda a: 1,
     "evi_relation_pairs": lambda a: 1,
     "evi_pair_context": lambda a: 1,
-    "evi_score_edges": lambda a: (6 if a[0]._obj.want_features else 4) * _num_chunks(a[0]._obj),
+    "evi_score_edges": lambda a: (6 if a[0]._obj.want_features else 4) * _num_chunks(a[0]._obj),  # same kernels in either mode
     "evi_segmented_topk": lambda a: 1,
     "evi_topk_gather_payload": lambda a: 1,
     "evi_topk_metrics": lambda a: 1,

@@ -21,6 +21,8 @@ What differs (B200 design):
 """
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 from dataclasses import dataclass
 from typing import Any, Dict, Optional
@@ -99,6 +101,7 @@ class Retriever(nn.Module):
         return_edge_embeddings: bool = False,
         max_workspace_bytes: int = 12 << 30,
         pipeline_chunks: int = 4,
+        overlap_streams: bool = False,
         validate: bool = True,
         **_: Any,
     ) -> None:
@@ -119,6 +122,10 @@ class Retriever(nn.Module):
         self.return_edge_embeddings = bool(return_edge_embeddings)
         self.max_workspace_bytes = int(max_workspace_bytes)
         self.pipeline_chunks = max(1, int(pipeline_chunks))
+        # off by default: measured on B200 the step is power-capped, overlapping the tensor-bound and HBM-bound stages
+        # lowers the clocks and leaves the step time unchanged (profiles/r01i_overlap_ab.md)
+        self.overlap_streams = bool(overlap_streams) or os.environ.get("EVI_OVERLAP", "0") == "1"
+        self._aux_stream = None
         self.validate = bool(validate)
 
         d, h = self.emb_dim, self.hidden_dim
@@ -493,8 +500,15 @@ class Retriever(nn.Module):
         chunk = min(chunk_cap, max(16384, (chunk + 1023) // 1024 * 1024))
         if chunk >= E:
             chunk = E
-        ws = self._score_workspace(int(L.evi_score_workspace_bytes(chunk, direction, int(return_features))), dev)
+        per_chunk = int(L.evi_score_workspace_bytes(chunk, direction, int(return_features)))
+        # two workspace halves + a second stream: the GEMMs of chunk c overlap the HBM-bound stages of chunks c-1 / c+1
+        overlap = self.overlap_streams and chunk < E and not return_features
+        ws = self._score_workspace(per_chunk * (2 if overlap else 1), dev)
         a = _lib.ScoreArgs()
+        if overlap:
+            if self._aux_stream is None or self._aux_stream.device != dev:
+                self._aux_stream = torch.cuda.Stream(device=dev)
+            a.aux_stream = self._aux_stream.cuda_stream
         a.emb_dim, a.hidden_dim, a.direction, a.operand_format = d, self.hidden_dim, direction, fmt
         a.want_features, a.num_sms = int(return_features), p["num_sms"]
         a.num_nodes, a.num_rel_rows, a.num_questions, a.flags = N, int(rel_repr.size(0)), B, flags.data_ptr()

@@ -200,6 +200,10 @@ typedef struct evi_score_args {
   void* ev_gemm_end;
   /* edges are processed `chunk_edges` at a time (<= 0: all at once) to bound the workspace */
   long long chunk_edges;
+  /* optional second stream (cudaStream_t): with >= 2 chunks and workspace_bytes >= 2 chunks' worth, the tensor-bound
+   * GEMMs of chunk c run on the call's stream while this stream runs the HBM-bound stages of chunks c-1 / c+1; the
+   * call's stream is joined with it before returning. NULL: everything in order on the call's stream. */
+  void* aux_stream;
 } evi_score_args;
 
 /* bytes of the per-chunk workspace for `chunk_edges` edges */

@@ -734,3 +734,35 @@ def test_retriever_loss_degenerate_and_errors(dev, golden_dir):
                                             edge_batch=torch.zeros(4, dtype=torch.long), num_graphs=1)
     with pytest.raises(ValueError):
         RetrieverLoss()(types.SimpleNamespace(logits=torch.zeros(4, device=dev)), torch.zeros(4), edge_batch=None)
+
+
+def test_overlapped_chunk_pipeline_equals_serial(dev):
+    """The two-stream chunk pipeline of evi_score_edges (GEMMs of chunk c beside tail c-1 / operand c+1) is the same
+    kernels on the same data: logits must be bit-identical to the serial order."""
+    import types
+
+    spec = tiny_spec(24, 4000, seed=9, num_relations=64, num_entities=3000)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(2)
+    ent = (rng.standard_normal((spec.num_entities + 1, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((spec.num_relations, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(4, trained_like=True)
+    outs = []
+    for overlap in (False, True):
+        from evi_rag_b200.retriever import Retriever
+
+        model = Retriever(emb_dim=1024, hidden_dim=1024, pipeline_chunks=4, overlap_streams=overlap).eval()
+        model.load_state_dict(sd, strict=True)
+        model.to(dev)
+        model.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(rel))
+        batch = types.SimpleNamespace(
+            edge_index=torch.from_numpy(qb.edge_index), ptr=torch.from_numpy(qb.ptr),
+            question_emb=torch.from_numpy(qb.question_emb), node_embedding_ids=torch.from_numpy(qb.node_embedding_ids),
+            edge_attr=torch.from_numpy(qb.edge_attr), topic_one_hot=torch.from_numpy(qb.topic_one_hot))
+        out = model(batch)
+        torch.cuda.synchronize()
+        assert qb.num_edges > 4 * 16384  # really several chunks
+        outs.append((out.logits.clone(), out.logits_fwd.clone(), out.logits_bwd.clone()))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
