@@ -62,25 +62,36 @@ def dist_env():
 # ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle restatement of the reference algorithm on the host cores
 # ------------------------------------------------------------------------------------------------
+CPU_STAGE_SECONDS = {"gather+scoring": 0.0, "topk+payload": 0.0, "adjacency+bfs": 0.0}
+
+
 def cpu_reference_step(qb, sd, ent, rel, k=TOP_K):
     """One pass of the reference's path on the CPU for batch ``qb``: CPU index_select of the
     embedding rows (embedding_store.py:101-150), Retriever.forward in fp32 (same op order as the
     reference, per-edge projections included), writer-style sigmoid + per-graph top-k + gathers,
-    and the per-question adjacency build + multi-source BFS of the dataset builder."""
+    and the per-question adjacency build + multi-source BFS of the dataset builder. Stage times
+    accumulate in CPU_STAGE_SECONDS (CPU baseline timing plan steps 3-5)."""
     from oracle import evi_oracle as orc
 
     t = torch.from_numpy
+    t0 = time.perf_counter()
     node_rows = ent.index_select(0, t(qb.node_embedding_ids))
     edge_rows = rel.index_select(0, t(qb.edge_attr))
     out = orc.retriever_forward(sd, edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
                                 node_embeddings=node_rows, node_embedding_ids=t(qb.node_embedding_ids),
                                 edge_embeddings=edge_rows, topic_one_hot=t(qb.topic_one_hot))
+    t1 = time.perf_counter()
     payload = orc.writer_payload(out.logits.numpy(), out.logits_fwd.numpy(), out.logits_bwd.numpy(), qb.edge_index,
                                  qb.edge_attr, np.zeros(qb.num_edges, np.float32), qb.node_global_ids, qb.edge_ptr, k)
+    t2 = time.perf_counter()
     for b in range(qb.num_graphs):
         n0, n1, e0, e1 = qb.ptr[b], qb.ptr[b + 1], qb.edge_ptr[b], qb.edge_ptr[b + 1]
         adj = orc.build_undirected_adjacency(int(n1 - n0), qb.edge_index[0, e0:e1] - n0, qb.edge_index[1, e0:e1] - n0)
         orc.bfs_dist(int(n1 - n0), adj, qb.q_local_indices[qb.q_ptr[b]:qb.q_ptr[b + 1]] - n0)
+    t3 = time.perf_counter()
+    CPU_STAGE_SECONDS["gather+scoring"] += t1 - t0
+    CPU_STAGE_SECONDS["topk+payload"] += t2 - t1
+    CPU_STAGE_SECONDS["adjacency+bfs"] += t3 - t2
     return payload
 
 
@@ -91,11 +102,18 @@ def time_cpu(spec, sd, ent, rel, questions_per_step, steps, warmup):
                                   q_count=questions_per_step) for i in range(steps + warmup)]
     for qb in batches[:warmup]:
         cpu_reference_step(qb, sd, ent_t, rel_t)
+    for key in CPU_STAGE_SECONDS:
+        CPU_STAGE_SECONDS[key] = 0.0
     t0 = time.perf_counter()
     for qb in batches[warmup:]:
         cpu_reference_step(qb, sd, ent_t, rel_t)
     dt = time.perf_counter() - t0
     return steps * questions_per_step / dt, dt
+
+
+def cpu_stage_qps(num_questions):
+    """questions/s of each CPU stage alone over the timed sample."""
+    return {key: (num_questions / sec if sec > 0 else None) for key, sec in CPU_STAGE_SECONDS.items()}
 
 
 def run_reference(args):
@@ -116,7 +134,8 @@ def run_reference(args):
         "cpu_baseline": {"value": qps, "unit": "questions/s", "cores": cores, "kind": "port",
                          "sample": f"{args.steps} steps x {args.ref_questions_per_step} questions of the same workload; "
                                    "oracle port of the reference (pure-Python reference cannot travel), torch fp32, "
-                                   f"{cores} threads"},
+                                   f"{cores} threads",
+                         "stage_questions_per_s": cpu_stage_qps(args.steps * args.ref_questions_per_step)},
         "e2e": {"value": qps, "unit": "questions/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -344,7 +363,7 @@ def run_ours(args):
         "gpu_launches": int(launches_all),
         "clocks": clocks,
         "roofline": {
-            "bound": "tensor", "kernel": "gemm_kernel<EpiStoreF32> (W_sc block of state_net.0: [2E_chunk,1024]x[1024,1024]; "
+            "bound": "tensor", "kernel": "gemm2::gemm2_kernel<EpiF32Tma> (W_sc block of state_net.0: [2E_chunk,1024]x[1024,1024]; "
                                          "flops counted = executed by that launch)",
             "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
             "traffic": roofline_traffic(), "peak_source": peak_src,
@@ -360,7 +379,8 @@ def run_ours(args):
         line["cpu_baseline"] = {"value": qps, "unit": "questions/s", "cores": os.cpu_count() or 1, "kind": "port",
                                 "sample": f"{n_steps * per} questions of the same workload in batches of {per} after one "
                                           f"warm-up batch; oracle port of the reference path (torch fp32, "
-                                          f"{os.cpu_count()} threads), {dt:.1f} s"}
+                                          f"{os.cpu_count()} threads), {dt:.1f} s",
+                                "stage_questions_per_s": cpu_stage_qps(n_steps * per)}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
