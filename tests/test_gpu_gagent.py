@@ -185,3 +185,30 @@ def test_gagent_errors(dev):
         GA.GAgentSettings(edge_top_k=0)
     with pytest.raises(ValueError):
         GA.GAgentSettings(start_min_edges=9, start_max_edges=3)
+
+
+def test_gagent_question_without_edges_is_skipped(dev):
+    """g_agent_builder.py:205-207: a question with no edges is skipped, the others are unaffected."""
+    import types
+
+    ei = torch.tensor([[0, 1, 5, 6], [1, 2, 6, 5]])
+    ptr = torch.tensor([0, 3, 5, 7])             # q1 has nodes 3..4 and no edges
+    batch = types.SimpleNamespace(ptr=ptr, edge_index=ei, edge_attr=torch.tensor([0, 1, 2, 2]), labels=torch.tensor([1., 0, 0, 1]),
+                                  node_global_ids=torch.arange(100, 107), node_embedding_ids=torch.arange(7),
+                                  sample_id=["a", "b", "c"])
+
+    class Store:
+        def load_sample(self, sid):
+            return {"question_emb": [0.0, 1.0], "question": sid, "seed_entity_ids": {"a": [100], "c": [105]}[sid],
+                    "answer_entity_ids": {"a": [102], "c": [106]}[sid]}
+
+    out = types.SimpleNamespace(logits=torch.tensor([0.5, -1.0, 2.0, 0.1], device=dev), query_ids=torch.tensor([0, 0, 2, 2]))
+    builder = GA.GAgentBuilder(GA.GAgentSettings(edge_top_k=8), embedding_store=Store())
+    builder.process_batch(batch, out)
+    assert [s.sample_id for s in builder.samples] == ["a", "c"]
+    a, c = builder.samples
+    assert a.node_entity_ids.tolist() == [100, 101, 102] and a.edge_head_locals.tolist() == [0, 1]
+    assert c.node_entity_ids.tolist() == [105, 106] and c.edge_relations.tolist() == [2, 2]
+    assert c.start_node_locals.tolist() == [0] and c.answer_node_locals.tolist() == [1] and c.question_emb.shape == (1, 2)
+    builder.process_batch(batch, types.SimpleNamespace(logits=torch.empty(0, device=dev), query_ids=torch.empty(0)))
+    assert len(builder.samples) == 2

@@ -130,3 +130,31 @@ def test_pool_retrieve_scores_and_topk(dev):
         want = ref_b["edge_global_id"][ref_b["edge_ptr"][q] + idx[q, :kt]]
         assert np.array_equal(res["edge_id"][q, :kt].cpu().numpy(), want)
         assert (res["edge_id"][q, kt:] == -1).all()
+
+
+def test_pool_edge_cases(dev):
+    """A query without valid seeds yields an empty subgraph; depth 0 keeps only seed-to-seed edges; an isolated seed
+    yields no candidates; counts and pointers stay consistent."""
+    num_nodes = 50
+    h = np.array([0, 1, 2, 3, 3, 7], dtype=np.int64)
+    t = np.array([1, 2, 3, 3, 0, 8], dtype=np.int64)
+    r = np.arange(6, dtype=np.int64)
+    shard = TriplePoolShard.from_triples(h, r, t, np.arange(6), num_nodes, dev)
+    seeds = np.array([-1, 99, 0, 1, 40, 3], dtype=np.int64)      # q0: invalid only, q1: {0, 1}, q2: isolated, q3: {3}
+    sp = np.array([0, 2, 4, 5, 6], dtype=np.int64)
+    for depth in (0, 2):
+        pr = PoolRetriever([shard], model=None, cap=16, top_k=4, depth=depth, table_capacity=1 << 10)
+        b = pr.extract(seeds, sp)
+        ref = orc.pool_subgraph_batch(h, r, t, num_nodes, [seeds[sp[q]:sp[q + 1]].tolist() for q in range(4)], depth=depth,
+                                      cap=16)
+        assert np.array_equal(b.edge_ptr.cpu().numpy(), ref["edge_ptr"])
+        assert np.array_equal(b.edge_global_id.cpu().numpy(), ref["edge_global_id"])
+        assert np.array_equal(b.ptr.cpu().numpy(), ref["ptr"])
+        assert int(b.edge_ptr[1]) == 0 and int(b.edge_ptr[3]) == int(b.edge_ptr[2])
+    assert ref["edge_global_id"].tolist()[:1] == [0]  # depth 2 from {0, 1} starts with edge 0
+    with pytest.raises(ValueError):
+        PoolRetriever([shard], model=None, cap=0)
+    with pytest.raises(ValueError):
+        PoolRetriever([shard], model=None, table_capacity=1000)
+    with pytest.raises(ValueError):
+        TriplePoolShard.from_triples([0], [0], [60], [0], num_nodes, dev)
