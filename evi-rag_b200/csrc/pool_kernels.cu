@@ -8,7 +8,7 @@
 // Data layout. A shard owns a subset of the triples, indexed twice by GLOBAL node id: rows by head (fwd) and rows
 // by tail (rev), each row a contiguous run of (other endpoint, relation, global edge id), so one warp reads a row
 // with coalesced 4-byte loads. The visited set of a query batch is one open-addressing hash table keyed by
-// (query << 32 | node) with the hop distance as value: HBM-bound integer work, no tensor cores.
+// (query << 32 | node) with the hop distance packed in the same word: HBM-bound integer work, no tensor cores.
 //
 //   evi_pool_expand      warp per frontier pair: insert every neighbour (both directions) at dist level+1
 //   evi_pool_insert      thread per pair: merge the pairs other shards discovered (the frontier exchange)
@@ -25,9 +25,13 @@ constexpr unsigned long long kPoolEmpty = ~0ull;
 constexpr int kPoolEidBits = 40;
 constexpr unsigned long long kPoolEidMask = (1ull << kPoolEidBits) - 1ull;
 
+// One 8-byte word per slot: hop distance in the top 6 bits, (query << 32 | node) below, so a lookup is ONE random
+// access (a separate distance array costs a second DRAM sector per probe: 146 B per scanned entry measured).
+constexpr int kPoolDistShift = 58;
+constexpr unsigned long long kPoolKeyMask = (1ull << kPoolDistShift) - 1ull;
+
 struct PoolTable {
-  unsigned long long* keys;  // [capacity] (query << 32 | node), kPoolEmpty when free
-  unsigned char* dist;       // [capacity]
+  unsigned long long* keys;  // [capacity] dist << 58 | query << 32 | node, kPoolEmpty when free
   int* local_id;             // [capacity] scratch of evi_pool_relabel
   unsigned mask;             // capacity - 1 (capacity is a power of two)
 };
@@ -42,13 +46,13 @@ EVI_DEVINL unsigned long long pool_mix(unsigned long long x) {  // splitmix64 fi
 EVI_DEVINL int pool_insert(const PoolTable& t, unsigned long long key, unsigned char d, unsigned* slot_out) {
   unsigned slot = static_cast<unsigned>(pool_mix(key)) & t.mask;
   for (unsigned probe = 0; probe <= t.mask; ++probe) {
-    const unsigned long long prev = atomicCAS(&t.keys[slot], kPoolEmpty, key);
+    const unsigned long long prev =
+        atomicCAS(&t.keys[slot], kPoolEmpty, key | (static_cast<unsigned long long>(d) << kPoolDistShift));
     if (prev == kPoolEmpty) {
-      t.dist[slot] = d;
       if (slot_out) *slot_out = slot;
       return 1;
     }
-    if (prev == key) {
+    if ((prev & kPoolKeyMask) == key) {
       if (slot_out) *slot_out = slot;
       return 0;
     }
@@ -56,12 +60,16 @@ EVI_DEVINL int pool_insert(const PoolTable& t, unsigned long long key, unsigned 
   }
   return -1;
 }
-EVI_DEVINL int pool_find(const PoolTable& t, unsigned long long key) {
+// slot of `key` (or -1); *dist receives its hop distance
+EVI_DEVINL int pool_find(const PoolTable& t, unsigned long long key, int* dist = nullptr) {
   unsigned slot = static_cast<unsigned>(pool_mix(key)) & t.mask;
   for (unsigned probe = 0; probe <= t.mask; ++probe) {
     const unsigned long long cur = t.keys[slot];
-    if (cur == key) return static_cast<int>(slot);
     if (cur == kPoolEmpty) return -1;
+    if ((cur & kPoolKeyMask) == key) {
+      if (dist) *dist = static_cast<int>(cur >> kPoolDistShift);
+      return static_cast<int>(slot);
+    }
     slot = (slot + 1) & t.mask;
   }
   return -1;
@@ -154,7 +162,8 @@ pool_candidates_kernel(PoolTable t, PoolShard s, const unsigned long long* __res
     const int u = static_cast<int>(key & 0xFFFFFFFFull);
     const int r0 = s.fwd_ptr[u], r1 = s.fwd_ptr[u + 1];
     if (r0 == r1) continue;
-    const int du = t.dist[pool_find(t, key)];
+    int du = 0;
+    pool_find(t, key, &du);
     const int limit = EMIT ? class_limit[q] : 0;
     if (EMIT && du > limit) continue;  // dist_v >= 0: every edge of this row is above the limit
     int found[kPoolPrioBins];
@@ -162,12 +171,12 @@ pool_candidates_kernel(PoolTable t, PoolShard s, const unsigned long long* __res
     for (int b = 0; b < kPoolPrioBins; ++b) found[b] = 0;
     for (int base = r0; base < r1; base += 32) {
       const int i = base + lane;
-      int slot = -1, v = 0;
+      int slot = -1, v = 0, dv = 0;
       if (i < r1) {
         v = s.fwd_other[i];
-        slot = pool_find(t, qbits | static_cast<unsigned>(v));
+        slot = pool_find(t, qbits | static_cast<unsigned>(v), &dv);
       }
-      const int prio = slot >= 0 ? du + t.dist[slot] : 0;
+      const int prio = slot >= 0 ? du + dv : 0;
       const int cls = prio < kPoolPrioBins - 1 ? prio : kPoolPrioBins - 1;
       if (!EMIT) {
         if (slot >= 0) {
@@ -361,12 +370,13 @@ __global__ void pool_assign_kernel(PoolTable t, const unsigned long long* __rest
 #pragma unroll
   for (int side = 0; side < 2; ++side) {
     const unsigned node = static_cast<unsigned>(side == 0 ? (ht >> 32) : (ht & 0xFFFFFFFFull));
-    const int slot = pool_find(t, qbits | node);
+    int dn = 0;
+    const int slot = pool_find(t, qbits | node, &dn);
     if (atomicCAS(&t.local_id[slot], -2, -3) == -2) {
       const int id = atomicAdd(&node_count[q], 1);
       t.local_id[slot] = id;
       node_global[static_cast<size_t>(q) * 2 * cap + id] = static_cast<int>(node);
-      node_is_seed[static_cast<size_t>(q) * 2 * cap + id] = t.dist[slot] == 0 ? 1 : 0;
+      node_is_seed[static_cast<size_t>(q) * 2 * cap + id] = dn == 0 ? 1 : 0;
     }
   }
 }
@@ -410,11 +420,11 @@ using namespace evi;
 namespace {
 
 inline bool table_ok(const evi_pool_table* t) {
-  return t != nullptr && t->keys != nullptr && t->dist != nullptr && t->local_id != nullptr && t->capacity >= 2 &&
+  return t != nullptr && t->keys != nullptr && t->local_id != nullptr && t->capacity >= 2 &&
          (t->capacity & (t->capacity - 1)) == 0 && t->capacity <= (1ull << 32);
 }
 inline PoolTable as_table(const evi_pool_table* t) {
-  return PoolTable{t->keys, t->dist, t->local_id, static_cast<unsigned>(t->capacity - 1)};
+  return PoolTable{t->keys, t->local_id, static_cast<unsigned>(t->capacity - 1)};
 }
 inline bool shard_ok(const evi_pool_shard* s) {
   return s != nullptr && s->fwd_ptr != nullptr && s->rev_ptr != nullptr && s->num_nodes > 0;
@@ -441,7 +451,7 @@ int evi_pool_insert(const evi_pool_table* table, const unsigned long long* pairs
                     unsigned* flags, cudaStream_t stream) {
   if (num_pairs <= 0) return kOk;
   if (!table_ok(table) || pairs == nullptr || visited == nullptr || visited_count == nullptr || flags == nullptr ||
-      dist_value < 0 || dist_value > 254)
+      dist_value < 0 || dist_value > 62)
     return kErrInvalidArg;
   pool_insert_kernel<<<static_cast<int>((num_pairs + 255) / 256), 256, 0, stream>>>(
       as_table(table), pairs, num_pairs, dist_value, visited, visited_count, visited_cap, flags);
@@ -454,7 +464,7 @@ int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, un
                     unsigned long long fresh_cap, unsigned* flags, int num_sms, cudaStream_t stream) {
   if (end <= begin) return kOk;
   if (!table_ok(table) || !shard_ok(shard) || visited == nullptr || visited_count == nullptr || flags == nullptr ||
-      level < 0 || level > 253 || (fresh != nullptr && fresh_count == nullptr))
+      level < 0 || level > 61 || (fresh != nullptr && fresh_count == nullptr))
     return kErrInvalidArg;
   const unsigned long long warps = end - begin;
   const int grid = static_cast<int>(warps * 32 / 256 + 1 < static_cast<unsigned long long>(sweep_grid(num_sms))

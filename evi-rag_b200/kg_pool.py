@@ -103,8 +103,7 @@ class _ShardState:
 
     def __init__(self, shard: TriplePoolShard, table_capacity: int, visited_cap: int, dev):
         self.shard = shard
-        self.keys = torch.empty(table_capacity, dtype=torch.long, device=dev)
-        self.dist = torch.empty(table_capacity, dtype=torch.uint8, device=dev)
+        self.keys = torch.empty(table_capacity, dtype=torch.long, device=dev)  # dist << 58 | query << 32 | node
         self.local_id = torch.empty(table_capacity, dtype=torch.int32, device=dev)
         self.visited = torch.empty(visited_cap, dtype=torch.long, device=dev)
         self.visited_count = torch.zeros(1, dtype=torch.long, device=dev)
@@ -112,7 +111,7 @@ class _ShardState:
         self.fresh_count = torch.zeros(1, dtype=torch.long, device=dev)
         self.flags = torch.zeros(1, dtype=torch.int32, device=dev)
         self.table = _lib.PoolTable()
-        self.table.keys, self.table.dist = self.keys.data_ptr(), self.dist.data_ptr()
+        self.table.keys = self.keys.data_ptr()
         self.table.local_id, self.table.capacity = self.local_id.data_ptr(), table_capacity
         self.cshard = shard.c_struct()
         self.bounds = [0]
@@ -123,13 +122,13 @@ class PoolRetriever:
 
     def __init__(self, shards: Sequence[TriplePoolShard], model: Any, *, node_embedding_ids: Optional[torch.Tensor] = None,
                  cap: int = 20000, top_k: int = 500, depth: int = 2, table_capacity: int = 1 << 22,
-                 visited_cap: Optional[int] = None, group=None, num_sms: int = 148) -> None:
+                 max_table_capacity: int = 1 << 30, group=None, num_sms: int = 148) -> None:
         if not shards:
             raise ValueError("at least one shard is required")
         if not (0 < cap <= _lib.POOL_MAX_CAP):
             raise ValueError(f"cap must be in [1, {_lib.POOL_MAX_CAP}], got {cap}")
-        if not (0 <= depth <= 250):
-            raise ValueError(f"depth must be in [0, 250], got {depth}")
+        if not (0 <= depth <= 60):
+            raise ValueError(f"depth must be in [0, 60], got {depth}")
         if table_capacity & (table_capacity - 1):
             raise ValueError("table_capacity must be a power of two")
         self.shards = list(shards)
@@ -138,8 +137,10 @@ class PoolRetriever:
         if self.dev.type != "cuda":
             raise RuntimeError("PoolRetriever runs on CUDA tensors only (no CPU fallback).")
         self.cap, self.top_k, self.depth = int(cap), int(top_k), int(depth)
+        # the table starts small (32 MB of keys at 2^22 slots: L2-resident probes) and is re-sized x4 whenever a batch
+        # fills half of it; the size that worked is kept for the next batch
         self.table_capacity = int(table_capacity)
-        self.visited_cap = int(visited_cap) if visited_cap is not None else self.table_capacity // 2
+        self.max_table_capacity = max(int(max_table_capacity), self.table_capacity)
         self.node_embedding_ids = None if node_embedding_ids is None else \
             node_embedding_ids.to(device=self.dev, dtype=torch.long).contiguous()
         self.group = group
@@ -163,43 +164,31 @@ class PoolRetriever:
         dist.all_gather_into_tensor(out, buf, group=self.group)
         return [out[r * m: r * m + sizes[r]] for r in range(self.world)]
 
-    def _check(self, st: _ShardState) -> None:
-        word = int(st.flags.item())
-        if word & _lib.POOL_TABLE_FULL:
-            raise RuntimeError("visited hash table full: raise table_capacity or use smaller query batches")
-        if word & _lib.POOL_VISITED_FULL:
-            raise RuntimeError("visited list full: raise visited_cap or use smaller query batches")
-
-    # ------------------------------------------------------------------ steps 1-2: BFS + candidate cut
-    def extract(self, seeds: torch.Tensor, seed_ptr: torch.Tensor) -> types.SimpleNamespace:
-        """``seeds`` = global node ids grouped by ``seed_ptr [Q+1]``. Returns the subgraph batch (device tensors under
-        the reference's PyG attribute names) plus ``edge_global_id [E]`` and ``edge_ptr [Q+1]``."""
+    def _traverse(self, seed_pairs: torch.Tensor) -> Optional[List[_ShardState]]:
+        """Depth-capped BFS of the whole batch on every local shard with the per-level frontier exchange. Returns the
+        shard states, or None when the visited set outgrew the table (the caller re-sizes and repeats)."""
         L, dev, stream = self.L, self.dev, _lib.stream_handle()
-        seeds = torch.as_tensor(seeds, dtype=torch.long, device=dev).view(-1)
-        seed_ptr = torch.as_tensor(seed_ptr, dtype=torch.long, device=dev).view(-1)
-        Q = int(seed_ptr.numel() - 1)
-        num_nodes = self.shards[0].num_nodes
-        qid = torch.repeat_interleave(torch.arange(Q, device=dev), seed_ptr[1:] - seed_ptr[:-1])
-        ok = (seeds >= 0) & (seeds < num_nodes)  # out-of-range sources are ignored (:616-618)
-        seed_pairs = torch.where(ok, (qid << 32) | seeds.clamp(min=0), torch.full_like(seeds, _EMPTY)).contiguous()
-        states = [_ShardState(s, self.table_capacity, self.visited_cap, dev) for s in self.shards]
+        visited_cap = self.table_capacity // 4  # load factor <= 0.25 keeps linear-probe chains and CAS retries short
+        states = [_ShardState(s, self.table_capacity, visited_cap, dev) for s in self.shards]
         multi = len(states) > 1 or self.world > 1
         for st in states:
             _lib.check(L.evi_pool_reset(C.byref(st.table), stream), "evi_pool_reset")
             _lib.check(L.evi_pool_insert(C.byref(st.table), seed_pairs.data_ptr(), int(seed_pairs.numel()), 0,
-                                         st.visited.data_ptr(), st.visited_count.data_ptr(), self.visited_cap,
+                                         st.visited.data_ptr(), st.visited_count.data_ptr(), visited_cap,
                                          st.flags.data_ptr(), stream), "evi_pool_insert")
-            st.bounds.append(int(st.visited_count.item()))
+            st.bounds.append(min(int(st.visited_count.item()), visited_cap))
+        if self._overflowed(states):
+            return None
         for level in range(self.depth):
             for st in states:
                 st.fresh_count.zero_()
                 _lib.check(L.evi_pool_expand(
                     C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), st.bounds[level], st.bounds[level + 1],
-                    level, st.visited_count.data_ptr(), self.visited_cap, st.fresh.data_ptr() if multi else None,
-                    st.fresh_count.data_ptr() if multi else None, self.visited_cap, st.flags.data_ptr(), self.num_sms,
+                    level, st.visited_count.data_ptr(), visited_cap, st.fresh.data_ptr() if multi else None,
+                    st.fresh_count.data_ptr() if multi else None, visited_cap, st.flags.data_ptr(), self.num_sms,
                     stream), "evi_pool_expand")
             if multi:  # frontier exchange: every shard learns the pairs the others reached at this level
-                lists = [st.fresh[: int(st.fresh_count.item())] for st in states]
+                lists = [st.fresh[: min(int(st.fresh_count.item()), visited_cap)] for st in states]
                 if self.world > 1:
                     remote = self._gather_var(lists[0], int(lists[0].numel()))
                     others_of = [[remote[r] for r in range(self.world) if r != self.rank]]
@@ -211,10 +200,43 @@ class PoolRetriever:
                             pairs = pairs.contiguous()
                             _lib.check(L.evi_pool_insert(C.byref(st.table), pairs.data_ptr(), int(pairs.numel()), level + 1,
                                                          st.visited.data_ptr(), st.visited_count.data_ptr(),
-                                                         self.visited_cap, st.flags.data_ptr(), stream), "evi_pool_insert")
+                                                         visited_cap, st.flags.data_ptr(), stream), "evi_pool_insert")
             for st in states:
-                st.bounds.append(int(st.visited_count.item()))
-                self._check(st)
+                st.bounds.append(min(int(st.visited_count.item()), visited_cap))
+            if self._overflowed(states):
+                return None
+        return states
+
+    def _overflowed(self, states: List[_ShardState]) -> bool:
+        """True when any shard (on any rank) filled its table beyond half or overran its visited list."""
+        word = torch.stack([st.flags for st in states]).max().view(1)
+        if self.world > 1:
+            dist.all_reduce(word, op=dist.ReduceOp.MAX, group=self.group)
+        return int(word.item()) != 0
+
+    # ------------------------------------------------------------------ steps 1-2: BFS + candidate cut
+    def extract(self, seeds: torch.Tensor, seed_ptr: torch.Tensor) -> types.SimpleNamespace:
+        """``seeds`` = global node ids grouped by ``seed_ptr [Q+1]``. Returns the subgraph batch (device tensors under
+        the reference's PyG attribute names) plus ``edge_global_id [E]`` and ``edge_ptr [Q+1]``."""
+        dev = self.dev
+        seeds = torch.as_tensor(seeds, dtype=torch.long, device=dev).view(-1)
+        seed_ptr = torch.as_tensor(seed_ptr, dtype=torch.long, device=dev).view(-1)
+        Q = int(seed_ptr.numel() - 1)
+        if Q >= (1 << 26):
+            raise ValueError("at most 2^26 queries per batch (query id bits of the visited-table key)")
+        num_nodes = self.shards[0].num_nodes
+        qid = torch.repeat_interleave(torch.arange(Q, device=dev), seed_ptr[1:] - seed_ptr[:-1])
+        ok = (seeds >= 0) & (seeds < num_nodes)  # out-of-range sources are ignored (:616-618)
+        seed_pairs = torch.where(ok, (qid << 32) | seeds.clamp(min=0), torch.full_like(seeds, _EMPTY)).contiguous()
+        while True:
+            states = self._traverse(seed_pairs)
+            if states is not None:
+                break
+            if self.table_capacity >= self.max_table_capacity:
+                raise RuntimeError(f"visited set does not fit {self.max_table_capacity} table slots: use smaller query "
+                                   "batches or raise max_table_capacity")
+            self.table_capacity = min(self.table_capacity * 4, self.max_table_capacity)
+        multi = len(states) > 1 or self.world > 1
         self._last_state = states[0]  # kept for traversal_stats()
         sels = [self._shard_candidates(st, Q) for st in states]
         sel = self._merge(sels, Q) if multi else sels[0]

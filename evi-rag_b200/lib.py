@@ -71,7 +71,7 @@ class PoolShard(C.Structure):
 class PoolTable(C.Structure):
     """``evi_pool_table`` (include/evi_rag_b200.h)."""
 
-    _fields_ = [("keys", _vp), ("dist", _vp), ("local_id", _vp), ("capacity", C.c_ulonglong)]
+    _fields_ = [("keys", _vp), ("local_id", _vp), ("capacity", C.c_ulonglong)]
 
 
 POOL_TABLE_FULL, POOL_VISITED_FULL, POOL_MAX_CAP = 1, 2, 32768

@@ -353,8 +353,7 @@ typedef struct evi_pool_shard {
   int num_nodes;
 } evi_pool_shard;
 typedef struct evi_pool_table {
-  unsigned long long* keys;   /* [capacity] */
-  unsigned char* dist;        /* [capacity] */
+  unsigned long long* keys;   /* [capacity] hop distance << 58 | query << 32 | node (queries < 2^26, depth <= 62) */
   int* local_id;              /* [capacity] */
   unsigned long long capacity;/* power of two */
 } evi_pool_table;

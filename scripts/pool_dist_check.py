@@ -34,7 +34,7 @@ def main():
     ap.add_argument("--queries", type=int, default=64)
     ap.add_argument("--cap", type=int, default=20000)
     ap.add_argument("--k", type=int, default=500)
-    ap.add_argument("--table", type=int, default=1 << 26)
+    ap.add_argument("--table", type=int, default=1 << 22, help="initial visited-table slots (grows x4 on overflow)")
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--hub-seeds", action="store_true", help="draw seeds in proportion to degree (popular entities)")
     args = ap.parse_args()
@@ -93,7 +93,7 @@ def main():
     # 8 B hash probe (+ 12 B of relation / edge id when emitted)
     stats = pr.traversal_stats()
     out = {"world": world, "triples": args.triples, "nodes": args.nodes, "queries": args.queries, "cap": args.cap, "k": args.k,
-           "candidates": int(b.edge_ptr[-1]), "extract_ms": min(times["extract_ms"]), "score_ms": min(times["score_ms"]), **stats}
+           "candidates": int(b.edge_ptr[-1]), "table_slots": pr.table_capacity, "extract_ms": min(times["extract_ms"]), "score_ms": min(times["score_ms"]), **stats}
     entries = stats["expand_entries"] + stats["candidate_entries"]
     out["traversal_entries_per_s"] = entries / (out["extract_ms"] * 1e-3)
     out["traversal_algorithmic_GBps"] = entries * 12 / (out["extract_ms"] * 1e-3) / 1e9

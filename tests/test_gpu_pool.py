@@ -65,8 +65,9 @@ def test_pool_candidates_match_oracle(dev, world, cap):
     shards = make_shards(h, r, t, num_nodes, world, dev)
     seeds, sp = make_queries(11, num_nodes, 12)
     emb_ids = torch.arange(num_nodes) * 3 % 1000
-    pr = PoolRetriever(shards, model=None, node_embedding_ids=emb_ids, cap=cap, top_k=50, depth=2, table_capacity=1 << 18)
+    pr = PoolRetriever(shards, model=None, node_embedding_ids=emb_ids, cap=cap, top_k=50, depth=2, table_capacity=1 << 10)
     b = pr.extract(seeds, sp)
+    assert pr.table_capacity > 1 << 10  # the visited set outgrew the first table: re-sized and repeated
     ref = orc.pool_subgraph_batch(h, r, t, num_nodes, [seeds[sp[q]:sp[q + 1]].tolist() for q in range(12)], depth=2,
                                   cap=cap, node_embedding_ids=emb_ids.numpy())
     assert np.array_equal(b.edge_ptr.cpu().numpy(), ref["edge_ptr"])
