@@ -766,3 +766,75 @@ def test_overlapped_chunk_pipeline_equals_serial(dev):
         outs.append((out.logits.clone(), out.logits_fwd.clone(), out.logits_bwd.clone()))
     for a, b in zip(*outs):
         assert torch.equal(a, b)
+
+
+# ------------------------------------------------------------------ full-size properties (BASELINE config[1] step)
+def test_full_size_step_properties(dev):
+    """One bench-sized step (128 WebQSP-shaped questions, ~635k edges, the size the oracle cannot finish in seconds)
+    checked through size-independent properties: top-k order / uniqueness / counts, the softmax combine identity of
+    retriever.py:369-381, BFS level structure, and run-to-run bit stability."""
+    from evi_rag_b200.pipeline import RetrievalPipeline, device_batch, host_batch
+    from evi_rag_b200.retriever import Retriever
+    from evi_rag_b200.synthetic import WEBQSP_10K, make_embedding_tables
+
+    spec, k = WEBQSP_10K, 100
+    model = Retriever(emb_dim=1024, hidden_dim=1024).eval()
+    model.load_state_dict(make_state_dict(0, trained_like=True), strict=True)
+    model.to(dev)
+    ent, rel = make_embedding_tables(spec)
+    model.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(rel))
+    qb = generate_questions(spec, q_start=256, q_count=128)
+    b = device_batch(host_batch(qb, pin=False), dev)
+    pipe = RetrievalPipeline(model, top_k=k, bfs_max_depth=2, writer_scores=True, validate=True)
+    res = pipe.run_device(b)
+    res2 = pipe.run_device(device_batch(host_batch(qb, pin=False), dev))
+    torch.cuda.synchronize()
+    assert int(res["flags"].item()) == 0
+    E, B = qb.num_edges, qb.num_graphs
+    assert E > 400_000
+    ecount = torch.from_numpy(np.diff(qb.edge_ptr)).to(dev)
+    # top-k: counts, descending scores, unique in-range indices, padding
+    assert torch.equal(res["count"].long(), torch.clamp(ecount, max=k))
+    valid = torch.arange(k, device=dev).unsqueeze(0) < res["count"].unsqueeze(1)
+    sc = res["score"]
+    assert bool(((sc[:, :-1] >= sc[:, 1:]) | ~valid[:, 1:]).all())
+    assert bool(((sc >= 0) & (sc <= 1))[valid].all())  # writer flavour: sigmoid scores (fp32 saturates to 1.0)
+    idx = res["index"].long()
+    assert bool(((idx >= 0) & (idx < ecount.unsqueeze(1)))[valid].all()) and bool((idx[~valid] == -1).all())
+    srt = torch.sort(torch.where(valid, idx, torch.arange(k, device=dev).unsqueeze(0) + 10 ** 7), dim=1).values
+    assert bool((srt[:, 1:] != srt[:, :-1]).all())
+    # every selected score is >= every unselected score of its question (checked through the k-th score)
+    out = model(b)
+    sig = torch.sigmoid(out.logits)
+    kth = torch.where(valid, sc, torch.full_like(sc, 2.0)).min(dim=1).values
+    qid = torch.repeat_interleave(torch.arange(B, device=dev), ecount)
+    sel = torch.zeros(E, dtype=torch.bool, device=dev)
+    gidx = (idx + torch.from_numpy(qb.edge_ptr[:-1]).to(dev).unsqueeze(1))[valid]
+    sel[gidx] = True
+    assert bool((sig[~sel] <= kth[qid][~sel] + 1e-7).all())
+    # softmax combine identity: logit = w_f * logit_f + w_b * logit_b with w = softmax([logit_f, logit_b])
+    lf, lb = out.logits_fwd.double(), out.logits_bwd.double()
+    w = torch.softmax(torch.stack([lf, lb], dim=-1), dim=-1)
+    comb = w[:, 0] * lf + w[:, 1] * lb
+    assert float((comb - out.logits.double()).abs().max()) <= 1e-5 * max(1.0, float(out.logits.abs().max()))
+    assert bool(torch.isfinite(out.logits).all())
+    # BFS (depth cap 2): seeds are 0, values in {-1, 0, 1, 2}, reached endpoints of an edge differ by <= 1, and every
+    # node at distance d > 0 has a neighbour at d - 1
+    dist = res["bfs_dist"].long()
+    seeds = torch.from_numpy(qb.q_local_indices).to(dev)
+    assert bool((dist[seeds] == 0).all()) and int(dist.min()) >= -1 and int(dist.max()) <= 2
+    u, v = b.edge_index[0], b.edge_index[1]
+    both = (dist[u] >= 0) & (dist[v] >= 0)
+    assert bool(((dist[u] - dist[v]).abs()[both] <= 1).all())
+    inf = torch.full_like(dist, 99)
+    dpos = torch.where(dist >= 0, dist, inf)
+    best = inf.clone()
+    best.scatter_reduce_(0, u, dpos[v], reduce="amin")
+    best.scatter_reduce_(0, v, dpos[u], reduce="amin")
+    pos = dist > 0
+    assert bool((best[pos] == dist[pos] - 1).all())
+    frontier1 = (dist == -1) & (best <= 1)  # an unreached node next to a node at distance <= 1 would be a miss
+    assert not bool(frontier1.any())
+    # bit-stable run to run
+    for key in ("score", "index", "count", "head_id", "tail_id", "relation_id", "bfs_dist"):
+        assert torch.equal(res[key], res2[key]), key
