@@ -471,16 +471,36 @@ class Retriever(nn.Module):
                 "rebuild g_retrieval caches or update configs/build_retrieval_pipeline.yaml."
             )
         topic = topic.contiguous()
-        rev = getattr(batch, "reverse_edge_index", None)
-        if rev is not None and torch.is_tensor(rev):
-            raise NotImplementedError("reverse_edge_index override is not supported (the dataset never sets it).")
-        ns_dim = 2 * (1 + self.dde.num_rounds + self.dde.num_reverse_rounds)
+        rf, rr = self.dde.num_rounds, self.dde.num_reverse_rounds
+        ns_dim = 2 * (1 + rf + rr)
         node_struct = torch.empty((N, ns_dim), dtype=torch.float32, device=dev)
         dde_ws = self._workspace(int(L.evi_dde_workspace_bytes(N)), dev)
-        st = L.evi_dde_forward(head32.data_ptr(), tail32.data_ptr(), E, N, topic.data_ptr(), topic.size(1),
-                               self.dde.num_rounds, self.dde.num_reverse_rounds, node_struct.data_ptr(),
-                               dde_ws.data_ptr(), dde_ws.numel(), stream)
-        _lib.check(st, "evi_dde_forward")
+
+        def dde(h32, t32, n_edges, fwd_rounds, rev_rounds, out):
+            st_ = L.evi_dde_forward(h32.data_ptr(), t32.data_ptr(), n_edges, N, topic.data_ptr(), topic.size(1),
+                                    fwd_rounds, rev_rounds, out.data_ptr(), dde_ws.data_ptr(), dde_ws.numel(), stream)
+            _lib.check(st_, "evi_dde_forward")
+
+        rev = getattr(batch, "reverse_edge_index", None)
+        if rev is not None and torch.is_tensor(rev):
+            # retriever.py:547-550 / graph.py:47-51: the reverse rounds propagate over the given edge list (source ->
+            # target) instead of the flipped one. Two launches of the same kernel (forward rounds only) and a column
+            # stitch into the (x0, f1..fRf, r1..rRr) layout; the dataset never sets this attribute.
+            rev = rev.to(device=dev, dtype=torch.long)
+            if rev.dim() != 2 or rev.size(0) != 2:
+                raise ValueError(f"reverse_edge_index must have shape [2, E], got {tuple(rev.shape)}")
+            if rev.numel() and (int(rev.min()) < 0 or int(rev.max()) >= N):
+                raise ValueError("reverse_edge_index out of range for node embeddings.")
+            part_f = torch.empty((N, 2 * (1 + rf)), dtype=torch.float32, device=dev)
+            part_r = torch.empty((N, 2 * (1 + rr)), dtype=torch.float32, device=dev)
+            dde(head32, tail32, E, rf, 0, part_f)
+            rh, rt = rev[0].to(torch.int32).contiguous(), rev[1].to(torch.int32).contiguous()
+            dde(rh, rt, int(rh.numel()), rr, 0, part_r)
+            ns3 = node_struct.view(N, 2, 1 + rf + rr)
+            ns3[:, :, : 1 + rf] = part_f.view(N, 2, 1 + rf)
+            ns3[:, :, 1 + rf:] = part_r.view(N, 2, 1 + rr)[:, :, 1:]
+        else:
+            dde(head32, tail32, E, rf, rr, node_struct)
         node_uv = torch.empty((N, 2 * d), dtype=torch.float32, device=dev)
         _lib.check(L.evi_struct_project(node_struct.data_ptr(), N, ns_dim, p["ws_t"].data_ptr(), p["bs"].data_ptr(),
                                         node_uv.data_ptr(), stream), "evi_struct_project")

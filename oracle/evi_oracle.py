@@ -73,9 +73,11 @@ def dde_node_features(
     num_rounds: int = 2,
     num_reverse_rounds: int = 2,
     num_topics: int = 2,
+    reverse_edge_index: Optional[torch.Tensor] = None,
 ) -> torch.Tensor:
     """Node structure features ``[N, C*(1+R_f+R_r)]`` laid out per topic class
-    ``[c0:(x0,f1..,r1..), c1:(...)]`` (retriever.py:519-553, graph.py:41-74)."""
+    ``[c0:(x0,f1..,r1..), c1:(...)]`` (retriever.py:519-553, graph.py:41-74). ``reverse_edge_index`` replaces the
+    flipped edge list of the reverse rounds (retriever.py:547-550)."""
     x0 = topic_one_hot.to(torch.float32)[:, :num_topics]
     feats = [x0]
     h = x0
@@ -83,8 +85,10 @@ def dde_node_features(
         h = _mean_propagate(h, edge_index[0], edge_index[1])
         feats.append(h)
     h = x0
+    rsrc, rdst = (edge_index[1], edge_index[0]) if reverse_edge_index is None else \
+        (reverse_edge_index[0].long(), reverse_edge_index[1].long())  # edge_index.flip(0), graph.py:47-48
     for _ in range(num_reverse_rounds):
-        h = _mean_propagate(h, edge_index[1], edge_index[0])  # edge_index.flip(0), graph.py:47-48
+        h = _mean_propagate(h, rsrc, rdst)
         feats.append(h)
     stacked = torch.stack(feats, dim=-1)
     return stacked.reshape(stacked.size(0), -1)
@@ -141,6 +145,7 @@ def retriever_forward(
     num_reverse_rounds: int = 2,
     want_features: bool = False,
     edge_chunk: int = 32768,
+    reverse_edge_index: Optional[torch.Tensor] = None,
 ) -> OracleOutput:
     """``Retriever._forward_impl`` in eval mode (retriever.py:195-289), fp32, same op order as the
     reference (per-edge relation / gate / bias projections included). Edges are processed in
@@ -159,7 +164,8 @@ def retriever_forward(
     mask = node_embedding_ids.long() == 0  # retriever.py:499-506
     if bool(mask.any()):
         node_repr = torch.where(mask.unsqueeze(-1), non_text.unsqueeze(0), node_repr)
-    ns = dde_node_features(topic_one_hot, edge_index.long(), num_rounds, num_reverse_rounds)
+    ns = dde_node_features(topic_one_hot, edge_index.long(), num_rounds, num_reverse_rounds,
+                           reverse_edge_index=reverse_edge_index)
 
     lf_all, lb_all, lo_all, fe_all = [], [], [], []
     for s in range(0, E, edge_chunk):

@@ -121,7 +121,14 @@ def golden_dde(Retriever):
         b = types.SimpleNamespace(topic_one_hot=torch.from_numpy(topic))
         ns = m._build_node_structure_features(b, edge_index=torch.from_numpy(edge_index), num_nodes=n)
         res[f"ns_{rf}_{rr}"] = ns.numpy()
-    np.savez_compressed(os.path.join(GOLDEN, "dde.npz"), edge_index=edge_index, topic=topic, **res)
+    # batch.reverse_edge_index override (retriever.py:547-550): the reverse rounds use this list instead of the flip
+    rev = np.stack([rng.integers(0, n, 90), rng.integers(0, n, 90)]).astype(np.int64)
+    for rf, rr in [(2, 2), (1, 3)]:
+        m = Retriever(emb_dim=8, hidden_dim=8, dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr})
+        b = types.SimpleNamespace(topic_one_hot=torch.from_numpy(topic), reverse_edge_index=torch.from_numpy(rev))
+        ns = m._build_node_structure_features(b, edge_index=torch.from_numpy(edge_index), num_nodes=n)
+        res[f"ns_rev_{rf}_{rr}"] = ns.numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "dde.npz"), edge_index=edge_index, topic=topic, reverse_edge_index=rev, **res)
     print("dde ok")
 
 

@@ -838,3 +838,43 @@ def test_full_size_step_properties(dev):
     # bit-stable run to run
     for key in ("score", "index", "count", "head_id", "tail_id", "relation_id", "bfs_dist"):
         assert torch.equal(res[key], res2[key]), key
+
+
+def test_reverse_edge_index_override(dev, golden_dir):
+    """batch.reverse_edge_index (retriever.py:547-550): the flipped list reproduces the default path bit for bit; an
+    unrelated list matches the oracle (whose DDE is pinned to the reference for this case by tests/golden/dde.npz)."""
+    import types
+
+    from evi_rag_b200.retriever import Retriever
+
+    g = _g(golden_dir, "scorer_d1024_trained.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    sd = make_state_dict(seed, dim, dim, rf, rr, trained_like=bool(trained))
+    model = Retriever(emb_dim=dim, hidden_dim=dim, dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr}).eval()
+    model.load_state_dict(sd, strict=True)
+    model.to(dev)
+    rel = torch.from_numpy(g["relation_table"])
+
+    def batch(**kw):
+        return types.SimpleNamespace(
+            edge_index=torch.from_numpy(g["edge_index"]), ptr=torch.from_numpy(g["ptr"]),
+            question_emb=torch.from_numpy(g["question_emb"]), node_embedding_ids=torch.from_numpy(g["node_embedding_ids"]),
+            edge_attr=torch.from_numpy(g["edge_attr"]), node_embeddings=torch.from_numpy(g["entity_rows"]),
+            edge_embeddings=rel[torch.from_numpy(g["edge_attr"])], topic_one_hot=torch.from_numpy(g["topic_one_hot"]), **kw)
+
+    base = model(batch()).logits
+    flipped = model(batch(reverse_edge_index=torch.from_numpy(g["edge_index"]).flip(0))).logits
+    assert torch.equal(base, flipped)
+    n = int(g["ptr"][-1])
+    rng = np.random.default_rng(1)
+    rev = torch.from_numpy(np.stack([rng.integers(0, n, 300), rng.integers(0, n, 300)]).astype(np.int64))
+    got = model(batch(reverse_edge_index=rev)).logits.cpu().numpy()
+    ref = orc.retriever_forward(
+        sd, edge_index=torch.from_numpy(g["edge_index"]), ptr=torch.from_numpy(g["ptr"]),
+        question_emb=torch.from_numpy(g["question_emb"]), node_embeddings=torch.from_numpy(g["entity_rows"]),
+        node_embedding_ids=torch.from_numpy(g["node_embedding_ids"]), edge_embeddings=rel[torch.from_numpy(g["edge_attr"])],
+        topic_one_hot=torch.from_numpy(g["topic_one_hot"]), num_rounds=rf, num_reverse_rounds=rr, reverse_edge_index=rev)
+    check_scores(got, ref.logits.numpy(), "fp16", "reverse_edge_index", small=True)
+    assert not np.allclose(got, base.cpu().numpy(), atol=1e-3)  # the override really changes the structure features
+    with pytest.raises(ValueError):
+        model(batch(reverse_edge_index=torch.tensor([[0, n + 5], [1, 2]])))

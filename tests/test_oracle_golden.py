@@ -53,6 +53,10 @@ def test_dde_corner_cases(golden_dir):
     for rf, rr in [(2, 2), (4, 4), (1, 0), (0, 0)]:
         ns = orc.dde_node_features(torch.from_numpy(g["topic"]), torch.from_numpy(g["edge_index"]), rf, rr)
         np.testing.assert_allclose(ns.numpy(), g[f"ns_{rf}_{rr}"], atol=1e-7, rtol=0)
+    for rf, rr in [(2, 2), (1, 3)]:
+        ns = orc.dde_node_features(torch.from_numpy(g["topic"]), torch.from_numpy(g["edge_index"]), rf, rr,
+                                   reverse_edge_index=torch.from_numpy(g["reverse_edge_index"]))
+        np.testing.assert_allclose(ns.numpy(), g[f"ns_rev_{rf}_{rr}"], atol=1e-7, rtol=0)
 
 
 def test_edge_batch(golden_dir):
