@@ -517,7 +517,7 @@ class Retriever(nn.Module):
         per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features))) / float(1 << 20)
         chunk_cap = max(1024, int(self.max_workspace_bytes / per_edge) // 1024 * 1024)
         chunk = -(-E // self.pipeline_chunks)
-        chunk = min(chunk_cap, max(16384, (chunk + 1023) // 1024 * 1024))
+        chunk = min(chunk_cap, max(int(os.environ.get("EVI_MIN_CHUNK", "16384")), (chunk + 1023) // 1024 * 1024))
         if chunk >= E:
             chunk = E
         per_chunk = int(L.evi_score_workspace_bytes(chunk, direction, int(return_features)))
