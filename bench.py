@@ -288,13 +288,14 @@ def run_ours(args):
     evilib.LAUNCHES["kernels"] = 0
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    chunk_edges = []
+    chunk_edges, chunk_counts = [], []
     for i in range(args.steps):
         model.gemm_events = gemm_ev[i]
         b = dev_batches[args.warmup + i]
         res = pipe.run_device(b)
         exchange(res, b.num_graphs, args.warmup + i)
         chunk_edges.append(model.last_chunk_edges)
+        chunk_counts.append(model.last_num_chunks)
     e1.record()
     sync_all()
     model.gemm_events = None
@@ -367,7 +368,9 @@ def run_ours(args):
                                          "flops counted = executed by that launch)",
             "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
             "traffic": roofline_traffic(), "peak_source": peak_src,
-            "ms_per_launch": float(np.mean(gemm_ms)), "share_of_step": float(np.sum(gemm_ms)) / ms_dev,
+            "ms_per_launch": float(np.mean(gemm_ms)), "launches_per_step": float(np.mean(chunk_counts)),
+            # one W_sc launch per step carries the events (a full-sized chunk); the step runs one such launch per chunk
+            "share_of_step": float(np.sum([ms * c for ms, c in zip(gemm_ms, chunk_counts)])) / ms_dev,
             "step_algorithmic_tflops": step_flops / (ms_dev * 1e-3) / 1e12 / world,
             "step_frac_of_peak": step_flops / (ms_dev * 1e-3) / 1e12 / world / peak_tf,
         },

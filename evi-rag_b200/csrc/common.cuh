@@ -7,6 +7,7 @@
 #include <cuda_fp16.h>
 #include <cuda_bf16.h>
 #include <stdint.h>
+#include <atomic>
 
 #define EVI_DEVINL __device__ __forceinline__
 
@@ -33,6 +34,19 @@ enum EdgeFlag : unsigned {
 // ---------------------------------------------------------------------------------------------
 // generic helpers
 // ---------------------------------------------------------------------------------------------
+// Opt a kernel into `bytes` of dynamic shared memory once per device: the attribute is per device (a process that
+// drives several GPUs needs it on each) and `done` is one bit per device ordinal, safe under concurrent callers.
+template <class Kernel>
+inline bool ensure_dynamic_smem(Kernel kern, int bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return true;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess) return false;
+  done.fetch_or(bit, std::memory_order_release);
+  return true;
+}
+
 EVI_DEVINL uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
@@ -55,10 +69,11 @@ EVI_DEVINL float warp_sum(float v) {
 }
 
 // erf GELU (nn.GELU() default, retriever.py:163,178), branch-free:
-//   gelu(x) = max(x, 0) - 0.5 |x| erfc(|x| / sqrt 2),   erfc(t) = 2^-q(t) on [0, 4.2] (clamped: erfc(4.2) = 3e-9)
-// q is a degree-7 least-squares fit of -log2(erfc(t)) at Chebyshev nodes (scripts/fit_gelu.py);
-// max |gelu_fast - gelu_erf| = 6.7e-7 over [-12, 12] in fp32: 7 FMA + 1 MUFU.EX2 instead of erff's
-// two divergent polynomial branches.
+//   gelu(x) = max(x, 0) - |x| * (0.5 erfc(|x| / sqrt 2)),   0.5 erfc(a / sqrt 2) = 2^-q(a)
+// q is a degree-7 weighted least-squares fit of 1 - log2(erfc(a / sqrt 2)) at Chebyshev nodes of [0, 5.94]
+// (scripts/fit_gelu.py). Beyond the fitted range q keeps growing (q(5.94) = 29.4, leading coefficient > 0),
+// so 2^-q underflows towards 0 on its own and no clamp is needed.
+// max |gelu_fast - gelu_erf| = 4.8e-7 over [-12, 12] in fp32; 7 FMA + MUFU.EX2 + FMNMX + FMA.
 EVI_DEVINL float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -66,16 +81,15 @@ EVI_DEVINL float ex2_approx(float x) {
 }
 EVI_DEVINL float gelu_fast(float x) {
   const float ax = fabsf(x);
-  const float t = fminf(ax * 0.70710678118654752440f, 4.2f);
-  float q = 2.1488724087248556e-05f;
-  q = fmaf(q, t, -0.0005029611056670547f);
-  q = fmaf(q, t, 0.005319129675626755f);
-  q = fmaf(q, t, -0.0341791957616806f);
-  q = fmaf(q, t, 0.15282225608825684f);
-  q = fmaf(q, t, 0.916801393032074f);
-  q = fmaf(q, t, 1.6281447410583496f);
-  q = fmaf(q, t, -5.820251317345537e-06f);
-  return fmaxf(x, 0.f) - 0.5f * ax * ex2_approx(-q);
+  float q = 1.8662889260667725e-06f;
+  q = fmaf(q, ax, -6.2319784774445e-05f);
+  q = fmaf(q, ax, 0.0009371304186061025f);
+  q = fmaf(q, ax, -0.008538476191461086f);
+  q = fmaf(q, ax, 0.05403471365571022f);
+  q = fmaf(q, ax, 0.45837363600730896f);
+  q = fmaf(q, ax, 1.1512972116470337f);
+  q = fmaf(q, ax, 0.9999892115592957f);
+  return fmaf(-ax, ex2_approx(-q), fmaxf(x, 0.f));
 }
 EVI_DEVINL float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 EVI_DEVINL float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }

@@ -308,12 +308,8 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
       return kErrCuda;
   }
   auto kern = gemm2_kernel<FMT, Epi>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
-      return kErrCuda;
-    attr_set = true;
-  }
+  static std::atomic<unsigned long long> smem_ready{0};  // per template instantiation
+  if (!ensure_dynamic_smem(kern, SMEM_BYTES, smem_ready)) return kErrCuda;
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int pairs_max = num_sms / 2;
   const int pairs = tiles < pairs_max ? tiles : pairs_max;

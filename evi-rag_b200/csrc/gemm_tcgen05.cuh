@@ -460,12 +460,8 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
       return kErrCuda;
   }
   auto kern = gemm_kernel<FMT, Epi>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
-      return kErrCuda;
-    attr_set = true;
-  }
+  static std::atomic<unsigned long long> smem_ready{0};  // per template instantiation
+  if (!ensure_dynamic_smem(kern, SMEM_BYTES, smem_ready)) return kErrCuda;
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms ? tiles : num_sms;
   kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, M, N, K, m_dev, ep);

@@ -594,13 +594,8 @@ int evi_bfs_edge_sweep(const int* head32, const int* tail32, int num_jobs, const
                        int sources_are_global, int directed, int max_depth, int* dist_out, cudaStream_t stream) {
   if (num_jobs <= 0) return kOk;
   constexpr int kSmemNodes = 40 * 1024;  // 160 KB of dist per CTA
-  static bool attr_set = false;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(bfs_sweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemNodes * 4) !=
-        cudaSuccess)
-      return kErrCuda;
-    attr_set = true;
-  }
+  static std::atomic<unsigned long long> smem_ready{0};
+  if (!ensure_dynamic_smem(bfs_sweep_kernel, kSmemNodes * 4, smem_ready)) return kErrCuda;
   bfs_sweep_kernel<<<num_jobs, kSweepThreads, kSmemNodes * 4, stream>>>(
       head32, tail32, job_edge_begin, job_edge_end, job_node_begin, job_node_end, job_dist_off, job_src_ptr, sources,
       sources_are_global, directed, max_depth, kSmemNodes, dist_out);

@@ -217,8 +217,8 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
   float var = 0.f;
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
-    const float d = x[j] - mean;
-    var = fmaf(d, d, var);
+    x[j] -= mean;  // centred in place: the normalisation below is one multiply
+    var = fmaf(x[j], x[j], var);
   }
   const float rstd = rsqrtf(warp_sum(var) * (1.0f / D) + kLnEps);
   float nav = 0.f;
@@ -231,7 +231,7 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
     ldg_v8_keep(sp.wn + c, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      y[j] = gelu_fast(fmaf((x[i * 8 + j] - mean) * rstd, g[j], b[j]));
+      y[j] = gelu_fast(fmaf(x[i * 8 + j] * rstd, g[j], b[j]));
       nav = fmaf(y[j], w[j], nav);
     }
     st_cs_v4(sc_out + c, pack8<FMT>(y));
@@ -239,14 +239,70 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
   return 1.0f / (1.0f + __expf(-(warp_sum(nav) + sp.bn)));
 }
 
+// Both directions of one edge in one pass over the parameter vectors: x_f = U[h] + V[t], x_b = U[t] + V[h].
+// ln_g / ln_b / w_n are read once per edge instead of once per direction (the kernel is bound by L1 throughput).
+template <int FMT>
+EVI_DEVINL void struct_context_pair(const float* __restrict__ uv_h, const float* __restrict__ uv_t,
+                                    const StructParams& sp, int lane, uint16_t* __restrict__ sc_f,
+                                    uint16_t* __restrict__ sc_b, float& nav_f, float& nav_b) {
+  float xf[32], xb[32];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 256 + lane * 8;
+    float uh[8], vt[8], ut[8], vh[8];
+    ldg_v8_stream(uv_h + c, uh);
+    ldg_v8_stream(uv_t + D + c, vt);
+    ldg_v8_stream(uv_t + c, ut);
+    ldg_v8_stream(uv_h + D + c, vh);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) xf[i * 8 + j] = uh[j] + vt[j], xb[i * 8 + j] = ut[j] + vh[j];
+  }
+  float sum_f = 0.f, sum_b = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) sum_f += xf[j], sum_b += xb[j];
+  const float mean_f = warp_sum(sum_f) * (1.0f / D), mean_b = warp_sum(sum_b) * (1.0f / D);
+  float var_f = 0.f, var_b = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    xf[j] -= mean_f, xb[j] -= mean_b;  // centred in place: the normalisation below is one multiply
+    var_f = fmaf(xf[j], xf[j], var_f);
+    var_b = fmaf(xb[j], xb[j], var_b);
+  }
+  const float rstd_f = rsqrtf(warp_sum(var_f) * (1.0f / D) + kLnEps);
+  const float rstd_b = rsqrtf(warp_sum(var_b) * (1.0f / D) + kLnEps);
+  float acc_f = 0.f, acc_b = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = i * 256 + lane * 8;
+    float g[8], b[8], w[8], yf[8], yb[8];
+    ldg_v8_keep(sp.ln_g + c, g);
+    ldg_v8_keep(sp.ln_b + c, b);
+    ldg_v8_keep(sp.wn + c, w);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      yf[j] = gelu_fast(fmaf(xf[i * 8 + j] * rstd_f, g[j], b[j]));
+      yb[j] = gelu_fast(fmaf(xb[i * 8 + j] * rstd_b, g[j], b[j]));
+      acc_f = fmaf(yf[j], w[j], acc_f);
+      acc_b = fmaf(yb[j], w[j], acc_b);
+    }
+    st_cs_v4(sc_f + c, pack8<FMT>(yf));
+    st_cs_v4(sc_b + c, pack8<FMT>(yb));
+  }
+  nav_f = 1.0f / (1.0f + __expf(-(warp_sum(acc_f) + sp.bn)));
+  nav_b = 1.0f / (1.0f + __expf(-(warp_sum(acc_b) + sp.bn)));
+}
+
 constexpr int kEdgeWarps = 8;
+#ifndef EVI_OPERAND_CTAS
+#define EVI_OPERAND_CTAS 2  // 128 registers: both directions' rows stay in registers (struct_context_pair)
+#endif
 
 // Operand rows of one chunk of edges (the inputs of the two per-edge contractions of state_net.0):
 //   m16  [E, D]   h * r_ctx * t            (shared by both directions: iv_dir = nav_dir * m)
 //   sc16 [nd*E, D] struct context, forward rows first, then backward rows
 //   scal [E, 4]   nav_f, nav_b, dist_f, dist_b
 template <int FMT>
-__global__ void __launch_bounds__(kEdgeWarps * 32, 3)
+__global__ void __launch_bounds__(kEdgeWarps * 32, EVI_OPERAND_CTAS)
 edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
                     const uint16_t* __restrict__ node_repr,   // [N, D]
@@ -258,8 +314,8 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
                     uint16_t* __restrict__ m16, uint16_t* __restrict__ sc_fwd, uint16_t* __restrict__ sc_bwd,
                     float4* __restrict__ scal) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (long long e = blockIdx.x * static_cast<long long>(kEdgeWarps) + warp; e < num_edges;
-       e += static_cast<long long>(gridDim.x) * kEdgeWarps) {
+  const long long stride = static_cast<long long>(gridDim.x) * kEdgeWarps;
+  for (long long e = blockIdx.x * static_cast<long long>(kEdgeWarps) + warp; e < num_edges; e += stride) {
     int h = __ldg(head + e), t = __ldg(tail + e), q = __ldg(qid + e), rs = __ldg(rel_slot + e);
     if (static_cast<unsigned>(h) >= static_cast<unsigned>(num_nodes) ||
         static_cast<unsigned>(t) >= static_cast<unsigned>(num_nodes) ||
@@ -271,8 +327,11 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
     const float* uv_h = node_uv + static_cast<size_t>(h) * 2 * D;
     const float* uv_t = node_uv + static_cast<size_t>(t) * 2 * D;
     float nav_f = 0.f, nav_b = 0.f;
-    if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, sc_fwd + static_cast<size_t>(e) * D);
-    if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, sp, lane, sc_bwd + static_cast<size_t>(e) * D);
+    if (do_fwd && do_bwd)
+      struct_context_pair<FMT>(uv_h, uv_t, sp, lane, sc_fwd + static_cast<size_t>(e) * D,
+                               sc_bwd + static_cast<size_t>(e) * D, nav_f, nav_b);
+    else if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, sc_fwd + static_cast<size_t>(e) * D);
+    else if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, sp, lane, sc_bwd + static_cast<size_t>(e) * D);
 
     const uint16_t* hp = node_repr + static_cast<size_t>(h) * D;
     const uint16_t* tp = node_repr + static_cast<size_t>(t) * D;
@@ -323,8 +382,8 @@ struct TailParams {
   float c0;             // w_o . b_2 + b_o
 };
 
-template <int FMT>
-EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
+// LayerNorm statistics of one pre-activation row spread over the warp: rstd and -mean * rstd
+EVI_DEVINL void row_norm_stats(const float (&z)[32], float& rstd, float& shift) {
   float sum = 0.f;
 #pragma unroll
   for (int j = 0; j < 32; ++j) sum += z[j];
@@ -335,7 +394,15 @@ EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uin
     const float d = z[j] - mean;
     var = fmaf(d, d, var);
   }
-  const float rstd = rsqrtf(warp_sum(var) * (1.0f / D) + kLnEps);
+  rstd = rsqrtf(warp_sum(var) * (1.0f / D) + kLnEps);
+  shift = -mean * rstd;
+}
+
+// LayerNorm + GELU + collapsed score head of one direction (z is overwritten with g)
+template <int FMT>
+EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
+  float rstd, shift;
+  row_norm_stats(z, rstd, shift);
   float acc = 0.f;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -346,13 +413,43 @@ EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uin
     ldg_v8_keep(tp.v + col, vv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float y = gelu_fast(fmaf((z[i * 8 + j] - mean) * rstd, gg[j], bb[j]));
+      const float y = gelu_fast(fmaf(fmaf(z[i * 8 + j], rstd, shift), gg[j], bb[j]));
       z[i * 8 + j] = y;
       acc = fmaf(y, vv[j], acc);
     }
   }
   if (g_out != nullptr) store_row16<FMT>(g_out, lane, z);
   return warp_sum(acc) + tp.c0;
+}
+
+// Both directions of one edge in one pass over the parameter vectors (ln_g, ln_b, v are read once per edge)
+template <int FMT>
+EVI_DEVINL void tail_finish_pair(float (&zf)[32], float (&zb)[32], const TailParams& tp, int lane,
+                                 uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd, float& lf, float& lb) {
+  float rstd_f, shift_f, rstd_b, shift_b;
+  row_norm_stats(zf, rstd_f, shift_f);
+  row_norm_stats(zb, rstd_b, shift_b);
+  float acc_f = 0.f, acc_b = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int col = i * 256 + lane * 8;
+    float gg[8], bb[8], vv[8];
+    ldg_v8_keep(tp.ln_g + col, gg);
+    ldg_v8_keep(tp.ln_b + col, bb);
+    ldg_v8_keep(tp.v + col, vv);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float yf = gelu_fast(fmaf(fmaf(zf[i * 8 + j], rstd_f, shift_f), gg[j], bb[j]));
+      const float yb = gelu_fast(fmaf(fmaf(zb[i * 8 + j], rstd_b, shift_b), gg[j], bb[j]));
+      zf[i * 8 + j] = yf, zb[i * 8 + j] = yb;
+      acc_f = fmaf(yf, vv[j], acc_f);
+      acc_b = fmaf(yb, vv[j], acc_b);
+    }
+  }
+  if (g_fwd != nullptr) store_row16<FMT>(g_fwd, lane, zf);
+  if (g_bwd != nullptr) store_row16<FMT>(g_bwd, lane, zb);
+  lf = warp_sum(acc_f) + tp.c0;
+  lb = warp_sum(acc_b) + tp.c0;
 }
 
 template <int FMT>
@@ -402,8 +499,11 @@ score_tail_kernel(const float* __restrict__ mm,                                 
     }
   }
   float lf = 0.f, lb = 0.f;
-  if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
-  if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
+  if (has_f && has_b)
+    tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr,
+                          g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr, lf, lb);
+  else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
+  else if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
   if (lane == 0) {
     if (has_f && logits_fwd) logits_fwd[e] = lf;
     if (has_b && logits_bwd) logits_bwd[e] = lb;
@@ -525,8 +625,11 @@ score_tail_bulk_kernel(const float* __restrict__ mm, const float* __restrict__ s
       issue(partner_bar, e_part, hn, tn, pn);
     }
     float lf = 0.f, lb = 0.f;
-    if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
-    if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
+    if (has_f && has_b)
+      tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr,
+                            g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr, lf, lb);
+    else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
+    else if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
     if (lane == 0) {
       if (has_f && logits_fwd) logits_fwd[e] = lf;
       if (has_b && logits_bwd) logits_bwd[e] = lb;
@@ -822,7 +925,10 @@ struct ChunkPlan {
     StructParams sp;
     sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
     const long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
-    const int grid = static_cast<int>(want < 8LL * a.num_sms ? want : 8LL * a.num_sms);
+    // resident CTAs only: one sweep over the chunk in edge order, so the node rows of a question (~15 MB) stay in
+    // L2 while its edges are processed; a larger grid makes later waves sweep the chunk again from DRAM
+    const long long resident = static_cast<long long>(EVI_OPERAND_CTAS) * a.num_sms;
+    const int grid = static_cast<int>(want < resident ? want : resident);
     edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
         a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
         static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
@@ -867,13 +973,8 @@ struct ChunkPlan {
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     } else {
-      static bool attr_set[2] = {false, false};
-      if (!attr_set[FMT]) {
-        if (cudaFuncSetAttribute(score_tail_bulk_kernel<FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 kTailSmemBytes) != cudaSuccess)
-          return kErrCuda;
-        attr_set[FMT] = true;
-      }
+      static std::atomic<unsigned long long> smem_ready{0};  // per FMT instantiation
+      if (!ensure_dynamic_smem(score_tail_bulk_kernel<FMT>, kTailSmemBytes, smem_ready)) return kErrCuda;
       const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
       const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
       score_tail_bulk_kernel<FMT><<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
@@ -1057,13 +1158,8 @@ int evi_relation_pairs(const int* rel32, const long long* edge_ptr, int num_ques
   const int words = (num_relations + 31) / 32;
   const size_t smem = static_cast<size_t>(words) * 8;
   if (smem > 200 * 1024) return kErrUnsupported;  // > 819k relation ids
-  static bool attr_set = false;
-  if (smem > 48 * 1024 && !attr_set) {
-    if (cudaFuncSetAttribute(relation_pairs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) !=
-        cudaSuccess)
-      return kErrCuda;
-    attr_set = true;
-  }
+  static std::atomic<unsigned long long> smem_ready{0};
+  if (smem > 48 * 1024 && !ensure_dynamic_smem(relation_pairs_kernel, 200 * 1024, smem_ready)) return kErrCuda;
   if (cudaMemsetAsync(num_pairs, 0, sizeof(int), stream) != cudaSuccess) return kErrCuda;
   relation_pairs_kernel<<<num_questions, 256, smem, stream>>>(rel32, edge_ptr, num_relations, words, capacity,
                                                               pair_slot32, pair_q32, pair_rel32, num_pairs, flags);

@@ -158,6 +158,7 @@ class Retriever(nn.Module):
         self._ws_score: Optional[torch.Tensor] = None
         self.gemm_events = None
         self.last_chunk_edges = 0
+        self.last_num_chunks = 0
         self._flags: Optional[torch.Tensor] = None
         self._pending_flags = False
 
@@ -550,6 +551,7 @@ class Retriever(nn.Module):
         a.logits_bwd = logits_bwd.data_ptr() if logits_bwd is not None else None
         a.edge_embeddings = feats.data_ptr() if feats is not None else None
         self.last_chunk_edges = min(chunk, E)
+        self.last_num_chunks = -(-E // max(1, min(chunk, E)))
         events = self.gemm_events  # (torch.cuda.Event begin, end) around one W_sc GEMM launch, or None
         a.ev_gemm_begin = events[0].cuda_event if events is not None else None
         a.ev_gemm_end = events[1].cuda_event if events is not None else None
