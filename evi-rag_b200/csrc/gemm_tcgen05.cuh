@@ -256,8 +256,15 @@ struct EpiBiasAct {
       v[i + 3] = __uint_as_float(r[i + 3]) + b.w;
     }
     if (act == kActTanh) {
+      if (p.out32 == nullptr) {
+        // 16-bit output only (the per-node / per-relation projections): tanh_fast is good to ~1e-6, far below the
+        // 2^-12 rounding of the store, and keeps the epilogue shorter than the tile's MMA time
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);
+        for (int i = 0; i < 32; ++i) v[i] = tanh_fast(v[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);
+      }
     } else if (act == kActSigmoid) {
 #pragma unroll
       for (int i = 0; i < 32; ++i) v[i] = 1.0f / (1.0f + expf(-v[i]));

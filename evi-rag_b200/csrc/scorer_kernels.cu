@@ -864,7 +864,10 @@ static int linear_act_impl(const void* x16, int m, const int* m_dev, const void*
   gemm::EpiBiasAct::Params p;
   p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = n, p.ld32 = n;
   for (int i = 0; i < 8; ++i) p.act[i] = act_per_block[i];
-  return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
+  static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr;
+  if (one_sm || num_sms < 2)
+    return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
+  return gemm2::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
 }
 
 // workspace of one chunk of `E` edges:
