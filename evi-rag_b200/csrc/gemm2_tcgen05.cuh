@@ -232,7 +232,42 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
           tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
       typename Epi::RowState st;
       Epi::init_row(st);
-      if constexpr (Epi::kTmaStore) {
+      if constexpr (Epi::kTmaStore && Epi::kOut16) {
+        // fp16 rows: sub-tiles 2i and 2i+1 fill the two 64-byte halves of one staging line, one store per 32 x 64 box
+        uint8_t* my_stage = epi_stage + quarter * 2 * gemm::EPI_STAGE_BYTES;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
+          uint8_t* buf = my_stage + ((c >> 1) & 1) * gemm::EPI_STAGE_BYTES;
+          if ((c & 1) == 0) {
+            if (lane == 0) bulk_wait_group_read<1>();  // the store issued two boxes ago has left `buf`
+            __syncwarp();
+          }
+          tmem_ld_wait();
+          const int col0 = n_blk * BN + c * 32;
+          Epi::template transform<FMT>(ep, st, row, col0, r);
+          uint8_t* dst = buf + lane * 128;
+          const int unit0 = (c & 1) * 4;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 w;
+            w.x = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            w.y = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            w.z = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            w.w = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            *reinterpret_cast<uint4*>(dst + (((unit0 + j) ^ (lane & 7)) << 4)) = w;
+          }
+          if (c & 1) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (row0 < M && col0 - 32 < N) tma_store_2d(&tmap_c, buf, col0 - 32, row0);
+              bulk_commit_group();
+            }
+          }
+        }
+      } else if constexpr (Epi::kTmaStore) {
         uint8_t* my_stage = epi_stage + quarter * 2 * gemm::EPI_STAGE_BYTES;
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
@@ -290,7 +325,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 template <int FMT, class Epi>
 inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const typename Epi::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev = nullptr,
-                  float* out32 = nullptr, int ldc = 0) {
+                  void* out = nullptr, int ldc = 0) {  // out: fp32 rows, or fp16 rows when Epi::kOut16
   if (M <= 0) return kOk;
   if (K % 8 != 0 || lda % 8 != 0 || ldb % 8 != 0 || N % 32 != 0) return kErrInvalidArg;
   CUtensorMap ta, tb;
@@ -302,10 +337,18 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
     return kErrCuda;
   CUtensorMap tc = ta;
   if (Epi::kTmaStore) {
-    if (out32 == nullptr || ldc % 4 != 0 || (reinterpret_cast<uintptr_t>(out32) & 15) != 0) return kErrInvalidArg;
-    if (!gemm::make_tmap_out_f32(&tc, out32, static_cast<uint64_t>(M), static_cast<uint64_t>(N),
-                                 static_cast<uint64_t>(ldc)))
-      return kErrCuda;
+    if (out == nullptr || (reinterpret_cast<uintptr_t>(out) & 15) != 0) return kErrInvalidArg;
+    if (Epi::kOut16) {
+      if (ldc % 8 != 0 || N % 64 != 0) return kErrInvalidArg;
+      if (!gemm::make_tmap_out_f16(&tc, out, static_cast<uint64_t>(M), static_cast<uint64_t>(N),
+                                   static_cast<uint64_t>(ldc)))
+        return kErrCuda;
+    } else {
+      if (ldc % 4 != 0) return kErrInvalidArg;
+      if (!gemm::make_tmap_out_f32(&tc, out, static_cast<uint64_t>(M), static_cast<uint64_t>(N),
+                                   static_cast<uint64_t>(ldc)))
+        return kErrCuda;
+    }
   }
   auto kern = gemm2_kernel<FMT, Epi>;
   static std::atomic<unsigned long long> smem_ready{0};  // per template instantiation

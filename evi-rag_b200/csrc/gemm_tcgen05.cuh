@@ -167,6 +167,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
           tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + static_cast<uint32_t>(acc * BN);
       typename Epi::RowState st;
       Epi::init_row(st);
+      static_assert(!Epi::kOut16, "the 16-bit TMA-store epilogue exists in the CTA-pair kernel only");
       if constexpr (Epi::kTmaStore) {
         // accumulator row -> registers -> epilogue math -> swizzled 32x32 fp32 sub-tile in shared memory ->
         // one TMA store per sub-tile (full 128-byte lines, clipped at the matrix edge by the tensor map)
@@ -233,6 +234,7 @@ enum Act : int { kActNone = 0, kActTanh = 1, kActSigmoid = 2 };
 // one N=2048 GEMM). Writes a 16-bit copy (next GEMM operand / gather source) and/or fp32.
 struct EpiBiasAct {
   static constexpr bool kTmaStore = false;
+  static constexpr bool kOut16 = false;
   struct Params {
     const float* bias;   // [N]
     void* out16;         // [M, ld16] 16-bit or null
@@ -297,6 +299,7 @@ struct EpiBiasAct {
 // 256-column block.
 struct EpiPreNorm {
   static constexpr bool kTmaStore = false;
+  static constexpr bool kOut16 = false;
   struct Params {
     const float* bias;    // [N] state_net.0.bias
     const float* w_dist;  // [N] state_net.0.weight[:, 3D]
@@ -339,6 +342,7 @@ struct EpiPreNorm {
 // state_net.4 output: feat = acc + b2 (fp32, retriever.py:180) — only when edge features are requested
 struct EpiBiasF32 {
   static constexpr bool kTmaStore = false;
+  static constexpr bool kOut16 = false;
   struct Params {
     const float* bias;
     float* out32;
@@ -359,11 +363,26 @@ struct EpiBiasF32 {
   static EVI_DEVINL void finish_row(const Params&, RowState&, int, int) {}
 };
 
+// Plain accumulator rows stored as fp16 through the same staged TMA-store path (two 32-column sub-tiles share one
+// 128-byte staging line, one store per 32 x 64 box). Used for W_iv m (CTA-pair kernel only): the term is one addend
+// of the state_net.0 pre-activation and its 2^-12 rounding is far below the operand rounding already in z
+// (scripts/precision_model.py), while the 16-bit rows halve what this launch writes and what the tail re-reads.
+struct EpiF16Tma {
+  static constexpr bool kTmaStore = true;
+  static constexpr bool kOut16 = true;
+  struct Params {};
+  struct RowState {};
+  static EVI_DEVINL void init_row(RowState&) {}
+  template <int FMT>
+  static EVI_DEVINL void transform(const Params&, RowState&, int, int, uint32_t (&)[32]) {}
+};
+
 // fp32 output through the staged TMA store: out = act(acc + bias[n]) with bias optional and the
 // activation chosen per 256-column block. Covers the partial products W_iv m / W_sc sc of state_net.0
 // (no bias, no activation), P = W_err node_repr, Rq = W_err r_ctx + b_1 and the gate|bias projection.
 struct EpiF32Tma {
   static constexpr bool kTmaStore = true;
+  static constexpr bool kOut16 = false;
   struct Params {
     const float* bias;  // [N] or null
     int act[8];         // per n-block activation
@@ -426,6 +445,20 @@ inline bool make_tmap_out_f32(CUtensorMap* map, const void* base, uint64_t rows,
   cuuint32_t box[2] = {32, 32};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS;
+}
+
+// row-major [rows, cols] fp16 output matrix with row pitch ld (elements); box = 32 rows x 64 cols (128 B)
+inline bool make_tmap_out_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return false;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {64, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;

@@ -452,9 +452,9 @@ EVI_DEVINL void tail_finish_pair(float (&zf)[32], float (&zb)[32], const TailPar
   lb = warp_sum(acc_b) + tp.c0;
 }
 
-template <int FMT>
+template <int FMT, bool MM16>
 __global__ void __launch_bounds__(256)
-score_tail_kernel(const float* __restrict__ mm,                                  // [E, D]  W_iv m
+score_tail_kernel(const void* __restrict__ mm,                                   // [E, D]  W_iv m (fp32, or fp16 if MM16)
                   const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,  // [E, D]  W_sc sc_dir (or null)
                   const float4* __restrict__ scal, const int* __restrict__ head, const int* __restrict__ tail,
                   const int* __restrict__ pair_slot, const float* __restrict__ node_p, const float* __restrict__ pair_rq,
@@ -471,7 +471,8 @@ score_tail_kernel(const float* __restrict__ mm,                                 
     h = t = ps = 0;  // flagged by the operand kernel / pair kernel
   const float4 sc = __ldg(scal + e);
   const bool has_f = s_fwd != nullptr, has_b = s_bwd != nullptr;
-  const float* mrow = mm + static_cast<size_t>(e) * D;
+  const float* mrow = static_cast<const float*>(mm) + static_cast<size_t>(e) * D;
+  const uint16_t* mrow16 = static_cast<const uint16_t*>(mm) + static_cast<size_t>(e) * D;
   const float* ph = node_p + static_cast<size_t>(h) * D;
   const float* pt = node_p + static_cast<size_t>(t) * D;
   const float* rq = pair_rq + static_cast<size_t>(ps) * D;
@@ -480,7 +481,8 @@ score_tail_kernel(const float* __restrict__ mm,                                 
   for (int i = 0; i < 4; ++i) {
     const int c = i * 256 + lane * 8;
     float m[8], a[8], b[8], r[8], wd[8];
-    ldg_v8_stream(mrow + c, m);
+    if constexpr (MM16) unpack8<kFmtF16>(ldg_nc_v4(mrow16 + c), m);
+    else ldg_v8_stream(mrow + c, m);
     ldg_v8_keep(ph + c, a);
     ldg_v8_keep(pt + c, b);
     ldg_v8_keep(rq + c, r);
@@ -536,9 +538,9 @@ constexpr int kTailRowBytes = D * 4;
 constexpr int kTailBufBytes = 6 * kTailRowBytes;
 constexpr int kTailSmemBytes = kTailBufs * kTailBufBytes + kTailWarps * 8;
 
-template <int FMT>
+template <int FMT, bool MM16>
 __global__ void __launch_bounds__(kTailWarps * 32, 1)
-score_tail_bulk_kernel(const float* __restrict__ mm, const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,
+score_tail_bulk_kernel(const void* __restrict__ mm, const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,
                        const float4* __restrict__ scal, const int* __restrict__ head, const int* __restrict__ tail,
                        const int* __restrict__ pair_slot, const float* __restrict__ node_p,
                        const float* __restrict__ pair_rq, int num_nodes, int pair_rows, long long num_edges,
@@ -551,7 +553,9 @@ score_tail_bulk_kernel(const float* __restrict__ mm, const float* __restrict__ s
   uint64_t* my_bar = bars + warp;
   uint64_t* partner_bar = bars + (warp + kTailBufs) % kTailWarps;
   const bool has_f = s_fwd != nullptr, has_b = s_bwd != nullptr;
-  const uint32_t tx_bytes = static_cast<uint32_t>((4 + (has_f ? 1 : 0) + (has_b ? 1 : 0)) * kTailRowBytes);
+  constexpr uint32_t kMmRowBytes = MM16 ? D * 2 : kTailRowBytes;  // W_iv m rows are fp16 when MM16
+  const uint32_t tx_bytes =
+      static_cast<uint32_t>((3 + (has_f ? 1 : 0) + (has_b ? 1 : 0)) * kTailRowBytes) + kMmRowBytes;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kTailWarps; ++i) mbar_init(&bars[i], 1);
     fence_barrier_init();
@@ -569,7 +573,7 @@ score_tail_bulk_kernel(const float* __restrict__ mm, const float* __restrict__ s
   };
   auto issue = [&](uint64_t* bar, long long edge, int h, int t, int ps) {  // one lane
     mbar_arrive_expect_tx(bar, tx_bytes);
-    bulk_load_1d(buf + 0 * D, mm + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
+    bulk_load_1d(buf + 0 * D, static_cast<const uint8_t*>(mm) + static_cast<size_t>(edge) * kMmRowBytes, kMmRowBytes, bar);
     if (has_f) bulk_load_1d(buf + 1 * D, s_fwd + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
     if (has_b) bulk_load_1d(buf + 2 * D, s_bwd + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
     bulk_load_1d(buf + 3 * D, node_p + static_cast<size_t>(h) * D, kTailRowBytes, bar);
@@ -598,11 +602,16 @@ score_tail_bulk_kernel(const float* __restrict__ mm, const float* __restrict__ s
       const int c = i * 256 + lane * 8;
       float wd[8];
       ldg_v8_keep(tp.w_dist + c, wd);
-      const float4 m0 = *reinterpret_cast<const float4*>(buf + c), m1 = *reinterpret_cast<const float4*>(buf + c + 4);
+      float m[8];
+      if constexpr (MM16) {
+        unpack8<kFmtF16>(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf) + c), m);
+      } else {
+        const float4 m0 = *reinterpret_cast<const float4*>(buf + c), m1 = *reinterpret_cast<const float4*>(buf + c + 4);
+        m[0] = m0.x, m[1] = m0.y, m[2] = m0.z, m[3] = m0.w, m[4] = m1.x, m[5] = m1.y, m[6] = m1.z, m[7] = m1.w;
+      }
       const float4 a0 = *reinterpret_cast<const float4*>(buf + 3 * D + c), a1 = *reinterpret_cast<const float4*>(buf + 3 * D + c + 4);
       const float4 b0 = *reinterpret_cast<const float4*>(buf + 4 * D + c), b1 = *reinterpret_cast<const float4*>(buf + 4 * D + c + 4);
       const float4 r0 = *reinterpret_cast<const float4*>(buf + 5 * D + c), r1 = *reinterpret_cast<const float4*>(buf + 5 * D + c + 4);
-      const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
       const float d[8] = {a0.x - b0.x, a0.y - b0.y, a0.z - b0.z, a0.w - b0.w, a1.x - b1.x, a1.y - b1.y, a1.z - b1.z, a1.w - b1.w};
       const float r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
       if (has_f) {
@@ -895,9 +904,9 @@ struct ChunkPlan {
   int do_f, do_b;
   size_t nd, n;
   uint16_t *M16, *SC16, *G;
-  float *MM, *S, *FEAT;
+  float *MM, *S, *FEAT;  // MM holds fp16 rows when mm16 (the buffer keeps its fp32 size)
   float4* SCAL;
-  bool ok;
+  bool ok, mm16;
 
   ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes)
       : a(args), e0(e0_), E(E_), G(nullptr), FEAT(nullptr) {
@@ -920,6 +929,9 @@ struct ChunkPlan {
       FEAT = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
     }
     ok = off <= ws_bytes;
+    // W_iv m in fp16 needs the CTA-pair kernel's 16-bit TMA-store epilogue
+    static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr, mm32 = getenv("EVI_MM_F32") != nullptr;
+    mm16 = !one_sm && !mm32 && a.num_sms >= 2;
   }
 
   int operand(cudaStream_t stream) const {
@@ -946,7 +958,9 @@ struct ChunkPlan {
     gemm::EpiF32Tma::Params plain;
     plain.bias = nullptr;
     for (int i = 0; i < 8; ++i) plain.act[i] = gemm::kActNone;
-    int rc = gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, gemm_sms, stream, nullptr, MM, D);
+    int rc = mm16 ? gemm2::launch<FMT, gemm::EpiF16Tma>(M16, D, w1, 3 * D, static_cast<int>(E), D, D,
+                                                         gemm::EpiF16Tma::Params{}, gemm_sms, stream, nullptr, MM, D)
+                  : gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, gemm_sms, stream, nullptr, MM, D);
     if (rc != kOk) return rc;
     if (time_begin) cudaEventRecord(time_begin, stream);
     rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, gemm_sms, stream, nullptr, S, D);
@@ -971,16 +985,18 @@ struct ChunkPlan {
     if (tail_mode == 1) {
       const int warps = tail_threads / 32;
       const int tgrid = static_cast<int>((E + warps - 1) / warps);
-      score_tail_kernel<FMT><<<tgrid, tail_threads, 0, stream>>>(
+      auto kern = mm16 ? score_tail_kernel<FMT, true> : score_tail_kernel<FMT, false>;
+      kern<<<tgrid, tail_threads, 0, stream>>>(
           MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     } else {
-      static std::atomic<unsigned long long> smem_ready{0};  // per FMT instantiation
-      if (!ensure_dynamic_smem(score_tail_bulk_kernel<FMT>, kTailSmemBytes, smem_ready)) return kErrCuda;
+      auto kern = mm16 ? score_tail_bulk_kernel<FMT, true> : score_tail_bulk_kernel<FMT, false>;
+      static std::atomic<unsigned long long> smem_ready[2] = {{0}, {0}};  // per FMT instantiation, per MM format
+      if (!ensure_dynamic_smem(kern, kTailSmemBytes, smem_ready[mm16 ? 1 : 0])) return kErrCuda;
       const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
       const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
-      score_tail_bulk_kernel<FMT><<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
+      kern<<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
           MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);

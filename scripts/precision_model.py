@@ -27,7 +27,7 @@ def rnd(x, dt):
     return x.to(dt).float() if dt is not None else x
 
 
-def gpu_model(sd, qb, ent, rel, op=torch.float16, uv=None, prq=None, part=None, sites=None):
+def gpu_model(sd, qb, ent, rel, op=torch.float16, uv=None, prq=None, part=None, sites=None, mm=None):
     """op: operand dtype; uv / prq / part: extra rounding of U,V / P,Rq / W_iv m, W_sc sc (None = fp32)."""
     t = torch.from_numpy
     W = lambda n: sd[n].float()
@@ -62,7 +62,7 @@ def gpu_model(sd, qb, ent, rel, op=torch.float16, uv=None, prq=None, part=None, 
     rc = rel_repr[r_i] * gate[q_i] + bias[q_i]
     Rq = rnd(rnd(rc, S_.rc) @ w_err.t() + W("state_net.0.bias"), prq)
     m = rnd(h * rc * tt, S_.m)
-    Mm = rnd(m @ w_iv.t(), part)
+    Mm = rnd(rnd(m @ w_iv.t(), part), mm)  # mm: W_iv m alone stored in 16 bits
     ln = lambda x, n: F.layer_norm(x, (d,), W(n + ".weight"), W(n + ".bias"), 1e-5)
     v = (W("state_net.4.weight").double().t() @ W("score_head.weight").double()[0]).float()
     c0 = float(W("score_head.weight").double()[0] @ W("state_net.4.bias").double() + W("score_head.bias").double()[0])
@@ -104,6 +104,8 @@ def main():
             ("fp16 + P/Rq fp16", dict(op=torch.float16, prq=torch.float16)),
             ("fp16 + partial products fp16", dict(op=torch.float16, part=torch.float16)),
             ("fp16 + U/V + P/Rq fp16", dict(op=torch.float16, uv=torch.float16, prq=torch.float16)),
+            ("fp16 + W_iv m stored fp16", dict(op=torch.float16, mm=torch.float16)),
+            ("fp16 + W_iv m stored bf16", dict(op=torch.float16, mm=torch.bfloat16)),
             ("bf16 operands", dict(op=torch.bfloat16)),
             ("fp16, fp32 kept: proj weights", dict(op=torch.float16, sites={"w"})),
             ("fp16, fp32 kept: state_net.0 weights", dict(op=torch.float16, sites={"w1"})),
