@@ -252,10 +252,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 w;
-            w.x = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-            w.y = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-            w.z = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-            w.w = Op16<kFmtF16>::pack2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            using Out = Op16<(Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt)>;
+            w.x = Out::pack2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+            w.y = Out::pack2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+            w.z = Out::pack2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+            w.w = Out::pack2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
             *reinterpret_cast<uint4*>(dst + (((unit0 + j) ^ (lane & 7)) << 4)) = w;
           }
           if (c & 1) {
@@ -325,7 +326,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 template <int FMT, class Epi>
 inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const typename Epi::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev = nullptr,
-                  void* out = nullptr, int ldc = 0) {  // out: fp32 rows, or fp16 rows when Epi::kOut16
+                  void* out = nullptr, int ldc = 0) {  // out: fp32 rows, or 16-bit rows when Epi::kOut16
   if (M <= 0) return kOk;
   if (K % 8 != 0 || lda % 8 != 0 || ldb % 8 != 0 || N % 32 != 0) return kErrInvalidArg;
   CUtensorMap ta, tb;
@@ -340,8 +341,8 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
     if (out == nullptr || (reinterpret_cast<uintptr_t>(out) & 15) != 0) return kErrInvalidArg;
     if (Epi::kOut16) {
       if (ldc % 8 != 0 || N % 64 != 0) return kErrInvalidArg;
-      if (!gemm::make_tmap_out_f16(&tc, out, static_cast<uint64_t>(M), static_cast<uint64_t>(N),
-                                   static_cast<uint64_t>(ldc)))
+      if (!gemm::make_tmap_out_16(&tc, Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt, out, static_cast<uint64_t>(M),
+                                  static_cast<uint64_t>(N), static_cast<uint64_t>(ldc)))
         return kErrCuda;
     } else {
       if (ldc % 4 != 0) return kErrInvalidArg;

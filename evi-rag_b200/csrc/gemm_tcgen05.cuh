@@ -235,6 +235,7 @@ enum Act : int { kActNone = 0, kActTanh = 1, kActSigmoid = 2 };
 struct EpiBiasAct {
   static constexpr bool kTmaStore = false;
   static constexpr bool kOut16 = false;
+  static constexpr int kOutFmt = -1;
   struct Params {
     const float* bias;   // [N]
     void* out16;         // [M, ld16] 16-bit or null
@@ -300,6 +301,7 @@ struct EpiBiasAct {
 struct EpiPreNorm {
   static constexpr bool kTmaStore = false;
   static constexpr bool kOut16 = false;
+  static constexpr int kOutFmt = -1;
   struct Params {
     const float* bias;    // [N] state_net.0.bias
     const float* w_dist;  // [N] state_net.0.weight[:, 3D]
@@ -343,6 +345,7 @@ struct EpiPreNorm {
 struct EpiBiasF32 {
   static constexpr bool kTmaStore = false;
   static constexpr bool kOut16 = false;
+  static constexpr int kOutFmt = -1;
   struct Params {
     const float* bias;
     float* out32;
@@ -370,11 +373,50 @@ struct EpiBiasF32 {
 struct EpiF16Tma {
   static constexpr bool kTmaStore = true;
   static constexpr bool kOut16 = true;
+  static constexpr int kOutFmt = kFmtF16;  // always fp16 (-1: the operand format)
   struct Params {};
   struct RowState {};
   static EVI_DEVINL void init_row(RowState&) {}
   template <int FMT>
   static EVI_DEVINL void transform(const Params&, RowState&, int, int, uint32_t (&)[32]) {}
+};
+
+// out16 = act(acc + bias[n]) in the operand format through the same 16-bit staged TMA store: the per-node /
+// per-relation / per-question projections whose only consumer reads 16-bit rows (EpiBiasAct's per-thread row
+// stores made those launches epilogue-bound).
+struct EpiBiasAct16Tma {
+  static constexpr bool kTmaStore = true;
+  static constexpr bool kOut16 = true;
+  static constexpr int kOutFmt = -1;
+  struct Params {
+    const float* bias;  // [N] or null
+    int act[8];         // per n-block activation
+  };
+  struct RowState {};
+  static EVI_DEVINL void init_row(RowState&) {}
+  template <int FMT>
+  static EVI_DEVINL void transform(const Params& p, RowState&, int, int col0, uint32_t (&r)[32]) {
+    const int act = p.act[(col0 / BN) & 7];
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 b = p.bias != nullptr ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+      v[i + 0] = __uint_as_float(r[i + 0]) + b.x;
+      v[i + 1] = __uint_as_float(r[i + 1]) + b.y;
+      v[i + 2] = __uint_as_float(r[i + 2]) + b.z;
+      v[i + 3] = __uint_as_float(r[i + 3]) + b.w;
+    }
+    if (act == kActTanh) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = tanh_fast(v[i]);  // ~1e-6, below the 16-bit rounding of the store
+    } else if (act == kActSigmoid) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = 1.0f / (1.0f + expf(-v[i]));
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
+  }
 };
 
 // fp32 output through the staged TMA store: out = act(acc + bias[n]) with bias optional and the
@@ -383,6 +425,7 @@ struct EpiF16Tma {
 struct EpiF32Tma {
   static constexpr bool kTmaStore = true;
   static constexpr bool kOut16 = false;
+  static constexpr int kOutFmt = -1;
   struct Params {
     const float* bias;  // [N] or null
     int act[8];         // per n-block activation
@@ -450,15 +493,16 @@ inline bool make_tmap_out_f32(CUtensorMap* map, const void* base, uint64_t rows,
   return r == CUDA_SUCCESS;
 }
 
-// row-major [rows, cols] fp16 output matrix with row pitch ld (elements); box = 32 rows x 64 cols (128 B)
-inline bool make_tmap_out_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld) {
+// row-major [rows, cols] 16-bit output matrix with row pitch ld (elements); box = 32 rows x 64 cols (128 B)
+inline bool make_tmap_out_16(CUtensorMap* map, int fmt, const void* base, uint64_t rows, uint64_t cols, uint64_t ld) {
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) return false;
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {ld * 2};
   cuuint32_t box[2] = {64, 32};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = fn(map, fmt == kFmtBF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                  const_cast<void*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS;

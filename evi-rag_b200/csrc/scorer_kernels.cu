@@ -870,10 +870,16 @@ static int linear_act_impl(const void* x16, int m, const int* m_dev, const void*
     for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
     return gemm_f32<FMT>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out32, n);
   }
+  static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr;
+  if (out32 == nullptr && !one_sm && num_sms >= 2 && n % 64 == 0 && (reinterpret_cast<uintptr_t>(out16) & 15) == 0) {
+    gemm::EpiBiasAct16Tma::Params t;  // 16-bit rows only: staged TMA store instead of per-thread row stores
+    t.bias = bias;
+    for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
+    return gemm2::launch<FMT, gemm::EpiBiasAct16Tma>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out16, n);
+  }
   gemm::EpiBiasAct::Params p;
   p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = n, p.ld32 = n;
   for (int i = 0; i < 8; ++i) p.act[i] = act_per_block[i];
-  static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr;
   if (one_sm || num_sms < 2)
     return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
   return gemm2::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
