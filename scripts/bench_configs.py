@@ -51,6 +51,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=6)
     ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--sweep", action="store_true",
+                    help="config 5 as separate top-k launches at every k in {50, 100, 200, 500}, DDE on and off")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     torch.cuda.set_device(dev)
@@ -65,6 +67,11 @@ def main():
         run_case(f"config5_k500_dde_{'on' if dde_on else 'off'}", WEBQSP_10K, 128, 500, 2, dde_on, args.steps, args.warmup,
                  dev, model)
     run_case("config2_k100_reference_point", WEBQSP_10K, 128, 100, 2, True, args.steps, args.warmup, dev, model)
+    if args.sweep:
+        for k in (50, 100, 200, 500):
+            for dde_on in (True, False):
+                run_case(f"config5_sweep_k{k}_dde_{'on' if dde_on else 'off'}", WEBQSP_10K, 128, k, 2, dde_on, args.steps,
+                         args.warmup, dev, model)
 
 
 if __name__ == "__main__":
