@@ -36,6 +36,9 @@ F_EDGE = 16_871_424                              # SURVEY §8d, bidirectional sc
 F_NODE = 2_097_152
 TOP_K = 100
 BFS_DEPTH = 2
+# epilogue of the W_sc sc launch (csrc/scorer_kernels.cu, ChunkPlan): 16-bit block fixed-point rows unless an
+# experiment knob keeps the fp32 rows
+W_SC_EPILOGUE = "EpiF32Tma" if any(os.environ.get(k) for k in ("EVI_S_F32", "EVI_MM_F32", "EVI_GEMM_1SM")) else "EpiQ16Tma"
 
 
 def parse_args():
@@ -364,8 +367,8 @@ def run_ours(args):
         "gpu_launches": int(launches_all),
         "clocks": clocks,
         "roofline": {
-            "bound": "tensor", "kernel": "gemm2::gemm2_kernel<EpiF32Tma> (W_sc block of state_net.0: [2E_chunk,1024]x[1024,1024]; "
-                                         "flops counted = executed by that launch)",
+            "bound": "tensor", "kernel": f"gemm2::gemm2_kernel<{W_SC_EPILOGUE}> (W_sc block of state_net.0: "
+                                         "[2E_chunk,1024]x[1024,1024]; flops counted = executed by that launch)",
             "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
             "traffic": roofline_traffic(), "peak_source": peak_src,
             "ms_per_launch": float(np.mean(gemm_ms)), "launches_per_step": float(np.mean(chunk_counts)),

@@ -235,6 +235,24 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       if constexpr (Epi::kTmaStore && Epi::kOut16) {
         // fp16 rows: sub-tiles 2i and 2i+1 fill the two 64-byte halves of one staging line, one store per 32 x 64 box
         uint8_t* my_stage = epi_stage + quarter * 2 * gemm::EPI_STAGE_BYTES;
+        constexpr bool kQuant = gemm::epi_is_quant<Epi>::value;
+        float q_inv = 0.f;
+        if constexpr (kQuant) {
+          // first pass over this thread's accumulator row of the tile: max |acc| -> scale of the (row, tile) block
+          float mx = 0.f;
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) mx = fmaxf(mx, fabsf(__uint_as_float(r[j])));
+          }
+          const bool live = mx > 0.f && mx < 3.0e38f;  // an all-zero (or non-finite) tile row stores zeros
+          q_inv = live ? 32767.0f / mx : 0.f;
+          if (row < M && n_blk < ep.ld_scale)
+            ep.scale[static_cast<size_t>(row) * ep.ld_scale + n_blk] = live ? mx * (1.0f / 32767.0f) : 1.0f;
+        }
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
           uint32_t r[32];
@@ -252,11 +270,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 w;
-            using Out = Op16<(Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt)>;
-            w.x = Out::pack2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
-            w.y = Out::pack2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
-            w.z = Out::pack2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
-            w.w = Out::pack2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            if constexpr (kQuant) {
+              // u = rn(acc * q_inv) + 32768 sits in the low 16 bits of acc * q_inv + (1.5 * 2^23 + 32768)
+              uint32_t u[8];
+#pragma unroll
+              for (int t = 0; t < 8; ++t)
+                u[t] = __float_as_uint(fmaf(__uint_as_float(r[8 * j + t]), q_inv, gemm::kQ16Magic));
+              w.x = __byte_perm(u[0], u[1], 0x5410);
+              w.y = __byte_perm(u[2], u[3], 0x5410);
+              w.z = __byte_perm(u[4], u[5], 0x5410);
+              w.w = __byte_perm(u[6], u[7], 0x5410);
+            } else {
+              using Out = Op16<(Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt)>;
+              w.x = Out::pack2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1]));
+              w.y = Out::pack2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3]));
+              w.z = Out::pack2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5]));
+              w.w = Out::pack2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
+            }
             *reinterpret_cast<uint4*>(dst + (((unit0 + j) ^ (lane & 7)) << 4)) = w;
           }
           if (c & 1) {

@@ -452,10 +452,21 @@ EVI_DEVINL void tail_finish_pair(float (&zf)[32], float (&zb)[32], const TailPar
   lb = warp_sum(acc_b) + tp.c0;
 }
 
-template <int FMT, bool MM16>
+// 16-bit block fixed-point rows of W_sc sc (gemm::EpiQ16Tma): eight u16 -> floats 2^23 + u (the u16 spliced under
+// the exponent of 2^23 by one PRMT each). value = (2^23 + u - kQ16Bias) * scale; callers fold -kQ16Bias * scale into an
+// fma addend they already have.
+constexpr float kQ16Bias = 8388608.0f + 32768.0f;
+EVI_DEVINL void splice_u16x8(const uint4& q, float (&fb)[8]) {
+  const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+  for (int j = 0; j < 8; ++j) fb[j] = __uint_as_float(__byte_perm(w[j >> 1], 0x4B000000u, (j & 1) ? 0x7632 : 0x7610));
+}
+
+template <int FMT, bool MM16, bool SQ16>
 __global__ void __launch_bounds__(256)
 score_tail_kernel(const void* __restrict__ mm,                                   // [E, D]  W_iv m (fp32, or fp16 if MM16)
-                  const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,  // [E, D]  W_sc sc_dir (or null)
+                  const void* __restrict__ s_fwd, const void* __restrict__ s_bwd,  // [E, D]  W_sc sc_dir (or null)
+                  const float4* __restrict__ s_scale_fwd, const float4* __restrict__ s_scale_bwd,  // SQ16 block scales
                   const float4* __restrict__ scal, const int* __restrict__ head, const int* __restrict__ tail,
                   const int* __restrict__ pair_slot, const float* __restrict__ node_p, const float* __restrict__ pair_rq,
                   int num_nodes, int pair_rows, long long num_edges, TailParams tp, uint16_t* __restrict__ g_fwd,
@@ -487,17 +498,36 @@ score_tail_kernel(const void* __restrict__ mm,                                  
     ldg_v8_keep(pt + c, b);
     ldg_v8_keep(rq + c, r);
     ldg_v8_keep(tp.w_dist + c, wd);
-    if (has_f) {
-      float s[8];
-      ldg_v8_stream(s_fwd + static_cast<size_t>(e) * D + c, s);
+    if constexpr (SQ16) {
+      if (has_f) {
+        float fb[8];
+        splice_u16x8(ldg_nc_v4(static_cast<const uint16_t*>(s_fwd) + static_cast<size_t>(e) * D + c), fb);
+        const float qs = __ldg(reinterpret_cast<const float*>(s_scale_fwd + e) + i), off = -kQ16Bias * qs;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], s[j]) + (a[j] - b[j]) + fmaf(sc.z, wd[j], r[j]);
-    }
-    if (has_b) {
-      float s[8];
-      ldg_v8_stream(s_bwd + static_cast<size_t>(e) * D + c, s);
+        for (int j = 0; j < 8; ++j)
+          zf[i * 8 + j] = fmaf(fb[j], qs, (fmaf(sc.x, m[j], off) + (a[j] - b[j])) + fmaf(sc.z, wd[j], r[j]));
+      }
+      if (has_b) {
+        float fb[8];
+        splice_u16x8(ldg_nc_v4(static_cast<const uint16_t*>(s_bwd) + static_cast<size_t>(e) * D + c), fb);
+        const float qs = __ldg(reinterpret_cast<const float*>(s_scale_bwd + e) + i), off = -kQ16Bias * qs;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], s[j]) - (a[j] - b[j]) + fmaf(sc.w, wd[j], r[j]);
+        for (int j = 0; j < 8; ++j)
+          zb[i * 8 + j] = fmaf(fb[j], qs, (fmaf(sc.y, m[j], off) - (a[j] - b[j])) + fmaf(sc.w, wd[j], r[j]));
+      }
+    } else {
+      if (has_f) {
+        float s[8];
+        ldg_v8_stream(static_cast<const float*>(s_fwd) + static_cast<size_t>(e) * D + c, s);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], s[j]) + (a[j] - b[j]) + fmaf(sc.z, wd[j], r[j]);
+      }
+      if (has_b) {
+        float s[8];
+        ldg_v8_stream(static_cast<const float*>(s_bwd) + static_cast<size_t>(e) * D + c, s);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], s[j]) - (a[j] - b[j]) + fmaf(sc.w, wd[j], r[j]);
+      }
     }
   }
   float lf = 0.f, lb = 0.f;
@@ -538,9 +568,13 @@ constexpr int kTailRowBytes = D * 4;
 constexpr int kTailBufBytes = 6 * kTailRowBytes;
 constexpr int kTailSmemBytes = kTailBufs * kTailBufBytes + kTailWarps * 8;
 
-template <int FMT, bool MM16>
+// SQ16: the W_sc sc rows arrive as 16-bit block fixed point (gemm::EpiQ16Tma): u16 values with one fp32 scale per
+// (row, 256-column block) in s_scale_*[edge * 4 + block]; value = (u - 32768) * scale. The u16 is spliced under the
+// exponent of 2^23 (one PRMT), and the constant -(2^23 + 32768) * scale rides in an existing fma addend.
+template <int FMT, bool MM16, bool SQ16>
 __global__ void __launch_bounds__(kTailWarps * 32, 1)
-score_tail_bulk_kernel(const void* __restrict__ mm, const float* __restrict__ s_fwd, const float* __restrict__ s_bwd,
+score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_fwd, const void* __restrict__ s_bwd,
+                       const float4* __restrict__ s_scale_fwd, const float4* __restrict__ s_scale_bwd,
                        const float4* __restrict__ scal, const int* __restrict__ head, const int* __restrict__ tail,
                        const int* __restrict__ pair_slot, const float* __restrict__ node_p,
                        const float* __restrict__ pair_rq, int num_nodes, int pair_rows, long long num_edges,
@@ -554,8 +588,9 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const float* __restrict__ s_
   uint64_t* partner_bar = bars + (warp + kTailBufs) % kTailWarps;
   const bool has_f = s_fwd != nullptr, has_b = s_bwd != nullptr;
   constexpr uint32_t kMmRowBytes = MM16 ? D * 2 : kTailRowBytes;  // W_iv m rows are fp16 when MM16
-  const uint32_t tx_bytes =
-      static_cast<uint32_t>((3 + (has_f ? 1 : 0) + (has_b ? 1 : 0)) * kTailRowBytes) + kMmRowBytes;
+  constexpr uint32_t kSRowBytes = SQ16 ? D * 2 : kTailRowBytes;   // W_sc sc rows are 16-bit fixed point when SQ16
+  const uint32_t tx_bytes = static_cast<uint32_t>(3 * kTailRowBytes) +
+                            static_cast<uint32_t>((has_f ? 1 : 0) + (has_b ? 1 : 0)) * kSRowBytes + kMmRowBytes;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kTailWarps; ++i) mbar_init(&bars[i], 1);
     fence_barrier_init();
@@ -574,8 +609,10 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const float* __restrict__ s_
   auto issue = [&](uint64_t* bar, long long edge, int h, int t, int ps) {  // one lane
     mbar_arrive_expect_tx(bar, tx_bytes);
     bulk_load_1d(buf + 0 * D, static_cast<const uint8_t*>(mm) + static_cast<size_t>(edge) * kMmRowBytes, kMmRowBytes, bar);
-    if (has_f) bulk_load_1d(buf + 1 * D, s_fwd + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
-    if (has_b) bulk_load_1d(buf + 2 * D, s_bwd + static_cast<size_t>(edge) * D, kTailRowBytes, bar);
+    if (has_f)
+      bulk_load_1d(buf + 1 * D, static_cast<const uint8_t*>(s_fwd) + static_cast<size_t>(edge) * kSRowBytes, kSRowBytes, bar);
+    if (has_b)
+      bulk_load_1d(buf + 2 * D, static_cast<const uint8_t*>(s_bwd) + static_cast<size_t>(edge) * kSRowBytes, kSRowBytes, bar);
     bulk_load_1d(buf + 3 * D, node_p + static_cast<size_t>(h) * D, kTailRowBytes, bar);
     bulk_load_1d(buf + 4 * D, node_p + static_cast<size_t>(t) * D, kTailRowBytes, bar);
     bulk_load_1d(buf + 5 * D, pair_rq + static_cast<size_t>(ps) * D, kTailRowBytes, bar);
@@ -594,6 +631,11 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const float* __restrict__ s_
     int hn = 0, tn = 0, pn = 0;
     if (e_part < num_edges) load_ids(e_part, hn, tn, pn);  // in flight while this edge's rows land
     const float4 sc = __ldg(scal + e);
+    float qs_lane = 0.f;  // lanes 0-3: forward block scales, lanes 4-7: backward (one register instead of eight)
+    if constexpr (SQ16) {
+      if (lane < 4 && has_f) qs_lane = __ldg(reinterpret_cast<const float*>(s_scale_fwd + e) + lane);
+      if (lane >= 4 && lane < 8 && has_b) qs_lane = __ldg(reinterpret_cast<const float*>(s_scale_bwd + e) + (lane - 4));
+    }
     mbar_wait(my_bar, phase);
     phase ^= 1u;
     float zf[32], zb[32];
@@ -614,17 +656,33 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const float* __restrict__ s_
       const float4 r0 = *reinterpret_cast<const float4*>(buf + 5 * D + c), r1 = *reinterpret_cast<const float4*>(buf + 5 * D + c + 4);
       const float d[8] = {a0.x - b0.x, a0.y - b0.y, a0.z - b0.z, a0.w - b0.w, a1.x - b1.x, a1.y - b1.y, a1.z - b1.z, a1.w - b1.w};
       const float r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-      if (has_f) {
-        const float4 s0 = *reinterpret_cast<const float4*>(buf + 1 * D + c), s1 = *reinterpret_cast<const float4*>(buf + 1 * D + c + 4);
-        const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+      if constexpr (SQ16) {
+        // rows of an absent direction are never loaded: their slots hold stale bytes and the results are unused
+        const float qf = __shfl_sync(0xffffffffu, qs_lane, i), qb = __shfl_sync(0xffffffffu, qs_lane, 4 + i);
+        const float off_f = -kQ16Bias * qf, off_b = -kQ16Bias * qb;
+        float ff[8], fbk[8];
+        splice_u16x8(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf + 1 * D) + c), ff);
+        splice_u16x8(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf + 2 * D) + c), fbk);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], sv[j]) + d[j] + fmaf(sc.z, wd[j], r[j]);
-      }
-      if (has_b) {
-        const float4 s0 = *reinterpret_cast<const float4*>(buf + 2 * D + c), s1 = *reinterpret_cast<const float4*>(buf + 2 * D + c + 4);
-        const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+        for (int j = 0; j < 8; ++j) {
+          zf[i * 8 + j] = fmaf(ff[j], qf, (fmaf(sc.x, m[j], off_f) + d[j]) + fmaf(sc.z, wd[j], r[j]));
+          zb[i * 8 + j] = fmaf(fbk[j], qb, (fmaf(sc.y, m[j], off_b) - d[j]) + fmaf(sc.w, wd[j], r[j]));
+        }
+      } else {
+        if (has_f) {
+          const float* sp = buf + 1 * D + c;
+          const float4 s0 = *reinterpret_cast<const float4*>(sp), s1 = *reinterpret_cast<const float4*>(sp + 4);
+          const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
 #pragma unroll
-        for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], sv[j]) - d[j] + fmaf(sc.w, wd[j], r[j]);
+          for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], sv[j]) + d[j] + fmaf(sc.z, wd[j], r[j]);
+        }
+        if (has_b) {
+          const float* sp = buf + 2 * D + c;
+          const float4 s0 = *reinterpret_cast<const float4*>(sp), s1 = *reinterpret_cast<const float4*>(sp + 4);
+          const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], sv[j]) - d[j] + fmaf(sc.w, wd[j], r[j]);
+        }
       }
     }
     // every lane has moved its part of the buffer into registers: hand the buffer to the partner's next edge
@@ -912,9 +970,9 @@ struct ChunkPlan {
   uint16_t *M16, *SC16, *G;
   float *MM, *S, *FEAT;  // MM holds fp16 rows when mm16 (the buffer keeps its fp32 size)
   float4* SCAL;
-  bool ok, mm16;
+  bool ok, mm16, sq16;
 
-  ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes)
+  ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes, int tail_mode)
       : a(args), e0(e0_), E(E_), G(nullptr), FEAT(nullptr) {
     do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
     nd = static_cast<size_t>(do_f + do_b);
@@ -938,6 +996,17 @@ struct ChunkPlan {
     // W_iv m in fp16 needs the CTA-pair kernel's 16-bit TMA-store epilogue
     static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr, mm32 = getenv("EVI_MM_F32") != nullptr;
     mm16 = !one_sm && !mm32 && a.num_sms >= 2;
+    // W_sc sc as 16-bit block fixed point: the CTA-pair kernel's quantising epilogue + the TMA-ring tail. The S
+    // buffer keeps its fp32 size: u16 rows in the first half, the [nd * n, 4] scales behind them.
+    static const bool s32 = getenv("EVI_S_F32") != nullptr;
+    sq16 = mm16 && !s32;
+    (void)tail_mode;
+  }
+  uint8_t* s_rows(int dir_slot) const {  // dir_slot: 0 = first direction present, 1 = second
+    return reinterpret_cast<uint8_t*>(S) + static_cast<size_t>(dir_slot) * n * D * (sq16 ? 2 : 4);
+  }
+  float* s_scales(int dir_slot) const {
+    return reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(S) + nd * n * D * 2) + static_cast<size_t>(dir_slot) * n * 4;
   }
 
   int operand(cudaStream_t stream) const {
@@ -969,7 +1038,14 @@ struct ChunkPlan {
                   : gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, gemm_sms, stream, nullptr, MM, D);
     if (rc != kOk) return rc;
     if (time_begin) cudaEventRecord(time_begin, stream);
-    rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, gemm_sms, stream, nullptr, S, D);
+    if (sq16) {
+      gemm::EpiQ16Tma::Params qp;
+      qp.scale = s_scales(0), qp.ld_scale = D / 256;
+      rc = gemm2::launch<FMT, gemm::EpiQ16Tma>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, qp, gemm_sms, stream,
+                                               nullptr, S, D);
+    } else {
+      rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, gemm_sms, stream, nullptr, S, D);
+    }
     if (time_end) cudaEventRecord(time_end, stream);
     return rc;
   }
@@ -983,27 +1059,33 @@ struct ChunkPlan {
     float* edge_emb = a.edge_embeddings ? a.edge_embeddings + static_cast<size_t>(e0) * D : nullptr;
     TailParams tp;
     tp.w_dist = a.w1_dist_col, tp.ln_g = a.ln1_g, tp.ln_b = a.ln1_b, tp.v = a.head_v, tp.c0 = a.head_c0;
-    const float* s_f = do_f ? S : nullptr;
-    const float* s_b = do_b ? S + (do_f ? n * D : 0) : nullptr;
+    const void* sq_f = do_f ? s_rows(0) : nullptr;
+    const void* sq_b = do_b ? s_rows(do_f ? 1 : 0) : nullptr;
+    const float4* sqs_f = reinterpret_cast<const float4*>(s_scales(0));
+    const float4* sqs_b = reinterpret_cast<const float4*>(s_scales(do_f ? 1 : 0));
     uint16_t* g_f = G;
     uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
     const bool feats = a.want_features != 0;
     if (tail_mode == 1) {
       const int warps = tail_threads / 32;
       const int tgrid = static_cast<int>((E + warps - 1) / warps);
-      auto kern = mm16 ? score_tail_kernel<FMT, true> : score_tail_kernel<FMT, false>;
+      auto kern = sq16   ? score_tail_kernel<FMT, true, true>
+                  : mm16 ? score_tail_kernel<FMT, true, false>
+                         : score_tail_kernel<FMT, false, false>;
       kern<<<tgrid, tail_threads, 0, stream>>>(
-          MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+          MM, sq_f, sq_b, sqs_f, sqs_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     } else {
-      auto kern = mm16 ? score_tail_bulk_kernel<FMT, true> : score_tail_bulk_kernel<FMT, false>;
-      static std::atomic<unsigned long long> smem_ready[2] = {{0}, {0}};  // per FMT instantiation, per MM format
-      if (!ensure_dynamic_smem(kern, kTailSmemBytes, smem_ready[mm16 ? 1 : 0])) return kErrCuda;
+      auto kern = sq16   ? score_tail_bulk_kernel<FMT, true, true>
+                  : mm16 ? score_tail_bulk_kernel<FMT, true, false>
+                         : score_tail_bulk_kernel<FMT, false, false>;
+      static std::atomic<unsigned long long> smem_ready[3] = {{0}, {0}, {0}};  // per FMT instantiation, per row format
+      if (!ensure_dynamic_smem(kern, kTailSmemBytes, smem_ready[sq16 ? 2 : mm16 ? 1 : 0])) return kErrCuda;
       const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
       const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
       kern<<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
-          MM, s_f, s_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+          MM, sq_f, sq_b, sqs_f, sqs_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     }
@@ -1054,7 +1136,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
     for (long long c = 0; c < nchunks; ++c) {
       const bool timed = c == (nchunks > 1 ? 1 : 0);
       const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-      ChunkPlan<FMT> plan(a, e0, n, ws, per);
+      ChunkPlan<FMT> plan(a, e0, n, ws, per, tail_mode_serial);
       if (!plan.ok) return kErrWorkspace;
       int rc = plan.operand(stream);
       if (rc != kOk) return rc;
@@ -1080,7 +1162,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   cudaEvent_t ev_start = evs[2 * nchunks], ev_end = evs[2 * nchunks + 1];
   auto plan_of = [&](long long c) {
     const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-    return ChunkPlan<FMT>(a, e0, n, ws + (c & 1) * per, per);
+    return ChunkPlan<FMT>(a, e0, n, ws + (c & 1) * per, per, tail_mode_pipe);
   };
   int rc = kOk;
   cudaEventRecord(ev_start, stream);

@@ -27,7 +27,20 @@ def rnd(x, dt):
     return x.to(dt).float() if dt is not None else x
 
 
-def gpu_model(sd, qb, ent, rel, op=torch.float16, uv=None, prq=None, part=None, sites=None, mm=None):
+def quant_rows_i16(x, block=256):
+    """W_sc sc rows as stored by the EpiQ16Tma epilogue: per (row, 256-column block) scale = max|x| / 32767 and
+    round-to-nearest 16-bit integers; the tail folds the dequantisation offset into one fma, which adds one fp32
+    rounding at 2^8 x the block maximum (modelled by the second term)."""
+    r, c = x.shape
+    xb = x.view(r, c // block, block)
+    mx = xb.abs().amax(-1, keepdim=True)
+    scale = torch.where(mx > 0, mx / 32767.0, torch.ones_like(mx))
+    q = torch.round(xb / scale)
+    fold = (torch.rand_like(xb) - 0.5) * (256.0 * mx * 2.0 ** -23)
+    return (q * scale + fold).view(r, c)
+
+
+def gpu_model(sd, qb, ent, rel, op=torch.float16, uv=None, prq=None, part=None, sites=None, mm=None, sq=False):
     """op: operand dtype; uv / prq / part: extra rounding of U,V / P,Rq / W_iv m, W_sc sc (None = fp32)."""
     t = torch.from_numpy
     W = lambda n: sd[n].float()
@@ -71,6 +84,8 @@ def gpu_model(sd, qb, ent, rel, op=torch.float16, uv=None, prq=None, part=None, 
         sc = F.gelu(ln(U[a] + V[b], "struct_proj.1"))
         nav = torch.sigmoid(sc @ W("struct_gate_net.0.weight")[0] + W("struct_gate_net.0.bias")[0])
         S = rnd(rnd(sc, S_.sc) @ w_sc.t(), part)
+        if sq:
+            S = quant_rows_i16(S)
         dist = -torch.norm(rc + sign * (h - tt), dim=-1)
         z = nav[:, None] * Mm + S + sign * (P[h_i] - P[t_i]) + Rq + dist[:, None] * w_d[None]
         g = F.gelu(ln(z, "state_net.1"))
@@ -105,6 +120,7 @@ def main():
             ("fp16 + partial products fp16", dict(op=torch.float16, part=torch.float16)),
             ("fp16 + U/V + P/Rq fp16", dict(op=torch.float16, uv=torch.float16, prq=torch.float16)),
             ("fp16 + W_iv m stored fp16", dict(op=torch.float16, mm=torch.float16)),
+            ("fp16 + W_iv m fp16 + W_sc sc int16/block (shipped)", dict(op=torch.float16, mm=torch.float16, sq=True)),
             ("fp16 + W_iv m stored bf16", dict(op=torch.float16, mm=torch.bfloat16)),
             ("bf16 operands", dict(op=torch.bfloat16)),
             ("fp16, fp32 kept: proj weights", dict(op=torch.float16, sites={"w"})),
