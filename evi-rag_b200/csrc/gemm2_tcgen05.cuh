@@ -248,10 +248,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 #pragma unroll
             for (int j = 0; j < 32; ++j) mx = fmaxf(mx, fabsf(__uint_as_float(r[j])));
           }
-          const bool live = mx > 0.f && mx < 3.0e38f;  // an all-zero (or non-finite) tile row stores zeros
+          // an all-zero tile row gets scale 0 (not 1: the reader's folded offset -(2^23 + 32768) * scale must vanish
+          // with the values, or its fp32 rounding would be an absolute error); a non-finite one gets NaN
+          const bool live = mx > 0.f && mx < 3.0e38f;
           q_inv = live ? 32767.0f / mx : 0.f;
           if (row < M && n_blk < ep.ld_scale)
-            ep.scale[static_cast<size_t>(row) * ep.ld_scale + n_blk] = live ? mx * (1.0f / 32767.0f) : 1.0f;
+            ep.scale[static_cast<size_t>(row) * ep.ld_scale + n_blk] = live ? mx * (1.0f / 32767.0f) : mx * 0.0f;
         }
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {

@@ -387,7 +387,7 @@ struct EpiF16Tma {
 // maximum (6.41e-4 -> 6.44e-4) while the launch writes, and the tail re-reads, half the bytes of fp32 rows.
 // The epilogue thread owns one accumulator row of the tile: a first pass over its TMEM columns finds max|acc|, the
 // second quantises u = rn(acc * 32767 / max) + 32768 through the 1.5 * 2^23 magic add (the low 16 bits of the sum)
-// and goes through the 16-bit staged TMA store. scale[row * ld_scale + n_blk] = max / 32767 (1 when the tile row is 0).
+// and goes through the 16-bit staged TMA store. scale[row * ld_scale + n_blk] = max / 32767 (0 when the tile row is 0).
 struct EpiQ16Tma {
   static constexpr bool kTmaStore = true;
   static constexpr bool kOut16 = true;

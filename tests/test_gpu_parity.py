@@ -384,6 +384,40 @@ def test_retriever_vs_oracle_medium_with_topk(dev):
             assert abs(refl[e0 + i] - kth) <= tol, (q, i)
 
 
+def test_zero_structure_context_rows(dev):
+    """struct_proj.1 (LayerNorm) with zero weight and bias makes sc = GELU(0) = 0 on every edge, so every W_sc sc
+    row is exactly zero: the 16-bit block fixed-point rows must then carry scale 0 (a dead block with scale 1 would
+    leave the tail's folded offset -(2^23 + 32768) * scale as an absolute error of ~0.5 in the pre-activation)."""
+    import types
+
+    from evi_rag_b200.retriever import Retriever
+
+    spec = tiny_spec(4, 700, seed=33, num_relations=48, num_entities=1500)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(5)
+    ent = (rng.standard_normal((1501, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((48, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(2, trained_like=True)
+    sd["struct_proj.1.weight"] = torch.zeros_like(sd["struct_proj.1.weight"])
+    sd["struct_proj.1.bias"] = torch.zeros_like(sd["struct_proj.1.bias"])
+    t = torch.from_numpy
+    ref = orc.retriever_forward(sd, edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
+                                node_embeddings=t(ent[qb.node_embedding_ids]), node_embedding_ids=t(qb.node_embedding_ids),
+                                edge_embeddings=t(rel[qb.edge_attr]), topic_one_hot=t(qb.topic_one_hot))
+    m = Retriever(emb_dim=1024, hidden_dim=1024).eval()
+    m.load_state_dict(sd)
+    m.to(dev)
+    m.attach_embedding_tables(t(ent), t(rel))
+    b = types.SimpleNamespace(edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
+                              node_embedding_ids=t(qb.node_embedding_ids), edge_attr=t(qb.edge_attr),
+                              topic_one_hot=t(qb.topic_one_hot))
+    out = m(b)
+    check_scores(out.logits.cpu().numpy(), ref.logits.numpy(), "fp16", "zero_sc/logits")
+    check_scores(out.logits_fwd.cpu().numpy(), ref.logits_fwd.numpy(), "fp16", "zero_sc/fwd")
+    check_scores(out.logits_bwd.cpu().numpy(), ref.logits_bwd.numpy(), "fp16", "zero_sc/bwd")
+
+
 def test_retriever_errors_and_empty(dev):
     from evi_rag_b200.retriever import Retriever
     import types
