@@ -197,6 +197,9 @@ EVI_DEVINL void st_cs_v4(void* p, const uint4& w) {
 
 // struct context of one direction: writes sc (16-bit) to `sc_out`, returns nav.
 // ua / vb: the U row of the first node and the V row of the second.
+#ifndef EVI_SC_GELU
+#define EVI_SC_GELU gelu_fast5  // sc is rounded to 16 bits on the spot; -DEVI_SC_GELU=gelu_fast for the degree-7 fit
+#endif
 template <int FMT>
 EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __restrict__ vb,
                                 const StructParams& sp, int lane, uint16_t* __restrict__ sc_out) {
@@ -231,7 +234,7 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
     ldg_v8_keep(sp.wn + c, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      y[j] = gelu_fast(fmaf(x[i * 8 + j] * rstd, g[j], b[j]));
+      y[j] = EVI_SC_GELU(fmaf(x[i * 8 + j] * rstd, g[j], b[j]));
       nav = fmaf(y[j], w[j], nav);
     }
     st_cs_v4(sc_out + c, pack8<FMT>(y));
@@ -280,8 +283,8 @@ EVI_DEVINL void struct_context_pair(const float* __restrict__ uv_h, const float*
     ldg_v8_keep(sp.wn + c, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      yf[j] = gelu_fast(fmaf(xf[i * 8 + j] * rstd_f, g[j], b[j]));
-      yb[j] = gelu_fast(fmaf(xb[i * 8 + j] * rstd_b, g[j], b[j]));
+      yf[j] = EVI_SC_GELU(fmaf(xf[i * 8 + j] * rstd_f, g[j], b[j]));
+      yb[j] = EVI_SC_GELU(fmaf(xb[i * 8 + j] * rstd_b, g[j], b[j]));
       acc_f = fmaf(yf[j], w[j], acc_f);
       acc_b = fmaf(yb[j], w[j], acc_b);
     }

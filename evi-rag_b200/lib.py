@@ -10,7 +10,8 @@ import os
 from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libevi_rag_b200.so")
+# EVI_LIB_PATH: another build of the same library (A/B of compile-time choices on one GPU box)
+LIB_PATH = os.environ.get("EVI_LIB_PATH") or os.path.join(_HERE, "libevi_rag_b200.so")
 
 EVI_OK = 0
 _STATUS = {1: "invalid argument", 2: "CUDA error", 3: "workspace too small", 4: "unsupported shape"}
