@@ -558,7 +558,7 @@ score_tail_kernel(const void* __restrict__ mm,                                  
 }
 
 // Same tail, fed by the TMA engine: persistent CTAs of 16 warps around a ring of eight 24 KB shared-memory
-// buffers. 1-D bulk copies fill a buffer with the six fp32 rows of one edge (W_iv m, W_sc sc_f, W_sc sc_b,
+// buffers. 1-D bulk copies fill a buffer with the six rows of one edge (W_iv m, W_sc sc_f, W_sc sc_b in fp32 or 16 bits,
 // P[h], P[t], Rq[pair]); warps b and b+8 take turns on buffer b: the warp that has just moved its edge
 // from the buffer into registers hands the buffer back to the TMA engine for its partner's next edge and
 // then does LayerNorm / GELU / the head dot in registers. 192 KB stay in flight per SM without spending
@@ -948,6 +948,8 @@ static int linear_act_impl(const void* x16, int m, const int* m_dev, const void*
 
 // workspace of one chunk of `E` edges:
 //   m16 [E, D] 16-bit | sc16 [nd*E, D] 16-bit | mm [E, D] f32 | s [nd*E, D] f32 | scal [E] float4
+//   (the mm / s regions keep their fp32 size; by default they hold fp16 rows, and u16 block fixed-point rows followed
+//   by the [nd*E, 4] block scales: ChunkPlan::mm16 / sq16)
 //   (features) g16 [nd*E, D] 16-bit | feat [nd*E, D] f32
 static size_t chunk_workspace_bytes(long long num_edges, int direction, int want_features) {
   const size_t nd = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
