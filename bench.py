@@ -360,6 +360,9 @@ def run_ours(args):
             "workload": workload_name(QB), "top_k": TOP_K, "bfs_depth": BFS_DEPTH, "parallelism": f"questions sharded x{world}",
             "l2": "fresh batch every step; per-step working set (operand rows + activations) is several GB >> 126 MB L2",
             "edges_per_step": e_all / args.steps / world, "validation_flags": flags_word,
+            "intermediates": ("W_iv m rows fp16, W_sc sc rows 16-bit block fixed point (one fp32 scale per row and 256 columns), "
+                              "everything else fp32; scores within 1e-3 of the fp32 reference (tests/test_gpu_parity.py)"
+                              if W_SC_EPILOGUE == "EpiQ16Tma" else "fp32 partial products (experiment knob set)"),
         },
         "e2e": {"value": q_all / (ms_e2e * 1e-3), "unit": "questions/s",
                 "h2d_bytes_per_step": h2d_bytes(host_batches[args.warmup]), "d2h_bytes_per_step": d2h,
