@@ -574,7 +574,7 @@ constexpr int kTailSmemBytes = kTailBufs * kTailBufBytes + kTailWarps * 8;
 // SQ16: the W_sc sc rows arrive as 16-bit block fixed point (gemm::EpiQ16Tma): u16 values with one fp32 scale per
 // (row, 256-column block) in s_scale_*[edge * 4 + block]; value = (u - 32768) * scale. The u16 is spliced under the
 // exponent of 2^23 (one PRMT), and the constant -(2^23 + 32768) * scale rides in an existing fma addend.
-template <int FMT, bool MM16, bool SQ16>
+template <int FMT, bool MM16, bool SQ16, bool BIDIR = false>
 __global__ void __launch_bounds__(kTailWarps * 32, 1)
 score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_fwd, const void* __restrict__ s_bwd,
                        const float4* __restrict__ s_scale_fwd, const float4* __restrict__ s_scale_bwd,
@@ -589,7 +589,8 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail_smem + kTailBufs * kTailBufBytes);
   uint64_t* my_bar = bars + warp;
   uint64_t* partner_bar = bars + (warp + kTailBufs) % kTailWarps;
-  const bool has_f = s_fwd != nullptr, has_b = s_bwd != nullptr;
+  // BIDIR: both directions present, known at compile time (the default bidirectional mode)
+  const bool has_f = BIDIR || s_fwd != nullptr, has_b = BIDIR || s_bwd != nullptr;
   constexpr uint32_t kMmRowBytes = MM16 ? D * 2 : kTailRowBytes;  // W_iv m rows are fp16 when MM16
   constexpr uint32_t kSRowBytes = SQ16 ? D * 2 : kTailRowBytes;   // W_sc sc rows are 16-bit fixed point when SQ16
   const uint32_t tx_bytes = static_cast<uint32_t>(3 * kTailRowBytes) +
@@ -1082,11 +1083,13 @@ struct ChunkPlan {
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     } else {
-      auto kern = sq16   ? score_tail_bulk_kernel<FMT, true, true>
+      const bool bidir = sq16 && do_f && do_b;
+      auto kern = bidir  ? score_tail_bulk_kernel<FMT, true, true, true>
+                  : sq16 ? score_tail_bulk_kernel<FMT, true, true>
                   : mm16 ? score_tail_bulk_kernel<FMT, true, false>
                          : score_tail_bulk_kernel<FMT, false, false>;
-      static std::atomic<unsigned long long> smem_ready[3] = {{0}, {0}, {0}};  // per FMT instantiation, per row format
-      if (!ensure_dynamic_smem(kern, kTailSmemBytes, smem_ready[sq16 ? 2 : mm16 ? 1 : 0])) return kErrCuda;
+      static std::atomic<unsigned long long> smem_ready[4] = {{0}, {0}, {0}, {0}};  // per FMT instantiation, per variant
+      if (!ensure_dynamic_smem(kern, kTailSmemBytes, smem_ready[bidir ? 3 : sq16 ? 2 : mm16 ? 1 : 0])) return kErrCuda;
       const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
       const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
       kern<<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(

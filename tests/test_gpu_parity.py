@@ -418,6 +418,21 @@ def test_zero_structure_context_rows(dev):
     check_scores(out.logits_bwd.cpu().numpy(), ref.logits_bwd.numpy(), "fp16", "zero_sc/bwd")
 
 
+@pytest.mark.parametrize("knob", ["EVI_S_F32", "EVI_MM_F32"])
+def test_fp32_partial_product_knobs(dev, knob):
+    """The experiment knobs that keep fp32 rows for W_sc sc / W_iv m are read once per process: run two scorer
+    parity tests in a child process with the knob set, so the fp32 code paths stay green next to the default."""
+    import subprocess
+    import sys
+
+    env = dict(os.environ, **{knob: "1"})
+    here = os.path.abspath(__file__)
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu",
+                        f"{here}::test_retriever_vs_oracle_medium_with_topk", f"{here}::test_zero_structure_context_rows"],
+                       env=env, capture_output=True, text=True, timeout=600, cwd=os.path.dirname(os.path.dirname(here)))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_retriever_errors_and_empty(dev):
     from evi_rag_b200.retriever import Retriever
     import types
