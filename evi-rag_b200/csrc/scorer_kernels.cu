@@ -304,7 +304,7 @@ constexpr int kEdgeWarps = 8;
 //   m16  [E, D]   h * r_ctx * t            (shared by both directions: iv_dir = nav_dir * m)
 //   sc16 [nd*E, D] struct context, forward rows first, then backward rows
 //   scal [E, 4]   nav_f, nav_b, dist_f, dist_b
-template <int FMT>
+template <int FMT, bool BIDIR = false>
 __global__ void __launch_bounds__(kEdgeWarps * 32, EVI_OPERAND_CTAS)
 edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
@@ -330,7 +330,7 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
     const float* uv_h = node_uv + static_cast<size_t>(h) * 2 * D;
     const float* uv_t = node_uv + static_cast<size_t>(t) * 2 * D;
     float nav_f = 0.f, nav_b = 0.f;
-    if (do_fwd && do_bwd)
+    if (BIDIR || (do_fwd && do_bwd))  // BIDIR: both directions, known at compile time (the default mode)
       struct_context_pair<FMT>(uv_h, uv_t, sp, lane, sc_fwd + static_cast<size_t>(e) * D,
                                sc_bwd + static_cast<size_t>(e) * D, nav_f, nav_b);
     else if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, sc_fwd + static_cast<size_t>(e) * D);
@@ -1025,7 +1025,8 @@ struct ChunkPlan {
     // L2 while its edges are processed; a larger grid makes later waves sweep the chunk again from DRAM
     const long long resident = static_cast<long long>(EVI_OPERAND_CTAS) * a.num_sms;
     const int grid = static_cast<int>(want < resident ? want : resident);
-    edge_operand_kernel<FMT><<<grid, kEdgeWarps * 32, 0, stream>>>(
+    auto kern = do_f && do_b ? edge_operand_kernel<FMT, true> : edge_operand_kernel<FMT, false>;
+    kern<<<grid, kEdgeWarps * 32, 0, stream>>>(
         a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
         static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
         a.num_rel_rows, a.num_questions, a.flags, M16, sc_f, sc_b, SCAL);
