@@ -426,7 +426,8 @@ EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uin
 }
 
 // Both directions of one edge in one pass over the parameter vectors (ln_g, ln_b, v are read once per edge)
-template <int FMT>
+// FEATS = false: the GELU outputs are not stored (no feature path), so they need not be kept in registers
+template <int FMT, bool FEATS = true>
 EVI_DEVINL void tail_finish_pair(float (&zf)[32], float (&zb)[32], const TailParams& tp, int lane,
                                  uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd, float& lf, float& lb) {
   float rstd_f, shift_f, rstd_b, shift_b;
@@ -444,13 +445,15 @@ EVI_DEVINL void tail_finish_pair(float (&zf)[32], float (&zb)[32], const TailPar
     for (int j = 0; j < 8; ++j) {
       const float yf = gelu_fast(fmaf(fmaf(zf[i * 8 + j], rstd_f, shift_f), gg[j], bb[j]));
       const float yb = gelu_fast(fmaf(fmaf(zb[i * 8 + j], rstd_b, shift_b), gg[j], bb[j]));
-      zf[i * 8 + j] = yf, zb[i * 8 + j] = yb;
+      if constexpr (FEATS) zf[i * 8 + j] = yf, zb[i * 8 + j] = yb;
       acc_f = fmaf(yf, vv[j], acc_f);
       acc_b = fmaf(yb, vv[j], acc_b);
     }
   }
-  if (g_fwd != nullptr) store_row16<FMT>(g_fwd, lane, zf);
-  if (g_bwd != nullptr) store_row16<FMT>(g_bwd, lane, zb);
+  if constexpr (FEATS) {
+    if (g_fwd != nullptr) store_row16<FMT>(g_fwd, lane, zf);
+    if (g_bwd != nullptr) store_row16<FMT>(g_bwd, lane, zb);
+  }
   lf = warp_sum(acc_f) + tp.c0;
   lb = warp_sum(acc_b) + tp.c0;
 }
@@ -589,7 +592,7 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
   uint64_t* bars = reinterpret_cast<uint64_t*>(tail_smem + kTailBufs * kTailBufBytes);
   uint64_t* my_bar = bars + warp;
   uint64_t* partner_bar = bars + (warp + kTailBufs) % kTailWarps;
-  // BIDIR: both directions present, known at compile time (the default bidirectional mode)
+  // BIDIR: both directions present and no feature rows wanted, known at compile time (the default mode)
   const bool has_f = BIDIR || s_fwd != nullptr, has_b = BIDIR || s_bwd != nullptr;
   constexpr uint32_t kMmRowBytes = MM16 ? D * 2 : kTailRowBytes;  // W_iv m rows are fp16 when MM16
   constexpr uint32_t kSRowBytes = SQ16 ? D * 2 : kTailRowBytes;   // W_sc sc rows are 16-bit fixed point when SQ16
@@ -696,7 +699,9 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
       issue(partner_bar, e_part, hn, tn, pn);
     }
     float lf = 0.f, lb = 0.f;
-    if (has_f && has_b)
+    if constexpr (BIDIR)  // both directions, logits only
+      tail_finish_pair<FMT, false>(zf, zb, tp, lane, nullptr, nullptr, lf, lb);
+    else if (has_f && has_b)
       tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr,
                             g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr, lf, lb);
     else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
@@ -1084,7 +1089,7 @@ struct ChunkPlan {
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     } else {
-      const bool bidir = sq16 && do_f && do_b;
+      const bool bidir = sq16 && do_f && do_b && !feats;  // the compile-time variant: both directions, logits only
       auto kern = bidir  ? score_tail_bulk_kernel<FMT, true, true, true>
                   : sq16 ? score_tail_bulk_kernel<FMT, true, true>
                   : mm16 ? score_tail_bulk_kernel<FMT, true, false>
