@@ -983,7 +983,7 @@ struct ChunkPlan {
   float4* SCAL;
   bool ok, mm16, sq16;
 
-  ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes, int tail_mode)
+  ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes)
       : a(args), e0(e0_), E(E_), G(nullptr), FEAT(nullptr) {
     do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
     nd = static_cast<size_t>(do_f + do_b);
@@ -1007,11 +1007,10 @@ struct ChunkPlan {
     // W_iv m in fp16 needs the CTA-pair kernel's 16-bit TMA-store epilogue
     static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr, mm32 = getenv("EVI_MM_F32") != nullptr;
     mm16 = !one_sm && !mm32 && a.num_sms >= 2;
-    // W_sc sc as 16-bit block fixed point: the CTA-pair kernel's quantising epilogue + the TMA-ring tail. The S
+    // W_sc sc as 16-bit block fixed point: the CTA-pair kernel's quantising epilogue; both tail kernels read it. The S
     // buffer keeps its fp32 size: u16 rows in the first half, the [nd * n, 4] scales behind them.
     static const bool s32 = getenv("EVI_S_F32") != nullptr;
     sq16 = mm16 && !s32;
-    (void)tail_mode;
   }
   uint8_t* s_rows(int dir_slot) const {  // dir_slot: 0 = first direction present, 1 = second
     return reinterpret_cast<uint8_t*>(S) + static_cast<size_t>(dir_slot) * n * D * (sq16 ? 2 : 4);
@@ -1150,7 +1149,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
     for (long long c = 0; c < nchunks; ++c) {
       const bool timed = c == (nchunks > 1 ? 1 : 0);
       const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-      ChunkPlan<FMT> plan(a, e0, n, ws, per, tail_mode_serial);
+      ChunkPlan<FMT> plan(a, e0, n, ws, per);
       if (!plan.ok) return kErrWorkspace;
       int rc = plan.operand(stream);
       if (rc != kOk) return rc;
@@ -1176,7 +1175,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
   cudaEvent_t ev_start = evs[2 * nchunks], ev_end = evs[2 * nchunks + 1];
   auto plan_of = [&](long long c) {
     const long long e0 = c * chunk, n = E - e0 < chunk ? E - e0 : chunk;
-    return ChunkPlan<FMT>(a, e0, n, ws + (c & 1) * per, per, tail_mode_pipe);
+    return ChunkPlan<FMT>(a, e0, n, ws + (c & 1) * per, per);
   };
   int rc = kOk;
   cudaEventRecord(ev_start, stream);
