@@ -108,7 +108,7 @@ template <int FMT, class Epi>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
              const __grid_constant__ CUtensorMap tmap_c, int M, int N, int K, const int* __restrict__ m_dev,
-             typename Epi::Params ep) {
+             typename Epi::Params ep, const gemm::SplitK sk) {
   if (m_dev != nullptr) {
     const int md = __ldg(m_dev);
     M = md < M ? md : M;
@@ -133,7 +133,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
   const int num_m_blocks = (M + BM - 1) / BM;
   const int num_n_blocks = (N + BN - 1) / BN;
   const int num_tiles = num_m_blocks * num_n_blocks;
-  const int num_k_blocks = (K + BK - 1) / BK;
+  const int k_blocks_per_pass = (K + BK - 1) / BK;
+  const int num_k_blocks = k_blocks_per_pass * sk.passes;  // split operands: up to three passes over K (gemm::SplitK)
 
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -165,13 +166,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         const int m_blk = tile / num_n_blocks, n_blk = tile % num_n_blocks;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
+          const int pass = kb / k_blocks_per_pass, kk = (kb - pass * k_blocks_per_pass) * BK;
           mbar_wait_guarded(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_STAGE_BYTES;
           if (leader) mbar_arrive_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
           const uint32_t lbar = map_to_cta(smem_u32(&full_bar[stage]), 0);
-          tma_load_2d_pair(sa, &tmap_a, lbar, kb * BK, m_blk * BM + static_cast<int>(rank) * BM_CTA);
-          tma_load_2d_pair(sb, &tmap_b, lbar, kb * BK, n_blk * BN + static_cast<int>(rank) * BN_CTA);
+          tma_load_2d_pair(sa, &tmap_a, lbar, sk.a_off[pass] + kk, m_blk * BM + static_cast<int>(rank) * BM_CTA);
+          tma_load_2d_pair(sb, &tmap_b, lbar, sk.b_off[pass] + kk, n_blk * BN + static_cast<int>(rank) * BN_CTA);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1u;
@@ -358,14 +360,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
 template <int FMT, class Epi>
 inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const typename Epi::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev = nullptr,
-                  void* out = nullptr, int ldc = 0) {  // out: fp32 rows, or 16-bit rows when Epi::kOut16
+                  void* out = nullptr, int ldc = 0,  // out: fp32 rows, or 16-bit rows when Epi::kOut16
+                  const gemm::SplitK& sk = gemm::make_split(-1, -1)) {
   if (M <= 0) return kOk;
   if (K % 8 != 0 || lda % 8 != 0 || ldb % 8 != 0 || N % 32 != 0) return kErrInvalidArg;
+  if (sk.passes > 1 && K % BK != 0) return kErrInvalidArg;
+  const int wa = gemm::split_width(sk, sk.a_off, K), wb = gemm::split_width(sk, sk.b_off, K);
+  if (wa > lda || wb > ldb) return kErrInvalidArg;
   CUtensorMap ta, tb;
-  if (!gemm::make_tmap_2d(&ta, FMT, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K), static_cast<uint64_t>(lda),
+  if (!gemm::make_tmap_2d(&ta, FMT, A, static_cast<uint64_t>(M), static_cast<uint64_t>(wa), static_cast<uint64_t>(lda),
                           BM_CTA))
     return kErrCuda;
-  if (!gemm::make_tmap_2d(&tb, FMT, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K), static_cast<uint64_t>(ldb),
+  if (!gemm::make_tmap_2d(&tb, FMT, B, static_cast<uint64_t>(N), static_cast<uint64_t>(wb), static_cast<uint64_t>(ldb),
                           BN_CTA))
     return kErrCuda;
   CUtensorMap tc = ta;
@@ -389,7 +395,7 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int pairs_max = num_sms / 2;
   const int pairs = tiles < pairs_max ? tiles : pairs_max;
-  kern<<<2 * pairs, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, M, N, K, m_dev, ep);
+  kern<<<2 * pairs, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, M, N, K, m_dev, ep, sk);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 

@@ -41,11 +41,31 @@ struct TileCoord {
   int m_blk, n_blk;
 };
 
+// K-block schedule over split operands. A 16-bit operand row may carry a second half `lo = x - fp16(x)` at a column
+// offset of the same matrix ([hi | lo] rows); the contraction then runs up to three passes over K into the same fp32
+// accumulator:  A_hi B_hi  (+ A_lo B_hi)  (+ A_hi B_lo)   -- the lo * lo term is below fp32 rounding.
+// Two fp16 halves carry ~22 significant bits, so a split contraction is as good as an fp32 one
+// (tests/test_gpu_parity.py::test_project_split_matches_fp32); lo halves of small weights are fp16 subnormals, which
+// the tensor core takes as they are.
+struct SplitK {
+  int passes;    // 1..3
+  int a_off[3];  // K coordinate (elements) where pass p starts in A's rows
+  int b_off[3];
+};
+inline SplitK make_split(int a_lo_off, int b_lo_off) {  // negative offset: that operand has no lo half
+  SplitK s;
+  s.passes = 1;
+  for (int i = 0; i < 3; ++i) s.a_off[i] = 0, s.b_off[i] = 0;
+  if (a_lo_off >= 0) s.a_off[s.passes] = a_lo_off, s.b_off[s.passes] = 0, ++s.passes;
+  if (b_lo_off >= 0) s.a_off[s.passes] = 0, s.b_off[s.passes] = b_lo_off, ++s.passes;
+  return s;
+}
+
 template <int FMT, class Epi>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
             const __grid_constant__ CUtensorMap tmap_c, int M, int N, int K, const int* __restrict__ m_dev,
-            typename Epi::Params ep) {
+            typename Epi::Params ep, const SplitK sk) {
   // optional device-side row count (e.g. the number of distinct (question, relation) pairs, known
   // only on the device): rows beyond it are neither loaded nor written
   if (m_dev != nullptr) {
@@ -68,7 +88,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
   const int num_m_blocks = (M + BM - 1) / BM;
   const int num_n_blocks = (N + BN - 1) / BN;
   const int num_tiles = num_m_blocks * num_n_blocks;
-  const int num_k_blocks = (K + BK - 1) / BK;
+  const int k_blocks_per_pass = (K + BK - 1) / BK;
+  const int num_k_blocks = k_blocks_per_pass * sk.passes;  // split operands: up to three passes over K
 
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -102,12 +123,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ 
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         const int m_blk = tile / num_n_blocks, n_blk = tile % num_n_blocks;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
+          const int pass = kb / k_blocks_per_pass, kk = (kb - pass * k_blocks_per_pass) * BK;
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_STAGE_BYTES;
           mbar_arrive_expect_tx(&full_bar[stage], STAGE_BYTES);
-          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BK, m_blk * BM);
-          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BK, n_blk * BN);
+          tma_load_2d(sa, &tmap_a, &full_bar[stage], sk.a_off[pass] + kk, m_blk * BM);
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], sk.b_off[pass] + kk, n_blk * BN);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1u;
@@ -242,6 +264,7 @@ struct EpiBiasAct {
     float* out32;        // [M, ld32] or null
     int ld16, ld32;
     int act[8];          // per n-block activation
+    int lo_off;          // >= 0: out16 rows are [hi | lo], lo = out - hi stored at this column offset; < 0: hi only
   };
   struct RowState {};
   static EVI_DEVINL void init_row(RowState&) {}
@@ -259,7 +282,7 @@ struct EpiBiasAct {
       v[i + 3] = __uint_as_float(r[i + 3]) + b.w;
     }
     if (act == kActTanh) {
-      if (p.out32 == nullptr) {
+      if (p.out32 == nullptr && p.lo_off < 0) {
         // 16-bit output only (the per-node / per-relation projections): tanh_fast is good to ~1e-6, far below the
         // 2^-12 rounding of the store, and keeps the epilogue shorter than the tile's MMA time
 #pragma unroll
@@ -288,6 +311,16 @@ struct EpiBiasAct {
         w.z = Op16<FMT>::pack2(v[8 * i + 4], v[8 * i + 5]);
         w.w = Op16<FMT>::pack2(v[8 * i + 6], v[8 * i + 7]);
         o[i] = w;
+        if (p.lo_off >= 0) {  // residual half: the next contraction reads [hi | lo] rows (SplitK)
+          const float2 h0 = Op16<FMT>::unpack2(w.x), h1 = Op16<FMT>::unpack2(w.y), h2 = Op16<FMT>::unpack2(w.z),
+                       h3 = Op16<FMT>::unpack2(w.w);
+          uint4 l;
+          l.x = Op16<FMT>::pack2(v[8 * i + 0] - h0.x, v[8 * i + 1] - h0.y);
+          l.y = Op16<FMT>::pack2(v[8 * i + 2] - h1.x, v[8 * i + 3] - h1.y);
+          l.z = Op16<FMT>::pack2(v[8 * i + 4] - h2.x, v[8 * i + 5] - h2.y);
+          l.w = Op16<FMT>::pack2(v[8 * i + 6] - h3.x, v[8 * i + 7] - h3.y);
+          o[i + p.lo_off / 8] = l;
+        }
       }
     }
   }
@@ -556,17 +589,27 @@ inline bool make_tmap_2d(CUtensorMap* map, int fmt, const void* base, uint64_t r
   return r == CUDA_SUCCESS;
 }
 
+// columns a tensor map must address from the operand's base pointer: K, or the end of the last split pass
+inline int split_width(const SplitK& sk, const int (&off)[3], int K) {
+  int w = K;
+  for (int i = 0; i < sk.passes; ++i) w = off[i] + K > w ? off[i] + K : w;
+  return w;
+}
+
 template <int FMT, class Epi>
 inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const typename Epi::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev = nullptr,
-                  float* out32 = nullptr, int ldc = 0) {
+                  float* out32 = nullptr, int ldc = 0, const SplitK& sk = make_split(-1, -1)) {
   if (M <= 0) return kOk;
   if (K % 8 != 0 || lda % 8 != 0 || ldb % 8 != 0 || N % 32 != 0) return kErrInvalidArg;
+  if (sk.passes > 1 && K % BK != 0) return kErrInvalidArg;  // a pass must end on a k-block boundary
+  const int wa = split_width(sk, sk.a_off, K), wb = split_width(sk, sk.b_off, K);
+  if (wa > lda || wb > ldb) return kErrInvalidArg;
   CUtensorMap ta, tb;
-  if (!make_tmap_2d(&ta, FMT, A, static_cast<uint64_t>(M), static_cast<uint64_t>(K),
+  if (!make_tmap_2d(&ta, FMT, A, static_cast<uint64_t>(M), static_cast<uint64_t>(wa),
                     static_cast<uint64_t>(lda), BM))
     return kErrCuda;
-  if (!make_tmap_2d(&tb, FMT, B, static_cast<uint64_t>(N), static_cast<uint64_t>(K),
+  if (!make_tmap_2d(&tb, FMT, B, static_cast<uint64_t>(N), static_cast<uint64_t>(wb),
                     static_cast<uint64_t>(ldb), BN))
     return kErrCuda;
   CUtensorMap tc = ta;  // placeholder when the epilogue stores by itself
@@ -580,7 +623,7 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
   if (!ensure_dynamic_smem(kern, SMEM_BYTES, smem_ready)) return kErrCuda;
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < num_sms ? tiles : num_sms;
-  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, M, N, K, m_dev, ep);
+  kern<<<grid, NUM_THREADS, SMEM_BYTES, stream>>>(ta, tb, tc, M, N, K, m_dev, ep, sk);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 

@@ -23,25 +23,29 @@ static inline int check_launch() { return cudaGetLastError() == cudaSuccess ? kO
 template <int FMT>
 static int gemm_f32(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                     const gemm::EpiF32Tma::Params& ep, int num_sms, cudaStream_t stream, const int* m_dev, float* out32,
-                    int ldc) {
+                    int ldc, const gemm::SplitK& sk = gemm::make_split(-1, -1)) {
   static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr;
   if (one_sm || num_sms < 2)
-    return gemm::launch<FMT, gemm::EpiF32Tma>(A, lda, B, ldb, M, N, K, ep, num_sms, stream, m_dev, out32, ldc);
-  return gemm2::launch<FMT, gemm::EpiF32Tma>(A, lda, B, ldb, M, N, K, ep, num_sms, stream, m_dev, out32, ldc);
+    return gemm::launch<FMT, gemm::EpiF32Tma>(A, lda, B, ldb, M, N, K, ep, num_sms, stream, m_dev, out32, ldc, sk);
+  return gemm2::launch<FMT, gemm::EpiF32Tma>(A, lda, B, ldb, M, N, K, ep, num_sms, stream, m_dev, out32, ldc, sk);
 }
 
 // ---------------------------------------------------------------------------------------------
-// Row gather / convert: fp32 or 16-bit source rows -> dense 16-bit GEMM operand.
+// Row gather / convert: fp32 or 16-bit source rows -> dense 16-bit GEMM operand rows.
 // ids == nullptr: identity. Rows with sub_mask_ids[row] == 0 take `sub_row` (fp32) instead
 // (the non-text entity embedding, retriever.py:499-506 — tanh(W x + b) is applied by the GEMM
 // epilogue, so substituting the *input* row is equivalent to substituting the projected row).
+// SPLIT: destination rows are [hi | lo] (lo = x - hi at column D, gemm::SplitK); a 16-bit source then holds
+// [hi | lo] rows as well, an fp32 source (or the substitute row) is split on the fly.
+// rows_dev (optional): device-side row count, e.g. the number of distinct embedding ids of a batch.
 // ---------------------------------------------------------------------------------------------
-template <int FMT, bool SRC_F32>
-__global__ void gather_rows_kernel(const void* __restrict__ src, long long src_rows,
+template <int FMT, bool SRC_F32, bool SPLIT>
+__global__ void gather_rows_kernel(const void* __restrict__ src, long long src_rows, int src_ld,
                                    const long long* __restrict__ ids, const long long* __restrict__ sub_mask_ids,
-                                   const float* __restrict__ sub_row, int num_rows,
-                                   uint16_t* __restrict__ dst, unsigned* __restrict__ flags) {
+                                   const float* __restrict__ sub_row, int num_rows, const int* __restrict__ rows_dev,
+                                   uint16_t* __restrict__ dst, int dst_ld, unsigned* __restrict__ flags) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (rows_dev != nullptr) num_rows = min(num_rows, __ldg(rows_dev));
   if (row >= num_rows) return;
   const int lane = threadIdx.x & 31;
   long long sid = ids ? __ldg(ids + row) : row;
@@ -50,25 +54,35 @@ __global__ void gather_rows_kernel(const void* __restrict__ src, long long src_r
     if (lane == 0) atomicOr(flags, kFlagOutOfRange);
     sid = 0;
   }
-  uint4* out = reinterpret_cast<uint4*>(dst + static_cast<size_t>(row) * D);
+  uint16_t* out = dst + static_cast<size_t>(row) * dst_ld;
 #pragma unroll
   for (int i = 0; i < D / 256; ++i) {
     const int col = i * 256 + lane * 8;
-    float v[8];
     if (substitute || SRC_F32) {
-      const float* s = substitute ? sub_row : reinterpret_cast<const float*>(src) + static_cast<size_t>(sid) * D;
-      const float4 a = __ldg(reinterpret_cast<const float4*>(s + col));
-      const float4 b = __ldg(reinterpret_cast<const float4*>(s + col + 4));
-      v[0] = a.x, v[1] = a.y, v[2] = a.z, v[3] = a.w, v[4] = b.x, v[5] = b.y, v[6] = b.z, v[7] = b.w;
+      const float* sp = substitute ? sub_row : reinterpret_cast<const float*>(src) + static_cast<size_t>(sid) * src_ld;
+      const float4 a = __ldg(reinterpret_cast<const float4*>(sp + col));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(sp + col + 4));
+      const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
       uint4 w;
       w.x = Op16<FMT>::pack2(v[0], v[1]);
       w.y = Op16<FMT>::pack2(v[2], v[3]);
       w.z = Op16<FMT>::pack2(v[4], v[5]);
       w.w = Op16<FMT>::pack2(v[6], v[7]);
-      out[i * 32 + lane] = w;
+      *reinterpret_cast<uint4*>(out + col) = w;
+      if (SPLIT) {
+        const float2 h0 = Op16<FMT>::unpack2(w.x), h1 = Op16<FMT>::unpack2(w.y), h2 = Op16<FMT>::unpack2(w.z),
+                     h3 = Op16<FMT>::unpack2(w.w);
+        uint4 l;
+        l.x = Op16<FMT>::pack2(v[0] - h0.x, v[1] - h0.y);
+        l.y = Op16<FMT>::pack2(v[2] - h1.x, v[3] - h1.y);
+        l.z = Op16<FMT>::pack2(v[4] - h2.x, v[5] - h2.y);
+        l.w = Op16<FMT>::pack2(v[6] - h3.x, v[7] - h3.y);
+        *reinterpret_cast<uint4*>(out + D + col) = l;
+      }
     } else {
-      out[i * 32 + lane] =
-          ldg_nc_v4(reinterpret_cast<const uint16_t*>(src) + static_cast<size_t>(sid) * D + col);
+      const uint16_t* sp = reinterpret_cast<const uint16_t*>(src) + static_cast<size_t>(sid) * src_ld;
+      *reinterpret_cast<uint4*>(out + col) = ldg_nc_v4(sp + col);
+      if (SPLIT) *reinterpret_cast<uint4*>(out + D + col) = ldg_nc_v4(sp + D + col);
     }
   }
 }
@@ -136,10 +150,14 @@ node_struct_proj_kernel(const float* __restrict__ node_struct, int num_nodes, in
 // Lane l owns columns {256*i + 8*l .. +7}, i = 0..3  (128-bit loads / stores).
 // ---------------------------------------------------------------------------------------------
 struct StructParams {
-  const float* ln_g;   // [D] struct_proj.1.weight
-  const float* ln_b;   // [D]
-  const float* wn;     // [D] struct_gate_net.0.weight
+  const float* ln_g;    // [D] struct_proj.1.weight
+  const float* ln_b;    // [D]
+  const float* wn;      // [D] struct_gate_net.0.weight
   float bn;
+  // [D] or null: a batch-constant row c subtracted from sc before it is rounded to 16 bits. W_sc sc = W_sc (sc - c) +
+  // W_sc c, and the caller adds W_sc c (fp32 weights) to the pair bias: the rounding error of the operand scales with
+  // |sc - c| instead of |sc| (most edges of a batch have similar structure contexts), at no tensor cost.
+  const float* center;
 };
 
 template <int FMT>
@@ -195,12 +213,31 @@ EVI_DEVINL void st_cs_v4(void* p, const uint4& w) {
                : "memory");
 }
 
+// one 8-column group of an operand row: the 16-bit value at row[c], and with SPLIT its residual at row[D + c]
+template <int FMT, bool SPLIT>
+EVI_DEVINL void store_operand8(uint16_t* __restrict__ row, int c, const float (&v)[8]) {
+  const uint4 w = pack8<FMT>(v);
+  st_cs_v4(row + c, w);
+  if constexpr (SPLIT) {
+    float h[8], l[8];
+    unpack8<FMT>(w, h);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) l[j] = v[j] - h[j];
+    st_cs_v4(row + D + c, pack8<FMT>(l));
+  }
+}
+
 // struct context of one direction: writes sc (16-bit) to `sc_out`, returns nav.
 // ua / vb: the U row of the first node and the V row of the second.
 #ifndef EVI_SC_GELU
 #define EVI_SC_GELU gelu_fast5  // sc is rounded to 16 bits on the spot; -DEVI_SC_GELU=gelu_fast for the degree-7 fit
 #endif
-template <int FMT>
+template <bool SPLIT>
+EVI_DEVINL float sc_gelu(float x) {
+  if constexpr (SPLIT) return gelu_fast(x);  // [hi | lo] rows keep ~22 bits: the degree-7 fit (4.8e-7)
+  else return EVI_SC_GELU(x);
+}
+template <int FMT, bool SPLIT>
 EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __restrict__ vb,
                                 const StructParams& sp, int lane, uint16_t* __restrict__ sc_out) {
   float x[32];
@@ -234,17 +271,23 @@ EVI_DEVINL float struct_context(const float* __restrict__ ua, const float* __res
     ldg_v8_keep(sp.wn + c, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      y[j] = EVI_SC_GELU(fmaf(x[i * 8 + j] * rstd, g[j], b[j]));
+      y[j] = sc_gelu<SPLIT>(fmaf(x[i * 8 + j] * rstd, g[j], b[j]));
       nav = fmaf(y[j], w[j], nav);
     }
-    st_cs_v4(sc_out + c, pack8<FMT>(y));
+    if (sp.center != nullptr) {
+      float cen[8];
+      ldg_v8_keep(sp.center + c, cen);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) y[j] -= cen[j];
+    }
+    store_operand8<FMT, SPLIT>(sc_out, c, y);
   }
   return 1.0f / (1.0f + __expf(-(warp_sum(nav) + sp.bn)));
 }
 
 // Both directions of one edge in one pass over the parameter vectors: x_f = U[h] + V[t], x_b = U[t] + V[h].
 // ln_g / ln_b / w_n are read once per edge instead of once per direction (the kernel is bound by L1 throughput).
-template <int FMT>
+template <int FMT, bool SPLIT>
 EVI_DEVINL void struct_context_pair(const float* __restrict__ uv_h, const float* __restrict__ uv_t,
                                     const StructParams& sp, int lane, uint16_t* __restrict__ sc_f,
                                     uint16_t* __restrict__ sc_b, float& nav_f, float& nav_b) {
@@ -283,13 +326,19 @@ EVI_DEVINL void struct_context_pair(const float* __restrict__ uv_h, const float*
     ldg_v8_keep(sp.wn + c, w);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      yf[j] = EVI_SC_GELU(fmaf(xf[i * 8 + j] * rstd_f, g[j], b[j]));
-      yb[j] = EVI_SC_GELU(fmaf(xb[i * 8 + j] * rstd_b, g[j], b[j]));
+      yf[j] = sc_gelu<SPLIT>(fmaf(xf[i * 8 + j] * rstd_f, g[j], b[j]));
+      yb[j] = sc_gelu<SPLIT>(fmaf(xb[i * 8 + j] * rstd_b, g[j], b[j]));
       acc_f = fmaf(yf[j], w[j], acc_f);
       acc_b = fmaf(yb[j], w[j], acc_b);
     }
-    st_cs_v4(sc_f + c, pack8<FMT>(yf));
-    st_cs_v4(sc_b + c, pack8<FMT>(yb));
+    if (sp.center != nullptr) {
+      float cen[8];
+      ldg_v8_keep(sp.center + c, cen);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) yf[j] -= cen[j], yb[j] -= cen[j];
+    }
+    store_operand8<FMT, SPLIT>(sc_f, c, yf);
+    store_operand8<FMT, SPLIT>(sc_b, c, yb);
   }
   nav_f = 1.0f / (1.0f + __expf(-(warp_sum(acc_f) + sp.bn)));
   nav_b = 1.0f / (1.0f + __expf(-(warp_sum(acc_b) + sp.bn)));
@@ -301,46 +350,56 @@ constexpr int kEdgeWarps = 8;
 #endif
 
 // Operand rows of one chunk of edges (the inputs of the two per-edge contractions of state_net.0):
-//   m16  [E, D]   h * r_ctx * t            (shared by both directions: iv_dir = nav_dir * m)
-//   sc16 [nd*E, D] struct context, forward rows first, then backward rows
-//   scal [E, 4]   nav_f, nav_b, dist_f, dist_b
-template <int FMT, bool BIDIR = false>
+//   m16  [E, ld]    h * r_ctx * t            (shared by both directions: iv_dir = nav_dir * m)
+//   sc16 [nd*E, ld] struct context (minus the batch centre), forward rows first, then backward rows
+//   scal [E, 4]     nav_f, nav_b, dist_f, dist_b
+// ld = D, or 2D with SPLIT ([hi | lo] rows for the three-pass contraction of the strict mode; the node / relation
+// rows are then read as hi + lo too).
+// head / tail index the per-node rows U | V; head_rep / tail_rep the rows of node_repr (one per distinct embedding id).
+template <int FMT, bool BIDIR = false, bool SPLIT = false>
 __global__ void __launch_bounds__(kEdgeWarps * 32, EVI_OPERAND_CTAS)
-edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ qid,
+edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, const int* __restrict__ head_rep,
+                    const int* __restrict__ tail_rep, const int* __restrict__ qid,
                     const int* __restrict__ rel_slot, long long num_edges,
-                    const uint16_t* __restrict__ node_repr,   // [N, D]
-                    const uint16_t* __restrict__ rel_repr,    // [R, D]
+                    const uint16_t* __restrict__ node_repr, int node_ld,   // [rep rows, node_ld]
+                    const uint16_t* __restrict__ rel_repr, int rel_ld,     // [R, rel_ld]
                     const float* __restrict__ gate_bias,      // [B, 2D]: sigmoid gate | tanh bias
                     const float* __restrict__ node_uv,        // [N, 2D]: U | V (node_struct_proj_kernel)
-                    StructParams sp, int do_fwd, int do_bwd, int num_nodes, int num_rel_rows, int num_questions,
-                    unsigned* __restrict__ flags,
+                    StructParams sp, int do_fwd, int do_bwd, int num_nodes, int num_rep_rows, int num_rel_rows,
+                    int num_questions, unsigned* __restrict__ flags,
                     uint16_t* __restrict__ m16, uint16_t* __restrict__ sc_fwd, uint16_t* __restrict__ sc_bwd,
                     float4* __restrict__ scal) {
+  constexpr int kRowLd = SPLIT ? 2 * D : D;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long stride = static_cast<long long>(gridDim.x) * kEdgeWarps;
   for (long long e = blockIdx.x * static_cast<long long>(kEdgeWarps) + warp; e < num_edges; e += stride) {
     int h = __ldg(head + e), t = __ldg(tail + e), q = __ldg(qid + e), rs = __ldg(rel_slot + e);
+    int hr = __ldg(head_rep + e), tr = __ldg(tail_rep + e);
     if (static_cast<unsigned>(h) >= static_cast<unsigned>(num_nodes) ||
         static_cast<unsigned>(t) >= static_cast<unsigned>(num_nodes) ||
+        static_cast<unsigned>(hr) >= static_cast<unsigned>(num_rep_rows) ||
+        static_cast<unsigned>(tr) >= static_cast<unsigned>(num_rep_rows) ||
         static_cast<unsigned>(q) >= static_cast<unsigned>(num_questions) ||
         static_cast<unsigned>(rs) >= static_cast<unsigned>(num_rel_rows)) {
       if (lane == 0) atomicOr(flags, kFlagOutOfRange);  // keep going on row 0: no wild reads
-      h = t = q = rs = 0;
+      h = t = q = rs = hr = tr = 0;
     }
     const float* uv_h = node_uv + static_cast<size_t>(h) * 2 * D;
     const float* uv_t = node_uv + static_cast<size_t>(t) * 2 * D;
     float nav_f = 0.f, nav_b = 0.f;
     if (BIDIR || (do_fwd && do_bwd))  // BIDIR: both directions, known at compile time (the default mode)
-      struct_context_pair<FMT>(uv_h, uv_t, sp, lane, sc_fwd + static_cast<size_t>(e) * D,
-                               sc_bwd + static_cast<size_t>(e) * D, nav_f, nav_b);
-    else if (do_fwd) nav_f = struct_context<FMT>(uv_h, uv_t + D, sp, lane, sc_fwd + static_cast<size_t>(e) * D);
-    else if (do_bwd) nav_b = struct_context<FMT>(uv_t, uv_h + D, sp, lane, sc_bwd + static_cast<size_t>(e) * D);
+      struct_context_pair<FMT, SPLIT>(uv_h, uv_t, sp, lane, sc_fwd + static_cast<size_t>(e) * kRowLd,
+                                      sc_bwd + static_cast<size_t>(e) * kRowLd, nav_f, nav_b);
+    else if (do_fwd)
+      nav_f = struct_context<FMT, SPLIT>(uv_h, uv_t + D, sp, lane, sc_fwd + static_cast<size_t>(e) * kRowLd);
+    else if (do_bwd)
+      nav_b = struct_context<FMT, SPLIT>(uv_t, uv_h + D, sp, lane, sc_bwd + static_cast<size_t>(e) * kRowLd);
 
-    const uint16_t* hp = node_repr + static_cast<size_t>(h) * D;
-    const uint16_t* tp = node_repr + static_cast<size_t>(t) * D;
-    const uint16_t* rp = rel_repr + static_cast<size_t>(rs) * D;
+    const uint16_t* hp = node_repr + static_cast<size_t>(hr) * node_ld;
+    const uint16_t* tp = node_repr + static_cast<size_t>(tr) * node_ld;
+    const uint16_t* rp = rel_repr + static_cast<size_t>(rs) * rel_ld;
     const float* gp = gate_bias + static_cast<size_t>(q) * 2 * D;
-    uint16_t* mrow = m16 + static_cast<size_t>(e) * D;
+    uint16_t* mrow = m16 + static_cast<size_t>(e) * kRowLd;
     float n2f = 0.f, n2b = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -349,6 +408,18 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
       unpack8<FMT>(ldg_nc_v4(hp + c), hv);
       unpack8<FMT>(ldg_nc_v4(tp + c), tv);
       unpack8<FMT>(ldg_nc_v4(rp + c), rv);
+      if constexpr (SPLIT) {  // the residual halves of the projected rows
+        float lo[8];
+        unpack8<FMT>(ldg_nc_v4(hp + D + c), lo);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) hv[j] += lo[j];
+        unpack8<FMT>(ldg_nc_v4(tp + D + c), lo);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) tv[j] += lo[j];
+        unpack8<FMT>(ldg_nc_v4(rp + D + c), lo);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) rv[j] += lo[j];
+      }
       ldg_v8_keep(gp + c, g);
       ldg_v8_keep(gp + D + c, b);
 #pragma unroll
@@ -360,11 +431,175 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
         n2b = fmaf(eb, eb, n2b);
         rv[j] = hv[j] * rv[j] * tv[j];  // symmetric DistMult term (retriever.py:472)
       }
-      st_cs_v4(mrow + c, pack8<FMT>(rv));
+      store_operand8<FMT, SPLIT>(mrow, c, rv);
     }
     n2f = warp_sum(n2f);
     n2b = warp_sum(n2b);
     if (lane == 0) scal[e] = make_float4(nav_f, nav_b, -sqrtf(n2f), -sqrtf(n2b));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Batch centre of the structure context (StructParams::center): the mean of sc over a fixed-stride sample of the
+// batch's edges (both directions). Any row would do for correctness — W_sc c is added back exactly — the mean is
+// the one that makes |sc - c| smallest. Deterministic: per-warp register sums, fixed-order reductions, no atomics.
+//   sc_center_partial_kernel: grid x 8 warps, partial [grid, D]
+//   sc_center_finish_kernel : center [D] = sum of partials / count
+//   sc_center_bias_kernel   : bias_out [H] = b1 + W_sc (fp32) center     (folded into Rq's bias)
+// ---------------------------------------------------------------------------------------------
+constexpr int kCenterCtas = 64;
+constexpr int kCenterSample = 4096;  // edges sampled per batch (each contributes its forward and backward rows)
+
+__global__ void __launch_bounds__(256)
+sc_center_partial_kernel(const int* __restrict__ head, const int* __restrict__ tail, long long num_edges,
+                         long long sample, const float* __restrict__ node_uv, int num_nodes,
+                         const float* __restrict__ ln_g, const float* __restrict__ ln_b, int do_fwd, int do_bwd,
+                         float* __restrict__ partial) {
+  __shared__ float red[8][D];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) acc[j] = 0.f;
+  const long long total_warps = static_cast<long long>(gridDim.x) * 8;
+  for (long long i = blockIdx.x * 8LL + warp; i < sample; i += total_warps) {
+    const long long e = sample >= num_edges ? i : (i * num_edges) / sample;
+    int h = __ldg(head + e), t = __ldg(tail + e);
+    if (static_cast<unsigned>(h) >= static_cast<unsigned>(num_nodes) ||
+        static_cast<unsigned>(t) >= static_cast<unsigned>(num_nodes))
+      h = t = 0;  // flagged by the operand kernel
+    for (int dir = 0; dir < 2; ++dir) {
+      if (dir == 0 ? !do_fwd : !do_bwd) continue;
+      const float* ua = node_uv + static_cast<size_t>(dir == 0 ? h : t) * 2 * D;
+      const float* vb = node_uv + static_cast<size_t>(dir == 0 ? t : h) * 2 * D + D;
+      float x[32];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int c = k * 256 + lane * 8;
+        float u[8], v[8];
+        ldg_v8_keep(ua + c, u);
+        ldg_v8_keep(vb + c, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) x[k * 8 + j] = u[j] + v[j];
+      }
+      float sum = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) sum += x[j];
+      const float mean = warp_sum(sum) * (1.0f / D);
+      float var = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        x[j] -= mean;
+        var = fmaf(x[j], x[j], var);
+      }
+      const float rstd = rsqrtf(warp_sum(var) * (1.0f / D) + kLnEps);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int c = k * 256 + lane * 8;
+        float g[8], b[8];
+        ldg_v8_keep(ln_g + c, g);
+        ldg_v8_keep(ln_b + c, b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[k * 8 + j] += gelu_fast(fmaf(x[k * 8 + j] * rstd, g[j], b[j]));
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][k * 256 + lane * 8 + j] = acc[k * 8 + j];
+  __syncthreads();
+  for (int c = threadIdx.x; c < D; c += blockDim.x) {
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += red[w][c];
+    partial[static_cast<size_t>(blockIdx.x) * D + c] = v;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+sc_center_finish_kernel(const float* __restrict__ partial, int num_partials, float inv_count, float* __restrict__ center) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D) return;
+  float v = 0.f;
+  for (int b = 0; b < num_partials; ++b) v += partial[static_cast<size_t>(b) * D + c];
+  center[c] = v * inv_count;
+}
+
+// one warp per output row j: bias_out[j] = b1[j] + sum_k w_sc32[j, k] * center[k]
+__global__ void __launch_bounds__(256)
+sc_center_bias_kernel(const float* __restrict__ w_sc32, const float* __restrict__ center, const float* __restrict__ b1,
+                      float* __restrict__ bias_out) {
+  const int j = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (j >= D) return;
+  const float* wr = w_sc32 + static_cast<size_t>(j) * D;
+  float acc = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int c = k * 256 + lane * 8;
+    float w[8], cv[8];
+    ldg_v8_stream(wr + c, w);
+    ldg_v8_keep(center + c, cv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc = fmaf(w[i], cv[i], acc);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) bias_out[j] = (b1 != nullptr ? __ldg(b1 + j) : 0.f) + acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Distinct embedding ids of a batch. tanh(W_e x + b) and P = W_err node_repr depend only on the embedding id
+// (retriever.py:497-507): 35 % of a WebQSP-shaped batch's nodes are non-text (one shared row) and the text ids of
+// 128 questions repeat, so the projection and the P contraction run once per distinct id.
+//   slot_map [table_rows] int32, all -1 between calls (claim -> lookup -> reset inside one call).
+//   Slot numbering follows an atomic counter (arbitrary); rows are computed independently, so nothing depends on it.
+// ---------------------------------------------------------------------------------------------
+__global__ void unique_claim_kernel(const long long* __restrict__ ids, int n, int* __restrict__ slot_map,
+                                    long long table_rows, long long* __restrict__ uniq_ids,
+                                    int* __restrict__ num_unique, unsigned* __restrict__ flags) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  long long id = __ldg(ids + i);
+  if (id < 0 || id >= table_rows) {
+    atomicOr(flags, kFlagOutOfRange);
+    id = 0;
+  }
+  if (atomicCAS(slot_map + id, -1, -2) == -1) {
+    const int s = atomicAdd(num_unique, 1);
+    uniq_ids[s] = id;
+    slot_map[id] = s;  // read by the next kernel only
+  }
+}
+__global__ void unique_lookup_kernel(const long long* __restrict__ ids, int n, const int* __restrict__ slot_map,
+                                     long long table_rows, int* __restrict__ node_slot) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  long long id = __ldg(ids + i);
+  if (id < 0 || id >= table_rows) id = 0;
+  node_slot[i] = slot_map[id];
+}
+__global__ void unique_reset_kernel(const long long* __restrict__ uniq_ids, const int* __restrict__ num_unique, int n,
+                                    int* __restrict__ slot_map) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || i >= __ldg(num_unique)) return;
+  slot_map[uniq_ids[i]] = -1;
+}
+// per-edge rows of node_repr / P (through node_slot) and the int32 relation row
+__global__ void edge_rep_index_kernel(const int* __restrict__ head, const int* __restrict__ tail, long long num_edges,
+                                      const int* __restrict__ node_slot, int num_nodes,
+                                      const long long* __restrict__ edge_attr, int* __restrict__ head_rep,
+                                      int* __restrict__ tail_rep, int* __restrict__ rel_slot) {
+  const long long e = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (e >= num_edges) return;
+  if (node_slot != nullptr) {
+    const int h = __ldg(head + e), t = __ldg(tail + e);
+    const bool ok = static_cast<unsigned>(h) < static_cast<unsigned>(num_nodes) &&
+                    static_cast<unsigned>(t) < static_cast<unsigned>(num_nodes);  // flagged by the operand kernel
+    head_rep[e] = ok ? __ldg(node_slot + h) : 0;
+    tail_rep[e] = ok ? __ldg(node_slot + t) : 0;
+  }
+  if (edge_attr != nullptr) {
+    const long long r = __ldg(edge_attr + e);
+    rel_slot[e] = r < 0 || r > 0x7fffffffLL ? -1 : static_cast<int>(r);  // -1: flagged as out of range downstream
   }
 }
 
@@ -875,12 +1110,13 @@ relation_pairs_kernel(const int* __restrict__ rel, const long long* __restrict__
   }
 }
 
-// rc16[slot] = fp16/bf16(rel_repr[pair_rel] * gate[pair_q] + bias[pair_q]); one warp per pair slot
-template <int FMT>
+// rc16[slot] = fp16/bf16(rel_repr[pair_rel] * gate[pair_q] + bias[pair_q]); one warp per pair slot.
+// SPLIT: rel_repr rows are [hi | lo] and so are the rc rows written (strict mode)
+template <int FMT, bool SPLIT>
 __global__ void __launch_bounds__(256)
 pair_context_kernel(const int* __restrict__ pair_q, const int* __restrict__ pair_rel, const int* __restrict__ num_pairs,
-                    int capacity, const uint16_t* __restrict__ rel_repr, int num_rel_rows,
-                    const float* __restrict__ gate_bias, int num_questions, uint16_t* __restrict__ rc16,
+                    int capacity, const uint16_t* __restrict__ rel_repr, int rel_ld, int num_rel_rows,
+                    const float* __restrict__ gate_bias, int num_questions, uint16_t* __restrict__ rc16, int rc_ld,
                     unsigned* __restrict__ flags) {
   const int slot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int n = min(__ldg(num_pairs), capacity);
@@ -892,19 +1128,33 @@ pair_context_kernel(const int* __restrict__ pair_q, const int* __restrict__ pair
     if (lane == 0) atomicOr(flags, kFlagOutOfRange);
     q = r = 0;
   }
-  const uint16_t* rp = rel_repr + static_cast<size_t>(r) * D;
+  const uint16_t* rp = rel_repr + static_cast<size_t>(r) * rel_ld;
   const float* gp = gate_bias + static_cast<size_t>(q) * 2 * D;
-  uint16_t* out = rc16 + static_cast<size_t>(slot) * D;
+  uint16_t* out = rc16 + static_cast<size_t>(slot) * rc_ld;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int c = i * 256 + lane * 8;
     float rv[8], g[8], b[8];
     unpack8<FMT>(ldg_nc_v4(rp + c), rv);
+    if constexpr (SPLIT) {
+      float lo[8];
+      unpack8<FMT>(ldg_nc_v4(rp + D + c), lo);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rv[j] += lo[j];
+    }
     ldg_v8_keep(gp + c, g);
     ldg_v8_keep(gp + D + c, b);
 #pragma unroll
     for (int j = 0; j < 8; ++j) rv[j] = fmaf(rv[j], g[j], b[j]);
-    *reinterpret_cast<uint4*>(out + c) = pack8<FMT>(rv);
+    const uint4 w = pack8<FMT>(rv);
+    *reinterpret_cast<uint4*>(out + c) = w;
+    if constexpr (SPLIT) {
+      float h[8];
+      unpack8<FMT>(w, h);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) rv[j] -= h[j];
+      *reinterpret_cast<uint4*>(out + D + c) = pack8<FMT>(rv);
+    }
   }
 }
 
@@ -912,44 +1162,57 @@ pair_context_kernel(const int* __restrict__ pair_q, const int* __restrict__ pair
 // host-side dispatch on operand format
 // -------------------------------------------------------------------------------------------
 template <int FMT>
-static int gather_rows_impl(const void* src, int src_is_f32, long long src_rows, const long long* ids,
-                            const long long* sub_mask_ids, const float* sub_row, int num_rows, void* dst,
-                            unsigned* flags, cudaStream_t stream) {
+static int gather_rows_impl(const void* src, int src_is_f32, long long src_rows, int src_ld, const long long* ids,
+                            const long long* sub_mask_ids, const float* sub_row, int num_rows, const int* rows_dev,
+                            void* dst, int dst_ld, int split, unsigned* flags, cudaStream_t stream) {
   if (num_rows <= 0) return kOk;
+  if (src_ld < (split && !src_is_f32 ? 2 * D : D) || dst_ld < (split ? 2 * D : D) || dst_ld % 8 != 0 ||
+      src_ld % (src_is_f32 ? 4 : 8) != 0)
+    return kErrInvalidArg;
   const int warps = 8;
   const int grid = (num_rows + warps - 1) / warps;
-  if (src_is_f32)
-    gather_rows_kernel<FMT, true><<<grid, warps * 32, 0, stream>>>(src, src_rows, ids, sub_mask_ids, sub_row,
-                                                                  num_rows, static_cast<uint16_t*>(dst), flags);
-  else
-    gather_rows_kernel<FMT, false><<<grid, warps * 32, 0, stream>>>(src, src_rows, ids, sub_mask_ids, sub_row,
-                                                                   num_rows, static_cast<uint16_t*>(dst), flags);
+  auto go = [&](auto kern) {
+    kern<<<grid, warps * 32, 0, stream>>>(src, src_rows, src_ld, ids, sub_mask_ids, sub_row, num_rows, rows_dev,
+                                          static_cast<uint16_t*>(dst), dst_ld, flags);
+  };
+  if (src_is_f32) {
+    if (split) go(gather_rows_kernel<FMT, true, true>);
+    else go(gather_rows_kernel<FMT, true, false>);
+  } else {
+    if (split) go(gather_rows_kernel<FMT, false, true>);
+    else go(gather_rows_kernel<FMT, false, false>);
+  }
   return check_launch();
 }
 
+// out = act(x W^T + b) with optional [hi | lo] halves of x (x_lo_off), W (w_lo_off) and of the 16-bit output (out_lo_off)
 template <int FMT>
-static int linear_act_impl(const void* x16, int m, const int* m_dev, const void* w16, int ldw, int n, int k,
-                           const float* bias, const int* act_per_block, void* out16, float* out32, int num_sms,
-                           cudaStream_t stream) {
+static int linear_act_impl(const void* x16, int ld_x, int x_lo_off, int m, const int* m_dev, const void* w16, int ldw,
+                           int w_lo_off, int n, int k, const float* bias, const int* act_per_block, void* out16, int ld16,
+                           int out_lo_off, float* out32, int num_sms, cudaStream_t stream) {
+  const gemm::SplitK sk = gemm::make_split(x_lo_off, w_lo_off);
   if (out16 == nullptr && out32 != nullptr) {  // fp32 only: staged TMA-store epilogue
     gemm::EpiF32Tma::Params t;
     t.bias = bias;
     for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
-    return gemm_f32<FMT>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out32, n);
+    return gemm_f32<FMT>(x16, ld_x, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out32, n, sk);
   }
   static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr;
-  if (out32 == nullptr && !one_sm && num_sms >= 2 && n % 64 == 0 && (reinterpret_cast<uintptr_t>(out16) & 15) == 0) {
+  if (out32 == nullptr && out_lo_off < 0 && !one_sm && num_sms >= 2 && n % 64 == 0 && ld16 % 8 == 0 &&
+      (reinterpret_cast<uintptr_t>(out16) & 15) == 0) {
     gemm::EpiBiasAct16Tma::Params t;  // 16-bit rows only: staged TMA store instead of per-thread row stores
     t.bias = bias;
     for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
-    return gemm2::launch<FMT, gemm::EpiBiasAct16Tma>(x16, k, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out16, n);
+    return gemm2::launch<FMT, gemm::EpiBiasAct16Tma>(x16, ld_x, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out16, ld16,
+                                                      sk);
   }
+  if (out_lo_off >= 0 && (out_lo_off % 8 != 0 || out_lo_off + n > ld16)) return kErrInvalidArg;
   gemm::EpiBiasAct::Params p;
-  p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = n, p.ld32 = n;
+  p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = ld16, p.ld32 = n, p.lo_off = out_lo_off;
   for (int i = 0; i < 8; ++i) p.act[i] = act_per_block[i];
   if (one_sm || num_sms < 2)
-    return gemm::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
-  return gemm2::launch<FMT, gemm::EpiBiasAct>(x16, k, w16, ldw, m, n, k, p, num_sms, stream, m_dev);
+    return gemm::launch<FMT, gemm::EpiBiasAct>(x16, ld_x, w16, ldw, m, n, k, p, num_sms, stream, m_dev, nullptr, 0, sk);
+  return gemm2::launch<FMT, gemm::EpiBiasAct>(x16, ld_x, w16, ldw, m, n, k, p, num_sms, stream, m_dev, nullptr, 0, sk);
 }
 
 // workspace of one chunk of `E` edges:
@@ -957,11 +1220,12 @@ static int linear_act_impl(const void* x16, int m, const int* m_dev, const void*
 //   (the mm / s regions keep their fp32 size; by default they hold fp16 rows, and u16 block fixed-point rows followed
 //   by the [nd*E, 4] block scales: ChunkPlan::mm16 / sq16)
 //   (features) g16 [nd*E, D] 16-bit | feat [nd*E, D] f32
-static size_t chunk_workspace_bytes(long long num_edges, int direction, int want_features) {
+static size_t chunk_workspace_bytes(long long num_edges, int direction, int want_features, int strict) {
   const size_t nd = direction == EVI_DIR_BIDIRECTIONAL ? 2 : 1;
   const size_t E = static_cast<size_t>(num_edges);
+  const size_t op_ld = strict ? 2 * D : D;  // strict: [hi | lo] operand rows
   auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
-  size_t total = al(E * D * 2) + al(nd * E * D * 2) + al(E * D * sizeof(float)) + al(nd * E * D * sizeof(float)) +
+  size_t total = al(E * op_ld * 2) + al(nd * E * op_ld * 2) + al(E * D * sizeof(float)) + al(nd * E * D * sizeof(float)) +
                  al(E * sizeof(float4));
   if (want_features) total += al(nd * E * D * 2) + al(nd * E * D * sizeof(float));
   return total + 256;
@@ -981,21 +1245,27 @@ struct ChunkPlan {
   uint16_t *M16, *SC16, *G;
   float *MM, *S, *FEAT;  // MM holds fp16 rows when mm16 (the buffer keeps its fp32 size)
   float4* SCAL;
-  bool ok, mm16, sq16;
+  bool ok, mm16, sq16, strict;
+  size_t op_ld;  // row pitch of the operand rows: D, or 2D in the strict mode ([hi | lo])
+  int w1_ld, w1_lo;
 
   ChunkPlan(const evi_score_args& args, long long e0_, long long E_, uint8_t* ws, size_t ws_bytes)
       : a(args), e0(e0_), E(E_), G(nullptr), FEAT(nullptr) {
     do_f = a.direction != EVI_DIR_BACKWARD, do_b = a.direction != EVI_DIR_FORWARD;
     nd = static_cast<size_t>(do_f + do_b);
     n = static_cast<size_t>(E);
+    strict = a.precision == EVI_PRECISION_STRICT;
+    op_ld = strict ? 2 * D : D;
+    w1_ld = a.w1_ld > 0 ? a.w1_ld : 3 * D;
+    w1_lo = a.w1_lo_off;
     size_t off = 0;
     auto take = [&](size_t bytes) {
       uint8_t* p = ws + off;
       off += (bytes + 255) & ~static_cast<size_t>(255);
       return p;
     };
-    M16 = reinterpret_cast<uint16_t*>(take(n * D * 2));
-    SC16 = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
+    M16 = reinterpret_cast<uint16_t*>(take(n * op_ld * 2));
+    SC16 = reinterpret_cast<uint16_t*>(take(nd * n * op_ld * 2));
     MM = reinterpret_cast<float*>(take(n * D * sizeof(float)));
     S = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
     SCAL = reinterpret_cast<float4*>(take(n * sizeof(float4)));
@@ -1003,10 +1273,10 @@ struct ChunkPlan {
       G = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
       FEAT = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
     }
-    ok = off <= ws_bytes;
+    ok = off <= ws_bytes && (!strict || (w1_lo > 0 && w1_lo + 3 * D <= w1_ld));
     // W_iv m in fp16 needs the CTA-pair kernel's 16-bit TMA-store epilogue
     static const bool one_sm = getenv("EVI_GEMM_1SM") != nullptr, mm32 = getenv("EVI_MM_F32") != nullptr;
-    mm16 = !one_sm && !mm32 && a.num_sms >= 2;
+    mm16 = !one_sm && !mm32 && a.num_sms >= 2 && !strict;  // strict keeps fp32 rows of both partial products
     // W_sc sc as 16-bit block fixed point: the CTA-pair kernel's quantising epilogue; both tail kernels read it. The S
     // buffer keeps its fp32 size: u16 rows in the first half, the [nd * n, 4] scales behind them.
     static const bool s32 = getenv("EVI_S_F32") != nullptr;
@@ -1021,19 +1291,25 @@ struct ChunkPlan {
 
   int operand(cudaStream_t stream) const {
     uint16_t* sc_f = SC16;
-    uint16_t* sc_b = SC16 + (do_f ? n * D : 0);
+    uint16_t* sc_b = SC16 + (do_f ? n * op_ld : 0);
     StructParams sp;
-    sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b;
+    sp.ln_g = a.struct_ln_g, sp.ln_b = a.struct_ln_b, sp.wn = a.nav_w, sp.bn = a.nav_b, sp.center = a.sc_center;
     const long long want = (E + kEdgeWarps - 1) / kEdgeWarps;
     // resident CTAs only: one sweep over the chunk in edge order, so the node rows of a question (~15 MB) stay in
     // L2 while its edges are processed; a larger grid makes later waves sweep the chunk again from DRAM
     const long long resident = static_cast<long long>(EVI_OPERAND_CTAS) * a.num_sms;
     const int grid = static_cast<int>(want < resident ? want : resident);
-    auto kern = do_f && do_b ? edge_operand_kernel<FMT, true> : edge_operand_kernel<FMT, false>;
+    auto kern = strict            ? edge_operand_kernel<FMT, false, true>
+                : do_f && do_b ? edge_operand_kernel<FMT, true, false>
+                               : edge_operand_kernel<FMT, false, false>;
+    const int* head_rep = a.head_rep32 != nullptr ? a.head_rep32 : a.head32;
+    const int* tail_rep = a.tail_rep32 != nullptr ? a.tail_rep32 : a.tail32;
+    const int rep_rows = a.num_rep_rows > 0 ? a.num_rep_rows : a.num_nodes;
     kern<<<grid, kEdgeWarps * 32, 0, stream>>>(
-        a.head32 + e0, a.tail32 + e0, a.qid32 + e0, a.rel_slot32 + e0, E, static_cast<const uint16_t*>(a.node_repr16),
-        static_cast<const uint16_t*>(a.rel_repr16), a.gate_bias32, a.node_uv32, sp, do_f, do_b, a.num_nodes,
-        a.num_rel_rows, a.num_questions, a.flags, M16, sc_f, sc_b, SCAL);
+        a.head32 + e0, a.tail32 + e0, head_rep + e0, tail_rep + e0, a.qid32 + e0, a.rel_slot32 + e0, E,
+        static_cast<const uint16_t*>(a.node_repr16), a.node_repr_ld > 0 ? a.node_repr_ld : D,
+        static_cast<const uint16_t*>(a.rel_repr16), a.rel_repr_ld > 0 ? a.rel_repr_ld : D, a.gate_bias32, a.node_uv32,
+        sp, do_f, do_b, a.num_nodes, rep_rows, a.num_rel_rows, a.num_questions, a.flags, M16, sc_f, sc_b, SCAL);
     return check_launch();
   }
 
@@ -1044,18 +1320,23 @@ struct ChunkPlan {
     gemm::EpiF32Tma::Params plain;
     plain.bias = nullptr;
     for (int i = 0; i < 8; ++i) plain.act[i] = gemm::kActNone;
-    int rc = mm16 ? gemm2::launch<FMT, gemm::EpiF16Tma>(M16, D, w1, 3 * D, static_cast<int>(E), D, D,
+    // strict: [hi | lo] operand rows against [hi | lo] weight blocks, three passes into the same accumulator
+    const gemm::SplitK sk = strict ? gemm::make_split(D, w1_lo) : gemm::make_split(-1, -1);
+    const int lda = static_cast<int>(op_ld);
+    int rc = mm16 ? gemm2::launch<FMT, gemm::EpiF16Tma>(M16, lda, w1, w1_ld, static_cast<int>(E), D, D,
                                                          gemm::EpiF16Tma::Params{}, gemm_sms, stream, nullptr, MM, D)
-                  : gemm_f32<FMT>(M16, D, w1, 3 * D, static_cast<int>(E), D, D, plain, gemm_sms, stream, nullptr, MM, D);
+                  : gemm_f32<FMT>(M16, lda, w1, w1_ld, static_cast<int>(E), D, D, plain, gemm_sms, stream, nullptr, MM, D,
+                                  sk);
     if (rc != kOk) return rc;
     if (time_begin) cudaEventRecord(time_begin, stream);
     if (sq16) {
       gemm::EpiQ16Tma::Params qp;
       qp.scale = s_scales(0), qp.ld_scale = D / 256;
-      rc = gemm2::launch<FMT, gemm::EpiQ16Tma>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, qp, gemm_sms, stream,
-                                               nullptr, S, D);
+      rc = gemm2::launch<FMT, gemm::EpiQ16Tma>(SC16, lda, w1 + D, w1_ld, static_cast<int>(nd * n), D, D, qp, gemm_sms,
+                                               stream, nullptr, S, D);
     } else {
-      rc = gemm_f32<FMT>(SC16, D, w1 + D, 3 * D, static_cast<int>(nd * n), D, D, plain, gemm_sms, stream, nullptr, S, D);
+      rc = gemm_f32<FMT>(SC16, lda, w1 + D, w1_ld, static_cast<int>(nd * n), D, D, plain, gemm_sms, stream, nullptr, S, D,
+                         sk);
     }
     if (time_end) cudaEventRecord(time_end, stream);
     return rc;
@@ -1077,6 +1358,10 @@ struct ChunkPlan {
     uint16_t* g_f = G;
     uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
     const bool feats = a.want_features != 0;
+    // the tail reads node ids only to fetch P rows, which exist once per distinct embedding id
+    const int* p_head = (a.head_rep32 != nullptr ? a.head_rep32 : a.head32) + e0;
+    const int* p_tail = (a.tail_rep32 != nullptr ? a.tail_rep32 : a.tail32) + e0;
+    const int p_rows = a.num_rep_rows > 0 ? a.num_rep_rows : a.num_nodes;
     if (tail_mode == 1) {
       const int warps = tail_threads / 32;
       const int tgrid = static_cast<int>((E + warps - 1) / warps);
@@ -1084,7 +1369,7 @@ struct ChunkPlan {
                   : mm16 ? score_tail_kernel<FMT, true, false>
                          : score_tail_kernel<FMT, false, false>;
       kern<<<tgrid, tail_threads, 0, stream>>>(
-          MM, sq_f, sq_b, sqs_f, sqs_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+          MM, sq_f, sq_b, sqs_f, sqs_b, SCAL, p_head, p_tail, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, p_rows,
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     } else {
@@ -1098,7 +1383,7 @@ struct ChunkPlan {
       const long long want_ctas = (E + kTailWarps - 1) / kTailWarps;
       const int bgrid = static_cast<int>(want_ctas < a.num_sms ? want_ctas : a.num_sms);  // one persistent CTA per SM
       kern<<<bgrid, kTailWarps * 32, kTailSmemBytes, stream>>>(
-          MM, sq_f, sq_b, sqs_f, sqs_b, SCAL, a.head32 + e0, a.tail32 + e0, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, a.num_nodes,
+          MM, sq_f, sq_b, sqs_f, sqs_b, SCAL, p_head, p_tail, a.pair_slot32 + e0, a.node_p32, a.pair_rq32, p_rows,
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     }
@@ -1133,7 +1418,7 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
     return kErrInvalidArg;
   const long long chunk = a.chunk_edges > 0 && a.chunk_edges < E ? a.chunk_edges : E;
   const long long nchunks = (E + chunk - 1) / chunk;
-  const size_t per = chunk_workspace_bytes(chunk, a.direction, a.want_features);
+  const size_t per = chunk_workspace_bytes(chunk, a.direction, a.want_features, a.precision == EVI_PRECISION_STRICT);
   if (a.workspace_bytes < per) return kErrWorkspace;
   uint8_t* ws = static_cast<uint8_t*>(a.workspace);
   // experiment knobs (A/B on the GPU box): tail kernel flavour / CTA size, SMs given to the GEMM
@@ -1214,20 +1499,30 @@ using namespace evi;
 extern "C" {
 
 size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features) {
-  return chunk_workspace_bytes(chunk_edges, direction, want_features);
+  return chunk_workspace_bytes(chunk_edges, direction, want_features, 0);
+}
+size_t evi_score_workspace_bytes2(long long chunk_edges, int direction, int want_features, int precision) {
+  return chunk_workspace_bytes(chunk_edges, direction, want_features, precision == EVI_PRECISION_STRICT);
+}
+
+int evi_gather_rows2(const void* src, int src_is_f32, long long src_rows, int src_ld, const long long* ids,
+                     const long long* sub_mask_ids, const float* sub_row, int num_rows, const int* num_rows_dev, int dim,
+                     void* dst16, int dst_ld, int split, int operand_format, unsigned* flags, cudaStream_t stream) {
+  if (dim != D) return kErrUnsupported;
+  if (operand_format == kFmtF16)
+    return gather_rows_impl<kFmtF16>(src, src_is_f32, src_rows, src_ld, ids, sub_mask_ids, sub_row, num_rows,
+                                     num_rows_dev, dst16, dst_ld, split, flags, stream);
+  if (operand_format == kFmtBF16)
+    return gather_rows_impl<kFmtBF16>(src, src_is_f32, src_rows, src_ld, ids, sub_mask_ids, sub_row, num_rows,
+                                      num_rows_dev, dst16, dst_ld, split, flags, stream);
+  return kErrInvalidArg;
 }
 
 int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const long long* ids,
                     const long long* sub_mask_ids, const float* sub_row, int num_rows, int dim, void* dst16,
                     int operand_format, unsigned* flags, cudaStream_t stream) {
-  if (dim != D) return kErrUnsupported;
-  if (operand_format == kFmtF16)
-    return gather_rows_impl<kFmtF16>(src, src_is_f32, src_rows, ids, sub_mask_ids, sub_row, num_rows, dst16, flags,
-                                     stream);
-  if (operand_format == kFmtBF16)
-    return gather_rows_impl<kFmtBF16>(src, src_is_f32, src_rows, ids, sub_mask_ids, sub_row, num_rows, dst16, flags,
-                                      stream);
-  return kErrInvalidArg;
+  return evi_gather_rows2(src, src_is_f32, src_rows, dim, ids, sub_mask_ids, sub_row, num_rows, nullptr, dim, dst16, dim,
+                          0, operand_format, flags, stream);
 }
 
 int evi_struct_project(const float* node_struct, int num_nodes, int ns_dim, const float* struct_w_t,
@@ -1255,17 +1550,73 @@ int evi_convert_f32(const float* src, void* dst16, long long count, int operand_
   return check_launch();
 }
 
+int evi_project_split(const void* x16, int ld_x, int x_lo_off, int num_rows, const int* num_rows_dev, const void* w16,
+                      int ld_w, int w_lo_off, int out_dim, int in_dim, const float* bias, const int* act_per_block,
+                      void* out16, int ld_out16, int out_lo_off, float* out32, int operand_format, int num_sms,
+                      cudaStream_t stream) {
+  if (out_dim % gemm::BN != 0 || out_dim / gemm::BN > 8 || in_dim % gemm::BK != 0 || ld_w < in_dim || ld_x < in_dim)
+    return kErrUnsupported;
+  if (out16 != nullptr && ld_out16 < out_dim) return kErrInvalidArg;
+  if (operand_format == kFmtF16)
+    return linear_act_impl<kFmtF16>(x16, ld_x, x_lo_off, num_rows, num_rows_dev, w16, ld_w, w_lo_off, out_dim, in_dim,
+                                    bias, act_per_block, out16, ld_out16, out_lo_off, out32, num_sms, stream);
+  if (operand_format == kFmtBF16)
+    return linear_act_impl<kFmtBF16>(x16, ld_x, x_lo_off, num_rows, num_rows_dev, w16, ld_w, w_lo_off, out_dim, in_dim,
+                                     bias, act_per_block, out16, ld_out16, out_lo_off, out32, num_sms, stream);
+  return kErrInvalidArg;
+}
+
 int evi_project(const void* x16, int num_rows, const int* num_rows_dev, const void* w16, int ld_w, int out_dim,
                 int in_dim, const float* bias, const int* act_per_block, void* out16, float* out32,
                 int operand_format, int num_sms, cudaStream_t stream) {
-  if (out_dim % gemm::BN != 0 || out_dim / gemm::BN > 8 || in_dim % gemm::BK != 0 || ld_w < in_dim) return kErrUnsupported;
-  if (operand_format == kFmtF16)
-    return linear_act_impl<kFmtF16>(x16, num_rows, num_rows_dev, w16, ld_w, out_dim, in_dim, bias, act_per_block, out16,
-                                    out32, num_sms, stream);
-  if (operand_format == kFmtBF16)
-    return linear_act_impl<kFmtBF16>(x16, num_rows, num_rows_dev, w16, ld_w, out_dim, in_dim, bias, act_per_block,
-                                     out16, out32, num_sms, stream);
-  return kErrInvalidArg;
+  return evi_project_split(x16, in_dim, -1, num_rows, num_rows_dev, w16, ld_w, -1, out_dim, in_dim, bias, act_per_block,
+                           out16, out_dim, -1, out32, operand_format, num_sms, stream);
+}
+
+int evi_sc_center(const int* head32, const int* tail32, long long num_edges, const float* node_uv32, int num_nodes,
+                  const float* struct_ln_g, const float* struct_ln_b, int direction, const float* w_sc32,
+                  const float* b1, float* workspace, size_t workspace_bytes, float* center, float* bias_out,
+                  cudaStream_t stream) {
+  if (num_edges <= 0) return kOk;
+  if (head32 == nullptr || tail32 == nullptr || node_uv32 == nullptr || struct_ln_g == nullptr || struct_ln_b == nullptr ||
+      w_sc32 == nullptr || workspace == nullptr || center == nullptr || bias_out == nullptr || num_nodes <= 0)
+    return kErrInvalidArg;
+  if (workspace_bytes < static_cast<size_t>(kCenterCtas) * D * sizeof(float)) return kErrWorkspace;
+  const int do_f = direction != EVI_DIR_BACKWARD, do_b = direction != EVI_DIR_FORWARD;
+  const long long sample = num_edges < kCenterSample ? num_edges : kCenterSample;
+  const int grid = static_cast<int>((sample + 7) / 8 < kCenterCtas ? (sample + 7) / 8 : kCenterCtas);
+  sc_center_partial_kernel<<<grid, 256, 0, stream>>>(head32, tail32, num_edges, sample, node_uv32, num_nodes, struct_ln_g,
+                                                     struct_ln_b, do_f, do_b, workspace);
+  sc_center_finish_kernel<<<D / 256, 256, 0, stream>>>(workspace, grid, 1.0f / static_cast<float>(sample * (do_f + do_b)),
+                                                       center);
+  sc_center_bias_kernel<<<D / 8, 256, 0, stream>>>(w_sc32, center, b1, bias_out);
+  return check_launch();
+}
+
+int evi_unique_rows(const long long* ids, int num_rows, int* slot_map, long long table_rows, long long* uniq_ids,
+                    int* node_slot, int* num_unique, unsigned* flags, cudaStream_t stream) {
+  if (num_rows <= 0) return kOk;
+  if (ids == nullptr || slot_map == nullptr || uniq_ids == nullptr || node_slot == nullptr || num_unique == nullptr ||
+      flags == nullptr || table_rows <= 0)
+    return kErrInvalidArg;
+  if (cudaMemsetAsync(num_unique, 0, sizeof(int), stream) != cudaSuccess) return kErrCuda;
+  const int grid = (num_rows + 255) / 256;
+  unique_claim_kernel<<<grid, 256, 0, stream>>>(ids, num_rows, slot_map, table_rows, uniq_ids, num_unique, flags);
+  unique_lookup_kernel<<<grid, 256, 0, stream>>>(ids, num_rows, slot_map, table_rows, node_slot);
+  unique_reset_kernel<<<grid, 256, 0, stream>>>(uniq_ids, num_unique, num_rows, slot_map);
+  return check_launch();
+}
+
+int evi_edge_rep_index(const int* head32, const int* tail32, long long num_edges, const int* node_slot, int num_nodes,
+                       const long long* edge_attr, int* head_rep32, int* tail_rep32, int* rel_slot32,
+                       cudaStream_t stream) {
+  if (num_edges <= 0) return kOk;
+  if (node_slot != nullptr && (head32 == nullptr || tail32 == nullptr || head_rep32 == nullptr || tail_rep32 == nullptr))
+    return kErrInvalidArg;
+  if (edge_attr != nullptr && rel_slot32 == nullptr) return kErrInvalidArg;
+  edge_rep_index_kernel<<<static_cast<int>((num_edges + 255) / 256), 256, 0, stream>>>(
+      head32, tail32, num_edges, node_slot, num_nodes, edge_attr, head_rep32, tail_rep32, rel_slot32);
+  return check_launch();
 }
 
 int evi_relation_pairs(const int* rel32, const long long* edge_ptr, int num_questions, int num_relations,
@@ -1286,22 +1637,35 @@ int evi_relation_pairs(const int* rel32, const long long* edge_ptr, int num_ques
   return check_launch();
 }
 
+int evi_pair_context2(const int* pair_q32, const int* pair_rel32, const int* num_pairs, int capacity,
+                      const void* rel_repr16, int rel_ld, int num_rel_rows, const float* gate_bias32, int num_questions,
+                      void* rc16, int rc_ld, int split, int operand_format, unsigned* flags, cudaStream_t stream) {
+  if (capacity <= 0) return kOk;
+  if (rel_ld < (split ? 2 * D : D) || rc_ld < (split ? 2 * D : D) || rel_ld % 8 != 0 || rc_ld % 8 != 0)
+    return kErrInvalidArg;
+  const int grid = (capacity + 7) / 8;
+  auto go = [&](auto kern) {
+    kern<<<grid, 256, 0, stream>>>(pair_q32, pair_rel32, num_pairs, capacity, static_cast<const uint16_t*>(rel_repr16),
+                                   rel_ld, num_rel_rows, gate_bias32, num_questions, static_cast<uint16_t*>(rc16), rc_ld,
+                                   flags);
+  };
+  if (operand_format == kFmtF16) {
+    if (split) go(pair_context_kernel<kFmtF16, true>);
+    else go(pair_context_kernel<kFmtF16, false>);
+  } else if (operand_format == kFmtBF16) {
+    if (split) go(pair_context_kernel<kFmtBF16, true>);
+    else go(pair_context_kernel<kFmtBF16, false>);
+  } else {
+    return kErrInvalidArg;
+  }
+  return check_launch();
+}
+
 int evi_pair_context(const int* pair_q32, const int* pair_rel32, const int* num_pairs, int capacity,
                      const void* rel_repr16, int num_rel_rows, const float* gate_bias32, int num_questions,
                      void* rc16, int operand_format, unsigned* flags, cudaStream_t stream) {
-  if (capacity <= 0) return kOk;
-  const int grid = (capacity + 7) / 8;
-  if (operand_format == kFmtF16)
-    pair_context_kernel<kFmtF16><<<grid, 256, 0, stream>>>(pair_q32, pair_rel32, num_pairs, capacity,
-                                                           static_cast<const uint16_t*>(rel_repr16), num_rel_rows,
-                                                           gate_bias32, num_questions, static_cast<uint16_t*>(rc16), flags);
-  else if (operand_format == kFmtBF16)
-    pair_context_kernel<kFmtBF16><<<grid, 256, 0, stream>>>(pair_q32, pair_rel32, num_pairs, capacity,
-                                                            static_cast<const uint16_t*>(rel_repr16), num_rel_rows,
-                                                            gate_bias32, num_questions, static_cast<uint16_t*>(rc16), flags);
-  else
-    return kErrInvalidArg;
-  return check_launch();
+  return evi_pair_context2(pair_q32, pair_rel32, num_pairs, capacity, rel_repr16, D, num_rel_rows, gate_bias32,
+                           num_questions, rc16, D, 0, operand_format, flags, stream);
 }
 
 int evi_score_edges(const evi_score_args* args, cudaStream_t stream) {

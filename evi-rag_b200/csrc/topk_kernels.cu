@@ -296,7 +296,7 @@ using namespace evi;
 
 extern "C" {
 
-int evi_abi_version(void) { return 4; }
+int evi_abi_version(void) { return 5; }
 
 int evi_segmented_topk(const float* scores, const long long* edge_ptr, int num_graphs, int k, int transform,
                        float* values, int* indices, int* counts, cudaStream_t stream) {

@@ -109,6 +109,7 @@ class GAgentSample:
     is_dummy_agent: bool = False
 
 
+@_lib.device_guard
 def node_softmax_logit(scores: torch.Tensor, head: torch.Tensor, tail: torch.Tensor, num_nodes: int, *,
                        temperature: float = 1.0, bias: float = 0.0, score_mode: str = SCORE_MODE_NODE_SOFTMAX):
     """``_node_softmax_logit`` (g_agent_builder.py:594-626) over any edge list with node ids in
@@ -143,6 +144,7 @@ def _ragged(lists: Sequence[Sequence[int]], dev) -> tuple:
             else torch.zeros(1, dtype=torch.long, device=dev)), torch.tensor(ptr, dtype=torch.long, device=dev)
 
 
+@_lib.device_guard
 def select_batch(*, logits: torch.Tensor, edge_index: torch.Tensor, edge_ptr: torch.Tensor, ptr: torch.Tensor,
                  edge_attr: torch.Tensor, labels: Optional[torch.Tensor], node_global_ids: torch.Tensor,
                  node_embedding_ids: torch.Tensor, start_entity_ids: Sequence[Sequence[int]],

@@ -48,6 +48,7 @@ def _raise_edge_flags(word: int) -> None:
         )
 
 
+@_lib.device_guard
 def compute_edge_batch(
     edge_index: torch.Tensor,
     *,
@@ -109,6 +110,11 @@ class GraphBatch:
         """``ptr`` is the host copy of the node offsets; ``ptr_dev`` an optional device copy (saves a
         synchronous pageable H2D when the caller already has one)."""
         dev = _dev(device)
+        with torch.cuda.device(dev):  # the C ABI launches on the current device
+            return cls._from_edge_index(edge_index, ptr, dev, validate, ptr_dev)
+
+    @classmethod
+    def _from_edge_index(cls, edge_index, ptr, dev, validate, ptr_dev) -> "GraphBatch":
         L = _lib.load()
         ei = torch.as_tensor(edge_index).to(device=dev, dtype=torch.long).contiguous()
         ptr_host = np.asarray(torch.as_tensor(ptr).cpu().numpy(), dtype=np.int64)
@@ -136,6 +142,7 @@ class GraphBatch:
         return self.edge_ptr_host
 
 
+@_lib.device_guard
 def dde_node_features(gb: GraphBatch, topic_one_hot: torch.Tensor, num_rounds: int = 2,
                       num_reverse_rounds: int = 2) -> torch.Tensor:
     """``Retriever._build_node_structure_features`` (retriever.py:519-553) on the device."""
@@ -152,6 +159,7 @@ def dde_node_features(gb: GraphBatch, topic_one_hot: torch.Tensor, num_rounds: i
     return ns
 
 
+@_lib.device_guard
 def build_csr(head32: torch.Tensor, tail32: torch.Tensor, num_nodes: int, mode: int) -> Tuple[torch.Tensor, torch.Tensor]:
     """CSR adjacency over batch-global ids (build_retrieval_pipeline.py:570-603)."""
     L = _lib.load()
@@ -166,6 +174,7 @@ def build_csr(head32: torch.Tensor, tail32: torch.Tensor, num_nodes: int, mode: 
     return row_ptr, adj
 
 
+@_lib.device_guard
 def bfs_jobs(row_ptr: torch.Tensor, adj: torch.Tensor, job_node_begin: np.ndarray, job_node_end: np.ndarray,
              job_src_ptr: np.ndarray, sources_local: np.ndarray, max_depth: int = -1,
              dist: Optional[torch.Tensor] = None, dist_off: Optional[np.ndarray] = None):
@@ -196,6 +205,7 @@ def bfs_jobs(row_ptr: torch.Tensor, adj: torch.Tensor, job_node_begin: np.ndarra
     return dist[:total], dist_off
 
 
+@_lib.device_guard
 def batched_bfs(gb: GraphBatch, sources: np.ndarray, src_ptr: np.ndarray, *, directed: bool = False,
                 max_depth: int = -1) -> torch.Tensor:
     """Multi-source hop distance for every question of the batch: ``sources`` are batch-global
@@ -211,6 +221,7 @@ def batched_bfs(gb: GraphBatch, sources: np.ndarray, src_ptr: np.ndarray, *, dir
     return dist
 
 
+@_lib.device_guard
 def _sweep_bfs(gb: GraphBatch, sources: np.ndarray, src_ptr: np.ndarray, *, directed: bool, max_depth: int) -> torch.Tensor:
     """Depth-capped multi-source BFS straight from the edge list (``evi_bfs_edge_sweep``)."""
     L = _lib.load()
@@ -231,6 +242,7 @@ def _sweep_bfs(gb: GraphBatch, sources: np.ndarray, src_ptr: np.ndarray, *, dire
     return dist[:n_total]
 
 
+@_lib.device_guard
 def batched_shortest_path_labels(gb: GraphBatch, seeds: np.ndarray, seed_ptr: np.ndarray, answers: np.ndarray,
                                  answer_ptr: np.ndarray, *, path_mode: str = "undirected",
                                  return_pairs: bool = False):
@@ -417,6 +429,7 @@ def _next_pow2(x: np.ndarray) -> np.ndarray:
     return (1 << np.ceil(np.log2(x)).astype(np.int64)).astype(np.int64)
 
 
+@_lib.device_guard
 def shortest_path_single_jobs(head32: torch.Tensor, tail32: torch.Tensor, edge_begin, edge_end, node_begin, node_end,
                               sources, src_ptr, targets, tgt_ptr, *, ids_are_global: bool = True,
                               max_len: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:

@@ -216,6 +216,10 @@ class PoolRetriever:
 
     # ------------------------------------------------------------------ steps 1-2: BFS + candidate cut
     def extract(self, seeds: torch.Tensor, seed_ptr: torch.Tensor) -> types.SimpleNamespace:
+        with torch.cuda.device(self.dev):  # the C ABI launches on the current device
+            return self._extract_on_device(seeds, seed_ptr)
+
+    def _extract_on_device(self, seeds: torch.Tensor, seed_ptr: torch.Tensor) -> types.SimpleNamespace:
         """``seeds`` = global node ids grouped by ``seed_ptr [Q+1]``. Returns the subgraph batch (device tensors under
         the reference's PyG attribute names) plus ``edge_global_id [E]`` and ``edge_ptr [Q+1]``."""
         dev = self.dev
@@ -358,6 +362,10 @@ class PoolRetriever:
         return s
 
     def score(self, b: types.SimpleNamespace, question_emb: torch.Tensor) -> Dict[str, torch.Tensor]:
+        with torch.cuda.device(self.dev):  # the C ABI launches on the current device
+            return self._score_on_device(b, question_emb)
+
+    def _score_on_device(self, b: types.SimpleNamespace, question_emb: torch.Tensor) -> Dict[str, torch.Tensor]:
         """Bidirectional scores of every candidate and the per-query top-k as global edge ids."""
         dev, k = self.dev, self.top_k
         Q = b.num_graphs

@@ -21,6 +21,7 @@ FMT_F16, FMT_BF16 = 0, 1
 DIR_BIDIRECTIONAL, DIR_FORWARD, DIR_BACKWARD = 0, 1, 2
 ACT_NONE, ACT_TANH, ACT_SIGMOID = 0, 1, 2
 TOPK_RAW, TOPK_SIGMOID = 0, 1
+PRECISION_FAST, PRECISION_STRICT = 0, 1
 
 _vp, _i, _ll, _f, _sz = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_size_t
 
@@ -45,6 +46,8 @@ class ScoreArgs(C.Structure):
         ("ev_gemm_begin", _vp), ("ev_gemm_end", _vp),
         ("chunk_edges", _ll),
         ("aux_stream", _vp),
+        ("precision", _i), ("node_repr_ld", _i), ("rel_repr_ld", _i), ("w1_ld", _i), ("w1_lo_off", _i),
+        ("num_rep_rows", _i), ("head_rep32", _vp), ("tail_rep32", _vp), ("sc_center", _vp),
     ]
 
 
@@ -91,6 +94,13 @@ PROTOTYPES = {
     "evi_shortest_path_pairs": (_i, [_vp, _vp, _i] + [_vp] * 9 + [_i] + [_vp] * 4 + [_vp]),
     "evi_shortest_path_single": (_i, [_vp, _vp, _i] + [_vp] * 8 + [_i] + [_vp] * 5 + [_i] + [_vp] * 3 + [_vp]),
     "evi_gather_rows": (_i, [_vp, _i, _ll, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp]),
+    "evi_gather_rows2": (_i, [_vp, _i, _ll, _i, _vp, _vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "evi_unique_rows": (_i, [_vp, _i, _vp, _ll, _vp, _vp, _vp, _vp, _vp]),
+    "evi_edge_rep_index": (_i, [_vp, _vp, _ll, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "evi_project_split": (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _vp]),
+    "evi_sc_center": (_i, [_vp, _vp, _ll, _vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _sz, _vp, _vp, _vp]),
+    "evi_pair_context2": (_i, [_vp, _vp, _vp, _i, _vp, _i, _i, _vp, _i, _vp, _i, _i, _i, _vp, _vp]),
+    "evi_score_workspace_bytes2": (_sz, [_ll, _i, _i, _i]),
     "evi_struct_project": (_i, [_vp, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_convert_f32": (_i, [_vp, _vp, _ll, _i, _vp]),
     "evi_project": (_i, [_vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
@@ -129,6 +139,12 @@ _KERNELS_PER_CALL = {
     "evi_shortest_path_pairs": lambda a: 1,
     "evi_shortest_path_single": lambda a: 1,
     "evi_gather_rows": lambda a: 1,
+    "evi_gather_rows2": lambda a: 1,
+    "evi_unique_rows": lambda a: 3 if a[1] > 0 else 0,
+    "evi_edge_rep_index": lambda a: 1 if a[2] > 0 else 0,
+    "evi_project_split": lambda a: 1,
+    "evi_sc_center": lambda a: 3 if a[2] > 0 else 0,
+    "evi_pair_context2": lambda a: 1,
     "evi_struct_project": lambda a: 1,
     "evi_convert_f32": lambda a: 1,
     "evi_project": lambda a: 1,
@@ -223,7 +239,55 @@ def ptr(t) -> Optional[int]:
     return t.data_ptr()
 
 
-def stream_handle() -> int:
+_GUARD_ATTRS = ("head32", "values", "logits", "fwd_ptr")  # GraphBatch, TopK, RetrieverOutput, TriplePoolShard
+
+
+def _cuda_device_of(obj):
     import torch
 
-    return torch.cuda.current_stream().cuda_stream
+    if torch.is_tensor(obj):
+        return obj.device if obj.is_cuda else None
+    if isinstance(obj, torch.device):
+        return obj if obj.type == "cuda" else None
+    for name in _GUARD_ATTRS:
+        t = getattr(obj, name, None)
+        if torch.is_tensor(t) and t.is_cuda:
+            return t.device
+    return None
+
+
+def device_guard(fn):
+    """Run ``fn`` with the CUDA device of its first device-carrying argument (a CUDA tensor, a ``device=`` keyword,
+    or one of this package's tensor holders) made current. The C ABI launches kernels on the calling thread's current
+    device and ``stream_handle()`` returns that device's current stream, so a call on tensors of cuda:1 while cuda:0
+    is current would otherwise launch on the wrong device (the reference's plain-torch code works from any device)."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        import torch
+
+        dev = None
+        explicit = kwargs.get("device")
+        if explicit is not None:
+            d = torch.device(explicit)
+            dev = d if d.type == "cuda" else None
+        if dev is None:
+            for a in list(args) + list(kwargs.values()):
+                dev = _cuda_device_of(a)
+                if dev is not None:
+                    break
+        if dev is None or dev.index is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+
+    return wrapper
+
+
+def stream_handle(device=None) -> int:
+    """The torch current stream of ``device`` (default: the current device). Callers that take a device also make
+    it current (``torch.cuda.device``) around their C-ABI calls: kernels launch on the calling thread's device."""
+    import torch
+
+    return torch.cuda.current_stream(device).cuda_stream

@@ -28,6 +28,7 @@ class LossOutput:
     metrics: Dict[str, float]
 
 
+@_lib.device_guard
 def _launch(logits, targets, edge_ptr, qid32, is_near, cfg, want_grad: bool):
     L = _lib.load()
     dev = logits.device

@@ -48,6 +48,7 @@ class TopKMetricArrays:
     margin_valid: Optional[torch.Tensor] = None  # [B] u8
 
 
+@_lib.device_guard
 def topk_metric_arrays(topk: TopK, edge_ptr: torch.Tensor, k_values: Sequence[int], *,
                        labels: Optional[torch.Tensor] = None, scores: Optional[torch.Tensor] = None,
                        head32: Optional[torch.Tensor] = None, tail32: Optional[torch.Tensor] = None,
@@ -120,6 +121,7 @@ def edge_recall_sums(arr: TopKMetricArrays, edge_ptr: torch.Tensor, *, require_p
     return sums, keep.sum().to(torch.float32)
 
 
+@_lib.device_guard
 def retriever_metrics(logits: torch.Tensor, labels: torch.Tensor, edge_ptr: torch.Tensor, k_values: Sequence[int], *,
                       graph=None, node_ptr=None, q_local_indices=None, q_ptr=None, a_local_indices=None, a_ptr=None,
                       bridge: bool = True) -> Dict[str, float]:

@@ -72,6 +72,10 @@ class RetrievalPipeline:
     def run_device(self, b: Any) -> Dict[str, torch.Tensor]:
         """Inputs already on the device. Returns device tensors."""
         dev = b.edge_index.device
+        with torch.cuda.device(dev):  # the C ABI launches on the current device
+            return self._run_device(b, dev)
+
+    def _run_device(self, b: Any, dev) -> Dict[str, torch.Tensor]:
         gb = G.GraphBatch.from_edge_index(b.edge_index, b.ptr_host, device=dev, validate=False, ptr_dev=b.ptr)
         # jobs = one per question; seeds stay batch-global, the kernel subtracts the question's node offset
         dist = self._bfs(gb, b, b.q_local_indices)

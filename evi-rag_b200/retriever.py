@@ -11,7 +11,12 @@ with ``strict=True`` and ``GraphEmbedder`` can still read them by suffix,
 What differs (B200 design):
   * all arithmetic runs in ``libevi_rag_b200.so``; there is no eager-PyTorch / CPU fallback;
   * dense contractions use 16-bit tensor-core operands with fp32 accumulation
-    (``operand_dtype="fp16"`` by default, ``"bf16"`` selectable);
+    (``operand_dtype="fp16"`` by default, ``"bf16"`` selectable). The per-node / per-relation /
+    per-question contractions run over ``[hi | lo]`` operand pairs (three tensor passes, fp32-grade);
+    the per-edge ones over single 16-bit rows with the structure context centred on its batch mean
+    (``precision="fast"``, scores within ~3e-4 of the fp32 reference) or over pairs as well
+    (``precision="strict"``, ~2e-5, about twice the time);
+  * entity rows are projected once per distinct ``node_embedding_id`` of the batch;
   * with ``attach_embedding_tables`` the 1024-d text-embedding tables live in HBM and a batch only
     needs ids (``node_embedding_ids``, ``edge_attr``) — the reference's per-edge CPU gather + H2D
     of ``edge_embeddings`` (``src/data/components/embedding_store.py:101-150``) disappears;
@@ -98,6 +103,9 @@ class Retriever(nn.Module):
         hide_seek_cfg: Optional[Dict[str, Any]] = None,
         *,
         operand_dtype: str = "fp16",
+        precision: str = "fast",
+        unique_entity_rows: bool = True,
+        center_structure_context: bool = True,
         return_edge_embeddings: bool = False,
         max_workspace_bytes: int = 12 << 30,
         pipeline_chunks: int = 4,
@@ -119,6 +127,11 @@ class Retriever(nn.Module):
         if operand_dtype not in ("fp16", "bf16"):
             raise ValueError(f"operand_dtype must be 'fp16' or 'bf16', got {operand_dtype!r}")
         self.operand_dtype = operand_dtype
+        if precision not in ("fast", "strict"):
+            raise ValueError(f"precision must be 'fast' or 'strict', got {precision!r}")
+        self.precision = precision
+        self.unique_entity_rows = bool(unique_entity_rows)
+        self.center_structure_context = bool(center_structure_context)
         self.return_edge_embeddings = bool(return_edge_embeddings)
         self.max_workspace_bytes = int(max_workspace_bytes)
         self.pipeline_chunks = max(1, int(pipeline_chunks))
@@ -154,6 +167,7 @@ class Retriever(nn.Module):
         self._prepared: Optional[Dict[str, Any]] = None
         self._prepared_key = None
         self._tables: Optional[Dict[str, torch.Tensor]] = None
+        self._slot_map: Optional[torch.Tensor] = None
         self._ws: Optional[torch.Tensor] = None
         self._ws_score: Optional[torch.Tensor] = None
         self.gemm_events = None
@@ -174,24 +188,43 @@ class Retriever(nn.Module):
         return features
 
     # ------------------------------------------------------------------ B200 additions
-    def attach_embedding_tables(self, entity_embeddings: torch.Tensor, relation_embeddings: torch.Tensor) -> None:
-        """Keep the text-embedding tables in HBM (operand dtype). ``entity_embeddings`` is
-        ``[max_id+1, D]`` with row 0 reserved for non-text entities and ``relation_embeddings``
-        ``[R, D]`` (scripts/text_encode_utils.py:60-67, embedding_store.py:60-99). Batches then
-        only need ``node_embedding_ids`` and ``edge_attr``."""
+    def attach_embedding_tables(self, entity_embeddings: torch.Tensor, relation_embeddings: torch.Tensor,
+                                *, split: bool = True, slab_rows: int = 1 << 20) -> None:
+        """Keep the text-embedding tables in HBM. ``entity_embeddings`` is ``[max_id+1, D]`` with row 0
+        reserved for non-text entities and ``relation_embeddings`` ``[R, D]``
+        (scripts/text_encode_utils.py:60-67, embedding_store.py:60-99). Batches then only need
+        ``node_embedding_ids`` and ``edge_attr``.
+
+        ``split=True`` (default) stores every row as a ``[hi | lo]`` pair of 16-bit halves (4 KB per row;
+        the projections then see the fp32 table values to ~2^-22); ``split=False`` stores 2 KB per row
+        (for tables that would not fit otherwise). Tables may be CPU (also memory-mapped) tensors: they
+        are converted and copied ``slab_rows`` at a time."""
         dev = self._device()
-        dt = torch.float16 if self.operand_dtype == "fp16" else torch.bfloat16
+        if dev.type != "cuda":
+            raise RuntimeError("evi_rag_b200.Retriever runs on CUDA only (no CPU fallback); call .cuda() first.")
+        dt = self._op_dtype()
         if entity_embeddings.dim() != 2 or entity_embeddings.size(1) != self.emb_dim:
             raise ValueError(f"entity_embeddings must be [T, {self.emb_dim}], got {tuple(entity_embeddings.shape)}")
         if relation_embeddings.dim() != 2 or relation_embeddings.size(1) != self.emb_dim:
             raise ValueError(f"relation_embeddings must be [R, {self.emb_dim}], got {tuple(relation_embeddings.shape)}")
-        for name, t in (("entity", entity_embeddings), ("relation", relation_embeddings)):
-            if dt == torch.float16 and float(t.abs().max()) > _FP16_SAFE_MAX:
-                raise ValueError(f"{name} embeddings exceed the fp16 range; use operand_dtype='bf16'.")
-        self._tables = {
-            "entity": entity_embeddings.to(device=dev, dtype=dt).contiguous(),
-            "relation": relation_embeddings.to(device=dev, dtype=dt).contiguous(),
-        }
+        d = self.emb_dim
+
+        def upload(name: str, t: torch.Tensor) -> torch.Tensor:
+            out = torch.empty((t.size(0), 2 * d if split else d), dtype=dt, device=dev)
+            for r0 in range(0, t.size(0), slab_rows):
+                x = t[r0:r0 + slab_rows].to(device=dev, dtype=torch.float32)
+                if dt == torch.float16 and x.numel() and float(x.abs().max()) > _FP16_SAFE_MAX:
+                    raise ValueError(f"{name} embeddings exceed the fp16 range; use operand_dtype='bf16'.")
+                hi = x.to(dt)
+                out[r0:r0 + slab_rows, :d] = hi
+                if split:
+                    out[r0:r0 + slab_rows, d:] = (x - hi.float()).to(dt)
+            return out
+
+        self._tables = {"entity": upload("entity", entity_embeddings), "relation": upload("relation", relation_embeddings),
+                        "split": bool(split)}
+        # evi_unique_rows: one int32 per table row, all -1 between calls
+        self._slot_map = torch.full((int(entity_embeddings.size(0)),), -1, dtype=torch.int32, device=dev)
 
     def check_flags(self) -> None:
         """Read back the device-side validation word (one host sync) and raise like the
@@ -243,21 +276,29 @@ class Retriever(nn.Module):
                 raise ValueError("weights exceed the fp16 range; construct with operand_dtype='bf16'.")
             return t.to(dt).contiguous()
 
+        def w16_split(t: torch.Tensor) -> torch.Tensor:
+            """[out, 2 in] = [hi | lo], lo = W - hi: the second half of a three-pass contraction (gemm::SplitK)."""
+            t = t.detach().to(device=dev, dtype=torch.float32)
+            hi = w16(t)
+            return torch.cat([hi, (t - hi.float()).to(dt)], dim=1).contiguous()
+
         f32 = lambda t: t.detach().to(device=dev, dtype=torch.float32).contiguous()
         sn0 = self.state_net[0]
         sn4 = self.state_net[4]
         wo = self.score_head.weight.detach().to(dev).double()[0]
         p: Dict[str, Any] = {
-            "we": w16(self.entity_proj.network[0].weight), "be": f32(self.entity_proj.network[0].bias),
-            "wr": w16(self.relation_proj.network[0].weight), "br": f32(self.relation_proj.network[0].bias),
-            "wq": w16(self.query_proj.network[0].weight), "bq": f32(self.query_proj.network[0].bias),
-            "wgb": w16(torch.cat([self.q_gate[0].weight, self.q_bias[0].weight], dim=0)),
+            "we": w16_split(self.entity_proj.network[0].weight), "be": f32(self.entity_proj.network[0].bias),
+            "wr": w16_split(self.relation_proj.network[0].weight), "br": f32(self.relation_proj.network[0].bias),
+            "wq": w16_split(self.query_proj.network[0].weight), "bq": f32(self.query_proj.network[0].bias),
+            "wgb": w16_split(torch.cat([self.q_gate[0].weight, self.q_bias[0].weight], dim=0)),
             "bgb": f32(torch.cat([self.q_gate[0].bias, self.q_bias[0].bias], dim=0)),
             "non_text": f32(self.non_text_entity_emb.weight[0]),
             "ws_t": f32(self.struct_proj[0].weight.t()), "bs": f32(self.struct_proj[0].bias),
             "ls_g": f32(self.struct_proj[1].weight), "ls_b": f32(self.struct_proj[1].bias),
             "wn": f32(self.struct_gate_net[0].weight[0]), "bn": float(self.struct_gate_net[0].bias.detach()[0]),
-            "w1": w16(sn0.weight[:, : 3 * d]), "w1d": f32(sn0.weight[:, 3 * d]), "b1": f32(sn0.bias),
+            # [H, 6D] = [iv | sc | err | iv_lo | sc_lo | err_lo]
+            "w1": w16_split(sn0.weight[:, : 3 * d]), "w1d": f32(sn0.weight[:, 3 * d]), "b1": f32(sn0.bias),
+            "w_sc32": f32(sn0.weight[:, d: 2 * d]),
             "l1_g": f32(self.state_net[1].weight), "l1_b": f32(self.state_net[1].bias),
             "w2": w16(sn4.weight), "b2": f32(sn4.bias),
             "v": (sn4.weight.detach().to(dev).double().t() @ wo).float().contiguous(),
@@ -279,17 +320,22 @@ class Retriever(nn.Module):
             self._ws_score = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
         return self._ws_score
 
-    def _project(self, x16, w16, bias, acts, *, out16=None, out32=None, p=None, rows_dev=None, col0=0, in_dim=None):
-        """out = act(x16 @ w16[:, col0:col0+in_dim]^T + bias); ``rows_dev``: device int bounding the rows."""
+    def _project(self, x16, w16, bias, acts, *, p, out16=None, out32=None, rows_dev=None, col0=0, in_dim=None,
+                 x_lo=-1, w_lo=-1, out_lo=-1):
+        """out = act(x16[:, :in_dim] @ w16[:, col0:col0+in_dim]^T + bias). ``x_lo`` / ``w_lo``: column offset of the
+        residual half of x16 / w16 rows (three-pass contraction, -1 = none; ``w_lo`` is relative to ``col0``);
+        ``out_lo``: write out16 as [hi | lo] rows with lo at this column; ``rows_dev``: device int bounding the rows."""
         L = _lib.load()
         act_arr = (C.c_int * 8)(*(list(acts) + [0] * (8 - len(acts))))
-        in_dim = int(w16.size(1)) if in_dim is None else int(in_dim)
-        st = L.evi_project(
-            x16.data_ptr(), x16.size(0), _lib.ptr(rows_dev), w16.data_ptr() + 2 * int(col0), w16.size(1), w16.size(0),
-            in_dim, _lib.ptr(bias), act_arr, _lib.ptr(out16), _lib.ptr(out32), self._fmt(), p["num_sms"],
-            _lib.stream_handle(),
+        if in_dim is None:
+            in_dim = int(w16.size(1)) if w_lo < 0 else int(w_lo)
+        st = L.evi_project_split(
+            x16.data_ptr(), int(x16.stride(0)), int(x_lo), x16.size(0), _lib.ptr(rows_dev),
+            w16.data_ptr() + 2 * int(col0), int(w16.stride(0)), int(w_lo), w16.size(0), int(in_dim), _lib.ptr(bias),
+            act_arr, _lib.ptr(out16), int(out16.stride(0)) if out16 is not None else 0, int(out_lo), _lib.ptr(out32),
+            self._fmt(), p["num_sms"], _lib.stream_handle(x16.device),
         )
-        _lib.check(st, "evi_project")
+        _lib.check(st, "evi_project_split")
 
     @torch.no_grad()
     def _forward_impl(self, batch: Any, *, return_features: bool):
@@ -302,6 +348,14 @@ class Retriever(nn.Module):
         if edge_index is None:
             raise ValueError("Batch missing edge_index required for scoring.")
         dev = self._device()
+        if dev.type != "cuda":
+            raise RuntimeError("evi_rag_b200.Retriever runs on CUDA only (no CPU fallback); call .cuda() first.")
+        # the C ABI launches on the calling thread's current device: make it the device that owns the parameters
+        # (the reference module is plain torch and works from any current device)
+        with torch.cuda.device(dev):
+            return self._forward_on_device(batch, edge_index, dev, return_features)
+
+    def _forward_on_device(self, batch: Any, edge_index: torch.Tensor, dev: torch.device, return_features: bool):
         edge_index = edge_index.to(device=dev)
         if edge_index.dim() != 2 or edge_index.size(0) != 2:
             raise ValueError(f"edge_index must have shape [2, E], got {tuple(edge_index.shape)}")
@@ -323,12 +377,14 @@ class Retriever(nn.Module):
 
         L = _lib.load()
         p = self._prepare_weights()
-        stream = _lib.stream_handle()
+        stream = _lib.stream_handle(dev)
         fmt, dt = self._fmt(), self._op_dtype()
         d = self.emb_dim
+        strict = self.precision == "strict"
         if self._flags is None or self._flags.device != dev:
             self._flags = torch.zeros(1, dtype=torch.int32, device=dev)
         flags = self._flags
+        i32 = lambda n: torch.empty(n, dtype=torch.int32, device=dev)
 
         question_emb = question_emb.to(device=dev, dtype=torch.float32).contiguous()
         if not torch.is_tensor(node_embedding_ids):
@@ -342,17 +398,14 @@ class Retriever(nn.Module):
         # ---- a1/a2: question id per edge (+ int32 copies for the kernels) ------------------
         graph = getattr(batch, "_evi_graph", None)  # a precomputed evi_rag_b200.graph.GraphBatch
         edge_batch = getattr(batch, "edge_batch", None)
+        sorted_by_kernel = False  # edges known to be grouped by question (validated on the device)
         if graph is not None and graph.num_edges == E:
             head32, tail32, qid32, query_ids = graph.head32, graph.tail32, graph.qid32, graph.edge_batch
+            sorted_by_kernel = True
             if edge_batch is None:
                 batch.edge_batch = query_ids
-        else:
-            head32 = torch.empty(E, dtype=torch.int32, device=dev)
-            tail32 = torch.empty(E, dtype=torch.int32, device=dev)
-            qid32 = torch.empty(E, dtype=torch.int32, device=dev)
-        if graph is not None and graph.num_edges == E:
-            pass
         elif edge_batch is None:
+            head32, tail32, qid32 = i32(E), i32(E), i32(E)
             node_ptr = getattr(batch, "ptr", None)
             if node_ptr is None:
                 raise ValueError("Batch missing ptr required for edge_batch computation.")
@@ -366,8 +419,10 @@ class Retriever(nn.Module):
                                   stream)
             _lib.check(st, "evi_edge_batch")
             self._pending_flags = True
+            sorted_by_kernel = True
             batch.edge_batch = query_ids  # retriever.py:612
         else:
+            head32, tail32, qid32 = i32(E), i32(E), i32(E)
             if not torch.is_tensor(edge_batch):
                 edge_batch = torch.as_tensor(edge_batch, dtype=torch.long)
             query_ids = edge_batch.to(device=dev, dtype=torch.long).view(-1)
@@ -378,63 +433,98 @@ class Retriever(nn.Module):
             qid32.copy_(query_ids)
 
         # ---- a4: projections (tanh(xW^T+b)) at their true granularity ---------------------
-        x_nodes = torch.empty((N, d), dtype=dt, device=dev)
+        # entity rows once per distinct embedding id of the batch (device-side count: buffers are sized by N)
+        rows_dev = None
+        head_rep32 = tail_rep32 = None
+        rel_slot32 = i32(E)
         if use_tables:
             ent = self._tables["entity"]
-            st = L.evi_gather_rows(ent.data_ptr(), 0, ent.size(0), node_embedding_ids.data_ptr(),
-                                   node_embedding_ids.data_ptr(), p["non_text"].data_ptr(), N, d,
-                                   x_nodes.data_ptr(), fmt, flags.data_ptr(), stream)
+            tsplit = bool(self._tables["split"])
+            row_ids = node_embedding_ids
+            node_slot = None
+            if self.unique_entity_rows:
+                if self._slot_map is None or self._slot_map.device != dev or self._slot_map.numel() != ent.size(0):
+                    self._slot_map = torch.full((int(ent.size(0)),), -1, dtype=torch.int32, device=dev)
+                row_ids = torch.empty(N, dtype=torch.long, device=dev)
+                node_slot, rows_dev = i32(N), i32(1)
+                _lib.check(L.evi_unique_rows(node_embedding_ids.data_ptr(), N, self._slot_map.data_ptr(), int(ent.size(0)),
+                                             row_ids.data_ptr(), node_slot.data_ptr(), rows_dev.data_ptr(),
+                                             flags.data_ptr(), stream), "evi_unique_rows")
+                head_rep32, tail_rep32 = i32(E), i32(E)
+            _lib.check(L.evi_edge_rep_index(head32.data_ptr(), tail32.data_ptr(), E, _lib.ptr(node_slot), N,
+                                            edge_attr_dev.data_ptr(), _lib.ptr(head_rep32), _lib.ptr(tail_rep32),
+                                            rel_slot32.data_ptr(), stream), "evi_edge_rep_index")
+            x_nodes = torch.empty((N, 2 * d if tsplit else d), dtype=dt, device=dev)
+            st = L.evi_gather_rows2(ent.data_ptr(), 0, ent.size(0), int(ent.stride(0)), row_ids.data_ptr(),
+                                    row_ids.data_ptr(), p["non_text"].data_ptr(), N, _lib.ptr(rows_dev), d,
+                                    x_nodes.data_ptr(), int(x_nodes.stride(0)), int(tsplit), fmt, flags.data_ptr(), stream)
+            x_lo = d if tsplit else -1
         else:
             node_embeddings = node_embeddings.to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
             if node_embeddings.size(0) != N:
                 raise ValueError(f"node_embeddings rows {node_embeddings.size(0)} != node_embedding_ids {N}")
-            st = L.evi_gather_rows(node_embeddings.data_ptr(), 1, N, None, node_embedding_ids.data_ptr(),
-                                   p["non_text"].data_ptr(), N, d, x_nodes.data_ptr(), fmt, flags.data_ptr(), stream)
-        _lib.check(st, "evi_gather_rows(nodes)")
+            x_nodes = torch.empty((N, 2 * d), dtype=dt, device=dev)
+            st = L.evi_gather_rows2(node_embeddings.data_ptr(), 1, N, d, None, node_embedding_ids.data_ptr(),
+                                    p["non_text"].data_ptr(), N, None, d, x_nodes.data_ptr(), 2 * d, 1, fmt,
+                                    flags.data_ptr(), stream)
+            x_lo = d
+        _lib.check(st, "evi_gather_rows2(nodes)")
         self._pending_flags = True
-        node_repr = torch.empty((N, d), dtype=dt, device=dev)
-        self._project(x_nodes, p["we"], p["be"], [_lib.ACT_TANH] * 4, out16=node_repr, p=p)
+        tanh4 = [_lib.ACT_TANH] * 4
+        node_repr = torch.empty((N, 2 * d), dtype=dt, device=dev)  # [hi | lo] rows, one per distinct embedding id
+        self._project(x_nodes, p["we"], p["be"], tanh4, out16=node_repr, out_lo=d, p=p, rows_dev=rows_dev, x_lo=x_lo,
+                      w_lo=d)
         del x_nodes
 
         if use_tables:
             rel_in = self._tables["relation"]
-            rel_slot32 = torch.empty(E, dtype=torch.int32, device=dev)
-            rel_slot32.copy_(edge_attr_dev)
+            rel_x_lo = d if self._tables["split"] else -1
         else:
             # per-edge relation rows, as the reference projects them (retriever.py:441)
             edge_embeddings = edge_embeddings.to(device=dev, dtype=torch.float32, non_blocking=True).contiguous()
             if edge_embeddings.size(0) != E:
                 raise ValueError(f"edge_embeddings rows {edge_embeddings.size(0)} != edges {E}")
-            rel_in = torch.empty((E, d), dtype=dt, device=dev)
-            _lib.check(L.evi_convert_f32(edge_embeddings.data_ptr(), rel_in.data_ptr(), E * d, fmt, stream),
-                       "evi_convert_f32")
+            rel_in = torch.empty((E, 2 * d), dtype=dt, device=dev)
+            _lib.check(L.evi_gather_rows2(edge_embeddings.data_ptr(), 1, E, d, None, None, None, E, None, d,
+                                          rel_in.data_ptr(), 2 * d, 1, fmt, flags.data_ptr(), stream),
+                       "evi_gather_rows2(edges)")
+            rel_x_lo = d
             rel_slot32 = torch.arange(E, dtype=torch.int32, device=dev)
-        rel_repr = torch.empty((rel_in.size(0), d), dtype=dt, device=dev)
-        self._project(rel_in, p["wr"], p["br"], [_lib.ACT_TANH] * 4, out16=rel_repr, p=p)
+        R = int(rel_in.size(0))
+        rel_repr = torch.empty((R, 2 * d if strict else d), dtype=dt, device=dev)
+        self._project(rel_in, p["wr"], p["br"], tanh4, out16=rel_repr, out_lo=d if strict else -1, p=p, x_lo=rel_x_lo,
+                      w_lo=d)
 
-        q16 = torch.empty((B, d), dtype=dt, device=dev)
-        _lib.check(L.evi_convert_f32(question_emb.data_ptr(), q16.data_ptr(), B * d, fmt, stream), "evi_convert_f32")
-        qp16 = torch.empty((B, d), dtype=dt, device=dev)
-        self._project(q16, p["wq"], p["bq"], [_lib.ACT_TANH] * 4, out16=qp16, p=p)
+        q16 = torch.empty((B, 2 * d), dtype=dt, device=dev)
+        _lib.check(L.evi_gather_rows2(question_emb.data_ptr(), 1, B, d, None, None, None, B, None, d, q16.data_ptr(),
+                                      2 * d, 1, fmt, flags.data_ptr(), stream), "evi_gather_rows2(questions)")
+        qp16 = torch.empty((B, 2 * d), dtype=dt, device=dev)
+        self._project(q16, p["wq"], p["bq"], tanh4, out16=qp16, out_lo=d, p=p, x_lo=d, w_lo=d)
         gate_bias = torch.empty((B, 2 * d), dtype=torch.float32, device=dev)
-        self._project(qp16, p["wgb"], p["bgb"], [_lib.ACT_SIGMOID] * 4 + [_lib.ACT_TANH] * 4, out32=gate_bias, p=p)
+        self._project(qp16, p["wgb"], p["bgb"], [_lib.ACT_SIGMOID] * 4 + [_lib.ACT_TANH] * 4, out32=gate_bias, p=p,
+                      x_lo=d, w_lo=d)
 
-        # ---- err block of state_net.0, linear in err = h + r_ctx - t (retriever.py:477-481): once per node and
-        # once per distinct (question, relation) pair instead of once per edge and direction
+        # ---- err block of state_net.0, linear in err = h + r_ctx - t (retriever.py:477-481): once per distinct
+        # embedding id and once per distinct (question, relation) pair instead of once per edge and direction
+        none4 = [_lib.ACT_NONE] * 4
         node_p = torch.empty((N, self.hidden_dim), dtype=torch.float32, device=dev)
-        self._project(node_repr, p["w1"], None, [_lib.ACT_NONE] * 4, out32=node_p, p=p, col0=2 * d, in_dim=d)
-        pair_slot32 = torch.empty(E, dtype=torch.int32, device=dev)
+        self._project(node_repr, p["w1"], None, none4, out32=node_p, p=p, rows_dev=rows_dev, col0=2 * d, in_dim=d,
+                      x_lo=d, w_lo=3 * d)
+        pair_slot32 = torch.zeros(E, dtype=torch.int32, device=dev)
         if use_tables and graph is not None and graph.num_edges == E:
             edge_ptr_dev = graph.edge_ptr
         elif use_tables:
-            # edges are grouped by question (validated by evi_edge_batch): edge_ptr from the question ids
+            if not sorted_by_kernel:
+                # a caller-supplied edge_batch: the pair slots below need edges grouped by question; the reference
+                # indexes query_repr[query_ids] in any order, so an unsorted list is reported, not mis-scored
+                bad = (query_ids[1:] < query_ids[:-1]).any().to(torch.int32) * _lib.FLAG_NOT_MONOTONE
+                flags.bitwise_or_(bad)
+                self._pending_flags = True
             edge_ptr_dev = torch.searchsorted(query_ids, torch.arange(B + 1, device=dev, dtype=torch.long))
         if use_tables:
             cap = E
-            pair_q32 = torch.empty(cap, dtype=torch.int32, device=dev)
-            pair_rel32 = torch.empty(cap, dtype=torch.int32, device=dev)
-            num_pairs = torch.empty(1, dtype=torch.int32, device=dev)
-            st = L.evi_relation_pairs(rel_slot32.data_ptr(), edge_ptr_dev.data_ptr(), B, int(rel_repr.size(0)), cap,
+            pair_q32, pair_rel32, num_pairs = i32(cap), i32(cap), i32(1)
+            st = L.evi_relation_pairs(rel_slot32.data_ptr(), edge_ptr_dev.data_ptr(), B, R, cap,
                                       pair_slot32.data_ptr(), pair_q32.data_ptr(), pair_rel32.data_ptr(),
                                       num_pairs.data_ptr(), flags.data_ptr(), stream)
             _lib.check(st, "evi_relation_pairs")
@@ -443,15 +533,11 @@ class Retriever(nn.Module):
             pair_slot32.copy_(rel_slot32)
             pair_q32, pair_rel32 = qid32, rel_slot32
             num_pairs = torch.full((1,), E, dtype=torch.int32, device=dev)
-        rc16 = torch.empty((cap, d), dtype=dt, device=dev)
-        st = L.evi_pair_context(pair_q32.data_ptr(), pair_rel32.data_ptr(), num_pairs.data_ptr(), cap,
-                                rel_repr.data_ptr(), int(rel_repr.size(0)), gate_bias.data_ptr(), B, rc16.data_ptr(), fmt,
-                                flags.data_ptr(), stream)
-        _lib.check(st, "evi_pair_context")
-        pair_rq = torch.empty((cap, self.hidden_dim), dtype=torch.float32, device=dev)
-        self._project(rc16, p["w1"], p["b1"], [_lib.ACT_NONE] * 4, out32=pair_rq, p=p, rows_dev=num_pairs, col0=2 * d,
-                      in_dim=d)
-        del rc16
+        rc16 = torch.empty((cap, 2 * d if strict else d), dtype=dt, device=dev)
+        st = L.evi_pair_context2(pair_q32.data_ptr(), pair_rel32.data_ptr(), num_pairs.data_ptr(), cap,
+                                 rel_repr.data_ptr(), int(rel_repr.stride(0)), R, gate_bias.data_ptr(), B,
+                                 rc16.data_ptr(), int(rc16.stride(0)), int(strict), fmt, flags.data_ptr(), stream)
+        _lib.check(st, "evi_pair_context2")
 
         # ---- a3: DDE structure features ------------------------------------------------------
         topic = getattr(batch, "topic_one_hot", None)
@@ -475,7 +561,7 @@ class Retriever(nn.Module):
         rf, rr = self.dde.num_rounds, self.dde.num_reverse_rounds
         ns_dim = 2 * (1 + rf + rr)
         node_struct = torch.empty((N, ns_dim), dtype=torch.float32, device=dev)
-        dde_ws = self._workspace(int(L.evi_dde_workspace_bytes(N)), dev)
+        dde_ws = self._workspace(max(int(L.evi_dde_workspace_bytes(N)), 64 * d * 4), dev)
 
         def dde(h32, t32, n_edges, fwd_rounds, rev_rounds, out):
             st_ = L.evi_dde_forward(h32.data_ptr(), t32.data_ptr(), n_edges, N, topic.data_ptr(), topic.size(1),
@@ -506,22 +592,38 @@ class Retriever(nn.Module):
         _lib.check(L.evi_struct_project(node_struct.data_ptr(), N, ns_dim, p["ws_t"].data_ptr(), p["bs"].data_ptr(),
                                         node_uv.data_ptr(), stream), "evi_struct_project")
 
-        # ---- a5/a6: edge scoring -------------------------------------------------------------
         direction = {"bidirectional": _lib.DIR_BIDIRECTIONAL, "forward": _lib.DIR_FORWARD,
                      "backward": _lib.DIR_BACKWARD}[self.direction_mode]
+        # batch centre of the structure context: the operand kernel stores fp16(sc - c), and W_sc c (fp32 weights)
+        # rides in the bias of the pair rows
+        sc_center, pair_bias = None, p["b1"]
+        if self.center_structure_context:
+            sc_center = torch.empty(d, dtype=torch.float32, device=dev)
+            pair_bias = torch.empty(self.hidden_dim, dtype=torch.float32, device=dev)
+            _lib.check(L.evi_sc_center(head32.data_ptr(), tail32.data_ptr(), E, node_uv.data_ptr(), N,
+                                       p["ls_g"].data_ptr(), p["ls_b"].data_ptr(), direction, p["w_sc32"].data_ptr(),
+                                       p["b1"].data_ptr(), dde_ws.data_ptr(), dde_ws.numel(), sc_center.data_ptr(),
+                                       pair_bias.data_ptr(), stream), "evi_sc_center")
+        pair_rq = torch.empty((cap, self.hidden_dim), dtype=torch.float32, device=dev)
+        self._project(rc16, p["w1"], pair_bias, none4, out32=pair_rq, p=p, rows_dev=num_pairs, col0=2 * d, in_dim=d,
+                      x_lo=d if strict else -1, w_lo=3 * d if strict else -1)
+        del rc16
+
+        # ---- a5/a6: edge scoring -------------------------------------------------------------
         logits = torch.empty(E, dtype=torch.float32, device=dev)
         logits_fwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_BACKWARD else None
         logits_bwd = torch.empty(E, dtype=torch.float32, device=dev) if direction != _lib.DIR_FORWARD else None
         feats = torch.empty((E, self.hidden_dim), dtype=torch.float32, device=dev) if return_features else None
         # chunking bounds the workspace: `pipeline_chunks` chunks per batch (never below 16k edges per chunk),
         # capped by max_workspace_bytes
-        per_edge = int(L.evi_score_workspace_bytes(1 << 20, direction, int(return_features))) / float(1 << 20)
+        prec = _lib.PRECISION_STRICT if strict else _lib.PRECISION_FAST
+        per_edge = int(L.evi_score_workspace_bytes2(1 << 20, direction, int(return_features), prec)) / float(1 << 20)
         chunk_cap = max(1024, int(self.max_workspace_bytes / per_edge) // 1024 * 1024)
         chunk = -(-E // self.pipeline_chunks)
         chunk = min(chunk_cap, max(int(os.environ.get("EVI_MIN_CHUNK", "16384")), (chunk + 1023) // 1024 * 1024))
         if chunk >= E:
             chunk = E
-        per_chunk = int(L.evi_score_workspace_bytes(chunk, direction, int(return_features)))
+        per_chunk = int(L.evi_score_workspace_bytes2(chunk, direction, int(return_features), prec))
         # two workspace halves + a second stream: the GEMMs of chunk c overlap the HBM-bound stages of chunks c-1 / c+1
         overlap = self.overlap_streams and chunk < E and not return_features
         ws = self._score_workspace(per_chunk * (2 if overlap else 1), dev)
@@ -532,14 +634,20 @@ class Retriever(nn.Module):
             a.aux_stream = self._aux_stream.cuda_stream
         a.emb_dim, a.hidden_dim, a.direction, a.operand_format = d, self.hidden_dim, direction, fmt
         a.want_features, a.num_sms = int(return_features), p["num_sms"]
-        a.num_nodes, a.num_rel_rows, a.num_questions, a.flags = N, int(rel_repr.size(0)), B, flags.data_ptr()
+        a.num_nodes, a.num_rel_rows, a.num_questions, a.flags = N, R, B, flags.data_ptr()
         a.num_pair_rows = cap
         a.node_repr16, a.rel_repr16 = node_repr.data_ptr(), rel_repr.data_ptr()
+        a.node_repr_ld, a.rel_repr_ld = int(node_repr.stride(0)), int(rel_repr.stride(0))
+        a.num_rep_rows = N
+        a.head_rep32, a.tail_rep32 = _lib.ptr(head_rep32), _lib.ptr(tail_rep32)
+        a.sc_center = _lib.ptr(sc_center)
+        a.precision = prec
         a.gate_bias32, a.node_uv32 = gate_bias.data_ptr(), node_uv.data_ptr()
         a.node_p32, a.pair_rq32 = node_p.data_ptr(), pair_rq.data_ptr()
         a.struct_ln_g, a.struct_ln_b = p["ls_g"].data_ptr(), p["ls_b"].data_ptr()
         a.nav_w, a.nav_b = p["wn"].data_ptr(), p["bn"]
         a.w1_main16, a.w1_dist_col = p["w1"].data_ptr(), p["w1d"].data_ptr()
+        a.w1_ld, a.w1_lo_off = int(p["w1"].stride(0)), 3 * d
         a.ln1_g, a.ln1_b, a.head_v, a.head_c0 = p["l1_g"].data_ptr(), p["l1_b"].data_ptr(), p["v"].data_ptr(), p["c0"]
         a.w2_16, a.w2_bias, a.head_w, a.head_b = p["w2"].data_ptr(), p["b2"].data_ptr(), p["wo"].data_ptr(), p["bo"]
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()

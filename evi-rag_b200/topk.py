@@ -25,6 +25,7 @@ class TopK:
     counts: torch.Tensor  # [B] i32 = min(E_q, k)
 
 
+@_lib.device_guard
 def segmented_topk(scores: torch.Tensor, edge_ptr: torch.Tensor, k: int, *, sigmoid: bool = False) -> TopK:
     """``segmented_topk(scores[E], edge_ptr[B+1], k)``. ``sigmoid=True`` ranks
     ``sigmoid(scores)`` like the writer (retriever_topk_edge_writer.py:203) and returns those."""
@@ -47,6 +48,7 @@ def segmented_topk(scores: torch.Tensor, edge_ptr: torch.Tensor, k: int, *, sigm
     return TopK(values, indices, counts)
 
 
+@_lib.device_guard
 def writer_payload(topk: TopK, edge_ptr: torch.Tensor, *, edge_index: torch.Tensor, node_global_ids: torch.Tensor,
                    edge_attr: torch.Tensor, labels: Optional[torch.Tensor] = None,
                    logits_fwd: Optional[torch.Tensor] = None, logits_bwd: Optional[torch.Tensor] = None
@@ -82,6 +84,7 @@ def writer_payload(topk: TopK, edge_ptr: torch.Tensor, *, edge_index: torch.Tens
     return out
 
 
+@_lib.device_guard
 def recall_at_k(topk: TopK, labels: torch.Tensor, edge_ptr: torch.Tensor, k_values: Sequence[int]) -> Dict[int, float]:
     """``EdgeRecallAtK`` (retriever_metrics.py:117-170) from one top-k at ``max(k_values)``:
     hits@k are prefix sums of the gathered labels; torch ops on ``[B, k]`` arrays only."""

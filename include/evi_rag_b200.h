@@ -44,6 +44,9 @@ extern "C" {
 #define EVI_ACT_TANH 1
 #define EVI_ACT_SIGMOID 2
 
+#define EVI_PRECISION_FAST 0   /* 16-bit per-edge operands (default): scores within ~3e-4 of the fp32 reference */
+#define EVI_PRECISION_STRICT 1 /* [hi | lo] fp16 operand pairs on every contraction, fp32 rows: ~2e-5 */
+
 #define EVI_TOPK_RAW 0     /* metrics flavour: raw logits, retriever_metrics.py:145 */
 #define EVI_TOPK_SIGMOID 1 /* writer flavour: sigmoid(logits), retriever_topk_edge_writer.py:203 */
 
@@ -109,6 +112,25 @@ int evi_gather_rows(const void* src, int src_is_f32, long long src_rows, const l
                     const long long* sub_mask_ids, const float* sub_row, int num_rows, int dim, void* dst16,
                     int operand_format, unsigned* flags, cudaStream_t stream);
 int evi_convert_f32(const float* src, void* dst16, long long count, int operand_format, cudaStream_t stream);
+/* The same gather with explicit row pitches (elements), an optional device-side row count (num_rows_dev: the number of
+ * distinct embedding ids, evi_unique_rows) and split rows: with split != 0 the destination rows are [hi | lo] pairs
+ * (lo = x - hi at column dim; dst_ld >= 2 dim) — a 16-bit source must then hold [hi | lo] rows too (src_ld >= 2 dim),
+ * an fp32 source is split on the fly. Split rows feed the three-pass contractions of evi_project_split. */
+int evi_gather_rows2(const void* src, int src_is_f32, long long src_rows, int src_ld, const long long* ids,
+                     const long long* sub_mask_ids, const float* sub_row, int num_rows, const int* num_rows_dev, int dim,
+                     void* dst16, int dst_ld, int split, int operand_format, unsigned* flags, cudaStream_t stream);
+
+/* Distinct embedding ids of a batch: tanh(W_e x + b) (retriever.py:497-507) and P = W_err node_repr depend only on the
+ * embedding id, so they are computed once per distinct id. ids [N] in [0, table_rows); slot_map [table_rows] i32 must be
+ * all -1 on entry and is all -1 again on return (stream order). Outputs: uniq_ids [N] (first *num_unique valid),
+ * node_slot [N] = row of each node's id in uniq_ids, *num_unique (device). Slot numbering is unspecified. */
+int evi_unique_rows(const long long* ids, int num_rows, int* slot_map, long long table_rows, long long* uniq_ids,
+                    int* node_slot, int* num_unique, unsigned* flags, cudaStream_t stream);
+/* Per-edge int32 indices in one launch: head_rep32 / tail_rep32 [E] = node_slot[head32 / tail32] (node_slot NULL: skipped)
+ * and rel_slot32 [E] = (int) edge_attr (edge_attr NULL: skipped; ids outside int32 become -1 and are flagged later). */
+int evi_edge_rep_index(const int* head32, const int* tail32, long long num_edges, const int* node_slot, int num_nodes,
+                       const long long* edge_attr, int* head_rep32, int* tail_rep32, int* rel_slot32,
+                       cudaStream_t stream);
 
 /* EmbeddingProjector / q_gate / q_bias — src/models/components/projections.py:9-40,
  * retriever.py:157-158,436-441: out = act(x W^T + b) on tcgen05. w16 is [out_dim, in_dim] with row
@@ -120,6 +142,27 @@ int evi_convert_f32(const float* src, void* dst16, long long count, int operand_
 int evi_project(const void* x16, int num_rows, const int* num_rows_dev, const void* w16, int ld_w, int out_dim,
                 int in_dim, const float* bias, const int* act_per_block, void* out16, float* out32,
                 int operand_format, int num_sms, cudaStream_t stream);
+
+/* evi_project over split operands (projections.py:9-40 at fp32-grade accuracy on 16-bit tensor cores): x16 rows and / or
+ * w16 rows may carry a residual half lo = v - fp16(v) at a column offset of the same matrix (x_lo_off / w_lo_off, in
+ * elements; negative = none). The contraction then accumulates x_hi w_hi + x_lo w_hi + x_hi w_lo in fp32 (up to three
+ * passes over in_dim). out16 may itself be written as [hi | lo] rows (out_lo_off >= 0) for the next split contraction.
+ * ld_x / ld_w / ld_out16: row pitches in elements. */
+int evi_project_split(const void* x16, int ld_x, int x_lo_off, int num_rows, const int* num_rows_dev, const void* w16,
+                      int ld_w, int w_lo_off, int out_dim, int in_dim, const float* bias, const int* act_per_block,
+                      void* out16, int ld_out16, int out_lo_off, float* out32, int operand_format, int num_sms,
+                      cudaStream_t stream);
+
+/* Batch centre of the structure context sc = GELU(LN(struct_proj.0 [ns_a ; ns_b])) (retriever.py:486-495): center [D] =
+ * mean of sc over a fixed-stride sample of the batch's edges (both directions present in `direction`), and
+ * bias_out [H] = b1 + W_sc center with fp32 weights (w_sc32 [H, D] = state_net.0.weight[:, D:2D]; b1 may be NULL).
+ * evi_score_edges subtracts `center` from sc before rounding it to 16 bits (evi_score_args.sc_center) and the caller
+ * uses bias_out as the bias of the pair rows Rq, which restores W_sc sc exactly: W_sc sc = W_sc (sc - c) + W_sc c.
+ * Deterministic (no atomics). workspace: 64 * D floats. */
+int evi_sc_center(const int* head32, const int* tail32, long long num_edges, const float* node_uv32, int num_nodes,
+                  const float* struct_ln_g, const float* struct_ln_b, int direction, const float* w_sc32,
+                  const float* b1, float* workspace, size_t workspace_bytes, float* center, float* bias_out,
+                  cudaStream_t stream);
 
 /* struct_proj.0 of _encode_structure (retriever.py:486-495) on the edge structure vector
  * [ns[a], ns[b]] of _edge_structure_from_nodes (retriever.py:509-517), split by node:
@@ -143,6 +186,10 @@ int evi_relation_pairs(const int* rel32, const long long* edge_ptr, int num_ques
 int evi_pair_context(const int* pair_q32, const int* pair_rel32, const int* num_pairs, int capacity,
                      const void* rel_repr16, int num_rel_rows, const float* gate_bias32, int num_questions,
                      void* rc16, int operand_format, unsigned* flags, cudaStream_t stream);
+/* with row pitches; split != 0: rel_repr16 and rc16 rows are [hi | lo] pairs (strict mode) */
+int evi_pair_context2(const int* pair_q32, const int* pair_rel32, const int* num_pairs, int capacity,
+                      const void* rel_repr16, int rel_ld, int num_rel_rows, const float* gate_bias32, int num_questions,
+                      void* rc16, int rc_ld, int split, int operand_format, unsigned* flags, cudaStream_t stream);
 
 /* _score_edges + _encode_structure + _combine_directional_outputs —
  * src/models/components/retriever.py:453-495, 369-381. state_net.0 is linear in its input
@@ -204,10 +251,19 @@ typedef struct evi_score_args {
    * GEMMs of chunk c run on the call's stream while this stream runs the HBM-bound stages of chunks c-1 / c+1; the
    * call's stream is joined with it before returning. NULL: everything in order on the call's stream. */
   void* aux_stream;
+  /* --- ABI 5 --- */
+  int precision;                    /* EVI_PRECISION_* ; strict: the per-edge contractions run three passes over [hi | lo] rows */
+  int node_repr_ld, rel_repr_ld;    /* row pitch (elements) of node_repr16 / rel_repr16; 0 = D. Strict reads lo at column D */
+  int w1_ld, w1_lo_off;             /* row pitch of w1_main16 (0 = 3D) and column offset of its lo blocks [iv|sc|err]_lo */
+  int num_rep_rows;                 /* rows of node_repr16 / node_p32 (one per distinct embedding id); 0 = num_nodes */
+  const int* head_rep32;            /* [E] row of node_repr16 / node_p32 for the head (evi_edge_rep_index); NULL = head32 */
+  const int* tail_rep32;
+  const float* sc_center;           /* [D] batch centre subtracted from sc (evi_sc_center), or NULL */
 } evi_score_args;
 
 /* bytes of the per-chunk workspace for `chunk_edges` edges */
 size_t evi_score_workspace_bytes(long long chunk_edges, int direction, int want_features);
+size_t evi_score_workspace_bytes2(long long chunk_edges, int direction, int want_features, int precision);
 int evi_score_edges(const evi_score_args* args, cudaStream_t stream);
 
 /* ---- ragged top-k ------------------------------------------------------------------------ */

@@ -13,24 +13,37 @@ from evi_rag_b200.weights import make_state_dict
 
 pytestmark = pytest.mark.gpu
 
-# Score tolerance (north star: "within 1e-3 relative"), stated as a norm-wise relative error over
-# the batch, ||gpu - ref||_2 / ||ref||_2 <= REL_L2, plus a max-abs guard relative to max|ref|.
-# fp16 operands (default; same 10-bit mantissa as the TF32 matmuls of the reference's own GPU eval,
-# configs/trainer/predict.yaml:8) measure 4e-4..9e-4 -> 1e-3 on realistic batches; the few-hundred-
-# edge golden batches are noisier and get 1.5e-3. bf16 operands (7-bit mantissa) measure 4e-3..7e-3.
-REL_L2 = {"fp16": 1.0e-3, "bf16": 8.0e-3}
-REL_L2_SMALL = {"fp16": 1.5e-3, "bf16": 8.0e-3}
-MAX_ABS = {"fp16": 2.5e-3, "bf16": 1.5e-2}
+# Score tolerance = the north star's contract, "triple scores within 1e-3 relative", asserted in BOTH norms on every
+# batch, golden or synthetic: ||gpu - ref||_2 / ||ref||_2 <= 1e-3 and max|gpu - ref| / max|ref| <= 1e-3. The default
+# mode (fp16 operands, [hi | lo] pairs on the per-node / per-relation / per-question contractions, centred structure
+# context) measures 1.5e-4 .. 4e-4; precision="strict" a few 1e-5 (STRICT). bf16 operands (7-bit mantissa on the
+# per-edge contractions) measure 4e-3 .. 7e-3 and are an explicit lower-precision opt-in with their own bound.
+REL_L2 = {"fp16": 1.0e-3, "bf16": 8.0e-3, "strict": 1.0e-4}
+MAX_ABS = {"fp16": 1.0e-3, "bf16": 1.5e-2, "strict": 1.5e-4}
 SCORE_TOL = MAX_ABS  # band used by the top-k set rule
+# edge features (extract_edge_tokens; no caller in the reference): one more single-pass 16-bit contraction on top
+FEAT_REL_L2, FEAT_MAX_ABS = 1.5e-3, 2.5e-3
+MEASURED = {}  # what -> (rel_l2, max_rel); printed by the tests, collected by scripts/gpu_round.sh through -s
 
 
-def check_scores(got, ref, operand, what="", small=False):
-    got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+def score_errors(got, ref):
+    got, ref = np.asarray(got, dtype=np.float64).ravel(), np.asarray(ref, dtype=np.float64).ravel()
+    scale = max(np.abs(ref).max(), 1e-30)
     rel_l2 = np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-30)
-    max_rel = np.abs(got - ref).max() / max(np.abs(ref).max(), 1e-30)
-    print(f"[parity] {what} {operand}: rel_l2={rel_l2:.3e} max_abs/max_ref={max_rel:.3e}")
-    assert rel_l2 <= (REL_L2_SMALL if small else REL_L2)[operand], (what, operand, rel_l2)
-    assert max_rel <= MAX_ABS[operand], (what, operand, max_rel)
+    max_rel = np.abs(got - ref).max() / scale
+    # per-edge relative error over the edges that are not near zero (|ref| > 5 % of the batch maximum)
+    big = np.abs(ref) > 0.05 * scale
+    per_edge = np.abs(got - ref)[big] / np.abs(ref)[big] if big.any() else np.zeros(1)
+    return rel_l2, max_rel, np.percentile(per_edge, 50), np.percentile(per_edge, 99), per_edge.max()
+
+
+def check_scores(got, ref, operand, what="", rel_l2_tol=None, max_abs_tol=None):
+    rel_l2, max_rel, p50, p99, pmax = score_errors(got, ref)
+    print(f"[parity] {what} {operand}: rel_l2={rel_l2:.3e} max_abs/max_ref={max_rel:.3e} "
+          f"per-edge rel p50={p50:.2e} p99={p99:.2e} max={pmax:.2e}")
+    MEASURED[f"{what} {operand}"] = (rel_l2, max_rel)
+    assert rel_l2 <= (REL_L2[operand] if rel_l2_tol is None else rel_l2_tol), (what, operand, rel_l2)
+    assert max_rel <= (MAX_ABS[operand] if max_abs_tol is None else max_abs_tol), (what, operand, max_rel)
 
 
 def _g(golden_dir, name):
@@ -299,21 +312,22 @@ def test_retriever_matches_reference_golden(dev, golden_dir, tag, operand):
         batch = _batch_from_golden(g, dev)
         out = m(batch)
         scale = float(np.abs(g[f"{mode}.logits"]).max())
-        check_scores(out.logits.cpu().numpy(), g[f"{mode}.logits"], operand, f"{tag}/{mode}/logits", small=True)
+        check_scores(out.logits.cpu().numpy(), g[f"{mode}.logits"], operand, f"{tag}/{mode}/logits")
         assert np.array_equal(out.query_ids.cpu().numpy(), g[f"{mode}.query_ids"])
         assert out.query_ids.dtype == torch.long and out.relation_ids is batch.edge_attr
         assert torch.equal(batch.edge_batch, out.query_ids)
         if mode != "backward":
-            check_scores(out.logits_fwd.cpu().numpy(), g[f"{mode}.logits_fwd"], operand, f"{tag}/{mode}/fwd", small=True)
+            check_scores(out.logits_fwd.cpu().numpy(), g[f"{mode}.logits_fwd"], operand, f"{tag}/{mode}/fwd")
         else:
             assert out.logits_fwd is None
         if mode != "forward":
-            check_scores(out.logits_bwd.cpu().numpy(), g[f"{mode}.logits_bwd"], operand, f"{tag}/{mode}/bwd", small=True)
+            check_scores(out.logits_bwd.cpu().numpy(), g[f"{mode}.logits_bwd"], operand, f"{tag}/{mode}/bwd")
         else:
             assert out.logits_bwd is None
         fe = out.edge_embeddings.cpu().numpy()
-        check_scores(fe[:4], g[f"{mode}.feat_head"], operand, f"{tag}/{mode}/features", small=True)
-        check_scores(fe.sum(1), g[f"{mode}.feat_rowsum"], operand, f"{tag}/{mode}/feature rowsums", small=True)
+        ft = dict(rel_l2_tol=FEAT_REL_L2, max_abs_tol=FEAT_MAX_ABS) if operand == "fp16" else {}
+        check_scores(fe[:4], g[f"{mode}.feat_head"], operand, f"{tag}/{mode}/features", **ft)
+        check_scores(fe.sum(1), g[f"{mode}.feat_rowsum"], operand, f"{tag}/{mode}/feature rowsums", **ft)
         # the feature path recomputes logits the reference way; the collapsed head must agree with it
         m.return_edge_embeddings = False
         out2 = m(_batch_from_golden(g, dev))
@@ -923,7 +937,205 @@ def test_reverse_edge_index_override(dev, golden_dir):
         question_emb=torch.from_numpy(g["question_emb"]), node_embeddings=torch.from_numpy(g["entity_rows"]),
         node_embedding_ids=torch.from_numpy(g["node_embedding_ids"]), edge_embeddings=rel[torch.from_numpy(g["edge_attr"])],
         topic_one_hot=torch.from_numpy(g["topic_one_hot"]), num_rounds=rf, num_reverse_rounds=rr, reverse_edge_index=rev)
-    check_scores(got, ref.logits.numpy(), "fp16", "reverse_edge_index", small=True)
+    check_scores(got, ref.logits.numpy(), "fp16", "reverse_edge_index")
     assert not np.allclose(got, base.cpu().numpy(), atol=1e-3)  # the override really changes the structure features
     with pytest.raises(ValueError):
         model(batch(reverse_edge_index=torch.tensor([[0, n + 5], [1, 2]])))
+
+
+# ------------------------------------------------------------------ round 2: precision, unique rows, devices
+@pytest.mark.parametrize("m", [1, 130, 1111])
+def test_project_split_matches_fp32(dev, m):
+    """Three tensor passes over [hi | lo] fp16 operand pairs (gemm::SplitK) against an fp64 matmul of the fp32
+    values: ~1e-6 of the row scale, 100x below one single-pass fp16 contraction. Weight lo halves are fp16
+    subnormals (|W| ~ 1/32): the test fails if the tensor core flushed them."""
+    from evi_rag_b200 import lib
+
+    L = lib.load()
+    g = torch.Generator(device="cpu").manual_seed(100 + m)
+    k, n = 1024, 1024
+    x = (torch.randn(m, k, generator=g) * 0.5)
+    w = ((torch.rand(n, k, generator=g) * 2 - 1) / 32)
+    b = torch.randn(n, generator=g)
+
+    def split(t):
+        hi = t.half()
+        return torch.cat([hi, (t - hi.float()).half()], dim=1).contiguous().to(dev)
+
+    xs, ws, bd = split(x), split(w), b.to(dev)
+    ref = (x.double() @ w.double().t() + b.double())
+    scale = float(ref.abs().max())
+    acts = (C.c_int * 8)(*[lib.ACT_NONE] * 8)
+    stream = torch.cuda.current_stream().cuda_stream
+    out32 = torch.full((m, n), float("nan"), device=dev)
+    st = L.evi_project_split(xs.data_ptr(), 2 * k, k, m, None, ws.data_ptr(), 2 * k, k, n, k, bd.data_ptr(), acts,
+                             None, 0, -1, out32.data_ptr(), lib.FMT_F16, 148, stream)
+    assert st == 0
+    out1 = torch.full((m, n), float("nan"), device=dev)  # single pass over the hi halves, same buffers
+    st = L.evi_project_split(xs.data_ptr(), 2 * k, -1, m, None, ws.data_ptr(), 2 * k, -1, n, k, bd.data_ptr(), acts,
+                             None, 0, -1, out1.data_ptr(), lib.FMT_F16, 148, stream)
+    assert st == 0
+    # [hi | lo] 16-bit output rows (direct-store epilogue): hi + lo reproduces the fp32 result
+    out16 = torch.zeros((m, 2 * n), dtype=torch.float16, device=dev)
+    st = L.evi_project_split(xs.data_ptr(), 2 * k, k, m, None, ws.data_ptr(), 2 * k, k, n, k, bd.data_ptr(), acts,
+                             out16.data_ptr(), 2 * n, n, None, lib.FMT_F16, 148, stream)
+    assert st == 0
+    torch.cuda.synchronize()
+    e3 = float((out32.double().cpu() - ref).abs().max()) / scale
+    e1 = float((out1.double().cpu() - ref).abs().max()) / scale
+    e16 = float(((out16[:, :n].float() + out16[:, n:].float()).double().cpu() - ref).abs().max()) / scale
+    print(f"[parity] split GEMM m={m}: three passes {e3:.2e}, one pass {e1:.2e}, hi+lo rows {e16:.2e} (of max|ref|)")
+    assert e3 <= 3e-6 and e16 <= 5e-6
+    assert e1 >= 20 * e3  # the lo passes are really there
+
+
+def _table_model(dev, sd, ent, rel, **kw):
+    from evi_rag_b200.retriever import Retriever
+
+    m = Retriever(emb_dim=1024, hidden_dim=1024, **kw).eval()
+    m.load_state_dict(sd, strict=True)
+    m.to(dev)
+    m.attach_embedding_tables(torch.from_numpy(ent), torch.from_numpy(rel))
+    return m
+
+
+def _ids_batch(qb):
+    import types
+
+    t = torch.from_numpy
+    return types.SimpleNamespace(edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
+                                 node_embedding_ids=t(qb.node_embedding_ids), edge_attr=t(qb.edge_attr),
+                                 topic_one_hot=t(qb.topic_one_hot))
+
+
+def test_unique_entity_rows_bit_identical(dev):
+    """Projecting each distinct embedding id once (evi_unique_rows) gives the same bits as projecting every node:
+    rows are computed independently, whatever their position."""
+    spec = tiny_spec(8, 700, seed=52, num_relations=40, num_entities=300)  # few entities: many repeats
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(3)
+    ent = (rng.standard_normal((301, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((40, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(6, trained_like=True)
+    outs = []
+    for uniq in (True, False):
+        m = _table_model(dev, sd, ent, rel, unique_entity_rows=uniq)
+        o = m(_ids_batch(qb))
+        outs.append((o.logits.clone(), o.logits_fwd.clone(), o.logits_bwd.clone()))
+        assert int(m._slot_map.max()) == -1  # the slot map is clean again
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    n_unique = len(np.unique(qb.node_embedding_ids))
+    assert n_unique < 0.5 * qb.num_nodes  # the case really exercises repeats
+
+
+def test_centering_and_single_tables_stay_in_tolerance(dev):
+    """The optional pieces of the default mode each stay inside the contract when switched off: no batch centre,
+    and 2 KB table rows (attach_embedding_tables(split=False))."""
+    from evi_rag_b200.retriever import Retriever
+
+    spec = tiny_spec(5, 800, seed=61, num_relations=64, num_entities=1500)
+    qb = generate_questions(spec)
+    ref, m, b = _oracle_and_model(qb, spec, dev, sd_seed=7, center_structure_context=False)
+    check_scores(m(b).logits.cpu().numpy(), ref.logits.numpy(), "fp16", "no-centre/logits")
+    ref, m, b = _oracle_and_model(qb, spec, dev, sd_seed=7)
+    ent, rel = m._tables["entity"], m._tables["relation"]
+    full = m(b).logits.clone()
+    check_scores(full.cpu().numpy(), ref.logits.numpy(), "fp16", "default/logits")
+    rng = np.random.default_rng(spec.seed)  # the same tables as _oracle_and_model
+    ent32 = (rng.standard_normal((spec.num_entities + 1, 1024)) * 0.5).astype(np.float32)
+    ent32[0] = 0
+    rel32 = (rng.standard_normal((spec.num_relations, 1024)) * 0.5).astype(np.float32)
+    m.attach_embedding_tables(torch.from_numpy(ent32), torch.from_numpy(rel32), split=False)
+    assert m._tables["entity"].shape[1] == 1024 and ent.shape[1] == 2048
+    check_scores(m(b).logits.cpu().numpy(), ref.logits.numpy(), "fp16", "single-tables/logits")
+
+
+@pytest.mark.parametrize("tag", ["d1024_init", "d1024_trained"])
+def test_strict_mode_golden_scores_and_topk_sets(dev, golden_dir, tag):
+    """precision="strict": every contraction over [hi | lo] pairs, fp32 rows. Scores within 1e-4 of the reference's
+    golden logits in all three direction modes, and the top-k index SETS equal the reference's for every k that cuts
+    a question's edge list (k = 10, 50, 100), with no tolerance band."""
+    from evi_rag_b200.retriever import Retriever
+    from evi_rag_b200.topk import segmented_topk
+
+    g = _g(golden_dir, f"scorer_{tag}.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    sd = make_state_dict(seed, dim, dim, rf, rr, trained_like=bool(trained))
+    edge_ptr = np.searchsorted(g["bidirectional.query_ids"], np.arange(len(g["ptr"]))).astype(np.int64)
+    for mode in ("bidirectional", "forward", "backward"):
+        m = Retriever(emb_dim=dim, hidden_dim=dim, direction_mode=mode, precision="strict",
+                      dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr}).eval()
+        m.load_state_dict(sd, strict=True)
+        m.to(dev)
+        out = m(_batch_from_golden(g, dev))
+        refl = g[f"{mode}.logits"]
+        check_scores(out.logits.cpu().numpy(), refl, "strict", f"strict/{tag}/{mode}/logits")
+        for k in (10, 50, 100):
+            tk = segmented_topk(out.logits, torch.from_numpy(edge_ptr).to(dev), k)
+            _, ref_idx, ref_cnt = orc.segmented_topk(refl, edge_ptr, k)
+            idx, cnt = tk.indices.cpu().numpy(), tk.counts.cpu().numpy()
+            assert np.array_equal(cnt, ref_cnt)
+            for q in range(len(edge_ptr) - 1):
+                assert set(idx[q, :cnt[q]].tolist()) == set(ref_idx[q, :cnt[q]].tolist()), (mode, k, q)
+
+
+def test_bench_slice_vs_oracle(dev):
+    """A 32-question slice of the bench workload itself (WEBQSP_10K generator, bench tables and weights, E_q ~ 5k):
+    scores and top-100 sets against the oracle at the configuration the headline number is quoted on."""
+    from evi_rag_b200.synthetic import WEBQSP_10K, make_embedding_tables
+    from evi_rag_b200.topk import segmented_topk
+
+    spec = WEBQSP_10K
+    qb = generate_questions(spec, q_start=512, q_count=32)
+    ent, rel = make_embedding_tables(spec)
+    sd = make_state_dict(0, trained_like=True)
+    t = torch.from_numpy
+    torch.set_num_threads(os.cpu_count() or 1)
+    ref = orc.retriever_forward(sd, edge_index=t(qb.edge_index), ptr=t(qb.ptr), question_emb=t(qb.question_emb),
+                                node_embeddings=t(ent[qb.node_embedding_ids]), node_embedding_ids=t(qb.node_embedding_ids),
+                                edge_embeddings=t(rel[qb.edge_attr]), topic_one_hot=t(qb.topic_one_hot))
+    m = _table_model(dev, sd, ent, rel)
+    out = m(_ids_batch(qb))
+    refl = ref.logits.numpy()
+    check_scores(out.logits.cpu().numpy(), refl, "fp16", "bench-slice/logits")
+    check_scores(out.logits_fwd.cpu().numpy(), ref.logits_fwd.numpy(), "fp16", "bench-slice/fwd")
+    check_scores(out.logits_bwd.cpu().numpy(), ref.logits_bwd.numpy(), "fp16", "bench-slice/bwd")
+    tk = segmented_topk(out.logits, t(qb.edge_ptr).to(dev), 100)
+    _check_topk_sets(tk.indices.cpu().numpy(), tk.counts.cpu().numpy(), refl, qb.edge_ptr, 100,
+                     SCORE_TOL["fp16"] * float(np.abs(refl).max()))
+    # how many of the 3200 selected triples differ from the reference's (all inside the band, checked above)
+    _, ref_idx, ref_cnt = orc.segmented_topk(refl, qb.edge_ptr, 100)
+    idx = tk.indices.cpu().numpy()
+    moved = sum(len(set(idx[q, :ref_cnt[q]].tolist()) ^ set(ref_idx[q, :ref_cnt[q]].tolist())) // 2
+                for q in range(qb.num_graphs))
+    print(f"[parity] bench-slice top-100: {moved} of {int(ref_cnt.sum())} selected triples differ from the reference's")
+    assert moved <= 0.01 * ref_cnt.sum()
+
+
+def test_model_on_non_current_device():
+    """The reference module is plain torch and runs on whatever device holds its parameters; the C ABI launches on
+    the calling thread's current device, so every entry point makes the tensors' device current."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from evi_rag_b200.topk import segmented_topk
+
+    spec = tiny_spec(3, 300, seed=71, num_relations=20, num_entities=400)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(8)
+    ent = (rng.standard_normal((401, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((20, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(1, trained_like=True)
+    outs = []
+    for ordinal in (0, 1):
+        torch.cuda.set_device(0)  # current device stays 0 throughout
+        d = torch.device("cuda", ordinal)
+        m = _table_model(d, sd, ent, rel)
+        o = m(_ids_batch(qb))
+        tk = segmented_topk(o.logits, torch.from_numpy(qb.edge_ptr).to(d), 20)
+        torch.cuda.synchronize(d)
+        assert o.logits.device == d and tk.indices.device == d
+        outs.append((o.logits.cpu(), tk.indices.cpu()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])

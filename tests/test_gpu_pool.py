@@ -123,7 +123,7 @@ def test_pool_retrieve_scores_and_topk(dev):
     refl = ref.logits.numpy()
     rel_l2 = np.linalg.norm(got - refl) / np.linalg.norm(refl)
     print(f"[parity] pool retrieval: rel_l2={rel_l2:.3e}")
-    assert rel_l2 <= 1.5e-3  # fp16 operands / fp32 accumulate, small batch (tests/test_gpu_parity.py REL_L2_SMALL)
+    assert rel_l2 <= 1.0e-3  # the score contract (tests/test_gpu_parity.py REL_L2)
     _, idx, cnt = orc.segmented_topk(got, ref_b["edge_ptr"], k)
     for q in range(Q):
         kt = int(cnt[q])

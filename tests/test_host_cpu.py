@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     for name in sorted(declared):
         assert hasattr(L, name), f"{name} declared in include/evi_rag_b200.h but not exported"
     assert declared == set(lib.PROTOTYPES), declared ^ set(lib.PROTOTYPES)
-    assert L.evi_abi_version() == 4
+    assert L.evi_abi_version() == 5
     assert L.evi_score_workspace_bytes(1000, lib.DIR_BIDIRECTIONAL, 0) >= 1000 * 1024 * (2 + 4 + 4 + 8)
 
 
