@@ -180,6 +180,8 @@ EVI_DEVINL void load_row32(const float* __restrict__ base, int lane, float (&v)[
     for (int j = 0; j < 8; ++j) v[i * 8 + j] = t[j];
   }
 }
+// one [hi | lo] row (2D elements): the 16-bit value at base[c] and its residual at base[D + c] — the operand of the
+// three-pass state_net.4 contraction of the features path
 template <int FMT>
 EVI_DEVINL void store_row16(uint16_t* __restrict__ base, int lane, const float (&v)[32]) {
 #pragma unroll
@@ -190,6 +192,14 @@ EVI_DEVINL void store_row16(uint16_t* __restrict__ base, int lane, const float (
     w.z = Op16<FMT>::pack2(v[i * 8 + 4], v[i * 8 + 5]);
     w.w = Op16<FMT>::pack2(v[i * 8 + 6], v[i * 8 + 7]);
     *reinterpret_cast<uint4*>(base + i * 256 + lane * 8) = w;
+    const float2 h0 = Op16<FMT>::unpack2(w.x), h1 = Op16<FMT>::unpack2(w.y), h2 = Op16<FMT>::unpack2(w.z),
+                 h3 = Op16<FMT>::unpack2(w.w);
+    uint4 l;
+    l.x = Op16<FMT>::pack2(v[i * 8 + 0] - h0.x, v[i * 8 + 1] - h0.y);
+    l.y = Op16<FMT>::pack2(v[i * 8 + 2] - h1.x, v[i * 8 + 3] - h1.y);
+    l.z = Op16<FMT>::pack2(v[i * 8 + 4] - h2.x, v[i * 8 + 5] - h2.y);
+    l.w = Op16<FMT>::pack2(v[i * 8 + 6] - h3.x, v[i * 8 + 7] - h3.y);
+    *reinterpret_cast<uint4*>(base + D + i * 256 + lane * 8) = l;
   }
 }
 template <int FMT>
@@ -447,7 +457,7 @@ edge_operand_kernel(const int* __restrict__ head, const int* __restrict__ tail, 
 //   sc_center_finish_kernel : center [D] = sum of partials / count
 //   sc_center_bias_kernel   : bias_out [H] = b1 + W_sc (fp32) center     (folded into Rq's bias)
 // ---------------------------------------------------------------------------------------------
-constexpr int kCenterCtas = 64;
+constexpr int kCenterCtas = 256;
 constexpr int kCenterSample = 4096;  // edges sampled per batch (each contributes its forward and backward rows)
 
 __global__ void __launch_bounds__(256)
@@ -563,7 +573,9 @@ __global__ void unique_claim_kernel(const long long* __restrict__ ids, int n, in
     atomicOr(flags, kFlagOutOfRange);
     id = 0;
   }
-  if (atomicCAS(slot_map + id, -1, -2) == -1) {
+  // a third of a WebQSP-shaped batch shares id 0: a plain (volatile) look first, so that only the first arrivals
+  // reach the atomic instead of tens of thousands of CAS operations serialising on one address
+  if (*reinterpret_cast<volatile int*>(slot_map + id) == -1 && atomicCAS(slot_map + id, -1, -2) == -1) {
     const int s = atomicAdd(num_unique, 1);
     uniq_ids[s] = id;
     slot_map[id] = s;  // read by the next kernel only
@@ -773,10 +785,10 @@ score_tail_kernel(const void* __restrict__ mm,                                  
   }
   float lf = 0.f, lb = 0.f;
   if (has_f && has_b)
-    tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr,
-                          g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr, lf, lb);
-  else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
-  else if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
+    tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * 2 * D : nullptr,
+                          g_bwd ? g_bwd + static_cast<size_t>(e) * 2 * D : nullptr, lf, lb);
+  else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * 2 * D : nullptr);
+  else if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * 2 * D : nullptr);
   if (lane == 0) {
     if (has_f && logits_fwd) logits_fwd[e] = lf;
     if (has_b && logits_bwd) logits_bwd[e] = lb;
@@ -937,10 +949,10 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
     if constexpr (BIDIR)  // both directions, logits only
       tail_finish_pair<FMT, false>(zf, zb, tp, lane, nullptr, nullptr, lf, lb);
     else if (has_f && has_b)
-      tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr,
-                            g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr, lf, lb);
-    else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * D : nullptr);
-    else if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * D : nullptr);
+      tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * 2 * D : nullptr,
+                            g_bwd ? g_bwd + static_cast<size_t>(e) * 2 * D : nullptr, lf, lb);
+    else if (has_f) lf = tail_finish<FMT>(zf, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * 2 * D : nullptr);
+    else if (has_b) lb = tail_finish<FMT>(zb, tp, lane, g_bwd ? g_bwd + static_cast<size_t>(e) * 2 * D : nullptr);
     if (lane == 0) {
       if (has_f && logits_fwd) logits_fwd[e] = lf;
       if (has_b && logits_bwd) logits_bwd[e] = lb;
@@ -1227,7 +1239,7 @@ static size_t chunk_workspace_bytes(long long num_edges, int direction, int want
   auto al = [](size_t b) { return (b + 255) & ~static_cast<size_t>(255); };
   size_t total = al(E * op_ld * 2) + al(nd * E * op_ld * 2) + al(E * D * sizeof(float)) + al(nd * E * D * sizeof(float)) +
                  al(E * sizeof(float4));
-  if (want_features) total += al(nd * E * D * 2) + al(nd * E * D * sizeof(float));
+  if (want_features) total += al(nd * E * 2 * D * 2) + al(nd * E * D * sizeof(float));  // g rows are [hi | lo]
   return total + 256;
 }
 
@@ -1270,7 +1282,7 @@ struct ChunkPlan {
     S = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
     SCAL = reinterpret_cast<float4*>(take(n * sizeof(float4)));
     if (a.want_features) {
-      G = reinterpret_cast<uint16_t*>(take(nd * n * D * 2));
+      G = reinterpret_cast<uint16_t*>(take(nd * n * 2 * D * 2));
       FEAT = reinterpret_cast<float*>(take(nd * n * D * sizeof(float)));
     }
     ok = off <= ws_bytes && (!strict || (w1_lo > 0 && w1_lo + 3 * D <= w1_ld));
@@ -1356,7 +1368,7 @@ struct ChunkPlan {
     const float4* sqs_f = reinterpret_cast<const float4*>(s_scales(0));
     const float4* sqs_b = reinterpret_cast<const float4*>(s_scales(do_f ? 1 : 0));
     uint16_t* g_f = G;
-    uint16_t* g_b = G ? G + (do_f ? n * D : 0) : nullptr;
+    uint16_t* g_b = G ? G + (do_f ? n * 2 * D : 0) : nullptr;
     const bool feats = a.want_features != 0;
     // the tail reads node ids only to fetch P rows, which exist once per distinct embedding id
     const int* p_head = (a.head_rep32 != nullptr ? a.head_rep32 : a.head32) + e0;
@@ -1392,7 +1404,11 @@ struct ChunkPlan {
     // feature path: state_net.4 as a second GEMM, logits from the fp32 features, softmax-weighted blend
     gemm::EpiBiasF32::Params fp;
     fp.bias = a.w2_bias, fp.out32 = FEAT, fp.ld32 = D;
-    int rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, D, a.w2_16, D, static_cast<int>(nd * n), D, D, fp, a.num_sms, stream);
+    // state_net.4 over [hi | lo] rows of g and of W_2 (a.w2_ld >= 2D: lo block at column D): fp32-grade features
+    const bool w2_split = a.w2_ld >= 2 * D;
+    int rc = gemm::launch<FMT, gemm::EpiBiasF32>(G, 2 * D, a.w2_16, w2_split ? a.w2_ld : D, static_cast<int>(nd * n), D, D,
+                                                 fp, a.num_sms, stream, nullptr, nullptr, 0,
+                                                 gemm::make_split(D, w2_split ? D : -1));
     if (rc != kOk) return rc;
     const float* f_f = do_f ? FEAT : nullptr;
     const float* f_b = do_b ? FEAT + (do_f ? n * D : 0) : nullptr;

@@ -47,7 +47,7 @@ class ScoreArgs(C.Structure):
         ("chunk_edges", _ll),
         ("aux_stream", _vp),
         ("precision", _i), ("node_repr_ld", _i), ("rel_repr_ld", _i), ("w1_ld", _i), ("w1_lo_off", _i),
-        ("num_rep_rows", _i), ("head_rep32", _vp), ("tail_rep32", _vp), ("sc_center", _vp),
+        ("num_rep_rows", _i), ("head_rep32", _vp), ("tail_rep32", _vp), ("sc_center", _vp), ("w2_ld", _i),
     ]
 
 

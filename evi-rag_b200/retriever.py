@@ -300,7 +300,7 @@ class Retriever(nn.Module):
             "w1": w16_split(sn0.weight[:, : 3 * d]), "w1d": f32(sn0.weight[:, 3 * d]), "b1": f32(sn0.bias),
             "w_sc32": f32(sn0.weight[:, d: 2 * d]),
             "l1_g": f32(self.state_net[1].weight), "l1_b": f32(self.state_net[1].bias),
-            "w2": w16(sn4.weight), "b2": f32(sn4.bias),
+            "w2": w16_split(sn4.weight), "b2": f32(sn4.bias),
             "v": (sn4.weight.detach().to(dev).double().t() @ wo).float().contiguous(),
             "c0": float(wo @ sn4.bias.detach().to(dev).double() + self.score_head.bias.detach().to(dev).double()[0]),
             "wo": f32(self.score_head.weight[0]), "bo": float(self.score_head.bias.detach()[0]),
@@ -561,7 +561,7 @@ class Retriever(nn.Module):
         rf, rr = self.dde.num_rounds, self.dde.num_reverse_rounds
         ns_dim = 2 * (1 + rf + rr)
         node_struct = torch.empty((N, ns_dim), dtype=torch.float32, device=dev)
-        dde_ws = self._workspace(max(int(L.evi_dde_workspace_bytes(N)), 64 * d * 4), dev)
+        dde_ws = self._workspace(max(int(L.evi_dde_workspace_bytes(N)), 256 * d * 4), dev)
 
         def dde(h32, t32, n_edges, fwd_rounds, rev_rounds, out):
             st_ = L.evi_dde_forward(h32.data_ptr(), t32.data_ptr(), n_edges, N, topic.data_ptr(), topic.size(1),
@@ -650,6 +650,7 @@ class Retriever(nn.Module):
         a.w1_ld, a.w1_lo_off = int(p["w1"].stride(0)), 3 * d
         a.ln1_g, a.ln1_b, a.head_v, a.head_c0 = p["l1_g"].data_ptr(), p["l1_b"].data_ptr(), p["v"].data_ptr(), p["c0"]
         a.w2_16, a.w2_bias, a.head_w, a.head_b = p["w2"].data_ptr(), p["b2"].data_ptr(), p["wo"].data_ptr(), p["bo"]
+        a.w2_ld = int(p["w2"].stride(0))
         a.workspace, a.workspace_bytes = ws.data_ptr(), ws.numel()
         a.num_edges, a.chunk_edges = E, chunk
         a.head32, a.tail32, a.qid32, a.rel_slot32 = head32.data_ptr(), tail32.data_ptr(), qid32.data_ptr(), rel_slot32.data_ptr()

@@ -158,7 +158,7 @@ int evi_project_split(const void* x16, int ld_x, int x_lo_off, int num_rows, con
  * bias_out [H] = b1 + W_sc center with fp32 weights (w_sc32 [H, D] = state_net.0.weight[:, D:2D]; b1 may be NULL).
  * evi_score_edges subtracts `center` from sc before rounding it to 16 bits (evi_score_args.sc_center) and the caller
  * uses bias_out as the bias of the pair rows Rq, which restores W_sc sc exactly: W_sc sc = W_sc (sc - c) + W_sc c.
- * Deterministic (no atomics). workspace: 64 * D floats. */
+ * Deterministic (no atomics). workspace: 256 * D floats. */
 int evi_sc_center(const int* head32, const int* tail32, long long num_edges, const float* node_uv32, int num_nodes,
                   const float* struct_ln_g, const float* struct_ln_b, int direction, const float* w_sc32,
                   const float* b1, float* workspace, size_t workspace_bytes, float* center, float* bias_out,
@@ -259,6 +259,7 @@ typedef struct evi_score_args {
   const int* head_rep32;            /* [E] row of node_repr16 / node_p32 for the head (evi_edge_rep_index); NULL = head32 */
   const int* tail_rep32;
   const float* sc_center;           /* [D] batch centre subtracted from sc (evi_sc_center), or NULL */
+  int w2_ld;                        /* row pitch of w2_16; >= 2H: rows are [hi | lo] and the features path runs three passes */
 } evi_score_args;
 
 /* bytes of the per-chunk workspace for `chunk_edges` edges */

@@ -867,3 +867,31 @@ def retriever_loss(logits, targets, edge_batch, num_graphs: int, *, infonce_temp
             "pos_prob": float(sig[pos].mean()) if pos.any() else 0.0,
             "neg_prob": float(sig[~pos].mean()) if (~pos).any() else 0.0}
     return infonce_weight * l_inf + bce_weight * l_bce, grad, info
+
+
+# ----------------------------------------------------------------------------------------------
+# a7: hide-and-seek bias (src/models/components/retriever.py:307-367)
+# ----------------------------------------------------------------------------------------------
+def hide_seek_bias(edge_index: torch.Tensor, like: torch.Tensor, *, p_near: float, p_far: float, bias_near: float,
+                   bias_far: float, num_nodes: Optional[int] = None, q_local_indices=None, a_local_indices=None,
+                   edge_is_near=None) -> Optional[torch.Tensor]:
+    """Restatement of ``_compute_hide_seek_bias`` for an enabled module: near mask from ``edge_is_near`` or from the
+    q/a local indices (``compute_qa_edge_mask``, graph_utils.py:107-153); one uniform draw per edge from the torch
+    generator of ``like``'s device (``torch.rand_like``, retriever.py:362); edges whose draw falls below p_near / p_far
+    receive bias_near / bias_far. Returns None in the reference's early-exit cases (:352-359)."""
+    dev = edge_index.device
+    if edge_is_near is None:
+        mask = torch.zeros(int(num_nodes), dtype=torch.bool, device=dev)
+        qa = torch.cat([torch.as_tensor(q_local_indices, dtype=torch.long, device=dev).view(-1),
+                        torch.as_tensor(a_local_indices, dtype=torch.long, device=dev).view(-1)])
+        if qa.numel():
+            mask[qa] = True
+        near = mask[edge_index[0]] | mask[edge_index[1]]
+    else:
+        near = torch.as_tensor(edge_is_near).to(device=dev, dtype=torch.bool)
+    if near.numel() == 0 or (p_near <= 0.0 and p_far <= 0.0) or (bias_near == 0.0 and bias_far == 0.0):
+        return None
+    drop_prob = torch.where(near, like.new_tensor(p_near), like.new_tensor(p_far))
+    drop = torch.rand_like(drop_prob) < drop_prob
+    values = torch.where(near, like.new_tensor(bias_near), like.new_tensor(bias_far))
+    return torch.where(drop, values, like.new_zeros(drop_prob.shape))

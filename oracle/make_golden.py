@@ -468,6 +468,37 @@ def golden_loss():
     print("loss ok", {c["tag"]: float(store[f"{c['tag']}_loss"]) for c in LOSS_CASES})
 
 
+HIDE_SEEK_CFG = dict(enabled=True, apply_in_eval=True, p_near=0.6, p_far=0.15, bias_near=-2.5, bias_far=-0.75)
+HIDE_SEEK_SEED = 4321
+
+
+def golden_hide_seek(Retriever):
+    """a7: the reference's hide-and-seek bias (retriever.py:307-367) in eval with apply_in_eval, drawn from the CPU
+    generator after torch.manual_seed(HIDE_SEEK_SEED): once from q/a local indices (compute_qa_edge_mask,
+    graph_utils.py:107-153), once from a supplied edge_is_near mask."""
+    qb, _, _ = small_batch(15, 64, num_questions=4, median_edges=150)
+    m = Retriever(emb_dim=64, hidden_dim=64, hide_seek_cfg=dict(HIDE_SEEK_CFG)).eval()
+    ei = torch.from_numpy(qb.edge_index)
+    like = torch.zeros(qb.num_edges, dtype=torch.float32)
+    b = types.SimpleNamespace(q_local_indices=torch.from_numpy(qb.q_local_indices),
+                              a_local_indices=torch.from_numpy(qb.a_local_indices), num_nodes=qb.num_nodes)
+    torch.manual_seed(HIDE_SEEK_SEED)
+    bias_qa = m._compute_hide_seek_bias(b, edge_index=ei, logits=like)
+    rng = np.random.default_rng(6)
+    near = rng.random(qb.num_edges) < 0.3
+    torch.manual_seed(HIDE_SEEK_SEED)
+    bias_mask = m._compute_hide_seek_bias(types.SimpleNamespace(edge_is_near=torch.from_numpy(near)), edge_index=ei,
+                                          logits=like)
+    m_off = Retriever(emb_dim=64, hidden_dim=64, hide_seek_cfg=dict(HIDE_SEEK_CFG, apply_in_eval=False)).eval()
+    assert m_off._compute_hide_seek_bias(b, edge_index=ei, logits=like) is None
+    np.savez_compressed(os.path.join(GOLDEN, "hide_seek.npz"), edge_index=qb.edge_index,
+                        q_local_indices=qb.q_local_indices, a_local_indices=qb.a_local_indices,
+                        num_nodes=np.array(qb.num_nodes), edge_is_near=near, bias_qa=bias_qa.numpy(),
+                        bias_mask=bias_mask.numpy(), seed=np.array(HIDE_SEEK_SEED),
+                        cfg=np.array([HIDE_SEEK_CFG[k] for k in ("p_near", "p_far", "bias_near", "bias_far")]))
+    print("hide_seek ok", float((bias_qa != 0).float().mean()), float((bias_mask != 0).float().mean()))
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     Retriever, ref_ceb, brp, kind = load_reference()
@@ -479,6 +510,7 @@ def main():
     golden_gagent()
     golden_writer()
     golden_loss()
+    golden_hide_seek(Retriever)
     with open(os.path.join(GOLDEN, "PROVENANCE.txt"), "w", encoding="utf-8") as f:
         f.write(
             "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"

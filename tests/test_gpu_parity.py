@@ -305,12 +305,15 @@ def test_retriever_matches_reference_golden(dev, golden_dir, tag, operand):
     sd = make_state_dict(seed, dim, dim, rf, rr, trained_like=bool(trained))
     tol = SCORE_TOL[operand]
     for mode in ("bidirectional", "forward", "backward"):
-        m = Retriever(emb_dim=dim, hidden_dim=dim, direction_mode=mode, operand_dtype=operand,
-                      dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr}, return_edge_embeddings=True).eval()
+        kw = dict(emb_dim=dim, hidden_dim=dim, direction_mode=mode, operand_dtype=operand,
+                  dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr})
+        # the scoring path proper (logits only: what eval runs, retriever_module.py:447-450)
+        m = Retriever(**kw).eval()
         m.load_state_dict(sd, strict=True)
         m.to(dev)
         batch = _batch_from_golden(g, dev)
         out = m(batch)
+        assert out.edge_embeddings is None
         scale = float(np.abs(g[f"{mode}.logits"]).max())
         check_scores(out.logits.cpu().numpy(), g[f"{mode}.logits"], operand, f"{tag}/{mode}/logits")
         assert np.array_equal(out.query_ids.cpu().numpy(), g[f"{mode}.query_ids"])
@@ -324,15 +327,19 @@ def test_retriever_matches_reference_golden(dev, golden_dir, tag, operand):
             check_scores(out.logits_bwd.cpu().numpy(), g[f"{mode}.logits_bwd"], operand, f"{tag}/{mode}/bwd")
         else:
             assert out.logits_bwd is None
-        fe = out.edge_embeddings.cpu().numpy()
+        # the features path (return_edge_embeddings / extract_edge_tokens): state_net.4 as a real contraction over
+        # [hi | lo] rows, logits recomputed from the features the reference way; it must agree with the collapsed head
+        mf = Retriever(return_edge_embeddings=True, **kw).eval()
+        mf.load_state_dict(sd, strict=True)
+        mf.to(dev)
+        outf = mf(_batch_from_golden(g, dev))
+        check_scores(outf.logits.cpu().numpy(), g[f"{mode}.logits"], operand, f"{tag}/{mode}/logits (features path)")
+        fe = outf.edge_embeddings.cpu().numpy()
         ft = dict(rel_l2_tol=FEAT_REL_L2, max_abs_tol=FEAT_MAX_ABS) if operand == "fp16" else {}
         check_scores(fe[:4], g[f"{mode}.feat_head"], operand, f"{tag}/{mode}/features", **ft)
         check_scores(fe.sum(1), g[f"{mode}.feat_rowsum"], operand, f"{tag}/{mode}/feature rowsums", **ft)
-        # the feature path recomputes logits the reference way; the collapsed head must agree with it
-        m.return_edge_embeddings = False
-        out2 = m(_batch_from_golden(g, dev))
-        assert out2.edge_embeddings is None
-        assert (out2.logits - out.logits).abs().max().item() <= tol * scale
+        assert (outf.logits - out.logits).abs().max().item() <= tol * scale
+        assert torch.equal(mf.extract_edge_tokens(_batch_from_golden(g, dev)), outf.edge_embeddings)
 
 
 def test_retriever_table_mode_equals_batch_mode(dev, golden_dir):
@@ -1139,3 +1146,50 @@ def test_model_on_non_current_device():
         assert o.logits.device == d and tk.indices.device == d
         outs.append((o.logits.cpu(), tk.indices.cpu()))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+
+
+def test_hide_seek_bias_apply_in_eval(dev, golden_dir):
+    """a7 (retriever.py:307-367): with hide_seek_cfg.apply_in_eval the module adds the bias drawn from the CUDA
+    generator; after the same seed the oracle's restatement (pinned to the reference on the CPU stream by
+    tests/golden/hide_seek.npz) draws the same numbers on the device, so logits = unbiased logits + bias exactly on
+    the directional logits and up to one rounding of the combine on the bidirectional ones."""
+    from evi_rag_b200.retriever import Retriever
+
+    g = _g(golden_dir, "scorer_d1024_trained.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    sd = make_state_dict(seed, dim, dim, rf, rr, trained_like=True)
+    cfg = dict(enabled=True, apply_in_eval=True, p_near=0.5, p_far=0.2, bias_near=-3.0, bias_far=-1.0)
+    kw = {k: cfg[k] for k in ("p_near", "p_far", "bias_near", "bias_far")}
+    n = int(g["ptr"][-1])
+    rng = np.random.default_rng(9)
+    q_loc, a_loc = rng.choice(n, 4, replace=False), rng.choice(n, 5, replace=False)
+    near = torch.from_numpy(rng.random(g["edge_index"].shape[1]) < 0.4)
+
+    def run(hide, **extra):
+        m = Retriever(emb_dim=dim, hidden_dim=dim, hide_seek_cfg=hide,
+                      dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr}).eval()
+        m.load_state_dict(sd, strict=True)
+        m.to(dev)
+        b = _batch_from_golden(g, dev)
+        for k, v in extra.items():
+            setattr(b, k, v)
+        torch.manual_seed(777)
+        return m(b)
+
+    base = run(None)
+    ei = torch.from_numpy(g["edge_index"]).to(dev)
+    for extra, okw in ((dict(q_local_indices=torch.from_numpy(q_loc), a_local_indices=torch.from_numpy(a_loc), num_nodes=n),
+                        dict(num_nodes=n, q_local_indices=q_loc, a_local_indices=a_loc)),
+                       (dict(edge_is_near=near), dict(edge_is_near=near))):
+        out = run(cfg, **extra)
+        torch.manual_seed(777)
+        bias = orc.hide_seek_bias(ei, base.logits_fwd, **okw, **kw)
+        assert bias is not None and 0.1 < float((bias != 0).float().mean()) < 0.6
+        assert torch.equal(out.logits_fwd, base.logits_fwd + bias)
+        assert torch.equal(out.logits_bwd, base.logits_bwd + bias)
+        assert float((out.logits - (base.logits + bias)).abs().max()) <= 4e-6 * float(base.logits.abs().max())
+    # eval without apply_in_eval: no draw, no bias (retriever.py:307-312)
+    off = run(dict(cfg, apply_in_eval=False), edge_is_near=near)
+    assert torch.equal(off.logits, base.logits)
+    with pytest.raises(ValueError, match="q_local_indices/a_local_indices"):
+        run(cfg)

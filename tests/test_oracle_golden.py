@@ -226,3 +226,25 @@ def test_retriever_loss_matches_reference(golden_dir, tag):
     np.testing.assert_allclose(grad, g[f"{tag}_grad"], atol=2e-6, rtol=1e-4)
     for k in ("infonce", "bce", "infonce_graphs", "pos_prob", "neg_prob"):
         assert abs(info[k] - float(g[f"{tag}_m_{k}"])) <= 2e-5 * max(1.0, abs(info[k])), k
+
+
+def test_hide_seek_bias_matches_reference(golden_dir):
+    """a7: the oracle's restatement of `_compute_hide_seek_bias` draws the same CPU stream as the reference after the
+    same seed and lands on the same bias vector, for both ways of naming the near edges."""
+    import torch
+
+    g = np.load(os.path.join(golden_dir, "hide_seek.npz"))
+    p_near, p_far, bias_near, bias_far = [float(x) for x in g["cfg"]]
+    kw = dict(p_near=p_near, p_far=p_far, bias_near=bias_near, bias_far=bias_far)
+    ei = torch.from_numpy(g["edge_index"])
+    like = torch.zeros(ei.size(1))
+    torch.manual_seed(int(g["seed"]))
+    got = orc.hide_seek_bias(ei, like, num_nodes=int(g["num_nodes"]), q_local_indices=g["q_local_indices"],
+                             a_local_indices=g["a_local_indices"], **kw)
+    assert np.array_equal(got.numpy(), g["bias_qa"])
+    torch.manual_seed(int(g["seed"]))
+    got = orc.hide_seek_bias(ei, like, edge_is_near=g["edge_is_near"], **kw)
+    assert np.array_equal(got.numpy(), g["bias_mask"])
+    assert set(np.unique(g["bias_qa"]).tolist()) == {bias_near, bias_far, 0.0}
+    assert orc.hide_seek_bias(ei, like, edge_is_near=g["edge_is_near"], p_near=0.0, p_far=0.0, bias_near=-1.0,
+                              bias_far=-1.0) is None
