@@ -22,7 +22,7 @@ from typing import Any, Dict, List, Optional, Sequence
 import torch
 import torch.distributed as dist
 
-from .topk import segmented_topk, writer_payload
+from .topk import MAX_K, segmented_topk, writer_payload
 
 _DEFAULT_TOPK_VALUES = (1, 5, 10)
 
@@ -77,46 +77,66 @@ def _questions(batch: Any, num_graphs: int) -> List[str]:
     return [str(raw) for _ in range(num_graphs)]
 
 
+_EDGE_KEYS = ("head_entity_id", "relation_id", "tail_entity_id", "head_text", "relation_text", "tail_text", "score",
+              "label", "rank")
+_HOST_KEYS = ("score", "count", "head_id", "tail_id", "relation_id", "label", "logit_fwd", "logit_bwd")
+
+
+class _PendingBatch:
+    """Selected triples of one batch on their way to the host: pinned arrays, the event that marks the end of the
+    device->host copies, and the per-question metadata the records need."""
+
+    __slots__ = ("done", "host", "sample_ids", "questions", "answers", "answer_ptr", "has_fwd", "has_bwd", "num_graphs")
+
+
 class RetrieverTopKEdgeWriter:
-    """Persist retriever top-k edges during predict/test (retriever_topk_edge_writer.py:68-170)."""
+    """Persist retriever top-k edges during predict/test (retriever_topk_edge_writer.py:68-170).
+
+    Per batch the hook enqueues one ragged top-k, one payload gather and the device->host copies into rotating pinned
+    buffers and returns without synchronising; the Python records of batch i are built while the device already works
+    on batch i+1 (``pipeline_depth`` batches stay in flight), the rest in ``on_predict_end`` / ``on_test_end``."""
 
     def __init__(self, *, output_dir, split: str = "test", enabled: bool = True, artifact_name: str = "eval_retriever",
                  schema_version: int = 1, topk_values: Optional[Sequence[int]] = None, textualize: bool = False,
                  entity_vocab_path: Optional[str] = None, relation_vocab_path: Optional[str] = None,
-                 overwrite: bool = True) -> None:
-        self.enabled = bool(enabled)
-        self.output_dir = Path(output_dir)
-        self.split = str(split)
-        self.artifact_name = str(artifact_name).strip()
-        if not self.artifact_name:
+                 overwrite: bool = True, pipeline_depth: int = 1) -> None:
+        name = str(artifact_name).strip()
+        version = int(schema_version)
+        ks = normalize_k_values(topk_values, default=_DEFAULT_TOPK_VALUES)
+        if not name:
             raise ValueError("artifact_name must be a non-empty string.")
-        self.schema_version = int(schema_version)
-        if self.schema_version <= 0:
+        if version <= 0:
             raise ValueError("schema_version must be a positive integer.")
-        self.topk_values = normalize_k_values(topk_values, default=_DEFAULT_TOPK_VALUES)
-        if not self.topk_values:
+        if not ks:
             raise ValueError("topk_values must be a non-empty list of positive integers.")
-        self._max_topk = max(int(k) for k in self.topk_values)
-        self.textualize = bool(textualize)
-        self.entity_vocab_path = entity_vocab_path
-        self.relation_vocab_path = relation_vocab_path
-        self.overwrite = bool(overwrite)
+        if ks[-1] > MAX_K:
+            raise ValueError(f"topk_values up to {MAX_K} are supported by the selection kernel (one CTA sorts a "
+                             f"question's candidates in shared memory); got max k = {ks[-1]}.")
+        self.enabled, self.overwrite, self.textualize = bool(enabled), bool(overwrite), bool(textualize)
+        self.output_dir, self.split = Path(output_dir), str(split)
+        self.artifact_name, self.schema_version = name, version
+        self.topk_values, self._max_topk = ks, ks[-1]
+        self.entity_vocab_path, self.relation_vocab_path = entity_vocab_path, relation_vocab_path
+        self.pipeline_depth = max(0, int(pipeline_depth))
         self._records: List[Dict[str, Any]] = []
-        self._output_path: Optional[Path] = None
-        self._manifest_path: Optional[Path] = None
+        self._pending: List[_PendingBatch] = []
+        self._pinned: List[Dict[str, torch.Tensor]] = []
+        self._batches_seen = 0
         self._entity_map: Optional[Dict[int, str]] = None
         self._relation_map: Optional[Dict[int, str]] = None
+        self._output_path: Optional[Path] = None
+        self._manifest_path: Optional[Path] = None
 
     # ------------------------------------------------------------------ hooks
     def on_predict_start(self, trainer=None, pl_module=None) -> None:
         if not self.enabled:
             return
-        self._records = []
+        self._records, self._pending, self._batches_seen = [], [], 0
         self.output_dir.mkdir(parents=True, exist_ok=True)
-        self._output_path = self.output_dir / f"{self.split}.pt"
-        self._manifest_path = self.output_dir / f"{self.split}.manifest.json"
-        if self._output_path.exists() and not self.overwrite:
-            raise FileExistsError(f"Output path already exists: {self._output_path}")
+        target = self.output_dir / f"{self.split}.pt"
+        if target.exists() and not self.overwrite:
+            raise FileExistsError(f"Output path already exists: {target}")
+        self._output_path, self._manifest_path = target, target.with_name(f"{self.split}.manifest.json")
         if self.textualize:
             self._entity_map, self._relation_map = self._resolve_vocab_maps()
 
@@ -124,26 +144,23 @@ class RetrieverTopKEdgeWriter:
         self._collect_prediction(prediction=prediction, batch=batch)
 
     def on_predict_end(self, trainer=None, pl_module=None) -> None:
-        if not self.enabled or not self._records:
+        if not self.enabled:
+            return
+        self._drain(0)
+        if not self._records:
             return
         records = self._gather_records(self._records)
-        if not records:
-            return
-        if trainer is not None and int(getattr(trainer, "global_rank", 0)) != 0:
+        is_writer_rank = trainer is None or int(getattr(trainer, "global_rank", 0)) == 0
+        if not records or not is_writer_rank:
             return
         if self._output_path is None or self._manifest_path is None:
             raise RuntimeError("RetrieverTopKEdgeWriter missing output path; on_predict_start was not called.")
-        payload = {"settings": {"split": self.split, "topk_values": [int(k) for k in self.topk_values]},
-                   "samples": records}
-        torch.save(payload, self._output_path)
-        manifest = {
-            "artifact": self.artifact_name,
-            "schema_version": self.schema_version,
-            "file": self._output_path.name,
-            "created_at": datetime.now(timezone.utc).replace(tzinfo=None).isoformat(timespec="seconds") + "Z",
-            "producer": "retriever_topk_edge_writer",
-        }
-        self._manifest_path.write_text(json.dumps(manifest, indent=2), encoding="utf-8")
+        torch.save({"settings": {"split": self.split, "topk_values": list(map(int, self.topk_values))},
+                    "samples": records}, self._output_path)
+        stamp = datetime.now(timezone.utc).replace(tzinfo=None).isoformat(timespec="seconds") + "Z"
+        self._manifest_path.write_text(json.dumps({
+            "artifact": self.artifact_name, "schema_version": self.schema_version, "file": self._output_path.name,
+            "created_at": stamp, "producer": "retriever_topk_edge_writer"}, indent=2), encoding="utf-8")
 
     def on_test_start(self, trainer=None, pl_module=None) -> None:
         self.on_predict_start(trainer, pl_module)
@@ -168,9 +185,57 @@ class RetrieverTopKEdgeWriter:
                 logits_fwd=prediction.get("logits_fwd"), logits_bwd=prediction.get("logits_bwd"))
         elif not hasattr(prediction, "logits") or not hasattr(prediction, "query_ids"):
             return
-        self._records.extend(self._build_records(batch=batch, output=prediction))
+        self._pending.append(self._enqueue(batch=batch, output=prediction))
+        self._drain(self.pipeline_depth)
 
     def _build_records(self, *, batch: Any, output: Any) -> List[Dict[str, Any]]:
+        """Records of one batch, synchronously (the per-batch path goes through ``_enqueue`` / ``_drain``)."""
+        return self._materialise(self._enqueue(batch=batch, output=output))
+
+    def _drain(self, keep: int) -> None:
+        """Turn all but the newest ``keep`` in-flight batches into records."""
+        while len(self._pending) > keep:
+            self._records.extend(self._materialise(self._pending.pop(0)))
+
+    def _host_buffers(self, pay: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """Pinned destination of one batch's payload: a rotating set per in-flight batch (allocating pinned memory per
+        batch would call cudaHostAlloc, which synchronises the device)."""
+        n_sets = self.pipeline_depth + 2
+        while len(self._pinned) < n_sets:
+            self._pinned.append({})
+        slot = self._pinned[self._batches_seen % n_sets]
+        self._batches_seen += 1
+        out = {}
+        for k in _HOST_KEYS:
+            src = pay[k]
+            buf = slot.get(k)
+            if buf is None or buf.numel() < src.numel() or buf.dtype != src.dtype:
+                buf = torch.empty(max(1, int(src.numel() * 1.25)), dtype=src.dtype, pin_memory=True)
+                slot[k] = buf
+            view = buf[: src.numel()].view(src.shape)
+            view.copy_(src, non_blocking=True)
+            out[k] = view
+        return out
+
+    def _edge_ptr(self, batch: Any, query_ids: torch.Tensor, num_edges: int, B: int, dev) -> torch.Tensor:
+        """Edge offsets per question: the collate's slice dict (:389-395), a precomputed ``batch.edge_ptr``
+        (loader.py:81-99), else the counts of the (sorted) query ids."""
+        slice_dict = getattr(batch, "_slice_dict", None)
+        for cand in (slice_dict.get("edge_index") if isinstance(slice_dict, dict) else None,
+                     getattr(batch, "edge_ptr", None)):
+            if cand is not None:
+                cand = torch.as_tensor(cand, dtype=torch.long).view(-1)
+                if cand.numel() == B + 1:
+                    return cand.to(dev)
+        if query_ids.numel() != num_edges:
+            raise ValueError(f"query_ids/scores mismatch: {tuple(query_ids.shape)} vs {num_edges}")
+        if bool((query_ids[1:] < query_ids[:-1]).any()):
+            raise ValueError("writer expects edges grouped by question (PyG collate order).")
+        edge_ptr = torch.zeros(B + 1, dtype=torch.long, device=dev)
+        edge_ptr[1:] = torch.cumsum(torch.bincount(query_ids, minlength=B)[:B], 0)
+        return edge_ptr
+
+    def _enqueue(self, *, batch: Any, output: Any) -> _PendingBatch:
         logits = output.logits.detach().view(-1)
         if logits.device.type != "cuda":
             raise RuntimeError("RetrieverTopKEdgeWriter selects on the device: logits must be a CUDA tensor.")
@@ -183,68 +248,66 @@ class RetrieverTopKEdgeWriter:
                 raise ValueError(f"Batch missing {name} required for persistence.")
         query_ids = output.query_ids.detach().view(-1).to(dev)
         B = self._num_graphs(batch, query_ids)
+        edge_ptr = self._edge_ptr(batch, query_ids, logits.numel(), B, dev)
         slice_dict = getattr(batch, "_slice_dict", None)
-        edge_ptr = None
-        if isinstance(slice_dict, dict) and "edge_index" in slice_dict:
-            cand = torch.as_tensor(slice_dict["edge_index"], dtype=torch.long).view(-1)
-            if cand.numel() == B + 1:
-                edge_ptr = cand.to(dev)
-        if edge_ptr is None:
-            if query_ids.numel() != logits.numel():
-                raise ValueError(f"query_ids/scores mismatch: {query_ids.shape} vs {logits.shape}")
-            if bool((query_ids[1:] < query_ids[:-1]).any()):
-                raise ValueError("writer expects edges grouped by question (PyG collate order).")
-            edge_ptr = torch.zeros(B + 1, dtype=torch.long, device=dev)
-            edge_ptr[1:] = torch.cumsum(torch.bincount(query_ids, minlength=B)[:B], 0)
         answer_ptr_raw = getattr(batch, "answer_entity_ids_ptr", None)
         if answer_ptr_raw is None and isinstance(slice_dict, dict):
             answer_ptr_raw = slice_dict.get("answer_entity_ids")
         if answer_ptr_raw is None:
             raise ValueError("Batch missing answer_entity_ids_ptr required for persistence.")
-        answer_ptr = torch.as_tensor(answer_ptr_raw, dtype=torch.long).view(-1).tolist()
-        if len(answer_ptr) != B + 1:
-            raise ValueError(f"answer_entity_ids_ptr length mismatch: {len(answer_ptr)} vs expected {B + 1}")
-        answers = batch.answer_entity_ids.detach().cpu().view(-1).tolist()
+        item = _PendingBatch()
+        item.answer_ptr = torch.as_tensor(answer_ptr_raw, dtype=torch.long).view(-1).tolist()
+        if len(item.answer_ptr) != B + 1:
+            raise ValueError(f"answer_entity_ids_ptr length mismatch: {len(item.answer_ptr)} vs expected {B + 1}")
+        item.answers = batch.answer_entity_ids.detach().cpu().view(-1).tolist()
+        item.has_fwd = getattr(output, "logits_fwd", None) is not None
+        item.has_bwd = getattr(output, "logits_bwd", None) is not None
+        item.sample_ids, item.questions, item.num_graphs = _sample_ids(batch, B), _questions(batch, B), B
+        with torch.cuda.device(dev):
+            top = segmented_topk(logits, edge_ptr, self._max_topk, sigmoid=True)  # scores = sigmoid(logits) (:203)
+            pay = writer_payload(top, edge_ptr, edge_index=batch.edge_index, node_global_ids=batch.node_global_ids,
+                                 edge_attr=batch.edge_attr, labels=labels,
+                                 logits_fwd=getattr(output, "logits_fwd", None),
+                                 logits_bwd=getattr(output, "logits_bwd", None))
+            item.host = self._host_buffers(pay)
+            item.done = torch.cuda.Event()
+            item.done.record(torch.cuda.current_stream(dev))
+        return item
 
-        top = segmented_topk(logits, edge_ptr, self._max_topk, sigmoid=True)  # scores = sigmoid(logits) (:203)
-        pay = writer_payload(top, edge_ptr, edge_index=batch.edge_index, node_global_ids=batch.node_global_ids,
-                             edge_attr=batch.edge_attr, labels=labels,
-                             logits_fwd=getattr(output, "logits_fwd", None), logits_bwd=getattr(output, "logits_bwd", None))
-        host = {k: pay[k].cpu().tolist() for k in ("score", "count", "head_id", "tail_id", "relation_id", "label",
-                                                   "logit_fwd", "logit_bwd")}
-        has_fwd = getattr(output, "logits_fwd", None) is not None
-        has_bwd = getattr(output, "logits_bwd", None) is not None
-        sample_ids = _sample_ids(batch, B)
-        questions = _questions(batch, B)
+    def _materialise(self, item: _PendingBatch) -> List[Dict[str, Any]]:
+        """The reference's per-question record (:321-349) from the [B, max_k] host arrays. Columns become Python lists
+        once per batch; an edge dict is one zip step (the values are Python ints / floats already)."""
+        item.done.synchronize()
+        cols = {k: v.tolist() for k, v in item.host.items()}
+        ent, rel = self._entity_map, self._relation_map
+        keys = _EDGE_KEYS + (("logit_fwd",) if item.has_fwd else ()) + (("logit_bwd",) if item.has_bwd else ())
+        ks = [int(k) for k in self.topk_values]
         records: List[Dict[str, Any]] = []
-        for gid in range(B):
-            kt = int(host["count"][gid])
+        for gid in range(item.num_graphs):
+            kt = cols["count"][gid]
             if kt <= 0:
                 continue
-            edges = [self._edge_record(host, gid, j, has_fwd, has_bwd) for j in range(kt)]
-            triplets_by_k = {int(k): [dict(e) for e in edges[: min(int(k), kt)]] for k in self.topk_values}
+            h, r, t = cols["head_id"][gid][:kt], cols["relation_id"][gid][:kt], cols["tail_id"][gid][:kt]
+            none = [None] * kt
+            fields = [h, r, t,
+                      none if ent is None else [ent.get(x) for x in h],
+                      none if rel is None else [rel.get(x) for x in r],
+                      none if ent is None else [ent.get(x) for x in t],
+                      cols["score"][gid][:kt], cols["label"][gid][:kt], range(1, kt + 1)]
+            if item.has_fwd:
+                fields.append(cols["logit_fwd"][gid][:kt])
+            if item.has_bwd:
+                fields.append(cols["logit_bwd"][gid][:kt])
+            rows = list(zip(*fields))
+            # every k gets its own dict objects, like the reference's per-k list comprehension (:324-327)
+            triplets_by_k = {k: [dict(zip(keys, row)) for row in rows[: min(k, kt)]] for k in ks}
             records.append({
-                "sample_id": sample_ids[gid] if gid < len(sample_ids) else str(gid),
-                "question": questions[gid] if gid < len(questions) else "",
+                "sample_id": item.sample_ids[gid] if gid < len(item.sample_ids) else str(gid),
+                "question": item.questions[gid] if gid < len(item.questions) else "",
                 "triplets_by_k": triplets_by_k,
-                "answer_entity_ids": [int(x) for x in answers[answer_ptr[gid]:answer_ptr[gid + 1]]],
+                "answer_entity_ids": item.answers[item.answer_ptr[gid]:item.answer_ptr[gid + 1]],
             })
         return records
-
-    def _edge_record(self, host, gid: int, j: int, has_fwd: bool, has_bwd: bool) -> Dict[str, Any]:
-        h, r, t = int(host["head_id"][gid][j]), int(host["relation_id"][gid][j]), int(host["tail_id"][gid][j])
-        rec = {
-            "head_entity_id": h, "relation_id": r, "tail_entity_id": t,
-            "head_text": self._lookup_text(self._entity_map, h),
-            "relation_text": self._lookup_text(self._relation_map, r),
-            "tail_text": self._lookup_text(self._entity_map, t),
-            "score": float(host["score"][gid][j]), "label": float(host["label"][gid][j]), "rank": j + 1,
-        }
-        if has_fwd:
-            rec["logit_fwd"] = float(host["logit_fwd"][gid][j])
-        if has_bwd:
-            rec["logit_bwd"] = float(host["logit_bwd"][gid][j])
-        return rec
 
     @staticmethod
     def _num_graphs(batch: Any, query_ids: torch.Tensor) -> int:
@@ -256,12 +319,6 @@ class RetrieverTopKEdgeWriter:
         if ptr is not None:
             return int(ptr.numel() - 1)
         return int(query_ids.max().item()) + 1 if query_ids.numel() else 0
-
-    @staticmethod
-    def _lookup_text(mapping: Optional[Dict[int, str]], key: Optional[int]) -> Optional[str]:
-        if mapping is None or key is None:
-            return None
-        return mapping.get(key)
 
     def _resolve_vocab_maps(self):
         """entity / relation parquet vocabularies ``(id, label)`` (:409-441)."""

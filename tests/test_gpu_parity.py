@@ -752,6 +752,45 @@ def test_writer_artifact_matches_reference(dev, golden_dir, tmp_path):
                             assert x[key] == y[key], (key, x, y)
 
 
+def test_writer_pipelined_batches_keep_order(dev, golden_dir, tmp_path):
+    """The hook leaves `pipeline_depth` batches in flight (records of batch i are built while the device works on
+    batch i+1): three batches through depth 0 / 1 / 2 give the same records in the same order as one by one."""
+    import types
+
+    from evi_rag_b200.writer import RetrieverTopKEdgeWriter
+
+    g = _g(golden_dir, "writer_inputs.npz")
+    B = len(g["ptr"]) - 1
+    qid = torch.from_numpy(np.repeat(np.arange(B), np.diff(g["edge_ptr"]))).to(dev)
+
+    def batch_and_out(shift):
+        batch = types.SimpleNamespace(
+            num_graphs=B, ptr=torch.from_numpy(g["ptr"]), edge_index=torch.from_numpy(g["edge_index"]),
+            edge_attr=torch.from_numpy(g["edge_attr"]), labels=torch.from_numpy(g["labels"]),
+            node_global_ids=torch.from_numpy(g["node_global_ids"]), answer_entity_ids=torch.from_numpy(g["answer_entity_ids"]),
+            answer_entity_ids_ptr=torch.from_numpy(g["answer_ptr"]), sample_id=[f"s{shift}_{i}" for i in range(B)],
+            edge_ptr=torch.from_numpy(g["edge_ptr"]))
+        lg = torch.from_numpy(np.roll(g["logits"], shift)).to(dev)
+        return batch, types.SimpleNamespace(logits=lg, query_ids=qid, logits_fwd=None, logits_bwd=lg)
+
+    runs = []
+    for depth in (0, 1, 2):
+        w = RetrieverTopKEdgeWriter(output_dir=tmp_path / f"d{depth}", topk_values=[3, 50], pipeline_depth=depth)
+        w.on_predict_start()
+        for shift in (0, 7, 19):
+            b, o = batch_and_out(shift)
+            w.write_on_batch_end(None, None, o, None, b, 0)
+            assert len(w._pending) <= depth
+        w.on_predict_end()
+        runs.append(w._records)
+        assert (tmp_path / f"d{depth}" / "test.pt").exists()
+    assert runs[0] == runs[1] == runs[2] and len(runs[0]) == 3 * sum(1 for c in np.diff(g["edge_ptr"]) if c > 0)
+    assert [r["sample_id"].split("_")[0] for r in runs[0]][::len(runs[0]) // 3] == ["s0", "s7", "s19"]
+    assert "logit_fwd" not in runs[0][0]["triplets_by_k"][3][0] and "logit_bwd" in runs[0][0]["triplets_by_k"][3][0]
+    with pytest.raises(ValueError, match="topk_values up to"):
+        RetrieverTopKEdgeWriter(output_dir=tmp_path, topk_values=[5, 2000])
+
+
 # ------------------------------------------------------------------ (f4) RetrieverLoss
 LOSS_CASES = {
     "infonce": dict(),
