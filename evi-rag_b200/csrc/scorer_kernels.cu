@@ -1356,7 +1356,8 @@ struct ChunkPlan {
 
   // tail_mode 0: TMA ring (persistent, 192 KB of shared memory per CTA); 1: register-fed, `tail_threads` per CTA
   // (no shared memory, so its CTAs fit beside a resident GEMM CTA)
-  int tail(cudaStream_t stream, int tail_mode, int tail_threads) const {
+  int tail(cudaStream_t stream, int tail_mode, int tail_threads, cudaEvent_t time_begin = nullptr,
+           cudaEvent_t time_end = nullptr) const {
     float* logits = a.logits ? a.logits + e0 : nullptr;
     float* logits_fwd = a.logits_fwd ? a.logits_fwd + e0 : nullptr;
     float* logits_bwd = a.logits_bwd ? a.logits_bwd + e0 : nullptr;
@@ -1374,6 +1375,7 @@ struct ChunkPlan {
     const int* p_head = (a.head_rep32 != nullptr ? a.head_rep32 : a.head32) + e0;
     const int* p_tail = (a.tail_rep32 != nullptr ? a.tail_rep32 : a.tail32) + e0;
     const int p_rows = a.num_rep_rows > 0 ? a.num_rep_rows : a.num_nodes;
+    if (time_begin) cudaEventRecord(time_begin, stream);
     if (tail_mode == 1) {
       const int warps = tail_threads / 32;
       const int tgrid = static_cast<int>((E + warps - 1) / warps);
@@ -1399,6 +1401,7 @@ struct ChunkPlan {
           a.num_pair_rows, E, tp, feats && do_f ? g_f : nullptr, feats && do_b ? g_b : nullptr, feats ? nullptr : logits,
           feats ? nullptr : logits_fwd, feats ? nullptr : logits_bwd);
     }
+    if (time_end) cudaEventRecord(time_end, stream);
     if (check_launch() != kOk) return kErrCuda;
     if (!feats) return kOk;
     // feature path: state_net.4 as a second GEMM, logits from the fp32 features, softmax-weighted blend
@@ -1457,7 +1460,8 @@ static int score_edges_impl(const evi_score_args& a, cudaStream_t stream) {
       rc = plan.gemms(stream, gemm_sms, timed ? static_cast<cudaEvent_t>(a.ev_gemm_begin) : nullptr,
                       timed ? static_cast<cudaEvent_t>(a.ev_gemm_end) : nullptr);
       if (rc != kOk) return rc;
-      rc = plan.tail(stream, tail_mode_serial, 256);
+      rc = plan.tail(stream, tail_mode_serial, 256, timed ? static_cast<cudaEvent_t>(a.ev_tail_begin) : nullptr,
+                     timed ? static_cast<cudaEvent_t>(a.ev_tail_end) : nullptr);
       if (rc != kOk) return rc;
     }
     return kOk;

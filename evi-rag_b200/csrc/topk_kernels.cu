@@ -186,6 +186,7 @@ topk_metrics_kernel(const int* __restrict__ indices, const int* __restrict__ cou
                     unsigned char* __restrict__ reach_valid, float* __restrict__ margin,
                     unsigned char* __restrict__ margin_valid) {
   __shared__ float red_a[kMetricThreads / 32], red_b[kMetricThreads / 32];
+  __shared__ int red_i[kMetricThreads / 32], s_num_pos;
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const long long e0 = edge_ptr[b];
   const int ne = static_cast<int>(edge_ptr[b + 1] - e0);
@@ -194,28 +195,31 @@ topk_metrics_kernel(const int* __restrict__ indices, const int* __restrict__ cou
 
   if (labels != nullptr) {
     // positives of the whole question, and hits at each k
-    float p = 0.f;
-    for (int i = tid; i < ne; i += kMetricThreads) p += labels[e0 + i] > 0.5f ? 1.f : 0.f;
-    p = warp_sum(p);
-    if (lane == 0) red_a[w] = p;
+    int p = 0;  // counted as integers: exact for any question size
+    for (int i = tid; i < ne; i += kMetricThreads) p += labels[e0 + i] > 0.5f ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) p += __shfl_xor_sync(0xffffffffu, p, o);
+    if (lane == 0) red_i[w] = p;
     __syncthreads();
     if (tid == 0) {
-      float t = 0.f;
-      for (int i = 0; i < kMetricThreads / 32; ++i) t += red_a[i];
-      pos[b] = t;
+      int t = 0;
+      for (int i = 0; i < kMetricThreads / 32; ++i) t += red_i[i];
+      s_num_pos = t;
+      pos[b] = static_cast<float>(t);
     }
     __syncthreads();
     for (int ki = 0; ki < ks.n; ++ki) {
       const int ke = ks.v[ki] < kt ? ks.v[ki] : kt;
-      float h = 0.f;
-      for (int j = tid; j < ke; j += kMetricThreads) h += labels[e0 + idx[j]] > 0.5f ? 1.f : 0.f;
-      h = warp_sum(h);
-      if (lane == 0) red_a[w] = h;
+      int h = 0;
+      for (int j = tid; j < ke; j += kMetricThreads) h += labels[e0 + idx[j]] > 0.5f ? 1 : 0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) h += __shfl_xor_sync(0xffffffffu, h, o);
+      if (lane == 0) red_i[w] = h;
       __syncthreads();
       if (tid == 0) {
-        float t = 0.f;
-        for (int i = 0; i < kMetricThreads / 32; ++i) t += red_a[i];
-        hits[static_cast<size_t>(b) * ks.n + ki] = t;
+        int t = 0;
+        for (int i = 0; i < kMetricThreads / 32; ++i) t += red_i[i];
+        hits[static_cast<size_t>(b) * ks.n + ki] = static_cast<float>(t);
       }
       __syncthreads();
     }
@@ -234,7 +238,9 @@ topk_metrics_kernel(const int* __restrict__ indices, const int* __restrict__ cou
       __syncthreads();
       if (tid == 0) {
         for (int i = 1; i < kMetricThreads / 32; ++i) mn = fminf(mn, red_a[i]), mx = fmaxf(mx, red_b[i]);
-        const bool ok = mn != INFINITY && mx != -INFINITY;  // has a positive and a negative
+        // validity from label presence like the reference (labels.any() / (~labels).any(), retriever_metrics.py:372-386),
+        // not from the sentinels: a question whose only positive scores +inf is still a valid question
+        const bool ok = s_num_pos > 0 && ne - s_num_pos > 0;
         margin[b] = ok ? mn - mx : 0.f;
         margin_valid[b] = ok ? 1 : 0;
       }

@@ -48,6 +48,7 @@ class ScoreArgs(C.Structure):
         ("aux_stream", _vp),
         ("precision", _i), ("node_repr_ld", _i), ("rel_repr_ld", _i), ("w1_ld", _i), ("w1_lo_off", _i),
         ("num_rep_rows", _i), ("head_rep32", _vp), ("tail_rep32", _vp), ("sc_center", _vp), ("w2_ld", _i),
+        ("ev_tail_begin", _vp), ("ev_tail_end", _vp),
     ]
 
 

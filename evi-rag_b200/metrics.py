@@ -17,7 +17,7 @@ from typing import Dict, Optional, Sequence
 import torch
 
 from . import lib as _lib
-from .topk import TopK, segmented_topk
+from .topk import MAX_K, TopK, segmented_topk
 
 MAX_K_VALUES = 16
 
@@ -131,7 +131,10 @@ def retriever_metrics(logits: torch.Tensor, labels: torch.Tensor, edge_ptr: torc
     ks = normalize_k_values(k_values)
     dev = logits.device
     edge_ptr = edge_ptr.to(device=dev, dtype=torch.long)
-    tk = segmented_topk(logits, edge_ptr, min(max(ks), 1024))
+    if max(ks) > MAX_K:
+        raise ValueError(f"k up to {MAX_K} is supported by the selection kernel (one CTA sorts a question's candidates "
+                         f"in shared memory); got max k = {max(ks)}. The reference's configs stop at k = 500.")
+    tk = segmented_topk(logits, edge_ptr, max(ks))
     gargs = {}
     if graph is not None:
         gargs = dict(head32=graph.head32, tail32=graph.tail32, node_ptr=node_ptr, q_local_indices=q_local_indices,

@@ -203,12 +203,21 @@ class RetrievalPipeline:
             done.record(compute)
             self._slot_free[i & 1] = done
             if pending is not None:
-                pending[0].synchronize()
-                yield pending[1]
+                yield self._finish(pending)
             pending = (done, out)
         if pending is not None:
-            pending[0].synchronize()
-            yield pending[1]
+            yield self._finish(pending)
+
+    def _finish(self, pending):
+        """Wait for a batch's device->host copies; with ``validate`` raise for its validation word like ``run``."""
+        done, out = pending
+        done.synchronize()
+        if self.validate:
+            word = int(out["flags"].item())
+            if word != 0:
+                self.model._flags.zero_()
+                self.model.raise_for_flags(word)
+        return out
 
     @staticmethod
     def d2h_bytes(res: Dict[str, torch.Tensor]) -> int:

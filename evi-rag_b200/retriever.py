@@ -171,6 +171,7 @@ class Retriever(nn.Module):
         self._ws: Optional[torch.Tensor] = None
         self._ws_score: Optional[torch.Tensor] = None
         self.gemm_events = None
+        self.tail_events = None
         self.last_chunk_edges = 0
         self.last_num_chunks = 0
         self._flags: Optional[torch.Tensor] = None
@@ -236,6 +237,11 @@ class Retriever(nn.Module):
         if word == 0:
             return
         self._flags.zero_()
+        self.raise_for_flags(word)
+
+    @staticmethod
+    def raise_for_flags(word: int) -> None:
+        """The reference's ``ValueError`` for a non-zero validation word (``EVI_FLAG_*`` bits)."""
         if word & _lib.FLAG_OUT_OF_RANGE:
             raise ValueError("Invalid edge_index range; edge_index / embedding ids out of range for this batch.")
         if word & _lib.FLAG_CROSS_GRAPH:
@@ -664,6 +670,9 @@ class Retriever(nn.Module):
         events = self.gemm_events  # (torch.cuda.Event begin, end) around one W_sc GEMM launch, or None
         a.ev_gemm_begin = events[0].cuda_event if events is not None else None
         a.ev_gemm_end = events[1].cuda_event if events is not None else None
+        tail_events = self.tail_events  # the same for the tail kernel of that chunk
+        a.ev_tail_begin = tail_events[0].cuda_event if tail_events is not None else None
+        a.ev_tail_end = tail_events[1].cuda_event if tail_events is not None else None
         _lib.check(L.evi_score_edges(C.byref(a), stream), "evi_score_edges")
         self._pending_flags = True
 

@@ -260,6 +260,8 @@ typedef struct evi_score_args {
   const int* tail_rep32;
   const float* sc_center;           /* [D] batch centre subtracted from sc (evi_sc_center), or NULL */
   int w2_ld;                        /* row pitch of w2_16; >= 2H: rows are [hi | lo] and the features path runs three passes */
+  void* ev_tail_begin;              /* optional cudaEvent_t pair around the tail kernel of the same chunk as ev_gemm_* */
+  void* ev_tail_end;
 } evi_score_args;
 
 /* bytes of the per-chunk workspace for `chunk_edges` edges */

@@ -1232,3 +1232,68 @@ def test_hide_seek_bias_apply_in_eval(dev, golden_dir):
     assert torch.equal(off.logits, base.logits)
     with pytest.raises(ValueError, match="q_local_indices/a_local_indices"):
         run(cfg)
+
+
+# ------------------------------------------------------------------ round 2: advisor findings
+def test_run_stream_validates_like_run(dev):
+    """run_stream with validate=True raises the same ValueError as run for a batch whose edge leaves its graph."""
+    from evi_rag_b200.pipeline import RetrievalPipeline, host_batch
+    from evi_rag_b200.synthetic import make_embedding_tables
+
+    spec = tiny_spec(6, 300, seed=23, num_relations=40, num_entities=800)
+    ent, rel = make_embedding_tables(spec)
+    model = _table_model(dev, make_state_dict(2, trained_like=True), ent, rel)
+    pipe = RetrievalPipeline(model, top_k=20, bfs_max_depth=2, validate=True)
+    good = host_batch(generate_questions(spec, q_start=0, q_count=3), pin=False)
+    bad = host_batch(generate_questions(spec, q_start=3, q_count=3), pin=False)
+    bad.edge_index = bad.edge_index.clone()
+    bad.edge_index[1, 0] = int(bad.ptr_host[-1]) - 1  # tail in the last graph, head in the first
+    with pytest.raises(ValueError, match="crosses graph boundaries"):
+        pipe.run(bad, dev)
+    with pytest.raises(ValueError, match="crosses graph boundaries"):
+        for _ in pipe.run_stream([good, bad, good], dev):
+            pass
+    assert len(list(pipe.run_stream([good, good], dev))) == 2  # the flag word is clean again
+
+
+def test_unsorted_supplied_edge_batch_is_reported(dev):
+    """Table mode derives the (question, relation) pair slots from sorted question ids; a caller-supplied edge_batch
+    that is not grouped by question must raise instead of scoring with another question's relation context."""
+    import types
+
+    spec = tiny_spec(3, 200, seed=31, num_relations=16, num_entities=300)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(4)
+    ent = (rng.standard_normal((301, 1024)) * 0.5).astype(np.float32)
+    rel = (rng.standard_normal((16, 1024)) * 0.5).astype(np.float32)
+    m = _table_model(dev, make_state_dict(1, trained_like=True), ent, rel)
+    b = _ids_batch(qb)
+    qid = np.repeat(np.arange(qb.num_graphs), np.diff(qb.edge_ptr))
+    b.edge_batch = torch.from_numpy(qid)
+    ok = m(b).logits.clone()
+    b2 = _ids_batch(qb)
+    assert torch.equal(m(b2).logits, ok)  # a sorted supplied edge_batch equals the computed one
+    perm = rng.permutation(qb.num_edges)
+    b3 = _ids_batch(qb)
+    b3.edge_index, b3.edge_attr = b3.edge_index[:, perm], b3.edge_attr[perm]
+    b3.edge_batch = torch.from_numpy(qid[perm])
+    with pytest.raises(ValueError, match="not non-decreasing"):
+        m(b3)
+
+
+def test_metrics_k_limit_and_margin_validity(dev):
+    from evi_rag_b200.metrics import retriever_metrics, topk_metric_arrays
+    from evi_rag_b200.topk import segmented_topk
+
+    edge_ptr = torch.tensor([0, 4, 8, 10], device=dev)
+    logits = torch.tensor([float("inf"), 0.5, 0.1, -1.0, 1.0, 2.0, 3.0, 4.0, 0.3, float("-inf")], device=dev)
+    labels = torch.tensor([1.0, 0, 0, 0, 1, 1, 1, 1, 1, 0], device=dev)
+    with pytest.raises(ValueError, match="k up to 1024"):
+        retriever_metrics(logits, labels, edge_ptr, [10, 2000])
+    tk = segmented_topk(logits, edge_ptr, 4)
+    arr = topk_metric_arrays(tk, edge_ptr, [1, 4], labels=labels, scores=logits)
+    # question 0: its only positive scores +inf (valid, margin +inf); question 1: no negative (invalid);
+    # question 2: its only negative scores -inf (valid, margin +inf)
+    assert arr.margin_valid.cpu().tolist() == [1, 0, 1]
+    assert arr.margin.cpu().tolist()[0] == float("inf") and arr.margin.cpu().tolist()[2] == float("inf")
+    assert arr.pos.cpu().tolist() == [1.0, 4.0, 1.0]
