@@ -8,9 +8,9 @@ mkdir -p "$OUT"
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > "$OUT/${TAG}_smi.txt" 2>&1
 timeout 900 python -m pytest tests -m gpu -x -q -s > "$OUT/${TAG}_pytest.log" 2>&1; echo "pytest exit $?" | tee -a "$OUT/${TAG}_pytest.log"
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > "$OUT/${TAG}_smoke.log" 2>&1; echo "smoke exit $?" | tee -a "$OUT/${TAG}_smoke.log"
-timeout 900 python bench.py --steps 10 --warmup 3 > "$OUT/${TAG}_bench.json" 2> "$OUT/${TAG}_bench.err"; echo "bench exit $?"
+timeout 1200 python bench.py --steps 10 --warmup 3 > "$OUT/${TAG}_bench.json" 2> "$OUT/${TAG}_bench.err"; echo "bench exit $?"
 tail -c 3000 "$OUT/${TAG}_bench.json"
-BARGS="--steps 2 --warmup 1 --no-cpu-baseline"
+BARGS="--steps 2 --warmup 1 --no-cpu-baseline --no-other-configs"
 timeout 600 python bench.py $BARGS > "$OUT/${TAG}_plain.log" 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
     --log-file "$OUT/${TAG}_launches.csv" python bench.py $BARGS > "$OUT/${TAG}_ncu_list.log" 2>&1
