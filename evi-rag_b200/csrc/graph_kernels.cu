@@ -51,7 +51,10 @@ __global__ void edge_batch_kernel(const long long* __restrict__ edge_index, long
   if (qid32) qid32[e] = gh;
   if (head32) head32[e] = static_cast<int>(h);
   if (tail32) tail32[e] = static_cast<int>(t);
-  if (edge_ptr != nullptr && f == 0) {
+  // A cross-graph edge still opens its head's graph: only an out-of-range or out-of-order head leaves edge_ptr alone
+  // (entries nobody writes keep the host-side prefill num_edges = an empty range; consumers run before the flag
+  // word is read back, so every offset must stay inside [0, num_edges]).
+  if (edge_ptr != nullptr && (f & (kFlagOutOfRange | kFlagNotMonotone)) == 0) {
     // edges are grouped by graph: edge e opens every graph in (gprev, gh]
     for (int g = gprev + 1; g <= gh; ++g) edge_ptr[g] = e;
     if (e == num_edges - 1)
@@ -519,6 +522,7 @@ int evi_edge_batch(const long long* edge_index, long long num_edges, const long 
     return check_launch();
   }
   if (edge_index == nullptr) return kErrInvalidArg;
+  if (edge_ptr) fill_i64_kernel<<<cdiv(num_graphs + 1, 256), 256, 0, stream>>>(edge_ptr, num_graphs + 1, num_edges);
   edge_batch_kernel<<<cdiv(num_edges, 256), 256, 0, stream>>>(edge_index, num_edges, ptr, num_graphs,
                                                               edge_batch64, qid32, head32, tail32,
                                                               edge_ptr, flags);

@@ -122,7 +122,8 @@ class PoolRetriever:
 
     def __init__(self, shards: Sequence[TriplePoolShard], model: Any, *, node_embedding_ids: Optional[torch.Tensor] = None,
                  cap: int = 20000, top_k: int = 500, depth: int = 2, table_capacity: int = 1 << 22,
-                 max_table_capacity: int = 1 << 30, group=None, num_sms: int = 148) -> None:
+                 max_table_capacity: int = 1 << 30, group=None, num_sms: int = 148,
+                 score_edges_per_batch: int = 1 << 18) -> None:
         if not shards:
             raise ValueError("at least one shard is required")
         if not (0 < cap <= _lib.POOL_MAX_CAP):
@@ -149,6 +150,10 @@ class PoolRetriever:
         if self.world > 1 and len(self.shards) != 1:
             raise ValueError("with torch.distributed every rank holds exactly one shard")
         self.num_sms = int(num_sms)
+        # scoring walks the slab's queries in sub-batches of about this many candidate edges (the scorer's per-node
+        # rows cost ~20 KB per node: a 64k-query slab does not fit as one batch)
+        self.score_edges_per_batch = max(1, int(score_edges_per_batch))
+        self.timings: Dict[str, float] = {}
         self.L = _lib.load()
 
     # ------------------------------------------------------------------ exchange helpers
@@ -242,9 +247,24 @@ class PoolRetriever:
             self.table_capacity = min(self.table_capacity * 4, self.max_table_capacity)
         multi = len(states) > 1 or self.world > 1
         self._last_state = states[0]  # kept for traversal_stats()
-        sels = [self._shard_candidates(st, Q) for st in states]
-        sel = self._merge(sels, Q) if multi else sels[0]
-        return self._pack(states[0], sel, Q)
+        raw = [self._shard_candidates(st, Q) for st in states]
+        # Row stride of the fixed-shape [Q, stride] selection arrays: the batch's largest per-query candidate count
+        # (power of two), not `cap` — uniform-seed queries keep a few hundred candidates against cap = 20000, and
+        # [Q, cap] rows of a 64k-query slab would take tens of GB. Every count fits its row, so the selection is the
+        # same; one read-back (and one MAX all-reduce across ranks) per slab.
+        most = torch.stack([r[4] for r in raw]).max().view(1)
+        if self.world > 1:
+            dist.all_reduce(most, op=dist.ReduceOp.MAX, group=self.group)
+        stride = min(self.cap, _next_pow2(max(int(most.item()), 1)))
+        sels = [self._select(key, ht, rel, off, Q, stride) for key, ht, rel, off, _ in raw]
+        if multi:
+            n_sh = len(states) * self.world
+            out_stride = min(self.cap, n_sh * stride)
+            sel = self._merge(sels, Q, stride, out_stride)
+            stride = out_stride
+        else:
+            sel = sels[0]
+        return self._pack(states[0], sel, Q, stride)
 
     def traversal_stats(self) -> Dict[str, int]:
         """Adjacency entries shard 0 read for the last batch (bandwidth accounting, not on the timed path): both
@@ -258,8 +278,9 @@ class PoolRetriever:
                 "expand_entries": int((fdeg[:n_exp] + rdeg[:n_exp]).sum()),
                 "candidate_entries": int(2 * fdeg.sum())}
 
-    def _select(self, key, ht, rel, seg_off, Q: int):
-        dev, cap = self.dev, self.cap
+    def _select(self, key, ht, rel, seg_off, Q: int, cap: int):
+        """``cap`` = rows' stride and the number of keys kept per query (``self.cap``, or the batch's largest count)."""
+        dev = self.dev
         sort_len = _next_pow2(cap)
         u64 = lambda *s: torch.empty(s, dtype=torch.long, device=dev)
         stage_key, stage_ht, stage_rel = u64(Q, cap), u64(Q, cap), torch.empty((Q, cap), dtype=torch.int32, device=dev)
@@ -292,11 +313,12 @@ class PoolRetriever:
                                          count.data_ptr(), limit.data_ptr(), emit_count.data_ptr(), off.data_ptr(),
                                          cursor.data_ptr(), key.data_ptr(), ht.data_ptr(), rel.data_ptr(), self.num_sms,
                                          stream), "evi_pool_candidates")
-        return self._select(key, ht, rel, off, Q)
+        return key, ht, rel, off, emit_count.max()
 
-    def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int):
-        """The cap smallest keys over the union of every shard's survivors (padding = all-ones keys)."""
-        dev, cap = self.dev, self.cap
+    def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int, cap: int, out_cap: int):
+        """The smallest keys over the union of every shard's survivors (rows of stride ``cap``, padding = all-ones
+        keys), ``out_cap`` kept per query."""
+        dev = self.dev
         valid = lambda s: torch.arange(cap, device=dev).unsqueeze(0) < s["count"].unsqueeze(1)
         for s in sels:
             s["key"] = torch.where(valid(s), s["key"], torch.full_like(s["key"], _EMPTY))
@@ -312,10 +334,10 @@ class PoolRetriever:
         S = int(parts["key"].shape[0])
         cat = {name: t.permute(1, 0, 2).reshape(Q * S * cap).contiguous() for name, t in parts.items()}
         seg_off = torch.arange(Q + 1, dtype=torch.long, device=dev) * (S * cap)
-        return self._select(cat["key"], cat["ht"], cat["rel"], seg_off, Q)
+        return self._select(cat["key"], cat["ht"], cat["rel"], seg_off, Q, out_cap)
 
-    def _pack(self, st: _ShardState, sel, Q: int) -> types.SimpleNamespace:
-        L, dev, cap, stream = self.L, self.dev, self.cap, _lib.stream_handle()
+    def _pack(self, st: _ShardState, sel, Q: int, cap: int) -> types.SimpleNamespace:
+        L, dev, stream = self.L, self.dev, _lib.stream_handle()
         node_count = torch.empty(Q, dtype=torch.int32, device=dev)
         node_global = torch.empty((Q, 2 * cap), dtype=torch.int32, device=dev)
         node_is_seed = torch.empty((Q, 2 * cap), dtype=torch.uint8, device=dev)
@@ -349,9 +371,9 @@ class PoolRetriever:
 
     # ------------------------------------------------------------------ step 3: score + top-k
     @staticmethod
-    def _slice(b, q0: int, q1: int, question_emb: torch.Tensor) -> types.SimpleNamespace:
-        """Questions [q0, q1) of a subgraph batch, re-based to their own batch-global node ids."""
-        ep, npt = b.edge_ptr.tolist(), b.ptr.tolist()
+    def _slice(b, q0: int, q1: int, question_emb: torch.Tensor, ep, npt) -> types.SimpleNamespace:
+        """Questions [q0, q1) of a subgraph batch, re-based to their own batch-global node ids. ``ep`` / ``npt`` are
+        host copies of ``b.edge_ptr`` / ``b.ptr``."""
         e0, e1, n0, n1 = ep[q0], ep[q1], npt[q0], npt[q1]
         s = types.SimpleNamespace()
         s.edge_index = (b.edge_index[:, e0:e1] - n0).contiguous()
@@ -366,32 +388,49 @@ class PoolRetriever:
             return self._score_on_device(b, question_emb)
 
     def _score_on_device(self, b: types.SimpleNamespace, question_emb: torch.Tensor) -> Dict[str, torch.Tensor]:
-        """Bidirectional scores of every candidate and the per-query top-k as global edge ids."""
+        """Bidirectional scores of every candidate and the per-query top-k as global edge ids. The rank's queries are
+        scored in sub-batches of about ``score_edges_per_batch`` candidate edges."""
         dev, k = self.dev, self.top_k
         Q = b.num_graphs
         question_emb = question_emb.to(device=dev, dtype=torch.float32)
-        if self.world > 1:  # queries shard across ranks by candidate count; results are gathered on every rank
-            counts = (b.edge_ptr[1:] - b.edge_ptr[:-1]).tolist()
-            parts = partition_by_edges(counts, self.world)
+        ep, npt = b.edge_ptr.tolist(), b.ptr.tolist()  # one read-back per slab: the sub-batch cuts are host decisions
+        # Sub-batch cuts are made on the whole query list, whatever the world size, and a rank takes a contiguous run
+        # of whole sub-batches (balanced by edges): a query is always scored inside the same sub-batch, so the N-rank
+        # scores equal the 1-rank scores bit for bit (the batch centre of the structure context depends on the batch).
+        cuts_all = [0]
+        while cuts_all[-1] < Q:
+            a = cuts_all[-1]
+            c = a + 1
+            while c < Q and ep[c + 1] - ep[a] <= self.score_edges_per_batch:
+                c += 1
+            cuts_all.append(c)
+        if self.world > 1:  # results are gathered on every rank
+            sub_edges = [ep[c] - ep[a] for a, c in zip(cuts_all[:-1], cuts_all[1:])]
+            sparts = partition_by_edges(sub_edges, self.world)
+            parts = [(cuts_all[s0], cuts_all[s1]) for s0, s1 in sparts]
+            s0, s1 = sparts[self.rank]
+            cuts = cuts_all[s0:s1 + 1]
             q0, q1 = parts[self.rank]
-            sb = self._slice(b, q0, q1, question_emb)
         else:
-            parts, q0, q1, sb = [(0, Q)], 0, Q, b
-            sb.question_emb = question_emb.contiguous()
+            parts, q0, q1, cuts = [(0, Q)], 0, Q, cuts_all
         nq = q1 - q0
-        if nq > 0 and sb.edge_index.size(1) > 0:
+        edge_id = torch.full((nq, k), -1, dtype=torch.long, device=dev)
+        score = torch.full((nq, k), float("-inf"), device=dev)
+        count = torch.zeros(nq, dtype=torch.int32, device=dev)
+        logits = torch.empty(ep[q1] - ep[q0], dtype=torch.float32, device=dev)
+        ar_k = torch.arange(k, device=dev).unsqueeze(0)
+        for a, c in zip(cuts[:-1], cuts[1:]):
+            if ep[c] == ep[a]:
+                continue  # no candidates in this range
+            sb = self._slice(b, a, c, question_emb, ep, npt)
             out = self.model(sb)
             top = segmented_topk(out.logits, sb.edge_ptr, k)
             gidx = (top.indices.long() + sb.edge_ptr[:-1].unsqueeze(1)).clamp(min=0, max=sb.edge_global_id.numel() - 1)
-            valid = torch.arange(k, device=dev).unsqueeze(0) < top.counts.unsqueeze(1)
-            res = {"edge_id": torch.where(valid, sb.edge_global_id[gidx], torch.full_like(gidx, -1)),
-                   "score": top.values, "count": top.counts}
-            logits = out.logits
-        else:
-            res = {"edge_id": torch.full((nq, k), -1, dtype=torch.long, device=dev),
-                   "score": torch.full((nq, k), float("-inf"), device=dev),
-                   "count": torch.zeros(nq, dtype=torch.int32, device=dev)}
-            logits = torch.empty(0, device=dev)
+            valid = ar_k < top.counts.unsqueeze(1)
+            edge_id[a - q0:c - q0] = torch.where(valid, sb.edge_global_id[gidx], torch.full_like(gidx, -1))
+            score[a - q0:c - q0], count[a - q0:c - q0] = top.values, top.counts
+            logits[ep[a] - ep[q0]:ep[c] - ep[q0]] = out.logits
+        res = {"edge_id": edge_id, "score": score, "count": count}
         if self.world > 1:
             res = gather_topk(res, nq, group=self.group, counts=[b_ - a_ for a_, b_ in parts])
         res["logits_local"] = logits

@@ -132,7 +132,7 @@ _lib: Optional[C.CDLL] = None
 
 # kernels launched per C-ABI call (bench.py reports the total as `gpu_launches`)
 _KERNELS_PER_CALL = {
-    "evi_edge_batch": lambda a: 1,
+    "evi_edge_batch": lambda a: (2 if a[8] else 1) if a[1] > 0 else 1,
     "evi_dde_forward": lambda a: 1 + (2 if a[2] > 0 else 1) * max(a[6], a[7]),
     "evi_build_csr": lambda a: 3 if a[2] > 0 else 1,
     "evi_bfs_multi_source": lambda a: 1,

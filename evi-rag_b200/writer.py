@@ -93,13 +93,16 @@ class RetrieverTopKEdgeWriter:
     """Persist retriever top-k edges during predict/test (retriever_topk_edge_writer.py:68-170).
 
     Per batch the hook enqueues one ragged top-k, one payload gather and the device->host copies into rotating pinned
-    buffers and returns without synchronising; the Python records of batch i are built while the device already works
-    on batch i+1 (``pipeline_depth`` batches stay in flight), the rest in ``on_predict_end`` / ``on_test_end``."""
+    buffers and returns without synchronising. The selected triples stay columnar ([B, max_k] host arrays) until
+    ``on_predict_end`` / ``on_test_end`` turns them into the reference's per-question records in one go
+    (``materialise="end"``, the default: building ~100 Python dicts per question costs more host time than the device
+    needs for the batch, so doing it per batch would stall the next forward). ``materialise="batch"`` builds the
+    records of batch i while the device works on batch i+1, ``pipeline_depth`` batches in flight."""
 
     def __init__(self, *, output_dir, split: str = "test", enabled: bool = True, artifact_name: str = "eval_retriever",
                  schema_version: int = 1, topk_values: Optional[Sequence[int]] = None, textualize: bool = False,
                  entity_vocab_path: Optional[str] = None, relation_vocab_path: Optional[str] = None,
-                 overwrite: bool = True, pipeline_depth: int = 1) -> None:
+                 overwrite: bool = True, pipeline_depth: int = 1, materialise: str = "end") -> None:
         name = str(artifact_name).strip()
         version = int(schema_version)
         ks = normalize_k_values(topk_values, default=_DEFAULT_TOPK_VALUES)
@@ -118,6 +121,10 @@ class RetrieverTopKEdgeWriter:
         self.topk_values, self._max_topk = ks, ks[-1]
         self.entity_vocab_path, self.relation_vocab_path = entity_vocab_path, relation_vocab_path
         self.pipeline_depth = max(0, int(pipeline_depth))
+        if materialise not in ("end", "batch"):
+            raise ValueError(f"materialise must be 'end' or 'batch', got {materialise!r}")
+        self.materialise = materialise
+        self._columnar: List[_PendingBatch] = []
         self._records: List[Dict[str, Any]] = []
         self._pending: List[_PendingBatch] = []
         self._pinned: List[Dict[str, torch.Tensor]] = []
@@ -131,7 +138,7 @@ class RetrieverTopKEdgeWriter:
     def on_predict_start(self, trainer=None, pl_module=None) -> None:
         if not self.enabled:
             return
-        self._records, self._pending, self._batches_seen = [], [], 0
+        self._records, self._pending, self._columnar, self._batches_seen = [], [], [], 0
         self.output_dir.mkdir(parents=True, exist_ok=True)
         target = self.output_dir / f"{self.split}.pt"
         if target.exists() and not self.overwrite:
@@ -147,6 +154,9 @@ class RetrieverTopKEdgeWriter:
         if not self.enabled:
             return
         self._drain(0)
+        for item in self._columnar:  # materialise="end": every batch's records now, in batch order
+            self._records.extend(self._materialise(item))
+        self._columnar = []
         if not self._records:
             return
         records = self._gather_records(self._records)
@@ -195,7 +205,13 @@ class RetrieverTopKEdgeWriter:
     def _drain(self, keep: int) -> None:
         """Turn all but the newest ``keep`` in-flight batches into records."""
         while len(self._pending) > keep:
-            self._records.extend(self._materialise(self._pending.pop(0)))
+            item = self._pending.pop(0)
+            if self.materialise == "batch":
+                self._records.extend(self._materialise(item))
+            else:  # keep the columns, free the pinned buffers for the next batches
+                item.done.synchronize()
+                item.host = {k: v.clone() for k, v in item.host.items()}
+                self._columnar.append(item)
 
     def _host_buffers(self, pay: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         """Pinned destination of one batch's payload: a rotating set per in-flight batch (allocating pinned memory per

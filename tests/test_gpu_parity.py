@@ -753,8 +753,8 @@ def test_writer_artifact_matches_reference(dev, golden_dir, tmp_path):
 
 
 def test_writer_pipelined_batches_keep_order(dev, golden_dir, tmp_path):
-    """The hook leaves `pipeline_depth` batches in flight (records of batch i are built while the device works on
-    batch i+1): three batches through depth 0 / 1 / 2 give the same records in the same order as one by one."""
+    """The hook leaves `pipeline_depth` batches in flight; records are built per batch (materialise="batch") or once at
+    the end from the kept columns (the default): three batches give the same records in the same order either way."""
     import types
 
     from evi_rag_b200.writer import RetrieverTopKEdgeWriter
@@ -774,17 +774,18 @@ def test_writer_pipelined_batches_keep_order(dev, golden_dir, tmp_path):
         return batch, types.SimpleNamespace(logits=lg, query_ids=qid, logits_fwd=None, logits_bwd=lg)
 
     runs = []
-    for depth in (0, 1, 2):
-        w = RetrieverTopKEdgeWriter(output_dir=tmp_path / f"d{depth}", topk_values=[3, 50], pipeline_depth=depth)
+    for depth, mode in ((0, "batch"), (1, "batch"), (2, "batch"), (1, "end")):
+        w = RetrieverTopKEdgeWriter(output_dir=tmp_path / f"d{depth}{mode}", topk_values=[3, 50], pipeline_depth=depth,
+                                    materialise=mode)
         w.on_predict_start()
         for shift in (0, 7, 19):
             b, o = batch_and_out(shift)
             w.write_on_batch_end(None, None, o, None, b, 0)
-            assert len(w._pending) <= depth
+            assert len(w._pending) <= depth and (mode == "batch" or not w._records)
         w.on_predict_end()
         runs.append(w._records)
-        assert (tmp_path / f"d{depth}" / "test.pt").exists()
-    assert runs[0] == runs[1] == runs[2] and len(runs[0]) == 3 * sum(1 for c in np.diff(g["edge_ptr"]) if c > 0)
+        assert (tmp_path / f"d{depth}{mode}" / "test.pt").exists()
+    assert runs[0] == runs[1] == runs[2] == runs[3] and len(runs[0]) == 3 * sum(1 for c in np.diff(g["edge_ptr"]) if c > 0)
     assert [r["sample_id"].split("_")[0] for r in runs[0]][::len(runs[0]) // 3] == ["s0", "s7", "s19"]
     assert "logit_fwd" not in runs[0][0]["triplets_by_k"][3][0] and "logit_bwd" in runs[0][0]["triplets_by_k"][3][0]
     with pytest.raises(ValueError, match="topk_values up to"):
