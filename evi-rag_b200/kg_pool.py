@@ -24,6 +24,7 @@ boundaries.
 from __future__ import annotations
 
 import ctypes as C
+import time
 import types
 from dataclasses import dataclass
 from typing import Any, Dict, List, Optional, Sequence, Tuple
@@ -67,10 +68,8 @@ class TriplePoolShard:
     @classmethod
     def from_triples(cls, heads, rels, tails, edge_ids, num_nodes: int, device) -> "TriplePoolShard":
         dev = torch.device(device)
-        h = torch.as_tensor(np.asarray(heads), dtype=torch.long, device=dev)
-        t = torch.as_tensor(np.asarray(tails), dtype=torch.long, device=dev)
-        r = torch.as_tensor(np.asarray(rels), dtype=torch.long, device=dev)
-        e = torch.as_tensor(np.asarray(edge_ids), dtype=torch.long, device=dev)
+        put = lambda x: (x if torch.is_tensor(x) else torch.as_tensor(np.asarray(x))).to(device=dev, dtype=torch.long)
+        h, t, r, e = put(heads), put(tails), put(rels), put(edge_ids)
         if h.numel() and (int(h.min()) < 0 or int(t.min()) < 0 or int(h.max()) >= num_nodes or int(t.max()) >= num_nodes):
             raise ValueError("triple endpoints must lie in [0, num_nodes)")
 
@@ -154,6 +153,7 @@ class PoolRetriever:
         # rows cost ~20 KB per node: a 64k-query slab does not fit as one batch)
         self.score_edges_per_batch = max(1, int(score_edges_per_batch))
         self.timings: Dict[str, float] = {}
+        self.profile = False  # True: synchronise around the frontier exchange and accumulate timings["exchange_s"]
         self.L = _lib.load()
 
     # ------------------------------------------------------------------ exchange helpers
@@ -193,6 +193,9 @@ class PoolRetriever:
                     st.fresh_count.data_ptr() if multi else None, visited_cap, st.flags.data_ptr(), self.num_sms,
                     stream), "evi_pool_expand")
             if multi:  # frontier exchange: every shard learns the pairs the others reached at this level
+                if self.profile:
+                    torch.cuda.synchronize(dev)
+                    t_x0 = time.perf_counter()
                 lists = [st.fresh[: min(int(st.fresh_count.item()), visited_cap)] for st in states]
                 if self.world > 1:
                     remote = self._gather_var(lists[0], int(lists[0].numel()))
@@ -206,6 +209,9 @@ class PoolRetriever:
                             _lib.check(L.evi_pool_insert(C.byref(st.table), pairs.data_ptr(), int(pairs.numel()), level + 1,
                                                          st.visited.data_ptr(), st.visited_count.data_ptr(),
                                                          visited_cap, st.flags.data_ptr(), stream), "evi_pool_insert")
+                if self.profile:
+                    torch.cuda.synchronize(dev)
+                    self.timings["exchange_s"] = self.timings.get("exchange_s", 0.0) + time.perf_counter() - t_x0
             for st in states:
                 st.bounds.append(min(int(st.visited_count.item()), visited_cap))
             if self._overflowed(states):
