@@ -92,6 +92,7 @@ class GraphBatch:
     edge_ptr: torch.Tensor  # int64 [B+1] device
     ptr_host: np.ndarray  # int64 [B+1]
     edge_ptr_host: Optional[np.ndarray] = None
+    flags: Optional[torch.Tensor] = None  # int32 [1]: the validation word of evi_edge_batch (EVI_FLAG_* bits)
 
     @property
     def num_nodes(self) -> int:
@@ -134,7 +135,7 @@ class GraphBatch:
         _lib.check(st, "evi_edge_batch")
         if validate:
             _raise_edge_flags(int(flags.item()))
-        return cls(head32, tail32, qid32, eb, ep, ptr_host)
+        return cls(head32, tail32, qid32, eb, ep, ptr_host, flags=flags)
 
     def edge_ptr_np(self) -> np.ndarray:
         if self.edge_ptr_host is None:

@@ -91,7 +91,10 @@ class RetrievalPipeline:
                              edge_attr=b.edge_attr, labels=None, logits_fwd=out.logits_fwd,
                              logits_bwd=out.logits_bwd)
         res["bfs_dist"] = dist
-        res["flags"] = self.model._flags
+        # one validation word per batch: the segmentation's (cross-graph / out-of-range / unsorted edges) OR the scorer's;
+        # the scorer's accumulator is cleared for the next batch, all in stream order (no host synchronisation)
+        res["flags"] = torch.bitwise_or(self.model._flags, gb.flags) if gb.flags is not None else self.model._flags.clone()
+        self.model._flags.zero_()
         return res
 
     def _bfs(self, gb, b, seeds_global):
@@ -143,8 +146,9 @@ class RetrievalPipeline:
         out = {k: res[k].to("cpu", non_blocking=True) for k in keys}
         torch.cuda.current_stream(dev).synchronize()
         if self.validate:
-            self.model._pending_flags = True
-            self.model.check_flags()
+            word = int(out["flags"].item())
+            if word != 0:
+                self.model.raise_for_flags(word)
         return out
 
     @torch.no_grad()
@@ -215,7 +219,6 @@ class RetrievalPipeline:
         if self.validate:
             word = int(out["flags"].item())
             if word != 0:
-                self.model._flags.zero_()
                 self.model.raise_for_flags(word)
         return out
 
