@@ -322,24 +322,51 @@ class PoolRetriever:
         return key, ht, rel, off, emit_count.max()
 
     def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int, cap: int, out_cap: int):
-        """The smallest keys over the union of every shard's survivors (rows of stride ``cap``, padding = all-ones
-        keys), ``out_cap`` kept per query."""
+        """The ``out_cap`` smallest keys per query over the union of every shard's survivors. Only the valid entries
+        travel: each shard's [Q, cap] rows are compacted to a ragged list (grouped by query), ranks exchange the
+        per-query counts and then one padded all-gather of the compact lists — the exchange volume follows the real
+        candidate counts (a few hundred per query), not world x Q x cap."""
         dev = self.dev
-        valid = lambda s: torch.arange(cap, device=dev).unsqueeze(0) < s["count"].unsqueeze(1)
+        ar = torch.arange(cap, device=dev).unsqueeze(0)
+        flats, counts = [], []
         for s in sels:
-            s["key"] = torch.where(valid(s), s["key"], torch.full_like(s["key"], _EMPTY))
+            valid = ar < s["count"].unsqueeze(1)
+            flats.append({name: s[name][valid] for name in ("key", "ht", "rel")})  # row-major: grouped by query
+            counts.append(s["count"].long())
         if self.world > 1:
-            parts = {}
+            cnt_all = torch.empty((self.world, Q), dtype=torch.long, device=dev)
+            dist.all_gather_into_tensor(cnt_all, counts[0].contiguous(), group=self.group)
+            totals = cnt_all.sum(dim=1).tolist()  # one read-back per slab: sizes of the exchange
+            m = max(max(totals), 1)
+            parts = []
             for name in ("key", "ht", "rel"):
-                t = sels[0][name].contiguous()
-                out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=dev)
-                dist.all_gather_into_tensor(out, t, group=self.group)
-                parts[name] = out
-        else:
-            parts = {name: torch.stack([s[name] for s in sels]) for name in ("key", "ht", "rel")}
-        S = int(parts["key"].shape[0])
-        cat = {name: t.permute(1, 0, 2).reshape(Q * S * cap).contiguous() for name, t in parts.items()}
-        seg_off = torch.arange(Q + 1, dtype=torch.long, device=dev) * (S * cap)
+                t = flats[0][name]
+                buf = torch.zeros(m, dtype=t.dtype, device=dev)
+                buf[: t.numel()] = t
+                out = torch.empty(self.world * m, dtype=t.dtype, device=dev)
+                dist.all_gather_into_tensor(out, buf, group=self.group)
+                parts.append([out[r * m: r * m + totals[r]] for r in range(self.world)])
+            flats = [{"key": parts[0][r], "ht": parts[1][r], "rel": parts[2][r]} for r in range(self.world)]
+            counts = [cnt_all[r] for r in range(self.world)]
+        cnt = torch.stack(counts)                                  # [S, Q]
+        per_q = cnt.sum(dim=0)                                     # union size per query
+        seg_off = torch.zeros(Q + 1, dtype=torch.long, device=dev)
+        seg_off[1:] = torch.cumsum(per_q, 0)
+        before = torch.cumsum(cnt, dim=0) - cnt                    # entries of earlier shards inside the query's segment
+        total = int(seg_off[-1].item())
+        cat = {"key": torch.empty(max(total, 1), dtype=torch.long, device=dev),
+               "ht": torch.empty(max(total, 1), dtype=torch.long, device=dev),
+               "rel": torch.empty(max(total, 1), dtype=torch.int32, device=dev)}
+        qs = torch.arange(Q, device=dev)
+        for r, f in enumerate(flats):
+            n_r = int(f["key"].numel())
+            if n_r == 0:
+                continue
+            qid = torch.repeat_interleave(qs, cnt[r], output_size=n_r)
+            start_r = torch.cumsum(cnt[r], 0) - cnt[r]             # segment starts inside shard r's list
+            dest = seg_off[qid] + before[r][qid] + (torch.arange(n_r, device=dev) - start_r[qid])
+            for name in ("key", "ht", "rel"):
+                cat[name][dest] = f[name]
         return self._select(cat["key"], cat["ht"], cat["rel"], seg_off, Q, out_cap)
 
     def _pack(self, st: _ShardState, sel, Q: int, cap: int) -> types.SimpleNamespace:
