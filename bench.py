@@ -63,7 +63,7 @@ def parse_args():
     ap.add_argument("--no-other-configs", action="store_true",
                     help="skip the compact other_configs array (configs 3 and 5, a few steps each) of the default run")
     ap.add_argument("--precision", default="fast", choices=["fast", "strict"])
-    ap.add_argument("--cwq-questions-per-step", type=int, default=64,
+    ap.add_argument("--cwq-questions-per-step", type=int, default=128,
                     help="config 3: questions of the fixed global batch split over the ranks by cumulative edge count")
     return ap.parse_args()
 

@@ -243,6 +243,8 @@ class PoolRetriever:
         qid = torch.repeat_interleave(torch.arange(Q, device=dev), seed_ptr[1:] - seed_ptr[:-1])
         ok = (seeds >= 0) & (seeds < num_nodes)  # out-of-range sources are ignored (:616-618)
         seed_pairs = torch.where(ok, (qid << 32) | seeds.clamp(min=0), torch.full_like(seeds, _EMPTY)).contiguous()
+        tick = self._tick
+        tick(None)
         while True:
             states = self._traverse(seed_pairs)
             if states is not None:
@@ -253,7 +255,9 @@ class PoolRetriever:
             self.table_capacity = min(self.table_capacity * 4, self.max_table_capacity)
         multi = len(states) > 1 or self.world > 1
         self._last_state = states[0]  # kept for traversal_stats()
+        tick("traverse_s")
         raw = [self._shard_candidates(st, Q) for st in states]
+        tick("candidates_s")
         # Row stride of the fixed-shape [Q, stride] selection arrays: the batch's largest per-query candidate count
         # (power of two), not `cap` — uniform-seed queries keep a few hundred candidates against cap = 20000, and
         # [Q, cap] rows of a 64k-query slab would take tens of GB. Every count fits its row, so the selection is the
@@ -263,14 +267,28 @@ class PoolRetriever:
             dist.all_reduce(most, op=dist.ReduceOp.MAX, group=self.group)
         stride = min(self.cap, _next_pow2(max(int(most.item()), 1)))
         sels = [self._select(key, ht, rel, off, Q, stride) for key, ht, rel, off, _ in raw]
+        tick("select_s")
         if multi:
             n_sh = len(states) * self.world
             out_stride = min(self.cap, n_sh * stride)
             sel = self._merge(sels, Q, stride, out_stride)
             stride = out_stride
+            tick("merge_s")
         else:
             sel = sels[0]
-        return self._pack(states[0], sel, Q, stride)
+        b = self._pack(states[0], sel, Q, stride)
+        tick("pack_s")
+        return b
+
+    def _tick(self, name: Optional[str]) -> None:
+        """profile mode: synchronise and add the time since the previous tick to timings[name]"""
+        if not self.profile:
+            return
+        torch.cuda.synchronize(self.dev)
+        now = time.perf_counter()
+        if name is not None:
+            self.timings[name] = self.timings.get(name, 0.0) + now - self._t_last
+        self._t_last = now
 
     def traversal_stats(self) -> Dict[str, int]:
         """Adjacency entries shard 0 read for the last batch (bandwidth accounting, not on the timed path): both

@@ -133,7 +133,7 @@ def run_group(args, n, group, rank, dev, pool, model, reference):
     rec = {"world": n, "triples": args.triples, "nodes": args.nodes, "queries": args.queries, "slab": args.slab,
            "cap": args.cap, "k": args.k, "shard_triples": shard.num_triples, "table_slots": pr.table_capacity,
            "wall_s": wall, "queries_per_s": args.queries / wall, "extract_ms": stage_ms["extract"],
-           "score_ms": stage_ms["score"], "candidates": cand_total, "exchange_s": pr.timings.get("exchange_s"),
+           "score_ms": stage_ms["score"], "candidates": cand_total, "stage_s": dict(pr.timings) if pr.timings else None,
            "rank0_visited_pairs": stats["visited_pairs"], "rank0_expand_entries": stats["expand_entries"],
            "rank0_candidate_entries": stats["candidate_entries"],
            # 12 B per adjacency entry read (other endpoint i32 + one 8-byte hash probe) — rank 0's shard only
