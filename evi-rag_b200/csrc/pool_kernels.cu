@@ -348,12 +348,13 @@ pool_select_kernel(const unsigned long long* __restrict__ cand_key, const unsign
 //   pack:   edge_index in batch-global node ids, relation ids, global edge ids
 // ---------------------------------------------------------------------------------------------
 __global__ void pool_mark_kernel(PoolTable t, const unsigned long long* __restrict__ sel_ht,
-                                 const int* __restrict__ sel_count, int cap, long long total) {
+                                 const int* __restrict__ sel_count, int cap, long long total, int query_base) {
   const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (i >= total) return;
   const int q = static_cast<int>(i / cap), j = static_cast<int>(i % cap);
   if (j >= sel_count[q]) return;
-  const unsigned long long ht = sel_ht[i], qbits = static_cast<unsigned long long>(q) << 32;
+  // row q of the selection arrays is query (query_base + q) of the batch the visited table was built for
+  const unsigned long long ht = sel_ht[i], qbits = static_cast<unsigned long long>(q + query_base) << 32;
   t.local_id[pool_find(t, qbits | (ht >> 32))] = -2;
   t.local_id[pool_find(t, qbits | (ht & 0xFFFFFFFFull))] = -2;
 }
@@ -361,12 +362,12 @@ __global__ void pool_mark_kernel(PoolTable t, const unsigned long long* __restri
 __global__ void pool_assign_kernel(PoolTable t, const unsigned long long* __restrict__ sel_ht,
                                    const int* __restrict__ sel_count, int cap, long long total,
                                    int* __restrict__ node_count, int* __restrict__ node_global /*[Q, 2 cap]*/,
-                                   unsigned char* __restrict__ node_is_seed) {
+                                   unsigned char* __restrict__ node_is_seed, int query_base) {
   const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (i >= total) return;
   const int q = static_cast<int>(i / cap), j = static_cast<int>(i % cap);
   if (j >= sel_count[q]) return;
-  const unsigned long long ht = sel_ht[i], qbits = static_cast<unsigned long long>(q) << 32;
+  const unsigned long long ht = sel_ht[i], qbits = static_cast<unsigned long long>(q + query_base) << 32;
 #pragma unroll
   for (int side = 0; side < 2; ++side) {
     const unsigned node = static_cast<unsigned>(side == 0 ? (ht >> 32) : (ht & 0xFFFFFFFFull));
@@ -389,7 +390,8 @@ __global__ void pool_pack_kernel(PoolTable t, const unsigned long long* __restri
                                  const long long* __restrict__ node_embedding_table, long long num_edges_out,
                                  long long* __restrict__ edge_index /*[2, E]*/, long long* __restrict__ edge_attr,
                                  long long* __restrict__ edge_global_id, long long* __restrict__ node_global_ids,
-                                 long long* __restrict__ node_embedding_ids, float* __restrict__ topic_one_hot) {
+                                 long long* __restrict__ node_embedding_ids, float* __restrict__ topic_one_hot,
+                                 int query_base) {
   const long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
   if (i >= total) return;
   const int q = static_cast<int>(i / cap), j = static_cast<int>(i % cap);
@@ -405,7 +407,7 @@ __global__ void pool_pack_kernel(PoolTable t, const unsigned long long* __restri
     topic_one_hot[2 * (nb + v) + 1] = seed ? 1.f : 0.f;
   }
   if (j >= sel_count[q]) return;
-  const unsigned long long ht = sel_ht[i], qbits = static_cast<unsigned long long>(q) << 32;
+  const unsigned long long ht = sel_ht[i], qbits = static_cast<unsigned long long>(q + query_base) << 32;
   const long long e = edge_ptr[q] + j;
   edge_index[e] = nb + t.local_id[pool_find(t, qbits | (ht >> 32))];
   edge_index[num_edges_out + e] = nb + t.local_id[pool_find(t, qbits | (ht & 0xFFFFFFFFull))];
@@ -520,8 +522,8 @@ int evi_pool_select(const unsigned long long* cand_key, const unsigned long long
 }
 
 int evi_pool_relabel(const evi_pool_table* table, const unsigned long long* sel_ht, const int* sel_count,
-                     int num_queries, int cap, int* node_count, int* node_global, unsigned char* node_is_seed,
-                     cudaStream_t stream) {
+                     int num_queries, int cap, int query_base, int* node_count, int* node_global,
+                     unsigned char* node_is_seed, cudaStream_t stream) {
   if (num_queries <= 0) return kOk;
   if (!table_ok(table) || sel_ht == nullptr || sel_count == nullptr || cap <= 0 || node_count == nullptr ||
       node_global == nullptr || node_is_seed == nullptr)
@@ -529,14 +531,15 @@ int evi_pool_relabel(const evi_pool_table* table, const unsigned long long* sel_
   const long long total = static_cast<long long>(num_queries) * cap;
   const int grid = static_cast<int>((total + 255) / 256);
   if (cudaMemsetAsync(node_count, 0, sizeof(int) * num_queries, stream) != cudaSuccess) return kErrCuda;
-  pool_mark_kernel<<<grid, 256, 0, stream>>>(as_table(table), sel_ht, sel_count, cap, total);
+  pool_mark_kernel<<<grid, 256, 0, stream>>>(as_table(table), sel_ht, sel_count, cap, total, query_base);
   pool_assign_kernel<<<grid, 256, 0, stream>>>(as_table(table), sel_ht, sel_count, cap, total, node_count, node_global,
-                                               node_is_seed);
+                                               node_is_seed, query_base);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 
 int evi_pool_pack(const evi_pool_table* table, const unsigned long long* sel_key, const unsigned long long* sel_ht,
-                  const int* sel_rel, const int* sel_count, int num_queries, int cap, const long long* edge_ptr,
+                  const int* sel_rel, const int* sel_count, int num_queries, int cap, int query_base,
+                  const long long* edge_ptr,
                   const long long* node_ptr, const int* node_global, const unsigned char* node_is_seed,
                   const long long* node_embedding_table, long long num_edges_out, long long* edge_index,
                   long long* edge_attr, long long* edge_global_id, long long* node_global_ids,
@@ -551,7 +554,7 @@ int evi_pool_pack(const evi_pool_table* table, const unsigned long long* sel_key
   pool_pack_kernel<<<static_cast<int>((total + 255) / 256), 256, 0, stream>>>(
       as_table(table), sel_key, sel_ht, sel_rel, sel_count, cap, total, edge_ptr, node_ptr, node_global, node_is_seed,
       node_embedding_table, num_edges_out, edge_index, edge_attr, edge_global_id, node_global_ids, node_embedding_ids,
-      topic_one_hot);
+      topic_one_hot, query_base);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 

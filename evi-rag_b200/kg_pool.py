@@ -268,8 +268,12 @@ class PoolRetriever:
         stride = min(self.cap, _next_pow2(max(int(most.item()), 1)))
         sels = [self._select(key, ht, rel, off, Q, stride) for key, ht, rel, off, _ in raw]
         tick("select_s")
+        if self.world > 1:
+            b = self._owner_merge_pack(states[0], sels[0], Q, stride)
+            tick("merge_pack_s")
+            return b
         if multi:
-            n_sh = len(states) * self.world
+            n_sh = len(states)
             out_stride = min(self.cap, n_sh * stride)
             sel = self._merge(sels, Q, stride, out_stride)
             stride = out_stride
@@ -339,61 +343,113 @@ class PoolRetriever:
                                          stream), "evi_pool_candidates")
         return key, ht, rel, off, emit_count.max()
 
-    def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int, cap: int, out_cap: int):
-        """The ``out_cap`` smallest keys per query over the union of every shard's survivors. Only the valid entries
-        travel: each shard's [Q, cap] rows are compacted to a ragged list (grouped by query), ranks exchange the
-        per-query counts and then one padded all-gather of the compact lists — the exchange volume follows the real
-        candidate counts (a few hundred per query), not world x Q x cap."""
+    def _compact(self, sel: Dict[str, torch.Tensor], cap: int) -> Dict[str, torch.Tensor]:
+        """The valid entries of [Q, cap] selection rows as flat lists grouped by query."""
+        valid = torch.arange(cap, device=self.dev).unsqueeze(0) < sel["count"].unsqueeze(1)
+        return {name: sel[name][valid] for name in ("key", "ht", "rel")}
+
+    def _union(self, flats: List[Dict[str, torch.Tensor]], cnt: torch.Tensor, nq: int):
+        """Per query the concatenation of every shard's survivors. ``flats[s]`` = shard s's entries grouped by query,
+        ``cnt [S, nq]`` their per-query counts. Returns the ragged union (key, ht, rel) and its offsets [nq + 1]."""
         dev = self.dev
-        ar = torch.arange(cap, device=dev).unsqueeze(0)
-        flats, counts = [], []
-        for s in sels:
-            valid = ar < s["count"].unsqueeze(1)
-            flats.append({name: s[name][valid] for name in ("key", "ht", "rel")})  # row-major: grouped by query
-            counts.append(s["count"].long())
-        if self.world > 1:
-            cnt_all = torch.empty((self.world, Q), dtype=torch.long, device=dev)
-            dist.all_gather_into_tensor(cnt_all, counts[0].contiguous(), group=self.group)
-            totals = cnt_all.sum(dim=1).tolist()  # one read-back per slab: sizes of the exchange
-            m = max(max(totals), 1)
-            parts = []
-            for name in ("key", "ht", "rel"):
-                t = flats[0][name]
-                buf = torch.zeros(m, dtype=t.dtype, device=dev)
-                buf[: t.numel()] = t
-                out = torch.empty(self.world * m, dtype=t.dtype, device=dev)
-                dist.all_gather_into_tensor(out, buf, group=self.group)
-                parts.append([out[r * m: r * m + totals[r]] for r in range(self.world)])
-            flats = [{"key": parts[0][r], "ht": parts[1][r], "rel": parts[2][r]} for r in range(self.world)]
-            counts = [cnt_all[r] for r in range(self.world)]
-        cnt = torch.stack(counts)                                  # [S, Q]
-        per_q = cnt.sum(dim=0)                                     # union size per query
-        seg_off = torch.zeros(Q + 1, dtype=torch.long, device=dev)
-        seg_off[1:] = torch.cumsum(per_q, 0)
-        before = torch.cumsum(cnt, dim=0) - cnt                    # entries of earlier shards inside the query's segment
-        total = int(seg_off[-1].item())
+        seg_off = torch.zeros(nq + 1, dtype=torch.long, device=dev)
+        seg_off[1:] = torch.cumsum(cnt.sum(dim=0), 0)
+        before = torch.cumsum(cnt, dim=0) - cnt  # entries of earlier shards inside the query's segment
+        total = sum(int(f["key"].numel()) for f in flats)
         cat = {"key": torch.empty(max(total, 1), dtype=torch.long, device=dev),
                "ht": torch.empty(max(total, 1), dtype=torch.long, device=dev),
                "rel": torch.empty(max(total, 1), dtype=torch.int32, device=dev)}
-        qs = torch.arange(Q, device=dev)
+        qs = torch.arange(nq, device=dev)
         for r, f in enumerate(flats):
             n_r = int(f["key"].numel())
             if n_r == 0:
                 continue
             qid = torch.repeat_interleave(qs, cnt[r], output_size=n_r)
-            start_r = torch.cumsum(cnt[r], 0) - cnt[r]             # segment starts inside shard r's list
+            start_r = torch.cumsum(cnt[r], 0) - cnt[r]  # segment starts inside shard r's list
             dest = seg_off[qid] + before[r][qid] + (torch.arange(n_r, device=dev) - start_r[qid])
             for name in ("key", "ht", "rel"):
                 cat[name][dest] = f[name]
+        return cat, seg_off
+
+    def _merge(self, sels: List[Dict[str, torch.Tensor]], Q: int, cap: int, out_cap: int):
+        """Several shards on one device: the ``out_cap`` smallest keys per query over the union of their survivors."""
+        flats = [self._compact(s, cap) for s in sels]
+        cnt = torch.stack([s["count"].long() for s in sels])
+        cat, seg_off = self._union(flats, cnt, Q)
         return self._select(cat["key"], cat["ht"], cat["rel"], seg_off, Q, out_cap)
 
-    def _pack(self, st: _ShardState, sel, Q: int, cap: int) -> types.SimpleNamespace:
+    def _sub_batch_cuts(self, ep: List[int], Q: int) -> List[int]:
+        """Query indices where the scoring sub-batches start: runs of whole queries of about ``score_edges_per_batch``
+        candidate edges, cut on the WHOLE query list whatever the world size (a query is always scored inside the same
+        sub-batch, so N-rank scores equal 1-rank scores bit for bit: the batch centre depends on the batch)."""
+        cuts = [0]
+        while cuts[-1] < Q:
+            a = cuts[-1]
+            c = a + 1
+            while c < Q and ep[c + 1] - ep[a] <= self.score_edges_per_batch:
+                c += 1
+            cuts.append(c)
+        return cuts
+
+    def _owner_merge_pack(self, st: _ShardState, sel: Dict[str, torch.Tensor], Q: int, cap: int) -> types.SimpleNamespace:
+        """One shard per rank: every rank becomes the OWNER of a contiguous run of the batch's queries (whole scoring
+        sub-batches, balanced by candidate edges) and only merges, relabels, packs and scores those. The per-query
+        survivor counts of every shard are all-gathered first — keys are unique per query, so the merged count is
+        min(sum of counts, cap) and every rank can lay out the sub-batches without doing the merge — then ONE uneven
+        all-to-all per array moves each shard's survivors to their owners."""
+        dev, W = self.dev, self.world
+        flat = self._compact(sel, cap)
+        counts = sel["count"].long().contiguous()
+        cnt_all = torch.empty((W, Q), dtype=torch.long, device=dev)
+        dist.all_gather_into_tensor(cnt_all, counts, group=self.group)
+        final = cnt_all.sum(dim=0).clamp(max=self.cap)
+        ep = [0] + torch.cumsum(final, 0).tolist()  # read-back 1 of 2 per slab: the sub-batch layout is a host decision
+        cuts_all = self._sub_batch_cuts(ep, Q)
+        sparts = partition_by_edges([ep[c] - ep[a] for a, c in zip(cuts_all[:-1], cuts_all[1:])], W)
+        parts = [(cuts_all[s0], cuts_all[s1]) for s0, s1 in sparts]
+        s0, s1 = sparts[self.rank]
+        q0, q1 = parts[self.rank]
+        nq = q1 - q0
+        # split sizes: what I send to every owner, what every shard sends me
+        csum = torch.zeros(Q + 1, dtype=torch.long, device=dev)
+        csum[1:] = torch.cumsum(counts, 0)
+        bounds = torch.tensor([p[0] for p in parts] + [parts[-1][1]], dtype=torch.long, device=dev)
+        sizes = torch.cat([csum[bounds], cnt_all[:, q0:q1].sum(dim=1)]).tolist()  # read-back 2 of 2
+        send = [sizes[i + 1] - sizes[i] for i in range(W)]
+        recv = [int(x) for x in sizes[W + 1:]]
+        got = {}
+        for name in ("key", "ht", "rel"):
+            out = torch.empty(max(sum(recv), 1), dtype=flat[name].dtype, device=dev)
+            dist.all_to_all_single(out[: sum(recv)], flat[name].contiguous(), output_split_sizes=recv,
+                                   input_split_sizes=send, group=self.group)
+            got[name] = out
+        offs = [0]
+        for x in recv:
+            offs.append(offs[-1] + x)
+        flats = [{name: got[name][offs[r]: offs[r + 1]] for name in got} for r in range(W)]
+        b = types.SimpleNamespace()
+        if nq > 0:
+            cat, seg_off = self._union(flats, cnt_all[:, q0:q1].contiguous(), nq)
+            most = int(final[q0:q1].max().item()) if nq else 1
+            stride = min(self.cap, _next_pow2(max(most, 1)))
+            merged = self._select(cat["key"], cat["ht"], cat["rel"], seg_off, nq, stride)
+            b = self._pack(st, merged, nq, stride, query_base=q0)
+        else:
+            z = lambda *shape, dt=torch.long: torch.zeros(shape, dtype=dt, device=dev)
+            b.edge_index, b.edge_attr, b.edge_global_id = z(2, 0), z(0), z(0)
+            b.node_global_ids, b.node_embedding_ids, b.topic_one_hot = z(0), z(0), z(0, 2, dt=torch.float32)
+            b.ptr, b.edge_ptr, b.num_graphs = z(1), z(1), 0
+        b.owner_parts, b.owner_range, b.num_queries_total = parts, (q0, q1), Q
+        b.owner_cuts = [c - q0 for c in cuts_all[s0:s1 + 1]] if nq > 0 else [0]
+        return b
+
+    def _pack(self, st: _ShardState, sel, Q: int, cap: int, query_base: int = 0) -> types.SimpleNamespace:
         L, dev, stream = self.L, self.dev, _lib.stream_handle()
         node_count = torch.empty(Q, dtype=torch.int32, device=dev)
         node_global = torch.empty((Q, 2 * cap), dtype=torch.int32, device=dev)
         node_is_seed = torch.empty((Q, 2 * cap), dtype=torch.uint8, device=dev)
         _lib.check(L.evi_pool_relabel(C.byref(st.table), sel["ht"].data_ptr(), sel["count"].data_ptr(), Q, cap,
-                                      node_count.data_ptr(), node_global.data_ptr(), node_is_seed.data_ptr(), stream),
+                                      int(query_base), node_count.data_ptr(), node_global.data_ptr(), node_is_seed.data_ptr(), stream),
                    "evi_pool_relabel")
         edge_ptr = torch.zeros(Q + 1, dtype=torch.long, device=dev)
         edge_ptr[1:] = torch.cumsum(sel["count"].long(), 0)
@@ -409,7 +465,7 @@ class PoolRetriever:
         b.node_embedding_ids = torch.zeros(max(N, 1), dtype=torch.long, device=dev)
         b.topic_one_hot = torch.zeros((max(N, 1), 2), dtype=torch.float32, device=dev)
         _lib.check(L.evi_pool_pack(C.byref(st.table), sel["key"].data_ptr(), sel["ht"].data_ptr(), sel["rel"].data_ptr(),
-                                   sel["count"].data_ptr(), Q, cap, edge_ptr.data_ptr(), node_ptr.data_ptr(),
+                                   sel["count"].data_ptr(), Q, cap, int(query_base), edge_ptr.data_ptr(), node_ptr.data_ptr(),
                                    node_global.data_ptr(), node_is_seed.data_ptr(), _lib.ptr(self.node_embedding_ids),
                                    max(E, 1), b.edge_index.data_ptr(), b.edge_attr.data_ptr(), b.edge_global_id.data_ptr(),
                                    b.node_global_ids.data_ptr(), b.node_embedding_ids.data_ptr(),
@@ -439,36 +495,24 @@ class PoolRetriever:
             return self._score_on_device(b, question_emb)
 
     def _score_on_device(self, b: types.SimpleNamespace, question_emb: torch.Tensor) -> Dict[str, torch.Tensor]:
-        """Bidirectional scores of every candidate and the per-query top-k as global edge ids. The rank's queries are
-        scored in sub-batches of about ``score_edges_per_batch`` candidate edges."""
+        """Bidirectional scores of every candidate and the per-query top-k as global edge ids, in sub-batches of about
+        ``score_edges_per_batch`` candidate edges. With one shard per rank ``b`` holds the rank's own query range
+        (``_owner_merge_pack``): each rank scores its queries and the ``[Q, k]`` results are gathered on every rank.
+        ``question_emb`` always covers the whole batch."""
         dev, k = self.dev, self.top_k
-        Q = b.num_graphs
         question_emb = question_emb.to(device=dev, dtype=torch.float32)
-        ep, npt = b.edge_ptr.tolist(), b.ptr.tolist()  # one read-back per slab: the sub-batch cuts are host decisions
-        # Sub-batch cuts are made on the whole query list, whatever the world size, and a rank takes a contiguous run
-        # of whole sub-batches (balanced by edges): a query is always scored inside the same sub-batch, so the N-rank
-        # scores equal the 1-rank scores bit for bit (the batch centre of the structure context depends on the batch).
-        cuts_all = [0]
-        while cuts_all[-1] < Q:
-            a = cuts_all[-1]
-            c = a + 1
-            while c < Q and ep[c + 1] - ep[a] <= self.score_edges_per_batch:
-                c += 1
-            cuts_all.append(c)
-        if self.world > 1:  # results are gathered on every rank
-            sub_edges = [ep[c] - ep[a] for a, c in zip(cuts_all[:-1], cuts_all[1:])]
-            sparts = partition_by_edges(sub_edges, self.world)
-            parts = [(cuts_all[s0], cuts_all[s1]) for s0, s1 in sparts]
-            s0, s1 = sparts[self.rank]
-            cuts = cuts_all[s0:s1 + 1]
-            q0, q1 = parts[self.rank]
+        nq = b.num_graphs
+        ep, npt = b.edge_ptr.tolist(), b.ptr.tolist()  # one read-back per slab: sub-batch slicing is a host decision
+        owner = getattr(b, "owner_range", None)
+        if owner is not None:
+            q0, cuts = owner[0], b.owner_cuts
+            question_emb = question_emb[q0:owner[1]]
         else:
-            parts, q0, q1, cuts = [(0, Q)], 0, Q, cuts_all
-        nq = q1 - q0
+            cuts = self._sub_batch_cuts(ep, nq)
         edge_id = torch.full((nq, k), -1, dtype=torch.long, device=dev)
         score = torch.full((nq, k), float("-inf"), device=dev)
         count = torch.zeros(nq, dtype=torch.int32, device=dev)
-        logits = torch.empty(ep[q1] - ep[q0], dtype=torch.float32, device=dev)
+        logits = torch.empty(ep[nq], dtype=torch.float32, device=dev)
         ar_k = torch.arange(k, device=dev).unsqueeze(0)
         for a, c in zip(cuts[:-1], cuts[1:]):
             if ep[c] == ep[a]:
@@ -478,12 +522,12 @@ class PoolRetriever:
             top = segmented_topk(out.logits, sb.edge_ptr, k)
             gidx = (top.indices.long() + sb.edge_ptr[:-1].unsqueeze(1)).clamp(min=0, max=sb.edge_global_id.numel() - 1)
             valid = ar_k < top.counts.unsqueeze(1)
-            edge_id[a - q0:c - q0] = torch.where(valid, sb.edge_global_id[gidx], torch.full_like(gidx, -1))
-            score[a - q0:c - q0], count[a - q0:c - q0] = top.values, top.counts
-            logits[ep[a] - ep[q0]:ep[c] - ep[q0]] = out.logits
+            edge_id[a:c] = torch.where(valid, sb.edge_global_id[gidx], torch.full_like(gidx, -1))
+            score[a:c], count[a:c] = top.values, top.counts
+            logits[ep[a]:ep[c]] = out.logits
         res = {"edge_id": edge_id, "score": score, "count": count}
-        if self.world > 1:
-            res = gather_topk(res, nq, group=self.group, counts=[b_ - a_ for a_, b_ in parts])
+        if owner is not None:
+            res = gather_topk(res, nq, group=self.group, counts=[q1_ - q0_ for q0_, q1_ in b.owner_parts])
         res["logits_local"] = logits
         return res
 

@@ -124,8 +124,8 @@ PROTOTYPES = {
     "evi_pool_candidates": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, _i, _i, _i] +
                             [_vp] * 8 + [_i, _vp]),
     "evi_pool_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i] + [_vp] * 8 + [_vp]),
-    "evi_pool_relabel": (_i, [C.POINTER(PoolTable), _vp, _vp, _i, _i, _vp, _vp, _vp, _vp]),
-    "evi_pool_pack": (_i, [C.POINTER(PoolTable)] + [_vp] * 4 + [_i, _i] + [_vp] * 5 + [_ll] + [_vp] * 6 + [_vp]),
+    "evi_pool_relabel": (_i, [C.POINTER(PoolTable), _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "evi_pool_pack": (_i, [C.POINTER(PoolTable)] + [_vp] * 4 + [_i, _i, _i] + [_vp] * 5 + [_ll] + [_vp] * 6 + [_vp]),
 }
 
 _lib: Optional[C.CDLL] = None

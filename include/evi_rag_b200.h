@@ -442,14 +442,17 @@ int evi_pool_select(const unsigned long long* cand_key, const unsigned long long
                     unsigned long long* stage_ht, int* stage_rel, unsigned long long* sort_ws,
                     unsigned long long* out_key, unsigned long long* out_ht, int* out_rel, int* out_count,
                     cudaStream_t stream);
-/* local node ids of the selected subgraphs: node_count [Q], node_global / node_is_seed [Q, 2 cap] */
+/* local node ids of the selected subgraphs: node_count [Q], node_global / node_is_seed [Q, 2 cap]. Row q of the
+ * selection arrays is query (query_base + q) of the batch the visited table holds (a rank that owns a query range of
+ * the batch passes the range's first query) */
 int evi_pool_relabel(const evi_pool_table* table, const unsigned long long* sel_ht, const int* sel_count,
-                     int num_queries, int cap, int* node_count, int* node_global, unsigned char* node_is_seed,
-                     cudaStream_t stream);
+                     int num_queries, int cap, int query_base, int* node_count, int* node_global,
+                     unsigned char* node_is_seed, cudaStream_t stream);
 /* the PyG-style batch the scorer takes (edge_index in batch-global node ids, one_hot(is_seed) topic features) */
 int evi_pool_pack(const evi_pool_table* table, const unsigned long long* sel_key, const unsigned long long* sel_ht,
-                  const int* sel_rel, const int* sel_count, int num_queries, int cap, const long long* edge_ptr,
-                  const long long* node_ptr, const int* node_global, const unsigned char* node_is_seed,
+                  const int* sel_rel, const int* sel_count, int num_queries, int cap, int query_base,
+                  const long long* edge_ptr, const long long* node_ptr, const int* node_global,
+                  const unsigned char* node_is_seed,
                   const long long* node_embedding_table, long long num_edges_out, long long* edge_index,
                   long long* edge_attr, long long* edge_global_id, long long* node_global_ids,
                   long long* node_embedding_ids, float* topic_one_hot, cudaStream_t stream);

@@ -71,11 +71,16 @@ def slab_queries(args, slab_idx, n, dev):
 def run_group(args, n, group, rank, dev, pool, model, reference):
     """Stream the query batch through an n-shard PoolRetriever (ranks 0..n-1). Returns rank 0's record."""
     h, r, t, emb = pool
-    lo, hi = head_ranges(h, args.nodes, n)[rank]
-    mine = (h >= lo) & (h < hi)
-    eid = torch.nonzero(mine).view(-1)
+    if args.partition == "head":  # contiguous head-node ranges with ~E / n triples each (SURVEY.md §8e)
+        lo, hi = head_ranges(h, args.nodes, n)[rank]
+        eid = torch.nonzero((h >= lo) & (h < hi)).view(-1)
+    else:
+        # contiguous edge-id ranges: every shard holds 1/n of every node's row, so a hub that many queries visit costs
+        # every shard the same (head ranges give equal triple counts but unequal scanning work: the shard that owns
+        # the hubs scans their rows for every query that reaches them)
+        per = (args.triples + n - 1) // n
+        eid = torch.arange(rank * per, min(args.triples, (rank + 1) * per), device=dev)
     shard = TriplePoolShard.from_triples(h[eid], r[eid], t[eid], eid, args.nodes, dev)
-    del mine
     # table sized for a whole slab up front (the retriever would otherwise grow it x4 and repeat the first slabs)
     slots = 1 << 22
     while slots < 4 * args.pairs_per_query * args.slab:
@@ -131,7 +136,7 @@ def run_group(args, n, group, rank, dev, pool, model, reference):
     entries = stats["expand_entries"] + stats["candidate_entries"]
     trav_s = stage_ms["extract"] * 1e-3
     rec = {"world": n, "triples": args.triples, "nodes": args.nodes, "queries": args.queries, "slab": args.slab,
-           "cap": args.cap, "k": args.k, "shard_triples": shard.num_triples, "table_slots": pr.table_capacity,
+           "partition": args.partition, "cap": args.cap, "k": args.k, "shard_triples": shard.num_triples, "table_slots": pr.table_capacity,
            "wall_s": wall, "queries_per_s": args.queries / wall, "extract_ms": stage_ms["extract"],
            "score_ms": stage_ms["score"], "candidates": cand_total, "stage_s": dict(pr.timings) if pr.timings else None,
            "rank0_visited_pairs": stats["visited_pairs"], "rank0_expand_entries": stats["expand_entries"],
@@ -139,8 +144,11 @@ def run_group(args, n, group, rank, dev, pool, model, reference):
            # 12 B per adjacency entry read (other endpoint i32 + one 8-byte hash probe) — rank 0's shard only
            "rank0_traversal_GBps": entries * 12 / trav_s / 1e9 if trav_s > 0 else None}
     if reference is not None:
-        rec["parity_candidates_equal"] = bool(torch.equal(first["cand"], reference["cand"]) and
-                                              torch.equal(first["cand_ptr"], reference["cand_ptr"]))
+        # with N > 1 rank 0 holds the candidates of the query range it owns: a prefix of the batch
+        n_e, n_p = first["cand"].numel(), first["cand_ptr"].numel()
+        rec["parity_candidates_equal"] = bool(torch.equal(first["cand"], reference["cand"][:n_e]) and
+                                              torch.equal(first["cand_ptr"], reference["cand_ptr"][:n_p]))
+        rec["parity_candidate_queries_checked"] = int(n_p - 1)
         rec["parity_edge_ids_equal"] = bool(torch.equal(first["edge_id"], reference["edge_id"]) and
                                             torch.equal(first["count"], reference["count"]))
         fin = torch.isfinite(reference["score"])
@@ -163,6 +171,9 @@ def main():
     ap.add_argument("--num-sms", type=int, default=148)
     ap.add_argument("--worlds", default="1,2,4,8")
     ap.add_argument("--profile-exchange", action="store_true")
+    ap.add_argument("--partition", default="edge", choices=["edge", "head"],
+                    help="how the pool is split over the ranks: contiguous edge-id ranges (balanced scanning work) or "
+                         "contiguous head-node ranges")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
