@@ -88,7 +88,8 @@ class _DDEConfig(nn.Module):
 
 
 class Retriever(nn.Module):
-    """Retriever with the reference interface; forward is eval-only (no autograd)."""
+    """Retriever with the reference interface. ``eval()`` / ``no_grad`` runs the fused inference kernels; in training
+    mode with autograd enabled ``forward`` builds the reference's graph with tensor-core contractions (training.py)."""
 
     def __init__(
         self,
@@ -343,13 +344,17 @@ class Retriever(nn.Module):
         )
         _lib.check(st, "evi_project_split")
 
-    @torch.no_grad()
     def _forward_impl(self, batch: Any, *, return_features: bool):
-        if self.training and torch.is_grad_enabled():
-            raise NotImplementedError(
-                "evi_rag_b200.Retriever implements the inference path; train with the reference module "
-                "(identical state_dict) and load the checkpoint here."
-            )
+        if self.training:
+            # training_step (retriever_module.py:290-334): the reference's per-edge formulation under autograd, every
+            # contraction (forward and backward) on the tcgen05 GEMM over [hi | lo] pairs — evi_rag_b200/training.py
+            from .training import forward_train
+
+            return forward_train(self, batch, return_features)
+        with torch.no_grad():
+            return self._forward_eval(batch, return_features=return_features)
+
+    def _forward_eval(self, batch: Any, *, return_features: bool):
         edge_index = getattr(batch, "edge_index", None)
         if edge_index is None:
             raise ValueError("Batch missing edge_index required for scoring.")

@@ -110,8 +110,9 @@ def _lin(x, sd, name):
     return F.linear(x, sd[f"{name}.weight"], sd[f"{name}.bias"])
 
 
-def _score_direction(sd, q, h, r, t, s20, want_features: bool):
-    """``_score_edges`` + ``_encode_structure`` (retriever.py:453-495)."""
+def _score_direction(sd, q, h, r, t, s20, want_features: bool, dropout_p: float = 0.0):
+    """``_score_edges`` + ``_encode_structure`` (retriever.py:453-495). ``dropout_p`` > 0: the training-mode
+    ``nn.Dropout`` of ``state_net`` (retriever.py:175-181), drawn from the torch generator of the tensors' device."""
     r_ctx = r * torch.sigmoid(_lin(q, sd, "q_gate.0")) + torch.tanh(_lin(q, sd, "q_bias.0"))
     sc = F.gelu(
         F.layer_norm(_lin(s20, sd, "struct_proj.0"), (sd["struct_proj.1.weight"].numel(),),
@@ -124,6 +125,8 @@ def _score_direction(sd, q, h, r, t, s20, want_features: bool):
     comb = torch.cat([iv, sc, err, dist], dim=-1)
     z = _lin(comb, sd, "state_net.0")
     g = F.gelu(F.layer_norm(z, (z.size(-1),), sd["state_net.1.weight"], sd["state_net.1.bias"], LN_EPS))
+    if dropout_p > 0.0:
+        g = F.dropout(g, p=dropout_p, training=True)
     feat = _lin(g, sd, "state_net.4")
     logit = _lin(feat, sd, "score_head").squeeze(-1)
     return logit, (feat if want_features else None)
@@ -895,3 +898,49 @@ def hide_seek_bias(edge_index: torch.Tensor, like: torch.Tensor, *, p_near: floa
     drop = torch.rand_like(drop_prob) < drop_prob
     values = torch.where(near, like.new_tensor(bias_near), like.new_tensor(bias_far))
     return torch.where(drop, values, like.new_zeros(drop_prob.shape))
+
+
+# ----------------------------------------------------------------------------------------------
+# (f) rank 4: the training-mode forward (src/models/components/retriever.py:195-289 with self.training)
+# ----------------------------------------------------------------------------------------------
+def retriever_train_forward(sd: Dict[str, torch.Tensor], *, edge_index, ptr, question_emb, node_embeddings,
+                            node_embedding_ids, edge_embeddings, topic_one_hot, direction_mode: str = "bidirectional",
+                            num_rounds: int = 2, num_reverse_rounds: int = 2, dropout_p: float = 0.1,
+                            hide_seek: Optional[Dict] = None) -> OracleOutput:
+    """The reference's forward under autograd (``sd`` holds the parameters, some requiring grad), on the device of
+    its tensors, fp32. Dropout (forward direction first, then backward) and the hide-and-seek draw consume the torch
+    generator in the reference's order, so a seeded run reproduces the reference's training logits. ``hide_seek`` =
+    keyword arguments of ``hide_seek_bias`` (an enabled hide_seek_cfg), or None."""
+    dev = sd["score_head.weight"].device
+    ei = edge_index.to(dev).long()
+    head, tail = ei[0], ei[1]
+    eb, _ = compute_edge_batch(edge_index.cpu().numpy(), ptr.cpu().numpy())
+    query_ids = torch.from_numpy(eb).to(dev)
+    f32 = lambda x: x.to(device=dev, dtype=torch.float32)
+    q_proj = torch.tanh(_lin(f32(question_emb), sd, "query_proj.network.0"))
+    node_repr = torch.tanh(_lin(f32(node_embeddings), sd, "entity_proj.network.0"))
+    non_text = torch.tanh(_lin(sd["non_text_entity_emb.weight"], sd, "entity_proj.network.0"))[0]
+    mask = node_embedding_ids.to(dev).long() == 0
+    node_repr = torch.where(mask.unsqueeze(-1), non_text.unsqueeze(0), node_repr)
+    with torch.no_grad():
+        ns = dde_node_features(topic_one_hot.cpu(), edge_index.cpu().long(), num_rounds, num_reverse_rounds).to(dev)
+    q = q_proj[query_ids]
+    h, t = node_repr[head], node_repr[tail]
+    r = torch.tanh(_lin(f32(edge_embeddings), sd, "relation_proj.network.0"))
+    s_f, s_b = torch.cat([ns[head], ns[tail]], dim=-1), torch.cat([ns[tail], ns[head]], dim=-1)
+    lf = lb = None
+    if direction_mode in ("forward", "bidirectional"):
+        lf, _ = _score_direction(sd, q, h, r, t, s_f, False, dropout_p)
+    if direction_mode in ("backward", "bidirectional"):
+        lb, _ = _score_direction(sd, q, t, r, h, s_b, False, dropout_p)
+    if hide_seek is not None:
+        bias = hide_seek_bias(ei, lf if lf is not None else lb, **hide_seek)
+        if bias is not None:
+            lf = lf + bias if lf is not None else None
+            lb = lb + bias if lb is not None else None
+    if direction_mode == "bidirectional":
+        st = torch.stack([lf, lb], dim=0)
+        lo = (torch.softmax(st, dim=0) * st).sum(dim=0)
+    else:
+        lo = lf if lf is not None else lb
+    return OracleOutput(lo, query_ids, lf, lb, None)

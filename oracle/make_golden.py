@@ -499,6 +499,50 @@ def golden_hide_seek(Retriever):
     print("hide_seek ok", float((bias_qa != 0).float().mean()), float((bias_mask != 0).float().mean()))
 
 
+TRAIN_SEED = 77
+
+
+def training_loss(out, n_edges: int):
+    """A fixed, non-symmetric scalar of the three logit vectors (numpy PCG64 coefficients), so every parameter gets a
+    gradient through both directions and the combine."""
+    rng = np.random.default_rng(2024)
+    c = [torch.from_numpy(rng.standard_normal(n_edges).astype(np.float32)) for _ in range(3)]
+    dev = out.logits.device
+    return (out.logits * c[0].to(dev)).sum() + 0.5 * (out.logits_fwd * c[1].to(dev)).sum() + \
+        0.25 * (out.logits_bwd * c[2].to(dev)).sum()
+
+
+def golden_training(Retriever):
+    """(f) rank 4: the reference in training mode on the CPU. Case `p0`: dropout 0, no hide-and-seek -> logits and the
+    gradient of `training_loss` for every parameter. Case `drop`: dropout 0.1 + hide-and-seek, CPU generator seeded
+    with TRAIN_SEED -> the same (pins the order in which the forward consumes the generator)."""
+    dim = 64
+    qb, ent, rel = small_batch(16, dim, num_questions=3, median_edges=90)
+    sd = make_state_dict(16, dim, dim, 2, 2, trained_like=True)
+    store = dict(edge_index=qb.edge_index, ptr=qb.ptr, edge_attr=qb.edge_attr, node_embedding_ids=qb.node_embedding_ids,
+                 topic_one_hot=qb.topic_one_hot, question_emb=qb.question_emb,
+                 entity_rows=ent[qb.node_embedding_ids].astype(np.float32), relation_table=rel,
+                 q_local_indices=qb.q_local_indices, a_local_indices=qb.a_local_indices,
+                 meta=np.array([dim, 16, TRAIN_SEED]))
+    for tag, p_drop, hs in (("p0", 0.0, None), ("drop", 0.1, dict(HIDE_SEEK_CFG))):
+        m = Retriever(emb_dim=dim, hidden_dim=dim, dropout_p=p_drop, hide_seek_cfg=hs).train()
+        m.load_state_dict(sd, strict=True)
+        batch = as_ref_batch(qb, ent, rel, with_edge_batch=False)
+        batch.q_local_indices = torch.from_numpy(qb.q_local_indices)
+        batch.a_local_indices = torch.from_numpy(qb.a_local_indices)
+        batch.num_nodes = qb.num_nodes
+        torch.manual_seed(TRAIN_SEED)
+        out = m(batch)
+        training_loss(out, qb.num_edges).backward()
+        store[f"{tag}.logits"] = out.logits.detach().numpy()
+        store[f"{tag}.logits_fwd"] = out.logits_fwd.detach().numpy()
+        store[f"{tag}.logits_bwd"] = out.logits_bwd.detach().numpy()
+        for name, prm in m.named_parameters():
+            store[f"{tag}.grad.{name}"] = (prm.grad if prm.grad is not None else torch.zeros_like(prm)).numpy()
+    np.savez_compressed(os.path.join(GOLDEN, "training_d64.npz"), **store)
+    print("training ok", {k: float(np.abs(v).max()) for k, v in store.items() if k.startswith("p0.grad.state_net.0")})
+
+
 def main():
     os.makedirs(GOLDEN, exist_ok=True)
     Retriever, ref_ceb, brp, kind = load_reference()
@@ -511,6 +555,7 @@ def main():
     golden_writer()
     golden_loss()
     golden_hide_seek(Retriever)
+    golden_training(Retriever)
     with open(os.path.join(GOLDEN, "PROVENANCE.txt"), "w", encoding="utf-8") as f:
         f.write(
             "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"

@@ -248,3 +248,45 @@ def test_hide_seek_bias_matches_reference(golden_dir):
     assert set(np.unique(g["bias_qa"]).tolist()) == {bias_near, bias_far, 0.0}
     assert orc.hide_seek_bias(ei, like, edge_is_near=g["edge_is_near"], p_near=0.0, p_far=0.0, bias_near=-1.0,
                               bias_far=-1.0) is None
+
+
+def _training_case(golden_dir):
+    import types
+
+    g = np.load(os.path.join(golden_dir, "training_d64.npz"))
+    dim, seed, rng_seed = [int(x) for x in g["meta"]]
+    t = torch.from_numpy
+    inputs = dict(edge_index=t(g["edge_index"]), ptr=t(g["ptr"]), question_emb=t(g["question_emb"]),
+                  node_embeddings=t(g["entity_rows"]), node_embedding_ids=t(g["node_embedding_ids"]),
+                  edge_embeddings=t(g["relation_table"][g["edge_attr"]]), topic_one_hot=t(g["topic_one_hot"]))
+    hs = dict(p_near=0.6, p_far=0.15, bias_near=-2.5, bias_far=-0.75, num_nodes=int(g["ptr"][-1]),
+              q_local_indices=g["q_local_indices"], a_local_indices=g["a_local_indices"])
+    return g, dim, seed, rng_seed, inputs, hs
+
+
+def training_loss(out, n_edges):
+    rng = np.random.default_rng(2024)  # oracle/make_golden.py::training_loss
+    c = [torch.from_numpy(rng.standard_normal(n_edges).astype(np.float32)).to(out.logits.device) for _ in range(3)]
+    return (out.logits * c[0]).sum() + 0.5 * (out.logits_fwd * c[1]).sum() + 0.25 * (out.logits_bwd * c[2]).sum()
+
+
+@pytest.mark.parametrize("tag", ["p0", "drop"])
+def test_training_forward_and_gradients_match_reference(golden_dir, tag):
+    """(f) rank 4: the oracle's training-mode forward under autograd against the reference in train() mode on the CPU:
+    logits and every parameter's gradient; the dropout + hide-and-seek case pins the generator consumption order."""
+    g, dim, seed, rng_seed, inputs, hs = _training_case(golden_dir)
+    sd = {k: (v.clone().requires_grad_(True) if v.is_floating_point() else v)
+          for k, v in make_state_dict(seed, dim, dim, 2, 2, trained_like=True).items()}
+    torch.manual_seed(rng_seed)
+    out = orc.retriever_train_forward(sd, **inputs, dropout_p=0.0 if tag == "p0" else 0.1,
+                                      hide_seek=None if tag == "p0" else hs)
+    for name in ("logits", "logits_fwd", "logits_bwd"):
+        ref = g[f"{tag}.{name}"]
+        assert np.abs(getattr(out, name).detach().numpy() - ref).max() <= 2e-5 * max(1.0, np.abs(ref).max()), name
+    training_loss(out, inputs["edge_index"].shape[1]).backward()
+    for k, v in sd.items():
+        if not v.is_floating_point():
+            continue
+        ref = g[f"{tag}.grad.{k}"]
+        got = v.grad.numpy() if v.grad is not None else np.zeros_like(ref)
+        assert np.abs(got - ref).max() <= 2e-4 * max(1e-3, np.abs(ref).max()), (k, np.abs(got - ref).max(), np.abs(ref).max())
