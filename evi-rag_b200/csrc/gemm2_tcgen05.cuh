@@ -238,6 +238,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         // fp16 rows: sub-tiles 2i and 2i+1 fill the two 64-byte halves of one staging line, one store per 32 x 64 box
         uint8_t* my_stage = epi_stage + quarter * 2 * gemm::EPI_STAGE_BYTES;
         constexpr bool kQuant = gemm::epi_is_quant<Epi>::value;
+        constexpr bool kHiLo = gemm::epi_is_hilo<Epi>::value;  // both staging buffers per box: hi rows and lo rows
         float q_inv = 0.f;
         if constexpr (kQuant) {
           // first pass over this thread's accumulator row of the tile: max |acc| -> scale of the (row, tile) block
@@ -261,9 +262,13 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
         for (int c = 0; c < BN / 32; ++c) {
           uint32_t r[32];
           tmem_ld_32x32(taddr + static_cast<uint32_t>(c * 32), r);
-          uint8_t* buf = my_stage + ((c >> 1) & 1) * gemm::EPI_STAGE_BYTES;
+          uint8_t* buf = my_stage + (kHiLo ? 0 : ((c >> 1) & 1)) * gemm::EPI_STAGE_BYTES;
           if ((c & 1) == 0) {
-            if (lane == 0) bulk_wait_group_read<1>();  // the store issued two boxes ago has left `buf`
+            // the store issued two boxes ago has left `buf` (hi / lo: the previous box's two stores have left both)
+            if (lane == 0) {
+              if constexpr (kHiLo) bulk_wait_group_read<0>();
+              else bulk_wait_group_read<1>();
+            }
             __syncwarp();
           }
           tmem_ld_wait();
@@ -292,12 +297,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__
               w.w = Out::pack2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]));
             }
             *reinterpret_cast<uint4*>(dst + (((unit0 + j) ^ (lane & 7)) << 4)) = w;
+            if constexpr (kHiLo) {  // residual half into the second staging buffer, same swizzled position
+              using Out = Op16<(Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt)>;
+              const float2 h0 = Out::unpack2(w.x), h1 = Out::unpack2(w.y), h2 = Out::unpack2(w.z), h3 = Out::unpack2(w.w);
+              uint4 l;
+              l.x = Out::pack2(__uint_as_float(r[8 * j + 0]) - h0.x, __uint_as_float(r[8 * j + 1]) - h0.y);
+              l.y = Out::pack2(__uint_as_float(r[8 * j + 2]) - h1.x, __uint_as_float(r[8 * j + 3]) - h1.y);
+              l.z = Out::pack2(__uint_as_float(r[8 * j + 4]) - h2.x, __uint_as_float(r[8 * j + 5]) - h2.y);
+              l.w = Out::pack2(__uint_as_float(r[8 * j + 6]) - h3.x, __uint_as_float(r[8 * j + 7]) - h3.y);
+              *reinterpret_cast<uint4*>(dst + gemm::EPI_STAGE_BYTES + (((unit0 + j) ^ (lane & 7)) << 4)) = l;
+            }
           }
           if (c & 1) {
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) {
-              if (row0 < M && col0 - 32 < N) tma_store_2d(&tmap_c, buf, col0 - 32, row0);
+              if (row0 < M && col0 - 32 < N) {
+                tma_store_2d(&tmap_c, buf, col0 - 32, row0);
+                if constexpr (kHiLo) tma_store_2d(&tmap_c, buf + gemm::EPI_STAGE_BYTES, ep.lo_off + col0 - 32, row0);
+              }
               bulk_commit_group();
             }
           }
@@ -379,8 +397,13 @@ inline int launch(const void* A, int lda, const void* B, int ldb, int M, int N, 
     if (out == nullptr || (reinterpret_cast<uintptr_t>(out) & 15) != 0) return kErrInvalidArg;
     if (Epi::kOut16) {
       if (ldc % 8 != 0 || N % 64 != 0) return kErrInvalidArg;
-      if (!gemm::make_tmap_out_16(&tc, Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt, out, static_cast<uint64_t>(M),
-                                  static_cast<uint64_t>(N), static_cast<uint64_t>(ldc)))
+      uint64_t out_cols = static_cast<uint64_t>(N);
+      if constexpr (gemm::epi_is_hilo<Epi>::value) {
+        if (ep.lo_off % 64 != 0 || ep.lo_off < N || ep.lo_off + N > ldc) return kErrInvalidArg;
+        out_cols = static_cast<uint64_t>(ep.lo_off) + static_cast<uint64_t>(N);
+      }
+      if (!gemm::make_tmap_out_16(&tc, Epi::kOutFmt < 0 ? FMT : Epi::kOutFmt, out, static_cast<uint64_t>(M), out_cols,
+                                  static_cast<uint64_t>(ldc)))
         return kErrCuda;
     } else {
       if (ldc % 4 != 0) return kErrInvalidArg;

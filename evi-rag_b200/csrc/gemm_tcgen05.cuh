@@ -484,6 +484,56 @@ struct EpiBiasAct16Tma {
   }
 };
 
+// [hi | lo] 16-bit rows through the staged TMA store (CTA-pair kernel only): out = act(acc + bias[n]) with exact
+// tanhf / expf, hi = 16-bit(out) at column n, lo = 16-bit(out - hi) at column lo_off + n of the same row. The rows are
+// the A operand of a later split contraction (gemm::SplitK): entity rows for P = W_err node_repr, projected question
+// rows for gate | bias. Both halves of a 32 x 64 box are staged and stored together.
+struct EpiBiasActHiLoTma {
+  static constexpr bool kTmaStore = true;
+  static constexpr bool kOut16 = true;
+  static constexpr bool kHiLo = true;
+  static constexpr int kOutFmt = -1;
+  struct Params {
+    const float* bias;  // [N] or null
+    int act[8];         // per n-block activation
+    int lo_off;         // column offset of the lo half (multiple of 64)
+  };
+  struct RowState {};
+  static EVI_DEVINL void init_row(RowState&) {}
+  template <int FMT>
+  static EVI_DEVINL void transform(const Params& p, RowState&, int, int col0, uint32_t (&r)[32]) {
+    const int act = p.act[(col0 / BN) & 7];
+    float v[32];
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      const float4 b = p.bias != nullptr ? __ldg(reinterpret_cast<const float4*>(p.bias + col0 + i))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
+      v[i + 0] = __uint_as_float(r[i + 0]) + b.x;
+      v[i + 1] = __uint_as_float(r[i + 1]) + b.y;
+      v[i + 2] = __uint_as_float(r[i + 2]) + b.z;
+      v[i + 3] = __uint_as_float(r[i + 3]) + b.w;
+    }
+    if (act == kActTanh) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = tanhf(v[i]);  // the lo half keeps ~22 bits: no fast approximation here
+    } else if (act == kActSigmoid) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[i] = 1.0f / (1.0f + expf(-v[i]));
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(v[i]);
+  }
+};
+
+template <class E, class = void>
+struct epi_is_hilo {
+  static constexpr bool value = false;
+};
+template <class E>
+struct epi_is_hilo<E, decltype(void(E::kHiLo))> {
+  static constexpr bool value = E::kHiLo;
+};
+
 // fp32 output through the staged TMA store: out = act(acc + bias[n]) with bias optional and the
 // activation chosen per 256-column block. Covers the partial products W_iv m / W_sc sc of state_net.0
 // (no bias, no activation), P = W_err node_repr, Rq = W_err r_ctx + b_1 and the gate|bias projection.

@@ -1219,6 +1219,15 @@ static int linear_act_impl(const void* x16, int ld_x, int x_lo_off, int m, const
                                                       sk);
   }
   if (out_lo_off >= 0 && (out_lo_off % 8 != 0 || out_lo_off + n > ld16)) return kErrInvalidArg;
+  static const bool hilo_direct = getenv("EVI_HILO_DIRECT") != nullptr;  // A/B knob: the per-thread row stores below
+  if (out32 == nullptr && out_lo_off >= n && out_lo_off % 64 == 0 && !one_sm && !hilo_direct && num_sms >= 2 &&
+      n % 64 == 0 && ld16 % 8 == 0 && (reinterpret_cast<uintptr_t>(out16) & 15) == 0) {
+    gemm::EpiBiasActHiLoTma::Params t;  // [hi | lo] rows: both halves staged and TMA-stored per 32 x 64 box
+    t.bias = bias, t.lo_off = out_lo_off;
+    for (int i = 0; i < 8; ++i) t.act[i] = act_per_block[i];
+    return gemm2::launch<FMT, gemm::EpiBiasActHiLoTma>(x16, ld_x, w16, ldw, m, n, k, t, num_sms, stream, m_dev, out16,
+                                                        ld16, sk);
+  }
   gemm::EpiBiasAct::Params p;
   p.bias = bias, p.out16 = out16, p.out32 = out32, p.ld16 = ld16, p.ld32 = n, p.lo_off = out_lo_off;
   for (int i = 0; i < 8; ++i) p.act[i] = act_per_block[i];
