@@ -15,6 +15,7 @@ both sides, max over ranks. Prints ONE JSON line on rank 0.
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -394,8 +395,15 @@ class Bench:
             a.record(); b.record()
         for i in range(warmup):
             ex(pipe.run_device(dev_batches[i]), dev_batches[i].num_graphs, counts[i])
+        # one more untimed pass over the LARGEST timed batch: the caching allocator then owns blocks big enough for
+        # every timed step (a cudaMalloc inside the region is a host-side stall of milliseconds), and the collector
+        # stays off while the region is timed
+        big = max(range(warmup, warmup + steps), key=lambda i: int(host_batches[i].edge_index.size(1)))
+        ex(pipe.run_device(dev_batches[big]), dev_batches[big].num_graphs, counts[big])
         ex.join()
         self.sync_all()
+        gc.collect()
+        gc.disable()
         self.evilib.LAUNCHES["kernels"] = 0
         e0, e1 = mk()
         chunk_edges, chunk_counts = [], []
@@ -412,6 +420,7 @@ class Bench:
         e1.record()
         m["enqueue_ms"] = (time.perf_counter() - t_host0) * 1e3  # host time to queue the region (no synchronisation)
         self.sync_all()
+        gc.enable()
         model.gemm_events = model.tail_events = None
         m["launches"] = self.evilib.LAUNCHES["kernels"]
         m["flags"] = int(res["flags"].item())
