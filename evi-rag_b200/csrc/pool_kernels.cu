@@ -100,17 +100,79 @@ __global__ void pool_insert_kernel(PoolTable t, const unsigned long long* __rest
   }
 }
 
+// Long rows. A warp scans a row 32 entries at a time with one hash probe per entry; a hub row of 40k entries is 1300
+// dependent iterations (milliseconds), and one such warp sets the duration of the whole launch. Rows longer than
+// kPoolSeg entries are therefore cut into segments: the warp that meets the row keeps segment 0 and appends the others
+// to an overflow list (evi_pool_overflow) that a second launch spreads over all warps. Segments that do not fit the
+// list are scanned by the first warp as before, so the result never depends on the list's capacity.
+constexpr int kPoolSeg = 1024;
+struct PoolOverflow {
+  unsigned long long* items;  // pair index << 17 | side << 16 | segment
+  unsigned long long* count;
+  unsigned long long capacity;
+};
+// reserve list slots for segments 1 .. nseg-1 of a long row; returns the first segment the caller must scan itself
+EVI_DEVINL int overflow_push(const PoolOverflow& o, unsigned long long pair, int side, int nseg, int lane) {
+  if (o.items == nullptr || nseg <= 1 || nseg > 65535) return 1;
+  unsigned long long pos = 0;
+  if (lane == 0) pos = atomicAdd(o.count, static_cast<unsigned long long>(nseg - 1));
+  pos = __shfl_sync(0xffffffffu, pos, 0);
+  const unsigned long long room = pos < o.capacity ? o.capacity - pos : 0ull;
+  for (int sgm = 1 + lane; sgm < nseg; sgm += 32)
+    if (static_cast<unsigned long long>(sgm - 1) < room)
+      o.items[pos + sgm - 1] = (pair << 17) | (static_cast<unsigned long long>(side) << 16) | static_cast<unsigned>(sgm);
+  const unsigned long long queued = room < static_cast<unsigned long long>(nseg - 1) ? room : nseg - 1;
+  return static_cast<int>(queued) + 1;  // segments [queued + 1, nseg) stay with the caller
+}
+
+// insert the neighbours listed in entries [i0, i1) of a row of `other` for the query in qbits
+EVI_DEVINL void expand_scan(PoolTable t, const int* __restrict__ other, int i0, int i1, unsigned long long qbits, int level,
+                            int lane, unsigned long long* __restrict__ visited,
+                            unsigned long long* __restrict__ visited_count, unsigned long long visited_cap,
+                            unsigned long long* __restrict__ fresh, unsigned long long* __restrict__ fresh_count,
+                            unsigned long long fresh_cap, unsigned* __restrict__ flags) {
+  for (int i = i0 + lane; i < i1; i += 32) {
+    const unsigned long long nk = qbits | static_cast<unsigned>(other[i]);
+    const int r = pool_insert(t, nk, static_cast<unsigned char>(level + 1), nullptr);
+    if (r < 0) atomicOr(flags, EVI_POOL_TABLE_FULL);
+    if (r == 1) {
+      const unsigned long long pos = atomicAdd(visited_count, 1ull);
+      if (pos < visited_cap) visited[pos] = nk; else atomicOr(flags, EVI_POOL_VISITED_FULL);
+      if (fresh != nullptr) {
+        const unsigned long long fp = atomicAdd(fresh_count, 1ull);
+        if (fp < fresh_cap) fresh[fp] = nk; else atomicOr(flags, EVI_POOL_VISITED_FULL);
+      }
+    }
+  }
+}
+
 // frontier = visited[begin, end); discoveries are inserted at level + 1 and appended to visited (own list) and to
-// fresh (what the other shards must be told about)
+// fresh (what the other shards must be told about). OVERFLOW = false: one warp per frontier pair (segment 0 of long
+// rows); OVERFLOW = true: one warp per queued segment.
+template <bool OVERFLOW>
 __global__ void __launch_bounds__(256)
 pool_expand_kernel(PoolTable t, PoolShard s, unsigned long long* __restrict__ visited, unsigned long long begin,
                    unsigned long long end, int level, unsigned long long* __restrict__ visited_count,
                    unsigned long long visited_cap, unsigned long long* __restrict__ fresh,
                    unsigned long long* __restrict__ fresh_count, unsigned long long fresh_cap,
-                   unsigned* __restrict__ flags) {
+                   unsigned* __restrict__ flags, PoolOverflow ovf) {
   const int lane = threadIdx.x & 31;
   const unsigned long long warp = (blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x) >> 5;
   const unsigned long long nwarps = (gridDim.x * static_cast<unsigned long long>(blockDim.x)) >> 5;
+  if constexpr (OVERFLOW) {
+    const unsigned long long n = *ovf.count < ovf.capacity ? *ovf.count : ovf.capacity;
+    for (unsigned long long it = warp; it < n; it += nwarps) {
+      const unsigned long long item = ovf.items[it];
+      const unsigned long long key = visited[item >> 17];
+      const int side = static_cast<int>((item >> 16) & 1ull), sgm = static_cast<int>(item & 0xFFFFull);
+      const int u = static_cast<int>(key & 0xFFFFFFFFull);
+      const int* ptr = side == 0 ? s.fwd_ptr : s.rev_ptr;
+      const int r0 = ptr[u], r1 = ptr[u + 1];
+      const int i0 = r0 + sgm * kPoolSeg, i1 = i0 + kPoolSeg < r1 ? i0 + kPoolSeg : r1;
+      expand_scan(t, side == 0 ? s.fwd_other : s.rev_other, i0, i1, key & 0xFFFFFFFF00000000ull, level, lane, visited,
+                  visited_count, visited_cap, fresh, fresh_count, fresh_cap, flags);
+    }
+  } else {
   for (unsigned long long p = begin + warp; p < end; p += nwarps) {
     const unsigned long long key = visited[p];
     const unsigned long long qbits = key & 0xFFFFFFFF00000000ull;
@@ -120,20 +182,15 @@ pool_expand_kernel(PoolTable t, PoolShard s, unsigned long long* __restrict__ vi
       const int* ptr = side == 0 ? s.fwd_ptr : s.rev_ptr;
       const int* other = side == 0 ? s.fwd_other : s.rev_other;
       const int r0 = ptr[u], r1 = ptr[u + 1];
-      for (int i = r0 + lane; i < r1; i += 32) {
-        const unsigned long long nk = qbits | static_cast<unsigned>(other[i]);
-        const int r = pool_insert(t, nk, static_cast<unsigned char>(level + 1), nullptr);
-        if (r < 0) atomicOr(flags, EVI_POOL_TABLE_FULL);
-        if (r == 1) {
-          const unsigned long long pos = atomicAdd(visited_count, 1ull);
-          if (pos < visited_cap) visited[pos] = nk; else atomicOr(flags, EVI_POOL_VISITED_FULL);
-          if (fresh != nullptr) {
-            const unsigned long long fp = atomicAdd(fresh_count, 1ull);
-            if (fp < fresh_cap) fresh[fp] = nk; else atomicOr(flags, EVI_POOL_VISITED_FULL);
-          }
-        }
-      }
+      const int nseg = (r1 - r0 + kPoolSeg - 1) / kPoolSeg;
+      const int mine = overflow_push(ovf, p, side, nseg, lane);  // segments [mine, nseg) stay here, like segment 0
+      expand_scan(t, other, r0, r0 + kPoolSeg < r1 ? r0 + kPoolSeg : r1, qbits, level, lane, visited, visited_count,
+                  visited_cap, fresh, fresh_count, fresh_cap, flags);
+      if (mine < nseg)
+        expand_scan(t, other, r0 + mine * kPoolSeg, r1, qbits, level, lane, visited, visited_count, visited_cap, fresh,
+                    fresh_count, fresh_cap, flags);
     }
+  }
   }
 }
 
@@ -145,17 +202,71 @@ pool_expand_kernel(PoolTable t, PoolShard s, unsigned long long* __restrict__ vi
 //                 the relation at cand_off[q] + cursor[q] (one atomicAdd per warp iteration, ballot-ranked lanes).
 constexpr int kPoolPrioBins = 8;
 
+// entries [i0, i1) of the head row of u for query q (du = hop distance of u): count or emit the edges whose tail is visited
 template <bool EMIT>
+EVI_DEVINL void candidates_scan(PoolTable t, PoolShard s, unsigned long long qbits, int q, int u, int du, int limit, int i0,
+                                int i1, int lane, int* __restrict__ cand_count, const long long* __restrict__ cand_off,
+                                int* __restrict__ cursor, unsigned long long* __restrict__ cand_key,
+                                unsigned long long* __restrict__ cand_ht, int* __restrict__ cand_rel) {
+  int found[kPoolPrioBins];
+#pragma unroll
+  for (int b = 0; b < kPoolPrioBins; ++b) found[b] = 0;
+  for (int base = i0; base < i1; base += 32) {
+    const int i = base + lane;
+    int slot = -1, v = 0, dv = 0;
+    if (i < i1) {
+      v = s.fwd_other[i];
+      slot = pool_find(t, qbits | static_cast<unsigned>(v), &dv);
+    }
+    const int prio = slot >= 0 ? du + dv : 0;
+    const int cls = prio < kPoolPrioBins - 1 ? prio : kPoolPrioBins - 1;
+    if (!EMIT) {
+      if (slot >= 0) {
+#pragma unroll
+        for (int b = 0; b < kPoolPrioBins; ++b) found[b] += cls == b ? 1 : 0;
+      }
+    } else {
+      const bool take = slot >= 0 && cls <= limit;
+      const unsigned m = __ballot_sync(0xffffffffu, take);
+      if (m != 0u) {
+        long long base_pos = 0;
+        if (lane == 0) base_pos = cand_off[q] + atomicAdd(&cursor[q], __popc(m));
+        base_pos = __shfl_sync(0xffffffffu, base_pos, 0);
+        if (take) {
+          const long long pos = base_pos + __popc(m & ((1u << lane) - 1u));
+          cand_key[pos] = (static_cast<unsigned long long>(prio) << kPoolEidBits) |
+                          static_cast<unsigned long long>(s.fwd_eid[i]);
+          cand_ht[pos] = (static_cast<unsigned long long>(static_cast<unsigned>(u)) << 32) | static_cast<unsigned>(v);
+          cand_rel[pos] = s.fwd_rel[i];
+        }
+      }
+    }
+  }
+  if (!EMIT) {
+#pragma unroll
+    for (int b = 0; b < kPoolPrioBins; ++b) {
+      const int c = __reduce_add_sync(0xffffffffu, found[b]);
+      if (lane == 0 && c) atomicAdd(&cand_count[q * kPoolPrioBins + b], c);
+    }
+  }
+}
+
+// OVERFLOW = false: one warp per visited pair (segment 0 of long rows); OVERFLOW = true: one warp per queued segment
+template <bool EMIT, bool OVERFLOW>
 __global__ void __launch_bounds__(256)
 pool_candidates_kernel(PoolTable t, PoolShard s, const unsigned long long* __restrict__ visited,
                        unsigned long long num_visited, int* __restrict__ cand_count,
                        const int* __restrict__ class_limit, const long long* __restrict__ cand_off,
                        int* __restrict__ cursor, unsigned long long* __restrict__ cand_key,
-                       unsigned long long* __restrict__ cand_ht, int* __restrict__ cand_rel) {
+                       unsigned long long* __restrict__ cand_ht, int* __restrict__ cand_rel, PoolOverflow ovf) {
   const int lane = threadIdx.x & 31;
   const unsigned long long warp = (blockIdx.x * static_cast<unsigned long long>(blockDim.x) + threadIdx.x) >> 5;
   const unsigned long long nwarps = (gridDim.x * static_cast<unsigned long long>(blockDim.x)) >> 5;
-  for (unsigned long long p = warp; p < num_visited; p += nwarps) {
+  const unsigned long long n_items =
+      OVERFLOW ? (*ovf.count < ovf.capacity ? *ovf.count : ovf.capacity) : num_visited;
+  for (unsigned long long it = warp; it < n_items; it += nwarps) {
+    const unsigned long long item = OVERFLOW ? ovf.items[it] : 0ull;
+    const unsigned long long p = OVERFLOW ? item >> 17 : it;
     const unsigned long long key = visited[p];
     const unsigned long long qbits = key & 0xFFFFFFFF00000000ull;
     const int q = static_cast<int>(key >> 32);
@@ -166,46 +277,18 @@ pool_candidates_kernel(PoolTable t, PoolShard s, const unsigned long long* __res
     pool_find(t, key, &du);
     const int limit = EMIT ? class_limit[q] : 0;
     if (EMIT && du > limit) continue;  // dist_v >= 0: every edge of this row is above the limit
-    int found[kPoolPrioBins];
-#pragma unroll
-    for (int b = 0; b < kPoolPrioBins; ++b) found[b] = 0;
-    for (int base = r0; base < r1; base += 32) {
-      const int i = base + lane;
-      int slot = -1, v = 0, dv = 0;
-      if (i < r1) {
-        v = s.fwd_other[i];
-        slot = pool_find(t, qbits | static_cast<unsigned>(v), &dv);
-      }
-      const int prio = slot >= 0 ? du + dv : 0;
-      const int cls = prio < kPoolPrioBins - 1 ? prio : kPoolPrioBins - 1;
-      if (!EMIT) {
-        if (slot >= 0) {
-#pragma unroll
-          for (int b = 0; b < kPoolPrioBins; ++b) found[b] += cls == b ? 1 : 0;
-        }
-      } else {
-        const bool take = slot >= 0 && cls <= limit;
-        const unsigned m = __ballot_sync(0xffffffffu, take);
-        if (m != 0u) {
-          long long base_pos = 0;
-          if (lane == 0) base_pos = cand_off[q] + atomicAdd(&cursor[q], __popc(m));
-          base_pos = __shfl_sync(0xffffffffu, base_pos, 0);
-          if (take) {
-            const long long pos = base_pos + __popc(m & ((1u << lane) - 1u));
-            cand_key[pos] = (static_cast<unsigned long long>(prio) << kPoolEidBits) |
-                            static_cast<unsigned long long>(s.fwd_eid[i]);
-            cand_ht[pos] = (static_cast<unsigned long long>(static_cast<unsigned>(u)) << 32) | static_cast<unsigned>(v);
-            cand_rel[pos] = s.fwd_rel[i];
-          }
-        }
-      }
-    }
-    if (!EMIT) {
-#pragma unroll
-      for (int b = 0; b < kPoolPrioBins; ++b) {
-        const int c = __reduce_add_sync(0xffffffffu, found[b]);
-        if (lane == 0 && c) atomicAdd(&cand_count[q * kPoolPrioBins + b], c);
-      }
+    if (OVERFLOW) {
+      const int i0 = r0 + static_cast<int>(item & 0xFFFFull) * kPoolSeg;
+      candidates_scan<EMIT>(t, s, qbits, q, u, du, limit, i0, i0 + kPoolSeg < r1 ? i0 + kPoolSeg : r1, lane, cand_count,
+                            cand_off, cursor, cand_key, cand_ht, cand_rel);
+    } else {
+      const int nseg = (r1 - r0 + kPoolSeg - 1) / kPoolSeg;
+      const int mine = overflow_push(ovf, p, 0, nseg, lane);  // segments [mine, nseg) stay here, like segment 0
+      candidates_scan<EMIT>(t, s, qbits, q, u, du, limit, r0, r0 + kPoolSeg < r1 ? r0 + kPoolSeg : r1, lane, cand_count,
+                            cand_off, cursor, cand_key, cand_ht, cand_rel);
+      if (mine < nseg)
+        candidates_scan<EMIT>(t, s, qbits, q, u, du, limit, r0 + mine * kPoolSeg, r1, lane, cand_count, cand_off, cursor,
+                              cand_key, cand_ht, cand_rel);
     }
   }
 }
@@ -435,6 +518,10 @@ inline PoolShard as_shard(const evi_pool_shard* s) {
   return PoolShard{s->fwd_ptr, s->fwd_other, s->fwd_rel, s->fwd_eid, s->rev_ptr, s->rev_other};
 }
 inline int sweep_grid(int num_sms) { return (num_sms > 0 ? num_sms : 148) * 8; }  // 8 CTAs of 8 warps per SM
+inline PoolOverflow as_overflow(const evi_pool_overflow* o) {
+  if (o == nullptr || o->items == nullptr || o->count == nullptr || o->capacity == 0) return PoolOverflow{nullptr, nullptr, 0};
+  return PoolOverflow{o->items, o->count, o->capacity};
+}
 
 }  // namespace
 
@@ -463,7 +550,8 @@ int evi_pool_insert(const evi_pool_table* table, const unsigned long long* pairs
 int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, unsigned long long* visited,
                     unsigned long long begin, unsigned long long end, int level, unsigned long long* visited_count,
                     unsigned long long visited_cap, unsigned long long* fresh, unsigned long long* fresh_count,
-                    unsigned long long fresh_cap, unsigned* flags, int num_sms, cudaStream_t stream) {
+                    unsigned long long fresh_cap, unsigned* flags, const evi_pool_overflow* overflow, int num_sms,
+                    cudaStream_t stream) {
   if (end <= begin) return kOk;
   if (!table_ok(table) || !shard_ok(shard) || visited == nullptr || visited_count == nullptr || flags == nullptr ||
       level < 0 || level > 61 || (fresh != nullptr && fresh_count == nullptr))
@@ -471,36 +559,58 @@ int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, un
   const unsigned long long warps = end - begin;
   const int grid = static_cast<int>(warps * 32 / 256 + 1 < static_cast<unsigned long long>(sweep_grid(num_sms))
                                         ? warps * 32 / 256 + 1 : sweep_grid(num_sms));
-  pool_expand_kernel<<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, begin, end, level,
-                                               visited_count, visited_cap, fresh, fresh_count, fresh_cap, flags);
+  const PoolOverflow ovf = as_overflow(overflow);
+  if (ovf.items != nullptr && cudaMemsetAsync(ovf.count, 0, sizeof(unsigned long long), stream) != cudaSuccess)
+    return kErrCuda;
+  pool_expand_kernel<false><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, begin, end, level,
+                                                      visited_count, visited_cap, fresh, fresh_count, fresh_cap, flags,
+                                                      ovf);
+  if (ovf.items != nullptr)  // the queued segments of long rows, spread over all warps
+    pool_expand_kernel<true><<<sweep_grid(num_sms), 256, 0, stream>>>(as_table(table), as_shard(shard), visited, begin,
+                                                                     end, level, visited_count, visited_cap, fresh,
+                                                                     fresh_count, fresh_cap, flags, ovf);
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }
 
 int evi_pool_candidates(const evi_pool_table* table, const evi_pool_shard* shard, const unsigned long long* visited,
                         unsigned long long num_visited, int emit, int num_queries, int cap, int* cand_count,
                         int* class_limit, int* emit_count, const long long* cand_off, int* cursor,
-                        unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel, int num_sms,
-                        cudaStream_t stream) {
+                        unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel,
+                        const evi_pool_overflow* overflow, int num_sms, cudaStream_t stream) {
   if (!table_ok(table) || !shard_ok(shard) || visited == nullptr || num_queries <= 0 || cap <= 0 ||
       cand_count == nullptr || class_limit == nullptr || emit_count == nullptr)
     return kErrInvalidArg;
   const int grid = static_cast<int>(num_visited * 32 / 256 + 1 < static_cast<unsigned long long>(sweep_grid(num_sms))
                                         ? num_visited * 32 / 256 + 1 : sweep_grid(num_sms));
+  const PoolOverflow ovf = as_overflow(overflow);
+  if (ovf.items != nullptr && cudaMemsetAsync(ovf.count, 0, sizeof(unsigned long long), stream) != cudaSuccess)
+    return kErrCuda;
+  const int ogrid = sweep_grid(num_sms);
   if (!emit) {
     if (cudaMemsetAsync(cand_count, 0, sizeof(int) * num_queries * kPoolPrioBins, stream) != cudaSuccess) return kErrCuda;
-    if (num_visited > 0)
-      pool_candidates_kernel<false><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
-                                                              cand_count, nullptr, nullptr, nullptr, nullptr, nullptr,
-                                                              nullptr);
+    if (num_visited > 0) {
+      pool_candidates_kernel<false, false><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited,
+                                                                     num_visited, cand_count, nullptr, nullptr, nullptr,
+                                                                     nullptr, nullptr, nullptr, ovf);
+      if (ovf.items != nullptr)
+        pool_candidates_kernel<false, true><<<ogrid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited,
+                                                                       num_visited, cand_count, nullptr, nullptr, nullptr,
+                                                                       nullptr, nullptr, nullptr, ovf);
+    }
     pool_boundary_kernel<<<(num_queries + 127) / 128, 128, 0, stream>>>(cand_count, num_queries, cap, class_limit,
                                                                        emit_count);
   } else {
     if (cand_off == nullptr || cursor == nullptr || cand_key == nullptr || cand_ht == nullptr || cand_rel == nullptr)
       return kErrInvalidArg;
-    if (num_visited > 0)
-      pool_candidates_kernel<true><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
-                                                             nullptr, class_limit, cand_off, cursor, cand_key, cand_ht,
-                                                             cand_rel);
+    if (num_visited > 0) {
+      pool_candidates_kernel<true, false><<<grid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited, num_visited,
+                                                                    nullptr, class_limit, cand_off, cursor, cand_key,
+                                                                    cand_ht, cand_rel, ovf);
+      if (ovf.items != nullptr)
+        pool_candidates_kernel<true, true><<<ogrid, 256, 0, stream>>>(as_table(table), as_shard(shard), visited,
+                                                                      num_visited, nullptr, class_limit, cand_off, cursor,
+                                                                      cand_key, cand_ht, cand_rel, ovf);
+    }
   }
   return cudaGetLastError() == cudaSuccess ? kOk : kErrCuda;
 }

@@ -114,6 +114,12 @@ class _ShardState:
         self.table.local_id, self.table.capacity = self.local_id.data_ptr(), table_capacity
         self.cshard = shard.c_struct()
         self.bounds = [0]
+        # work list for the segments of long adjacency rows (include/evi_rag_b200.h: evi_pool_overflow)
+        self.ovf_items = torch.empty(1 << 20, dtype=torch.long, device=dev)
+        self.ovf_count = torch.zeros(1, dtype=torch.long, device=dev)
+        self.overflow = _lib.PoolOverflow()
+        self.overflow.items, self.overflow.count = self.ovf_items.data_ptr(), self.ovf_count.data_ptr()
+        self.overflow.capacity = self.ovf_items.numel()
 
 
 class PoolRetriever:
@@ -153,6 +159,7 @@ class PoolRetriever:
         # rows cost ~20 KB per node: a 64k-query slab does not fit as one batch)
         self.score_edges_per_batch = max(1, int(score_edges_per_batch))
         self.timings: Dict[str, float] = {}
+        self.split_long_rows = True  # queue the segments of long adjacency rows for a second launch (evi_pool_overflow)
         self.profile = False  # True: synchronise around the frontier exchange and accumulate timings["exchange_s"]
         self.L = _lib.load()
 
@@ -190,8 +197,8 @@ class PoolRetriever:
                 _lib.check(L.evi_pool_expand(
                     C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), st.bounds[level], st.bounds[level + 1],
                     level, st.visited_count.data_ptr(), visited_cap, st.fresh.data_ptr() if multi else None,
-                    st.fresh_count.data_ptr() if multi else None, visited_cap, st.flags.data_ptr(), self.num_sms,
-                    stream), "evi_pool_expand")
+                    st.fresh_count.data_ptr() if multi else None, visited_cap, st.flags.data_ptr(),
+                    C.byref(st.overflow) if self.split_long_rows else None, self.num_sms, stream), "evi_pool_expand")
             if multi:  # frontier exchange: every shard learns the pairs the others reached at this level
                 if self.profile:
                     torch.cuda.synchronize(dev)
@@ -323,13 +330,14 @@ class PoolRetriever:
 
     def _shard_candidates(self, st: _ShardState, Q: int):
         L, dev, stream = self.L, self.dev, _lib.stream_handle()
+        ovf = C.byref(st.overflow) if self.split_long_rows else None
         nv = st.bounds[-1]
         count = torch.empty((Q, 8), dtype=torch.int32, device=dev)
         limit = torch.empty(Q, dtype=torch.int32, device=dev)
         emit_count = torch.empty(Q, dtype=torch.int32, device=dev)
         _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 0, Q, self.cap,
                                          count.data_ptr(), limit.data_ptr(), emit_count.data_ptr(), None, None, None, None,
-                                         None, self.num_sms, stream), "evi_pool_candidates")
+                                         None, ovf, self.num_sms, stream), "evi_pool_candidates")
         off = torch.zeros(Q + 1, dtype=torch.long, device=dev)
         off[1:] = torch.cumsum(emit_count.long(), 0)
         total = max(int(off[-1].item()), 1)
@@ -339,7 +347,7 @@ class PoolRetriever:
         cursor = torch.zeros(Q, dtype=torch.int32, device=dev)
         _lib.check(L.evi_pool_candidates(C.byref(st.table), C.byref(st.cshard), st.visited.data_ptr(), nv, 1, Q, self.cap,
                                          count.data_ptr(), limit.data_ptr(), emit_count.data_ptr(), off.data_ptr(),
-                                         cursor.data_ptr(), key.data_ptr(), ht.data_ptr(), rel.data_ptr(), self.num_sms,
+                                         cursor.data_ptr(), key.data_ptr(), ht.data_ptr(), rel.data_ptr(), ovf, self.num_sms,
                                          stream), "evi_pool_candidates")
         return key, ht, rel, off, emit_count.max()
 

@@ -73,6 +73,12 @@ class PoolShard(C.Structure):
         ("num_nodes", _i)]
 
 
+class PoolOverflow(C.Structure):
+    """``evi_pool_overflow`` (include/evi_rag_b200.h)."""
+
+    _fields_ = [("items", _vp), ("count", _vp), ("capacity", C.c_ulonglong)]
+
+
 class PoolTable(C.Structure):
     """``evi_pool_table`` (include/evi_rag_b200.h)."""
 
@@ -120,9 +126,9 @@ PROTOTYPES = {
     "evi_pool_reset": (_i, [C.POINTER(PoolTable), _vp]),
     "evi_pool_insert": (_i, [C.POINTER(PoolTable), _vp, _ll, _i, _vp, _vp, C.c_ulonglong, _vp, _vp]),
     "evi_pool_expand": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, C.c_ulonglong, _i, _vp,
-                             C.c_ulonglong, _vp, _vp, C.c_ulonglong, _vp, _i, _vp]),
+                             C.c_ulonglong, _vp, _vp, C.c_ulonglong, _vp, C.POINTER(PoolOverflow), _i, _vp]),
     "evi_pool_candidates": (_i, [C.POINTER(PoolTable), C.POINTER(PoolShard), _vp, C.c_ulonglong, _i, _i, _i] +
-                            [_vp] * 8 + [_i, _vp]),
+                            [_vp] * 8 + [C.POINTER(PoolOverflow), _i, _vp]),
     "evi_pool_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i] + [_vp] * 8 + [_vp]),
     "evi_pool_relabel": (_i, [C.POINTER(PoolTable), _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_pool_pack": (_i, [C.POINTER(PoolTable)] + [_vp] * 4 + [_i, _i, _i] + [_vp] * 5 + [_ll] + [_vp] * 6 + [_vp]),
@@ -160,8 +166,8 @@ _KERNELS_PER_CALL = {
     "evi_gagent_build": lambda a: 1,
     "evi_retriever_loss": lambda a: 3 if a[14] else 2,
     "evi_pool_insert": lambda a: 1 if a[2] > 0 else 0,
-    "evi_pool_expand": lambda a: 1 if a[4] > a[3] else 0,
-    "evi_pool_candidates": lambda a: (1 if a[3] > 0 else 0) + (0 if a[4] else 1),
+    "evi_pool_expand": lambda a: (2 if a[12] else 1) if a[4] > a[3] else 0,
+    "evi_pool_candidates": lambda a: ((2 if a[15] else 1) if a[3] > 0 else 0) + (0 if a[4] else 1),
     "evi_pool_select": lambda a: 1,
     "evi_pool_relabel": lambda a: 2,
     "evi_pool_pack": lambda a: 1,

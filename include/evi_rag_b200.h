@@ -416,6 +416,16 @@ typedef struct evi_pool_table {
   int* local_id;              /* [capacity] */
   unsigned long long capacity;/* power of two */
 } evi_pool_table;
+/* Optional work list for long adjacency rows: a warp scans a row 32 entries at a time, so a hub row of tens of thousands
+ * of entries would serialise the launch on one warp. With a list, rows longer than 1024 entries are cut into segments:
+ * the warp that meets the row scans the first and queues the others, and a second launch spreads the queued segments
+ * over all warps. Segments that do not fit `capacity` are scanned by the first warp (results never depend on it).
+ * NULL = every row is scanned by one warp. */
+typedef struct evi_pool_overflow {
+  unsigned long long* items;   /* [capacity] */
+  unsigned long long* count;   /* [1], cleared by the call */
+  unsigned long long capacity;
+} evi_pool_overflow;
 int evi_pool_reset(const evi_pool_table* table, cudaStream_t stream);
 /* merge pairs discovered elsewhere (the frontier exchange) or the seeds (dist_value 0); ~0 entries are padding */
 int evi_pool_insert(const evi_pool_table* table, const unsigned long long* pairs, long long num_pairs, int dist_value,
@@ -426,15 +436,16 @@ int evi_pool_insert(const evi_pool_table* table, const unsigned long long* pairs
 int evi_pool_expand(const evi_pool_table* table, const evi_pool_shard* shard, unsigned long long* visited,
                     unsigned long long begin, unsigned long long end, int level, unsigned long long* visited_count,
                     unsigned long long visited_cap, unsigned long long* fresh, unsigned long long* fresh_count,
-                    unsigned long long fresh_cap, unsigned* flags, int num_sms, cudaStream_t stream);
+                    unsigned long long fresh_cap, unsigned* flags, const evi_pool_overflow* overflow, int num_sms,
+                    cudaStream_t stream);
 /* emit == 0: cand_count [Q, 8] = candidates of this shard per priority class (dist_h + dist_t, clamped to 7),
  * class_limit [Q] = the class in which the running count reaches cap, emit_count [Q] = candidates of the classes up
  * to it; emit == 1: write those at cand_off[q] + cursor[q]++ (classes above the limit cannot survive the cut) */
 int evi_pool_candidates(const evi_pool_table* table, const evi_pool_shard* shard, const unsigned long long* visited,
                         unsigned long long num_visited, int emit, int num_queries, int cap, int* cand_count,
                         int* class_limit, int* emit_count, const long long* cand_off, int* cursor,
-                        unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel, int num_sms,
-                        cudaStream_t stream);
+                        unsigned long long* cand_key, unsigned long long* cand_ht, int* cand_rel,
+                        const evi_pool_overflow* overflow, int num_sms, cudaStream_t stream);
 /* per segment [seg_off[q], seg_off[q+1]): the cap smallest keys, ascending edge id; outputs [Q, cap];
  * stage_* [Q, cap] and sort_ws [Q, sort_len] (sort_len = power of two >= cap) are scratch */
 int evi_pool_select(const unsigned long long* cand_key, const unsigned long long* cand_ht, const int* cand_rel,
