@@ -62,7 +62,8 @@ def gather_topk(local: Dict[str, torch.Tensor], num_local_questions: int, group=
         t = local[name].contiguous()
         if t.shape[0] != num_local_questions:
             raise ValueError(f"{name}: leading dimension {t.shape[0]} != {num_local_questions} questions")
-        b = t.reshape(num_local_questions, -1).view(torch.uint8)
+        width = int(np.prod(t.shape[1:])) if t.dim() > 1 else 1  # explicit: reshape(0, -1) is ambiguous for 0 rows
+        b = t.reshape(num_local_questions, width).view(torch.uint8)
         rows.append(b)
         widths.append(int(b.shape[1]))
     packed = torch.zeros((q_max, sum(widths)), dtype=torch.uint8, device=dev)

@@ -80,3 +80,48 @@ def test_partition_by_edges_is_contiguous_and_balanced():
     assert sum(b - a for a, b in parts) == 2 and all(b >= a for a, b in parts)
     with pytest.raises(ValueError):
         partition_by_edges([1, 2, 3], 0)
+
+
+def _worker_empty_rank(rank: int, world: int, port: int, out_dir: str):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        parts = [(0, 2), (2, 2), (2, 5)]  # the middle rank owns no question (config 4: fewer sub-batches than ranks)
+        q0, q1 = parts[rank]
+        got = gather_topk(_fake_topk(q0, q1, 4), q1 - q0, counts=[b - a for a, b in parts])
+        full = _fake_topk(0, 5, 4)
+        for name in full:
+            assert torch.equal(got[name], full[name]), (rank, name)
+        open(os.path.join(out_dir, f"ok{rank}"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gather_topk_with_an_empty_rank(tmp_path):
+    mp.spawn(_worker_empty_rank, args=(3, _free_port(), str(tmp_path)), nprocs=3, join=True)
+    assert all((tmp_path / f"ok{r}").exists() for r in range(3))
+
+
+def test_pool_sub_batch_layout_is_world_independent():
+    """Config 4: scoring sub-batches are cut on the whole query list and ranks own whole sub-batches, so a query is
+    scored in the same sub-batch whatever the world size (the N-rank scores then equal the 1-rank scores bit for bit)."""
+    import types
+
+    from evi_rag_b200.kg_pool import PoolRetriever
+
+    rng = np.random.default_rng(3)
+    counts = np.minimum(rng.pareto(1.2, size=500) * 150, 20000).astype(int)  # heavy tail: a few capped queries
+    counts[7] = 0
+    ep = [0] + np.cumsum(counts).tolist()
+    stub = types.SimpleNamespace(score_edges_per_batch=4096)
+    cuts = PoolRetriever._sub_batch_cuts(stub, ep, len(counts))
+    assert cuts[0] == 0 and cuts[-1] == len(counts) and all(b > a for a, b in zip(cuts[:-1], cuts[1:]))
+    for a, b in zip(cuts[:-1], cuts[1:]):  # a sub-batch exceeds the budget only when one query alone does
+        assert ep[b] - ep[a] <= 4096 or b == a + 1
+    sub_edges = [ep[b] - ep[a] for a, b in zip(cuts[:-1], cuts[1:])]
+    for world in (2, 4, 8):
+        sparts = partition_by_edges(sub_edges, world)
+        owned = [c for s0, s1 in sparts for c in cuts[s0:s1]] + [cuts[-1]]
+        assert owned == cuts  # every rank's cuts are the global cuts inside its range
+        loads = [sum(sub_edges[s0:s1]) for s0, s1 in sparts]
+        assert max(loads) <= sum(loads) / world + max(sub_edges)
