@@ -391,7 +391,8 @@ class Bench:
         torch.cuda.synchronize(dev)
         mk = lambda: (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
         gemm_ev, tail_ev = [mk() for _ in range(steps)], [mk() for _ in range(steps)]
-        for a, b in gemm_ev + tail_ev:  # torch creates the cudaEvent_t lazily; record once so .cuda_event is live
+        stage_ev = {name: [mk() for _ in range(steps)] for name in ("bfs", "dde", "topk")}
+        for a, b in gemm_ev + tail_ev + [e for evs in stage_ev.values() for e in evs]:  # torch creates the cudaEvent_t lazily; record once so .cuda_event is live
             a.record(); b.record()
         for i in range(warmup):
             ex(pipe.run_device(dev_batches[i]), dev_batches[i].num_graphs, counts[i])
@@ -411,6 +412,8 @@ class Bench:
         e0.record()
         for i in range(steps):
             model.gemm_events, model.tail_events = (gemm_ev[i], tail_ev[i]) if full else (None, None)
+            model.dde_events = stage_ev["dde"][i] if full else None
+            pipe.stage_events = {"bfs": stage_ev["bfs"][i], "topk": stage_ev["topk"][i]} if full else None
             b = dev_batches[warmup + i]
             res = pipe.run_device(b)
             ex(res, b.num_graphs, counts[warmup + i])
@@ -421,13 +424,15 @@ class Bench:
         m["enqueue_ms"] = (time.perf_counter() - t_host0) * 1e3  # host time to queue the region (no synchronisation)
         self.sync_all()
         gc.enable()
-        model.gemm_events = model.tail_events = None
+        model.gemm_events = model.tail_events = model.dde_events = None
+        pipe.stage_events = None
         m["launches"] = self.evilib.LAUNCHES["kernels"]
         m["flags"] = int(res["flags"].item())
         m["ms_dev"] = e0.elapsed_time(e1)
         if full:
             m["gemm_ms"] = [a.elapsed_time(b) for a, b in gemm_ev]
             m["tail_ms"] = [a.elapsed_time(b) for a, b in tail_ev]
+            m["stage_ms"] = {name: [a.elapsed_time(b) for a, b in evs] for name, evs in stage_ev.items()}
         m["chunk_edges"], m["chunk_counts"] = chunk_edges, chunk_counts
         del dev_batches
         if not full:
@@ -663,6 +668,17 @@ def run_ours(args):
                     "not claimed as a roofline hit",
         },
     }
+    # the graph / selection stages against the HBM roofline on SURVEY.md §8(d)'s algorithmic bytes (rank 0's steps). Their
+    # working sets (5k edges per question) sit in L2 / shared memory, so the fractions are low by construction.
+    e_step, n_step, q_step = m["edges"] / args.steps, m["nodes"] / args.steps, m["questions"] / args.steps
+    stage_bytes = {"bfs": 8 * e_step + 12 * n_step,                      # adjacency entries + dist + frontier, per BFS
+                   "dde": 96 * e_step + 48 * n_step,                     # 4 rounds x 24 B per edge + features + degrees
+                   "topk": 4 * e_step + (8 + 40) * wl["k"] * q_step}     # scores read + [B, k] results + writer payload
+    line["stage_rooflines"] = {
+        name: {"bound": "hbm", "ms_per_step": float(np.mean(ms)), "algorithmic_bytes_per_step": stage_bytes[name],
+               "achieved": stage_bytes[name] / (float(np.mean(ms)) * 1e-3) / 1e9, "unit": "GB/s", "peak": peak_hbm,
+               "frac": stage_bytes[name] / (float(np.mean(ms)) * 1e-3) / 1e9 / peak_hbm}
+        for name, ms in m["stage_ms"].items()}
     if m["imbalance"] is not None:
         line["config"]["imbalance_max_over_mean_edges"] = m["imbalance"]
     if dropin is not None:

@@ -67,6 +67,8 @@ class RetrievalPipeline:
         self._slots = None
         self._slot_free = None
         self._out_slots = None
+        # optional {"bfs" | "topk": (torch.cuda.Event, torch.cuda.Event)} recorded around those stages (bench.py)
+        self.stage_events: Optional[Dict[str, Any]] = None
 
     @torch.no_grad()
     def run_device(self, b: Any) -> Dict[str, torch.Tensor]:
@@ -86,16 +88,23 @@ class RetrievalPipeline:
             out = self.model(b)
         finally:
             self.model.validate = was
+        self._mark("topk", 0)
         tk = segmented_topk(out.logits, gb.edge_ptr, self.top_k, sigmoid=self.writer_scores)
         res = writer_payload(tk, gb.edge_ptr, edge_index=b.edge_index, node_global_ids=b.node_global_ids,
                              edge_attr=b.edge_attr, labels=None, logits_fwd=out.logits_fwd,
                              logits_bwd=out.logits_bwd)
+        self._mark("topk", 1)
         res["bfs_dist"] = dist
         # one validation word per batch: the segmentation's (cross-graph / out-of-range / unsorted edges) OR the scorer's;
         # the scorer's accumulator is cleared for the next batch, all in stream order (no host synchronisation)
         res["flags"] = torch.bitwise_or(self.model._flags, gb.flags) if gb.flags is not None else self.model._flags.clone()
         self.model._flags.zero_()
         return res
+
+    def _mark(self, stage: str, which: int) -> None:
+        ev = self.stage_events.get(stage) if self.stage_events else None
+        if ev is not None:
+            ev[which].record()
 
     def _bfs(self, gb, b, seeds_global):
         """Multi-source hop distance from each question's seeds, undirected, capped at ``bfs_max_depth``:
@@ -118,11 +127,13 @@ class RetrievalPipeline:
         dist = torch.empty(max(1, n_total), dtype=torch.int32, device=dev)
         if 0 <= self.bfs_max_depth <= G.SWEEP_MAX_DEPTH:
             edge_end = gb.edge_ptr[1:].contiguous()
+            self._mark("bfs", 0)
             st = L.evi_bfs_edge_sweep(gb.head32.data_ptr(), gb.tail32.data_ptr(), B, gb.edge_ptr.data_ptr(),
                                       edge_end.data_ptr(), ptr32.data_ptr(), node_end32.data_ptr(), dist_off.data_ptr(),
                                       src_ptr32.data_ptr(), seeds32.data_ptr(), 1, 0, self.bfs_max_depth,
                                       dist.data_ptr(), _lib.stream_handle())
             _lib.check(st, "evi_bfs_edge_sweep")
+            self._mark("bfs", 1)
             return dist[:n_total]
         row_ptr, adj = G.build_csr(gb.head32, gb.tail32, gb.num_nodes, G.CSR_UNDIRECTED)
         queue = torch.empty(max(1, 2 * n_total), dtype=torch.int32, device=dev)

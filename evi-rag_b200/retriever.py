@@ -173,6 +173,7 @@ class Retriever(nn.Module):
         self._ws_score: Optional[torch.Tensor] = None
         self.gemm_events = None
         self.tail_events = None
+        self.dde_events = None
         self.last_chunk_edges = 0
         self.last_num_chunks = 0
         self._flags: Optional[torch.Tensor] = None
@@ -598,7 +599,12 @@ class Retriever(nn.Module):
             ns3[:, :, : 1 + rf] = part_f.view(N, 2, 1 + rf)
             ns3[:, :, 1 + rf:] = part_r.view(N, 2, 1 + rr)[:, :, 1:]
         else:
+            dde_ev = self.dde_events  # optional (begin, end) torch events around the propagation (bench.py)
+            if dde_ev is not None:
+                dde_ev[0].record()
             dde(head32, tail32, E, rf, rr, node_struct)
+            if dde_ev is not None:
+                dde_ev[1].record()
         node_uv = torch.empty((N, 2 * d), dtype=torch.float32, device=dev)
         _lib.check(L.evi_struct_project(node_struct.data_ptr(), N, ns_dim, p["ws_t"].data_ptr(), p["bs"].data_ptr(),
                                         node_uv.data_ptr(), stream), "evi_struct_project")
