@@ -1298,3 +1298,29 @@ def test_metrics_k_limit_and_margin_validity(dev):
     assert arr.margin_valid.cpu().tolist() == [1, 0, 1]
     assert arr.margin.cpu().tolist()[0] == float("inf") and arr.margin.cpu().tolist()[2] == float("inf")
     assert arr.pos.cpu().tolist() == [1.0, 4.0, 1.0]
+
+
+def test_strict_mode_tables_and_features(dev, golden_dir):
+    """precision="strict" on the other two routes: device-resident tables with per-id rows (synthetic batch against the
+    oracle) and the features path (golden features of the reference), both at the strict tolerance."""
+    from evi_rag_b200.retriever import Retriever
+
+    spec = tiny_spec(5, 600, seed=77, num_relations=48, num_entities=900)
+    qb = generate_questions(spec)
+    ref, m, b = _oracle_and_model(qb, spec, dev, sd_seed=3, precision="strict")
+    out = m(b)
+    check_scores(out.logits.cpu().numpy(), ref.logits.numpy(), "strict", "strict/tables/logits")
+    check_scores(out.logits_fwd.cpu().numpy(), ref.logits_fwd.numpy(), "strict", "strict/tables/fwd")
+    check_scores(out.logits_bwd.cpu().numpy(), ref.logits_bwd.numpy(), "strict", "strict/tables/bwd")
+    g = _g(golden_dir, "scorer_d1024_trained.npz")
+    dim, seed, trained, rf, rr = [int(x) for x in g["meta"]]
+    mf = Retriever(emb_dim=dim, hidden_dim=dim, precision="strict", return_edge_embeddings=True,
+                   dde_cfg={"num_rounds": rf, "num_reverse_rounds": rr}).eval()
+    mf.load_state_dict(make_state_dict(seed, dim, dim, rf, rr, trained_like=True), strict=True)
+    mf.to(dev)
+    outf = mf(_batch_from_golden(g, dev))
+    fe = outf.edge_embeddings.cpu().numpy()
+    check_scores(outf.logits.cpu().numpy(), g["bidirectional.logits"], "strict", "strict/features-path logits")
+    check_scores(fe[:4], g["bidirectional.feat_head"], "strict", "strict/features", rel_l2_tol=2e-4, max_abs_tol=3e-4)
+    check_scores(fe.sum(1), g["bidirectional.feat_rowsum"], "strict", "strict/feature rowsums", rel_l2_tol=2e-4,
+                 max_abs_tol=3e-4)
