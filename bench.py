@@ -343,6 +343,10 @@ class Exchanger:
             torch.cuda.current_stream(self.dev).wait_stream(self.side)
 
 
+def args_precision_strict(args) -> bool:
+    return args.precision == "strict"
+
+
 class Bench:
     """One process per GPU: the model with its device-resident tables, and the timing loops."""
 
@@ -426,6 +430,16 @@ class Bench:
         gc.enable()
         model.gemm_events = model.tail_events = model.dde_events = None
         pipe.stage_events = None
+        lc = model.last_counts  # of the last timed step: tensor FLOPs the step really executed
+        to_int = lambda v: int(v.item()) if torch.is_tensor(v) else int(v)
+        if lc is not None:
+            rows, pairs, e_last = to_int(lc["entity_rows"]), to_int(lc["pair_rows"]), lc["edges"]
+            strict = args_precision_strict(self.args)
+            per_edge = (9 if strict else 3) * e_last                      # W_iv m, W_sc sc_f, W_sc sc_b (x3 passes in strict)
+            per_id = 3 * rows * 2                                         # entity projection and P, three passes each
+            small = 3 * (lc["relation_rows"] + 3 * lc["questions"])       # relation / query / gate|bias projections
+            m["executed_flops_last_step"] = 2.0 * 1024 * 1024 * (per_edge + per_id + (3 if strict else 1) * pairs + small)
+            m["last_step_rows"] = {"entity_rows": rows, "pair_rows": pairs, "nodes": lc["nodes"], "edges": e_last}
         m["launches"] = self.evilib.LAUNCHES["kernels"]
         m["flags"] = int(res["flags"].item())
         m["ms_dev"] = e0.elapsed_time(e1)
@@ -657,6 +671,11 @@ def run_ours(args):
             "share_of_step": float(np.sum([ms * c for ms, c in zip(gemm_ms, chunk_counts)])) / ms_dev,
             "step_algorithmic_tflops": step_flops / (ms_dev * 1e-3) / 1e12 / world,
             "step_frac_of_peak": step_flops / (ms_dev * 1e-3) / 1e12 / world / peak_tf,
+            # what the tensor cores really executed in rank 0's last timed step (the linearity split of DESIGN.md §4 halves
+            # the per-edge work; the [hi | lo] passes add to the per-id work), over the average step time
+            "step_executed_tflops": m.get("executed_flops_last_step", 0.0) / (ms_dev / args.steps * 1e-3) / 1e12,
+            "step_executed_frac_of_peak": m.get("executed_flops_last_step", 0.0) / (ms_dev / args.steps * 1e-3) / 1e12 / peak_tf,
+            "last_step_rows": m.get("last_step_rows"),
         },
         "roofline_non_tensor": {
             "bound": "hbm", "kernel": "evi::score_tail_bulk_kernel (z assembly + LayerNorm + GELU + head dot + combine)",

@@ -174,6 +174,7 @@ class Retriever(nn.Module):
         self.gemm_events = None
         self.tail_events = None
         self.dde_events = None
+        self.last_counts = None
         self.last_chunk_edges = 0
         self.last_num_chunks = 0
         self._flags: Optional[torch.Tensor] = None
@@ -686,6 +687,11 @@ class Retriever(nn.Module):
         a.ev_tail_end = tail_events[1].cuda_event if tail_events is not None else None
         _lib.check(L.evi_score_edges(C.byref(a), stream), "evi_score_edges")
         self._pending_flags = True
+        # device-side row counts of the last forward (distinct embedding ids, (question, relation) pairs) for callers
+        # that account for executed work after a synchronisation (bench.py); None / N / E when not deduplicated
+        self.last_counts = {"nodes": N, "edges": E, "relation_rows": R, "questions": B,
+                            "entity_rows": rows_dev if rows_dev is not None else N,
+                            "pair_rows": num_pairs if use_tables else E}
 
         # ---- a7: hide-and-seek bias (eval only when apply_in_eval; retriever.py:247-256) ----
         logits_ref = logits_fwd if logits_fwd is not None else logits_bwd
