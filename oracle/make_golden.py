@@ -413,6 +413,7 @@ def golden_writer():
         w.on_predict_end(trainer, None)
         payload = torch.load(os.path.join(tmp, "test.pt"), weights_only=False)
         manifest = json.loads(open(os.path.join(tmp, "test.manifest.json")).read())
+    manifest["created_at"] = "1970-01-01T00:00:00Z"  # the one run-dependent field: pinned so the fixture reproduces bit for bit
     torch.save({"payload": payload, "manifest": manifest}, os.path.join(GOLDEN, "writer_artifact.pt"))
     np.savez_compressed(os.path.join(GOLDEN, "writer_inputs.npz"), edge_index=qb.edge_index, edge_attr=qb.edge_attr,
                         ptr=qb.ptr, edge_ptr=qb.edge_ptr, node_global_ids=qb.node_global_ids, logits=logits,
