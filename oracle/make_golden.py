@@ -561,6 +561,8 @@ def main():
         f.write(
             "Generated by oracle/make_golden.py from the unmodified reference at /root/reference\n"
             f"torch {torch.__version__}, numpy {np.__version__}; mean-aggregation provider: {kind}\n"
+            "Every fixture is rewritten bit for bit by `python oracle/make_golden.py` (the writer artifact's manifest\n"
+            "timestamp is pinned to 1970-01-01T00:00:00Z in the stored copy). Round 2 added hide_seek.npz and training_d64.npz.\n"
         )
 
 
