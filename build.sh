@@ -11,3 +11,8 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
   "$SRC/graph_kernels.cu" "$SRC/topk_kernels.cu" "$SRC/scorer_kernels.cu" "$SRC/gagent_kernels.cu" "$SRC/pool_kernels.cu" "$SRC/loss_kernels.cu" \
   -o "$OUT"
 echo "built $OUT"
+# host-side record builder of the writer (CPython extension, plain C; optional: writer.py falls back to its Python loop)
+PYINC="$(python -c 'import sysconfig; print(sysconfig.get_paths()["include"])')"
+EXT="$(python -c 'import sysconfig; print(sysconfig.get_config_var("EXT_SUFFIX"))')"
+gcc -O2 -shared -fPIC -I "$PYINC" "$SRC/records.c" -o "$ROOT/evi-rag_b200/_evi_records$EXT"
+echo "built $ROOT/evi-rag_b200/_evi_records$EXT"

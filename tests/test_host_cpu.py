@@ -142,3 +142,46 @@ def test_writer_and_gagent_host_validation(tmp_path):
     for bad in (dict(max_hops=-1), dict(score_temperature=0.0), dict(start_keep_ratio=1.5), dict(score_mode="x")):
         with pytest.raises(ValueError):
             GAgentSettings(**bad)
+
+
+def test_native_record_builder_equals_python_loop(tmp_path):
+    """csrc/records.c (the writer's plain-C record builder) against the Python loop it replaces: equal records for
+    ragged counts, optional logit columns and text maps."""
+    import numpy as np
+    import torch
+
+    from evi_rag_b200 import writer as W
+
+    if W._evi_records is None:
+        pytest.skip("_evi_records has not been built (./build.sh)")
+    B, K = 37, 24
+    rng = np.random.default_rng(0)
+    f32 = lambda: torch.from_numpy(rng.standard_normal((B, K)).astype(np.float32))
+    counts = rng.integers(0, K + 1, B).astype(np.int32)
+    counts[3], counts[5] = 0, K
+    host = {"score": f32(), "count": torch.from_numpy(counts), "head_id": torch.from_numpy(rng.integers(0, 1 << 40, (B, K))),
+            "tail_id": torch.from_numpy(rng.integers(0, 1 << 40, (B, K))),
+            "relation_id": torch.from_numpy(rng.integers(0, 50, (B, K))), "label": f32(), "logit_fwd": f32(),
+            "logit_bwd": f32()}
+
+    class Done:
+        def synchronize(self):
+            pass
+
+    for has_fwd, has_bwd, maps in ((True, True, False), (False, True, True), (False, False, False)):
+        item = W._PendingBatch()
+        item.host, item.done, item.num_graphs = host, Done(), B
+        item.sample_ids, item.questions = [f"s{i}" for i in range(B)], [f"q{i}" for i in range(B)]
+        item.answers, item.answer_ptr = list(range(2 * B)), list(range(0, 2 * B + 1, 2))
+        item.has_fwd, item.has_bwd = has_fwd, has_bwd
+        w = W.RetrieverTopKEdgeWriter(output_dir=tmp_path, topk_values=[3, 1, 50])
+        if maps:
+            w._relation_map = {i: f"rel{i}" for i in range(0, 50, 3)}
+            w._entity_map = {int(host["head_id"][0, 0]): "an entity"}
+        native = w._materialise(item)
+        w.use_native_records = False
+        python = w._materialise(item)
+        assert native == python and len(native) == int((counts > 0).sum())
+        edge = native[0]["triplets_by_k"][3][0]
+        assert list(edge)[:9] == list(W._EDGE_KEYS) and ("logit_fwd" in edge) == has_fwd and ("logit_bwd" in edge) == has_bwd
+        assert native[0]["triplets_by_k"][1][0] is not native[0]["triplets_by_k"][3][0]  # every k has its own dicts
