@@ -506,6 +506,8 @@ def measure_dropin(bench, wl, host_batches, warmup):
         b.answer_entity_ids = torch.zeros(hb.num_graphs, dtype=torch.long)
         b.answer_entity_ids_ptr = torch.arange(hb.num_graphs + 1, dtype=torch.long)
         b.sample_id = [f"q{i}_{j}" for j in range(hb.num_graphs)]
+        # a PyG Batch carries its per-graph edge offsets (the reference slices by them, retriever_topk_edge_writer.py:389-395)
+        b._slice_dict = {"edge_index": torch.from_numpy(hb.edge_ptr_host)}
         return b
 
     def run(batches, base):

@@ -38,6 +38,7 @@ def host_batch(qb, pin: bool = True) -> types.SimpleNamespace:
     b.num_graphs = qb.num_graphs
     b.q_ptr_host = np.asarray(qb.q_ptr)
     b.ptr_host = np.asarray(qb.ptr)
+    b.edge_ptr_host = np.asarray(qb.edge_ptr)  # what a PyG Batch carries as _slice_dict["edge_index"]
     return b
 
 
