@@ -249,7 +249,9 @@ class RetrieverTopKEdgeWriter:
             if cand is not None:
                 cand = torch.as_tensor(cand, dtype=torch.long).view(-1)
                 if cand.numel() == B + 1:
-                    return cand.to(dev)
+                    # non_blocking: a blocking copy from pageable memory synchronises the stream, i.e. waits for the
+                    # forward that was just queued, and the record building below would then run with the device idle
+                    return cand.to(dev, non_blocking=True)
         if query_ids.numel() != num_edges:
             raise ValueError(f"query_ids/scores mismatch: {tuple(query_ids.shape)} vs {num_edges}")
         if bool((query_ids[1:] < query_ids[:-1]).any()):
