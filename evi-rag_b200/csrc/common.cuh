@@ -110,6 +110,50 @@ EVI_DEVINL float tanh_fast(float x) {
   const float e = ex2_approx(-2.8853900817779268f * fabsf(x));
   return copysignf(__fdividef(1.0f - e, 1.0f + e), x);
 }
+// Packed fp32 pairs (sm_100 FFMA2 / FADD2 / FMUL2: two IEEE fp32 operations per instruction, each half bit-identical
+// to the scalar form; a scalar or immediate operand is broadcast by the instruction, |x| and -x are operand modifiers).
+// An FFMA2 holds the issue port for two cycles (scripts/probes/ffma2_probe.cu, profiles/r01y_gemm_vs_cublas.md), so it
+// buys no arithmetic throughput; what it buys is a 28 % shorter instruction stream. Measured A/B on one box
+// (profiles/r04a_f32x2_ab.md): score_tail_bulk_kernel -7 % (kept: the tail keeps a lane's columns as (even, odd)
+// pairs), edge_operand_kernel +17 % (not kept: that kernel stays scalar).
+// -DEVI_NO_F32X2 expands the same helpers to scalar operations.
+EVI_DEVINL float2 bc2(float a) { return make_float2(a, a); }
+EVI_DEVINL float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
+EVI_DEVINL float2 abs2(float2 a) { return make_float2(fabsf(a.x), fabsf(a.y)); }
+#ifndef EVI_NO_F32X2
+EVI_DEVINL float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+EVI_DEVINL float2 add2(float2 a, float2 b) { return __fadd2_rn(a, b); }
+EVI_DEVINL float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
+#else
+EVI_DEVINL float2 fma2(float2 a, float2 b, float2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+EVI_DEVINL float2 add2(float2 a, float2 b) { return make_float2(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y)); }
+EVI_DEVINL float2 mul2(float2 a, float2 b) { return make_float2(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)); }
+#endif
+EVI_DEVINL float2 sub2(float2 a, float2 b) { return add2(a, neg2(b)); }
+EVI_DEVINL float hsum2(float2 a) { return a.x + a.y; }
+// gelu_fast / gelu_fast5 on a pair: 8 (6) FFMA2 + 2 MUFU.EX2 + 2 FMNMX for two values
+EVI_DEVINL float2 gelu_fast(float2 x) {
+  const float2 ax = abs2(x);
+  float2 q = bc2(1.8662889260667725e-06f);
+  q = fma2(q, ax, bc2(-6.2319784774445e-05f));
+  q = fma2(q, ax, bc2(0.0009371304186061025f));
+  q = fma2(q, ax, bc2(-0.008538476191461086f));
+  q = fma2(q, ax, bc2(0.05403471365571022f));
+  q = fma2(q, ax, bc2(0.45837363600730896f));
+  q = fma2(q, ax, bc2(1.1512972116470337f));
+  q = fma2(q, ax, bc2(0.9999892115592957f));
+  return fma2(neg2(ax), make_float2(ex2_approx(-q.x), ex2_approx(-q.y)), make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)));
+}
+EVI_DEVINL float2 gelu_fast5(float2 x) {
+  const float2 ax = abs2(x);
+  float2 q = bc2(0.00023532388149760664f);
+  q = fma2(q, ax, bc2(-0.00492762541398406f));
+  q = fma2(q, ax, bc2(0.04495760053396225f));
+  q = fma2(q, ax, bc2(0.4690363109111786f));
+  q = fma2(q, ax, bc2(1.1463907957077026f));
+  q = fma2(q, ax, bc2(1.0005117654800415f));
+  return fma2(neg2(ax), make_float2(ex2_approx(-q.x), ex2_approx(-q.y)), make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f)));
+}
 EVI_DEVINL float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f)); }
 EVI_DEVINL float sigmoidf_(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
@@ -126,6 +170,7 @@ template <> struct Op16<kFmtF16> {
     __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
   }
+  static EVI_DEVINL uint32_t pack2(float2 v) { return pack2(v.x, v.y); }
   static EVI_DEVINL float2 unpack2(uint32_t u) {
     return __half22float2(*reinterpret_cast<__half2*>(&u));
   }
@@ -139,6 +184,7 @@ template <> struct Op16<kFmtBF16> {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
   }
+  static EVI_DEVINL uint32_t pack2(float2 v) { return pack2(v.x, v.y); }
   static EVI_DEVINL float2 unpack2(uint32_t u) {
     return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u));
   }
@@ -164,6 +210,25 @@ EVI_DEVINL void ldg_v8_keep(const float* p, float (&v)[8]) {
   asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
                : "l"(p));
+}
+
+// the same loads into four (even, odd) column pairs
+EVI_DEVINL void ldg_v8_stream(const float* p, float2 (&v)[4]) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0].x), "=f"(v[0].y), "=f"(v[1].x), "=f"(v[1].y), "=f"(v[2].x), "=f"(v[2].y), "=f"(v[3].x),
+                 "=f"(v[3].y)
+               : "l"(p));
+}
+EVI_DEVINL void ldg_v8_keep(const float* p, float2 (&v)[4]) {
+  asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=f"(v[0].x), "=f"(v[0].y), "=f"(v[1].x), "=f"(v[1].y), "=f"(v[2].x), "=f"(v[2].y), "=f"(v[3].x),
+                 "=f"(v[3].y)
+               : "l"(p));
+}
+// eight consecutive floats of shared (or generic) memory as four pairs: two 128-bit loads
+EVI_DEVINL void ld_v8(const float* p, float2 (&v)[4]) {
+  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+  v[0] = make_float2(a.x, a.y), v[1] = make_float2(a.z, a.w), v[2] = make_float2(b.x, b.y), v[3] = make_float2(b.z, b.w);
 }
 
 // ---------------------------------------------------------------------------------------------

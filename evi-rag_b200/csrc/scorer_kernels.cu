@@ -183,22 +183,20 @@ EVI_DEVINL void load_row32(const float* __restrict__ base, int lane, float (&v)[
 // one [hi | lo] row (2D elements): the 16-bit value at base[c] and its residual at base[D + c] — the operand of the
 // three-pass state_net.4 contraction of the features path
 template <int FMT>
-EVI_DEVINL void store_row16(uint16_t* __restrict__ base, int lane, const float (&v)[32]) {
+EVI_DEVINL void store_row16(uint16_t* __restrict__ base, int lane, const float2 (&v)[16]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     uint4 w;
-    w.x = Op16<FMT>::pack2(v[i * 8 + 0], v[i * 8 + 1]);
-    w.y = Op16<FMT>::pack2(v[i * 8 + 2], v[i * 8 + 3]);
-    w.z = Op16<FMT>::pack2(v[i * 8 + 4], v[i * 8 + 5]);
-    w.w = Op16<FMT>::pack2(v[i * 8 + 6], v[i * 8 + 7]);
+    w.x = Op16<FMT>::pack2(v[i * 4 + 0].x, v[i * 4 + 0].y);
+    w.y = Op16<FMT>::pack2(v[i * 4 + 1].x, v[i * 4 + 1].y);
+    w.z = Op16<FMT>::pack2(v[i * 4 + 2].x, v[i * 4 + 2].y);
+    w.w = Op16<FMT>::pack2(v[i * 4 + 3].x, v[i * 4 + 3].y);
     *reinterpret_cast<uint4*>(base + i * 256 + lane * 8) = w;
-    const float2 h0 = Op16<FMT>::unpack2(w.x), h1 = Op16<FMT>::unpack2(w.y), h2 = Op16<FMT>::unpack2(w.z),
-                 h3 = Op16<FMT>::unpack2(w.w);
     uint4 l;
-    l.x = Op16<FMT>::pack2(v[i * 8 + 0] - h0.x, v[i * 8 + 1] - h0.y);
-    l.y = Op16<FMT>::pack2(v[i * 8 + 2] - h1.x, v[i * 8 + 3] - h1.y);
-    l.z = Op16<FMT>::pack2(v[i * 8 + 4] - h2.x, v[i * 8 + 5] - h2.y);
-    l.w = Op16<FMT>::pack2(v[i * 8 + 6] - h3.x, v[i * 8 + 7] - h3.y);
+    l.x = Op16<FMT>::pack2(sub2(v[i * 4 + 0], Op16<FMT>::unpack2(w.x)));
+    l.y = Op16<FMT>::pack2(sub2(v[i * 4 + 1], Op16<FMT>::unpack2(w.y)));
+    l.z = Op16<FMT>::pack2(sub2(v[i * 4 + 2], Op16<FMT>::unpack2(w.z)));
+    l.w = Op16<FMT>::pack2(sub2(v[i * 4 + 3], Op16<FMT>::unpack2(w.w)));
     *reinterpret_cast<uint4*>(base + D + i * 256 + lane * 8) = l;
   }
 }
@@ -207,6 +205,11 @@ EVI_DEVINL void unpack8(const uint4& w, float (&v)[8]) {
   const float2 a = Op16<FMT>::unpack2(w.x), b = Op16<FMT>::unpack2(w.y), c = Op16<FMT>::unpack2(w.z),
                d = Op16<FMT>::unpack2(w.w);
   v[0] = a.x, v[1] = a.y, v[2] = b.x, v[3] = b.y, v[4] = c.x, v[5] = c.y, v[6] = d.x, v[7] = d.y;
+}
+template <int FMT>
+EVI_DEVINL void unpack8(const uint4& w, float2 (&v)[4]) {
+  v[0] = Op16<FMT>::unpack2(w.x), v[1] = Op16<FMT>::unpack2(w.y), v[2] = Op16<FMT>::unpack2(w.z),
+  v[3] = Op16<FMT>::unpack2(w.w);
 }
 template <int FMT>
 EVI_DEVINL uint4 pack8(const float (&v)[8]) {
@@ -236,7 +239,6 @@ EVI_DEVINL void store_operand8(uint16_t* __restrict__ row, int c, const float (&
     st_cs_v4(row + D + c, pack8<FMT>(l));
   }
 }
-
 // struct context of one direction: writes sc (16-bit) to `sc_out`, returns nav.
 // ua / vb: the U row of the first node and the V row of the second.
 #ifndef EVI_SC_GELU
@@ -633,86 +635,89 @@ struct TailParams {
 };
 
 // LayerNorm statistics of one pre-activation row spread over the warp: rstd and -mean * rstd
-EVI_DEVINL void row_norm_stats(const float (&z)[32], float& rstd, float& shift) {
-  float sum = 0.f;
+// (the lane's 32 columns as 16 (even, odd) pairs, see common.cuh)
+EVI_DEVINL void row_norm_stats(const float2 (&z)[16], float& rstd, float& shift) {
+  float2 sum = z[0];
 #pragma unroll
-  for (int j = 0; j < 32; ++j) sum += z[j];
-  const float mean = warp_sum(sum) * (1.0f / D);
-  float var = 0.f;
+  for (int j = 1; j < 16; ++j) sum = add2(sum, z[j]);
+  const float mean = warp_sum(hsum2(sum)) * (1.0f / D);
+  float2 var = bc2(0.f);
 #pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    const float d = z[j] - mean;
-    var = fmaf(d, d, var);
+  for (int j = 0; j < 16; ++j) {
+    const float2 d = sub2(z[j], bc2(mean));
+    var = fma2(d, d, var);
   }
-  rstd = rsqrtf(warp_sum(var) * (1.0f / D) + kLnEps);
+  rstd = rsqrtf(warp_sum(hsum2(var)) * (1.0f / D) + kLnEps);
   shift = -mean * rstd;
 }
 
 // LayerNorm + GELU + collapsed score head of one direction (z is overwritten with g)
 template <int FMT>
-EVI_DEVINL float tail_finish(float (&z)[32], const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
+EVI_DEVINL float tail_finish(float2 (&z)[16], const TailParams& tp, int lane, uint16_t* __restrict__ g_out) {
   float rstd, shift;
   row_norm_stats(z, rstd, shift);
-  float acc = 0.f;
+  float2 acc = bc2(0.f);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int col = i * 256 + lane * 8;
-    float gg[8], bb[8], vv[8];
+    float2 gg[4], bb[4], vv[4];
     ldg_v8_keep(tp.ln_g + col, gg);
     ldg_v8_keep(tp.ln_b + col, bb);
     ldg_v8_keep(tp.v + col, vv);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float y = gelu_fast(fmaf(fmaf(z[i * 8 + j], rstd, shift), gg[j], bb[j]));
-      z[i * 8 + j] = y;
-      acc = fmaf(y, vv[j], acc);
+    for (int j = 0; j < 4; ++j) {
+      const float2 y = gelu_fast(fma2(fma2(z[i * 4 + j], bc2(rstd), bc2(shift)), gg[j], bb[j]));
+      z[i * 4 + j] = y;
+      acc = fma2(y, vv[j], acc);
     }
   }
   if (g_out != nullptr) store_row16<FMT>(g_out, lane, z);
-  return warp_sum(acc) + tp.c0;
+  return warp_sum(hsum2(acc)) + tp.c0;
 }
 
 // Both directions of one edge in one pass over the parameter vectors (ln_g, ln_b, v are read once per edge)
 // FEATS = false: the GELU outputs are not stored (no feature path), so they need not be kept in registers
 template <int FMT, bool FEATS = true>
-EVI_DEVINL void tail_finish_pair(float (&zf)[32], float (&zb)[32], const TailParams& tp, int lane,
+EVI_DEVINL void tail_finish_pair(float2 (&zf)[16], float2 (&zb)[16], const TailParams& tp, int lane,
                                  uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd, float& lf, float& lb) {
   float rstd_f, shift_f, rstd_b, shift_b;
   row_norm_stats(zf, rstd_f, shift_f);
   row_norm_stats(zb, rstd_b, shift_b);
-  float acc_f = 0.f, acc_b = 0.f;
+  float2 acc_f = bc2(0.f), acc_b = bc2(0.f);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int col = i * 256 + lane * 8;
-    float gg[8], bb[8], vv[8];
+    float2 gg[4], bb[4], vv[4];
     ldg_v8_keep(tp.ln_g + col, gg);
     ldg_v8_keep(tp.ln_b + col, bb);
     ldg_v8_keep(tp.v + col, vv);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float yf = gelu_fast(fmaf(fmaf(zf[i * 8 + j], rstd_f, shift_f), gg[j], bb[j]));
-      const float yb = gelu_fast(fmaf(fmaf(zb[i * 8 + j], rstd_b, shift_b), gg[j], bb[j]));
-      if constexpr (FEATS) zf[i * 8 + j] = yf, zb[i * 8 + j] = yb;
-      acc_f = fmaf(yf, vv[j], acc_f);
-      acc_b = fmaf(yb, vv[j], acc_b);
+    for (int j = 0; j < 4; ++j) {
+      const float2 yf = gelu_fast(fma2(fma2(zf[i * 4 + j], bc2(rstd_f), bc2(shift_f)), gg[j], bb[j]));
+      const float2 yb = gelu_fast(fma2(fma2(zb[i * 4 + j], bc2(rstd_b), bc2(shift_b)), gg[j], bb[j]));
+      if constexpr (FEATS) zf[i * 4 + j] = yf, zb[i * 4 + j] = yb;
+      acc_f = fma2(yf, vv[j], acc_f);
+      acc_b = fma2(yb, vv[j], acc_b);
     }
   }
   if constexpr (FEATS) {
     if (g_fwd != nullptr) store_row16<FMT>(g_fwd, lane, zf);
     if (g_bwd != nullptr) store_row16<FMT>(g_bwd, lane, zb);
   }
-  lf = warp_sum(acc_f) + tp.c0;
-  lb = warp_sum(acc_b) + tp.c0;
+  lf = warp_sum(hsum2(acc_f)) + tp.c0;
+  lb = warp_sum(hsum2(acc_b)) + tp.c0;
 }
 
 // 16-bit block fixed-point rows of W_sc sc (gemm::EpiQ16Tma): eight u16 -> floats 2^23 + u (the u16 spliced under
 // the exponent of 2^23 by one PRMT each). value = (2^23 + u - kQ16Bias) * scale; callers fold -kQ16Bias * scale into an
 // fma addend they already have.
 constexpr float kQ16Bias = 8388608.0f + 32768.0f;
-EVI_DEVINL void splice_u16x8(const uint4& q, float (&fb)[8]) {
+EVI_DEVINL void splice_u16x8(const uint4& q, float2 (&fb)[4]) {
   const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
-  for (int j = 0; j < 8; ++j) fb[j] = __uint_as_float(__byte_perm(w[j >> 1], 0x4B000000u, (j & 1) ? 0x7632 : 0x7610));
+  for (int j = 0; j < 4; ++j)
+    fb[j] = make_float2(__uint_as_float(__byte_perm(w[j], 0x4B000000u, 0x7610)),
+                        __uint_as_float(__byte_perm(w[j], 0x4B000000u, 0x7632)));
 }
 
 template <int FMT, bool MM16, bool SQ16>
@@ -740,46 +745,52 @@ score_tail_kernel(const void* __restrict__ mm,                                  
   const float* ph = node_p + static_cast<size_t>(h) * D;
   const float* pt = node_p + static_cast<size_t>(t) * D;
   const float* rq = pair_rq + static_cast<size_t>(ps) * D;
-  float zf[32], zb[32];
+  float2 zf[16], zb[16];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int c = i * 256 + lane * 8;
-    float m[8], a[8], b[8], r[8], wd[8];
+    float2 m[4], a[4], b[4], r[4], wd[4], d[4], dw_f[4], dw_b[4];
     if constexpr (MM16) unpack8<kFmtF16>(ldg_nc_v4(mrow16 + c), m);
     else ldg_v8_stream(mrow + c, m);
     ldg_v8_keep(ph + c, a);
     ldg_v8_keep(pt + c, b);
     ldg_v8_keep(rq + c, r);
     ldg_v8_keep(tp.w_dist + c, wd);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      d[j] = sub2(a[j], b[j]);
+      dw_f[j] = fma2(bc2(sc.z), wd[j], r[j]);
+      dw_b[j] = fma2(bc2(sc.w), wd[j], r[j]);
+    }
     if constexpr (SQ16) {
       if (has_f) {
-        float fb[8];
+        float2 fb[4];
         splice_u16x8(ldg_nc_v4(static_cast<const uint16_t*>(s_fwd) + static_cast<size_t>(e) * D + c), fb);
         const float qs = __ldg(reinterpret_cast<const float*>(s_scale_fwd + e) + i), off = -kQ16Bias * qs;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          zf[i * 8 + j] = fmaf(fb[j], qs, (fmaf(sc.x, m[j], off) + (a[j] - b[j])) + fmaf(sc.z, wd[j], r[j]));
+        for (int j = 0; j < 4; ++j)
+          zf[i * 4 + j] = fma2(fb[j], bc2(qs), add2(add2(fma2(bc2(sc.x), m[j], bc2(off)), d[j]), dw_f[j]));
       }
       if (has_b) {
-        float fb[8];
+        float2 fb[4];
         splice_u16x8(ldg_nc_v4(static_cast<const uint16_t*>(s_bwd) + static_cast<size_t>(e) * D + c), fb);
         const float qs = __ldg(reinterpret_cast<const float*>(s_scale_bwd + e) + i), off = -kQ16Bias * qs;
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          zb[i * 8 + j] = fmaf(fb[j], qs, (fmaf(sc.y, m[j], off) - (a[j] - b[j])) + fmaf(sc.w, wd[j], r[j]));
+        for (int j = 0; j < 4; ++j)
+          zb[i * 4 + j] = fma2(fb[j], bc2(qs), add2(sub2(fma2(bc2(sc.y), m[j], bc2(off)), d[j]), dw_b[j]));
       }
     } else {
       if (has_f) {
-        float s[8];
-        ldg_v8_stream(static_cast<const float*>(s_fwd) + static_cast<size_t>(e) * D + c, s);
+        float2 sv[4];
+        ldg_v8_stream(static_cast<const float*>(s_fwd) + static_cast<size_t>(e) * D + c, sv);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], s[j]) + (a[j] - b[j]) + fmaf(sc.z, wd[j], r[j]);
+        for (int j = 0; j < 4; ++j) zf[i * 4 + j] = add2(add2(fma2(bc2(sc.x), m[j], sv[j]), d[j]), dw_f[j]);
       }
       if (has_b) {
-        float s[8];
-        ldg_v8_stream(static_cast<const float*>(s_bwd) + static_cast<size_t>(e) * D + c, s);
+        float2 sv[4];
+        ldg_v8_stream(static_cast<const float*>(s_bwd) + static_cast<size_t>(e) * D + c, sv);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], s[j]) - (a[j] - b[j]) + fmaf(sc.w, wd[j], r[j]);
+        for (int j = 0; j < 4; ++j) zb[i * 4 + j] = add2(sub2(fma2(bc2(sc.y), m[j], sv[j]), d[j]), dw_b[j]);
       }
     }
   }
@@ -892,50 +903,47 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
     }
     mbar_wait(my_bar, phase);
     phase ^= 1u;
-    float zf[32], zb[32];
+    float2 zf[16], zb[16];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int c = i * 256 + lane * 8;
-      float wd[8];
+      float2 wd[4], m[4], a[4], b[4], r[4], d[4], dw_f[4], dw_b[4];
       ldg_v8_keep(tp.w_dist + c, wd);
-      float m[8];
-      if constexpr (MM16) {
-        unpack8<kFmtF16>(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf) + c), m);
-      } else {
-        const float4 m0 = *reinterpret_cast<const float4*>(buf + c), m1 = *reinterpret_cast<const float4*>(buf + c + 4);
-        m[0] = m0.x, m[1] = m0.y, m[2] = m0.z, m[3] = m0.w, m[4] = m1.x, m[5] = m1.y, m[6] = m1.z, m[7] = m1.w;
+      if constexpr (MM16) unpack8<kFmtF16>(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf) + c), m);
+      else ld_v8(buf + c, m);
+      ld_v8(buf + 3 * D + c, a);
+      ld_v8(buf + 4 * D + c, b);
+      ld_v8(buf + 5 * D + c, r);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        d[j] = sub2(a[j], b[j]);
+        dw_f[j] = fma2(bc2(sc.z), wd[j], r[j]);
+        dw_b[j] = fma2(bc2(sc.w), wd[j], r[j]);
       }
-      const float4 a0 = *reinterpret_cast<const float4*>(buf + 3 * D + c), a1 = *reinterpret_cast<const float4*>(buf + 3 * D + c + 4);
-      const float4 b0 = *reinterpret_cast<const float4*>(buf + 4 * D + c), b1 = *reinterpret_cast<const float4*>(buf + 4 * D + c + 4);
-      const float4 r0 = *reinterpret_cast<const float4*>(buf + 5 * D + c), r1 = *reinterpret_cast<const float4*>(buf + 5 * D + c + 4);
-      const float d[8] = {a0.x - b0.x, a0.y - b0.y, a0.z - b0.z, a0.w - b0.w, a1.x - b1.x, a1.y - b1.y, a1.z - b1.z, a1.w - b1.w};
-      const float r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
       if constexpr (SQ16) {
         // rows of an absent direction are never loaded: their slots hold stale bytes and the results are unused
         const float qf = __shfl_sync(0xffffffffu, qs_lane, i), qb = __shfl_sync(0xffffffffu, qs_lane, 4 + i);
         const float off_f = -kQ16Bias * qf, off_b = -kQ16Bias * qb;
-        float ff[8], fbk[8];
+        float2 ff[4], fbk[4];
         splice_u16x8(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf + 1 * D) + c), ff);
         splice_u16x8(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf + 2 * D) + c), fbk);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          zf[i * 8 + j] = fmaf(ff[j], qf, (fmaf(sc.x, m[j], off_f) + d[j]) + fmaf(sc.z, wd[j], r[j]));
-          zb[i * 8 + j] = fmaf(fbk[j], qb, (fmaf(sc.y, m[j], off_b) - d[j]) + fmaf(sc.w, wd[j], r[j]));
+        for (int j = 0; j < 4; ++j) {
+          zf[i * 4 + j] = fma2(ff[j], bc2(qf), add2(add2(fma2(bc2(sc.x), m[j], bc2(off_f)), d[j]), dw_f[j]));
+          zb[i * 4 + j] = fma2(fbk[j], bc2(qb), add2(sub2(fma2(bc2(sc.y), m[j], bc2(off_b)), d[j]), dw_b[j]));
         }
       } else {
         if (has_f) {
-          const float* sp = buf + 1 * D + c;
-          const float4 s0 = *reinterpret_cast<const float4*>(sp), s1 = *reinterpret_cast<const float4*>(sp + 4);
-          const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+          float2 sv[4];
+          ld_v8(buf + 1 * D + c, sv);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) zf[i * 8 + j] = fmaf(sc.x, m[j], sv[j]) + d[j] + fmaf(sc.z, wd[j], r[j]);
+          for (int j = 0; j < 4; ++j) zf[i * 4 + j] = add2(add2(fma2(bc2(sc.x), m[j], sv[j]), d[j]), dw_f[j]);
         }
         if (has_b) {
-          const float* sp = buf + 2 * D + c;
-          const float4 s0 = *reinterpret_cast<const float4*>(sp), s1 = *reinterpret_cast<const float4*>(sp + 4);
-          const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+          float2 sv[4];
+          ld_v8(buf + 2 * D + c, sv);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) zb[i * 8 + j] = fmaf(sc.y, m[j], sv[j]) - d[j] + fmaf(sc.w, wd[j], r[j]);
+          for (int j = 0; j < 4; ++j) zb[i * 4 + j] = add2(sub2(fma2(bc2(sc.y), m[j], sv[j]), d[j]), dw_b[j]);
         }
       }
     }

@@ -1067,7 +1067,8 @@ def test_unique_entity_rows_bit_identical(dev):
     sd = make_state_dict(6, trained_like=True)
     outs = []
     for uniq in (True, False):
-        m = _table_model(dev, sd, ent, rel, unique_entity_rows=uniq)
+        m = _table_model(dev, sd, ent, rel, unique_entity_rows=uniq, project_entity_table=False)
+        assert not m.uses_projected_table()
         o = m(_ids_batch(qb))
         outs.append((o.logits.clone(), o.logits_fwd.clone(), o.logits_bwd.clone()))
         assert int(m._slot_map.max()) == -1  # the slot map is clean again
@@ -1075,6 +1076,52 @@ def test_unique_entity_rows_bit_identical(dev):
         assert torch.equal(a, b)
     n_unique = len(np.unique(qb.node_embedding_ids))
     assert n_unique < 0.5 * qb.num_nodes  # the case really exercises repeats
+
+
+def test_projected_entity_table_bit_identical(dev):
+    """Entity rows projected once per TABLE row (the default when the projected table fits) give the same bits as the
+    per-batch projection, follow a parameter update, survive invalidation, and report ids outside the table."""
+    spec = tiny_spec(8, 700, seed=53, num_relations=40, num_entities=300)
+    qb = generate_questions(spec)
+    rng = np.random.default_rng(4)
+    ent = (rng.standard_normal((301, 1024)) * 0.5).astype(np.float32)
+    ent[0] = 0
+    rel = (rng.standard_normal((40, 1024)) * 0.5).astype(np.float32)
+    sd = make_state_dict(6, trained_like=True)
+    per_batch = _table_model(dev, sd, ent, rel, project_entity_table=False)
+    table = _table_model(dev, sd, ent, rel)  # auto: 301 rows fit
+    assert table.uses_projected_table() and not per_batch.uses_projected_table()
+    b = _ids_batch(qb)
+
+    def same(x, y):
+        ox, oy = x(b), y(b)
+        return all(torch.equal(p, q) for p, q in ((ox.logits, oy.logits), (ox.logits_fwd, oy.logits_fwd),
+                                                  (ox.logits_bwd, oy.logits_bwd)))
+
+    assert same(per_batch, table)
+    assert table.last_counts["projected_table_rows"] == 301 and table.last_counts["entity_rows"] == 0
+    first = table(b).logits.clone()
+    rows = table._ptable["repr"]
+    table.invalidate_projected_table()
+    assert torch.equal(table(b).logits, first) and table._ptable["repr"] is rows  # rebuilt in the same buffers
+    # a parameter update (as after an optimizer step) re-projects the table: both paths move together
+    with torch.no_grad():
+        for m in (per_batch, table):
+            m.entity_proj.network[0].weight.mul_(0.97)
+            m.non_text_entity_emb.weight.add_(0.01)
+    assert same(per_batch, table)
+    assert not torch.equal(table(b).logits, first)
+    # an embedding id beyond the table is reported like every other out-of-range index
+    bad = _ids_batch(qb)
+    bad.node_embedding_ids = bad.node_embedding_ids.clone()
+    used = int(qb.edge_index[0, 0])  # a node that is an endpoint of an edge
+    bad.node_embedding_ids[used] = 301
+    with pytest.raises(ValueError, match="out of range"):
+        table(bad)
+    bad.node_embedding_ids[used] = -7
+    with pytest.raises(ValueError, match="out of range"):
+        table(bad)
+    assert same(per_batch, table)  # and the flag word is clean again
 
 
 def test_centering_and_single_tables_stay_in_tolerance(dev):
