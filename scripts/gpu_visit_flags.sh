@@ -1,6 +1,7 @@
 #!/usr/bin/env bash
 # One GPU-box visit: parity tests + smoke, then an alternating bench A/B over bench.py flag sets, then the ncu launch
 # list of the default run. Usage (under gpurun): bash scripts/gpu_visit_flags.sh TAG ROUNDS "FLAGS_A" "FLAGS_B" ...
+# A variant may carry environment settings before a '|': "EVI_LIB_PATH=build/other.so | --struct-norm analytic".
 set -uo pipefail
 TAG="$1"; R="$2"; shift 2
 OUT=gpurun_out; mkdir -p "$OUT"
@@ -11,7 +12,9 @@ for r in $(seq 1 "$R"); do
   i=0
   for flags in "$@"; do
     i=$((i+1))
-    timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-other-configs $flags > "$OUT/${TAG}_r${r}_v$i.json" 2> "$OUT/${TAG}_r${r}_v$i.err"
+    envs=""; args="$flags"
+    case "$flags" in *"|"*) envs="${flags%%|*}"; args="${flags#*|}";; esac
+    env $envs timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-other-configs $args > "$OUT/${TAG}_r${r}_v$i.json" 2> "$OUT/${TAG}_r${r}_v$i.err"
     python - "$OUT/${TAG}_r${r}_v$i.json" "v$i [$flags]" <<'PY'
 import json,sys
 try:
