@@ -65,6 +65,7 @@ class RetrievalPipeline:
         self.validate = bool(validate)
         self._out_pinned: Optional[Dict[str, torch.Tensor]] = None
         self._copy_stream = None
+        self._d2h_stream = None
         self._slots = None
         self._slot_free = None
         self._out_slots = None
@@ -173,6 +174,7 @@ class RetrievalPipeline:
         compute = torch.cuda.current_stream(dev)
         if self._copy_stream is None or self._copy_stream.device != dev:
             self._copy_stream = torch.cuda.Stream(device=dev)
+            self._d2h_stream = torch.cuda.Stream(device=dev)
             self._slots = [dict(), dict()]
             self._slot_free = [None, None]
             self._out_slots = [dict(), dict(), dict()]
@@ -206,18 +208,25 @@ class RetrievalPipeline:
             # two more batches have been yielded
             oslot = self._out_slots[i % 3]
             out = {}
-            for k in keys:
-                src = res[k]
-                buf = oslot.get(k)
-                if buf is None or buf.numel() < src.numel() or buf.dtype != src.dtype:
-                    buf = torch.empty(max(1, int(src.numel() * 1.25)), dtype=src.dtype, pin_memory=True)
-                    oslot[k] = buf
-                view = buf[: src.numel()].view(src.shape)
-                view.copy_(src, non_blocking=True)
-                out[k] = view
-            done = torch.cuda.Event()
-            done.record(compute)
-            self._slot_free[i & 1] = done
+            kernels_done = torch.cuda.Event()
+            kernels_done.record(compute)
+            self._slot_free[i & 1] = kernels_done  # the input slot is free once this batch's kernels have run
+            # the ten small device->host copies go to their own stream: the compute stream starts the next batch's
+            # kernels instead of waiting behind the copy engine
+            with torch.cuda.stream(self._d2h_stream):
+                self._d2h_stream.wait_event(kernels_done)
+                for k in keys:
+                    src = res[k]
+                    buf = oslot.get(k)
+                    if buf is None or buf.numel() < src.numel() or buf.dtype != src.dtype:
+                        buf = torch.empty(max(1, int(src.numel() * 1.25)), dtype=src.dtype, pin_memory=True)
+                        oslot[k] = buf
+                    view = buf[: src.numel()].view(src.shape)
+                    src.record_stream(self._d2h_stream)  # the allocator must not hand this block out before the copy ran
+                    view.copy_(src, non_blocking=True)
+                    out[k] = view
+                done = torch.cuda.Event()
+                done.record(self._d2h_stream)
             if pending is not None:
                 yield self._finish(pending)
             pending = (done, out)
