@@ -225,12 +225,6 @@ EVI_DEVINL void ldg_v8_keep(const float* p, float2 (&v)[4]) {
                  "=f"(v[3].y)
                : "l"(p));
 }
-// eight consecutive floats of shared (or generic) memory as four pairs: two 128-bit loads
-EVI_DEVINL void ld_v8(const float* p, float2 (&v)[4]) {
-  const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
-  v[0] = make_float2(a.x, a.y), v[1] = make_float2(a.z, a.w), v[2] = make_float2(b.x, b.y), v[3] = make_float2(b.z, b.w);
-}
-
 // ---------------------------------------------------------------------------------------------
 // mbarrier
 // ---------------------------------------------------------------------------------------------

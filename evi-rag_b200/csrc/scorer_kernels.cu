@@ -634,6 +634,46 @@ struct TailParams {
   float c0;             // w_o . b_2 + b_o
 };
 
+// Which columns of 256-column group i of a 1024-wide row a lane owns (the tail is elementwise per column, so any
+// mapping works as long as every row and parameter vector is read with the same one):
+//   SPLIT4 = false: 8 consecutive columns, c = 256 i + 8 lane — one 256-bit global load per group;
+//   SPLIT4 = true : two runs of 4, c = 256 i + 4 lane and c + 128 — the 32 lanes of a 128-bit shared-memory load then
+//                   cover 512 contiguous bytes. With 8 consecutive floats per lane a quarter-warp's two 128-bit loads put
+//                   lanes k and k + 4 on the same banks: ncu counted 15.6M excess shared wavefronts of 39.1M in the tail
+//                   (profiles/r04e_kernels_ncu.md, memory_l1_wavefronts_shared vs _ideal).
+template <bool SPLIT4>
+struct TailCols {
+  static EVI_DEVINL int col(int i, int lane) { return i * 256 + lane * (SPLIT4 ? 4 : 8); }
+  static constexpr int kSecond = SPLIT4 ? 128 : 4;  // offset of the lane's second run of four columns
+  // eight fp32 values of a shared-memory row as four (even, odd) pairs
+  static EVI_DEVINL void lds_f32(const float* __restrict__ row, int i, int lane, float2 (&v)[4]) {
+    const int c = col(i, lane);
+    const float4 a = *reinterpret_cast<const float4*>(row + c), b = *reinterpret_cast<const float4*>(row + c + kSecond);
+    v[0] = make_float2(a.x, a.y), v[1] = make_float2(a.z, a.w), v[2] = make_float2(b.x, b.y), v[3] = make_float2(b.z, b.w);
+  }
+  // the same eight columns of a global fp32 parameter vector (L1-resident)
+  static EVI_DEVINL void ldg_f32(const float* __restrict__ row, int i, int lane, float2 (&v)[4]) {
+    const int c = col(i, lane);
+    if constexpr (!SPLIT4) {
+      ldg_v8_keep(row + c, v);
+    } else {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(row + c));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(row + c + kSecond));
+      v[0] = make_float2(a.x, a.y), v[1] = make_float2(a.z, a.w), v[2] = make_float2(b.x, b.y), v[3] = make_float2(b.z, b.w);
+    }
+  }
+  // the same eight columns of a 16-bit shared-memory row, packed in column order
+  static EVI_DEVINL uint4 lds_16(const uint16_t* __restrict__ row, int i, int lane) {
+    const int c = col(i, lane);
+    if constexpr (!SPLIT4) {
+      return *reinterpret_cast<const uint4*>(row + c);
+    } else {
+      const uint2 a = *reinterpret_cast<const uint2*>(row + c), b = *reinterpret_cast<const uint2*>(row + c + kSecond);
+      return make_uint4(a.x, a.y, b.x, b.y);
+    }
+  }
+};
+
 // LayerNorm statistics of one pre-activation row spread over the warp: rstd and -mean * rstd
 // (the lane's 32 columns as 16 (even, odd) pairs, see common.cuh)
 EVI_DEVINL void row_norm_stats(const float2 (&z)[16], float& rstd, float& shift) {
@@ -677,20 +717,20 @@ EVI_DEVINL float tail_finish(float2 (&z)[16], const TailParams& tp, int lane, ui
 
 // Both directions of one edge in one pass over the parameter vectors (ln_g, ln_b, v are read once per edge)
 // FEATS = false: the GELU outputs are not stored (no feature path), so they need not be kept in registers
-template <int FMT, bool FEATS = true>
+template <int FMT, bool FEATS = true, bool SPLIT4 = false>
 EVI_DEVINL void tail_finish_pair(float2 (&zf)[16], float2 (&zb)[16], const TailParams& tp, int lane,
                                  uint16_t* __restrict__ g_fwd, uint16_t* __restrict__ g_bwd, float& lf, float& lb) {
+  static_assert(!(FEATS && SPLIT4), "feature rows are stored with 8 consecutive columns per lane");
   float rstd_f, shift_f, rstd_b, shift_b;
   row_norm_stats(zf, rstd_f, shift_f);
   row_norm_stats(zb, rstd_b, shift_b);
   float2 acc_f = bc2(0.f), acc_b = bc2(0.f);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
-    const int col = i * 256 + lane * 8;
     float2 gg[4], bb[4], vv[4];
-    ldg_v8_keep(tp.ln_g + col, gg);
-    ldg_v8_keep(tp.ln_b + col, bb);
-    ldg_v8_keep(tp.v + col, vv);
+    TailCols<SPLIT4>::ldg_f32(tp.ln_g, i, lane, gg);
+    TailCols<SPLIT4>::ldg_f32(tp.ln_b, i, lane, bb);
+    TailCols<SPLIT4>::ldg_f32(tp.v, i, lane, vv);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const float2 yf = gelu_fast(fma2(fma2(zf[i * 4 + j], bc2(rstd_f), bc2(shift_f)), gg[j], bb[j]));
@@ -903,17 +943,17 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
     }
     mbar_wait(my_bar, phase);
     phase ^= 1u;
+    using Cols = TailCols<BIDIR>;  // the default mode reads shared memory without bank conflicts (see TailCols)
     float2 zf[16], zb[16];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const int c = i * 256 + lane * 8;
       float2 wd[4], m[4], a[4], b[4], r[4], d[4], dw_f[4], dw_b[4];
-      ldg_v8_keep(tp.w_dist + c, wd);
-      if constexpr (MM16) unpack8<kFmtF16>(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf) + c), m);
-      else ld_v8(buf + c, m);
-      ld_v8(buf + 3 * D + c, a);
-      ld_v8(buf + 4 * D + c, b);
-      ld_v8(buf + 5 * D + c, r);
+      Cols::ldg_f32(tp.w_dist, i, lane, wd);
+      if constexpr (MM16) unpack8<kFmtF16>(Cols::lds_16(reinterpret_cast<const uint16_t*>(buf), i, lane), m);
+      else Cols::lds_f32(buf, i, lane, m);
+      Cols::lds_f32(buf + 3 * D, i, lane, a);
+      Cols::lds_f32(buf + 4 * D, i, lane, b);
+      Cols::lds_f32(buf + 5 * D, i, lane, r);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         d[j] = sub2(a[j], b[j]);
@@ -925,8 +965,8 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
         const float qf = __shfl_sync(0xffffffffu, qs_lane, i), qb = __shfl_sync(0xffffffffu, qs_lane, 4 + i);
         const float off_f = -kQ16Bias * qf, off_b = -kQ16Bias * qb;
         float2 ff[4], fbk[4];
-        splice_u16x8(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf + 1 * D) + c), ff);
-        splice_u16x8(*reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(buf + 2 * D) + c), fbk);
+        splice_u16x8(Cols::lds_16(reinterpret_cast<const uint16_t*>(buf + 1 * D), i, lane), ff);
+        splice_u16x8(Cols::lds_16(reinterpret_cast<const uint16_t*>(buf + 2 * D), i, lane), fbk);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           zf[i * 4 + j] = fma2(ff[j], bc2(qf), add2(add2(fma2(bc2(sc.x), m[j], bc2(off_f)), d[j]), dw_f[j]));
@@ -935,13 +975,13 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
       } else {
         if (has_f) {
           float2 sv[4];
-          ld_v8(buf + 1 * D + c, sv);
+          Cols::lds_f32(buf + 1 * D, i, lane, sv);
 #pragma unroll
           for (int j = 0; j < 4; ++j) zf[i * 4 + j] = add2(add2(fma2(bc2(sc.x), m[j], sv[j]), d[j]), dw_f[j]);
         }
         if (has_b) {
           float2 sv[4];
-          ld_v8(buf + 2 * D + c, sv);
+          Cols::lds_f32(buf + 2 * D, i, lane, sv);
 #pragma unroll
           for (int j = 0; j < 4; ++j) zb[i * 4 + j] = add2(sub2(fma2(bc2(sc.y), m[j], sv[j]), d[j]), dw_b[j]);
         }
@@ -950,12 +990,15 @@ score_tail_bulk_kernel(const void* __restrict__ mm, const void* __restrict__ s_f
     // every lane has moved its part of the buffer into registers: hand the buffer to the partner's next edge
     __syncwarp();
     if (e_part < num_edges && lane == 0) {
-      fence_proxy_async_all();
+      // the generic-proxy reads of this buffer above are ordered before the async-proxy writes of the next bulk copies;
+      // only shared memory is involved (the global rows were written by earlier launches), so the shared::cta form of
+      // the fence is enough (the state-space-wide form showed up as 0.7 warps per scheduler stalled on membar)
+      fence_proxy_async_smem();
       issue(partner_bar, e_part, hn, tn, pn);
     }
     float lf = 0.f, lb = 0.f;
     if constexpr (BIDIR)  // both directions, logits only
-      tail_finish_pair<FMT, false>(zf, zb, tp, lane, nullptr, nullptr, lf, lb);
+      tail_finish_pair<FMT, false, true>(zf, zb, tp, lane, nullptr, nullptr, lf, lb);
     else if (has_f && has_b)
       tail_finish_pair<FMT>(zf, zb, tp, lane, g_fwd ? g_fwd + static_cast<size_t>(e) * 2 * D : nullptr,
                             g_bwd ? g_bwd + static_cast<size_t>(e) * 2 * D : nullptr, lf, lb);

@@ -14,7 +14,7 @@ for r in $(seq 1 "$R"); do
     i=$((i+1))
     envs=""; args="$flags"
     case "$flags" in *"|"*) envs="${flags%%|*}"; args="${flags#*|}";; esac
-    env $envs timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-other-configs $args > "$OUT/${TAG}_r${r}_v$i.json" 2> "$OUT/${TAG}_r${r}_v$i.err"
+    env $envs timeout 600 python bench.py --steps ${STEPS:-10} --warmup 3 --no-cpu-baseline --no-other-configs $args > "$OUT/${TAG}_r${r}_v$i.json" 2> "$OUT/${TAG}_r${r}_v$i.err"
     python - "$OUT/${TAG}_r${r}_v$i.json" "v$i [$flags]" <<'PY'
 import json,sys
 try:

@@ -847,8 +847,10 @@ def test_retriever_loss_degenerate_and_errors(dev, golden_dir):
 
 
 def test_overlapped_chunk_pipeline_equals_serial(dev):
-    """The two-stream chunk pipeline of evi_score_edges (GEMMs of chunk c beside tail c-1 / operand c+1) is the same
-    kernels on the same data: logits must be bit-identical to the serial order."""
+    """The two-stream chunk pipeline of evi_score_edges (GEMMs of chunk c beside tail c-1 / operand c+1) runs the same
+    GEMMs and operand kernel on the same data; its tail is the register-fed kernel (no shared memory, fits beside the
+    GEMM CTAs), whose lanes own 8 consecutive columns where the bulk-copy tail's lanes own two runs of 4 (TailCols):
+    the LayerNorm sums are taken in a different order, so the logits agree to fp32 rounding, not bit for bit."""
     import types
 
     spec = tiny_spec(24, 4000, seed=9, num_relations=64, num_entities=3000)
@@ -875,7 +877,8 @@ def test_overlapped_chunk_pipeline_equals_serial(dev):
         assert qb.num_edges > 4 * 16384  # really several chunks
         outs.append((out.logits.clone(), out.logits_fwd.clone(), out.logits_bwd.clone()))
     for a, b in zip(*outs):
-        assert torch.equal(a, b)
+        err = float((a.double() - b.double()).abs().max()) / float(a.abs().max())
+        assert err <= 2e-6, err
 
 
 # ------------------------------------------------------------------ full-size properties (BASELINE config[1] step)
