@@ -16,7 +16,9 @@ What differs (B200 design):
     the per-edge ones over single 16-bit rows with the structure context centred on its batch mean
     (``precision="fast"``, scores within ~3e-4 of the fp32 reference) or over pairs as well
     (``precision="strict"``, ~2e-5, about twice the time);
-  * entity rows are projected once per distinct ``node_embedding_id`` of the batch;
+  * entity rows are projected once per row of the attached entity table and checkpoint
+    (``project_entity_table``), or once per distinct ``node_embedding_id`` of the batch when that
+    table would not fit;
   * with ``attach_embedding_tables`` the 1024-d text-embedding tables live in HBM and a batch only
     needs ids (``node_embedding_ids``, ``edge_attr``) — the reference's per-edge CPU gather + H2D
     of ``edge_embeddings`` (``src/data/components/embedding_store.py:101-150``) disappears;
