@@ -22,6 +22,7 @@ enum Status : int {
   kErrCuda = 2,
   kErrWorkspace = 3,
   kErrUnsupported = 4,
+  kErrStaticLimit = 5,  // a size beyond the fixed scratch of a *_static entry point
 };
 
 // bits of the device-side validation word written by evi_edge_batch (graph_utils.py:58-99)

@@ -565,6 +565,44 @@ int evi_dde_forward(const int* head32, const int* tail32, long long num_edges, i
   return check_launch();
 }
 
+// ---------------------------------------------------------------------------------------------
+// evi_dde_forward for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc): the same kernels with the propagation scratch (accumulators, degrees, per-round states) in a
+// file-scope device array instead of a caller-supplied workspace. No counterpart in the
+// reference.
+//   * the array is sized for EVI_DDE_STATIC_MAX_NODES nodes (56 bytes per node + 256 = 14 MiB); every GPU that
+//     loads the library holds it until the process exits;
+//   * in host code `g_dde_static_scratch` is a host-side stand-in, not a device address: the address the kernels get
+//     comes from cudaGetSymbolAddress, taken once per device with that device current;
+//   * every call shares the array, which keeps the previous call's contents: the accumulators and degrees are cleared
+//     on the stream at the start of each call (the per-round states are written before they are read); two calls that
+//     overlap on one GPU (different streams) race on it.
+// ---------------------------------------------------------------------------------------------
+constexpr size_t kDdeStaticBytes = static_cast<size_t>(EVI_DDE_STATIC_MAX_NODES) * 56 + 256;
+static __device__ __align__(256) unsigned char g_dde_static_scratch[kDdeStaticBytes];
+constexpr int kMaxDevices = 64;
+static std::atomic<void*> g_dde_static_addr[kMaxDevices];
+
+int evi_dde_static_max_nodes(void) { return EVI_DDE_STATIC_MAX_NODES; }
+
+int evi_dde_forward_static(const int* head32, const int* tail32, long long num_edges, int num_nodes,
+                           const float* topic_one_hot, int ld_topic, int num_rounds, int num_reverse_rounds,
+                           float* node_struct, cudaStream_t stream) {
+  if (num_nodes <= 0) return kOk;
+  if (num_nodes > EVI_DDE_STATIC_MAX_NODES) return kErrStaticLimit;  // beyond the static scratch: use evi_dde_forward
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) return kErrCuda;
+  if (dev < 0 || dev >= kMaxDevices) return kErrUnsupported;
+  void* scratch = g_dde_static_addr[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {  // once per device, with that device current (concurrent first calls get the same address)
+    if (cudaGetSymbolAddress(&scratch, g_dde_static_scratch) != cudaSuccess || scratch == nullptr) return kErrCuda;
+    g_dde_static_addr[dev].store(scratch, std::memory_order_release);
+  }
+  // evi_dde_forward clears acc / deg with cudaMemsetAsync on `stream` and allocates nothing
+  return evi_dde_forward(head32, tail32, num_edges, num_nodes, topic_one_hot, ld_topic, num_rounds, num_reverse_rounds,
+                         node_struct, scratch, kDdeStaticBytes, stream);
+}
+
 int evi_build_csr(const int* head32, const int* tail32, long long num_edges, int num_nodes, int mode,
                   int* row_ptr, int* adj, int* scratch_counts, cudaStream_t stream) {
   if (num_nodes < 0 || mode < 0 || mode > 2) return kErrInvalidArg;

@@ -14,7 +14,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("EVI_LIB_PATH") or os.path.join(_HERE, "libevi_rag_b200.so")
 
 EVI_OK = 0
-_STATUS = {1: "invalid argument", 2: "CUDA error", 3: "workspace too small", 4: "unsupported shape"}
+_STATUS = {1: "invalid argument", 2: "CUDA error", 3: "workspace too small", 4: "unsupported shape",
+           5: "size exceeds the fixed scratch of a *_static entry point (use the workspace form)"}
+EVI_ERR_STATIC_LIMIT = 5
 
 FLAG_OUT_OF_RANGE, FLAG_CROSS_GRAPH, FLAG_NOT_MONOTONE = 1, 2, 4
 FMT_F16, FMT_BF16 = 0, 1
@@ -95,6 +97,8 @@ PROTOTYPES = {
     "evi_edge_batch": (_i, [_vp, _ll, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "evi_dde_workspace_bytes": (_sz, [_i]),
     "evi_dde_forward": (_i, [_vp, _vp, _ll, _i, _vp, _i, _i, _i, _vp, _vp, _sz, _vp]),
+    "evi_dde_static_max_nodes": (_i, []),
+    "evi_dde_forward_static": (_i, [_vp, _vp, _ll, _i, _vp, _i, _i, _i, _vp, _vp]),
     "evi_build_csr": (_i, [_vp, _vp, _ll, _i, _i, _vp, _vp, _vp, _vp]),
     "evi_bfs_multi_source": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp]),
     "evi_bfs_edge_sweep": (_i, [_vp, _vp, _i] + [_vp] * 7 + [_i, _i, _i, _vp, _vp]),
@@ -140,6 +144,7 @@ _lib: Optional[C.CDLL] = None
 _KERNELS_PER_CALL = {
     "evi_edge_batch": lambda a: (2 if a[8] else 1) if a[1] > 0 else 1,
     "evi_dde_forward": lambda a: 1 + (2 if a[2] > 0 else 1) * max(a[6], a[7]),
+    "evi_dde_forward_static": lambda a: 1 + (2 if a[2] > 0 else 1) * max(a[6], a[7]),
     "evi_build_csr": lambda a: 3 if a[2] > 0 else 1,
     "evi_bfs_multi_source": lambda a: 1,
     "evi_bfs_edge_sweep": lambda a: 1,

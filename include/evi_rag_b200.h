@@ -8,7 +8,8 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns all memory
- *   - the library keeps no global state and allocates nothing; all work is enqueued on `stream`
+ *   - the library keeps no global state (one exception: the fixed scratch of evi_dde_forward_static) and allocates
+ *     nothing; all work is enqueued on `stream`
  *   - return value: EVI_OK or an EVI_ERR_* code; data-dependent validation failures are
  *     reported through a device-side `flags` word (EVI_FLAG_* bits) that the caller reads back
  *   - operand_format: EVI_FMT_F16 / EVI_FMT_BF16 — the 16-bit tensor-core operand type
@@ -28,6 +29,7 @@ extern "C" {
 #define EVI_ERR_CUDA 2
 #define EVI_ERR_WORKSPACE 3
 #define EVI_ERR_UNSUPPORTED 4
+#define EVI_ERR_STATIC_LIMIT 5 /* a size beyond the fixed scratch of a *_static entry point: use the workspace form */
 
 #define EVI_FLAG_OUT_OF_RANGE 1u /* graph_utils.py:66-77, retriever.py:594-604 */
 #define EVI_FLAG_CROSS_GRAPH 2u  /* graph_utils.py:78-88 */
@@ -69,6 +71,20 @@ size_t evi_dde_workspace_bytes(int num_nodes);
 int evi_dde_forward(const int* head32, const int* tail32, long long num_edges, int num_nodes,
                     const float* topic_one_hot, int ld_topic, int num_rounds, int num_reverse_rounds,
                     float* node_struct, void* workspace, size_t workspace_bytes, cudaStream_t stream);
+
+/* evi_dde_forward without a workspace argument, for callers that cannot allocate one (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+ * Same kernels, same results; the propagation scratch is a file-scope device array of
+ * EVI_DDE_STATIC_MAX_NODES * 56 + 256 bytes (14 MiB) that every GPU which loads the library holds until the process
+ * exits. num_nodes > EVI_DDE_STATIC_MAX_NODES returns EVI_ERR_STATIC_LIMIT (nothing is launched). The call allocates
+ * nothing (no cudaMalloc / cudaFree; the array's device address is looked up once per device). All calls share the
+ * array: it keeps the previous call's contents (what must start at zero is cleared on `stream` by every call), and two
+ * calls that overlap on one GPU race on it — serialise them on one stream. This is the library's only global state. */
+#define EVI_DDE_STATIC_MAX_NODES 262144
+int evi_dde_static_max_nodes(void);
+int evi_dde_forward_static(const int* head32, const int* tail32, long long num_edges, int num_nodes,
+                           const float* topic_one_hot, int ld_topic, int num_rounds, int num_reverse_rounds,
+                           float* node_struct, cudaStream_t stream);
 
 /* _build_undirected_adjacency / _build_directed_adjacency —
  * scripts/build_retrieval_pipeline.py:570-603, as CSR. mode 0 undirected, 1 head->tail,
