@@ -23,6 +23,8 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(L, name), f"{name} declared in include/evi_rag_b200.h but not exported"
     assert declared == set(lib.PROTOTYPES), declared ^ set(lib.PROTOTYPES)
     assert L.evi_abi_version() == 5
+    limit = re.search(r"#define EVI_DDE_STATIC_MAX_NODES (\d+)", header)
+    assert limit and L.evi_dde_static_max_nodes() == int(limit.group(1)) == 262144  # the static-scratch entry's stated limit
     assert L.evi_score_workspace_bytes(1000, lib.DIR_BIDIRECTIONAL, 0) >= 1000 * 1024 * (2 + 4 + 4 + 8)
 
 
